@@ -1,0 +1,672 @@
+// vgs_capi.cu -- the C ABI of libvgpuscore.so (include/vgpuscore.h): context, device
+// memory, request packing, kernel sequencing.  No CPU fallback anywhere: every scoring
+// entry point ends in a kernel launch or an error code.
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/vgpuscore.h"
+#include "vgs_kernels.h"
+#include "vgs_layout.h"
+
+using namespace vgs;
+
+namespace {
+
+enum { EV_UP0, EV_UP1, EV_DR1, EV_PH0, EV_PH1, EV_SC0, EV_SC1, EV_RS0, EV_RS1, EV_DH0, EV_DH1, EV_N };
+
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = false;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+        ok = cudaSetDevice(dev) == cudaSuccess;
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
+} // namespace
+
+struct vgs_ctx {
+    vgs_config cfg{};
+    int dm = 8;
+    cudaStream_t st = nullptr;
+    bool own_stream = false;
+    std::mutex mu;
+    std::string err;
+
+    // snapshot
+    int32_t *d_raw[VGS_NUM_PLANES] = {};
+    int32_t *d_ndev = nullptr;
+    int4 *d_walk = nullptr;
+    uint32_t *d_status = nullptr;
+    uint32_t *h_status = nullptr; // pinned
+    int32_t n_nodes = 0, dmax = 0, n_tiles = 0;
+    bool have_snapshot = false;
+    uint64_t version = 0;
+    vgs_delta *d_deltas = nullptr, *h_deltas = nullptr;
+    int32_t *d_rowlist = nullptr;
+    int32_t max_deltas = 0;
+
+    // pod batch
+    unsigned char *h_stage = nullptr, *d_stage = nullptr; // one block, carved below
+    size_t stage_bytes = 0;
+    size_t off_reqs = 0, off_pods = 0, off_pick = 0, off_reqsA = 0, off_origA = 0, off_reqsB = 0,
+           off_origB = 0, off_podsG = 0;
+    int32_t n_pods = 0, n_reqs = 0, nA = 0, nB = 0, nG = 0, n_picks = 0;
+    bool have_pods = false, scored = false, resolved = false;
+
+    // results
+    unsigned long long *d_keys = nullptr;
+    int32_t *d_counts = nullptr;
+    vgs_result *d_results = nullptr, *h_results = nullptr;
+    vgs_pick *d_picks = nullptr, *h_picks = nullptr;
+    uint32_t *d_vfit = nullptr;
+    float *d_vscore = nullptr;
+    int32_t vwords = 0;
+
+    cudaEvent_t ev[EV_N] = {};
+    bool ev_set[EV_N] = {};
+    long long launches = 0;
+};
+
+namespace {
+
+int fail_cuda(vgs_ctx *c, cudaError_t e, const char *what) {
+    char buf[512];
+    snprintf(buf, sizeof buf, "%s: %s", what, cudaGetErrorString(e));
+    if (c) c->err = buf;
+    return VGS_ECUDA;
+}
+int fail(vgs_ctx *c, int code, const char *what) {
+    if (c) c->err = what;
+    return code;
+}
+#define CU(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e__ = (call);                                                                  \
+        if (e__ != cudaSuccess) return fail_cuda(c, e__, #call);                                   \
+    } while (0)
+
+void rec(vgs_ctx *c, int which) {
+    cudaEventRecord(c->ev[which], c->st);
+    c->ev_set[which] = true;
+}
+
+size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+RawPlanes raw_const(const vgs_ctx *c) {
+    RawPlanes r;
+    for (int f = 0; f < VGS_NUM_PLANES; f++) r.p[f] = c->d_raw[f];
+    r.ndev = c->d_ndev;
+    return r;
+}
+
+int check_status(vgs_ctx *c) {
+    // d_status -> pinned word; stream must be synchronised by the caller afterwards
+    uint32_t s = *c->h_status;
+    if (s & S_NDEV) return fail(c, VGS_EDMAX, "ndev outside [0, dmax]");
+    if (s & S_TYPE) return fail(c, VGS_ERANGE, "type id outside [0, VGS_MAX_TYPES)");
+    if (s & S_RANGE) return fail(c, VGS_ERANGE, "Count/Used outside [0, VGS_MAX_SHARE)");
+    if (s & S_DELTA) return fail(c, VGS_EINVAL, "delta names a slot the node does not have");
+    if (s & S_MISMATCH) return fail(c, VGS_EINTERNAL, "resolve kernel disagrees with score kernel");
+    return VGS_OK;
+}
+
+int pull_status(vgs_ctx *c) {
+    CU(cudaMemcpyAsync(c->h_status, c->d_status, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->st));
+    CU(cudaStreamSynchronize(c->st));
+    int rc = check_status(c);
+    if (rc != VGS_OK) cudaMemsetAsync(c->d_status, 0, sizeof(uint32_t), c->st);
+    return rc;
+}
+
+int prepare_all(vgs_ctx *c) {
+    CU(launch_prepare(c->dm, raw_const(c), c->n_nodes, c->dmax, c->d_walk, c->n_tiles, c->d_status,
+                      nullptr, 0, c->st));
+    c->launches++;
+    return VGS_OK;
+}
+
+void free_all(vgs_ctx *c) {
+    for (int f = 0; f < VGS_NUM_PLANES; f++) cudaFree(c->d_raw[f]);
+    cudaFree(c->d_ndev);
+    cudaFree(c->d_walk);
+    cudaFree(c->d_status);
+    cudaFreeHost(c->h_status);
+    cudaFree(c->d_deltas);
+    cudaFreeHost(c->h_deltas);
+    cudaFree(c->d_rowlist);
+    cudaFree(c->d_stage);
+    cudaFreeHost(c->h_stage);
+    cudaFree(c->d_keys);
+    cudaFree(c->d_counts);
+    cudaFree(c->d_results);
+    cudaFreeHost(c->h_results);
+    cudaFree(c->d_picks);
+    cudaFreeHost(c->h_picks);
+    cudaFree(c->d_vfit);
+    cudaFree(c->d_vscore);
+    for (int i = 0; i < EV_N; i++)
+        if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+    if (c->own_stream && c->st) cudaStreamDestroy(c->st);
+}
+
+} // namespace
+
+extern "C" {
+
+int vgs_abi_version(void) { return VGS_ABI_VERSION; }
+
+const char *vgs_strerror(int status) {
+    switch (status) {
+    case VGS_OK: return "ok";
+    case VGS_EINVAL: return "invalid argument";
+    case VGS_ECUDA: return "CUDA error";
+    case VGS_ETOOBIG: return "exceeds the capacity given to vgs_init";
+    case VGS_EDMAX: return "more devices per node than supported";
+    case VGS_ERANGE: return "snapshot value out of range";
+    case VGS_ESTATE: return "call sequence error";
+    case VGS_EINTERNAL: return "internal self-check failed";
+    default: return "unknown status";
+    }
+}
+
+const char *vgs_last_error(vgs_ctx *c) { return c ? c->err.c_str() : ""; }
+
+int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
+    if (!cfg || !out) return VGS_EINVAL;
+    *out = nullptr;
+    if (cfg->max_nodes < 1 || cfg->max_pods < 1 || cfg->max_reqs < cfg->max_pods ||
+        cfg->max_picks < cfg->max_reqs || cfg->max_devices < 1)
+        return VGS_EINVAL;
+    if (cfg->max_devices > VGS_MAX_DEVICES) return VGS_EDMAX;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) return VGS_ECUDA; // no GPU, no fallback
+    if (cfg->device < 0 || cfg->device >= ndev) return VGS_EINVAL;
+    vgs_ctx *c = new (std::nothrow) vgs_ctx();
+    if (!c) return VGS_EINVAL;
+    c->cfg = *cfg;
+    c->dm = walk_dm(cfg->max_devices);
+    DeviceGuard g(cfg->device);
+    auto bail = [&](int rc) {
+        free_all(c);
+        delete c;
+        return rc;
+    };
+#define CUI(call)                                                                                  \
+    do {                                                                                           \
+        if ((call) != cudaSuccess) return bail(VGS_ECUDA);                                         \
+    } while (0)
+    if (!g.ok) return bail(VGS_ECUDA);
+    if (cfg->stream) {
+        c->st = (cudaStream_t)cfg->stream;
+    } else {
+        CUI(cudaStreamCreateWithFlags(&c->st, cudaStreamNonBlocking));
+        c->own_stream = true;
+    }
+    for (int i = 0; i < EV_N; i++) CUI(cudaEventCreate(&c->ev[i]));
+    const size_t cells = (size_t)cfg->max_nodes * cfg->max_devices;
+    for (int f = 0; f < VGS_NUM_PLANES; f++) CUI(cudaMalloc(&c->d_raw[f], cells * sizeof(int32_t)));
+    CUI(cudaMalloc(&c->d_ndev, (size_t)cfg->max_nodes * sizeof(int32_t)));
+    const size_t max_tiles = ((size_t)cfg->max_nodes + kWarp - 1) / kWarp;
+    CUI(cudaMalloc(&c->d_walk, max_tiles * walk_int4_per_tile(c->dm) * sizeof(int4)));
+    CUI(cudaMalloc(&c->d_status, sizeof(uint32_t)));
+    CUI(cudaMemset(c->d_status, 0, sizeof(uint32_t)));
+    CUI(cudaMallocHost(&c->h_status, sizeof(uint32_t)));
+    c->max_deltas = 4096;
+    CUI(cudaMalloc(&c->d_deltas, c->max_deltas * sizeof(vgs_delta)));
+    CUI(cudaMallocHost(&c->h_deltas, c->max_deltas * sizeof(vgs_delta)));
+    CUI(cudaMalloc(&c->d_rowlist, c->max_deltas * sizeof(int32_t)));
+
+    // pod staging block: [reqs][pods][pick_begin][reqsA][origA][reqsB][origB][podsG]
+    const size_t P = cfg->max_pods, R = cfg->max_reqs;
+    size_t o = 0;
+    c->off_reqs = o, o = align_up(o + R * sizeof(DevReq), 256);
+    c->off_pods = o, o = align_up(o + P * sizeof(vgs_pod), 256);
+    c->off_pick = o, o = align_up(o + (R + 1) * sizeof(int32_t), 256);
+    c->off_reqsA = o, o = align_up(o + P * sizeof(DevReq), 256);
+    c->off_origA = o, o = align_up(o + P * sizeof(int32_t), 256);
+    c->off_reqsB = o, o = align_up(o + P * sizeof(DevReq), 256);
+    c->off_origB = o, o = align_up(o + P * sizeof(int32_t), 256);
+    c->off_podsG = o, o = align_up(o + P * sizeof(GenPod), 256);
+    c->stage_bytes = o;
+    CUI(cudaMalloc(&c->d_stage, o));
+    CUI(cudaMallocHost(&c->h_stage, o));
+
+    CUI(cudaMalloc(&c->d_keys, P * sizeof(unsigned long long)));
+    CUI(cudaMalloc(&c->d_counts, P * sizeof(int32_t)));
+    CUI(cudaMalloc(&c->d_results, P * sizeof(vgs_result)));
+    CUI(cudaMallocHost(&c->h_results, P * sizeof(vgs_result)));
+    CUI(cudaMalloc(&c->d_picks, (size_t)cfg->max_picks * sizeof(vgs_pick)));
+    CUI(cudaMallocHost(&c->h_picks, (size_t)cfg->max_picks * sizeof(vgs_pick)));
+    if (cfg->verify) {
+        c->vwords = (int32_t)max_tiles;
+        CUI(cudaMalloc(&c->d_vfit, P * max_tiles * sizeof(uint32_t)));
+        CUI(cudaMalloc(&c->d_vscore, P * (size_t)cfg->max_nodes * sizeof(float)));
+    }
+#undef CUI
+    *out = c;
+    return VGS_OK;
+}
+
+void vgs_destroy(vgs_ctx *c) {
+    if (!c) return;
+    {
+        DeviceGuard g(c->cfg.device);
+        cudaStreamSynchronize(c->st);
+        free_all(c);
+    }
+    delete c;
+}
+
+static int snapshot_common(vgs_ctx *c, int32_t n_nodes, int32_t dmax,
+                           const int32_t *const planes[VGS_NUM_PLANES], const int32_t *ndev,
+                           cudaMemcpyKind kind, uint64_t *out_version) {
+    if (!planes || !ndev) return fail(c, VGS_EINVAL, "null planes");
+    if (n_nodes < 0 || dmax < 1) return fail(c, VGS_EINVAL, "bad snapshot shape");
+    if (dmax > VGS_MAX_DEVICES) return fail(c, VGS_EDMAX, "dmax > VGS_MAX_DEVICES");
+    if (n_nodes > c->cfg.max_nodes || dmax > c->cfg.max_devices)
+        return fail(c, VGS_ETOOBIG, "snapshot larger than vgs_init capacity");
+    for (int f = 0; f < VGS_NUM_PLANES; f++)
+        if (!planes[f]) return fail(c, VGS_EINVAL, "null plane");
+    c->have_snapshot = false;
+    c->scored = c->resolved = false;
+    const size_t cells = (size_t)n_nodes * dmax;
+    rec(c, EV_UP0);
+    if (cells) {
+        for (int f = 0; f < VGS_NUM_PLANES; f++)
+            CU(cudaMemcpyAsync(c->d_raw[f], planes[f], cells * sizeof(int32_t), kind, c->st));
+        CU(cudaMemcpyAsync(c->d_ndev, ndev, (size_t)n_nodes * sizeof(int32_t), kind, c->st));
+    }
+    rec(c, EV_UP1);
+    c->n_nodes = n_nodes;
+    c->dmax = dmax;
+    c->n_tiles = (n_nodes + kWarp - 1) / kWarp;
+    int rc = prepare_all(c);
+    if (rc != VGS_OK) return rc;
+    rec(c, EV_DR1);
+    rc = pull_status(c);
+    if (rc != VGS_OK) return rc;
+    c->have_snapshot = true;
+    c->version++;
+    if (out_version) *out_version = c->version;
+    return VGS_OK;
+}
+
+int vgs_snapshot_upload(vgs_ctx *c, int32_t n_nodes, int32_t dmax,
+                        const int32_t *const planes[VGS_NUM_PLANES], const int32_t *ndev,
+                        uint64_t *out_version) {
+    if (!c) return VGS_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard g(c->cfg.device);
+    return snapshot_common(c, n_nodes, dmax, planes, ndev, cudaMemcpyHostToDevice, out_version);
+}
+
+int vgs_snapshot_set_device(vgs_ctx *c, int32_t n_nodes, int32_t dmax,
+                            const int32_t *const dev_planes[VGS_NUM_PLANES], const int32_t *dev_ndev,
+                            uint64_t *out_version) {
+    if (!c) return VGS_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard g(c->cfg.device);
+    return snapshot_common(c, n_nodes, dmax, dev_planes, dev_ndev, cudaMemcpyDeviceToDevice, out_version);
+}
+
+int vgs_snapshot_delta(vgs_ctx *c, int32_t n, const vgs_delta *deltas) {
+    if (!c) return VGS_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard g(c->cfg.device);
+    if (!c->have_snapshot) return fail(c, VGS_ESTATE, "delta before snapshot upload");
+    if (n < 0 || (n > 0 && !deltas)) return fail(c, VGS_EINVAL, "bad delta list");
+    c->scored = c->resolved = false;
+    RawPlanesMut rm;
+    for (int f = 0; f < VGS_NUM_PLANES; f++) rm.p[f] = c->d_raw[f];
+    rm.ndev = c->d_ndev;
+    for (int32_t done = 0; done < n;) {
+        int32_t m = n - done < c->max_deltas ? n - done : c->max_deltas;
+        CU(cudaStreamSynchronize(c->st)); // staging buffer reuse
+        memcpy(c->h_deltas, deltas + done, (size_t)m * sizeof(vgs_delta));
+        CU(cudaMemcpyAsync(c->d_deltas, c->h_deltas, (size_t)m * sizeof(vgs_delta),
+                           cudaMemcpyHostToDevice, c->st));
+        CU(launch_delta(rm, c->n_nodes, c->dmax, c->cfg.row_base, c->d_deltas, m, c->d_rowlist,
+                        c->d_status, c->st));
+        CU(launch_prepare(c->dm, raw_const(c), c->n_nodes, c->dmax, c->d_walk, c->n_tiles, c->d_status,
+                          c->d_rowlist, m, c->st));
+        c->launches += 2;
+        done += m;
+    }
+    int rc = pull_status(c);
+    if (rc != VGS_OK) {
+        c->have_snapshot = false; // planes may hold out-of-range values now
+        return rc;
+    }
+    c->version++;
+    return VGS_OK;
+}
+
+int vgs_snapshot_download(vgs_ctx *c, int32_t *const planes[VGS_NUM_PLANES], int32_t *ndev) {
+    if (!c || !planes || !ndev) return VGS_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard g(c->cfg.device);
+    if (!c->have_snapshot) return fail(c, VGS_ESTATE, "no snapshot");
+    const size_t cells = (size_t)c->n_nodes * c->dmax;
+    if (cells) {
+        for (int f = 0; f < VGS_NUM_PLANES; f++)
+            CU(cudaMemcpyAsync(planes[f], c->d_raw[f], cells * sizeof(int32_t), cudaMemcpyDeviceToHost, c->st));
+        CU(cudaMemcpyAsync(ndev, c->d_ndev, (size_t)c->n_nodes * sizeof(int32_t), cudaMemcpyDeviceToHost, c->st));
+    }
+    CU(cudaStreamSynchronize(c->st));
+    return VGS_OK;
+}
+
+// ---- pod batch ---------------------------------------------------------------------
+
+static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_reqs,
+                              const vgs_req *reqs) {
+    if (n_pods < 0 || n_reqs < 0 || (n_pods > 0 && (!pods || !reqs)))
+        return fail(c, VGS_EINVAL, "bad pod batch");
+    if (n_pods > c->cfg.max_pods || n_reqs > c->cfg.max_reqs)
+        return fail(c, VGS_ETOOBIG, "pod batch larger than vgs_init capacity");
+    c->have_pods = false;
+    c->scored = c->resolved = false;
+    // the staging block may still be the source of an earlier async copy
+    CU(cudaStreamSynchronize(c->st));
+    DevReq *hreq = reinterpret_cast<DevReq *>(c->h_stage + c->off_reqs);
+    vgs_pod *hpod = reinterpret_cast<vgs_pod *>(c->h_stage + c->off_pods);
+    int32_t *hpick = reinterpret_cast<int32_t *>(c->h_stage + c->off_pick);
+    DevReq *hA = reinterpret_cast<DevReq *>(c->h_stage + c->off_reqsA);
+    int32_t *hoA = reinterpret_cast<int32_t *>(c->h_stage + c->off_origA);
+    DevReq *hB = reinterpret_cast<DevReq *>(c->h_stage + c->off_reqsB);
+    int32_t *hoB = reinterpret_cast<int32_t *>(c->h_stage + c->off_origB);
+    GenPod *hG = reinterpret_cast<GenPod *>(c->h_stage + c->off_podsG);
+
+    int64_t picks = 0;
+    for (int32_t r = 0; r < n_reqs; r++) {
+        const vgs_req &q = reqs[r];
+        if (q.nums < 1) return fail(c, VGS_EINVAL, "request with Nums < 1 (k8sutil/pod.go:33 drops those)");
+        DevReq d;
+        d.nums = q.nums;
+        d.memfix = q.memreq > 0 ? q.memreq : 0;                            // score.go:114-116
+        d.pct = q.mempct;
+        d.coresreq = q.coresreq;
+        d.flags = 0;
+        if (q.mempct != VGS_MEMPCT_UNSET && q.memreq == 0) d.flags |= R_USEPCT; // score.go:117
+        if (q.flags & VGS_REQ_NUMA_BIND) d.flags |= R_NUMA;
+        d.blockmask = M_NOFREE | M_PAD;
+        if (q.coresreq == 100) d.blockmask |= M_EXCL; // score.go:128
+        if (q.coresreq == 0) d.blockmask |= M_FULL;   // score.go:132
+        if (q.coresreq > 100) d.blockmask |= M_ALWAYS; // score.go:110-113: never fits
+        d.mask_lo = (uint32_t)q.typemask;
+        d.mask_hi = (uint32_t)(q.typemask >> 32);
+        hreq[r] = d;
+        hpick[r] = (int32_t)picks;
+        picks += q.nums;
+        if (picks > c->cfg.max_picks) return fail(c, VGS_ETOOBIG, "sum of nums exceeds max_picks");
+    }
+    hpick[n_reqs] = (int32_t)picks;
+
+    int32_t nA = 0, nB = 0, nG = 0;
+    for (int32_t p = 0; p < n_pods; p++) {
+        const vgs_pod &pd = pods[p];
+        if (pd.n_reqs < 1 || pd.n_reqs > VGS_MAX_REQS_PER_POD || pd.req_begin < 0 ||
+            (int64_t)pd.req_begin + pd.n_reqs > n_reqs)
+            return fail(c, VGS_EINVAL,
+                        "pod without requests or with a bad request range (Filter short-circuits "
+                        "pods that request nothing, scheduler.go:357-370)");
+        int32_t prev = -1;
+        for (int32_t r = pd.req_begin; r < pd.req_begin + pd.n_reqs; r++) {
+            if (reqs[r].ctr < prev || reqs[r].ctr < 0) return fail(c, VGS_EINVAL, "container index not monotone");
+            if (reqs[r].ctr != prev) hreq[r].flags |= R_NEWCTR;
+            prev = reqs[r].ctr;
+        }
+        hpod[p] = pd;
+        const DevReq &first = hreq[pd.req_begin];
+        if (pd.n_reqs == 1 && first.nums == 1) {
+            hA[nA] = first; // numa-bind cannot matter for a single device
+            hoA[nA++] = p;
+        } else if (pd.n_reqs == 1 && !(first.flags & R_NUMA)) {
+            hB[nB] = first;
+            hoB[nB++] = p;
+        } else {
+            hG[nG].req_begin = pd.req_begin;
+            hG[nG].n_reqs = pd.n_reqs;
+            hG[nG].orig = p;
+            hG[nG].pad = 0;
+            nG++;
+        }
+    }
+    c->n_pods = n_pods;
+    c->n_reqs = n_reqs;
+    c->nA = nA;
+    c->nB = nB;
+    c->nG = nG;
+    c->n_picks = (int32_t)picks;
+    rec(c, EV_PH0);
+    auto up = [&](size_t off, size_t bytes) -> cudaError_t {
+        if (!bytes) return cudaSuccess;
+        return cudaMemcpyAsync(c->d_stage + off, c->h_stage + off, bytes, cudaMemcpyHostToDevice, c->st);
+    };
+    CU(up(c->off_reqs, (size_t)n_reqs * sizeof(DevReq)));
+    CU(up(c->off_pods, (size_t)n_pods * sizeof(vgs_pod)));
+    CU(up(c->off_pick, (size_t)(n_reqs + 1) * sizeof(int32_t)));
+    CU(up(c->off_reqsA, (size_t)nA * sizeof(DevReq)));
+    CU(up(c->off_origA, (size_t)nA * sizeof(int32_t)));
+    CU(up(c->off_reqsB, (size_t)nB * sizeof(DevReq)));
+    CU(up(c->off_origB, (size_t)nB * sizeof(int32_t)));
+    CU(up(c->off_podsG, (size_t)nG * sizeof(GenPod)));
+    rec(c, EV_PH1);
+    c->have_pods = true;
+    return VGS_OK;
+}
+
+static int score_locked(vgs_ctx *c) {
+    if (!c->have_snapshot) return fail(c, VGS_ESTATE, "score before snapshot upload");
+    if (!c->have_pods) return fail(c, VGS_ESTATE, "score before pod upload");
+    const int32_t P = c->n_pods;
+    rec(c, EV_SC0);
+    if (P > 0) {
+        CU(cudaMemsetAsync(c->d_keys, 0, (size_t)P * sizeof(unsigned long long), c->st));
+        CU(cudaMemsetAsync(c->d_counts, 0, (size_t)P * sizeof(int32_t), c->st));
+    }
+    ScoreArgs a;
+    a.walk = c->d_walk;
+    a.n_tiles = c->n_tiles;
+    a.n_nodes = c->n_nodes;
+    a.row_base = c->cfg.row_base;
+    a.keys = c->d_keys;
+    a.counts = c->d_counts;
+    a.vfit = nullptr;
+    a.vscore = nullptr;
+    a.vwords = 0;
+    if (c->cfg.verify && P > 0) {
+        a.vfit = c->d_vfit;
+        a.vscore = c->d_vscore;
+        a.vwords = c->vwords;
+        CU(cudaMemsetAsync(c->d_vfit, 0, (size_t)P * c->vwords * sizeof(uint32_t), c->st));
+        if (c->n_nodes)
+            CU(cudaMemsetAsync(c->d_vscore, 0, (size_t)P * c->n_nodes * sizeof(float), c->st));
+    }
+    const DevReq *dreq = reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqs);
+    if (c->nA) {
+        CU(launch_score_single(c->dm, true, c->cfg.device, a,
+                               reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqsA),
+                               reinterpret_cast<const int32_t *>(c->d_stage + c->off_origA), c->nA, c->st));
+        if (c->n_tiles) c->launches++;
+    }
+    if (c->nB) {
+        CU(launch_score_single(c->dm, false, c->cfg.device, a,
+                               reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqsB),
+                               reinterpret_cast<const int32_t *>(c->d_stage + c->off_origB), c->nB, c->st));
+        if (c->n_tiles) c->launches++;
+    }
+    if (c->nG) {
+        CU(launch_score_general(c->dm, c->cfg.device, a, dreq,
+                                reinterpret_cast<const GenPod *>(c->d_stage + c->off_podsG), c->nG, c->st));
+        if (c->n_tiles) c->launches++;
+    }
+    rec(c, EV_SC1);
+    c->scored = true;
+    c->resolved = false;
+    return VGS_OK;
+}
+
+static int resolve_locked(vgs_ctx *c) {
+    if (!c->scored) return fail(c, VGS_ESTATE, "resolve before score");
+    rec(c, EV_RS0);
+    if (c->n_picks) CU(cudaMemsetAsync(c->d_picks, 0, (size_t)c->n_picks * sizeof(vgs_pick), c->st));
+    CU(launch_resolve(raw_const(c), c->n_nodes, c->dmax, c->cfg.row_base,
+                      reinterpret_cast<const vgs_pod *>(c->d_stage + c->off_pods),
+                      reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqs),
+                      reinterpret_cast<const int32_t *>(c->d_stage + c->off_pick), c->n_pods, c->d_keys,
+                      c->d_counts, c->d_results, c->d_picks, c->d_status, c->st));
+    if (c->n_pods) c->launches++;
+    rec(c, EV_RS1);
+    c->resolved = true;
+    return VGS_OK;
+}
+
+static int download_locked(vgs_ctx *c, vgs_result *results, vgs_pick *picks) {
+    if (!c->resolved) return fail(c, VGS_ESTATE, "download before resolve");
+    if (c->n_pods > 0 && !results) return fail(c, VGS_EINVAL, "null results");
+    rec(c, EV_DH0);
+    if (c->n_pods)
+        CU(cudaMemcpyAsync(c->h_results, c->d_results, (size_t)c->n_pods * sizeof(vgs_result),
+                           cudaMemcpyDeviceToHost, c->st));
+    if (c->n_picks && picks)
+        CU(cudaMemcpyAsync(c->h_picks, c->d_picks, (size_t)c->n_picks * sizeof(vgs_pick),
+                           cudaMemcpyDeviceToHost, c->st));
+    CU(cudaMemcpyAsync(c->h_status, c->d_status, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->st));
+    rec(c, EV_DH1);
+    CU(cudaStreamSynchronize(c->st));
+    int rc = check_status(c);
+    if (rc != VGS_OK) {
+        cudaMemsetAsync(c->d_status, 0, sizeof(uint32_t), c->st);
+        return rc;
+    }
+    if (c->n_pods) memcpy(results, c->h_results, (size_t)c->n_pods * sizeof(vgs_result));
+    if (c->n_picks && picks) memcpy(picks, c->h_picks, (size_t)c->n_picks * sizeof(vgs_pick));
+    return VGS_OK;
+}
+
+int vgs_pods_upload(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_reqs, const vgs_req *reqs) {
+    if (!c) return VGS_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard g(c->cfg.device);
+    return pods_upload_locked(c, n_pods, pods, n_reqs, reqs);
+}
+
+int vgs_score_resident(vgs_ctx *c) {
+    if (!c) return VGS_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard g(c->cfg.device);
+    return score_locked(c);
+}
+
+int vgs_resolve_resident(vgs_ctx *c) {
+    if (!c) return VGS_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard g(c->cfg.device);
+    return resolve_locked(c);
+}
+
+int vgs_results_download(vgs_ctx *c, vgs_result *results, vgs_pick *picks) {
+    if (!c) return VGS_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard g(c->cfg.device);
+    return download_locked(c, results, picks);
+}
+
+int vgs_score_batch(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_reqs, const vgs_req *reqs,
+                    vgs_result *results, vgs_pick *picks) {
+    if (!c) return VGS_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard g(c->cfg.device);
+    int rc;
+    if ((rc = pods_upload_locked(c, n_pods, pods, n_reqs, reqs)) != VGS_OK) return rc;
+    if ((rc = score_locked(c)) != VGS_OK) return rc;
+    if ((rc = resolve_locked(c)) != VGS_OK) return rc;
+    return download_locked(c, results, picks);
+}
+
+int vgs_sync(vgs_ctx *c) {
+    if (!c) return VGS_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard g(c->cfg.device);
+    CU(cudaStreamSynchronize(c->st));
+    return VGS_OK;
+}
+
+int vgs_keys_device(vgs_ctx *c, uint64_t **dev_keys, int32_t **dev_counts) {
+    if (!c) return VGS_EINVAL;
+    if (dev_keys) *dev_keys = reinterpret_cast<uint64_t *>(c->d_keys);
+    if (dev_counts) *dev_counts = c->d_counts;
+    return VGS_OK;
+}
+
+int vgs_results_device(vgs_ctx *c, vgs_result **dev_results, vgs_pick **dev_picks) {
+    if (!c) return VGS_EINVAL;
+    if (dev_results) *dev_results = c->d_results;
+    if (dev_picks) *dev_picks = c->d_picks;
+    return VGS_OK;
+}
+
+int vgs_keys_merge(vgs_ctx *c, const uint64_t *gk, const int32_t *gc, int32_t n_shards, int32_t stride) {
+    if (!c || !gk || n_shards < 1 || stride < 0) return VGS_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard g(c->cfg.device);
+    if (!c->scored) return fail(c, VGS_ESTATE, "merge before score");
+    if (stride < c->n_pods) return fail(c, VGS_EINVAL, "stride < n_pods");
+    CU(launch_merge(reinterpret_cast<const unsigned long long *>(gk), gc, n_shards, stride, c->n_pods,
+                    c->d_keys, c->d_counts, c->st));
+    if (c->n_pods) c->launches++;
+    return VGS_OK;
+}
+
+int vgs_verify_download(vgs_ctx *c, uint32_t *fit_bitmap, float *scores) {
+    if (!c) return VGS_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard g(c->cfg.device);
+    if (!c->cfg.verify) return fail(c, VGS_ESTATE, "context was not created with verify");
+    if (!c->scored) return fail(c, VGS_ESTATE, "verify download before score");
+    const size_t words = (size_t)(c->n_nodes + 31) / 32;
+    if (fit_bitmap && words && c->n_pods)
+        CU(cudaMemcpy2DAsync(fit_bitmap, words * sizeof(uint32_t), c->d_vfit,
+                             (size_t)c->vwords * sizeof(uint32_t), words * sizeof(uint32_t), c->n_pods,
+                             cudaMemcpyDeviceToHost, c->st));
+    if (scores && c->n_nodes && c->n_pods)
+        CU(cudaMemcpyAsync(scores, c->d_vscore, (size_t)c->n_pods * c->n_nodes * sizeof(float),
+                           cudaMemcpyDeviceToHost, c->st));
+    CU(cudaStreamSynchronize(c->st));
+    return VGS_OK;
+}
+
+int vgs_last_timing(vgs_ctx *c, vgs_timing *out) {
+    if (!c || !out) return VGS_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard g(c->cfg.device);
+    CU(cudaStreamSynchronize(c->st));
+    memset(out, 0, sizeof *out);
+    auto span = [&](int a, int b) -> float {
+        float ms = 0.f;
+        if (c->ev_set[a] && c->ev_set[b] && cudaEventElapsedTime(&ms, c->ev[a], c->ev[b]) == cudaSuccess)
+            return ms;
+        return 0.f;
+    };
+    out->snapshot_h2d_ms = span(EV_UP0, EV_UP1);
+    out->pods_h2d_ms = span(EV_PH0, EV_PH1);
+    out->derive_ms = span(EV_UP1, EV_DR1);
+    out->score_ms = span(EV_SC0, EV_SC1);
+    out->resolve_ms = span(EV_RS0, EV_RS1);
+    out->d2h_ms = span(EV_DH0, EV_DH1);
+    out->kernel_launches = (int32_t)(c->launches & 0x7fffffff);
+    return VGS_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,785 @@
+// vgs_kernels.cu -- sm_100a kernels of libvgpuscore.so
+//
+//   K0 k0_prepare      raw planes -> walk-ordered warp tiles (+ validation)
+//   K1 k1_score_single pods with ONE request: thread = node (state in registers),
+//                      loop over a pod chunk staged in shared memory
+//      k1_score_general pods with several requests / numa-bind multi-device requests
+//   K2 k2_merge        max over shards of the per-pod candidate keys
+//   K3 k3_resolve      re-run the winner node of every pod, emit the picks
+//   K4 k4_apply_delta  scatter usage deltas into the raw planes
+//
+// Reference semantics restated (never copied): pkg/scheduler/score.go:45-50 (device
+// order), :86-152 (fitInCertainDevice), :154-181 (fitInDevices), :183-214 (calcScore),
+// pkg/scheduler/scheduler.go:386-387 (best node).
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/vgpuscore.h"
+#include "vgs_kernels.h"
+#include "vgs_layout.h"
+
+namespace vgs {
+
+// ------------------------------------------------------------------------------------
+// small helpers
+// ------------------------------------------------------------------------------------
+__device__ __forceinline__ int32_t wrap_sub(int32_t a, int32_t b) {
+    return (int32_t)((uint32_t)a - (uint32_t)b);
+}
+__device__ __forceinline__ int32_t wrap_add(int32_t a, int32_t b) {
+    return (int32_t)((uint32_t)a + (uint32_t)b);
+}
+// Go: Totalmem * MemPercentagereq / 100 in int32 (score.go:119): wrapping multiply,
+// then division truncating toward zero.
+__device__ __forceinline__ int32_t pct_mem(int32_t totalmem, int32_t pct) {
+    return (int32_t)((uint32_t)totalmem * (uint32_t)pct) / 100;
+}
+// score.go:180  float32(total)/float32(free) + float32(len(node.Devices)-sums)
+__device__ __forceinline__ float container_score(int32_t total, int32_t free_, int32_t rest) {
+    return __fadd_rn(__fdiv_rn(__int2float_rn(total), __int2float_rn(free_)),
+                     __int2float_rn(rest));
+}
+__device__ __forceinline__ bool type_ok(uint32_t lo, uint32_t hi, uint32_t meta) {
+    uint32_t t = meta & M_TYPE_MASK;
+    uint32_t w = (t & 32u) ? hi : lo;
+    return (w >> (t & 31u)) & 1u;
+}
+
+__device__ __forceinline__ DevReq load_req(const DevReq *__restrict__ p) {
+    const int4 *q = reinterpret_cast<const int4 *>(p);
+    int4 a = __ldg(q), b = __ldg(q + 1);
+    DevReq r;
+    r.nums = a.x;
+    r.memfix = a.y;
+    r.pct = a.z;
+    r.coresreq = a.w;
+    r.blockmask = (uint32_t)b.x;
+    r.flags = (uint32_t)b.y;
+    r.mask_lo = (uint32_t)b.z;
+    r.mask_hi = (uint32_t)b.w;
+    return r;
+}
+
+template <int DM>
+__device__ __forceinline__ void load_word(const int4 *__restrict__ tile, int word, int lane,
+                                          int32_t (&dst)[DM]) {
+#pragma unroll
+    for (int q = 0; q < DM / 4; q++) {
+        int4 x = __ldg(&tile[(word * (DM / 4) + q) * kWarp + lane]);
+        dst[4 * q + 0] = x.x;
+        dst[4 * q + 1] = x.y;
+        dst[4 * q + 2] = x.z;
+        dst[4 * q + 3] = x.w;
+    }
+}
+
+// ------------------------------------------------------------------------------------
+// K0: prepare the walk-ordered copy.  One thread per node.
+// ------------------------------------------------------------------------------------
+template <int DM>
+__global__ void __launch_bounds__(128)
+    k0_prepare(RawPlanes raw, int32_t n_nodes, int32_t dmax, int4 *__restrict__ walk,
+               int32_t n_tiles, uint32_t *__restrict__ status, const int32_t *__restrict__ rowlist,
+               int32_t n_list) {
+    int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    int row;
+    if (rowlist) {
+        if (idx >= n_list) return;
+        row = rowlist[idx];
+        if (row < 0) return;
+    } else {
+        row = idx;
+    }
+    if (row >= n_tiles * kWarp) return;
+    const bool valid = row < n_nodes;
+    int32_t nd = valid ? raw.ndev[row] : 0;
+    uint32_t bad = 0;
+    if (nd < 0 || nd > dmax) {
+        bad |= S_NDEV;
+        nd = 0;
+    }
+    int32_t used[DM], count[DM], usedmem[DM], totalmem[DM], usedcores[DM], totalcore[DM],
+        numa[DM], type[DM];
+#pragma unroll
+    for (int j = 0; j < DM; j++) {
+        bool on = j < nd;
+        size_t x = (size_t)row * dmax + j;
+        used[j] = on ? raw.p[VGS_PLANE_USED][x] : 0;
+        count[j] = on ? raw.p[VGS_PLANE_COUNT][x] : 0;
+        usedmem[j] = on ? raw.p[VGS_PLANE_USEDMEM][x] : 0;
+        totalmem[j] = on ? raw.p[VGS_PLANE_TOTALMEM][x] : 0;
+        usedcores[j] = on ? raw.p[VGS_PLANE_USEDCORES][x] : 0;
+        totalcore[j] = on ? raw.p[VGS_PLANE_TOTALCORE][x] : 0;
+        numa[j] = on ? raw.p[VGS_PLANE_NUMA][x] : 0;
+        type[j] = on ? raw.p[VGS_PLANE_TYPEID][x] : 0;
+        if (on) {
+            if (used[j] < 0 || used[j] >= VGS_MAX_SHARE || count[j] < 0 || count[j] >= VGS_MAX_SHARE)
+                bad |= S_RANGE;
+            if (type[j] < 0 || type[j] >= VGS_MAX_TYPES) {
+                bad |= S_TYPE;
+                type[j] = 0;
+            }
+        }
+    }
+    if (bad) atomicOr(status, bad);
+
+    const int tile = row / kWarp, lane = row % kWarp;
+    int32_t *wbase = reinterpret_cast<int32_t *>(walk + (size_t)tile * kWalkWords * (DM / 4) * kWarp);
+    auto put = [&](int word, int w, int32_t v) {
+        wbase[((word * (DM / 4) + (w >> 2)) * kWarp + lane) * 4 + (w & 3)] = v;
+    };
+#pragma unroll
+    for (int j = 0; j < DM; j++) {
+        if (j < nd) {
+            // ascending position under score.go:45-50 with insertion-sort stability:
+            // (Numa, Count-Used, registration slot)
+            int rank = 0, nrank = 0;
+            int32_t fj = wrap_sub(count[j], used[j]);
+#pragma unroll
+            for (int i = 0; i < DM; i++) {
+                if (i < nd && i != j) {
+                    int32_t fi = wrap_sub(count[i], used[i]);
+                    bool less = numa[i] < numa[j] ||
+                                (numa[i] == numa[j] && (fi < fj || (fi == fj && i < j)));
+                    rank += less ? 1 : 0;
+                    nrank += numa[i] < numa[j] ? 1 : 0;
+                }
+            }
+            int w = nd - 1 - rank; // the reverse walk (score.go:92) visits the last first
+            uint32_t meta = (uint32_t)type[j] | ((uint32_t)nrank << M_NUMA_SHIFT) |
+                            ((uint32_t)j << M_SLOT_SHIFT) | ((uint32_t)nd << M_NDEV_SHIFT) | M_ALWAYS;
+            if (count[j] <= used[j]) meta |= M_NOFREE;
+            if (totalcore[j] == 100) meta |= M_IS100;
+            if (totalcore[j] != 0) meta |= M_CORENZ;
+            if (totalcore[j] == 100 && used[j] > 0) meta |= M_EXCL;
+            if (totalcore[j] != 0 && usedcores[j] == totalcore[j]) meta |= M_FULL;
+            float s1 = fj > 0 ? container_score(count[j], fj, nd - 1) : 0.0f;
+            put(W_TOTALMEM, w, totalmem[j]);
+            put(W_FREEMEM, w, wrap_sub(totalmem[j], usedmem[j]));
+            put(W_FREECORES, w, wrap_sub(totalcore[j], usedcores[j]));
+            put(W_COUNT, w, count[j]);
+            put(W_FREESLOTS, w, fj);
+            put(W_META, w, (int32_t)meta);
+            put(W_SCORE1, w, __float_as_int(s1));
+            put(W_SPARE, w, 0);
+        } else {
+            uint32_t meta = M_PAD | M_NOFREE | M_ALWAYS | ((uint32_t)j << M_SLOT_SHIFT) |
+                            ((uint32_t)nd << M_NDEV_SHIFT);
+            put(W_TOTALMEM, j, 0);
+            put(W_FREEMEM, j, 0);
+            put(W_FREECORES, j, 0);
+            put(W_COUNT, j, 0);
+            put(W_FREESLOTS, j, 0);
+            put(W_META, j, (int32_t)meta);
+            put(W_SCORE1, j, 0);
+            put(W_SPARE, j, 0);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------
+// warp-level publication of one pod's candidates: lane k keeps the result of the k-th
+// pod of a group of 32 so that the flush is one coalesced atomic per 32 pods.
+// ------------------------------------------------------------------------------------
+__device__ __forceinline__ void publish(bool fit, float score, int k, int lane, uint32_t row0,
+                                        unsigned long long &mykey, int32_t &mycnt) {
+    unsigned bal = __ballot_sync(0xffffffffu, fit);
+    if (bal) {
+        uint32_t sb = fit ? order_bits(__float_as_uint(score)) : 0u;
+        uint32_t m = __reduce_max_sync(0xffffffffu, sb);
+        unsigned who = __ballot_sync(0xffffffffu, sb == m);
+        uint32_t hl = 31u - (uint32_t)__clz((int)who); // ties -> highest row
+        if (lane == k) {
+            mykey = ((unsigned long long)m << 32) | (unsigned long long)(row0 + hl);
+            mycnt = __popc(bal);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------
+// K1 (single-request pods).  CTA item = (group of warps_per_cta node tiles, pod chunk).
+// NUMS1: Nums == 1 -> the first fitting device in walk order decides, its score was
+// prepared by K0.  Otherwise: first Nums fitting devices, total/free accumulated.
+// ------------------------------------------------------------------------------------
+template <int DM, bool NUMS1, bool VERIFY>
+__global__ void __launch_bounds__(256)
+    k1_score_single(const int4 *__restrict__ walk, int32_t n_tiles, int32_t n_nodes,
+                    int32_t row_base, const DevReq *__restrict__ reqs,
+                    const int32_t *__restrict__ orig, int32_t n_pods, ScoreLaunch L,
+                    unsigned long long *__restrict__ keys, int32_t *__restrict__ counts,
+                    uint32_t *__restrict__ vfit, float *__restrict__ vscore, int32_t vwords) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    DevReq *s_req = reinterpret_cast<DevReq *>(smem_raw);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int n_items = L.n_chunks * L.n_tile_groups;
+
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+        const int chunk = item / L.n_tile_groups, tg = item - chunk * L.n_tile_groups;
+        const int pod0 = chunk * L.chunk_len;
+        const int npod = min(L.chunk_len, n_pods - pod0);
+        __syncthreads(); // previous item's readers are done
+        {
+            const int4 *src = reinterpret_cast<const int4 *>(reqs + pod0);
+            int4 *dst = reinterpret_cast<int4 *>(s_req);
+            for (int i = threadIdx.x; i < npod * 2; i += blockDim.x) dst[i] = __ldg(&src[i]);
+        }
+        __syncthreads();
+        const int tile = tg * L.warps_per_cta + warp;
+        if (tile >= n_tiles) continue;
+
+        const int4 *tp = walk + (size_t)tile * kWalkWords * (DM / 4) * kWarp;
+        int32_t totalmem[DM], freemem[DM], freecores[DM], meta[DM];
+        int32_t count[DM], freeslots[DM], score1[DM];
+        load_word<DM>(tp, W_TOTALMEM, lane, totalmem);
+        load_word<DM>(tp, W_FREEMEM, lane, freemem);
+        load_word<DM>(tp, W_FREECORES, lane, freecores);
+        load_word<DM>(tp, W_META, lane, meta);
+        if (NUMS1) {
+            load_word<DM>(tp, W_SCORE1, lane, score1);
+        } else {
+            load_word<DM>(tp, W_COUNT, lane, count);
+            load_word<DM>(tp, W_FREESLOTS, lane, freeslots);
+        }
+        const int32_t ndev = (meta[0] >> M_NDEV_SHIFT) & 15;
+        const uint32_t row0 = (uint32_t)(row_base + tile * kWarp);
+        const int row = tile * kWarp + lane;
+
+        for (int pp = 0; pp < npod; pp += kWarp) {
+            unsigned long long mykey = 0ull;
+            int32_t mycnt = 0;
+            const int kend = min(kWarp, npod - pp);
+            for (int k = 0; k < kend; k++) {
+                const DevReq rq = s_req[pp + k];
+                bool fit;
+                float score;
+                if (NUMS1) {
+                    int32_t sb = 0;
+                    if (rq.flags & R_USEPCT) {
+#pragma unroll
+                        for (int j = DM - 1; j >= 0; j--) {
+                            bool f = !(meta[j] & rq.blockmask) &&
+                                     type_ok(rq.mask_lo, rq.mask_hi, meta[j]) &&
+                                     freemem[j] >= pct_mem(totalmem[j], rq.pct) &&
+                                     freecores[j] >= rq.coresreq;
+                            sb = f ? score1[j] : sb;
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = DM - 1; j >= 0; j--) {
+                            bool f = !(meta[j] & rq.blockmask) &&
+                                     type_ok(rq.mask_lo, rq.mask_hi, meta[j]) &&
+                                     freemem[j] >= rq.memfix && freecores[j] >= rq.coresreq;
+                            sb = f ? score1[j] : sb;
+                        }
+                    }
+                    fit = sb != 0; // a prepared score is >= 1.0f, never 0
+                    score = __int_as_float(sb);
+                } else {
+                    int32_t cnt = 0, total = 0, free_ = 0;
+                    const bool usepct = rq.flags & R_USEPCT;
+#pragma unroll
+                    for (int j = 0; j < DM; j++) {
+                        int32_t mem = usepct ? pct_mem(totalmem[j], rq.pct) : rq.memfix;
+                        bool f = !(meta[j] & rq.blockmask) &&
+                                 type_ok(rq.mask_lo, rq.mask_hi, meta[j]) && freemem[j] >= mem &&
+                                 freecores[j] >= rq.coresreq;
+                        bool take = f && cnt < rq.nums;
+                        cnt += f ? 1 : 0;
+                        total += take ? count[j] : 0;
+                        free_ += take ? freeslots[j] : 0;
+                    }
+                    fit = cnt >= rq.nums;
+                    score = fit ? container_score(total, free_, ndev - rq.nums) : 0.0f;
+                }
+                if (VERIFY) {
+                    int op = orig[pod0 + pp + k];
+                    unsigned b = __ballot_sync(0xffffffffu, fit);
+                    if (lane == 0) vfit[(size_t)op * vwords + tile] = b;
+                    if (row < n_nodes) vscore[(size_t)op * n_nodes + row] = fit ? score : 0.0f;
+                }
+                publish(fit, score, k, lane, row0, mykey, mycnt);
+            }
+            if (lane < kend && mykey != 0ull) {
+                int op = orig[pod0 + pp + lane];
+                atomicMax(&keys[op], mykey);
+                atomicAdd(&counts[op], mycnt);
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------
+// K1 (general pods): any number of containers / requests, numa-bind, state carried
+// from one request to the next exactly as calcScore/fitInDevices mutate node.Devices.
+//
+// Devices stay in their K0 walk order in registers.  The order the reference would see
+// after each sort.Sort is tracked as pos[j] (ascending position); the reverse walk then
+// visits devices by descending key (numa rank, free slots, pos).  "First Nums fitting
+// devices of the walk" = fitting devices with fewer than Nums fitting devices ahead.
+// ------------------------------------------------------------------------------------
+template <int DM, bool VERIFY>
+__global__ void __launch_bounds__(128)
+    k1_score_general(const int4 *__restrict__ walk, int32_t n_tiles, int32_t n_nodes,
+                     int32_t row_base, const DevReq *__restrict__ reqs,
+                     const GenPod *__restrict__ pods, int32_t n_pods, ScoreLaunch L,
+                     unsigned long long *__restrict__ keys, int32_t *__restrict__ counts,
+                     uint32_t *__restrict__ vfit, float *__restrict__ vscore, int32_t vwords) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int n_items = L.n_chunks * L.n_tile_groups;
+
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+        const int chunk = item / L.n_tile_groups, tg = item - chunk * L.n_tile_groups;
+        const int pod0 = chunk * L.chunk_len;
+        const int npod = min(L.chunk_len, n_pods - pod0);
+        const int tile = tg * L.warps_per_cta + warp;
+        if (tile >= n_tiles) continue;
+
+        const int4 *tp = walk + (size_t)tile * kWalkWords * (DM / 4) * kWarp;
+        int32_t totalmem[DM], freemem0[DM], freecores0[DM], meta0[DM], count[DM], freeslots0[DM];
+        load_word<DM>(tp, W_TOTALMEM, lane, totalmem);
+        load_word<DM>(tp, W_FREEMEM, lane, freemem0);
+        load_word<DM>(tp, W_FREECORES, lane, freecores0);
+        load_word<DM>(tp, W_META, lane, meta0);
+        load_word<DM>(tp, W_COUNT, lane, count);
+        load_word<DM>(tp, W_FREESLOTS, lane, freeslots0);
+        const int32_t ndev = (meta0[0] >> M_NDEV_SHIFT) & 15;
+        const uint32_t row0 = (uint32_t)(row_base + tile * kWarp);
+        const int row = tile * kWarp + lane;
+
+        for (int pp = 0; pp < npod; pp += kWarp) {
+            unsigned long long mykey = 0ull;
+            int32_t mycnt = 0;
+            const int kend = min(kWarp, npod - pp);
+            for (int k = 0; k < kend; k++) {
+                const GenPod pod = pods[pod0 + pp + k];
+                int32_t fm[DM], fc[DM], fs[DM], pos[DM];
+                uint32_t mt[DM];
+#pragma unroll
+                for (int j = 0; j < DM; j++) {
+                    fm[j] = freemem0[j];
+                    fc[j] = freecores0[j];
+                    fs[j] = freeslots0[j];
+                    mt[j] = (uint32_t)meta0[j];
+                    pos[j] = DM - 1 - j;
+                }
+                bool alive = true, in_ctr = false;
+                float score = 0.0f;
+                int32_t total = 0, free_ = 0, sums = 0;
+                for (int r = 0; r < pod.n_reqs; r++) {
+                    const DevReq rq = load_req(&reqs[pod.req_begin + r]);
+                    if (rq.flags & R_NEWCTR) {
+                        if (in_ctr) score = __fadd_rn(score, container_score(total, free_, ndev - sums));
+                        total = 0;
+                        free_ = 0;
+                        sums = 0;
+                        in_ctr = true;
+                    }
+                    sums += rq.nums;
+                    const bool usepct = rq.flags & R_USEPCT;
+                    const bool numa = rq.flags & R_NUMA;
+                    int32_t mem[DM], key[DM], nr[DM];
+                    bool fit[DM];
+                    int nfit = 0;
+#pragma unroll
+                    for (int j = 0; j < DM; j++) {
+                        mem[j] = usepct ? pct_mem(totalmem[j], rq.pct) : rq.memfix;
+                        fit[j] = !(mt[j] & rq.blockmask) && type_ok(rq.mask_lo, rq.mask_hi, mt[j]) &&
+                                 fm[j] >= mem[j] && fc[j] >= rq.coresreq;
+                        nr[j] = (mt[j] >> M_NUMA_SHIFT) & 15;
+                        key[j] = (nr[j] << (kKeyFreeBits + kKeyPosBits)) |
+                                 ((fs[j] + kKeyFreeBias) << kKeyPosBits) | pos[j];
+                        nfit += fit[j] ? 1 : 0;
+                    }
+                    // pairwise order: ahead[j] = fitting devices visited before j (same numa
+                    // group only when numa-bound); npos[j] = ascending position after this sort
+                    int ahead[DM], npos[DM], same[DM];
+#pragma unroll
+                    for (int j = 0; j < DM; j++) {
+                        ahead[j] = 0;
+                        npos[j] = 0;
+                        same[j] = fit[j] ? 1 : 0;
+                    }
+#pragma unroll
+                    for (int i = 0; i < DM; i++) {
+#pragma unroll
+                        for (int j = i + 1; j < DM; j++) {
+                            bool igtj = key[i] > key[j]; // keys are distinct (pos is a permutation)
+                            bool grp = !numa || nr[i] == nr[j];
+                            ahead[j] += (igtj && fit[i] && grp) ? 1 : 0;
+                            ahead[i] += (!igtj && fit[j] && grp) ? 1 : 0;
+                            npos[i] += igtj ? 1 : 0;
+                            npos[j] += igtj ? 0 : 1;
+                            if (numa) {
+                                same[i] += (fit[j] && nr[i] == nr[j]) ? 1 : 0;
+                                same[j] += (fit[i] && nr[i] == nr[j]) ? 1 : 0;
+                            }
+                        }
+                    }
+                    bool ok;
+                    int gstar = -1;
+                    if (numa) {
+                        // the walk restarts its picks at every numa change (score.go:99-104):
+                        // the first numa group (descending) holding >= Nums fitting devices wins
+#pragma unroll
+                        for (int j = 0; j < DM; j++)
+                            if (fit[j] && same[j] >= rq.nums) gstar = max(gstar, nr[j]);
+                        ok = gstar >= 0;
+                    } else {
+                        ok = nfit >= rq.nums;
+                    }
+                    alive = alive && ok;
+#pragma unroll
+                    for (int j = 0; j < DM; j++) {
+                        bool take = ok && fit[j] && ahead[j] < rq.nums && (!numa || nr[j] == gstar);
+                        if (take) { // score.go:168-174
+                            total = wrap_add(total, count[j]);
+                            free_ = wrap_add(free_, fs[j]);
+                            fs[j] -= 1;
+                            fm[j] = wrap_sub(fm[j], mem[j]);
+                            fc[j] = wrap_sub(fc[j], rq.coresreq);
+                            uint32_t m = mt[j] & ~(M_NOFREE | M_EXCL | M_FULL);
+                            if (fs[j] <= 0) m |= M_NOFREE;
+                            if (m & M_IS100) m |= M_EXCL;
+                            if ((m & M_CORENZ) && fc[j] == 0) m |= M_FULL;
+                            mt[j] = m;
+                        }
+                        pos[j] = npos[j];
+                    }
+                    if (!__any_sync(0xffffffffu, alive)) break;
+                }
+                if (alive && in_ctr) score = __fadd_rn(score, container_score(total, free_, ndev - sums));
+                const bool fitn = alive;
+                if (VERIFY) {
+                    unsigned b = __ballot_sync(0xffffffffu, fitn);
+                    if (lane == 0) vfit[(size_t)pod.orig * vwords + tile] = b;
+                    if (row < n_nodes) vscore[(size_t)pod.orig * n_nodes + row] = fitn ? score : 0.0f;
+                }
+                publish(fitn, score, k, lane, row0, mykey, mycnt);
+            }
+            if (lane < kend && mykey != 0ull) {
+                int op = pods[pod0 + pp + lane].orig;
+                atomicMax(&keys[op], mykey);
+                atomicAdd(&counts[op], mycnt);
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------
+// K2: merge shard candidates (after the allgather)
+// ------------------------------------------------------------------------------------
+__global__ void k2_merge(const unsigned long long *__restrict__ gk, const int32_t *__restrict__ gc,
+                         int32_t n_shards, int32_t stride, int32_t n_pods,
+                         unsigned long long *__restrict__ keys, int32_t *__restrict__ counts) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n_pods) return;
+    unsigned long long best = 0ull;
+    int32_t c = 0;
+    for (int g = 0; g < n_shards; g++) {
+        unsigned long long k = gk[(size_t)g * stride + p];
+        best = k > best ? k : best;
+        if (gc) c += gc[(size_t)g * stride + p];
+    }
+    keys[p] = best;
+    if (gc) counts[p] = c;
+}
+
+// ------------------------------------------------------------------------------------
+// K3: resolve.  One thread per pod re-runs the winner node from the RAW planes in the
+// plain way (sort, reverse walk, mutate) and emits the picks in take order
+// (score.go:138-144,175).  Its score must equal the key's score: self-check.
+// ------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(64)
+    k3_resolve(RawPlanes raw, int32_t n_nodes, int32_t dmax, int32_t row_base,
+               const vgs_pod *__restrict__ pods, const DevReq *__restrict__ reqs,
+               const int32_t *__restrict__ pick_begin, int32_t n_pods,
+               const unsigned long long *__restrict__ keys, const int32_t *__restrict__ counts,
+               vgs_result *__restrict__ results, vgs_pick *__restrict__ picks,
+               uint32_t *__restrict__ status) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n_pods) return;
+    const unsigned long long key = keys[p];
+    vgs_result res;
+    res.fit_count = counts[p];
+    if (key == 0ull) {
+        res.best_row = -1;
+        res.score = 0.0f;
+        res.n_picks = 0;
+        results[p] = res;
+        return;
+    }
+    const vgs_pod pod = pods[p];
+    const int32_t grow = (int32_t)(uint32_t)key;
+    const uint32_t kbits = unorder_bits((uint32_t)(key >> 32));
+    res.best_row = grow;
+    res.score = __uint_as_float(kbits);
+    res.n_picks = pick_begin[pod.req_begin + pod.n_reqs] - pick_begin[pod.req_begin];
+    results[p] = res;
+    const int32_t row = grow - row_base;
+    if (row < 0 || row >= n_nodes) return; // another shard owns the winner
+
+    const int32_t nd = raw.ndev[row];
+    const size_t base = (size_t)row * dmax;
+    int32_t used[VGS_MAX_DEVICES], usedmem[VGS_MAX_DEVICES], usedcores[VGS_MAX_DEVICES];
+    int32_t ord[VGS_MAX_DEVICES];
+    for (int d = 0; d < nd; d++) {
+        used[d] = raw.p[VGS_PLANE_USED][base + d];
+        usedmem[d] = raw.p[VGS_PLANE_USEDMEM][base + d];
+        usedcores[d] = raw.p[VGS_PLANE_USEDCORES][base + d];
+        ord[d] = d;
+    }
+    const int32_t *count = raw.p[VGS_PLANE_COUNT] + base;
+    const int32_t *totalmem = raw.p[VGS_PLANE_TOTALMEM] + base;
+    const int32_t *totalcore = raw.p[VGS_PLANE_TOTALCORE] + base;
+    const int32_t *numa = raw.p[VGS_PLANE_NUMA] + base;
+    const int32_t *type = raw.p[VGS_PLANE_TYPEID] + base;
+
+    float score = 0.0f;
+    bool alive = true, in_ctr = false;
+    int32_t total = 0, free_ = 0, sums = 0;
+    for (int r = 0; r < pod.n_reqs && alive; r++) {
+        const DevReq rq = reqs[pod.req_begin + r];
+        if (rq.flags & R_NEWCTR) {
+            if (in_ctr) score = __fadd_rn(score, container_score(total, free_, nd - sums));
+            total = free_ = sums = 0;
+            in_ctr = true;
+        }
+        sums += rq.nums;
+        if (rq.nums > nd) { // score.go:162
+            alive = false;
+            break;
+        }
+        // stable insertion sort, ascending (Numa, Count-Used)   score.go:45-50,165
+        for (int i = 1; i < nd; i++) {
+            for (int j = i; j > 0; j--) {
+                int a = ord[j], b = ord[j - 1];
+                bool less = numa[a] == numa[b]
+                                ? wrap_sub(count[a], used[a]) < wrap_sub(count[b], used[b])
+                                : numa[a] < numa[b];
+                if (!less) break;
+                ord[j] = b;
+                ord[j - 1] = a;
+            }
+        }
+        int32_t left = rq.nums, prevnuma = -1, nt = 0;
+        int32_t tdev[VGS_MAX_DEVICES], tmem[VGS_MAX_DEVICES];
+        bool ok = false;
+        for (int i = nd - 1; i >= 0; i--) { // score.go:92
+            const int d = ord[i];
+            uint32_t t = (uint32_t)type[d];
+            if (!(((t & 32u) ? rq.mask_hi : rq.mask_lo) >> (t & 31u) & 1u)) continue;
+            if ((rq.flags & R_NUMA) && prevnuma != numa[d]) { // :99-104
+                left = rq.nums;
+                prevnuma = numa[d];
+                nt = 0;
+            }
+            if (count[d] <= used[d]) continue; // :107
+            if (rq.coresreq > 100) break;      // :110
+            int32_t memreq = (rq.flags & R_USEPCT) ? pct_mem(totalmem[d], rq.pct) : rq.memfix;
+            if (wrap_sub(totalmem[d], usedmem[d]) < memreq) continue;
+            if (wrap_sub(totalcore[d], usedcores[d]) < rq.coresreq) continue;
+            if (totalcore[d] == 100 && rq.coresreq == 100 && used[d] > 0) continue;
+            if (totalcore[d] != 0 && usedcores[d] == totalcore[d] && rq.coresreq == 0) continue;
+            if (left > 0) {
+                left--;
+                tdev[nt] = d;
+                tmem[nt] = memreq;
+                nt++;
+            }
+            if (left == 0) {
+                ok = true;
+                break;
+            }
+        }
+        if (!ok) {
+            alive = false;
+            break;
+        }
+        const int32_t pb = pick_begin[pod.req_begin + r];
+        for (int t = 0; t < nt; t++) { // :168-174
+            const int d = tdev[t];
+            total = wrap_add(total, count[d]);
+            free_ = wrap_add(free_, wrap_sub(count[d], used[d]));
+            used[d] = wrap_add(used[d], 1);
+            usedcores[d] = wrap_add(usedcores[d], rq.coresreq);
+            usedmem[d] = wrap_add(usedmem[d], tmem[t]);
+            vgs_pick pk;
+            pk.slot = d;
+            pk.usedmem = tmem[t];
+            pk.usedcores = rq.coresreq;
+            picks[pb + t] = pk;
+        }
+    }
+    if (alive && in_ctr) score = __fadd_rn(score, container_score(total, free_, nd - sums));
+    if (!alive || __float_as_uint(score) != kbits) atomicOr(status, S_MISMATCH);
+}
+
+// ------------------------------------------------------------------------------------
+// K4: usage deltas (what addPod/delPod change between two Filters, scheduler.go:280-297)
+// ------------------------------------------------------------------------------------
+__global__ void k4_apply_delta(RawPlanesMut raw, int32_t n_nodes, int32_t dmax, int32_t row_base,
+                               const vgs_delta *__restrict__ deltas, int32_t n,
+                               int32_t *__restrict__ rowlist, uint32_t *__restrict__ status) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    vgs_delta d = deltas[i];
+    int32_t row = d.row - row_base;
+    if (row < 0 || row >= n_nodes) { // not this shard's row: ignore
+        rowlist[i] = -1;
+        return;
+    }
+    if (d.slot < 0 || d.slot >= dmax || d.slot >= raw.ndev[row]) {
+        atomicOr(status, S_DELTA);
+        rowlist[i] = -1;
+        return;
+    }
+    size_t x = (size_t)row * dmax + d.slot;
+    atomicAdd(&raw.p[VGS_PLANE_USED][x], d.d_used);
+    atomicAdd(&raw.p[VGS_PLANE_USEDMEM][x], d.d_usedmem);
+    atomicAdd(&raw.p[VGS_PLANE_USEDCORES][x], d.d_usedcores);
+    rowlist[i] = row;
+}
+
+// ------------------------------------------------------------------------------------
+// launchers
+// ------------------------------------------------------------------------------------
+static int g_sm_count[64];
+static int sm_count(int dev) {
+    if (dev < 0 || dev >= 64) return 148;
+    if (g_sm_count[dev] == 0) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+            n = 148;
+        g_sm_count[dev] = n;
+    }
+    return g_sm_count[dev];
+}
+
+cudaError_t launch_prepare(int dm, const RawPlanes &raw, int32_t n_nodes, int32_t dmax, int4 *walk,
+                           int32_t n_tiles, uint32_t *status, const int32_t *rowlist,
+                           int32_t n_list, cudaStream_t st) {
+    int n = rowlist ? n_list : n_tiles * kWarp;
+    if (n <= 0) return cudaSuccess;
+    int block = 128, grid = (n + block - 1) / block;
+    if (dm == 8)
+        k0_prepare<8><<<grid, block, 0, st>>>(raw, n_nodes, dmax, walk, n_tiles, status, rowlist, n_list);
+    else
+        k0_prepare<12><<<grid, block, 0, st>>>(raw, n_nodes, dmax, walk, n_tiles, status, rowlist, n_list);
+    return cudaGetLastError();
+}
+
+template <typename K>
+static cudaError_t plan(K kernel, int dev, int32_t n_tiles, int32_t n_pods, int max_warps,
+                        int smem_per_pod, ScoreLaunch *L) {
+    // small snapshots: fewer warps per CTA so that every SM still gets work
+    int sms = sm_count(dev);
+    int wpc = max_warps;
+    while (wpc > 1 && (n_tiles + wpc - 1) / wpc < 2 * sms) wpc >>= 1;
+    L->warps_per_cta = wpc;
+    L->block = wpc * kWarp;
+    L->n_tile_groups = (n_tiles + wpc - 1) / wpc;
+    int occ = 1;
+    // pod chunk: enough items for >= 8 rounds per resident CTA, chunk a multiple of 32
+    int chunk = 512;
+    for (;;) {
+        L->smem = chunk * smem_per_pod;
+        cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, L->block, L->smem);
+        if (e != cudaSuccess) return e;
+        if (occ < 1) occ = 1;
+        long long resident = (long long)sms * occ;
+        long long items = (long long)L->n_tile_groups * ((n_pods + chunk - 1) / chunk);
+        if (items >= 8 * resident || chunk <= 32) break;
+        chunk >>= 1;
+    }
+    if (chunk > ((n_pods + 31) / 32) * 32) chunk = ((n_pods + 31) / 32) * 32;
+    L->chunk_len = chunk;
+    L->smem = chunk * smem_per_pod;
+    L->n_chunks = (n_pods + chunk - 1) / chunk;
+    long long items = (long long)L->n_tile_groups * L->n_chunks;
+    long long resident = (long long)sms * occ;
+    L->grid = (int)(items < resident ? items : resident);
+    if (L->grid < 1) L->grid = 1;
+    return cudaSuccess;
+}
+
+template <int DM, bool NUMS1>
+static cudaError_t launch_single_t(int dev, const ScoreArgs &a, const DevReq *reqs, const int32_t *orig,
+                                   int32_t n_pods, cudaStream_t st) {
+    ScoreLaunch L;
+    cudaError_t e;
+    if (a.vfit) {
+        auto k = k1_score_single<DM, NUMS1, true>;
+        if ((e = plan(k, dev, a.n_tiles, n_pods, 8, (int)sizeof(DevReq), &L)) != cudaSuccess) return e;
+        k<<<L.grid, L.block, L.smem, st>>>(a.walk, a.n_tiles, a.n_nodes, a.row_base, reqs, orig, n_pods, L,
+                                          a.keys, a.counts, a.vfit, a.vscore, a.vwords);
+    } else {
+        auto k = k1_score_single<DM, NUMS1, false>;
+        if ((e = plan(k, dev, a.n_tiles, n_pods, 8, (int)sizeof(DevReq), &L)) != cudaSuccess) return e;
+        k<<<L.grid, L.block, L.smem, st>>>(a.walk, a.n_tiles, a.n_nodes, a.row_base, reqs, orig, n_pods, L,
+                                          a.keys, a.counts, nullptr, nullptr, 0);
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_score_single(int dm, bool nums1, int dev, const ScoreArgs &a, const DevReq *reqs,
+                                const int32_t *orig, int32_t n_pods, cudaStream_t st) {
+    if (n_pods <= 0 || a.n_tiles <= 0) return cudaSuccess;
+    if (dm == 8)
+        return nums1 ? launch_single_t<8, true>(dev, a, reqs, orig, n_pods, st)
+                     : launch_single_t<8, false>(dev, a, reqs, orig, n_pods, st);
+    return nums1 ? launch_single_t<12, true>(dev, a, reqs, orig, n_pods, st)
+                 : launch_single_t<12, false>(dev, a, reqs, orig, n_pods, st);
+}
+
+template <int DM>
+static cudaError_t launch_general_t(int dev, const ScoreArgs &a, const DevReq *reqs, const GenPod *pods,
+                                    int32_t n_pods, cudaStream_t st) {
+    ScoreLaunch L;
+    cudaError_t e;
+    if (a.vfit) {
+        auto k = k1_score_general<DM, true>;
+        if ((e = plan(k, dev, a.n_tiles, n_pods, 4, 0, &L)) != cudaSuccess) return e;
+        k<<<L.grid, L.block, 0, st>>>(a.walk, a.n_tiles, a.n_nodes, a.row_base, reqs, pods, n_pods, L,
+                                     a.keys, a.counts, a.vfit, a.vscore, a.vwords);
+    } else {
+        auto k = k1_score_general<DM, false>;
+        if ((e = plan(k, dev, a.n_tiles, n_pods, 4, 0, &L)) != cudaSuccess) return e;
+        k<<<L.grid, L.block, 0, st>>>(a.walk, a.n_tiles, a.n_nodes, a.row_base, reqs, pods, n_pods, L,
+                                     a.keys, a.counts, nullptr, nullptr, 0);
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_score_general(int dm, int dev, const ScoreArgs &a, const DevReq *reqs,
+                                 const GenPod *pods, int32_t n_pods, cudaStream_t st) {
+    if (n_pods <= 0 || a.n_tiles <= 0) return cudaSuccess;
+    return dm == 8 ? launch_general_t<8>(dev, a, reqs, pods, n_pods, st)
+                   : launch_general_t<12>(dev, a, reqs, pods, n_pods, st);
+}
+
+cudaError_t launch_merge(const unsigned long long *gk, const int32_t *gc, int32_t n_shards, int32_t stride,
+                         int32_t n_pods, unsigned long long *keys, int32_t *counts, cudaStream_t st) {
+    if (n_pods <= 0) return cudaSuccess;
+    k2_merge<<<(n_pods + 127) / 128, 128, 0, st>>>(gk, gc, n_shards, stride, n_pods, keys, counts);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_resolve(const RawPlanes &raw, int32_t n_nodes, int32_t dmax, int32_t row_base,
+                           const vgs_pod *pods, const DevReq *reqs, const int32_t *pick_begin,
+                           int32_t n_pods, const unsigned long long *keys, const int32_t *counts,
+                           vgs_result *results, vgs_pick *picks, uint32_t *status, cudaStream_t st) {
+    if (n_pods <= 0) return cudaSuccess;
+    k3_resolve<<<(n_pods + 63) / 64, 64, 0, st>>>(raw, n_nodes, dmax, row_base, pods, reqs, pick_begin,
+                                                 n_pods, keys, counts, results, picks, status);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_delta(const RawPlanesMut &raw, int32_t n_nodes, int32_t dmax, int32_t row_base,
+                         const vgs_delta *deltas, int32_t n, int32_t *rowlist, uint32_t *status,
+                         cudaStream_t st) {
+    if (n <= 0) return cudaSuccess;
+    k4_apply_delta<<<(n + 127) / 128, 128, 0, st>>>(raw, n_nodes, dmax, row_base, deltas, n, rowlist, status);
+    return cudaGetLastError();
+}
+
+} // namespace vgs

@@ -1,0 +1,51 @@
+// vgs_kernels.h -- launch interface between the C ABI (vgs_capi.cu) and the kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/vgpuscore.h"
+#include "vgs_layout.h"
+
+namespace vgs {
+
+struct RawPlanes {
+    const int32_t *p[VGS_NUM_PLANES];
+    const int32_t *ndev;
+};
+struct RawPlanesMut {
+    int32_t *p[VGS_NUM_PLANES];
+    int32_t *ndev;
+};
+
+struct ScoreArgs {
+    const int4 *walk;
+    int32_t n_tiles, n_nodes, row_base;
+    unsigned long long *keys;
+    int32_t *counts;
+    uint32_t *vfit; // verify mode only, else nullptr
+    float *vscore;
+    int32_t vwords;
+};
+
+inline int walk_dm(int dmax) { return dmax <= 8 ? 8 : 12; }
+inline size_t walk_int4_per_tile(int dm) { return (size_t)kWalkWords * (dm / 4) * kWarp; }
+
+cudaError_t launch_prepare(int dm, const RawPlanes &raw, int32_t n_nodes, int32_t dmax, int4 *walk,
+                           int32_t n_tiles, uint32_t *status, const int32_t *rowlist,
+                           int32_t n_list, cudaStream_t st);
+cudaError_t launch_score_single(int dm, bool nums1, int dev, const ScoreArgs &a, const DevReq *reqs,
+                                const int32_t *orig, int32_t n_pods, cudaStream_t st);
+cudaError_t launch_score_general(int dm, int dev, const ScoreArgs &a, const DevReq *reqs,
+                                 const GenPod *pods, int32_t n_pods, cudaStream_t st);
+cudaError_t launch_merge(const unsigned long long *gk, const int32_t *gc, int32_t n_shards,
+                         int32_t stride, int32_t n_pods, unsigned long long *keys, int32_t *counts,
+                         cudaStream_t st);
+cudaError_t launch_resolve(const RawPlanes &raw, int32_t n_nodes, int32_t dmax, int32_t row_base,
+                           const vgs_pod *pods, const DevReq *reqs, const int32_t *pick_begin,
+                           int32_t n_pods, const unsigned long long *keys, const int32_t *counts,
+                           vgs_result *results, vgs_pick *picks, uint32_t *status, cudaStream_t st);
+cudaError_t launch_delta(const RawPlanesMut &raw, int32_t n_nodes, int32_t dmax, int32_t row_base,
+                         const vgs_delta *deltas, int32_t n, int32_t *rowlist, uint32_t *status,
+                         cudaStream_t st);
+
+} // namespace vgs

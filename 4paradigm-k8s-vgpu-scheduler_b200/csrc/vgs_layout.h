@@ -1,0 +1,94 @@
+// vgs_layout.h -- device-side data layout shared by the kernels and the C ABI.
+//
+// Two copies of the usage snapshot live in HBM:
+//
+//  raw     the 8 int32 planes exactly as the host packed them, node-major
+//          (plane[f][row * dmax + slot]); source of truth, updated by deltas,
+//          read by the resolve kernel.
+//  walk    per node, the same devices re-ordered into the order in which the
+//          reference's fitInCertainDevice visits them for the FIRST request of
+//          a pod (score.go:165 sort, :92 reverse walk).  That order does not
+//          depend on the pod, so it is prepared once per snapshot (K0) instead
+//          of once per (pod, node).  Stored as warp tiles of 32 nodes:
+//              int4 walk[tile][word][q][lane]      q = device group of 4
+//          so that lane l of a warp reads node tile*32+l with 128-bit loads
+//          and a warp reads 512 contiguous bytes per instruction.
+#pragma once
+#include <stdint.h>
+
+namespace vgs {
+
+constexpr int kWarp = 32;
+
+// words per device in the walk-ordered copy
+enum {
+    W_TOTALMEM = 0,  // Totalmem
+    W_FREEMEM = 1,   // Totalmem - Usedmem      (score.go:121 left-hand side)
+    W_FREECORES = 2, // Totalcore - Usedcores   (score.go:124 left-hand side)
+    W_COUNT = 3,     // Count
+    W_FREESLOTS = 4, // Count - Used            (score.go:47,107,170)
+    W_META = 5,      // packed small fields, see M_*
+    W_SCORE1 = 6,    // f32 bits of Count/(Count-Used) + (ndev-1): the node score if this
+                     // device alone is picked (score.go:180 with Nums == 1)
+    W_SPARE = 7,
+    kWalkWords = 8
+};
+
+// W_META bits
+constexpr uint32_t M_TYPE_MASK = 0x3fu;   // bits 0-5  type id
+constexpr int M_NUMA_SHIFT = 6;           // bits 6-9  rank of Numa among the node's values
+constexpr int M_SLOT_SHIFT = 10;          // bits 10-13 registration slot
+constexpr int M_NDEV_SHIFT = 14;          // bits 14-17 len(node.Devices)
+constexpr uint32_t M_NOFREE = 1u << 18;   // Count <= Used                       (score.go:107)
+constexpr uint32_t M_EXCL = 1u << 19;     // Totalcore == 100 && Used > 0        (score.go:128)
+constexpr uint32_t M_FULL = 1u << 20;     // Totalcore != 0 && Usedcores == Totalcore (:132)
+constexpr uint32_t M_PAD = 1u << 21;      // slot >= len(node.Devices): not a device
+constexpr uint32_t M_IS100 = 1u << 22;    // Totalcore == 100
+constexpr uint32_t M_CORENZ = 1u << 23;   // Totalcore != 0
+constexpr uint32_t M_ALWAYS = 1u << 31;   // always set (lets a request block every device)
+
+// ordering key of a device inside one node: (numa rank, free share slots, previous position)
+constexpr int kKeyPosBits = 4;
+constexpr int kKeyFreeBits = 23;
+constexpr int32_t kKeyFreeBias = 1 << 22;
+
+// request as the kernels see it (built by the host from vgs_req)
+struct __align__(16) DevReq {
+    int32_t nums;
+    int32_t memfix;     // Memreq when > 0 else 0                           (score.go:114-116)
+    int32_t pct;        // MemPercentagereq, used when R_USEPCT             (score.go:117-120)
+    int32_t coresreq;
+    uint32_t blockmask; // W_META bits that rule a device out for this request
+    uint32_t flags;     // R_*
+    uint32_t mask_lo, mask_hi; // type mask
+};
+constexpr uint32_t R_NUMA = 1u;   // numa-bind asserted
+constexpr uint32_t R_USEPCT = 2u; // memreq = Totalmem * pct / 100 per device
+constexpr uint32_t R_NEWCTR = 4u; // first request of a container
+
+// pod of the general (multi-request) class
+struct GenPod {
+    int32_t req_begin, n_reqs, orig, pad;
+};
+
+// status word bits (device -> host)
+constexpr uint32_t S_RANGE = 1u;    // snapshot value out of range
+constexpr uint32_t S_TYPE = 2u;     // type id out of range
+constexpr uint32_t S_NDEV = 4u;     // ndev out of range
+constexpr uint32_t S_MISMATCH = 8u; // resolve kernel disagrees with score kernel
+constexpr uint32_t S_DELTA = 16u;   // delta names a row/slot outside the shard
+
+__host__ __device__ inline uint32_t order_bits(uint32_t fbits) {
+    // monotone map float bits -> unsigned, never 0 for a finite float
+    return fbits ^ ((uint32_t)((int32_t)fbits >> 31) | 0x80000000u);
+}
+__host__ __device__ inline uint32_t unorder_bits(uint32_t ob) {
+    return (ob & 0x80000000u) ? (ob ^ 0x80000000u) : ~ob;
+}
+
+struct ScoreLaunch {
+    int grid, block, smem;
+    int chunk_len, n_chunks, n_tile_groups, warps_per_cta;
+};
+
+} // namespace vgs

@@ -1,0 +1,225 @@
+/*
+ * vgpuscore.h -- C ABI of libvgpuscore.so
+ *
+ * B200 (sm_100a) implementation of the one data-parallel hot path of the
+ * 4paradigm k8s vGPU scheduler extender: the per-pod Filter scoring pass
+ *
+ *     Filter -> calcScore -> fitInDevices -> fitInCertainDevice + best-node pick
+ *     (reference: pkg/scheduler/scheduler.go:377,386-387 and
+ *      pkg/scheduler/score.go:45-50,71-214)
+ *
+ * The reference has no plugin interface at this seam (calcScore is package
+ * private, sole caller scheduler.go:377); this header IS the seam.  Everything
+ * is C99: plain pointers and sizes, caller-owned buffers, no callbacks, and the
+ * library keeps no caller pointer after a call returns (cgo pointer rules).
+ *
+ * Conventions
+ *   - every function returns 0 (VGS_OK) or a negative vgs_status;
+ *     "no node fits" is NOT an error (best_row = -1), mirroring
+ *     scheduler.go:381-385.  There is no CPU fallback: without a usable GPU
+ *     vgs_init fails with VGS_ECUDA.
+ *   - a context is bound to ONE GPU and holds ONE shard of the node set (rows
+ *     [row_base, row_base + n_nodes)); multi-GPU = one context per GPU, the
+ *     caller exchanges the per-pod candidate keys (see vgs_keys_* below).
+ *   - calls on one context are serialised by an internal mutex.
+ */
+#ifndef VGPUSCORE_H
+#define VGPUSCORE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VGS_ABI_VERSION 1
+
+/* Go 1.19 sort.Sort is a stable insertion sort only for n <= 12
+ * (score.go:165); more devices per node would need pdqsort semantics. */
+#define VGS_MAX_DEVICES 12
+/* distinct device type strings (util.DeviceUsage.Type) per snapshot */
+#define VGS_MAX_TYPES 64
+/* ContainerDeviceRequest.MemPercentagereq value meaning "unset"
+ * (pkg/device/nvidia/device.go:136) */
+#define VGS_MEMPCT_UNSET 101
+/* requests (containers x vendors) one pod may carry */
+#define VGS_MAX_REQS_PER_POD 32
+/* |Count| and |Used| must stay below this (ordering keys are packed) */
+#define VGS_MAX_SHARE 1048576
+
+/* plane order of vgs_snapshot_upload: fields of util.DeviceUsage
+ * (pkg/util/types.go:105-117) that scoring reads, plus the type id. */
+enum {
+    VGS_PLANE_USED = 0,
+    VGS_PLANE_COUNT = 1,
+    VGS_PLANE_USEDMEM = 2,
+    VGS_PLANE_TOTALMEM = 3,
+    VGS_PLANE_USEDCORES = 4,
+    VGS_PLANE_TOTALCORE = 5,
+    VGS_PLANE_NUMA = 6,
+    VGS_PLANE_TYPEID = 7, /* index into the caller's table of distinct Type strings */
+    VGS_NUM_PLANES = 8
+};
+
+typedef enum {
+    VGS_OK = 0,
+    VGS_EINVAL = -1,  /* bad argument / malformed batch */
+    VGS_ECUDA = -2,   /* CUDA runtime error (vgs_last_error has the text) */
+    VGS_ETOOBIG = -3, /* exceeds the capacities given to vgs_init */
+    VGS_EDMAX = -4,   /* more than VGS_MAX_DEVICES devices per node */
+    VGS_ERANGE = -5,  /* snapshot value outside the supported range */
+    VGS_ESTATE = -6,  /* call sequence error (e.g. score before upload) */
+    VGS_EINTERNAL = -7 /* self-check failed (score kernel vs resolve kernel) */
+} vgs_status;
+
+typedef struct vgs_ctx vgs_ctx;
+
+typedef struct {
+    int32_t device;      /* CUDA ordinal */
+    int32_t max_nodes;   /* rows this context can hold */
+    int32_t max_devices; /* device slots per node, 1..VGS_MAX_DEVICES */
+    int32_t max_pods;    /* pods per batch */
+    int32_t max_reqs;    /* requests per batch */
+    int32_t max_picks;   /* sum of nums per batch */
+    int32_t row_base;    /* global row index of local row 0 (node sharding) */
+    int32_t verify;      /* !=0: also keep the full pod x node fit bitmap and scores */
+    void *stream;        /* cudaStream_t to run on; NULL = library creates one */
+} vgs_config;
+
+/* One container x vendor request = util.ContainerDeviceRequest
+ * (pkg/util/types.go:93-99) with the string policy pre-evaluated by the host:
+ * bit t of typemask = checkType(annos, DeviceUsage{Type: types[t]}, req).pass
+ * (score.go:71-84, nvidia/device.go:62-94,107-112). */
+#define VGS_REQ_NUMA_BIND 1u /* checkType's numaAssert (nvidia/device.go:96-105) */
+typedef struct {
+    int32_t ctr;      /* container index inside the pod, non-decreasing */
+    int32_t nums;     /* Nums  (>= 1: k8sutil/pod.go:33 drops the rest) */
+    int32_t memreq;   /* Memreq */
+    int32_t mempct;   /* MemPercentagereq, VGS_MEMPCT_UNSET when unset */
+    int32_t coresreq; /* Coresreq */
+    uint32_t flags;   /* VGS_REQ_* */
+    uint64_t typemask;
+} vgs_req;
+
+/* One pending pod = the [][]ContainerDeviceRequest of k8sutil.Resourcereqs
+ * (pkg/k8sutil/pod.go:26-40), flattened.  Containers without a request simply
+ * do not appear (score.go:195-198 gives them an empty device list). */
+typedef struct {
+    int32_t req_begin; /* first request in the reqs array */
+    int32_t n_reqs;    /* 1..VGS_MAX_REQS_PER_POD */
+} vgs_pod;
+
+/* winner of one pod: NodeScore of the best node (score.go:29-33,
+ * scheduler.go:386-387).  Ties: highest global row. */
+typedef struct {
+    int32_t best_row;  /* global row, -1 = no node fits */
+    float score;       /* NodeScore.score */
+    int32_t fit_count; /* len(*nodeScores): number of candidate nodes */
+    int32_t n_picks;   /* sum of nums over the pod's requests, 0 when no fit */
+} vgs_result;
+
+/* One util.ContainerDevice (pkg/util/types.go:85-91) of the winner: slot is the
+ * device's registration slot on that node (the caller maps it to the UUID). */
+typedef struct {
+    int32_t slot;
+    int32_t usedmem;
+    int32_t usedcores;
+} vgs_pick;
+
+/* usage change of one device: what addPod/delPod do to the next snapshot
+ * (scheduler.go:280-297). */
+typedef struct {
+    int32_t row; /* global row */
+    int32_t slot;
+    int32_t d_used;
+    int32_t d_usedmem;
+    int32_t d_usedcores;
+} vgs_delta;
+
+/* CUDA-event time of the most recent run of each phase on the context's
+ * stream (0 if the phase never ran). */
+typedef struct {
+    float snapshot_h2d_ms; /* vgs_snapshot_upload / _set_device copies */
+    float derive_ms;       /* snapshot preparation kernel (K0) */
+    float pods_h2d_ms;     /* request records host -> device */
+    float score_ms;        /* score kernels (K1) incl. key reset */
+    float resolve_ms;      /* resolve kernel (K3) incl. pick reset */
+    float d2h_ms;          /* results device -> host */
+    int32_t kernel_launches; /* kernels launched since vgs_init (cumulative) */
+    int32_t reserved;
+} vgs_timing;
+
+/* ---- lifetime ----------------------------------------------------------- */
+int vgs_abi_version(void);
+const char *vgs_strerror(int status);
+int vgs_init(const vgs_config *cfg, vgs_ctx **out);
+void vgs_destroy(vgs_ctx *ctx);
+const char *vgs_last_error(vgs_ctx *ctx);
+
+/* ---- snapshot: replaces the per-Filter rebuild in getNodesUsage
+ *      (scheduler.go:249-310) with a device-resident copy -------------------- */
+/* planes[f] is node-major: planes[f][row * dmax + slot]; ndev[row] =
+ * len(node.Devices).  Copies, prepares the walk-ordered planes on the GPU,
+ * validates ranges.  Blocks until done. */
+int vgs_snapshot_upload(vgs_ctx *ctx, int32_t n_nodes, int32_t dmax,
+                        const int32_t *const planes[VGS_NUM_PLANES], const int32_t *ndev,
+                        uint64_t *out_version);
+/* same, from planes that already live in this GPU's memory */
+int vgs_snapshot_set_device(vgs_ctx *ctx, int32_t n_nodes, int32_t dmax,
+                            const int32_t *const dev_planes[VGS_NUM_PLANES],
+                            const int32_t *dev_ndev, uint64_t *out_version);
+int vgs_snapshot_delta(vgs_ctx *ctx, int32_t n, const vgs_delta *deltas);
+/* read the resident planes back (testing the delta path) */
+int vgs_snapshot_download(vgs_ctx *ctx, int32_t *const planes[VGS_NUM_PLANES], int32_t *ndev);
+
+/* ---- scoring: replaces calcScore (score.go:183-214) + the pick
+ *      (scheduler.go:386-387) for a batch of pods against one snapshot -------- */
+/* results[n_pods]; picks[sum of nums], request-major: request r owns
+ * picks[B(r) .. B(r)+nums), B = exclusive prefix sum of nums over reqs[]. */
+int vgs_score_batch(vgs_ctx *ctx, int32_t n_pods, const vgs_pod *pods, int32_t n_reqs,
+                    const vgs_req *reqs, vgs_result *results, vgs_pick *picks);
+
+/* the same pass in separate phases (resident benchmarking, node sharding) */
+int vgs_pods_upload(vgs_ctx *ctx, int32_t n_pods, const vgs_pod *pods, int32_t n_reqs,
+                    const vgs_req *reqs);
+int vgs_score_resident(vgs_ctx *ctx);   /* score kernels -> per-pod candidate keys */
+int vgs_resolve_resident(vgs_ctx *ctx); /* winners owned by this shard -> results, picks */
+int vgs_results_download(vgs_ctx *ctx, vgs_result *results, vgs_pick *picks);
+int vgs_sync(vgs_ctx *ctx);
+
+/* node sharding: per-pod candidate key = (ordered score bits << 32) | global
+ * row, 0 = none; max over shards = the global winner under the canonical tie
+ * rule.  keys_device returns this GPU's array of max_pods uint64 (allgather
+ * it), keys_merge takes the gathered [n_shards][stride] array (device memory)
+ * and reduces it back into the context; counts_* likewise for fit_count. */
+int vgs_keys_device(vgs_ctx *ctx, uint64_t **dev_keys, int32_t **dev_counts);
+int vgs_keys_merge(vgs_ctx *ctx, const uint64_t *dev_gathered_keys,
+                   const int32_t *dev_gathered_counts, int32_t n_shards, int32_t stride);
+/* device arrays behind vgs_results_download (shard combine of results/picks) */
+int vgs_results_device(vgs_ctx *ctx, vgs_result **dev_results, vgs_pick **dev_picks);
+
+/* verify mode (cfg.verify != 0): fit_bitmap[n_pods][ceil32(n_nodes)] words,
+ * bit (row & 31) of word row/32; scores[n_pods][n_nodes], 0 when not fit. */
+int vgs_verify_download(vgs_ctx *ctx, uint32_t *fit_bitmap, float *scores);
+
+int vgs_last_timing(vgs_ctx *ctx, vgs_timing *out);
+
+/* ---- host-side policy helpers (what the Go shim keeps in Go) ----------------
+ * bit t = checkType pass for device type string types[t] under the pod's
+ * annotations; NULL annotation = key absent.  Mirrors score.go:71-84 with the
+ * NVIDIA vendor (nvidia/device.go:62-94,107-112). */
+uint64_t vgs_host_typemask(const char *req_type, const char *use_gputype,
+                           const char *nouse_gputype, const char *const *types, int32_t n_types);
+/* nvidia/device.go:96-105 assertNuma */
+int32_t vgs_host_numa_bind(const char *numa_bind_anno);
+/* util.EncodePodDevices (pkg/util/util.go:110-126): "UUID,Type,mem,cores:" per
+ * pick, ';' between containers.  Returns length or VGS_ETOOBIG. */
+int32_t vgs_host_encode_pod_devices(int32_t n_ctrs, const int32_t *picks_per_ctr,
+                                    const char *const *uuids, const char *const *types,
+                                    const vgs_pick *picks, char *out, int32_t cap);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VGPUSCORE_H */

@@ -1,0 +1,6 @@
+"""TEST INFRASTRUCTURE ONLY -- CPU oracle of the Filter scoring pass.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+legs may import this package.  PARITY UNPINNED (see oracle/score_ref.h).
+"""
+from .ref import build, score_faithful, score_packed, typemask  # noqa: F401

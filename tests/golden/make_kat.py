@@ -1,0 +1,101 @@
+"""Writes tests/golden/kat.json: the hand-derived known-answer vectors of SURVEY.md 8(c).
+
+The expected values are LITERALS transcribed from the survey's table (derived by hand
+from pkg/scheduler/score.go), not outputs of the oracle or of the GPU path.  The
+reference has no test for pkg/scheduler and cannot be run here (no Go toolchain), so
+these vectors are the only pin the oracle has ("parity unpinned").
+
+node = 8 device slots, Count=10, Totalmem=32768, Totalcore=100, Numa=0,
+Type "NVIDIA-Tesla V100-PCIE-32GB", idle unless stated.
+request = (Nums, Memreq, MemPercentagereq, Coresreq); pick = (slot, Usedmem, Usedcores).
+"""
+import json
+import os
+
+V100 = "NVIDIA-Tesla V100-PCIE-32GB"
+A100 = "NVIDIA-NVIDIA A100-SXM4-40GB"
+
+
+def node(**over):
+    devs = []
+    for s in range(8):
+        d = dict(Used=0, Count=10, Usedmem=0, Totalmem=32768, Usedcores=0, Totalcore=100, Numa=0, Type=V100)
+        for k, v in over.items():
+            d[k] = v[s] if isinstance(v, (list, tuple)) else v
+        devs.append(d)
+    return devs
+
+
+def kat(name, devices, containers, annos, fit, bits=None, picks=None, n_nodes=1, best_row=None, cite=""):
+    return dict(name=name, n_nodes=n_nodes, devices=devices, containers=containers, annos=annos, fit=fit,
+                score_bits=bits, picks=picks, best_row=(best_row if best_row is not None else (0 if fit else -1)),
+                cite=cite)
+
+
+U = 101
+mixed_types = [V100] * 4 + [A100] * 4
+KATS = [
+    kat("1_baseline_cfg1_64_idle_nodes", node(), [[(1, 3000, U, 30)]], {}, True, "0x41000000", [[(7, 3000, 30)]],
+        n_nodes=64, best_row=63, cite="examples/nvidia/default_use.yaml; all 64 nodes tie -> highest row"),
+    kat("2_two_devices_spread", node(Used=[3, 0, 5, 0, 1, 2, 9, 10]), [[(2, 3000, U, 30)]], {}, True, "0x40e00000",
+        [[(3, 3000, 30), (1, 3000, 30)]], cite="equal free slots -> later slot first (stable sort + reverse walk)"),
+    kat("3_three_devices", node(Used=[3, 0, 5, 0, 1, 2, 9, 10]), [[(3, 3000, U, 30)]], {}, True, "0x40c11a7c",
+        [[(3, 3000, 30), (1, 3000, 30), (4, 3000, 30)]], cite="30/29 + 5"),
+    kat("4_two_containers_order_persists", node(), [[(1, 1000, U, 0)], [(1, 1000, U, 0)]], {}, True, "0x41800000",
+        [[(7, 1000, 0)], [(6, 1000, 0)]], cite="score.go:165 sorts in place; slot 7 moves to the front after ctr 0"),
+    kat("5_exclusive", node(Used=[1, 1, 1, 0, 1, 1, 1, 1], Usedcores=[10, 10, 10, 0, 10, 10, 10, 10]),
+        [[(1, 0, 100, 100)]], {}, True, "0x41000000", [[(3, 32768, 100)]], cite="score.go:128"),
+    kat("6_mem_percentage_hetero", node(Totalmem=[16384] * 4 + [40960] * 2 + [81920] * 2, Used=[0, 0, 0, 0, 0, 0, 2, 2]),
+        [[(2, 0, 50, 0)]], {}, True, "0x40e00000", [[(5, 20480, 0), (4, 20480, 0)]], cite="score.go:119 per device"),
+    kat("7_cores0_on_full_gpu", node(Usedcores=100, Used=1), [[(1, 1000, U, 0)]], {}, False, cite="score.go:132"),
+    kat("8_numa_bind", node(Numa=[0, 0, 0, 0, 1, 1, 1, 1], Used=[0, 0, 0, 0, 10, 10, 10, 0]), [[(2, 1000, U, 0)]],
+        {"nvidia.com/numa-bind": "true"}, True, "0x40e00000", [[(3, 1000, 0), (2, 1000, 0)]],
+        cite="score.go:99-104: slot 7 taken, then discarded at the numa change"),
+    kat("8b_no_numa_bind", node(Numa=[0, 0, 0, 0, 1, 1, 1, 1], Used=[0, 0, 0, 0, 10, 10, 10, 0]), [[(2, 1000, U, 0)]],
+        {}, True, "0x40e00000", [[(7, 1000, 0), (3, 1000, 0)]]),
+    kat("9_use_gputype", node(Type=mixed_types), [[(1, 1000, U, 0)]], {"nvidia.com/use-gputype": "a100"}, True,
+        "0x41000000", [[(7, 1000, 0)]], cite="nvidia/device.go:63-77 case-insensitive"),
+    kat("10_nouse_gputype", node(Type=mixed_types), [[(1, 1000, U, 0)]], {"nvidia.com/nouse-gputype": "A100,T4"}, True,
+        "0x41000000", [[(3, 1000, 0)]], cite="nvidia/device.go:78-92"),
+    kat("11_more_than_devices", node(), [[(9, 1000, U, 0)]], {}, False, cite="score.go:162"),
+    kat("12_no_memory_left", node(Usedmem=32000, Used=1), [[(1, 1000, U, 0)]], {}, False, cite="score.go:121"),
+    kat("13_container_without_gpu", node(), [[], [(2, 2000, U, 0)]], {}, True, "0x40e00000",
+        [[], [(7, 2000, 0), (6, 2000, 0)]], cite="score.go:195-198"),
+    kat("14_cores_over_100", node(), [[(1, 1000, U, 101)]], {}, False, cite="score.go:110-113"),
+    kat("15_all_eight", node(Used=[0, 1, 2, 3, 4, 5, 6, 7]), [[(8, 100, U, 5)]], {}, True, "0x3fc4ec4f",
+        [[(s, 100, 5) for s in range(8)]], cite="80/52 + 0"),
+]
+
+# string-policy truth table (nvidia/device.go:62-105), each line derived by hand
+POLICY = [
+    # (annos, card type, expected pass)
+    ({}, V100, True),
+    ({"nvidia.com/use-gputype": "v100"}, V100, True),
+    ({"nvidia.com/use-gputype": "A100"}, V100, False),
+    ({"nvidia.com/use-gputype": "A100,v100"}, V100, True),
+    ({"nvidia.com/use-gputype": ""}, V100, True),            # strings.Contains(x, "") is true
+    ({"nvidia.com/use-gputype": "A100,"}, V100, True),       # trailing comma -> empty token matches
+    ({"nvidia.com/nouse-gputype": "A100,"}, V100, False),    # ... and excludes everything for nouse
+    ({"nvidia.com/nouse-gputype": "a100"}, A100, False),
+    ({"nvidia.com/nouse-gputype": "a100"}, V100, True),
+    ({"nvidia.com/use-gputype": "v100", "nvidia.com/nouse-gputype": "v100"}, V100, True),   # use wins
+    ({"nvidia.com/use-gputype": "a100", "nvidia.com/nouse-gputype": "t4"}, V100, False),    # nouse not consulted
+    ({"nvidia.com/use-gputype": "Tesla V100"}, V100, True),
+    ({"nvidia.com/use-gputype": "tesla-v100"}, V100, False),
+]
+NUMA = [("true", 1), ("True", 1), ("TRUE", 1), ("t", 1), ("T", 1), ("1", 1), ("false", 0), ("0", 0), ("yes", 0),
+        ("tRuE", 0), ("", 0), (None, 0)]
+
+# pkg/util/util_test.go:42-56 (TestPodDevicesCoding) -- the one golden string the reference's
+# own tests imply for the result wire format, via util.go:110-126
+ENCODE = [
+    ([[("UUID1", "Type1", 1000, 30)], [], [("UUID1", "Type1", 1000, 30)]], "UUID1,Type1,1000,30:;;UUID1,Type1,1000,30:"),
+    ([], ""),
+    ([[]], ""),
+]
+
+if __name__ == "__main__":
+    out = os.path.join(os.path.dirname(os.path.abspath(__file__)), "kat.json")
+    with open(out, "w") as f:
+        json.dump(dict(kats=KATS, policy=POLICY, numa=NUMA, encode=ENCODE), f, indent=1)
+    print("wrote", out, len(KATS), "KATs")

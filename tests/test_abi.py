@@ -1,0 +1,81 @@
+"""The C-ABI library loads and exports every symbol include/vgpuscore.h declares (no GPU needed)."""
+import ctypes
+import os
+import re
+
+import numpy as np
+
+import vgpu_b200 as v
+from helpers import load_kats
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    src = open(os.path.join(ROOT, "include", "vgpuscore.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(vgs_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_exports(built):
+    lib = v.load_library()
+    names = declared_symbols()
+    assert len(names) >= 20
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/vgpuscore.h but not exported"
+    assert set(names) == set(v.capi.EXPORTS)
+    assert lib.vgs_abi_version() == 1
+    assert lib.vgs_strerror(0) == b"ok"
+
+
+def test_struct_layouts(built):
+    assert ctypes.sizeof(v.capi.VgsConfig) == 40
+    assert ctypes.sizeof(v.capi.VgsTiming) == 32
+    assert v.capi.REQ_DTYPE.itemsize == 32 and v.capi.REQ_DTYPE.fields["typemask"][1] == 24
+    assert v.capi.DELTA_DTYPE.itemsize == 20
+
+
+def test_init_without_gpu_fails_loudly(built):
+    import torch
+    if torch.cuda.is_available():
+        return
+    try:
+        v.Context(max_nodes=16)
+    except v.VgsError as e:
+        assert e.code == v.capi.VGS_ECUDA
+    else:
+        raise AssertionError("vgs_init must fail without a GPU (no CPU fallback)")
+
+
+def test_host_policy_matches_truth_table_and_oracle(built):
+    import oracle
+    K = load_kats()
+    for annos, card, want in K["policy"]:
+        m = v.capi.host_typemask("NVIDIA", annos, [card])
+        assert bool(m & 1) == want, (annos, card)
+        assert m == oracle.typemask(annos, "NVIDIA", [card])[0]
+    for val, want in K["numa"]:
+        annos = {} if val is None else {"nvidia.com/numa-bind": val}
+        assert v.capi.host_numa_bind(annos) == want, val
+    names = [t for t, _ in v.workload.GPU_TYPES]
+    _, batch = v.workload.make_config("cfg3", 8, 512)
+    for an in batch.annos:
+        assert v.capi.host_typemask("NVIDIA", an, names) == oracle.typemask(an, "NVIDIA", names)[0]
+    assert v.capi.host_typemask("MLU", {}, ["MLU370"]) == 0
+
+
+def test_encode_pod_devices_golden(built):
+    for ctrs, want in load_kats()["encode"]:
+        assert v.capi.encode_pod_devices([[tuple(d) for d in c] for c in ctrs]) == want
+
+
+def test_pack_batch_layout(built):
+    _, batch = v.workload.make_config("cfg4", 8, 50)
+    pods, reqs = v.capi.pack_batch(batch, [t for t, _ in v.workload.GPU_TYPES])
+    assert len(pods) == 50 and int(pods["n_reqs"].sum()) == len(reqs)
+    for p in range(50):
+        r0, n = int(pods["req_begin"][p]), int(pods["n_reqs"][p])
+        ctr = reqs["ctr"][r0:r0 + n]
+        assert ctr[0] == 0 and (np.diff(ctr) >= 0).all()
+    numa = np.array([1 if a else 0 for a in batch.annos])
+    assert numa.sum() > 0

@@ -1,0 +1,261 @@
+"""Parity tests proper: the CUDA path through the C ABI against the CPU oracle, bit-exact
+(winner row, score bits, fit counts, device picks, and in verify mode the whole
+pod x node fit bitmap and score matrix)."""
+import numpy as np
+import pytest
+
+import oracle
+import vgpu_b200 as v
+from helpers import assert_same, check_kat, kat_inputs, load_kats
+
+pytestmark = pytest.mark.gpu
+K = load_kats()
+
+
+def gpu_score(snap, batch, verify=True, **kw):
+    with v.Context(max_nodes=max(snap.n_nodes, 1), max_devices=snap.dmax, max_pods=max(batch.n_pods, 1),
+                   max_reqs=max(batch.n_reqs, batch.n_pods, 1), max_picks=max(int(batch.nums.sum()), batch.n_reqs, 1),
+                   verify=verify, **kw) as ctx:
+        ctx.upload(snap)
+        return ctx.score(batch)
+
+
+@pytest.mark.parametrize("k", K["kats"], ids=[k["name"] for k in K["kats"]])
+def test_kat_gpu(built, k):
+    snap, batch = kat_inputs(k)
+    check_kat(k, gpu_score(snap, batch), batch)
+
+
+@pytest.mark.parametrize("cfg,n,p", [("cfg1", 64, 1), ("cfg2", 10_000, 256), ("cfg3", 5000, 400),
+                                     ("cfg3", 33, 31), ("cfg4", 4000, 300), ("cfg4", 1000, 33)])
+def test_differential_full_matrix(built, cfg, n, p):
+    snap, batch = v.workload.make_config(cfg, n, p)
+    got = gpu_score(snap, batch)
+    want = oracle.score_packed(snap, batch, full=True)
+    assert_same(got, want, f"{cfg} {n}x{p}")
+    assert want.fit.any()
+
+
+def test_faithful_oracle_agrees_with_gpu(built):
+    """string/pointer restatement (R1) vs the GPU path incl. host-built type masks"""
+    snap, batch = v.workload.make_config("cfg3", 1500, 200)
+    assert_same(gpu_score(snap, batch), oracle.score_faithful(snap, batch, full=True), "R1")
+    snap, batch = v.workload.make_config("cfg4", 800, 100)
+    assert_same(gpu_score(snap, batch), oracle.score_faithful(snap, batch, full=True), "R1 multi")
+
+
+def _random_snapshot(rng, n, dmax, ragged=True, numa_vals=3, types=5):
+    planes = np.zeros((8, n, dmax), np.int32)
+    count = rng.integers(1, 12, (n, dmax))
+    planes[1] = count
+    planes[0] = np.minimum(rng.integers(0, 14, (n, dmax)), count + rng.integers(0, 2, (n, dmax)))
+    totalmem = rng.choice([8000, 16000, 32768, 81920], (n, dmax))
+    planes[3] = totalmem
+    planes[2] = (totalmem * rng.random((n, dmax)) * (planes[0] > 0)).astype(np.int32)
+    totalcore = rng.choice([100, 100, 100, 200, 0], (n, dmax))
+    planes[5] = totalcore
+    planes[4] = np.minimum(totalcore, rng.choice([0, 0, 10, 50, 100, 200], (n, dmax))) * (planes[0] > 0)
+    planes[6] = rng.integers(0, numa_vals, (n, dmax)) * 3 - 1  # includes numa -1
+    planes[7] = rng.integers(0, types, (n, dmax))
+    ndev = rng.integers(0, dmax + 1, n).astype(np.int32) if ragged else np.full(n, dmax, np.int32)
+    names = ["NVIDIA-Tesla V100", "NVIDIA-NVIDIA A100-SXM4-40GB", "NVIDIA-Tesla T4", "MLU370-X8", "NVIDIA-NVIDIA H100"][:types]
+    return v.Snapshot(planes, ndev, names)
+
+
+def _random_pods(rng, p, dmax, max_ctrs=4):
+    pods = []
+    for _ in range(p):
+        ctrs = []
+        for _ in range(int(rng.integers(1, max_ctrs + 1))):
+            if rng.random() < 0.15:
+                ctrs.append([])
+                continue
+            nums = int(rng.choice([1, 1, 2, 3, dmax, dmax + 1]))
+            if rng.random() < 0.5:
+                mem, pct = int(rng.choice([0, 500, 4000, 20000])), 101
+            else:
+                mem, pct = 0, int(rng.choice([0, 10, 50, 100, 101]))
+            cores = int(rng.choice([0, 0, 10, 50, 100, 101]))
+            ctrs.append([(nums, mem, pct, cores)])
+        if not any(ctrs):
+            ctrs.append([(1, 0, 101, 0)])
+        annos = {}
+        r = rng.random()
+        if r < 0.2:
+            annos["nvidia.com/use-gputype"] = str(rng.choice(["a100", "V100,t4", "h100,", "mlu"]))
+        elif r < 0.4:
+            annos["nvidia.com/nouse-gputype"] = str(rng.choice(["a100", "V100,t4", "T4"]))
+        if rng.random() < 0.35:
+            annos["nvidia.com/numa-bind"] = str(rng.choice(["true", "1", "false", "T"]))
+        pods.append({"containers": ctrs, "annos": annos})
+    return v.PodBatch.from_pods(pods)
+
+
+@pytest.mark.parametrize("dmax,seed", [(8, 1), (8, 2), (4, 3), (12, 4), (12, 5), (1, 6), (7, 7)])
+def test_random_ragged_edge_cases(built, dmax, seed):
+    """ragged nodes (0..dmax devices), hetero Count/Totalcore, negative numa ids, every
+    request shape incl. Nums > devices, Coresreq > 100, empty containers, numa-bind"""
+    rng = np.random.default_rng(seed)
+    snap = _random_snapshot(rng, 777, dmax)
+    batch = _random_pods(rng, 150, dmax)
+    got = gpu_score(snap, batch)
+    assert_same(got, oracle.score_packed(snap, batch, full=True), f"dmax={dmax}")
+    assert_same(got, oracle.score_faithful(snap, batch, full=True), f"dmax={dmax} R1")
+
+
+def test_multi_request_container(built):
+    """two requests inside ONE container (the second sees the first's usage; sums spans both)"""
+    rng = np.random.default_rng(11)
+    snap = _random_snapshot(rng, 500, 8, ragged=False, types=3)
+    pods = [{"containers": [[(2, 1000, 101, 10), (1, 0, 50, 0)], [(1, 100, 101, 0)]]},
+            {"containers": [[(5, 100, 101, 0), (5, 100, 101, 0)]]},  # sums > len(devices): negative tail
+            {"containers": [[(1, 100, 101, 0), (1, 100, 101, 0), (1, 100, 101, 0)]], "annos": {"nvidia.com/numa-bind": "true"}}]
+    batch = v.PodBatch.from_pods(pods)
+    assert_same(gpu_score(snap, batch), oracle.score_packed(snap, batch, full=True), "multi-req")
+
+
+def test_empty_and_tiny(built):
+    _, batch = v.workload.make_config("cfg3", 8, 40)
+    empty = v.Snapshot(np.zeros((8, 0, 8), np.int32), np.zeros(0, np.int32), [t for t, _ in v.workload.GPU_TYPES])
+    got = gpu_score(empty, batch, verify=False)
+    assert (got.best_row == -1).all() and (got.fit_count == 0).all()
+    snap, one = v.workload.make_config("cfg3", 1, 1)
+    assert_same(gpu_score(snap, one), oracle.score_packed(snap, one, full=True), "1x1")
+
+
+def test_error_codes(built):
+    snap, batch = v.workload.make_config("cfg2", 100, 4)
+    names = snap.type_names
+    with v.Context(max_nodes=100, max_pods=4) as ctx:
+        pods, reqs = v.capi.pack_batch(batch, names)
+        with pytest.raises(v.VgsError) as e:
+            ctx.score_packed(pods, reqs)  # no snapshot yet
+        assert e.value.code == v.capi.VGS_ESTATE
+        ctx.upload(snap)
+        bad = reqs.copy()
+        bad["nums"][0] = 0
+        with pytest.raises(v.VgsError) as e:
+            ctx.score_packed(pods, bad)
+        assert e.value.code == v.capi.VGS_EINVAL
+        big, _ = v.workload.make_config("cfg2", 101, 1)
+        with pytest.raises(v.VgsError) as e:
+            ctx.upload(big)
+        assert e.value.code == v.capi.VGS_ETOOBIG
+        rng = snap.planes.copy()
+        rng[1, 5, 2] = 1 << 21
+        with pytest.raises(v.VgsError) as e:
+            ctx.upload(v.Snapshot(rng, snap.ndev, names))
+        assert e.value.code == v.capi.VGS_ERANGE
+        nd = snap.ndev.copy()
+        nd[3] = 9
+        with pytest.raises(v.VgsError) as e:
+            ctx.upload(v.Snapshot(snap.planes, nd, names))
+        assert e.value.code == v.capi.VGS_EDMAX
+        ctx.upload(snap)  # context still usable
+        assert_same(ctx.score(batch), oracle.score_packed(snap, batch), "after errors")
+    with pytest.raises(v.VgsError) as e:
+        v.Context(max_nodes=10, max_devices=13)
+    assert e.value.code == v.capi.VGS_EDMAX
+
+
+def test_delta_equals_rebuild(built):
+    """commit the winners as usage deltas (addPod) == re-uploading a rebuilt snapshot"""
+    snap, batch = v.workload.make_config("cfg4", 3000, 64)
+    with v.Context(max_nodes=3000, max_pods=64, max_reqs=512, max_picks=1024, verify=True) as ctx:
+        ctx.upload(snap)
+        first = ctx.score(batch)
+        planes = snap.planes.copy()
+        deltas = []
+        pb = batch.pick_begin
+        for p in range(batch.n_pods):
+            if first.best_row[p] < 0:
+                continue
+            r0, r1 = batch.pod_req_range(p)
+            for r in range(r0, r1):
+                for j in range(int(batch.nums[r])):
+                    s, m, c = (int(x) for x in first.picks[int(pb[r]) + j])
+                    row = int(first.best_row[p])
+                    deltas.append((row, s, 1, m, c))
+                    planes[0, row, s] += 1
+                    planes[2, row, s] += m
+                    planes[4, row, s] += c
+        ctx.delta(np.array(deltas, dtype=v.capi.DELTA_DTYPE))
+        got_planes, got_ndev = ctx.download_snapshot()
+        assert np.array_equal(got_planes, planes) and np.array_equal(got_ndev, snap.ndev)
+        rebuilt = v.Snapshot(planes, snap.ndev, snap.type_names)
+        after = ctx.score(batch)
+        assert_same(after, oracle.score_packed(rebuilt, batch, full=True), "after delta")
+        # undo (delPod) -> original answers again
+        undo = np.array([(r, s, -1, -m, -c) for r, s, _, m, c in deltas], dtype=v.capi.DELTA_DTYPE)
+        ctx.delta(undo)
+        assert_same(ctx.score(batch), first, "after undo")
+
+
+def test_shards_on_one_gpu_equal_single(built):
+    """3 row shards (3 contexts on one GPU) + key merge == one context; 1-GPU result is the oracle"""
+    import torch
+    snap, batch = v.workload.make_config("cfg4", 5000, 96)
+    single = gpu_score(snap, batch, verify=False)
+    pods, reqs = v.capi.pack_batch(batch, snap.type_names)
+    G, P = 3, batch.n_pods
+    n_picks = int(reqs["nums"].sum())
+    ctxs = []
+    for g in range(G):
+        lo, hi = v.sharding.shard_range(snap.n_nodes, G, g)
+        c = v.Context(max_nodes=hi - lo, max_pods=P, max_reqs=len(reqs), max_picks=n_picks, row_base=lo)
+        c.upload(snap.rows(lo, hi))
+        c.pods_upload(pods, reqs)
+        c.score_resident()
+        c.sync()
+        ctxs.append(c)
+    dev = torch.device("cuda", 0)
+    gk = torch.zeros((G, P), dtype=torch.int64, device=dev)
+    gc = torch.zeros((G, P), dtype=torch.int32, device=dev)
+    for g, c in enumerate(ctxs):
+        kp, cp = c.keys_device()
+        gk[g] = v.sharding.device_view(kp, P, torch.int64, dev)
+        gc[g] = v.sharding.device_view(cp, P, torch.int32, dev)
+    torch.cuda.synchronize()
+    picks = np.zeros((n_picks, 3), np.int32)
+    res = None
+    for c in ctxs:
+        c.keys_merge(gk.data_ptr(), gc.data_ptr(), G, P)
+        c.resolve_resident()
+        r, pk = c.results_download()
+        picks += np.stack([pk["slot"], pk["usedmem"], pk["usedcores"]], axis=1)
+        res = r if res is None else res
+        assert np.array_equal(r, res)
+        c.close()
+    assert np.array_equal(res["best_row"], single.best_row)
+    assert np.array_equal(res["score"].view(np.uint32), single.score.view(np.uint32))
+    assert np.array_equal(res["fit_count"], single.fit_count)
+    assert np.array_equal(picks, single.picks)
+
+
+def test_full_size_properties(built):
+    """BASELINE config 3 at full size (100k nodes x 4096 pods): properties that do not need
+    the oracle over all 4e8 pairs -- determinism, a sampled-pod oracle check over all
+    nodes, and every winner re-checked by the oracle on its own node."""
+    snap, batch = v.workload.make_config("cfg3")
+    with v.Context(max_nodes=snap.n_nodes, max_pods=batch.n_pods) as ctx:
+        ctx.upload(snap)
+        a = ctx.score(batch)
+        b = ctx.score(batch)
+    assert_same(a, b, "idempotence")
+    assert (a.best_row >= 0).mean() > 0.9
+    idx = list(range(0, batch.n_pods, 64))
+    sub = batch.select(idx)
+    want = oracle.score_packed(snap, sub)
+    assert np.array_equal(a.best_row[idx], want.best_row)
+    assert np.array_equal(a.score[idx].view(np.uint32), want.score.view(np.uint32))
+    assert np.array_equal(a.fit_count[idx], want.fit_count)
+    # every pod: oracle on the winner node alone must reproduce score and picks
+    pb = batch.pick_begin
+    placed = np.nonzero(a.best_row >= 0)[0]
+    for p in placed[:: max(1, len(placed) // 512)]:
+        row = int(a.best_row[p])
+        one = oracle.score_packed(snap.rows(row, row + 1), batch.select([int(p)]))
+        assert one.best_row[0] == 0
+        assert one.score.view(np.uint32)[0] == a.score.view(np.uint32)[p]
+        r0, r1 = batch.pod_req_range(int(p))
+        assert np.array_equal(one.picks, a.picks[int(pb[r0]):int(pb[r1])])
