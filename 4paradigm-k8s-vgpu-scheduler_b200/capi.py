@@ -22,7 +22,7 @@ VGS_REQ_NUMA_BIND = 1
 # every symbol include/vgpuscore.h declares
 EXPORTS = (
     "vgs_abi_version", "vgs_strerror", "vgs_init", "vgs_destroy", "vgs_last_error",
-    "vgs_snapshot_upload", "vgs_snapshot_set_device", "vgs_snapshot_delta", "vgs_snapshot_download",
+    "vgs_snapshot_upload", "vgs_snapshot_set_device", "vgs_snapshot_refresh", "vgs_snapshot_delta", "vgs_snapshot_download",
     "vgs_score_batch", "vgs_pods_upload", "vgs_score_resident", "vgs_resolve_resident",
     "vgs_results_download", "vgs_sync", "vgs_keys_device", "vgs_keys_merge", "vgs_results_device",
     "vgs_verify_download", "vgs_last_timing", "vgs_host_typemask", "vgs_host_numa_bind",
@@ -80,6 +80,7 @@ def load_library() -> C.CDLL:
     lib.vgs_last_error.restype = C.c_char_p
     lib.vgs_snapshot_upload.argtypes = [vp, i32, i32, C.POINTER(vp), vp, u64p]
     lib.vgs_snapshot_set_device.argtypes = [vp, i32, i32, C.POINTER(vp), vp, u64p]
+    lib.vgs_snapshot_refresh.argtypes = [vp]
     lib.vgs_snapshot_delta.argtypes = [vp, i32, vp]
     lib.vgs_snapshot_download.argtypes = [vp, C.POINTER(vp), vp]
     lib.vgs_score_batch.argtypes = [vp, i32, vp, i32, vp, vp, vp]
@@ -237,6 +238,9 @@ class Context:
         self._check(fn(self.h, n_nodes, dmax, ptrs, C.c_void_p(ndev_ptr), C.byref(ver)))
         self.n_nodes, self.dmax = n_nodes, dmax
         return ver.value
+
+    def refresh(self):
+        self._check(self.lib.vgs_snapshot_refresh(self.h))
 
     def delta(self, deltas: np.ndarray):
         deltas = np.ascontiguousarray(deltas, dtype=DELTA_DTYPE)

@@ -319,6 +319,18 @@ int vgs_snapshot_set_device(vgs_ctx *c, int32_t n_nodes, int32_t dmax,
     return snapshot_common(c, n_nodes, dmax, dev_planes, dev_ndev, cudaMemcpyDeviceToDevice, out_version);
 }
 
+int vgs_snapshot_refresh(vgs_ctx *c) {
+    if (!c) return VGS_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard g(c->cfg.device);
+    if (!c->have_snapshot) return fail(c, VGS_ESTATE, "refresh before snapshot upload");
+    rec(c, EV_UP1);
+    int rc = prepare_all(c);
+    if (rc != VGS_OK) return rc;
+    rec(c, EV_DR1);
+    return VGS_OK;
+}
+
 int vgs_snapshot_delta(vgs_ctx *c, int32_t n, const vgs_delta *deltas) {
     if (!c) return VGS_EINVAL;
     std::lock_guard<std::mutex> lk(c->mu);

@@ -1,0 +1,320 @@
+#!/usr/bin/env python
+"""bench.py -- pod x node fit-evals/s of the Filter scoring pass (BASELINE.json metric).
+
+  python bench.py --gpus N --steps K --warmup W          (under torchrun for N > 1)
+  python bench.py --impl reference ...                   CPU arm: the oracle restatement
+
+Step = one pass of the hot path over one pod batch against the resident snapshot:
+K0 prepare (raw planes -> walk-ordered tiles) + K1 score + [all-gather + K2 merge for
+N > 1] + K3 resolve.  Workload at N=1 = BASELINE config 3 (100k nodes x 8 devices x
+4096 mixed pods); for N > 1 every rank holds its own 100k-node shard (weak scaling,
+N x 100k nodes in total) and the same 4096 pods.
+
+`value`   : device-timed (CUDA events per step on the launching stream, max over ranks),
+            inputs resident in HBM, L2 flushed between steps.
+`e2e`     : the same metric through the host-buffer C ABI calls the Go shim makes
+            (vgs_snapshot_upload + vgs_score_batch): pinned host planes and request
+            records in, results out, every step.
+`roofline`: the score kernels (K1) against the measured HBM peak, with the
+            algorithmic bytes of SURVEY 8(d).  The batch regime is integer-issue bound,
+            so this fraction is tiny by construction; see DESIGN.md.
+The reference (Go) cannot be built or run here; its CPU arm is the oracle's packed
+multi-threaded restatement ("port"), timed on this box's host cores.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "pod_x_node_fit_evals_per_sec"
+UNIT = "fit-evals/s"
+WORKLOAD = "cfg3: 100k nodes x 8 devices x 4096 mixed pods (mem MB / mem %, use/nouse-gputype, exclusive)"
+NODES_PER_GPU = 100_000
+N_PODS = 4096
+L2_FLUSH_BYTES = 256 << 20
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def algorithmic_bytes(n_nodes, dmax, n_pods, n_reqs):
+    # snapshot once + request records + results
+    r = n_reqs / max(n_pods, 1)
+    return n_nodes * (dmax * 32 + 4) + n_pods * (16 + r * 32) + n_pods * 80
+
+
+class ClockSampler:
+    """NVML sampling of SM clock / throttle reasons while the timed regions run."""
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._t = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4): "sw_power_cap",
+        }
+        while not self._stop.is_set():
+            try:
+                util = nv.nvmlDeviceGetUtilizationRates(self.h).gpu
+                mhz = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                self.samples.append((mhz, util))
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(0.02)
+
+    def start(self):
+        if self.nv:
+            self._t = threading.Thread(target=self._run, daemon=True)
+            self._t.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._t:
+            self._t.join()
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "samples": 0}
+        busy = [m for m, u in self.samples if u > 0] or [m for m, _ in self.samples]
+        busy.sort()
+        return {"sm_mhz": busy[len(busy) // 2], "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+def cpu_arm(snap, batch, n_pods_sample, threads=None):
+    """oracle packed restatement on a bounded sample: first n_pods_sample pods x all nodes"""
+    import oracle
+    sub = batch.select(list(range(min(n_pods_sample, batch.n_pods))))
+    t0 = time.perf_counter()
+    r = oracle.score_packed(snap, sub, threads=threads)
+    dt = time.perf_counter() - t0
+    return sub.n_pods * snap.n_nodes / r.seconds, r.threads, dt, sub.n_pods
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU algorithm (restated: no Go toolchain on this
+    image) on the host cores, rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import vgpu_b200 as v
+    snap, batch = v.workload.make_config("cfg3", NODES_PER_GPU, N_PODS)
+    threads = os.cpu_count() or 1
+    sample_pods = 128
+    for _ in range(max(args.warmup, 1)):
+        cpu_arm(snap, batch, 16, threads)
+    secs, evals = 0.0, 0
+    for _ in range(args.steps):
+        val, th, dt, sp = cpu_arm(snap, batch, sample_pods, threads)
+        evals += sp * snap.n_nodes
+        secs += sp * snap.n_nodes / val
+    value = evals / secs
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "sample": f"{sample_pods} pods x {snap.n_nodes} nodes per step"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
+                         "sample": f"{sample_pods} of {N_PODS} pods x all {snap.n_nodes} nodes per step, "
+                                   "oracle packed restatement (reference Go not runnable here)"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--nodes-per-gpu", type=int, default=NODES_PER_GPU)
+    ap.add_argument("--pods", type=int, default=N_PODS)
+    ap.add_argument("--config", default="cfg3")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    args.warmup = max(args.warmup, 3)
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    import vgpu_b200 as v
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA GPU: the scoring path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    v.load_library()
+
+    # ---- inputs: every rank builds its own shard (rows [rank*npg, (rank+1)*npg)) -------
+    npg = args.nodes_per_gpu
+    n_total = npg * world
+    snap = v.workload.make_snapshot(npg, v.workload.SEED + int(args.config[3:]) + 1000 * rank)
+    _, batch = v.workload.make_config(args.config, 8, args.pods)
+    pods, reqs = v.capi.pack_batch(batch, snap.type_names)
+    n_picks = int(reqs["nums"].sum())
+    P, R, D = len(pods), len(reqs), snap.dmax
+
+    sc = v.sharding.ShardedScorer(n_total, D, max_pods=P, max_reqs=max(R, P), max_picks=max(n_picks, R),
+                                  device=local, rank=rank, world=world)
+    ctx = sc.ctx
+    # pinned host copies (e2e leg) and the resident upload
+    pin_planes = torch.from_numpy(snap.planes).pin_memory()
+    pin_ndev = torch.from_numpy(snap.ndev).pin_memory()
+    plane_ptrs = [pin_planes[f].data_ptr() for f in range(8)]
+    ctx.upload_ptrs(npg, D, plane_ptrs, pin_ndev.data_ptr(), device=False)
+    ctx.pods_upload(pods, reqs)
+    flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step():
+        ctx.refresh()          # K0
+        sc.step_resident(n_picks)  # K1 (+ all-gather + K2) + K3
+
+    sampler = ClockSampler(local)
+    # ---- device-timed leg ---------------------------------------------------------------
+    for _ in range(args.warmup):
+        flush.zero_()
+        step()
+    barrier()
+    l0 = ctx.timing().kernel_launches
+    starts = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    ends = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    score_ms = []
+    sampler.start()
+    barrier()
+    for i in range(args.steps):
+        flush.zero_()          # evict the snapshot from L2 between steps (not timed)
+        starts[i].record()
+        step()
+        ends[i].record()
+        if i % 8 == 7 or i == args.steps - 1:
+            score_ms.append(ctx.timing().score_ms)  # syncs; last step's K1 time
+    barrier()
+    launches = ctx.timing().kernel_launches - l0
+    step_ms = [s.elapsed_time(e) for s, e in zip(starts, ends)]
+    total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)
+    k1_ms = torch.tensor([sum(score_ms) / len(score_ms)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(k1_ms, op=dist.ReduceOp.MAX)
+    total_ms, k1_ms = float(total_ms.item()), float(k1_ms.item())
+    ms_per_step = total_ms / args.steps
+    value = P * n_total / (ms_per_step * 1e-3)
+    results, picks = ctx.results_download()
+    placed = int((results["best_row"] >= 0).sum())
+
+    # ---- end-to-end leg: host buffers through the C ABI, every step -----------------------
+    e2e = None
+    if not args.no_e2e:
+        h2d = snap.planes.nbytes + snap.ndev.nbytes + pods.nbytes + reqs.nbytes
+        d2h = results.nbytes + picks.nbytes
+
+        def e2e_step():
+            ctx.upload_ptrs(npg, D, plane_ptrs, pin_ndev.data_ptr(), device=False)  # pinned H2D + K0
+            ctx.pods_upload(pods, reqs)
+            sc.step_resident(n_picks)
+            return ctx.results_download()
+
+        for _ in range(3):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        n_e2e = max(5, min(args.steps, 30))
+        for _ in range(n_e2e):
+            e2e_step()
+        barrier()
+        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        e2e = {"value": P * n_total / (float(dt.item()) / n_e2e), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+               "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * float(dt.item()) / n_e2e, "steps": n_e2e,
+               "api": "vgs_snapshot_upload + vgs_pods_upload/score/resolve/results_download (host buffers)"}
+    clocks = sampler.stop()
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peak, peak_src = measured_peak()
+    abytes = algorithmic_bytes(npg, D, P, R)
+    achieved = abytes / (k1_ms * 1e-3) / 1e9
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "k1_traffic.json")) as f:
+            traffic = json.load(f).get("dram_bytes_per_launch")
+    except Exception:
+        pass
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+        "config": {"workload": WORKLOAD if args.config == "cfg3" else args.config, "nodes_per_gpu": npg,
+                   "nodes_total": n_total, "devices_per_node": D, "pods": P, "requests": R,
+                   "parallelism": f"node-shard x{world}", "l2": "256 MiB memset between steps (untimed)",
+                   "placed_pods": placed},
+        "e2e": e2e,
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": {"bound": "hbm", "kernel": "k1_score_single (both launches of one step)",
+                     "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes": int(abytes),
+                     "kernel_ms": k1_ms,
+                     "note": "batch regime is integer-issue bound (SURVEY F6): see alu below and DESIGN.md"},
+        "device_evals_per_s": P * n_total * D / (ms_per_step * 1e-3),
+    }
+    if not args.no_cpu:
+        val, th, dt, sp = cpu_arm(snap, batch, 64)   # calibrate
+        sample = max(64, min(P, int(64 * 12.0 / max(dt, 1e-3))))
+        val, th, dt, sp = cpu_arm(snap, batch, sample)
+        line["cpu_baseline"] = {"value": val, "unit": UNIT, "cores": th, "kind": "port",
+                                "sample": f"first {sp} of {P} pods x all {npg} nodes ({dt:.1f} s), oracle packed "
+                                          "restatement; reference Go not runnable here"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -169,6 +169,9 @@ int vgs_snapshot_upload(vgs_ctx *ctx, int32_t n_nodes, int32_t dmax,
 int vgs_snapshot_set_device(vgs_ctx *ctx, int32_t n_nodes, int32_t dmax,
                             const int32_t *const dev_planes[VGS_NUM_PLANES],
                             const int32_t *dev_ndev, uint64_t *out_version);
+/* re-run the preparation kernel over the resident planes (asynchronous; a range
+ * error surfaces at the next vgs_results_download) */
+int vgs_snapshot_refresh(vgs_ctx *ctx);
 int vgs_snapshot_delta(vgs_ctx *ctx, int32_t n, const vgs_delta *deltas);
 /* read the resident planes back (testing the delta path) */
 int vgs_snapshot_download(vgs_ctx *ctx, int32_t *const planes[VGS_NUM_PLANES], int32_t *ndev);

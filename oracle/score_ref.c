@@ -571,6 +571,11 @@ typedef struct {
     int blocks_per_pod, block_nodes;
 } packed_job;
 
+/* monotone map float32 bits -> uint32 (negative scores exist when one container
+ * carries several requests: len(node.Devices)-sums < 0), never 0 for finite input */
+static inline uint32_t f32_order(uint32_t b) { return (b & 0x80000000u) ? ~b : (b | 0x80000000u); }
+static inline uint32_t f32_unorder(uint32_t o) { return (o & 0x80000000u) ? (o ^ 0x80000000u) : ~o; }
+
 static void *packed_worker(void *arg) {
     packed_job *j = (packed_job *)arg;
     int N = j->snap->n_nodes;
@@ -591,7 +596,7 @@ static void *packed_worker(void *arg) {
             if (ok) {
                 uint32_t bits;
                 memcpy(&bits, &sc, 4);
-                uint64_t key = ((uint64_t)bits << 32) | (uint32_t)row;
+                uint64_t key = ((uint64_t)f32_order(bits) << 32) | (uint32_t)row;
                 if (key > best) best = key;
                 cnt++;
             }
@@ -649,7 +654,7 @@ int ref_score_batch_packed(const ref_Snapshot *snap, const ref_PodBatchPacked *p
         ref_Result res;
         res.fit_count = c;
         if (c > 0) {
-            uint32_t bits = (uint32_t)(b >> 32);
+            uint32_t bits = f32_unorder((uint32_t)(b >> 32));
             res.best_row = (int32_t)(uint32_t)b;
             memcpy(&res.score, &bits, 4);
             res.n_picks = pick_begin[pods->req_begin[c1]] - pick_begin[pods->req_begin[c0]];

@@ -67,3 +67,23 @@ def test_ragged_and_empty():
     empty = v.Snapshot(np.zeros((8, 0, 8), np.int32), np.zeros(0, np.int32), ["NVIDIA-x"])
     r = oracle.score_packed(empty, batch)
     assert r.best_row.tolist() == [-1, -1]
+
+
+def test_negative_scores_keep_their_order():
+    """two requests in one container make len(devices)-sums negative (score.go:180); the
+    best-node pick must still be the numeric maximum in both oracle arms"""
+    rng = np.random.default_rng(11)
+    n = 300
+    planes = np.zeros((8, n, 8), np.int32)
+    planes[1] = 10
+    planes[0] = rng.integers(0, 10, (n, 8))
+    planes[3] = 32768
+    planes[5] = 100
+    snap = v.Snapshot(planes, np.full(n, 8, np.int32), ["NVIDIA-Tesla V100"])
+    batch = v.PodBatch.from_pods([{"containers": [[(5, 100, 101, 0), (5, 100, 101, 0)]]}])
+    a = oracle.score_faithful(snap, batch, full=True)
+    b = oracle.score_packed(snap, batch, full=True, threads=2)
+    from helpers import assert_same
+    assert_same(a, b, "negative")
+    fs = a.scores[0][a.fit[0]]
+    assert fs.min() < 0 and a.score[0] == fs.max()
