@@ -96,7 +96,11 @@ class ShardedScorer:
         self.lo, self.hi = shard_range(n_nodes_total, world, rank)
         self.device = torch.device("cuda", device)
         torch.cuda.set_device(self.device)
-        stream = torch.cuda.current_stream(self.device).cuda_stream
+        # a stream of our own, shared by the library, the collectives and the caller's timing
+        # events: run calls under `with torch.cuda.stream(scorer.stream)`
+        self.stream = torch.cuda.Stream(self.device)
+        stream = self.stream.cuda_stream
+        assert stream != 0
         self.ctx = Context(max_nodes=max(self.hi - self.lo, 1), max_devices=dmax, max_pods=max_pods,
                            max_reqs=max_reqs, max_picks=max_picks, device=device, row_base=self.lo, stream=stream)
         self.max_pods = max_pods
@@ -115,18 +119,20 @@ class ShardedScorer:
         self.ctx.upload(snap_shard)
 
     def step_resident(self, n_picks: int):
-        """score -> exchange -> merge -> resolve, everything on the device"""
+        """score -> exchange -> merge -> resolve, everything on the device (self.stream)"""
+        import torch
         import torch.distributed as dist
 
-        self.ctx.score_resident()
-        if self.world > 1:
-            dist.all_gather_into_tensor(self.gk, self.keys, group=self.group)
-            dist.all_gather_into_tensor(self.gc, self.counts, group=self.group)
-            self.ctx.keys_merge(self.gk.data_ptr(), self.gc.data_ptr(), self.world, self.max_pods)
-        self.ctx.resolve_resident()
-        if self.world > 1 and n_picks:
-            # picks are written by the owner of each winner row only (zero elsewhere)
-            dist.all_reduce(self.picks[: n_picks * 3], group=self.group)
+        with torch.cuda.stream(self.stream):
+            self.ctx.score_resident()
+            if self.world > 1:
+                dist.all_gather_into_tensor(self.gk, self.keys, group=self.group)
+                dist.all_gather_into_tensor(self.gc, self.counts, group=self.group)
+                self.ctx.keys_merge(self.gk.data_ptr(), self.gc.data_ptr(), self.world, self.max_pods)
+            self.ctx.resolve_resident()
+            if self.world > 1 and n_picks:
+                # picks are written by the owner of each winner row only (zero elsewhere)
+                dist.all_reduce(self.picks[: n_picks * 3], group=self.group)
 
     def score(self, pods: np.ndarray, reqs: np.ndarray):
         self.ctx.pods_upload(pods, reqs)

@@ -201,6 +201,7 @@ def main():
     ctx.upload_ptrs(npg, D, plane_ptrs, pin_ndev.data_ptr(), device=False)
     ctx.pods_upload(pods, reqs)
     flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=dev)
+    torch.cuda.set_stream(sc.stream)  # library kernels, collectives, flush and events: one stream
 
     def barrier():
         if world > 1:
