@@ -17,7 +17,9 @@ LIB_PATH = os.path.join(_HERE, "csrc", "libvgpuscore.so")
 
 VGS_OK = 0
 VGS_EINVAL, VGS_ECUDA, VGS_ETOOBIG, VGS_EDMAX, VGS_ERANGE, VGS_ESTATE, VGS_EINTERNAL = range(-1, -8, -1)
+VGS_ELIMIT = -8
 VGS_REQ_NUMA_BIND = 1
+NOALLOC_MAX_NODES, NOALLOC_MAX_DEVICES, NOALLOC_MAX_PODS, NOALLOC_MAX_REQS = 16384, 8, 256, 1024
 
 # every symbol include/vgpuscore.h declares
 EXPORTS = (
@@ -26,7 +28,7 @@ EXPORTS = (
     "vgs_score_batch", "vgs_pods_upload", "vgs_score_resident", "vgs_resolve_resident",
     "vgs_results_download", "vgs_sync", "vgs_keys_device", "vgs_keys_merge", "vgs_results_device",
     "vgs_verify_download", "vgs_last_timing", "vgs_host_typemask", "vgs_host_numa_bind",
-    "vgs_host_encode_pod_devices",
+    "vgs_host_encode_pod_devices", "vgs_score_batch_noalloc",
 )
 
 
@@ -94,6 +96,7 @@ def load_library() -> C.CDLL:
     lib.vgs_results_device.argtypes = [vp, C.POINTER(vp), C.POINTER(vp)]
     lib.vgs_verify_download.argtypes = [vp, vp, vp]
     lib.vgs_last_timing.argtypes = [vp, C.POINTER(VgsTiming)]
+    lib.vgs_score_batch_noalloc.argtypes = [i32, vp, i32, i32, i32, C.POINTER(vp), vp, i32, vp, i32, vp, vp, vp]
     lib.vgs_host_typemask.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.POINTER(C.c_char_p), i32]
     lib.vgs_host_typemask.restype = C.c_uint64
     lib.vgs_host_numa_bind.argtypes = [C.c_char_p]
@@ -176,6 +179,19 @@ def pack_batch(batch: PodBatch, type_names: List[str]):
                 numa_cache[nb] = f
             reqs["flags"][r] = VGS_REQ_NUMA_BIND if (f and batch.req_type[r] == "NVIDIA") else 0
     return pods, reqs
+
+
+def score_batch_noalloc(device: int, stream: int, n_nodes: int, dmax: int, row_base: int, plane_ptrs: List[int],
+                        ndev_ptr: int, pods: np.ndarray, reqs: np.ndarray, results_ptr: int, picks_ptr: int) -> int:
+    """vgs_score_batch_noalloc: planes / outputs are addresses of device memory the caller
+    owns; returns the status code (0 = ok) instead of raising so callers can test limits."""
+    lib = load_library()
+    ptrs = (C.c_void_p * 8)(*plane_ptrs)
+    return int(lib.vgs_score_batch_noalloc(device, C.c_void_p(stream) if stream else None, n_nodes, dmax, row_base,
+                                           ptrs, C.c_void_p(ndev_ptr), len(pods),
+                                           pods.ctypes.data if len(pods) else None, len(reqs),
+                                           reqs.ctypes.data if len(reqs) else None, C.c_void_p(results_ptr),
+                                           C.c_void_p(picks_ptr)))
 
 
 class Context:

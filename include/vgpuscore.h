@@ -70,7 +70,8 @@ typedef enum {
     VGS_EDMAX = -4,   /* more than VGS_MAX_DEVICES devices per node */
     VGS_ERANGE = -5,  /* snapshot value outside the supported range */
     VGS_ESTATE = -6,  /* call sequence error (e.g. score before upload) */
-    VGS_EINTERNAL = -7 /* self-check failed (score kernel vs resolve kernel) */
+    VGS_EINTERNAL = -7, /* self-check failed (score kernel vs resolve kernel) */
+    VGS_ELIMIT = -8 /* beyond the fixed VGS_NOALLOC_MAX_* sizes of vgs_score_batch_noalloc */
 } vgs_status;
 
 typedef struct vgs_ctx vgs_ctx;
@@ -201,6 +202,43 @@ int vgs_keys_merge(vgs_ctx *ctx, const uint64_t *dev_gathered_keys,
                    const int32_t *dev_gathered_counts, int32_t n_shards, int32_t stride);
 /* device arrays behind vgs_results_download (shard combine of results/picks) */
 int vgs_results_device(vgs_ctx *ctx, vgs_result **dev_results, vgs_pick **dev_picks);
+
+/* ---- scoring without any GPU allocation --------------------------------------
+ * (No counterpart in the reference: the Go extender never touches a GPU.)
+ *
+ * For callers that cannot let this library allocate device memory: an extender
+ * running in a container whose GPU memory is capped by the vGPU product itself
+ * (an allocation made at call time can be refused once the quota is spent), a
+ * process whose device memory is owned by another allocator's pool, or a caller
+ * that cannot afford the device-wide synchronisation cudaMalloc/cudaFree imply.
+ * vgs_init and the context API allocate; this call never does (no cudaMalloc,
+ * cudaFree, or allocating library routine).
+ *
+ * The caller supplies, in memory of GPU `device` that it already owns, the
+ * snapshot planes (same layout as vgs_snapshot_upload) and the output arrays
+ * dev_results[n_pods], dev_picks[sum of nums]; pods/reqs are host arrays as in
+ * vgs_score_batch.  All intermediate data (prepared snapshot, request records,
+ * candidate keys) lives in one fixed array inside the library image, ~4 MiB,
+ * which every GPU that loads the library holds until the process exits.  Hence
+ * the hard limits below; anything larger returns VGS_ELIMIT and touches nothing.
+ *
+ * The first call on each GPU looks up that array's device address (one-time
+ * set-up); make that first call outside of any stream capture.  Every call on a
+ * GPU shares the array and finds the previous call's contents in it (the call
+ * clears what has to start at zero).  Two calls executing at once on the same GPU
+ * would corrupt each other, so the function takes a process-wide lock and does
+ * not return until the GPU has finished and the outputs are complete.
+ * stream: cudaStream_t to run on (NULL = the default stream).
+ * Results are identical to vgs_score_batch on the same inputs. */
+#define VGS_NOALLOC_MAX_NODES 16384
+#define VGS_NOALLOC_MAX_DEVICES 8
+#define VGS_NOALLOC_MAX_PODS 256
+#define VGS_NOALLOC_MAX_REQS 1024
+int vgs_score_batch_noalloc(int32_t device, void *stream, int32_t n_nodes, int32_t dmax,
+                            int32_t row_base, const int32_t *const dev_planes[VGS_NUM_PLANES],
+                            const int32_t *dev_ndev, int32_t n_pods, const vgs_pod *pods,
+                            int32_t n_reqs, const vgs_req *reqs, vgs_result *dev_results,
+                            vgs_pick *dev_picks);
 
 /* verify mode (cfg.verify != 0): fit_bitmap[n_pods][ceil32(n_nodes)] words,
  * bit (row & 31) of word row/32; scores[n_pods][n_nodes], 0 when not fit. */
