@@ -160,6 +160,8 @@ def main():
     ap.add_argument("--config", default="cfg3")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--check", action="store_true",
+                    help="rank 0 re-checks a sample of pods against the oracle over ALL shards (not timed)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -278,6 +280,26 @@ def main():
             dist.destroy_process_group()
         return
 
+    check = None
+    if args.check:
+        import oracle
+        shards = [v.workload.make_snapshot(npg, v.workload.SEED + int(args.config[3:]) + 1000 * r) for r in range(world)]
+        whole = v.Snapshot(np.concatenate([s_.planes for s_ in shards], axis=1),
+                           np.concatenate([s_.ndev for s_ in shards]), snap.type_names)
+        idx = list(range(0, P, max(1, P // 48)))
+        want = oracle.score_packed(whole, batch.select(idx))
+        pb = batch.pick_begin
+        ok = (np.array_equal(results["best_row"][idx], want.best_row)
+              and np.array_equal(results["score"][idx].view(np.uint32), want.score.view(np.uint32))
+              and np.array_equal(results["fit_count"][idx], want.fit_count))
+        got_picks = np.concatenate([np.stack([picks["slot"], picks["usedmem"], picks["usedcores"]], axis=1)
+                                    [int(pb[batch.pod_req_range(p)[0]]):int(pb[batch.pod_req_range(p)[1]])] for p in idx])
+        ok = ok and np.array_equal(got_picks, want.picks)
+        check = {"pods_checked": len(idx), "nodes": whole.n_nodes, "bit_exact_vs_oracle": bool(ok)}
+        if not ok:
+            print(json.dumps({"error": "sharded result differs from the oracle", "check": check}), flush=True)
+            raise SystemExit(3)
+
     peak, peak_src = measured_peak()
     abytes = algorithmic_bytes(npg, D, P, R)
     achieved = abytes / (k1_ms * 1e-3) / 1e9
@@ -305,6 +327,8 @@ def main():
                      "note": "batch regime is integer-issue bound (SURVEY F6): see alu below and DESIGN.md"},
         "device_evals_per_s": P * n_total * D / (ms_per_step * 1e-3),
     }
+    if check:
+        line["check"] = check
     if not args.no_cpu:
         val, th, dt, sp = cpu_arm(snap, batch, 64)   # calibrate
         sample = max(64, min(P, int(64 * 12.0 / max(dt, 1e-3))))
