@@ -3,7 +3,9 @@
 // entry point ends in a kernel launch or an error code.
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -60,7 +62,15 @@ struct vgs_ctx {
     size_t stage_bytes = 0;
     size_t off_reqs = 0, off_pods = 0, off_pick = 0, off_reqsA = 0, off_origA = 0, off_reqsB = 0,
            off_origB = 0, off_podsG = 0;
-    int32_t n_pods = 0, n_reqs = 0, nA = 0, nB = 0, nG = 0, n_picks = 0;
+    size_t off_reqsC = 0, off_origC = 0;
+    int32_t n_pods = 0, n_reqs = 0, nA = 0, nB = 0, nC = 0, nG = 0, n_picks = 0;
+    // pod-sliced classes (A: Nums == 1, B: Nums == 2): bit tables, see SliceTab
+    uint32_t *h_slice[2] = {}, *d_slice[2] = {};
+    size_t slice_words = 0;
+    SliceTab tab[2] = {};
+    bool slice_on[2] = {false, false};
+    int32_t slice_min = 512;     // classes smaller than this use the per-pair kernels
+    bool snap_slice_ok = false;  // snapshot satisfies the sliced kernel's preconditions
     bool have_pods = false, scored = false, resolved = false;
 
     // results
@@ -124,6 +134,7 @@ int pull_status(vgs_ctx *c) {
     CU(cudaMemcpyAsync(c->h_status, c->d_status, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->st));
     CU(cudaStreamSynchronize(c->st));
     int rc = check_status(c);
+    c->snap_slice_ok = rc == VGS_OK && !(*c->h_status & S_BIGMEM) && c->dm == 8;
     if (rc != VGS_OK) cudaMemsetAsync(c->d_status, 0, sizeof(uint32_t), c->st);
     return rc;
 }
@@ -144,6 +155,10 @@ void free_all(vgs_ctx *c) {
     cudaFree(c->d_deltas);
     cudaFreeHost(c->h_deltas);
     cudaFree(c->d_rowlist);
+    for (int k = 0; k < 2; k++) {
+        cudaFree(c->d_slice[k]);
+        cudaFreeHost(c->h_slice[k]);
+    }
     cudaFree(c->d_stage);
     cudaFreeHost(c->h_stage);
     cudaFree(c->d_keys);
@@ -238,10 +253,22 @@ int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
     c->off_reqsB = o, o = align_up(o + P * sizeof(DevReq), 256);
     c->off_origB = o, o = align_up(o + P * sizeof(int32_t), 256);
     c->off_podsG = o, o = align_up(o + P * sizeof(GenPod), 256);
+    c->off_reqsC = o, o = align_up(o + P * sizeof(DevReq), 256);
+    c->off_origC = o, o = align_up(o + P * sizeof(int32_t), 256);
     c->stage_bytes = o;
     CUI(cudaMalloc(&c->d_stage, o));
     CUI(cudaMallocHost(&c->h_stage, o));
 
+    {
+        const size_t wp = align_up((P + 31) / 32, 32);
+        const size_t rows = VGS_MAX_TYPES + 2 * (kSliceMaxDistinct + 1) + (kSliceMaxPct + 1) + 3;
+        c->slice_words = rows * wp + 2 * kSliceMaxDistinct + kSliceMaxPct + P + 64;
+        for (int k = 0; k < 2; k++) {
+            CUI(cudaMalloc(&c->d_slice[k], c->slice_words * sizeof(uint32_t)));
+            CUI(cudaMallocHost(&c->h_slice[k], c->slice_words * sizeof(uint32_t)));
+        }
+        if (const char *e = getenv("VGS_SLICE_MIN")) c->slice_min = atoi(e);
+    }
     CUI(cudaMalloc(&c->d_keys, P * sizeof(unsigned long long)));
     CUI(cudaMalloc(&c->d_counts, P * sizeof(int32_t)));
     CUI(cudaMalloc(&c->d_results, P * sizeof(vgs_result)));
@@ -281,6 +308,7 @@ static int snapshot_common(vgs_ctx *c, int32_t n_nodes, int32_t dmax,
     c->have_snapshot = false;
     c->scored = c->resolved = false;
     const size_t cells = (size_t)n_nodes * dmax;
+    CU(cudaMemsetAsync(c->d_status, 0, sizeof(uint32_t), c->st));
     rec(c, EV_UP0);
     if (cells) {
         for (int f = 0; f < VGS_NUM_PLANES; f++)
@@ -381,6 +409,94 @@ int vgs_snapshot_download(vgs_ctx *c, int32_t *const planes[VGS_NUM_PLANES], int
 
 // ---- pod batch ---------------------------------------------------------------------
 
+// Build the bit tables of one pod-sliced class (see SliceTab) into pinned staging and queue the
+// upload.  Returns false when the class does not qualify (then the per-pair kernel runs).
+static bool build_slice_class(vgs_ctx *c, int k, const DevReq *req, const int32_t *orig, int32_t n,
+                              cudaError_t *err) {
+    *err = cudaSuccess;
+    c->slice_on[k] = false;
+    if (n < c->slice_min || n < 1) return false;
+    std::vector<int32_t> mv, pv, cv;
+    mv.reserve(n), cv.reserve(n);
+    for (int32_t i = 0; i < n; i++) {
+        const DevReq &d = req[i];
+        if (d.flags & R_USEPCT) {
+            if (d.pct < 0 || d.pct > 100) return false; // monotone in pct only on [0,100]
+            pv.push_back(d.pct);
+        } else {
+            mv.push_back(d.memfix);
+        }
+        cv.push_back(d.coresreq);
+    }
+    auto uniq = [](std::vector<int32_t> &v) {
+        std::sort(v.begin(), v.end());
+        v.erase(std::unique(v.begin(), v.end()), v.end());
+    };
+    uniq(mv), uniq(pv), uniq(cv);
+    if ((int)mv.size() > kSliceMaxDistinct || (int)cv.size() > kSliceMaxDistinct || (int)pv.size() > kSliceMaxPct)
+        return false;
+    const int32_t km = (int32_t)mv.size(), kp = (int32_t)pv.size(), kc = (int32_t)cv.size();
+    const int32_t W = (n + 31) / 32, Wp = (int32_t)align_up((size_t)W, 32);
+    uint32_t *h = c->h_slice[k];
+    size_t o = 0;
+    const size_t o_type = o; o += (size_t)VGS_MAX_TYPES * Wp;
+    const size_t o_mem = o;  o += (size_t)(km + 1) * Wp;
+    const size_t o_pct = o;  o += (size_t)(kp + 1) * Wp;
+    const size_t o_core = o; o += (size_t)(kc + 1) * Wp;
+    const size_t o_c100 = o; o += Wp;
+    const size_t o_c0 = o;   o += Wp;
+    const size_t o_never = o; o += Wp;
+    const size_t o_memv = o; o += km;
+    const size_t o_pctv = o; o += kp;
+    const size_t o_corev = o; o += kc;
+    const size_t o_orig = o; o += n;
+    if (o > c->slice_words) return false;
+    memset(h, 0, o_memv * sizeof(uint32_t));
+    auto idx_of = [](const std::vector<int32_t> &v, int32_t x) {
+        return (int32_t)(std::lower_bound(v.begin(), v.end(), x) - v.begin());
+    };
+    for (int32_t i = 0; i < n; i++) {
+        const DevReq &d = req[i];
+        const uint32_t bit = 1u << (i & 31);
+        const size_t wd = (size_t)(i >> 5);
+        uint64_t mask = ((uint64_t)d.mask_hi << 32) | d.mask_lo;
+        while (mask) {
+            int t = __builtin_ctzll(mask);
+            mask &= mask - 1;
+            h[o_type + (size_t)t * Wp + wd] |= bit;
+        }
+        if (d.flags & R_USEPCT) h[o_pct + (size_t)(idx_of(pv, d.pct) + 1) * Wp + wd] |= bit;
+        else h[o_mem + (size_t)(idx_of(mv, d.memfix) + 1) * Wp + wd] |= bit;
+        h[o_core + (size_t)(idx_of(cv, d.coresreq) + 1) * Wp + wd] |= bit;
+        if (d.coresreq == 100) h[o_c100 + wd] |= bit;
+        if (d.coresreq == 0) h[o_c0 + wd] |= bit;
+        if (d.coresreq > 100) h[o_never + wd] |= bit;
+    }
+    auto prefix_or = [&](size_t base, int32_t rows) { // row r |= row r-1
+        for (int32_t r = 1; r <= rows; r++)
+            for (int32_t x = 0; x < W; x++) h[base + (size_t)r * Wp + x] |= h[base + (size_t)(r - 1) * Wp + x];
+    };
+    prefix_or(o_mem, km), prefix_or(o_pct, kp), prefix_or(o_core, kc);
+    int32_t *hi = reinterpret_cast<int32_t *>(h);
+    std::copy(mv.begin(), mv.end(), hi + o_memv);
+    std::copy(pv.begin(), pv.end(), hi + o_pctv);
+    std::copy(cv.begin(), cv.end(), hi + o_corev);
+    std::copy(orig, orig + n, hi + o_orig);
+    *err = cudaMemcpyAsync(c->d_slice[k], h, o * sizeof(uint32_t), cudaMemcpyHostToDevice, c->st);
+    if (*err != cudaSuccess) return false;
+    const uint32_t *d = c->d_slice[k];
+    SliceTab &t = c->tab[k];
+    t.type = d + o_type, t.memle = d + o_mem, t.pctle = d + o_pct, t.corele = d + o_core;
+    t.c100 = d + o_c100, t.c0 = d + o_c0, t.never = d + o_never;
+    t.memv = reinterpret_cast<const int32_t *>(d + o_memv);
+    t.pctv = reinterpret_cast<const int32_t *>(d + o_pctv);
+    t.corev = reinterpret_cast<const int32_t *>(d + o_corev);
+    t.orig = reinterpret_cast<const int32_t *>(d + o_orig);
+    t.km = km, t.kp = kp, t.kc = kc, t.n_pods = n, t.W = W, t.Wp = Wp;
+    c->slice_on[k] = true;
+    return true;
+}
+
 static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_reqs,
                               const vgs_req *reqs) {
     if (n_pods < 0 || n_reqs < 0 || (n_pods > 0 && (!pods || !reqs)))
@@ -399,6 +515,8 @@ static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, i
     DevReq *hB = reinterpret_cast<DevReq *>(c->h_stage + c->off_reqsB);
     int32_t *hoB = reinterpret_cast<int32_t *>(c->h_stage + c->off_origB);
     GenPod *hG = reinterpret_cast<GenPod *>(c->h_stage + c->off_podsG);
+    DevReq *hC = reinterpret_cast<DevReq *>(c->h_stage + c->off_reqsC);
+    int32_t *hoC = reinterpret_cast<int32_t *>(c->h_stage + c->off_origC);
 
     int64_t picks = 0;
     for (int32_t r = 0; r < n_reqs; r++) {
@@ -425,7 +543,7 @@ static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, i
     }
     hpick[n_reqs] = (int32_t)picks;
 
-    int32_t nA = 0, nB = 0, nG = 0;
+    int32_t nA = 0, nB = 0, nC = 0, nG = 0;
     for (int32_t p = 0; p < n_pods; p++) {
         const vgs_pod &pd = pods[p];
         if (pd.n_reqs < 1 || pd.n_reqs > VGS_MAX_REQS_PER_POD || pd.req_begin < 0 ||
@@ -444,9 +562,12 @@ static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, i
         if (pd.n_reqs == 1 && first.nums == 1) {
             hA[nA] = first; // numa-bind cannot matter for a single device
             hoA[nA++] = p;
-        } else if (pd.n_reqs == 1 && !(first.flags & R_NUMA)) {
+        } else if (pd.n_reqs == 1 && !(first.flags & R_NUMA) && first.nums == 2) {
             hB[nB] = first;
             hoB[nB++] = p;
+        } else if (pd.n_reqs == 1 && !(first.flags & R_NUMA)) {
+            hC[nC] = first;
+            hoC[nC++] = p;
         } else {
             hG[nG].req_begin = pd.req_begin;
             hG[nG].n_reqs = pd.n_reqs;
@@ -459,6 +580,7 @@ static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, i
     c->n_reqs = n_reqs;
     c->nA = nA;
     c->nB = nB;
+    c->nC = nC;
     c->nG = nG;
     c->n_picks = (int32_t)picks;
     rec(c, EV_PH0);
@@ -474,6 +596,15 @@ static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, i
     CU(up(c->off_reqsB, (size_t)nB * sizeof(DevReq)));
     CU(up(c->off_origB, (size_t)nB * sizeof(int32_t)));
     CU(up(c->off_podsG, (size_t)nG * sizeof(GenPod)));
+    CU(up(c->off_reqsC, (size_t)nC * sizeof(DevReq)));
+    CU(up(c->off_origC, (size_t)nC * sizeof(int32_t)));
+    {
+        cudaError_t e;
+        build_slice_class(c, 0, hA, hoA, nA, &e);
+        CU(e);
+        build_slice_class(c, 1, hB, hoB, nB, &e);
+        CU(e);
+    }
     rec(c, EV_PH1);
     c->have_pods = true;
     return VGS_OK;
@@ -507,16 +638,29 @@ static int score_locked(vgs_ctx *c) {
             CU(cudaMemsetAsync(c->d_vscore, 0, (size_t)P * c->n_nodes * sizeof(float), c->st));
     }
     const DevReq *dreq = reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqs);
+    const bool sliced = c->snap_slice_ok && c->dm == 8;
     if (c->nA) {
-        CU(launch_score_single(c->dm, true, c->cfg.device, a,
-                               reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqsA),
-                               reinterpret_cast<const int32_t *>(c->d_stage + c->off_origA), c->nA, c->st));
+        if (sliced && c->slice_on[0])
+            CU(launch_score_sliced(1, c->cfg.device, a, c->tab[0], c->st));
+        else
+            CU(launch_score_single(c->dm, true, c->cfg.device, a,
+                                   reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqsA),
+                                   reinterpret_cast<const int32_t *>(c->d_stage + c->off_origA), c->nA, c->st));
         if (c->n_tiles) c->launches++;
     }
     if (c->nB) {
+        if (sliced && c->slice_on[1])
+            CU(launch_score_sliced(2, c->cfg.device, a, c->tab[1], c->st));
+        else
+            CU(launch_score_single(c->dm, false, c->cfg.device, a,
+                                   reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqsB),
+                                   reinterpret_cast<const int32_t *>(c->d_stage + c->off_origB), c->nB, c->st));
+        if (c->n_tiles) c->launches++;
+    }
+    if (c->nC) {
         CU(launch_score_single(c->dm, false, c->cfg.device, a,
-                               reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqsB),
-                               reinterpret_cast<const int32_t *>(c->d_stage + c->off_origB), c->nB, c->st));
+                               reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqsC),
+                               reinterpret_cast<const int32_t *>(c->d_stage + c->off_origC), c->nC, c->st));
         if (c->n_tiles) c->launches++;
     }
     if (c->nG) {

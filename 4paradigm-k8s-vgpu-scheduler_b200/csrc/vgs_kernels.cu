@@ -119,6 +119,7 @@ __global__ void __launch_bounds__(128)
                 bad |= S_TYPE;
                 type[j] = 0;
             }
+            if (totalmem[j] < 0 || totalmem[j] > kSliceMaxTotalmem) bad |= S_BIGMEM;
         }
     }
     if (bad) atomicOr(status, bad);
@@ -465,6 +466,274 @@ __global__ void __launch_bounds__(128)
     }
 }
 
+
+// ------------------------------------------------------------------------------------
+// K1 (pod-sliced): single-request pods with Nums == 1 or Nums == 2, 32 pods per register.
+//
+// The whole CTA works on ONE node at a time (every branch on node data is uniform); thread
+// t owns pod word w = 32 pods of the class.  A device's fit word is four table rows ANDed:
+// the type row, the memory row (fixed-MB pods | percentage pods), the cores row -- rows are
+// chosen by how many of the class's distinct thresholds the device's free capacity admits
+// (binary search per device, once per tile) -- and the flag word (exclusive / full-core /
+// never).  The reverse walk becomes word algebra: first = fit & ~seen, second = fit & seen
+// & ~seen2.  A candidate score is a scalar of the node (device or device pair), so the
+// per-pod best is touched only when that scalar beats the thread's current minimum: after
+// a few hundred nodes almost nothing does.  Node tiles (8 KB, 32 nodes) are staged into
+// shared memory with cp.async.bulk + mbarrier, double buffered, and reused by every pod
+// word of the CTA.  Nodes are visited in DESCENDING row order so that "strictly greater"
+// keeps the highest row among equal scores inside a CTA; across CTAs the 64-bit key max does.
+// ------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+constexpr int kTileInt4 = kWalkWords * 2 * kWarp; // DM = 8: 512 int4 = 8 KB per 32-node tile
+constexpr int kTileBytes = kTileInt4 * 16;
+
+// number of sorted values v[0..n) that satisfy pred(v) where pred is monotone (true prefix)
+template <typename F>
+__device__ __forceinline__ int count_prefix(const int32_t *__restrict__ v, int n, F pred) {
+    int lo = 0, hi = n; // invariant: pred true on [0,lo), false on [hi,n)
+    while (lo < hi) {
+        int mid = (lo + hi) >> 1;
+        if (pred(__ldg(&v[mid]))) lo = mid + 1;
+        else hi = mid;
+    }
+    return lo;
+}
+
+template <int NUMS, bool VERIFY>
+__global__ void __launch_bounds__(256)
+    k1_score_sliced(const int4 *__restrict__ walk, int32_t n_tiles, int32_t n_nodes, int32_t row_base,
+                    SliceTab tb, int32_t tiles_per_cta, unsigned long long *__restrict__ keys,
+                    int32_t *__restrict__ counts, uint32_t *__restrict__ vfit, float *__restrict__ vscore,
+                    int32_t vwords) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int T = blockDim.x, tid = threadIdx.x;
+    int4 *tilebuf = reinterpret_cast<int4 *>(smem_raw);                                // [2][kTileInt4]
+    uint64_t *bar = reinterpret_cast<uint64_t *>(smem_raw + 2 * kTileBytes);           // [2]
+    uint16_t *cut = reinterpret_cast<uint16_t *>(smem_raw + 2 * kTileBytes + 64);      // [3][256]
+    uint32_t *s_best = reinterpret_cast<uint32_t *>(smem_raw + 2 * kTileBytes + 64 + 3 * 256 * 2); // [32][T]
+    uint32_t *s_row = s_best + 32 * T;                                                 // [32][T]
+
+    const int w = blockIdx.y * T + tid;
+    const bool active = w < tb.W;
+    const int wl = active ? w : 0;
+    // tiles [t_lo, t_hi) of this CTA, visited from t_hi-1 down
+    const int t_hi = n_tiles - (int)blockIdx.x * tiles_per_cta;
+    const int t_lo = max(0, t_hi - tiles_per_cta);
+    if (t_hi <= 0) return;
+    const int n_my = t_hi - t_lo;
+
+    for (int b = 0; b < 32; b++) {
+        s_best[b * T + tid] = 0u;
+        s_row[b * T + tid] = 0u;
+    }
+    if (tid == 0) {
+        mbar_init(&bar[0], 1);
+        mbar_init(&bar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (tid == 0) {
+        mbar_expect_tx(&bar[0], kTileBytes);
+        bulk_g2s(tilebuf, walk + (size_t)(t_hi - 1) * kTileInt4, kTileBytes, &bar[0]);
+    }
+
+    const uint32_t c100 = __ldg(&tb.c100[wl]), c0 = __ldg(&tb.c0[wl]), never = __ldg(&tb.never[wl]);
+    uint32_t cnt[kSliceCountPlanes];
+#pragma unroll
+    for (int k = 0; k < kSliceCountPlanes; k++) cnt[k] = 0u;
+    // pruning state: `unseen` = my pods that have no candidate yet; minbest = min of s_best
+    // over the others (raw positive float bits).  A candidate word matters only if it
+    // reaches an unseen pod or carries a score above minbest.
+    uint32_t unseen = 0xffffffffu, minbest = 0xffffffffu;
+
+    auto update = [&](uint32_t word, uint32_t sbits, uint32_t row) {
+        // rare path: pods in `word` get candidate (sbits, row); rows only ever decrease here
+        uint32_t m = word;
+        while (m) {
+            int b = __ffs((int)m) - 1;
+            m &= m - 1;
+            if (sbits > s_best[b * T + tid]) {
+                s_best[b * T + tid] = sbits;
+                s_row[b * T + tid] = row;
+            }
+        }
+        unseen &= ~word;
+        uint32_t mn = 0xffffffffu;
+        for (int b = 0; b < 32; b++) {
+            const uint32_t v = s_best[b * T + tid];
+            mn = v ? min(mn, v) : mn;
+        }
+        minbest = mn;
+    };
+
+    for (int it = 0; it < n_my; it++) {
+        const int tile = t_hi - 1 - it;
+        const int4 *tb4 = tilebuf + (it & 1) * kTileInt4;
+        if (tid == 0 && it + 1 < n_my) { // prefetch the next tile into the other buffer
+            mbar_expect_tx(&bar[(it + 1) & 1], kTileBytes);
+            bulk_g2s(tilebuf + ((it + 1) & 1) * kTileInt4, walk + (size_t)(tile - 1) * kTileInt4, kTileBytes,
+                     &bar[(it + 1) & 1]);
+        }
+        mbar_wait(&bar[it & 1], (uint32_t)((it >> 1) & 1));
+        // thresholds admitted by each of the tile's 256 devices
+        const int32_t *ti = reinterpret_cast<const int32_t *>(tb4);
+        for (int d = tid; d < 256; d += T) {
+            const int l = d >> 3, j = d & 7;
+            auto word_of = [&](int wd) { return ti[(((wd * 2 + (j >> 2)) * kWarp + l) << 2) + (j & 3)]; };
+            const int32_t fm = word_of(W_FREEMEM), fc = word_of(W_FREECORES), tm = word_of(W_TOTALMEM);
+            cut[d] = (uint16_t)count_prefix(tb.memv, tb.km, [&](int32_t v) { return v <= fm; });
+            cut[256 + d] = (uint16_t)count_prefix(tb.pctv, tb.kp, [&](int32_t v) { return pct_mem(tm, v) <= fm; });
+            cut[512 + d] = (uint16_t)count_prefix(tb.corev, tb.kc, [&](int32_t v) { return v <= fc; });
+        }
+        __syncthreads();
+
+        for (int l = kWarp - 1; l >= 0; l--) {
+            const int node = tile * kWarp + l;
+            if (node >= n_nodes) continue; // uniform
+            int32_t meta[8], s1[8], cn[8], fs[8];
+            {
+                int4 a = tb4[(W_META * 2 + 0) * kWarp + l], b = tb4[(W_META * 2 + 1) * kWarp + l];
+                meta[0] = a.x, meta[1] = a.y, meta[2] = a.z, meta[3] = a.w;
+                meta[4] = b.x, meta[5] = b.y, meta[6] = b.z, meta[7] = b.w;
+                if (NUMS == 1) {
+                    a = tb4[(W_SCORE1 * 2 + 0) * kWarp + l], b = tb4[(W_SCORE1 * 2 + 1) * kWarp + l];
+                    s1[0] = a.x, s1[1] = a.y, s1[2] = a.z, s1[3] = a.w;
+                    s1[4] = b.x, s1[5] = b.y, s1[6] = b.z, s1[7] = b.w;
+                } else {
+                    a = tb4[(W_COUNT * 2 + 0) * kWarp + l], b = tb4[(W_COUNT * 2 + 1) * kWarp + l];
+                    cn[0] = a.x, cn[1] = a.y, cn[2] = a.z, cn[3] = a.w;
+                    cn[4] = b.x, cn[5] = b.y, cn[6] = b.z, cn[7] = b.w;
+                    a = tb4[(W_FREESLOTS * 2 + 0) * kWarp + l], b = tb4[(W_FREESLOTS * 2 + 1) * kWarp + l];
+                    fs[0] = a.x, fs[1] = a.y, fs[2] = a.z, fs[3] = a.w;
+                    fs[4] = b.x, fs[5] = b.y, fs[6] = b.z, fs[7] = b.w;
+                }
+            }
+            const int32_t ndev = (meta[0] >> M_NDEV_SHIFT) & 15;
+            uint32_t fit[8];
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                const uint32_t m = (uint32_t)meta[j];
+                if (m & (M_NOFREE | M_PAD)) { // uniform: Count <= Used, or not a device
+                    fit[j] = 0u;
+                    continue;
+                }
+                const int d = l * 8 + j;
+                const uint32_t ty = __ldg(&tb.type[(size_t)(m & M_TYPE_MASK) * tb.Wp + wl]);
+                const uint32_t mm = __ldg(&tb.memle[(size_t)cut[d] * tb.Wp + wl]);
+                const uint32_t pp = __ldg(&tb.pctle[(size_t)cut[256 + d] * tb.Wp + wl]);
+                const uint32_t cc = __ldg(&tb.corele[(size_t)cut[512 + d] * tb.Wp + wl]);
+                uint32_t blocked = never;
+                if (m & M_EXCL) blocked |= c100; // score.go:128
+                if (m & M_FULL) blocked |= c0;   // score.go:132
+                fit[j] = active ? (ty & (mm | pp) & cc & ~blocked) : 0u;
+            }
+            uint32_t anyfit;
+            if (NUMS == 1) {
+                uint32_t rem = 0xffffffffu;
+#pragma unroll
+                for (int j = 0; j < 8; j++) { // walk order: the first fitting device is taken
+                    const uint32_t nw = fit[j] & rem;
+                    rem &= ~fit[j];
+                    if (VERIFY) {
+                        for (uint32_t mth = nw; mth; mth &= mth - 1) {
+                            int p = tb.orig[w * 32 + __ffs((int)mth) - 1];
+                            vscore[(size_t)p * n_nodes + node] = __int_as_float(s1[j]);
+                        }
+                    }
+                    if ((nw & unseen) || (nw && (uint32_t)s1[j] > minbest)) update(nw, (uint32_t)s1[j], (uint32_t)node);
+                }
+                anyfit = ~rem;
+            } else {
+                uint32_t seen = 0u, seen2 = 0u, first[8], second[8];
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    first[j] = fit[j] & ~seen;
+                    second[j] = fit[j] & seen & ~seen2;
+                    seen2 |= seen & fit[j];
+                    seen |= fit[j];
+                }
+                anyfit = seen2; // the node fits a pod iff two devices fit
+#pragma unroll
+                for (int a = 0; a < 7; a++) {
+                    if (!__any_sync(0xffffffffu, first[a] != 0u)) continue;
+#pragma unroll
+                    for (int b = a + 1; b < 8; b++) {
+                        const uint32_t wab = first[a] & second[b];
+                        if (!__any_sync(0xffffffffu, wab != 0u)) continue;
+                        const float sc = container_score(wrap_add(cn[a], cn[b]), wrap_add(fs[a], fs[b]), ndev - 2);
+                        const uint32_t sb = __float_as_uint(sc);
+                        if (VERIFY) {
+                            for (uint32_t mth = wab; mth; mth &= mth - 1) {
+                                int p = tb.orig[w * 32 + __ffs((int)mth) - 1];
+                                vscore[(size_t)p * n_nodes + node] = sc;
+                            }
+                        }
+                        if ((wab & unseen) || (wab && sb > minbest)) update(wab, sb, (uint32_t)node);
+                    }
+                }
+            }
+            if (VERIFY) {
+                for (uint32_t mth = anyfit; mth; mth &= mth - 1) {
+                    int p = tb.orig[w * 32 + __ffs((int)mth) - 1];
+                    atomicOr(&vfit[(size_t)p * vwords + (node >> 5)], 1u << (node & 31));
+                }
+            }
+            // bit-sliced fit counter += anyfit
+            uint32_t carry = anyfit;
+#pragma unroll
+            for (int k = 0; k < kSliceCountPlanes; k++) {
+                const uint32_t t2 = cnt[k] & carry;
+                cnt[k] ^= carry;
+                carry = t2;
+            }
+        }
+        __syncthreads(); // everyone is done with this buffer and with cut[]
+    }
+
+    if (!active) return;
+    for (int b = 0; b < 32; b++) {
+        const int i = w * 32 + b;
+        if (i >= tb.n_pods) break;
+        const uint32_t sb = s_best[b * T + tid];
+        if (sb == 0u) continue;
+        int32_t c = 0;
+#pragma unroll
+        for (int k = 0; k < kSliceCountPlanes; k++) c |= (int32_t)((cnt[k] >> b) & 1u) << k;
+        const int p = __ldg(&tb.orig[i]);
+        // scores of single-request pods are positive: ordered bits = bits | sign bit
+        const unsigned long long key =
+            ((unsigned long long)(sb | 0x80000000u) << 32) | (unsigned long long)(uint32_t)(row_base + (int)s_row[b * T + tid]);
+        atomicMax(&keys[p], key);
+        atomicAdd(&counts[p], c);
+    }
+}
+
 // ------------------------------------------------------------------------------------
 // K2: merge shard candidates (after the allgather)
 // ------------------------------------------------------------------------------------
@@ -755,6 +1024,43 @@ cudaError_t launch_score_general(int dm, int dev, const ScoreArgs &a, const DevR
     if (n_pods <= 0 || a.n_tiles <= 0) return cudaSuccess;
     return dm == 8 ? launch_general_t<8>(dev, a, reqs, pods, n_pods, st)
                    : launch_general_t<12>(dev, a, reqs, pods, n_pods, st);
+}
+
+
+template <int NUMS>
+static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &tb, cudaStream_t st) {
+    const int sms = sm_count(dev);
+    int warps = (tb.W + 31) / 32;
+    if (warps > 8) warps = 8;
+    const int T = warps * 32;
+    const int gy = (tb.W + T - 1) / T;
+    const int smem = 2 * kTileBytes + 64 + 3 * 256 * 2 + 2 * 32 * T * 4;
+    cudaError_t e;
+    auto go = [&](auto kernel) -> cudaError_t {
+        if ((e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)) != cudaSuccess) return e;
+        int occ = 1;
+        if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, T, smem)) != cudaSuccess) return e;
+        if (occ < 1) occ = 1;
+        // one wave of CTAs; at least 4 tiles each so the per-CTA flush stays small, at most
+        // (2^planes - 1) nodes each so the bit-sliced counter cannot overflow
+        long long want = (long long)sms * occ / gy;
+        if (want < 1) want = 1;
+        int tiles_per = (int)((a.n_tiles + want - 1) / want);
+        if (tiles_per < 4) tiles_per = 4;
+        const int cap = ((1 << kSliceCountPlanes) - 1) / kWarp;
+        if (tiles_per > cap) tiles_per = cap;
+        const int gx = (a.n_tiles + tiles_per - 1) / tiles_per;
+        kernel<<<dim3(gx, gy), T, smem, st>>>(a.walk, a.n_tiles, a.n_nodes, a.row_base, tb, tiles_per, a.keys, a.counts,
+                                              a.vfit, a.vscore, a.vwords);
+        return cudaGetLastError();
+    };
+    if (a.vfit) return go(k1_score_sliced<NUMS, true>);
+    return go(k1_score_sliced<NUMS, false>);
+}
+
+cudaError_t launch_score_sliced(int nums, int dev, const ScoreArgs &a, const SliceTab &tb, cudaStream_t st) {
+    if (tb.n_pods <= 0 || a.n_tiles <= 0) return cudaSuccess;
+    return nums == 1 ? launch_sliced_t<1>(dev, a, tb, st) : launch_sliced_t<2>(dev, a, tb, st);
 }
 
 cudaError_t launch_merge(const unsigned long long *gk, const int32_t *gc, int32_t n_shards, int32_t stride,

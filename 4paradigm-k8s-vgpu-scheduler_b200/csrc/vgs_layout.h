@@ -71,12 +71,35 @@ struct GenPod {
     int32_t req_begin, n_reqs, orig, pad;
 };
 
+// Pod-sliced score kernel: per-class bit tables over the pods of one class (bit i of word
+// i/32 = pod i of the class).  Row stride Wp words.  "LE" tables are cumulative: row c holds
+// the pods whose threshold is among the c smallest distinct values, so a device whose
+// capacity admits exactly c of the distinct values selects row c.
+struct SliceTab {
+    const uint32_t *type;   // [VGS_MAX_TYPES][Wp]  pods whose type mask has the bit
+    const uint32_t *memle;  // [km+1][Wp]  fixed-MB pods by Memreq
+    const uint32_t *pctle;  // [kp+1][Wp]  percentage pods by MemPercentagereq
+    const uint32_t *corele; // [kc+1][Wp]  all pods by Coresreq
+    const uint32_t *c100;   // [Wp] Coresreq == 100
+    const uint32_t *c0;     // [Wp] Coresreq == 0
+    const uint32_t *never;  // [Wp] Coresreq > 100
+    const int32_t *memv, *pctv, *corev; // sorted distinct values
+    const int32_t *orig;                // class position -> pod index of the batch
+    int32_t km, kp, kc;
+    int32_t n_pods, W, Wp;
+};
+constexpr int kSliceMaxDistinct = 1024; // distinct Memreq / Coresreq values per class
+constexpr int kSliceMaxPct = 101;       // MemPercentagereq in [0, 100]
+constexpr int kSliceCountPlanes = 13;   // bit-sliced fit counter: < 8192 nodes per CTA
+constexpr int32_t kSliceMaxTotalmem = 21474836; // Totalmem * 100 must not wrap int32
+
 // status word bits (device -> host)
 constexpr uint32_t S_RANGE = 1u;    // snapshot value out of range
 constexpr uint32_t S_TYPE = 2u;     // type id out of range
 constexpr uint32_t S_NDEV = 4u;     // ndev out of range
 constexpr uint32_t S_MISMATCH = 8u; // resolve kernel disagrees with score kernel
 constexpr uint32_t S_DELTA = 16u;   // delta names a row/slot outside the shard
+constexpr uint32_t S_BIGMEM = 32u;  // (not an error) some Totalmem outside [0, kSliceMaxTotalmem]
 
 __host__ __device__ inline uint32_t order_bits(uint32_t fbits) {
     // monotone map float bits -> unsigned, never 0 for a finite float

@@ -259,3 +259,65 @@ def test_full_size_properties(built):
         assert one.score.view(np.uint32)[0] == a.score.view(np.uint32)[p]
         r0, r1 = batch.pod_req_range(int(p))
         assert np.array_equal(one.picks, a.picks[int(pb[r0]):int(pb[r1])])
+
+
+# ---- pod-sliced K1 (classes of single-request pods with Nums 1 / 2) -------------------------
+
+def test_sliced_default_threshold(built):
+    """classes >= 512 pods take the pod-sliced kernels; whole fit/score matrix vs the oracle"""
+    for cfg, n, p in (("cfg3", 3000, 2600), ("cfg2", 5000, 1024), ("cfg3", 40, 4096)):
+        snap, batch = v.workload.make_config(cfg, n, p)
+        assert_same(gpu_score(snap, batch), oracle.score_packed(snap, batch, full=True), f"sliced {cfg}")
+
+
+@pytest.mark.parametrize("k", K["kats"], ids=[k["name"] for k in K["kats"]])
+def test_sliced_forced_kats(built, monkeypatch, k):
+    monkeypatch.setenv("VGS_SLICE_MIN", "1")
+    snap, batch = kat_inputs(k)
+    check_kat(k, gpu_score(snap, batch), batch)
+
+
+@pytest.mark.parametrize("dmax,seed", [(8, 21), (8, 22), (7, 23), (4, 24), (1, 25), (2, 26)])
+def test_sliced_forced_random(built, monkeypatch, dmax, seed):
+    monkeypatch.setenv("VGS_SLICE_MIN", "1")
+    rng = np.random.default_rng(seed)
+    snap = _random_snapshot(rng, 1000 + seed, dmax)
+    batch = _random_pods(rng, 300, dmax, max_ctrs=1)  # single-container pods -> classes A/B/C
+    got = gpu_score(snap, batch)
+    assert_same(got, oracle.score_packed(snap, batch, full=True), f"sliced dmax={dmax}")
+    assert_same(got, oracle.score_faithful(snap, batch, full=True), f"sliced dmax={dmax} R1")
+
+
+def test_sliced_many_distinct_thresholds(built, monkeypatch):
+    """every pod its own Memreq / Coresreq value: long cumulative tables, binary search cut-offs"""
+    monkeypatch.setenv("VGS_SLICE_MIN", "1")
+    rng = np.random.default_rng(5)
+    snap, _ = v.workload.make_config("cfg3", 2000, 1)
+    pods = [{"containers": [[(int(rng.choice([1, 2])), int(rng.integers(0, 40000)), 101, int(rng.integers(0, 101)))]]}
+            for _ in range(900)]
+    pods += [{"containers": [[(int(rng.choice([1, 2])), 0, int(rng.integers(0, 101)), int(rng.integers(0, 101)))]]}
+             for _ in range(300)]
+    batch = v.PodBatch.from_pods(pods)
+    assert_same(gpu_score(snap, batch), oracle.score_packed(snap, batch, full=True), "distinct")
+
+
+def test_sliced_falls_back_when_preconditions_fail(built, monkeypatch):
+    """Totalmem * pct wrapping int32 (score.go:119) and pct outside [0,100] are only handled by
+    the per-pair kernels: the library must route there and still match the oracle"""
+    monkeypatch.setenv("VGS_SLICE_MIN", "1")
+    snap, batch = v.workload.make_config("cfg3", 1500, 600)
+    big = snap.planes.copy()
+    big[3] = 30_000_000       # * 100 wraps int32
+    big[2] = big[2] * 900
+    wrapped = v.Snapshot(big, snap.ndev, snap.type_names)
+    assert_same(gpu_score(wrapped, batch), oracle.score_packed(wrapped, batch, full=True), "bigmem")
+    odd = v.PodBatch.from_pods([{"containers": [[(1, 0, pct, 0)]]} for pct in (150, -5, 100, 0, 250)] * 20)
+    assert_same(gpu_score(snap, odd), oracle.score_packed(snap, odd, full=True), "odd pct")
+    # and the same context flips back to the sliced path when a normal snapshot returns
+    with v.Context(max_nodes=1500, max_pods=600, verify=True) as ctx:
+        ctx.upload(wrapped)
+        a = ctx.score(batch)
+        ctx.upload(snap)
+        b = ctx.score(batch)
+    assert_same(a, oracle.score_packed(wrapped, batch, full=True), "ctx bigmem")
+    assert_same(b, oracle.score_packed(snap, batch, full=True), "ctx normal")
