@@ -71,6 +71,7 @@ struct vgs_ctx {
     bool slice_on[2] = {false, false};
     int32_t slice_min = 512;     // classes smaller than this use the per-pair kernels
     bool snap_slice_ok = false;  // snapshot satisfies the sliced kernel's preconditions
+    int32_t n_types_used = VGS_MAX_TYPES; // largest type id of the snapshot + 1
     bool have_pods = false, scored = false, resolved = false;
 
     // results
@@ -131,10 +132,11 @@ int check_status(vgs_ctx *c) {
 }
 
 int pull_status(vgs_ctx *c) {
-    CU(cudaMemcpyAsync(c->h_status, c->d_status, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->st));
+    CU(cudaMemcpyAsync(c->h_status, c->d_status, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->st));
     CU(cudaStreamSynchronize(c->st));
     int rc = check_status(c);
     c->snap_slice_ok = rc == VGS_OK && !(*c->h_status & S_BIGMEM) && c->dm == 8;
+    c->n_types_used = (int32_t)c->h_status[1] + 1;
     if (rc != VGS_OK) cudaMemsetAsync(c->d_status, 0, sizeof(uint32_t), c->st);
     return rc;
 }
@@ -234,9 +236,9 @@ int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
     CUI(cudaMalloc(&c->d_ndev, (size_t)cfg->max_nodes * sizeof(int32_t)));
     const size_t max_tiles = ((size_t)cfg->max_nodes + kWarp - 1) / kWarp;
     CUI(cudaMalloc(&c->d_walk, max_tiles * walk_int4_per_tile(c->dm) * sizeof(int4)));
-    CUI(cudaMalloc(&c->d_status, sizeof(uint32_t)));
-    CUI(cudaMemset(c->d_status, 0, sizeof(uint32_t)));
-    CUI(cudaMallocHost(&c->h_status, sizeof(uint32_t)));
+    CUI(cudaMalloc(&c->d_status, 2 * sizeof(uint32_t))); // [0] S_* flags, [1] largest type id in use
+    CUI(cudaMemset(c->d_status, 0, 2 * sizeof(uint32_t)));
+    CUI(cudaMallocHost(&c->h_status, 2 * sizeof(uint32_t)));
     c->max_deltas = 4096;
     CUI(cudaMalloc(&c->d_deltas, c->max_deltas * sizeof(vgs_delta)));
     CUI(cudaMallocHost(&c->h_deltas, c->max_deltas * sizeof(vgs_delta)));
@@ -261,7 +263,7 @@ int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
 
     {
         const size_t wp = align_up((P + 31) / 32, 32);
-        const size_t rows = VGS_MAX_TYPES + 2 * (kSliceMaxDistinct + 1) + (kSliceMaxPct + 1) + 3;
+        const size_t rows = VGS_MAX_TYPES + 2 * (kSliceMaxDistinct + 1) + (kSliceMaxPct + 1) + 4;
         c->slice_words = rows * wp + 2 * kSliceMaxDistinct + kSliceMaxPct + P + 64;
         for (int k = 0; k < 2; k++) {
             CUI(cudaMalloc(&c->d_slice[k], c->slice_words * sizeof(uint32_t)));
@@ -308,7 +310,7 @@ static int snapshot_common(vgs_ctx *c, int32_t n_nodes, int32_t dmax,
     c->have_snapshot = false;
     c->scored = c->resolved = false;
     const size_t cells = (size_t)n_nodes * dmax;
-    CU(cudaMemsetAsync(c->d_status, 0, sizeof(uint32_t), c->st));
+    CU(cudaMemsetAsync(c->d_status, 0, 2 * sizeof(uint32_t), c->st));
     rec(c, EV_UP0);
     if (cells) {
         for (int f = 0; f < VGS_NUM_PLANES; f++)
@@ -443,9 +445,7 @@ static bool build_slice_class(vgs_ctx *c, int k, const DevReq *req, const int32_
     const size_t o_mem = o;  o += (size_t)(km + 1) * Wp;
     const size_t o_pct = o;  o += (size_t)(kp + 1) * Wp;
     const size_t o_core = o; o += (size_t)(kc + 1) * Wp;
-    const size_t o_c100 = o; o += Wp;
-    const size_t o_c0 = o;   o += Wp;
-    const size_t o_never = o; o += Wp;
+    const size_t o_flag = o; o += (size_t)4 * Wp;
     const size_t o_memv = o; o += km;
     const size_t o_pctv = o; o += kp;
     const size_t o_corev = o; o += kc;
@@ -468,9 +468,12 @@ static bool build_slice_class(vgs_ctx *c, int k, const DevReq *req, const int32_
         if (d.flags & R_USEPCT) h[o_pct + (size_t)(idx_of(pv, d.pct) + 1) * Wp + wd] |= bit;
         else h[o_mem + (size_t)(idx_of(mv, d.memfix) + 1) * Wp + wd] |= bit;
         h[o_core + (size_t)(idx_of(cv, d.coresreq) + 1) * Wp + wd] |= bit;
-        if (d.coresreq == 100) h[o_c100 + wd] |= bit;
-        if (d.coresreq == 0) h[o_c0 + wd] |= bit;
-        if (d.coresreq > 100) h[o_never + wd] |= bit;
+        // flag rows hold the pods that SURVIVE a device with (excl, full) = (f & 1, f >> 1):
+        // Coresreq == 100 loses on excl (score.go:128), == 0 on full (:132), > 100 always (:110)
+        for (int f = 0; f < 4; f++) {
+            const bool lose = d.coresreq > 100 || ((f & 1) && d.coresreq == 100) || ((f & 2) && d.coresreq == 0);
+            if (!lose) h[o_flag + (size_t)f * Wp + wd] |= bit;
+        }
     }
     auto prefix_or = [&](size_t base, int32_t rows) { // row r |= row r-1
         for (int32_t r = 1; r <= rows; r++)
@@ -486,8 +489,8 @@ static bool build_slice_class(vgs_ctx *c, int k, const DevReq *req, const int32_
     if (*err != cudaSuccess) return false;
     const uint32_t *d = c->d_slice[k];
     SliceTab &t = c->tab[k];
-    t.type = d + o_type, t.memle = d + o_mem, t.pctle = d + o_pct, t.corele = d + o_core;
-    t.c100 = d + o_c100, t.c0 = d + o_c0, t.never = d + o_never;
+    t.base = d + o_type;
+    (void)o_mem, (void)o_pct, (void)o_core, (void)o_flag;
     t.memv = reinterpret_cast<const int32_t *>(d + o_memv);
     t.pctv = reinterpret_cast<const int32_t *>(d + o_pctv);
     t.corev = reinterpret_cast<const int32_t *>(d + o_corev);
@@ -641,7 +644,7 @@ static int score_locked(vgs_ctx *c) {
     const bool sliced = c->snap_slice_ok && c->dm == 8;
     if (c->nA) {
         if (sliced && c->slice_on[0])
-            CU(launch_score_sliced(1, c->cfg.device, a, c->tab[0], c->st));
+            CU(launch_score_sliced(1, c->cfg.device, a, c->tab[0], c->n_types_used, c->st));
         else
             CU(launch_score_single(c->dm, true, c->cfg.device, a,
                                    reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqsA),
@@ -650,7 +653,7 @@ static int score_locked(vgs_ctx *c) {
     }
     if (c->nB) {
         if (sliced && c->slice_on[1])
-            CU(launch_score_sliced(2, c->cfg.device, a, c->tab[1], c->st));
+            CU(launch_score_sliced(2, c->cfg.device, a, c->tab[1], c->n_types_used, c->st));
         else
             CU(launch_score_single(c->dm, false, c->cfg.device, a,
                                    reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqsB),

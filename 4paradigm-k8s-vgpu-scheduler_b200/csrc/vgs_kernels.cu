@@ -123,6 +123,12 @@ __global__ void __launch_bounds__(128)
         }
     }
     if (bad) atomicOr(status, bad);
+    {
+        int mt = 0;
+#pragma unroll
+        for (int j = 0; j < DM; j++) mt = max(mt, type[j]);
+        if (mt > 0) atomicMax(status + 1, (uint32_t)mt); // status[1] = largest type id in use
+    }
 
     const int tile = row / kWarp, lane = row % kWarp;
     int32_t *wbase = reinterpret_cast<int32_t *>(walk + (size_t)tile * kWalkWords * (DM / 4) * kWarp);
@@ -512,6 +518,38 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t by
 
 constexpr int kTileInt4 = kWalkWords * 2 * kWarp; // DM = 8: 512 int4 = 8 KB per 32-node tile
 constexpr int kTileBytes = kTileInt4 * 16;
+constexpr int kDict = 64;        // distinct candidate scores a CTA tracks exactly
+constexpr int kPend = 1024;      // new scores queued per tile
+constexpr uint32_t kNoClass = 0xffu;
+
+// per device of the current tile, filled once per tile (word offsets of the table rows)
+struct __align__(16) DevInfo {
+    uint32_t o_type, o_mem, o_pct, o_core;
+    uint32_t o_flag, cls, score, pad;
+};
+
+// shared-memory carve-up of k1_score_sliced (bytes); T = threads per CTA
+struct SliceSmem {
+    int tile, bar, dev, pscore, pcls, vals, meta, pend, below, best, row, tab, total;
+};
+__host__ __device__ inline SliceSmem slice_smem(int T, int nums, int tab_rows) {
+    SliceSmem m;
+    int o = 0;
+    m.tile = o, o += 2 * kTileBytes;
+    m.bar = o, o += 64;
+    m.dev = o, o += 256 * (int)sizeof(DevInfo);
+    m.pscore = o, o += nums == 2 ? 32 * 28 * 4 : 0;
+    m.pcls = o, o += nums == 2 ? 32 * 28 : 0;
+    m.vals = o, o += kDict * 4;
+    m.meta = o, o += 16; // nvals, npend
+    m.pend = o, o += kPend * 4;
+    m.below = o, o += kDict * T * 4;
+    m.best = o, o += 32 * T * 4;
+    m.row = o, o += 32 * T * 4;
+    m.tab = o, o += tab_rows * T * 4;
+    m.total = o;
+    return m;
+}
 
 // number of sorted values v[0..n) that satisfy pred(v) where pred is monotone (true prefix)
 template <typename F>
@@ -525,24 +563,46 @@ __device__ __forceinline__ int count_prefix(const int32_t *__restrict__ v, int n
     return lo;
 }
 
-template <int NUMS, bool VERIFY>
-__global__ void __launch_bounds__(256)
+// sum = a^b^c, carry = majority: one step of a carry-save adder on 32 independent bit lanes
+__device__ __forceinline__ void csa(uint32_t &carry, uint32_t &sum, uint32_t a, uint32_t b, uint32_t c) {
+    sum = a ^ b ^ c;
+    carry = (a & b) | (a & c) | (b & c);
+}
+
+// pair index q of (a, b), a < b < 8, in the order the loops below enumerate them
+__host__ __device__ constexpr int pair_index(int a, int b) { return a * 7 - a * (a - 1) / 2 + (b - a - 1); }
+
+template <int NUMS, bool TABSMEM, bool VERIFY>
+__global__ void __launch_bounds__(128)
     k1_score_sliced(const int4 *__restrict__ walk, int32_t n_tiles, int32_t n_nodes, int32_t row_base,
-                    SliceTab tb, int32_t tiles_per_cta, unsigned long long *__restrict__ keys,
+                    SliceTab tb, int32_t n_types, int32_t tiles_per_cta, unsigned long long *__restrict__ keys,
                     int32_t *__restrict__ counts, uint32_t *__restrict__ vfit, float *__restrict__ vscore,
                     int32_t vwords) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int T = blockDim.x, tid = threadIdx.x;
-    int4 *tilebuf = reinterpret_cast<int4 *>(smem_raw);                                // [2][kTileInt4]
-    uint64_t *bar = reinterpret_cast<uint64_t *>(smem_raw + 2 * kTileBytes);           // [2]
-    uint16_t *cut = reinterpret_cast<uint16_t *>(smem_raw + 2 * kTileBytes + 64);      // [3][256]
-    uint32_t *s_best = reinterpret_cast<uint32_t *>(smem_raw + 2 * kTileBytes + 64 + 3 * 256 * 2); // [32][T]
-    uint32_t *s_row = s_best + 32 * T;                                                 // [32][T]
+    // table rows, global numbering: [type 0..63][mem 0..km][pct 0..kp][core 0..kc][flag 0..3]
+    const int r_mem = VGS_MAX_TYPES, r_pct = r_mem + tb.km + 1, r_core = r_pct + tb.kp + 1, r_flag = r_core + tb.kc + 1;
+    const int rows_g = r_flag + 4;
+    // the shared copy keeps only the type rows that can occur (ids < n_types)
+    const int drop = TABSMEM ? VGS_MAX_TYPES - n_types : 0;
+    const SliceSmem L = slice_smem(T, NUMS, TABSMEM ? rows_g - drop : 0);
+    int4 *tilebuf = reinterpret_cast<int4 *>(smem_raw + L.tile);
+    uint64_t *bar = reinterpret_cast<uint64_t *>(smem_raw + L.bar);
+    DevInfo *dev = reinterpret_cast<DevInfo *>(smem_raw + L.dev);
+    uint32_t *pscore = reinterpret_cast<uint32_t *>(smem_raw + L.pscore);
+    uint8_t *pcls = reinterpret_cast<uint8_t *>(smem_raw + L.pcls);
+    uint32_t *vals = reinterpret_cast<uint32_t *>(smem_raw + L.vals);
+    int *s_meta = reinterpret_cast<int *>(smem_raw + L.meta); // [0] nvals, [1] npend
+    uint32_t *pend = reinterpret_cast<uint32_t *>(smem_raw + L.pend);
+    uint32_t *below = reinterpret_cast<uint32_t *>(smem_raw + L.below); // [kDict][T]: pods with best < vals[k]
+    uint32_t *s_best = reinterpret_cast<uint32_t *>(smem_raw + L.best);  // [32][T] raw score bits, 0 = none
+    uint32_t *s_row = reinterpret_cast<uint32_t *>(smem_raw + L.row);    // [32][T] local row
+    const uint32_t *tabs = reinterpret_cast<const uint32_t *>(smem_raw + L.tab);
 
     const int w = blockIdx.y * T + tid;
     const bool active = w < tb.W;
-    const int wl = active ? w : 0;
-    // tiles [t_lo, t_hi) of this CTA, visited from t_hi-1 down
+    const int wc = min(w, tb.Wp - 1); // clamped column: inactive threads compute garbage, never publish
+    const int stride = TABSMEM ? T : tb.Wp;
     const int t_hi = n_tiles - (int)blockIdx.x * tiles_per_cta;
     const int t_lo = max(0, t_hi - tiles_per_cta);
     if (t_hi <= 0) return;
@@ -552,7 +612,17 @@ __global__ void __launch_bounds__(256)
         s_best[b * T + tid] = 0u;
         s_row[b * T + tid] = 0u;
     }
+    for (int k = 0; k < kDict; k++) below[k * T + tid] = 0xffffffffu;
+    if (TABSMEM) {
+        uint32_t *tw = reinterpret_cast<uint32_t *>(smem_raw + L.tab);
+        for (int r = 0; r < rows_g - drop; r++) {
+            const int rg = r < n_types ? r : r + drop;
+            tw[r * T + tid] = __ldg(&tb.base[(size_t)rg * tb.Wp + wc]);
+        }
+    }
     if (tid == 0) {
+        s_meta[0] = 0;
+        s_meta[1] = 0;
         mbar_init(&bar[0], 1);
         mbar_init(&bar[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -563,34 +633,43 @@ __global__ void __launch_bounds__(256)
         bulk_g2s(tilebuf, walk + (size_t)(t_hi - 1) * kTileInt4, kTileBytes, &bar[0]);
     }
 
-    const uint32_t c100 = __ldg(&tb.c100[wl]), c0 = __ldg(&tb.c0[wl]), never = __ldg(&tb.never[wl]);
-    uint32_t cnt[kSliceCountPlanes];
-#pragma unroll
-    for (int k = 0; k < kSliceCountPlanes; k++) cnt[k] = 0u;
-    // pruning state: `unseen` = my pods that have no candidate yet; minbest = min of s_best
-    // over the others (raw positive float bits).  A candidate word matters only if it
-    // reaches an unseen pod or carries a score above minbest.
-    uint32_t unseen = 0xffffffffu, minbest = 0xffffffffu;
-
-    auto update = [&](uint32_t word, uint32_t sbits, uint32_t row) {
-        // rare path: pods in `word` get candidate (sbits, row); rows only ever decrease here
-        uint32_t m = word;
-        while (m) {
-            int b = __ffs((int)m) - 1;
-            m &= m - 1;
-            if (sbits > s_best[b * T + tid]) {
-                s_best[b * T + tid] = sbits;
-                s_row[b * T + tid] = row;
+    auto TAB = [&](uint32_t off) -> uint32_t {
+        if (TABSMEM) return tabs[off + tid];
+        return __ldg(&tb.base[off + wc]);
+    };
+    auto row_off = [&](int rg) -> uint32_t { // global row number -> word offset in the table in use
+        const int r = (TABSMEM && rg >= VGS_MAX_TYPES) ? rg - drop : rg;
+        return (uint32_t)r * (uint32_t)stride;
+    };
+    auto find_class = [&](uint32_t sb, int nv) -> uint32_t { // index of sb in vals[0..nv) or kNoClass
+        int lo = 0, hi = nv;
+        while (lo < hi) {
+            int mid = (lo + hi) >> 1;
+            if (vals[mid] < sb) lo = mid + 1;
+            else hi = mid;
+        }
+        return (lo < nv && vals[lo] == sb) ? (uint32_t)lo : kNoClass;
+    };
+    // pods in `word` get candidate (sb, node); nodes only ever decrease, so equal scores keep
+    // the earlier (higher) row.  Keeps below[] exact: a pod whose best reaches sb leaves every
+    // below[k] with vals[k] <= sb.
+    auto raise = [&](uint32_t word, uint32_t sb, uint32_t node) {
+        uint32_t imp = 0u;
+        for (uint32_t m = word; m; m &= m - 1) {
+            const int b = __ffs((int)m) - 1;
+            if (sb > s_best[b * T + tid]) {
+                s_best[b * T + tid] = sb;
+                s_row[b * T + tid] = node;
+                imp |= 1u << b;
             }
         }
-        unseen &= ~word;
-        uint32_t mn = 0xffffffffu;
-        for (int b = 0; b < 32; b++) {
-            const uint32_t v = s_best[b * T + tid];
-            mn = v ? min(mn, v) : mn;
-        }
-        minbest = mn;
+        const int nv = s_meta[0];
+        for (int k = 0; k < nv && vals[k] <= sb; k++) below[k * T + tid] &= ~imp;
     };
+
+    uint32_t ones = 0u, twos = 0u, cnt[kSliceCountPlanes]; // fit counter: ones, twos, cnt[k] = bit k (k >= 2)
+#pragma unroll
+    for (int k = 0; k < kSliceCountPlanes; k++) cnt[k] = 0u;
 
     for (int it = 0; it < n_my; it++) {
         const int tile = t_hi - 1 - it;
@@ -601,119 +680,186 @@ __global__ void __launch_bounds__(256)
                      &bar[(it + 1) & 1]);
         }
         mbar_wait(&bar[it & 1], (uint32_t)((it >> 1) & 1));
-        // thresholds admitted by each of the tile's 256 devices
+
+        // ---- per-tile pre-pass: everything that depends on the node only -------------------
         const int32_t *ti = reinterpret_cast<const int32_t *>(tb4);
+        auto tile_word = [&](int wd, int l, int j) { return ti[(((wd * 2 + (j >> 2)) * kWarp + l) << 2) + (j & 3)]; };
+        int nv = s_meta[0];
         for (int d = tid; d < 256; d += T) {
             const int l = d >> 3, j = d & 7;
-            auto word_of = [&](int wd) { return ti[(((wd * 2 + (j >> 2)) * kWarp + l) << 2) + (j & 3)]; };
-            const int32_t fm = word_of(W_FREEMEM), fc = word_of(W_FREECORES), tm = word_of(W_TOTALMEM);
-            cut[d] = (uint16_t)count_prefix(tb.memv, tb.km, [&](int32_t v) { return v <= fm; });
-            cut[256 + d] = (uint16_t)count_prefix(tb.pctv, tb.kp, [&](int32_t v) { return pct_mem(tm, v) <= fm; });
-            cut[512 + d] = (uint16_t)count_prefix(tb.corev, tb.kc, [&](int32_t v) { return v <= fc; });
+            const uint32_t m = (uint32_t)tile_word(W_META, l, j);
+            DevInfo di;
+            di.pad = 0;
+            if (m & (M_NOFREE | M_PAD)) { // Count <= Used (score.go:107) or not a device: never fits
+                di.o_type = di.o_mem = di.o_pct = di.o_core = di.o_flag = row_off(r_mem); // memle row 0 is all zero
+                di.cls = 0;
+                di.score = 0;
+            } else {
+                const int32_t fm = tile_word(W_FREEMEM, l, j), fc = tile_word(W_FREECORES, l, j);
+                const int32_t tm = tile_word(W_TOTALMEM, l, j);
+                di.o_type = row_off((int)(m & M_TYPE_MASK));
+                di.o_mem = row_off(r_mem + count_prefix(tb.memv, tb.km, [&](int32_t v) { return v <= fm; }));
+                di.o_pct = row_off(r_pct + count_prefix(tb.pctv, tb.kp, [&](int32_t v) { return pct_mem(tm, v) <= fm; }));
+                di.o_core = row_off(r_core + count_prefix(tb.corev, tb.kc, [&](int32_t v) { return v <= fc; }));
+                di.o_flag = row_off(r_flag + ((m & M_EXCL) ? 1 : 0) + ((m & M_FULL) ? 2 : 0));
+                di.score = (uint32_t)tile_word(W_SCORE1, l, j);
+                di.cls = 0;
+                if (NUMS == 1) {
+                    di.cls = find_class(di.score, nv);
+                    if (di.cls == kNoClass) {
+                        const int slot = atomicAdd(&s_meta[1], 1);
+                        if (slot < kPend) pend[slot] = di.score;
+                    }
+                }
+            }
+            dev[d] = di;
+        }
+        if (NUMS == 2) {
+            for (int q = tid; q < 32 * 28; q += T) {
+                const int l = q / 28, pr = q - l * 28;
+                int a = 0, rest = pr; // pair number -> (a, b)
+                while (rest >= 7 - a) rest -= 7 - a, a++;
+                const int b = a + 1 + rest;
+                const uint32_t ma = (uint32_t)tile_word(W_META, l, a), mb = (uint32_t)tile_word(W_META, l, b);
+                uint32_t sb = 0u, cl = 0u;
+                if (!((ma | mb) & (M_NOFREE | M_PAD))) {
+                    const int32_t nd = (int32_t)((ma >> M_NDEV_SHIFT) & 15u);
+                    sb = __float_as_uint(container_score(
+                        wrap_add(tile_word(W_COUNT, l, a), tile_word(W_COUNT, l, b)),
+                        wrap_add(tile_word(W_FREESLOTS, l, a), tile_word(W_FREESLOTS, l, b)), nd - 2));
+                    cl = find_class(sb, nv);
+                    if (cl == kNoClass) {
+                        const int slot = atomicAdd(&s_meta[1], 1);
+                        if (slot < kPend) pend[slot] = sb;
+                    }
+                }
+                pscore[q] = sb;
+                pcls[q] = (uint8_t)cl;
+            }
         }
         __syncthreads();
-
-        for (int l = kWarp - 1; l >= 0; l--) {
-            const int node = tile * kWarp + l;
-            if (node >= n_nodes) continue; // uniform
-            int32_t meta[8], s1[8], cn[8], fs[8];
-            {
-                int4 a = tb4[(W_META * 2 + 0) * kWarp + l], b = tb4[(W_META * 2 + 1) * kWarp + l];
-                meta[0] = a.x, meta[1] = a.y, meta[2] = a.z, meta[3] = a.w;
-                meta[4] = b.x, meta[5] = b.y, meta[6] = b.z, meta[7] = b.w;
-                if (NUMS == 1) {
-                    a = tb4[(W_SCORE1 * 2 + 0) * kWarp + l], b = tb4[(W_SCORE1 * 2 + 1) * kWarp + l];
-                    s1[0] = a.x, s1[1] = a.y, s1[2] = a.z, s1[3] = a.w;
-                    s1[4] = b.x, s1[5] = b.y, s1[6] = b.z, s1[7] = b.w;
-                } else {
-                    a = tb4[(W_COUNT * 2 + 0) * kWarp + l], b = tb4[(W_COUNT * 2 + 1) * kWarp + l];
-                    cn[0] = a.x, cn[1] = a.y, cn[2] = a.z, cn[3] = a.w;
-                    cn[4] = b.x, cn[5] = b.y, cn[6] = b.z, cn[7] = b.w;
-                    a = tb4[(W_FREESLOTS * 2 + 0) * kWarp + l], b = tb4[(W_FREESLOTS * 2 + 1) * kWarp + l];
-                    fs[0] = a.x, fs[1] = a.y, fs[2] = a.z, fs[3] = a.w;
-                    fs[4] = b.x, fs[5] = b.y, fs[6] = b.z, fs[7] = b.w;
+        int npend = min(s_meta[1], kPend);
+        if (npend > 0) { // uniform: new score values -> insert into the sorted dictionary
+            for (int i = 0; i < npend; i++) {
+                const uint32_t x = pend[i];
+                int lo = 0, hi = nv;
+                while (lo < hi) {
+                    int mid = (lo + hi) >> 1;
+                    if (vals[mid] < x) lo = mid + 1;
+                    else hi = mid;
                 }
-            }
-            const int32_t ndev = (meta[0] >> M_NDEV_SHIFT) & 15;
-            uint32_t fit[8];
-#pragma unroll
-            for (int j = 0; j < 8; j++) {
-                const uint32_t m = (uint32_t)meta[j];
-                if (m & (M_NOFREE | M_PAD)) { // uniform: Count <= Used, or not a device
-                    fit[j] = 0u;
-                    continue;
+                if ((lo < nv && vals[lo] == x) || nv >= kDict) continue; // known, or dictionary full
+                __syncthreads();
+                // below[] of the new value = below[] of the next larger value (no best lies between)
+                for (int k = nv; k > lo; k--) below[k * T + tid] = below[(k - 1) * T + tid];
+                if (lo == nv) below[lo * T + tid] = 0xffffffffu; // larger than every best so far
+                if (tid == 0) {
+                    for (int k = nv; k > lo; k--) vals[k] = vals[k - 1];
+                    vals[lo] = x;
+                    s_meta[0] = nv + 1;
                 }
-                const int d = l * 8 + j;
-                const uint32_t ty = __ldg(&tb.type[(size_t)(m & M_TYPE_MASK) * tb.Wp + wl]);
-                const uint32_t mm = __ldg(&tb.memle[(size_t)cut[d] * tb.Wp + wl]);
-                const uint32_t pp = __ldg(&tb.pctle[(size_t)cut[256 + d] * tb.Wp + wl]);
-                const uint32_t cc = __ldg(&tb.corele[(size_t)cut[512 + d] * tb.Wp + wl]);
-                uint32_t blocked = never;
-                if (m & M_EXCL) blocked |= c100; // score.go:128
-                if (m & M_FULL) blocked |= c0;   // score.go:132
-                fit[j] = active ? (ty & (mm | pp) & cc & ~blocked) : 0u;
+                nv++;
+                __syncthreads();
             }
-            uint32_t anyfit;
+            __syncthreads();
+            if (tid == 0) s_meta[1] = 0;
+            // classes again, now that (almost always) every value is known
             if (NUMS == 1) {
-                uint32_t rem = 0xffffffffu;
-#pragma unroll
-                for (int j = 0; j < 8; j++) { // walk order: the first fitting device is taken
-                    const uint32_t nw = fit[j] & rem;
-                    rem &= ~fit[j];
-                    if (VERIFY) {
-                        for (uint32_t mth = nw; mth; mth &= mth - 1) {
-                            int p = tb.orig[w * 32 + __ffs((int)mth) - 1];
-                            vscore[(size_t)p * n_nodes + node] = __int_as_float(s1[j]);
-                        }
-                    }
-                    if ((nw & unseen) || (nw && (uint32_t)s1[j] > minbest)) update(nw, (uint32_t)s1[j], (uint32_t)node);
-                }
-                anyfit = ~rem;
+                for (int d = tid; d < 256; d += T)
+                    if (dev[d].score) dev[d].cls = find_class(dev[d].score, nv);
             } else {
-                uint32_t seen = 0u, seen2 = 0u, first[8], second[8];
+                for (int q = tid; q < 32 * 28; q += T)
+                    if (pscore[q]) pcls[q] = (uint8_t)find_class(pscore[q], nv);
+            }
+            __syncthreads();
+        }
+
+        // ---- 32 nodes, descending; four at a time for the carry-save fit counter ----------
+        for (int lq = 7; lq >= 0; lq--) {
+            uint32_t xs[4];
+#pragma unroll
+            for (int u = 3; u >= 0; u--) {
+                const int l = lq * 4 + u;
+                const int node = tile * kWarp + l;
+                uint32_t fit[8];
+                uint32_t dcls[8], dsc[8];
 #pragma unroll
                 for (int j = 0; j < 8; j++) {
-                    first[j] = fit[j] & ~seen;
-                    second[j] = fit[j] & seen & ~seen2;
-                    seen2 |= seen & fit[j];
-                    seen |= fit[j];
+                    const int4 o = *reinterpret_cast<const int4 *>(&dev[l * 8 + j]);
+                    const int4 o2 = *(reinterpret_cast<const int4 *>(&dev[l * 8 + j]) + 1);
+                    const uint32_t ty = TAB((uint32_t)o.x), mm = TAB((uint32_t)o.y), pp = TAB((uint32_t)o.z);
+                    const uint32_t cc = TAB((uint32_t)o.w), ok = TAB((uint32_t)o2.x);
+                    fit[j] = ty & (mm | pp) & cc & ok;
+                    dcls[j] = (uint32_t)o2.y;
+                    dsc[j] = (uint32_t)o2.z;
                 }
-                anyfit = seen2; // the node fits a pod iff two devices fit
+                uint32_t anyfit;
+                if (NUMS == 1) {
+                    uint32_t rem = 0xffffffffu;
 #pragma unroll
-                for (int a = 0; a < 7; a++) {
-                    if (!__any_sync(0xffffffffu, first[a] != 0u)) continue;
-#pragma unroll
-                    for (int b = a + 1; b < 8; b++) {
-                        const uint32_t wab = first[a] & second[b];
-                        if (!__any_sync(0xffffffffu, wab != 0u)) continue;
-                        const float sc = container_score(wrap_add(cn[a], cn[b]), wrap_add(fs[a], fs[b]), ndev - 2);
-                        const uint32_t sb = __float_as_uint(sc);
-                        if (VERIFY) {
-                            for (uint32_t mth = wab; mth; mth &= mth - 1) {
-                                int p = tb.orig[w * 32 + __ffs((int)mth) - 1];
-                                vscore[(size_t)p * n_nodes + node] = sc;
+                    for (int j = 0; j < 8; j++) { // walk order: the first fitting device is taken
+                        const uint32_t nw = fit[j] & rem;
+                        rem &= ~fit[j];
+                        if (VERIFY && active) {
+                            for (uint32_t mth = nw; mth; mth &= mth - 1) {
+                                const int p = tb.orig[w * 32 + __ffs((int)mth) - 1];
+                                vscore[(size_t)p * n_nodes + node] = __uint_as_float(dsc[j]);
                             }
                         }
-                        if ((wab & unseen) || (wab && sb > minbest)) update(wab, sb, (uint32_t)node);
+                        const uint32_t bl = dcls[j] < (uint32_t)kDict ? below[dcls[j] * T + tid] : 0xffffffffu;
+                        if (nw & bl) raise(nw & bl, dsc[j], (uint32_t)node);
+                    }
+                    anyfit = ~rem;
+                } else {
+                    uint32_t seen = 0u, seen2 = 0u, first[8], second[8];
+#pragma unroll
+                    for (int j = 0; j < 8; j++) {
+                        first[j] = fit[j] & ~seen;
+                        second[j] = fit[j] & seen & ~seen2;
+                        seen2 |= seen & fit[j];
+                        seen |= fit[j];
+                    }
+                    anyfit = seen2; // the node fits a pod iff two devices fit
+#pragma unroll
+                    for (int a = 0; a < 7; a++) {
+                        if (!__any_sync(0xffffffffu, first[a] != 0u)) continue;
+#pragma unroll
+                        for (int b = a + 1; b < 8; b++) {
+                            const uint32_t wab = first[a] & second[b];
+                            const int q = l * 28 + pair_index(a, b);
+                            const uint32_t cl = pcls[q];
+                            if (VERIFY && active) {
+                                for (uint32_t mth = wab; mth; mth &= mth - 1) {
+                                    const int p = tb.orig[w * 32 + __ffs((int)mth) - 1];
+                                    vscore[(size_t)p * n_nodes + node] = __uint_as_float(pscore[q]);
+                                }
+                            }
+                            const uint32_t bl = cl < (uint32_t)kDict ? below[cl * T + tid] : 0xffffffffu;
+                            if (wab & bl) raise(wab & bl, pscore[q], (uint32_t)node);
+                        }
                     }
                 }
-            }
-            if (VERIFY) {
-                for (uint32_t mth = anyfit; mth; mth &= mth - 1) {
-                    int p = tb.orig[w * 32 + __ffs((int)mth) - 1];
-                    atomicOr(&vfit[(size_t)p * vwords + (node >> 5)], 1u << (node & 31));
+                if (VERIFY && active) {
+                    for (uint32_t mth = anyfit; mth; mth &= mth - 1) {
+                        const int p = tb.orig[w * 32 + __ffs((int)mth) - 1];
+                        atomicOr(&vfit[(size_t)p * vwords + (node >> 5)], 1u << (node & 31));
+                    }
                 }
+                xs[u] = anyfit;
             }
-            // bit-sliced fit counter += anyfit
-            uint32_t carry = anyfit;
+            // counter += xs[0] + xs[1] + xs[2] + xs[3] (bit-sliced, carry-save)
+            uint32_t ca, sa, cb, cf;
+            csa(ca, sa, ones, xs[0], xs[1]);
+            csa(cb, ones, sa, xs[2], xs[3]);
+            csa(cf, twos, twos, ca, cb);
 #pragma unroll
-            for (int k = 0; k < kSliceCountPlanes; k++) {
-                const uint32_t t2 = cnt[k] & carry;
-                cnt[k] ^= carry;
-                carry = t2;
+            for (int k = 2; k < kSliceCountPlanes; k++) {
+                const uint32_t t2 = cnt[k] & cf;
+                cnt[k] ^= cf;
+                cf = t2;
             }
         }
-        __syncthreads(); // everyone is done with this buffer and with cut[]
+        __syncthreads(); // everyone is done with this tile buffer, dev[] and the pair tables
     }
 
     if (!active) return;
@@ -722,13 +868,13 @@ __global__ void __launch_bounds__(256)
         if (i >= tb.n_pods) break;
         const uint32_t sb = s_best[b * T + tid];
         if (sb == 0u) continue;
-        int32_t c = 0;
+        int32_t c = (int32_t)((ones >> b) & 1u) | ((int32_t)((twos >> b) & 1u) << 1);
 #pragma unroll
-        for (int k = 0; k < kSliceCountPlanes; k++) c |= (int32_t)((cnt[k] >> b) & 1u) << k;
+        for (int k = 2; k < kSliceCountPlanes; k++) c |= (int32_t)((cnt[k] >> b) & 1u) << k;
         const int p = __ldg(&tb.orig[i]);
         // scores of single-request pods are positive: ordered bits = bits | sign bit
-        const unsigned long long key =
-            ((unsigned long long)(sb | 0x80000000u) << 32) | (unsigned long long)(uint32_t)(row_base + (int)s_row[b * T + tid]);
+        const unsigned long long key = ((unsigned long long)(sb | 0x80000000u) << 32) |
+                                       (unsigned long long)(uint32_t)(row_base + (int)s_row[b * T + tid]);
         atomicMax(&keys[p], key);
         atomicAdd(&counts[p], c);
     }
@@ -1028,21 +1174,25 @@ cudaError_t launch_score_general(int dm, int dev, const ScoreArgs &a, const DevR
 
 
 template <int NUMS>
-static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &tb, cudaStream_t st) {
+static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &tb, int n_types, cudaStream_t st) {
     const int sms = sm_count(dev);
     int warps = (tb.W + 31) / 32;
-    if (warps > 8) warps = 8;
+    if (warps > 4) warps = 4;
     const int T = warps * 32;
     const int gy = (tb.W + T - 1) / T;
-    const int smem = 2 * kTileBytes + 64 + 3 * 256 * 2 + 2 * 32 * T * 4;
+    if (n_types < 1) n_types = 1;
+    if (n_types > VGS_MAX_TYPES) n_types = VGS_MAX_TYPES;
+    const int rows_s = n_types + (tb.km + 1) + (tb.kp + 1) + (tb.kc + 1) + 4;
+    const bool tabsmem = (size_t)rows_s * T * 4 <= 56 * 1024; // else the tables stay in global / L1
+    const int smem = slice_smem(T, NUMS, tabsmem ? rows_s : 0).total;
     cudaError_t e;
     auto go = [&](auto kernel) -> cudaError_t {
         if ((e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)) != cudaSuccess) return e;
         int occ = 1;
         if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, T, smem)) != cudaSuccess) return e;
         if (occ < 1) occ = 1;
-        // one wave of CTAs; at least 4 tiles each so the per-CTA flush stays small, at most
-        // (2^planes - 1) nodes each so the bit-sliced counter cannot overflow
+        // one wave of CTAs; at least 4 tiles each so the per-CTA set-up and flush stay small, at
+        // most (2^planes - 1) nodes each so the bit-sliced counter cannot overflow
         long long want = (long long)sms * occ / gy;
         if (want < 1) want = 1;
         int tiles_per = (int)((a.n_tiles + want - 1) / want);
@@ -1050,17 +1200,18 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
         const int cap = ((1 << kSliceCountPlanes) - 1) / kWarp;
         if (tiles_per > cap) tiles_per = cap;
         const int gx = (a.n_tiles + tiles_per - 1) / tiles_per;
-        kernel<<<dim3(gx, gy), T, smem, st>>>(a.walk, a.n_tiles, a.n_nodes, a.row_base, tb, tiles_per, a.keys, a.counts,
-                                              a.vfit, a.vscore, a.vwords);
+        kernel<<<dim3(gx, gy), T, smem, st>>>(a.walk, a.n_tiles, a.n_nodes, a.row_base, tb, n_types, tiles_per, a.keys,
+                                              a.counts, a.vfit, a.vscore, a.vwords);
         return cudaGetLastError();
     };
-    if (a.vfit) return go(k1_score_sliced<NUMS, true>);
-    return go(k1_score_sliced<NUMS, false>);
+    if (a.vfit) return tabsmem ? go(k1_score_sliced<NUMS, true, true>) : go(k1_score_sliced<NUMS, false, true>);
+    return tabsmem ? go(k1_score_sliced<NUMS, true, false>) : go(k1_score_sliced<NUMS, false, false>);
 }
 
-cudaError_t launch_score_sliced(int nums, int dev, const ScoreArgs &a, const SliceTab &tb, cudaStream_t st) {
+cudaError_t launch_score_sliced(int nums, int dev, const ScoreArgs &a, const SliceTab &tb, int n_types,
+                                cudaStream_t st) {
     if (tb.n_pods <= 0 || a.n_tiles <= 0) return cudaSuccess;
-    return nums == 1 ? launch_sliced_t<1>(dev, a, tb, st) : launch_sliced_t<2>(dev, a, tb, st);
+    return nums == 1 ? launch_sliced_t<1>(dev, a, tb, n_types, st) : launch_sliced_t<2>(dev, a, tb, n_types, st);
 }
 
 cudaError_t launch_merge(const unsigned long long *gk, const int32_t *gc, int32_t n_shards, int32_t stride,

@@ -76,13 +76,15 @@ struct GenPod {
 // the pods whose threshold is among the c smallest distinct values, so a device whose
 // capacity admits exactly c of the distinct values selects row c.
 struct SliceTab {
-    const uint32_t *type;   // [VGS_MAX_TYPES][Wp]  pods whose type mask has the bit
-    const uint32_t *memle;  // [km+1][Wp]  fixed-MB pods by Memreq
-    const uint32_t *pctle;  // [kp+1][Wp]  percentage pods by MemPercentagereq
-    const uint32_t *corele; // [kc+1][Wp]  all pods by Coresreq
-    const uint32_t *c100;   // [Wp] Coresreq == 100
-    const uint32_t *c0;     // [Wp] Coresreq == 0
-    const uint32_t *never;  // [Wp] Coresreq > 100
+    // all rows in one buffer, row r at base + r * Wp, in this order:
+    //   [0, 64)            type rows: pods whose type mask has bit t
+    //   [64, 64+km+1)      fixed-MB pods by Memreq (cumulative; row 0 is all zero)
+    //   then kp+1 rows     percentage pods by MemPercentagereq (cumulative)
+    //   then kc+1 rows     all pods by Coresreq (cumulative)
+    //   then 4 rows        pods NOT ruled out by the device flags: index = excl | full << 1
+    //                      (excl: Coresreq == 100 pods lose, full: Coresreq == 0 pods lose,
+    //                       Coresreq > 100 pods always lose)
+    const uint32_t *base;
     const int32_t *memv, *pctv, *corev; // sorted distinct values
     const int32_t *orig;                // class position -> pod index of the batch
     int32_t km, kp, kc;
