@@ -14,6 +14,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <cstdlib>
+
 #include "../../include/vgpuscore.h"
 #include "vgs_kernels.h"
 #include "vgs_layout.h"
@@ -518,49 +520,54 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t by
 
 constexpr int kTileInt4 = kWalkWords * 2 * kWarp; // DM = 8: 512 int4 = 8 KB per 32-node tile
 constexpr int kTileBytes = kTileInt4 * 16;
-constexpr int kDict = 64;        // distinct candidate scores a CTA tracks exactly
-constexpr int kPend = 1024;      // new scores queued per tile
-constexpr uint32_t kNoClass = 0xffu;
+constexpr int kDict = 32;   // distinct candidate scores a CTA tracks exactly (more: still correct, slower)
+constexpr int kPend = 256;  // new scores queued per tile
+constexpr int kPairs = 28;  // device pairs (a < b) of an 8-device node
 
-// per device of the current tile, filled once per tile (word offsets of the table rows)
+__constant__ uint8_t kPairA[kPairs] = {0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 1, 1, 2, 2, 2, 2, 2, 3, 3, 3, 3, 4, 4, 4, 5, 5, 6};
+__constant__ uint8_t kPairB[kPairs] = {1, 2, 3, 4, 5, 6, 7, 2, 3, 4, 5, 6, 7, 3, 4, 5, 6, 7, 4, 5, 6, 7, 5, 6, 7, 6, 7, 7};
+__host__ __device__ constexpr int pair_index(int a, int b) { return a * 7 - a * (a - 1) / 2 + (b - a - 1); }
+
+// per device of the current tile, filled once per tile: word offsets of its table rows, word
+// offset of its score class's row in below[], and its score
 struct __align__(16) DevInfo {
     uint32_t o_type, o_mem, o_pct, o_core;
-    uint32_t o_flag, cls, score, pad;
+    uint32_t o_flag, o_below, score, pad;
 };
 
 // shared-memory carve-up of k1_score_sliced (bytes); T = threads per CTA
 struct SliceSmem {
-    int tile, bar, dev, pscore, pcls, vals, meta, pend, below, best, row, tab, total;
+    int tile, bar, dev, pscore, pbelow, vals, meta, pend, below, best, row, tab, total;
 };
 __host__ __device__ inline SliceSmem slice_smem(int T, int nums, int tab_rows) {
     SliceSmem m;
     int o = 0;
-    m.tile = o, o += 2 * kTileBytes;
-    m.bar = o, o += 64;
+    m.tile = o, o += kTileBytes;
+    m.bar = o, o += 16;
     m.dev = o, o += 256 * (int)sizeof(DevInfo);
-    m.pscore = o, o += nums == 2 ? 32 * 28 * 4 : 0;
-    m.pcls = o, o += nums == 2 ? 32 * 28 : 0;
+    m.pscore = o, o += nums == 2 ? 32 * kPairs * 4 : 0;
+    m.pbelow = o, o += nums == 2 ? 32 * kPairs * 2 : 0;
     m.vals = o, o += kDict * 4;
     m.meta = o, o += 16; // nvals, npend
     m.pend = o, o += kPend * 4;
-    m.below = o, o += kDict * T * 4;
+    m.below = o, o += (kDict + 1) * T * 4;
     m.best = o, o += 32 * T * 4;
-    m.row = o, o += 32 * T * 4;
+    m.row = o, o += 32 * T * 2;
     m.tab = o, o += tab_rows * T * 4;
     m.total = o;
     return m;
 }
 
-// number of sorted values v[0..n) that satisfy pred(v) where pred is monotone (true prefix)
+// number of sorted values v[0..n) that satisfy the monotone predicate (true prefix); the
+// iteration count depends on n only, so a warp never diverges here
 template <typename F>
 __device__ __forceinline__ int count_prefix(const int32_t *__restrict__ v, int n, F pred) {
-    int lo = 0, hi = n; // invariant: pred true on [0,lo), false on [hi,n)
-    while (lo < hi) {
-        int mid = (lo + hi) >> 1;
-        if (pred(__ldg(&v[mid]))) lo = mid + 1;
-        else hi = mid;
+    int pos = 0;
+    for (int step = n > 0 ? 1 << (31 - __clz(n)) : 0; step > 0; step >>= 1) {
+        const int np = pos + step;
+        if (np <= n && pred(__ldg(&v[np - 1]))) pos = np;
     }
-    return lo;
+    return pos;
 }
 
 // sum = a^b^c, carry = majority: one step of a carry-save adder on 32 independent bit lanes
@@ -568,9 +575,6 @@ __device__ __forceinline__ void csa(uint32_t &carry, uint32_t &sum, uint32_t a, 
     sum = a ^ b ^ c;
     carry = (a & b) | (a & c) | (b & c);
 }
-
-// pair index q of (a, b), a < b < 8, in the order the loops below enumerate them
-__host__ __device__ constexpr int pair_index(int a, int b) { return a * 7 - a * (a - 1) / 2 + (b - a - 1); }
 
 template <int NUMS, bool TABSMEM, bool VERIFY>
 __global__ void __launch_bounds__(128)
@@ -590,13 +594,14 @@ __global__ void __launch_bounds__(128)
     uint64_t *bar = reinterpret_cast<uint64_t *>(smem_raw + L.bar);
     DevInfo *dev = reinterpret_cast<DevInfo *>(smem_raw + L.dev);
     uint32_t *pscore = reinterpret_cast<uint32_t *>(smem_raw + L.pscore);
-    uint8_t *pcls = reinterpret_cast<uint8_t *>(smem_raw + L.pcls);
+    uint16_t *pbelow = reinterpret_cast<uint16_t *>(smem_raw + L.pbelow);
     uint32_t *vals = reinterpret_cast<uint32_t *>(smem_raw + L.vals);
     int *s_meta = reinterpret_cast<int *>(smem_raw + L.meta); // [0] nvals, [1] npend
     uint32_t *pend = reinterpret_cast<uint32_t *>(smem_raw + L.pend);
-    uint32_t *below = reinterpret_cast<uint32_t *>(smem_raw + L.below); // [kDict][T]: pods with best < vals[k]
-    uint32_t *s_best = reinterpret_cast<uint32_t *>(smem_raw + L.best);  // [32][T] raw score bits, 0 = none
-    uint32_t *s_row = reinterpret_cast<uint32_t *>(smem_raw + L.row);    // [32][T] local row
+    // below[k][t]: my pods whose best is < vals[k] (may over-approximate, never under); row kDict = all ones
+    uint32_t *below = reinterpret_cast<uint32_t *>(smem_raw + L.below);
+    uint32_t *s_best = reinterpret_cast<uint32_t *>(smem_raw + L.best); // [32][T] raw score bits, 0 = none
+    uint16_t *s_row = reinterpret_cast<uint16_t *>(smem_raw + L.row);   // [32][T] row - first row of this CTA
     const uint32_t *tabs = reinterpret_cast<const uint32_t *>(smem_raw + L.tab);
 
     const int w = blockIdx.y * T + tid;
@@ -607,12 +612,13 @@ __global__ void __launch_bounds__(128)
     const int t_lo = max(0, t_hi - tiles_per_cta);
     if (t_hi <= 0) return;
     const int n_my = t_hi - t_lo;
+    const int node_lo = t_lo * kWarp;
 
     for (int b = 0; b < 32; b++) {
         s_best[b * T + tid] = 0u;
-        s_row[b * T + tid] = 0u;
+        s_row[b * T + tid] = 0;
     }
-    for (int k = 0; k < kDict; k++) below[k * T + tid] = 0xffffffffu;
+    for (int k = 0; k <= kDict; k++) below[k * T + tid] = 0xffffffffu;
     if (TABSMEM) {
         uint32_t *tw = reinterpret_cast<uint32_t *>(smem_raw + L.tab);
         for (int r = 0; r < rows_g - drop; r++) {
@@ -624,7 +630,6 @@ __global__ void __launch_bounds__(128)
         s_meta[0] = 0;
         s_meta[1] = 0;
         mbar_init(&bar[0], 1);
-        mbar_init(&bar[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
@@ -641,30 +646,83 @@ __global__ void __launch_bounds__(128)
         const int r = (TABSMEM && rg >= VGS_MAX_TYPES) ? rg - drop : rg;
         return (uint32_t)r * (uint32_t)stride;
     };
-    auto find_class = [&](uint32_t sb, int nv) -> uint32_t { // index of sb in vals[0..nv) or kNoClass
+    auto find_class = [&](uint32_t sb, int nv) -> int { // index of sb in vals[0..nv) or kDict
         int lo = 0, hi = nv;
         while (lo < hi) {
             int mid = (lo + hi) >> 1;
             if (vals[mid] < sb) lo = mid + 1;
             else hi = mid;
         }
-        return (lo < nv && vals[lo] == sb) ? (uint32_t)lo : kNoClass;
+        return (lo < nv && vals[lo] == sb) ? lo : kDict;
+    };
+    auto fit_word = [&](int d) -> uint32_t {
+        const int4 o = *reinterpret_cast<const int4 *>(&dev[d]);
+        const uint32_t ok = TAB(dev[d].o_flag);
+        return TAB((uint32_t)o.x) & (TAB((uint32_t)o.y) | TAB((uint32_t)o.z)) & TAB((uint32_t)o.w) & ok;
     };
     // pods in `word` get candidate (sb, node); nodes only ever decrease, so equal scores keep
-    // the earlier (higher) row.  Keeps below[] exact: a pod whose best reaches sb leaves every
-    // below[k] with vals[k] <= sb.
-    auto raise = [&](uint32_t word, uint32_t sb, uint32_t node) {
+    // the earlier (higher) row.  A pod whose best reaches sb leaves every below[k] with vals[k] <= sb.
+    auto raise = [&](uint32_t word, uint32_t sb, int node) {
         uint32_t imp = 0u;
         for (uint32_t m = word; m; m &= m - 1) {
             const int b = __ffs((int)m) - 1;
             if (sb > s_best[b * T + tid]) {
                 s_best[b * T + tid] = sb;
-                s_row[b * T + tid] = node;
+                s_row[b * T + tid] = (uint16_t)(node - node_lo);
                 imp |= 1u << b;
             }
         }
         const int nv = s_meta[0];
         for (int k = 0; k < nv && vals[k] <= sb; k++) below[k * T + tid] &= ~imp;
+    };
+    // exact, ordered handling of one node: the reference's walk for every pod of my word
+    auto slow_node = [&](int l, int node) {
+        if (NUMS == 1) {
+            uint32_t rem = 0xffffffffu;
+#pragma unroll 1
+            for (int j = 0; j < 8; j++) {
+                const int d = l * 8 + j;
+                const uint32_t f = fit_word(d);
+                const uint32_t nw = f & rem; // pods whose first fitting device is j
+                rem &= ~f;
+                if (VERIFY && active) {
+                    for (uint32_t mth = nw; mth; mth &= mth - 1) {
+                        const int p = tb.orig[w * 32 + __ffs((int)mth) - 1];
+                        vscore[(size_t)p * n_nodes + node] = __uint_as_float(dev[d].score);
+                    }
+                }
+                const uint32_t hit = nw & below[dev[d].o_below + tid];
+                if (hit) raise(hit, dev[d].score, node);
+            }
+        } else {
+            uint32_t seen = 0u, seen2 = 0u, first[8], second[8];
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                const uint32_t f = fit_word(l * 8 + j);
+                first[j] = f & ~seen;
+                second[j] = f & seen & ~seen2;
+                seen2 |= seen & f;
+                seen |= f;
+            }
+#pragma unroll
+            for (int a = 0; a < 7; a++) {
+                if (first[a] == 0u) continue;
+#pragma unroll
+                for (int b = a + 1; b < 8; b++) {
+                    const uint32_t wab = first[a] & second[b]; // pods taking exactly devices a and b
+                    if (wab == 0u) continue;
+                    const int q = l * kPairs + pair_index(a, b);
+                    if (VERIFY && active) {
+                        for (uint32_t mth = wab; mth; mth &= mth - 1) {
+                            const int p = tb.orig[w * 32 + __ffs((int)mth) - 1];
+                            vscore[(size_t)p * n_nodes + node] = __uint_as_float(pscore[q]);
+                        }
+                    }
+                    const uint32_t hit = wab & below[pbelow[q] + tid];
+                    if (hit) raise(hit, pscore[q], node);
+                }
+            }
+        }
     };
 
     uint32_t ones = 0u, twos = 0u, cnt[kSliceCountPlanes]; // fit counter: ones, twos, cnt[k] = bit k (k >= 2)
@@ -673,16 +731,10 @@ __global__ void __launch_bounds__(128)
 
     for (int it = 0; it < n_my; it++) {
         const int tile = t_hi - 1 - it;
-        const int4 *tb4 = tilebuf + (it & 1) * kTileInt4;
-        if (tid == 0 && it + 1 < n_my) { // prefetch the next tile into the other buffer
-            mbar_expect_tx(&bar[(it + 1) & 1], kTileBytes);
-            bulk_g2s(tilebuf + ((it + 1) & 1) * kTileInt4, walk + (size_t)(tile - 1) * kTileInt4, kTileBytes,
-                     &bar[(it + 1) & 1]);
-        }
-        mbar_wait(&bar[it & 1], (uint32_t)((it >> 1) & 1));
+        mbar_wait(&bar[0], (uint32_t)(it & 1));
 
         // ---- per-tile pre-pass: everything that depends on the node only -------------------
-        const int32_t *ti = reinterpret_cast<const int32_t *>(tb4);
+        const int32_t *ti = reinterpret_cast<const int32_t *>(tilebuf);
         auto tile_word = [&](int wd, int l, int j) { return ti[(((wd * 2 + (j >> 2)) * kWarp + l) << 2) + (j & 3)]; };
         int nv = s_meta[0];
         for (int d = tid; d < 256; d += T) {
@@ -690,9 +742,9 @@ __global__ void __launch_bounds__(128)
             const uint32_t m = (uint32_t)tile_word(W_META, l, j);
             DevInfo di;
             di.pad = 0;
+            di.o_below = (uint32_t)(kDict * T);
             if (m & (M_NOFREE | M_PAD)) { // Count <= Used (score.go:107) or not a device: never fits
-                di.o_type = di.o_mem = di.o_pct = di.o_core = di.o_flag = row_off(r_mem); // memle row 0 is all zero
-                di.cls = 0;
+                di.o_type = di.o_mem = di.o_pct = di.o_core = di.o_flag = row_off(r_mem); // memle row 0: all zero
                 di.score = 0;
             } else {
                 const int32_t fm = tile_word(W_FREEMEM, l, j), fc = tile_word(W_FREECORES, l, j);
@@ -703,10 +755,10 @@ __global__ void __launch_bounds__(128)
                 di.o_core = row_off(r_core + count_prefix(tb.corev, tb.kc, [&](int32_t v) { return v <= fc; }));
                 di.o_flag = row_off(r_flag + ((m & M_EXCL) ? 1 : 0) + ((m & M_FULL) ? 2 : 0));
                 di.score = (uint32_t)tile_word(W_SCORE1, l, j);
-                di.cls = 0;
                 if (NUMS == 1) {
-                    di.cls = find_class(di.score, nv);
-                    if (di.cls == kNoClass) {
+                    const int cl = find_class(di.score, nv);
+                    di.o_below = (uint32_t)(cl * T);
+                    if (cl == kDict) {
                         const int slot = atomicAdd(&s_meta[1], 1);
                         if (slot < kPend) pend[slot] = di.score;
                     }
@@ -715,30 +767,33 @@ __global__ void __launch_bounds__(128)
             dev[d] = di;
         }
         if (NUMS == 2) {
-            for (int q = tid; q < 32 * 28; q += T) {
-                const int l = q / 28, pr = q - l * 28;
-                int a = 0, rest = pr; // pair number -> (a, b)
-                while (rest >= 7 - a) rest -= 7 - a, a++;
-                const int b = a + 1 + rest;
+            for (int q = tid; q < 32 * kPairs; q += T) {
+                const int l = q / kPairs, pr = q - l * kPairs;
+                const int a = kPairA[pr], b = kPairB[pr];
                 const uint32_t ma = (uint32_t)tile_word(W_META, l, a), mb = (uint32_t)tile_word(W_META, l, b);
-                uint32_t sb = 0u, cl = 0u;
+                uint32_t sb = 0u;
+                int cl = kDict;
                 if (!((ma | mb) & (M_NOFREE | M_PAD))) {
                     const int32_t nd = (int32_t)((ma >> M_NDEV_SHIFT) & 15u);
                     sb = __float_as_uint(container_score(
                         wrap_add(tile_word(W_COUNT, l, a), tile_word(W_COUNT, l, b)),
                         wrap_add(tile_word(W_FREESLOTS, l, a), tile_word(W_FREESLOTS, l, b)), nd - 2));
                     cl = find_class(sb, nv);
-                    if (cl == kNoClass) {
+                    if (cl == kDict) {
                         const int slot = atomicAdd(&s_meta[1], 1);
                         if (slot < kPend) pend[slot] = sb;
                     }
                 }
                 pscore[q] = sb;
-                pcls[q] = (uint8_t)cl;
+                pbelow[q] = (uint16_t)(cl * T);
             }
         }
-        __syncthreads();
-        int npend = min(s_meta[1], kPend);
+        __syncthreads(); // tile fully consumed: dev[] / pair tables are complete
+        if (tid == 0 && it + 1 < n_my) { // the tile buffer is free during the node loop: prefetch
+            mbar_expect_tx(&bar[0], kTileBytes);
+            bulk_g2s(tilebuf, walk + (size_t)(tile - 1) * kTileInt4, kTileBytes, &bar[0]);
+        }
+        const int npend = min(s_meta[1], kPend);
         if (npend > 0) { // uniform: new score values -> insert into the sorted dictionary
             for (int i = 0; i < npend; i++) {
                 const uint32_t x = pend[i];
@@ -766,50 +821,33 @@ __global__ void __launch_bounds__(128)
             // classes again, now that (almost always) every value is known
             if (NUMS == 1) {
                 for (int d = tid; d < 256; d += T)
-                    if (dev[d].score) dev[d].cls = find_class(dev[d].score, nv);
+                    if (dev[d].score) dev[d].o_below = (uint32_t)(find_class(dev[d].score, nv) * T);
             } else {
-                for (int q = tid; q < 32 * 28; q += T)
-                    if (pscore[q]) pcls[q] = (uint8_t)find_class(pscore[q], nv);
+                for (int q = tid; q < 32 * kPairs; q += T)
+                    if (pscore[q]) pbelow[q] = (uint16_t)(find_class(pscore[q], nv) * T);
             }
             __syncthreads();
         }
 
-        // ---- 32 nodes, descending; four at a time for the carry-save fit counter ----------
+        // ---- 32 nodes, descending, four at a time.  Fast path: straight-line word algebra that
+        // only DETECTS whether any pod of my word could improve; the rare exact replay follows.
         for (int lq = 7; lq >= 0; lq--) {
             uint32_t xs[4];
+            uint32_t anyhit = VERIFY ? 0xffffffffu : 0u;
 #pragma unroll
             for (int u = 3; u >= 0; u--) {
                 const int l = lq * 4 + u;
-                const int node = tile * kWarp + l;
                 uint32_t fit[8];
-                uint32_t dcls[8], dsc[8];
 #pragma unroll
-                for (int j = 0; j < 8; j++) {
-                    const int4 o = *reinterpret_cast<const int4 *>(&dev[l * 8 + j]);
-                    const int4 o2 = *(reinterpret_cast<const int4 *>(&dev[l * 8 + j]) + 1);
-                    const uint32_t ty = TAB((uint32_t)o.x), mm = TAB((uint32_t)o.y), pp = TAB((uint32_t)o.z);
-                    const uint32_t cc = TAB((uint32_t)o.w), ok = TAB((uint32_t)o2.x);
-                    fit[j] = ty & (mm | pp) & cc & ok;
-                    dcls[j] = (uint32_t)o2.y;
-                    dsc[j] = (uint32_t)o2.z;
-                }
-                uint32_t anyfit;
+                for (int j = 0; j < 8; j++) fit[j] = fit_word(l * 8 + j);
                 if (NUMS == 1) {
                     uint32_t rem = 0xffffffffu;
 #pragma unroll
                     for (int j = 0; j < 8; j++) { // walk order: the first fitting device is taken
-                        const uint32_t nw = fit[j] & rem;
+                        anyhit |= fit[j] & rem & below[dev[l * 8 + j].o_below + tid];
                         rem &= ~fit[j];
-                        if (VERIFY && active) {
-                            for (uint32_t mth = nw; mth; mth &= mth - 1) {
-                                const int p = tb.orig[w * 32 + __ffs((int)mth) - 1];
-                                vscore[(size_t)p * n_nodes + node] = __uint_as_float(dsc[j]);
-                            }
-                        }
-                        const uint32_t bl = dcls[j] < (uint32_t)kDict ? below[dcls[j] * T + tid] : 0xffffffffu;
-                        if (nw & bl) raise(nw & bl, dsc[j], (uint32_t)node);
                     }
-                    anyfit = ~rem;
+                    xs[u] = ~rem;
                 } else {
                     uint32_t seen = 0u, seen2 = 0u, first[8], second[8];
 #pragma unroll
@@ -819,33 +857,24 @@ __global__ void __launch_bounds__(128)
                         seen2 |= seen & fit[j];
                         seen |= fit[j];
                     }
-                    anyfit = seen2; // the node fits a pod iff two devices fit
 #pragma unroll
-                    for (int a = 0; a < 7; a++) {
-                        if (!__any_sync(0xffffffffu, first[a] != 0u)) continue;
+                    for (int a = 0; a < 7; a++)
 #pragma unroll
-                        for (int b = a + 1; b < 8; b++) {
-                            const uint32_t wab = first[a] & second[b];
-                            const int q = l * 28 + pair_index(a, b);
-                            const uint32_t cl = pcls[q];
-                            if (VERIFY && active) {
-                                for (uint32_t mth = wab; mth; mth &= mth - 1) {
-                                    const int p = tb.orig[w * 32 + __ffs((int)mth) - 1];
-                                    vscore[(size_t)p * n_nodes + node] = __uint_as_float(pscore[q]);
-                                }
-                            }
-                            const uint32_t bl = cl < (uint32_t)kDict ? below[cl * T + tid] : 0xffffffffu;
-                            if (wab & bl) raise(wab & bl, pscore[q], (uint32_t)node);
-                        }
-                    }
+                        for (int b = a + 1; b < 8; b++)
+                            anyhit |= first[a] & second[b] & below[pbelow[l * kPairs + pair_index(a, b)] + tid];
+                    xs[u] = seen2; // the node fits a pod iff two devices fit
                 }
                 if (VERIFY && active) {
-                    for (uint32_t mth = anyfit; mth; mth &= mth - 1) {
+                    const int node = tile * kWarp + l;
+                    for (uint32_t mth = xs[u]; mth; mth &= mth - 1) {
                         const int p = tb.orig[w * 32 + __ffs((int)mth) - 1];
                         atomicOr(&vfit[(size_t)p * vwords + (node >> 5)], 1u << (node & 31));
                     }
                 }
-                xs[u] = anyfit;
+            }
+            if (anyhit) {
+#pragma unroll 1
+                for (int u = 3; u >= 0; u--) slow_node(lq * 4 + u, tile * kWarp + lq * 4 + u);
             }
             // counter += xs[0] + xs[1] + xs[2] + xs[3] (bit-sliced, carry-save)
             uint32_t ca, sa, cb, cf;
@@ -859,7 +888,7 @@ __global__ void __launch_bounds__(128)
                 cf = t2;
             }
         }
-        __syncthreads(); // everyone is done with this tile buffer, dev[] and the pair tables
+        __syncthreads(); // everyone is done with dev[] and the pair tables
     }
 
     if (!active) return;
@@ -874,7 +903,7 @@ __global__ void __launch_bounds__(128)
         const int p = __ldg(&tb.orig[i]);
         // scores of single-request pods are positive: ordered bits = bits | sign bit
         const unsigned long long key = ((unsigned long long)(sb | 0x80000000u) << 32) |
-                                       (unsigned long long)(uint32_t)(row_base + (int)s_row[b * T + tid]);
+                                       (unsigned long long)(uint32_t)(row_base + node_lo + (int)s_row[b * T + tid]);
         atomicMax(&keys[p], key);
         atomicAdd(&counts[p], c);
     }
@@ -1183,7 +1212,13 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
     if (n_types < 1) n_types = 1;
     if (n_types > VGS_MAX_TYPES) n_types = VGS_MAX_TYPES;
     const int rows_s = n_types + (tb.km + 1) + (tb.kp + 1) + (tb.kc + 1) + 4;
-    const bool tabsmem = (size_t)rows_s * T * 4 <= 56 * 1024; // else the tables stay in global / L1
+    static int force_tab = -2;
+    if (force_tab == -2) {
+        const char *e = getenv("VGS_SLICE_TABSMEM");
+        force_tab = e ? atoi(e) : -1;
+    }
+    // tables in shared memory when small (else global / L1)
+    const bool tabsmem = force_tab >= 0 ? force_tab != 0 : (size_t)rows_s * T * 4 <= 24 * 1024;
     const int smem = slice_smem(T, NUMS, tabsmem ? rows_s : 0).total;
     cudaError_t e;
     auto go = [&](auto kernel) -> cudaError_t {
