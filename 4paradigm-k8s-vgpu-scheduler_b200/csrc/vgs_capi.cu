@@ -263,7 +263,7 @@ int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
 
     {
         const size_t wp = align_up((P + 31) / 32, 32);
-        const size_t rows = VGS_MAX_TYPES + 2 * (kSliceMaxDistinct + 1) + (kSliceMaxPct + 1) + 4;
+        const size_t rows = VGS_MAX_TYPES + 5 * (kSliceMaxDistinct + 1) + (kSliceMaxPct + 1);
         c->slice_words = rows * wp + 2 * kSliceMaxDistinct + kSliceMaxPct + P + 64;
         for (int k = 0; k < 2; k++) {
             CUI(cudaMalloc(&c->d_slice[k], c->slice_words * sizeof(uint32_t)));
@@ -444,8 +444,7 @@ static bool build_slice_class(vgs_ctx *c, int k, const DevReq *req, const int32_
     const size_t o_type = o; o += (size_t)VGS_MAX_TYPES * Wp;
     const size_t o_mem = o;  o += (size_t)(km + 1) * Wp;
     const size_t o_pct = o;  o += (size_t)(kp + 1) * Wp;
-    const size_t o_core = o; o += (size_t)(kc + 1) * Wp;
-    const size_t o_flag = o; o += (size_t)4 * Wp;
+    const size_t o_core = o; o += (size_t)4 * (kc + 1) * Wp;
     const size_t o_memv = o; o += km;
     const size_t o_pctv = o; o += kp;
     const size_t o_corev = o; o += kc;
@@ -467,19 +466,17 @@ static bool build_slice_class(vgs_ctx *c, int k, const DevReq *req, const int32_
         }
         if (d.flags & R_USEPCT) h[o_pct + (size_t)(idx_of(pv, d.pct) + 1) * Wp + wd] |= bit;
         else h[o_mem + (size_t)(idx_of(mv, d.memfix) + 1) * Wp + wd] |= bit;
-        h[o_core + (size_t)(idx_of(cv, d.coresreq) + 1) * Wp + wd] |= bit;
-        // flag rows hold the pods that SURVIVE a device with (excl, full) = (f & 1, f >> 1):
-        // Coresreq == 100 loses on excl (score.go:128), == 0 on full (:132), > 100 always (:110)
+        // cores x flags: cumulative over the Coresreq cut, one row per flag combination f
         for (int f = 0; f < 4; f++) {
             const bool lose = d.coresreq > 100 || ((f & 1) && d.coresreq == 100) || ((f & 2) && d.coresreq == 0);
-            if (!lose) h[o_flag + (size_t)f * Wp + wd] |= bit;
+            if (!lose) h[o_core + ((size_t)(idx_of(cv, d.coresreq) + 1) * 4 + f) * Wp + wd] |= bit;
         }
     }
-    auto prefix_or = [&](size_t base, int32_t rows) { // row r |= row r-1
-        for (int32_t r = 1; r <= rows; r++)
-            for (int32_t x = 0; x < W; x++) h[base + (size_t)r * Wp + x] |= h[base + (size_t)(r - 1) * Wp + x];
+    auto prefix_or = [&](size_t base, int32_t rows, int32_t step) { // row r |= row r - step
+        for (int32_t r = step; r < (rows + 1) * step; r++)
+            for (int32_t x = 0; x < W; x++) h[base + (size_t)r * Wp + x] |= h[base + (size_t)(r - step) * Wp + x];
     };
-    prefix_or(o_mem, km), prefix_or(o_pct, kp), prefix_or(o_core, kc);
+    prefix_or(o_mem, km, 1), prefix_or(o_pct, kp, 1), prefix_or(o_core, kc, 4);
     int32_t *hi = reinterpret_cast<int32_t *>(h);
     std::copy(mv.begin(), mv.end(), hi + o_memv);
     std::copy(pv.begin(), pv.end(), hi + o_pctv);
@@ -490,7 +487,7 @@ static bool build_slice_class(vgs_ctx *c, int k, const DevReq *req, const int32_
     const uint32_t *d = c->d_slice[k];
     SliceTab &t = c->tab[k];
     t.base = d + o_type;
-    (void)o_mem, (void)o_pct, (void)o_core, (void)o_flag;
+    (void)o_mem, (void)o_pct, (void)o_core;
     t.memv = reinterpret_cast<const int32_t *>(d + o_memv);
     t.pctv = reinterpret_cast<const int32_t *>(d + o_pctv);
     t.corev = reinterpret_cast<const int32_t *>(d + o_corev);

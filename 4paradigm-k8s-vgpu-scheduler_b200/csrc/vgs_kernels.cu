@@ -584,9 +584,9 @@ __global__ void __launch_bounds__(128)
                     int32_t vwords) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int T = blockDim.x, tid = threadIdx.x;
-    // table rows, global numbering: [type 0..63][mem 0..km][pct 0..kp][core 0..kc][flag 0..3]
-    const int r_mem = VGS_MAX_TYPES, r_pct = r_mem + tb.km + 1, r_core = r_pct + tb.kp + 1, r_flag = r_core + tb.kc + 1;
-    const int rows_g = r_flag + 4;
+    // table rows, global numbering: [type 0..63][mem 0..km][pct 0..kp][cores x flags: 4 * (kc + 1)]
+    const int r_mem = VGS_MAX_TYPES, r_pct = r_mem + tb.km + 1, r_core = r_pct + tb.kp + 1;
+    const int rows_g = r_core + 4 * (tb.kc + 1);
     // the shared copy keeps only the type rows that can occur (ids < n_types)
     const int drop = TABSMEM ? VGS_MAX_TYPES - n_types : 0;
     const SliceSmem L = slice_smem(T, NUMS, TABSMEM ? rows_g - drop : 0);
@@ -655,11 +655,6 @@ __global__ void __launch_bounds__(128)
         }
         return (lo < nv && vals[lo] == sb) ? lo : kDict;
     };
-    auto fit_word = [&](int d) -> uint32_t {
-        const int4 o = *reinterpret_cast<const int4 *>(&dev[d]);
-        const uint32_t ok = TAB(dev[d].o_flag);
-        return TAB((uint32_t)o.x) & (TAB((uint32_t)o.y) | TAB((uint32_t)o.z)) & TAB((uint32_t)o.w) & ok;
-    };
     // pods in `word` get candidate (sb, node); nodes only ever decrease, so equal scores keep
     // the earlier (higher) row.  A pod whose best reaches sb leaves every below[k] with vals[k] <= sb.
     auto raise = [&](uint32_t word, uint32_t sb, int node) {
@@ -675,54 +670,77 @@ __global__ void __launch_bounds__(128)
         const int nv = s_meta[0];
         for (int k = 0; k < nv && vals[k] <= sb; k++) below[k * T + tid] &= ~imp;
     };
-    // exact, ordered handling of one node: the reference's walk for every pod of my word
-    auto slow_node = [&](int l, int node) {
+    // One node, given the fit words of its 8 devices in walk order.  First a branch-free test
+    // whether ANY pod of my word could improve (candidate class above the pod's best); only
+    // then the exact ordered replay.  Returns the word of pods this node fits.
+    auto node_step = [&](const uint32_t (&fit)[8], int l, int node) -> uint32_t {
+        uint32_t anyfit;
         if (NUMS == 1) {
-            uint32_t rem = 0xffffffffu;
-#pragma unroll 1
-            for (int j = 0; j < 8; j++) {
-                const int d = l * 8 + j;
-                const uint32_t f = fit_word(d);
-                const uint32_t nw = f & rem; // pods whose first fitting device is j
-                rem &= ~f;
-                if (VERIFY && active) {
-                    for (uint32_t mth = nw; mth; mth &= mth - 1) {
-                        const int p = tb.orig[w * 32 + __ffs((int)mth) - 1];
-                        vscore[(size_t)p * n_nodes + node] = __uint_as_float(dev[d].score);
-                    }
-                }
-                const uint32_t hit = nw & below[dev[d].o_below + tid];
-                if (hit) raise(hit, dev[d].score, node);
+            uint32_t nw[8], hit = VERIFY ? 0xffffffffu : 0u, rem = 0xffffffffu;
+#pragma unroll
+            for (int j = 0; j < 8; j++) { // walk order: the first fitting device is taken
+                nw[j] = fit[j] & rem;
+                rem &= ~fit[j];
+                hit |= nw[j] & below[dev[l * 8 + j].o_below + tid];
             }
-        } else {
-            uint32_t seen = 0u, seen2 = 0u, first[8], second[8];
+            anyfit = ~rem;
+            if (hit) {
 #pragma unroll
-            for (int j = 0; j < 8; j++) {
-                const uint32_t f = fit_word(l * 8 + j);
-                first[j] = f & ~seen;
-                second[j] = f & seen & ~seen2;
-                seen2 |= seen & f;
-                seen |= f;
-            }
-#pragma unroll
-            for (int a = 0; a < 7; a++) {
-                if (first[a] == 0u) continue;
-#pragma unroll
-                for (int b = a + 1; b < 8; b++) {
-                    const uint32_t wab = first[a] & second[b]; // pods taking exactly devices a and b
-                    if (wab == 0u) continue;
-                    const int q = l * kPairs + pair_index(a, b);
+                for (int j = 0; j < 8; j++) {
+                    const int d = l * 8 + j;
                     if (VERIFY && active) {
-                        for (uint32_t mth = wab; mth; mth &= mth - 1) {
+                        for (uint32_t mth = nw[j]; mth; mth &= mth - 1) {
                             const int p = tb.orig[w * 32 + __ffs((int)mth) - 1];
-                            vscore[(size_t)p * n_nodes + node] = __uint_as_float(pscore[q]);
+                            vscore[(size_t)p * n_nodes + node] = __uint_as_float(dev[d].score);
                         }
                     }
-                    const uint32_t hit = wab & below[pbelow[q] + tid];
-                    if (hit) raise(hit, pscore[q], node);
+                    const uint32_t h = nw[j] & below[dev[d].o_below + tid];
+                    if (h) raise(h, dev[d].score, node);
+                }
+            }
+        } else {
+            uint32_t seen = 0u, seen2 = 0u, first[8], second[8], hit = VERIFY ? 0xffffffffu : 0u;
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                first[j] = fit[j] & ~seen;
+                second[j] = fit[j] & seen & ~seen2;
+                seen2 |= seen & fit[j];
+                seen |= fit[j];
+            }
+            anyfit = seen2; // the node fits a pod iff two devices fit
+#pragma unroll
+            for (int a = 0; a < 7; a++)
+#pragma unroll
+                for (int b = a + 1; b < 8; b++)
+                    hit |= first[a] & second[b] & below[pbelow[l * kPairs + pair_index(a, b)] + tid];
+            if (hit) {
+#pragma unroll
+                for (int a = 0; a < 7; a++) {
+                    if (first[a] == 0u) continue;
+#pragma unroll
+                    for (int b = a + 1; b < 8; b++) {
+                        const uint32_t wab = first[a] & second[b]; // pods taking exactly devices a and b
+                        if (wab == 0u) continue;
+                        const int q = l * kPairs + pair_index(a, b);
+                        if (VERIFY && active) {
+                            for (uint32_t mth = wab; mth; mth &= mth - 1) {
+                                const int p = tb.orig[w * 32 + __ffs((int)mth) - 1];
+                                vscore[(size_t)p * n_nodes + node] = __uint_as_float(pscore[q]);
+                            }
+                        }
+                        const uint32_t h = wab & below[pbelow[q] + tid];
+                        if (h) raise(h, pscore[q], node);
+                    }
                 }
             }
         }
+        if (VERIFY && active) {
+            for (uint32_t mth = anyfit; mth; mth &= mth - 1) {
+                const int p = tb.orig[w * 32 + __ffs((int)mth) - 1];
+                atomicOr(&vfit[(size_t)p * vwords + (node >> 5)], 1u << (node & 31));
+            }
+        }
+        return anyfit;
     };
 
     uint32_t ones = 0u, twos = 0u, cnt[kSliceCountPlanes]; // fit counter: ones, twos, cnt[k] = bit k (k >= 2)
@@ -742,9 +760,10 @@ __global__ void __launch_bounds__(128)
             const uint32_t m = (uint32_t)tile_word(W_META, l, j);
             DevInfo di;
             di.pad = 0;
+            di.o_flag = 0;
             di.o_below = (uint32_t)(kDict * T);
             if (m & (M_NOFREE | M_PAD)) { // Count <= Used (score.go:107) or not a device: never fits
-                di.o_type = di.o_mem = di.o_pct = di.o_core = di.o_flag = row_off(r_mem); // memle row 0: all zero
+                di.o_type = di.o_mem = di.o_pct = di.o_core = row_off(r_mem); // memle row 0: all zero
                 di.score = 0;
             } else {
                 const int32_t fm = tile_word(W_FREEMEM, l, j), fc = tile_word(W_FREECORES, l, j);
@@ -752,8 +771,9 @@ __global__ void __launch_bounds__(128)
                 di.o_type = row_off((int)(m & M_TYPE_MASK));
                 di.o_mem = row_off(r_mem + count_prefix(tb.memv, tb.km, [&](int32_t v) { return v <= fm; }));
                 di.o_pct = row_off(r_pct + count_prefix(tb.pctv, tb.kp, [&](int32_t v) { return pct_mem(tm, v) <= fm; }));
-                di.o_core = row_off(r_core + count_prefix(tb.corev, tb.kc, [&](int32_t v) { return v <= fc; }));
-                di.o_flag = row_off(r_flag + ((m & M_EXCL) ? 1 : 0) + ((m & M_FULL) ? 2 : 0));
+                // cores x flags table: row = cut * 4 + (excl | full << 1)
+                di.o_core = row_off(r_core + 4 * count_prefix(tb.corev, tb.kc, [&](int32_t v) { return v <= fc; }) +
+                                    ((m & M_EXCL) ? 1 : 0) + ((m & M_FULL) ? 2 : 0));
                 di.score = (uint32_t)tile_word(W_SCORE1, l, j);
                 if (NUMS == 1) {
                     const int cl = find_class(di.score, nv);
@@ -829,53 +849,29 @@ __global__ void __launch_bounds__(128)
             __syncthreads();
         }
 
-        // ---- 32 nodes, descending, four at a time.  Fast path: straight-line word algebra that
-        // only DETECTS whether any pod of my word could improve; the rare exact replay follows.
+        // ---- 32 nodes, descending.  The fit words of the NEXT node are loaded (table rows,
+        // independent of any update) before the current node is handled, so the loads of one
+        // node overlap the word algebra of the other.
+        auto load_fit = [&](uint32_t (&fit)[8], int l) {
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                const int4 o = *reinterpret_cast<const int4 *>(&dev[l * 8 + j]);
+                fit[j] = TAB((uint32_t)o.x) & (TAB((uint32_t)o.y) | TAB((uint32_t)o.z)) & TAB((uint32_t)o.w);
+            }
+        };
+        uint32_t fa[8], fb[8];
+        load_fit(fa, kWarp - 1);
         for (int lq = 7; lq >= 0; lq--) {
             uint32_t xs[4];
-            uint32_t anyhit = VERIFY ? 0xffffffffu : 0u;
-#pragma unroll
-            for (int u = 3; u >= 0; u--) {
-                const int l = lq * 4 + u;
-                uint32_t fit[8];
-#pragma unroll
-                for (int j = 0; j < 8; j++) fit[j] = fit_word(l * 8 + j);
-                if (NUMS == 1) {
-                    uint32_t rem = 0xffffffffu;
-#pragma unroll
-                    for (int j = 0; j < 8; j++) { // walk order: the first fitting device is taken
-                        anyhit |= fit[j] & rem & below[dev[l * 8 + j].o_below + tid];
-                        rem &= ~fit[j];
-                    }
-                    xs[u] = ~rem;
-                } else {
-                    uint32_t seen = 0u, seen2 = 0u, first[8], second[8];
-#pragma unroll
-                    for (int j = 0; j < 8; j++) {
-                        first[j] = fit[j] & ~seen;
-                        second[j] = fit[j] & seen & ~seen2;
-                        seen2 |= seen & fit[j];
-                        seen |= fit[j];
-                    }
-#pragma unroll
-                    for (int a = 0; a < 7; a++)
-#pragma unroll
-                        for (int b = a + 1; b < 8; b++)
-                            anyhit |= first[a] & second[b] & below[pbelow[l * kPairs + pair_index(a, b)] + tid];
-                    xs[u] = seen2; // the node fits a pod iff two devices fit
-                }
-                if (VERIFY && active) {
-                    const int node = tile * kWarp + l;
-                    for (uint32_t mth = xs[u]; mth; mth &= mth - 1) {
-                        const int p = tb.orig[w * 32 + __ffs((int)mth) - 1];
-                        atomicOr(&vfit[(size_t)p * vwords + (node >> 5)], 1u << (node & 31));
-                    }
-                }
-            }
-            if (anyhit) {
-#pragma unroll 1
-                for (int u = 3; u >= 0; u--) slow_node(lq * 4 + u, tile * kWarp + lq * 4 + u);
-            }
+            const int l0 = lq * 4;
+            load_fit(fb, l0 + 2);
+            xs[3] = node_step(fa, l0 + 3, tile * kWarp + l0 + 3);
+            load_fit(fa, l0 + 1);
+            xs[2] = node_step(fb, l0 + 2, tile * kWarp + l0 + 2);
+            load_fit(fb, l0);
+            xs[1] = node_step(fa, l0 + 1, tile * kWarp + l0 + 1);
+            if (lq > 0) load_fit(fa, l0 - 1);
+            xs[0] = node_step(fb, l0, tile * kWarp + l0);
             // counter += xs[0] + xs[1] + xs[2] + xs[3] (bit-sliced, carry-save)
             uint32_t ca, sa, cb, cf;
             csa(ca, sa, ones, xs[0], xs[1]);
@@ -1211,14 +1207,14 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
     const int gy = (tb.W + T - 1) / T;
     if (n_types < 1) n_types = 1;
     if (n_types > VGS_MAX_TYPES) n_types = VGS_MAX_TYPES;
-    const int rows_s = n_types + (tb.km + 1) + (tb.kp + 1) + (tb.kc + 1) + 4;
+    const int rows_s = n_types + (tb.km + 1) + (tb.kp + 1) + 4 * (tb.kc + 1);
     static int force_tab = -2;
     if (force_tab == -2) {
         const char *e = getenv("VGS_SLICE_TABSMEM");
         force_tab = e ? atoi(e) : -1;
     }
     // tables in shared memory when small (else global / L1)
-    const bool tabsmem = force_tab >= 0 ? force_tab != 0 : (size_t)rows_s * T * 4 <= 24 * 1024;
+    const bool tabsmem = force_tab >= 0 ? force_tab != 0 : (size_t)rows_s * T * 4 <= 8 * 1024;
     const int smem = slice_smem(T, NUMS, tabsmem ? rows_s : 0).total;
     cudaError_t e;
     auto go = [&](auto kernel) -> cudaError_t {

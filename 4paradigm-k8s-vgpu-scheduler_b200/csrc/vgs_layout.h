@@ -80,10 +80,10 @@ struct SliceTab {
     //   [0, 64)            type rows: pods whose type mask has bit t
     //   [64, 64+km+1)      fixed-MB pods by Memreq (cumulative; row 0 is all zero)
     //   then kp+1 rows     percentage pods by MemPercentagereq (cumulative)
-    //   then kc+1 rows     all pods by Coresreq (cumulative)
-    //   then 4 rows        pods NOT ruled out by the device flags: index = excl | full << 1
-    //                      (excl: Coresreq == 100 pods lose, full: Coresreq == 0 pods lose,
-    //                       Coresreq > 100 pods always lose)
+    //   then 4*(kc+1) rows all pods by Coresreq (cumulative) AND surviving the device flags:
+    //                      row = cut * 4 + (excl | full << 1); excl: Coresreq == 100 pods lose
+    //                      (score.go:128), full: Coresreq == 0 pods lose (:132), Coresreq > 100
+    //                      pods always lose (:110)
     const uint32_t *base;
     const int32_t *memv, *pctv, *corev; // sorted distinct values
     const int32_t *orig;                // class position -> pod index of the batch
