@@ -576,6 +576,20 @@ static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, i
             nG++;
         }
     }
+    // The pod-sliced kernels cost the same per warp whether 32 or 1 of its pod words are in
+    // use, so a small remainder beyond a multiple of 1024 pods goes to the per-pair kernel.
+    auto trim_tail = [&](DevReq *h, int32_t *ho, int32_t &n) {
+        if (n < c->slice_min || n < 1024) return;
+        const int32_t rem = n % 1024;
+        if (rem == 0 || rem >= 512) return;
+        for (int32_t i = n - rem; i < n; i++) {
+            hC[nC] = h[i];
+            hoC[nC++] = ho[i];
+        }
+        n -= rem;
+    };
+    trim_tail(hA, hoA, nA);
+    trim_tail(hB, hoB, nB);
     c->n_pods = n_pods;
     c->n_reqs = n_reqs;
     c->nA = nA;

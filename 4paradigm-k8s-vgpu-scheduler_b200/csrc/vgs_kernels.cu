@@ -670,77 +670,49 @@ __global__ void __launch_bounds__(128)
         const int nv = s_meta[0];
         for (int k = 0; k < nv && vals[k] <= sb; k++) below[k * T + tid] &= ~imp;
     };
-    // One node, given the fit words of its 8 devices in walk order.  First a branch-free test
-    // whether ANY pod of my word could improve (candidate class above the pod's best); only
-    // then the exact ordered replay.  Returns the word of pods this node fits.
-    auto node_step = [&](const uint32_t (&fit)[8], int l, int node) -> uint32_t {
-        uint32_t anyfit;
-        if (NUMS == 1) {
-            uint32_t nw[8], hit = VERIFY ? 0xffffffffu : 0u, rem = 0xffffffffu;
+    // Exact ordered replay of one node whose detection word was non-zero.  NUMS == 1: nw[j] =
+    // pods whose first fitting device is j.  NUMS == 2: first/second fitting device words.
+    auto replay1 = [&](const uint32_t (&nw)[8], int l, int node) {
 #pragma unroll
-            for (int j = 0; j < 8; j++) { // walk order: the first fitting device is taken
-                nw[j] = fit[j] & rem;
-                rem &= ~fit[j];
-                hit |= nw[j] & below[dev[l * 8 + j].o_below + tid];
-            }
-            anyfit = ~rem;
-            if (hit) {
-#pragma unroll
-                for (int j = 0; j < 8; j++) {
-                    const int d = l * 8 + j;
-                    if (VERIFY && active) {
-                        for (uint32_t mth = nw[j]; mth; mth &= mth - 1) {
-                            const int p = tb.orig[w * 32 + __ffs((int)mth) - 1];
-                            vscore[(size_t)p * n_nodes + node] = __uint_as_float(dev[d].score);
-                        }
-                    }
-                    const uint32_t h = nw[j] & below[dev[d].o_below + tid];
-                    if (h) raise(h, dev[d].score, node);
+        for (int j = 0; j < 8; j++) {
+            const int d = l * 8 + j;
+            if (VERIFY && active) {
+                for (uint32_t mth = nw[j]; mth; mth &= mth - 1) {
+                    const int p = tb.orig[w * 32 + __ffs((int)mth) - 1];
+                    vscore[(size_t)p * n_nodes + node] = __uint_as_float(dev[d].score);
                 }
             }
-        } else {
-            uint32_t seen = 0u, seen2 = 0u, first[8], second[8], hit = VERIFY ? 0xffffffffu : 0u;
+            const uint32_t h = nw[j] & below[dev[d].o_below + tid];
+            if (h) raise(h, dev[d].score, node);
+        }
+    };
+    auto replay2 = [&](const uint32_t (&first)[8], const uint32_t (&second)[8], int l, int node) {
 #pragma unroll
-            for (int j = 0; j < 8; j++) {
-                first[j] = fit[j] & ~seen;
-                second[j] = fit[j] & seen & ~seen2;
-                seen2 |= seen & fit[j];
-                seen |= fit[j];
-            }
-            anyfit = seen2; // the node fits a pod iff two devices fit
+        for (int a = 0; a < 7; a++) {
+            if (first[a] == 0u) continue;
 #pragma unroll
-            for (int a = 0; a < 7; a++)
-#pragma unroll
-                for (int b = a + 1; b < 8; b++)
-                    hit |= first[a] & second[b] & below[pbelow[l * kPairs + pair_index(a, b)] + tid];
-            if (hit) {
-#pragma unroll
-                for (int a = 0; a < 7; a++) {
-                    if (first[a] == 0u) continue;
-#pragma unroll
-                    for (int b = a + 1; b < 8; b++) {
-                        const uint32_t wab = first[a] & second[b]; // pods taking exactly devices a and b
-                        if (wab == 0u) continue;
-                        const int q = l * kPairs + pair_index(a, b);
-                        if (VERIFY && active) {
-                            for (uint32_t mth = wab; mth; mth &= mth - 1) {
-                                const int p = tb.orig[w * 32 + __ffs((int)mth) - 1];
-                                vscore[(size_t)p * n_nodes + node] = __uint_as_float(pscore[q]);
-                            }
-                        }
-                        const uint32_t h = wab & below[pbelow[q] + tid];
-                        if (h) raise(h, pscore[q], node);
+            for (int b = a + 1; b < 8; b++) {
+                const uint32_t wab = first[a] & second[b]; // pods taking exactly devices a and b
+                if (wab == 0u) continue;
+                const int q = l * kPairs + pair_index(a, b);
+                if (VERIFY && active) {
+                    for (uint32_t mth = wab; mth; mth &= mth - 1) {
+                        const int p = tb.orig[w * 32 + __ffs((int)mth) - 1];
+                        vscore[(size_t)p * n_nodes + node] = __uint_as_float(pscore[q]);
                     }
                 }
+                const uint32_t h = wab & below[pbelow[q] + tid];
+                if (h) raise(h, pscore[q], node);
             }
         }
+    };
+    auto mark_fit = [&](uint32_t anyfit, int node) { // verify mode: the pod x node fit bitmap
         if (VERIFY && active) {
             for (uint32_t mth = anyfit; mth; mth &= mth - 1) {
                 const int p = tb.orig[w * 32 + __ffs((int)mth) - 1];
                 atomicOr(&vfit[(size_t)p * vwords + (node >> 5)], 1u << (node & 31));
             }
         }
-        return anyfit;
     };
 
     uint32_t ones = 0u, twos = 0u, cnt[kSliceCountPlanes]; // fit counter: ones, twos, cnt[k] = bit k (k >= 2)
@@ -849,29 +821,66 @@ __global__ void __launch_bounds__(128)
             __syncthreads();
         }
 
-        // ---- 32 nodes, descending.  The fit words of the NEXT node are loaded (table rows,
-        // independent of any update) before the current node is handled, so the loads of one
-        // node overlap the word algebra of the other.
-        auto load_fit = [&](uint32_t (&fit)[8], int l) {
-#pragma unroll
-            for (int j = 0; j < 8; j++) {
-                const int4 o = *reinterpret_cast<const int4 *>(&dev[l * 8 + j]);
-                fit[j] = TAB((uint32_t)o.x) & (TAB((uint32_t)o.y) | TAB((uint32_t)o.z)) & TAB((uint32_t)o.w);
-            }
-        };
-        uint32_t fa[8], fb[8];
-        load_fit(fa, kWarp - 1);
+        // ---- 32 nodes, descending, in groups of four.  Phase 1 is branch-free word algebra for
+        // all four nodes (independent chains for the scheduler to interleave): fit words from the
+        // table rows, the walk as masks, and a detection word "could any pod of mine improve
+        // here?" against below[] as it stands (stale = larger = safe).  Phase 2 replays, in
+        // order and against the live below[], only the nodes whose detection word is non-zero.
         for (int lq = 7; lq >= 0; lq--) {
-            uint32_t xs[4];
-            const int l0 = lq * 4;
-            load_fit(fb, l0 + 2);
-            xs[3] = node_step(fa, l0 + 3, tile * kWarp + l0 + 3);
-            load_fit(fa, l0 + 1);
-            xs[2] = node_step(fb, l0 + 2, tile * kWarp + l0 + 2);
-            load_fit(fb, l0);
-            xs[1] = node_step(fa, l0 + 1, tile * kWarp + l0 + 1);
-            if (lq > 0) load_fit(fa, l0 - 1);
-            xs[0] = node_step(fb, l0, tile * kWarp + l0);
+            uint32_t xs[4], hit[4];
+            if (NUMS == 1) {
+                uint32_t nw[4][8];
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const int l = lq * 4 + u;
+                    uint32_t rem = 0xffffffffu, h = VERIFY ? 0xffffffffu : 0u;
+#pragma unroll
+                    for (int j = 0; j < 8; j++) { // walk order: the first fitting device is taken
+                        const int4 o = *reinterpret_cast<const int4 *>(&dev[l * 8 + j]);
+                        const uint32_t f = TAB((uint32_t)o.x) & (TAB((uint32_t)o.y) | TAB((uint32_t)o.z)) & TAB((uint32_t)o.w);
+                        nw[u][j] = f & rem;
+                        rem &= ~f;
+                        h |= nw[u][j] & below[dev[l * 8 + j].o_below + tid];
+                    }
+                    xs[u] = ~rem;
+                    hit[u] = h;
+                }
+#pragma unroll
+                for (int u = 3; u >= 0; u--) {
+                    const int l = lq * 4 + u;
+                    if (hit[u]) replay1(nw[u], l, tile * kWarp + l);
+                    mark_fit(xs[u], tile * kWarp + l);
+                }
+            } else {
+                uint32_t first[4][8], second[4][8];
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const int l = lq * 4 + u;
+                    uint32_t seen = 0u, seen2 = 0u, h = VERIFY ? 0xffffffffu : 0u;
+#pragma unroll
+                    for (int j = 0; j < 8; j++) {
+                        const int4 o = *reinterpret_cast<const int4 *>(&dev[l * 8 + j]);
+                        const uint32_t f = TAB((uint32_t)o.x) & (TAB((uint32_t)o.y) | TAB((uint32_t)o.z)) & TAB((uint32_t)o.w);
+                        first[u][j] = f & ~seen;
+                        second[u][j] = f & seen & ~seen2;
+                        seen2 |= seen & f;
+                        seen |= f;
+                    }
+#pragma unroll
+                    for (int a = 0; a < 7; a++)
+#pragma unroll
+                        for (int b = a + 1; b < 8; b++)
+                            h |= first[u][a] & second[u][b] & below[pbelow[l * kPairs + pair_index(a, b)] + tid];
+                    xs[u] = seen2; // the node fits a pod iff two devices fit
+                    hit[u] = h;
+                }
+#pragma unroll
+                for (int u = 3; u >= 0; u--) {
+                    const int l = lq * 4 + u;
+                    if (hit[u]) replay2(first[u], second[u], l, tile * kWarp + l);
+                    mark_fit(xs[u], tile * kWarp + l);
+                }
+            }
             // counter += xs[0] + xs[1] + xs[2] + xs[3] (bit-sliced, carry-save)
             uint32_t ca, sa, cb, cf;
             csa(ca, sa, ones, xs[0], xs[1]);
