@@ -320,11 +320,11 @@ def main():
         "e2e": e2e,
         "gpu_launches": int(launches),
         "clocks": clocks,
-        "roofline": {"bound": "hbm", "kernel": "k1_score_single (both launches of one step)",
+        "roofline": {"bound": "hbm", "kernel": "K1 score kernels of one step (k1_score_sliced<1>, <2>, k1_score_single tails)",
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes": int(abytes),
                      "kernel_ms": k1_ms,
-                     "note": "batch regime is integer-issue bound (SURVEY F6): see alu below and DESIGN.md"},
+                     "note": "batch regime is instruction-issue bound, not HBM bound (SURVEY F6, DESIGN.md 4)"},
         "device_evals_per_s": P * n_total * D / (ms_per_step * 1e-3),
     }
     if check:
