@@ -6,5 +6,5 @@ in for the Go cgo shim on hosts without Go.  The directory name is not a legal
 Python identifier; import it through ``vgpu_b200`` (repo root, ``vgpu_b200.py``).
 """
 from .model import (ANNO_NOUSE, ANNO_NUMA, ANNO_USE, MEMPCT_UNSET, BatchResult, PodBatch, Snapshot)  # noqa: F401
-from . import capi, sharding, workload  # noqa: F401
+from . import capi, hostlib, sharding, workload  # noqa: F401
 from .capi import Context, VgsError, load_library  # noqa: F401

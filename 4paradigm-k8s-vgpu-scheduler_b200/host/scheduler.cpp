@@ -1,0 +1,384 @@
+// scheduler.cpp -- see scheduler.hpp.  Host logic of the Filter path, mirroring the Go code
+// it cites; the only call into the GPU library is calcScoreGPU.
+#include "scheduler.hpp"
+
+#include <algorithm>
+#include <cstring>
+#include <ctime>
+
+#include "../../include/vgpuscore.h"
+
+namespace vgpu {
+
+// ---- pkg/util/util.go:110-126 ------------------------------------------------------------
+std::string EncodeContainerDevices(const ContainerDevices &cd) {
+    std::string tmp;
+    for (const ContainerDevice &val : cd)
+        tmp += val.UUID + "," + val.Type + "," + std::to_string(val.Usedmem) + "," + std::to_string(val.Usedcores) + ":";
+    return tmp;
+}
+std::string EncodePodDevices(const PodDevices &pd) {
+    std::string out;
+    for (size_t i = 0; i < pd.size(); i++) {
+        if (i) out += ";"; // strings.Join(ss, ";")
+        out += EncodeContainerDevices(pd[i]);
+    }
+    return out;
+}
+
+// ---- pkg/device/nvidia/device.go:114-175 ---------------------------------------------------
+static bool lookup(const Container &ctr, const std::string &name, int64_t *v) {
+    auto it = ctr.Limits.find(name); // limits take precedence (:119-122)
+    if (it == ctr.Limits.end()) {
+        it = ctr.Requests.find(name);
+        if (it == ctr.Requests.end()) return false;
+    }
+    *v = it->second;
+    return true;
+}
+ContainerDeviceRequest GenerateResourceRequests(const Container &ctr, const Config &cfg) {
+    int64_t n;
+    if (!lookup(ctr, cfg.ResourceName, &n)) return ContainerDeviceRequest{};
+    int64_t v;
+    int memnum = 0;
+    if (lookup(ctr, cfg.ResourceMem, &v)) memnum = (int)v;
+    int32_t mempnum = 101; // "unset" (:136)
+    if (lookup(ctr, cfg.ResourceMemPercentage, &v)) mempnum = (int32_t)v;
+    if (mempnum == 101 && memnum == 0) { // :147-153
+        if (cfg.DefaultMem != 0) memnum = cfg.DefaultMem;
+        else mempnum = 100;
+    }
+    int32_t corenum = cfg.DefaultCores;
+    if (lookup(ctr, cfg.ResourceCores, &v)) corenum = (int32_t)v;
+    ContainerDeviceRequest r;
+    r.Nums = (int32_t)n;
+    r.Type = "NVIDIA";
+    r.Memreq = (int32_t)memnum;
+    r.MemPercentagereq = mempnum;
+    r.Coresreq = corenum;
+    return r;
+}
+
+// ---- pkg/k8sutil/pod.go:26-40 (vendors: NVIDIA) --------------------------------------------
+std::vector<std::vector<ContainerDeviceRequest>> Resourcereqs(const Pod &pod, const Config &cfg) {
+    std::vector<std::vector<ContainerDeviceRequest>> counts(pod.Containers.size());
+    for (size_t i = 0; i < pod.Containers.size(); i++) {
+        ContainerDeviceRequest request = GenerateResourceRequests(pod.Containers[i], cfg);
+        if (request.Nums > 0) counts[i].push_back(request); // :33
+    }
+    return counts;
+}
+
+// ---- registries -----------------------------------------------------------------------------
+Scheduler::Scheduler(int device, int max_nodes, bool incremental, const Config &cfg)
+    : cfg_(cfg), max_nodes_(max_nodes), incremental_(incremental) {
+    vgs_config c;
+    memset(&c, 0, sizeof c);
+    c.device = device;
+    c.max_nodes = max_nodes;
+    c.max_devices = VGS_MAX_DEVICES;
+    c.max_pods = 1; // Filter scores one pod per call
+    c.max_reqs = VGS_MAX_REQS_PER_POD;
+    c.max_picks = VGS_MAX_REQS_PER_POD * VGS_MAX_DEVICES;
+    if (vgs_init(&c, &ctx_) != VGS_OK) ctx_ = nullptr; // Filter reports it; there is no CPU fallback
+}
+Scheduler::~Scheduler() { vgs_destroy(ctx_); }
+
+void Scheduler::addNode(const std::string &nodeID, const NodeInfo &info) {
+    if (info.Devices.empty()) return; // nodes.go:60-62
+    nodes_[nodeID] = info;
+    nodes_[nodeID].ID = nodeID;
+    node_epoch_++;
+}
+
+void Scheduler::queueDelta(const std::string &nodeID, const PodDevices &devs, int sign) {
+    if (!incremental_) return;
+    auto row = resident_row_.find(nodeID);
+    auto node = nodes_.find(nodeID);
+    if (row == resident_row_.end() || node == nodes_.end()) return; // next Filter uploads in full
+    for (const ContainerDevices &cd : devs)
+        for (const ContainerDevice &u : cd)
+            for (size_t s = 0; s < node->second.Devices.size(); s++)
+                if (node->second.Devices[s].ID == u.UUID) // same match as scheduler.go:287-293
+                    pending_.push_back({row->second, (int32_t)s, sign, sign * u.Usedmem, sign * u.Usedcores});
+}
+
+void Scheduler::addPod(const Pod &pod, const std::string &nodeID, const PodDevices &devices) {
+    if (pods_.count(pod.UID)) return; // pods.go:49-58: only unknown pods are recorded
+    pods_[pod.UID] = podInfo{pod.Namespace, pod.Name, pod.UID, nodeID, devices};
+    queueDelta(nodeID, devices, +1);
+}
+void Scheduler::delPod(const Pod &pod) {
+    auto it = pods_.find(pod.UID);
+    if (it == pods_.end()) return;
+    queueDelta(it->second.NodeID, it->second.Devices, -1);
+    pods_.erase(it);
+}
+
+// ---- scheduler.go:249-310 ---------------------------------------------------------------------
+void Scheduler::getNodesUsage(const std::vector<std::string> &nodes, std::map<std::string, NodeUsage *> *cache,
+                              std::map<std::string, std::string> *failedNodes) {
+    overviewstatus_.clear();
+    for (const auto &kv : nodes_) { // :259-278 one fresh DeviceUsage per registered device
+        NodeUsage nu;
+        for (const DeviceInfo &d : kv.second.Devices) {
+            auto u = std::make_shared<DeviceUsage>();
+            u->Id = d.ID, u->Index = d.Index, u->Count = d.Count, u->Totalmem = d.Devmem;
+            u->Totalcore = d.Devcore, u->Type = d.Type, u->Numa = d.Numa, u->Health = d.Health;
+            nu.Devices.push_back(u);
+        }
+        overviewstatus_[kv.first] = nu;
+    }
+    for (const auto &kv : pods_) { // :280-297 fold the scheduled pods' usage in, matching by UUID
+        auto node = overviewstatus_.find(kv.second.NodeID);
+        if (node == overviewstatus_.end()) continue;
+        for (const ContainerDevices &ds : kv.second.Devices)
+            for (const ContainerDevice &udevice : ds)
+                for (auto &d : node->second.Devices)
+                    if (d->Id == udevice.UUID) {
+                        d->Used++;
+                        d->Usedmem += udevice.Usedmem;
+                        d->Usedcores += udevice.Usedcores;
+                    }
+    }
+    for (const std::string &nodeID : nodes) { // :299-307
+        auto it = overviewstatus_.find(nodeID);
+        if (it == overviewstatus_.end()) {
+            (*failedNodes)[nodeID] = "node unregisterd";
+            continue;
+        }
+        (*cache)[nodeID] = &it->second;
+    }
+}
+
+bool Scheduler::uploadSnapshot(const std::vector<std::string> &order, const std::map<std::string, NodeUsage *> &nodes,
+                               std::string *err) {
+    size_t dmax = 1;
+    for (const std::string &id : order) dmax = std::max(dmax, nodes.at(id)->Devices.size());
+    if (dmax > VGS_MAX_DEVICES) {
+        *err = vgs_strerror(VGS_EDMAX);
+        return false;
+    }
+    const size_t n = order.size();
+    std::vector<int32_t> planes[VGS_NUM_PLANES];
+    for (auto &p : planes) p.assign(std::max<size_t>(n * dmax, 1), 0);
+    std::vector<int32_t> ndev(std::max<size_t>(n, 1), 0);
+    resident_row_.clear();
+    for (size_t row = 0; row < n; row++) {
+        const DeviceUsageList &devs = nodes.at(order[row])->Devices;
+        ndev[row] = (int32_t)devs.size();
+        resident_row_[order[row]] = (int32_t)row;
+        for (size_t s = 0; s < devs.size(); s++) { // registration order == slot
+            const DeviceUsage &d = *devs[s];
+            const size_t i = row * dmax + s;
+            planes[VGS_PLANE_USED][i] = d.Used, planes[VGS_PLANE_COUNT][i] = d.Count;
+            planes[VGS_PLANE_USEDMEM][i] = d.Usedmem, planes[VGS_PLANE_TOTALMEM][i] = d.Totalmem;
+            planes[VGS_PLANE_USEDCORES][i] = d.Usedcores, planes[VGS_PLANE_TOTALCORE][i] = d.Totalcore;
+            planes[VGS_PLANE_NUMA][i] = d.Numa;
+            auto t = type_id_.find(d.Type);
+            if (t == type_id_.end()) {
+                if (types_.size() >= VGS_MAX_TYPES) {
+                    *err = "more than VGS_MAX_TYPES distinct device types";
+                    return false;
+                }
+                t = type_id_.emplace(d.Type, (int32_t)types_.size()).first;
+                types_.push_back(d.Type);
+            }
+            planes[VGS_PLANE_TYPEID][i] = t->second;
+        }
+    }
+    const int32_t *ptrs[VGS_NUM_PLANES];
+    for (int f = 0; f < VGS_NUM_PLANES; f++) ptrs[f] = planes[f].data();
+    int rc = vgs_snapshot_upload(ctx_, (int32_t)n, (int32_t)dmax, ptrs, ndev.data(), nullptr);
+    if (rc != VGS_OK) {
+        *err = std::string(vgs_strerror(rc)) + ": " + vgs_last_error(ctx_);
+        return false;
+    }
+    resident_order_ = order;
+    resident_epoch_ = node_epoch_;
+    pending_.clear();
+    return true;
+}
+
+// ---- calcScore (score.go:183-214) + pick (scheduler.go:386-387), on the GPU -----------------------
+bool Scheduler::calcScoreGPU(const std::vector<std::string> &order, const std::map<std::string, NodeUsage *> &nodes,
+                             const std::vector<std::vector<ContainerDeviceRequest>> &nums,
+                             const std::map<std::string, std::string> &annos, NodeScore *winner, bool *found,
+                             std::string *err) {
+    *found = false;
+    if (!ctx_) {
+        *err = "libvgpuscore: no usable GPU (vgs_init failed); there is no CPU fallback";
+        return false;
+    }
+    if ((int)order.size() > max_nodes_) {
+        *err = vgs_strerror(VGS_ETOOBIG);
+        return false;
+    }
+    // snapshot: resident + deltas when nothing but pod usage changed, else a full upload
+    if (incremental_ && resident_epoch_ == node_epoch_ && resident_order_ == order) {
+        if (!pending_.empty()) {
+            std::vector<vgs_delta> d(pending_.size());
+            for (size_t i = 0; i < pending_.size(); i++)
+                d[i] = vgs_delta{pending_[i].row, pending_[i].slot, pending_[i].used, pending_[i].mem, pending_[i].cores};
+            int rc = vgs_snapshot_delta(ctx_, (int32_t)d.size(), d.data());
+            if (rc != VGS_OK) {
+                *err = std::string(vgs_strerror(rc)) + ": " + vgs_last_error(ctx_);
+                return false;
+            }
+            pending_.clear();
+        }
+    } else if (!uploadSnapshot(order, nodes, err)) {
+        return false;
+    }
+    // requests: the string policy (checkType, score.go:71-84) evaluated once per distinct type
+    auto anno = [&](const char *k) -> const char * {
+        auto it = annos.find(k);
+        return it == annos.end() ? nullptr : it->second.c_str();
+    };
+    std::vector<const char *> type_c;
+    for (const std::string &t : types_) type_c.push_back(t.c_str());
+    std::vector<vgs_req> reqs;
+    int total = 0;
+    for (size_t ctr = 0; ctr < nums.size(); ctr++)
+        for (const ContainerDeviceRequest &k : nums[ctr]) {
+            vgs_req r;
+            memset(&r, 0, sizeof r);
+            r.ctr = (int32_t)ctr, r.nums = k.Nums, r.memreq = k.Memreq, r.mempct = k.MemPercentagereq;
+            r.coresreq = k.Coresreq;
+            r.typemask = vgs_host_typemask(k.Type.c_str(), anno("nvidia.com/use-gputype"),
+                                           anno("nvidia.com/nouse-gputype"), type_c.data(), (int32_t)type_c.size());
+            if (k.Type == "NVIDIA" && vgs_host_numa_bind(anno("nvidia.com/numa-bind"))) r.flags |= VGS_REQ_NUMA_BIND;
+            reqs.push_back(r);
+            total += k.Nums;
+        }
+    vgs_pod pod{0, (int32_t)reqs.size()};
+    vgs_result res;
+    std::vector<vgs_pick> picks(std::max(total, 1));
+    int rc = vgs_score_batch(ctx_, 1, &pod, (int32_t)reqs.size(), reqs.data(), &res, picks.data());
+    if (rc != VGS_OK) {
+        *err = std::string(vgs_strerror(rc)) + ": " + vgs_last_error(ctx_);
+        return false;
+    }
+    if (res.best_row < 0) return true; // len(*nodeScores) == 0
+    *found = true;
+    winner->nodeID = order[res.best_row];
+    winner->score = res.score;
+    winner->devices.clear();
+    const DeviceUsageList &devs = nodes.at(winner->nodeID)->Devices;
+    size_t i = 0;
+    for (size_t ctr = 0; ctr < nums.size(); ctr++) { // util.PodDevices: one list per container (score.go:196,201)
+        ContainerDevices cd;
+        for (const ContainerDeviceRequest &k : nums[ctr])
+            for (int j = 0; j < k.Nums; j++, i++) {
+                ContainerDevice c;
+                c.UUID = devs[picks[i].slot]->Id, c.Type = k.Type;
+                c.Usedmem = picks[i].usedmem, c.Usedcores = picks[i].usedcores;
+                cd.push_back(c);
+            }
+        winner->devices.push_back(cd);
+    }
+    return true;
+}
+
+// ---- scheduler.go:354-402 ---------------------------------------------------------------------
+bool Scheduler::Filter(const ExtenderArgs &args, ExtenderFilterResult *res, std::string *err) {
+    *res = ExtenderFilterResult();
+    auto nums = Resourcereqs(args.pod, cfg_);
+    int total = 0;
+    for (const auto &n : nums)
+        for (const auto &k : n) total += k.Nums;
+    if (total == 0) { // :357-370 nothing of ours requested: every node passes
+        res->NodeNames = args.NodeNames;
+        return true;
+    }
+    delPod(args.pod); // :372
+    std::map<std::string, NodeUsage *> nodeUsage;
+    getNodesUsage(args.NodeNames, &nodeUsage, &res->FailedNodes);
+    std::vector<std::string> order; // rows = args.NodeNames order, registered nodes only
+    for (const std::string &id : args.NodeNames)
+        if (nodeUsage.count(id) && std::find(order.begin(), order.end(), id) == order.end()) order.push_back(id);
+    NodeScore m;
+    bool found = false;
+    if (!calcScoreGPU(order, nodeUsage, nums, args.pod.Annotations, &m, &found, err)) return false; // :378-380
+    if (!found) return true; // :381-385 ExtenderFilterResult{FailedNodes}
+    std::map<std::string, std::string> &a = res->PatchedAnnotations; // :388-393
+    a[AssignedNodeAnnotations] = m.nodeID;
+    a[AssignedTimeAnnotations] = std::to_string((long long)time(nullptr));
+    a[AssignedIDsAnnotations] = EncodePodDevices(m.devices);
+    a[AssignedIDsToAllocateAnnotations] = a[AssignedIDsAnnotations];
+    addPod(args.pod, m.nodeID, m.devices); // :394
+    res->FailedNodes.clear();              // the success result carries NodeNames only (:400)
+    res->NodeNames = {m.nodeID};
+    return true;
+}
+
+} // namespace vgpu
+
+// ---- flat C façade so that the Python tests can drive the C++ host ----------------------------
+extern "C" {
+
+void *vgh_new(int device, int max_nodes, int incremental, int default_mem, int default_cores) {
+    vgpu::Config cfg;
+    cfg.DefaultMem = default_mem;
+    cfg.DefaultCores = default_cores;
+    return new vgpu::Scheduler(device, max_nodes, incremental != 0, cfg);
+}
+void vgh_free(void *s) { delete static_cast<vgpu::Scheduler *>(s); }
+
+void vgh_add_node(void *s, const char *node_id, int n, const char *const *ids, const int32_t *count,
+                  const int32_t *devmem, const int32_t *devcore, const char *const *types, const int32_t *numa) {
+    vgpu::NodeInfo info;
+    for (int i = 0; i < n; i++) {
+        vgpu::DeviceInfo d;
+        d.ID = ids[i], d.Index = (uint32_t)i, d.Count = count[i], d.Devmem = devmem[i], d.Devcore = devcore[i];
+        d.Type = types[i], d.Numa = numa[i];
+        info.Devices.push_back(d);
+    }
+    static_cast<vgpu::Scheduler *>(s)->addNode(node_id, info);
+}
+
+void vgh_del_pod(void *s, const char *uid) {
+    vgpu::Pod p;
+    p.UID = uid;
+    static_cast<vgpu::Scheduler *>(s)->delPod(p);
+}
+
+// res: [n_ctrs][4] = nvidia.com/gpu, gpumem, gpumem-percentage, gpucores; INT64_MIN = absent.
+// out: "node=<id>\nids=<vgpu-ids-new>\nfailed=<id>:<why>;...\npass=<id>,<id>...\n" ; returns 0, or -1 with
+// out = error text (the reference's `return nil, err`).
+int vgh_filter(void *s, const char *ns, const char *name, const char *uid, int n_annos, const char *const *keys,
+               const char *const *vals, int n_ctrs, const int64_t *res, int n_nodes, const char *const *node_names,
+               char *out, int cap) {
+    vgpu::ExtenderArgs args;
+    args.pod.Namespace = ns, args.pod.Name = name, args.pod.UID = uid;
+    for (int i = 0; i < n_annos; i++) args.pod.Annotations[keys[i]] = vals[i];
+    static const char *rn[4] = {"nvidia.com/gpu", "nvidia.com/gpumem", "nvidia.com/gpumem-percentage",
+                                "nvidia.com/gpucores"};
+    for (int c = 0; c < n_ctrs; c++) {
+        vgpu::Container ctr;
+        for (int k = 0; k < 4; k++)
+            if (res[c * 4 + k] != INT64_MIN) ctr.Limits[rn[k]] = res[c * 4 + k];
+        args.pod.Containers.push_back(ctr);
+    }
+    for (int i = 0; i < n_nodes; i++) args.NodeNames.push_back(node_names[i]);
+    vgpu::ExtenderFilterResult r;
+    std::string err, text;
+    if (!static_cast<vgpu::Scheduler *>(s)->Filter(args, &r, &err)) {
+        snprintf(out, (size_t)cap, "%s", err.c_str());
+        return -1;
+    }
+    if (!r.PatchedAnnotations.empty()) {
+        text += "node=" + r.PatchedAnnotations[vgpu::AssignedNodeAnnotations] + "\n";
+        text += "ids=" + r.PatchedAnnotations[vgpu::AssignedIDsAnnotations] + "\n";
+    }
+    text += "failed=";
+    for (const auto &kv : r.FailedNodes) text += kv.first + ":" + kv.second + ";";
+    text += "\npass=";
+    for (size_t i = 0; i < r.NodeNames.size(); i++) text += (i ? "," : "") + r.NodeNames[i];
+    text += "\n";
+    if ((int)text.size() + 1 > cap) return -2;
+    memcpy(out, text.c_str(), text.size() + 1);
+    return 0;
+}
+
+} // extern "C"
