@@ -149,6 +149,76 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+def run_sweep(args):
+    """--sweep: the CPU/GPU crossover: N x P grid, single-container mixed pods
+    (config 3 mix).  GPU times are wall clock around the C ABI calls the Go shim would make
+    (median of reps): `resident` = vgs_score_batch with the snapshot already on the GPU,
+    `with_upload` = vgs_snapshot_upload + vgs_score_batch.  CPU arms on bounded samples:
+    R1 = faithful single-thread restatement, R1io = R1 + the reference's log lines to /dev/null,
+    R2 = packed multi-thread restatement.  One JSON line per cell."""
+    import statistics
+
+    import numpy as np
+
+    import oracle
+    import vgpu_b200 as v
+
+    Ns = [int(x) for x in args.sweep_nodes.split(",")]
+    Ps = [int(x) for x in args.sweep_pods.split(",")]
+    threads = os.cpu_count() or 1
+    out = open(args.sweep_out, "w") if args.sweep_out else None
+    for N in Ns:
+        snap = v.workload.make_snapshot(N, v.workload.SEED + 3)
+        ctx = v.Context(max_nodes=N, max_pods=max(Ps), max_reqs=max(Ps), max_picks=4 * max(Ps))
+        t0 = time.perf_counter()
+        ctx.upload(snap)
+        for P in Ps:
+            _, batch = v.workload.make_config("cfg3", 8, P)
+            pods, reqs = v.capi.pack_batch(batch, snap.type_names)
+            reps = 30 if N * P <= 1e9 else 8
+            res_t, up_t, k1_t = [], [], []
+            for r in range(reps + 3):
+                t0 = time.perf_counter()
+                ctx.score_packed(pods, reqs)
+                t1 = time.perf_counter()
+                if r >= 3:
+                    res_t.append(t1 - t0)
+                    k1_t.append(ctx.timing().score_ms * 1e-3)
+            for r in range(max(3, reps // 4) + 1):
+                t0 = time.perf_counter()
+                ctx.upload(snap)
+                ctx.score_packed(pods, reqs)
+                t1 = time.perf_counter()
+                if r >= 1:
+                    up_t.append(t1 - t0)
+            # CPU arms, bounded: at most ~2e7 pairs for R1, ~2e8 for R2
+            def sample(limit):
+                sp = max(1, min(P, int(limit // max(N, 1))))
+                return batch.select(list(range(sp))), sp
+            b1, sp1 = sample(2e7)
+            r1 = oracle.score_faithful(snap, b1)
+            bio, spio = sample(2e6)
+            rio = oracle.score_faithful(snap, bio, log_io=True)
+            b2, sp2 = sample(3e8)
+            r2 = oracle.score_packed(snap, b2, threads=threads)
+            scale = lambda secs, sp: secs * P / sp
+            cell = {
+                "nodes": N, "pods": P, "pairs": N * P,
+                "gpu_resident_s": statistics.median(res_t), "gpu_with_upload_s": statistics.median(up_t),
+                "gpu_k1_s": statistics.median(k1_t),
+                "cpu_r1_s": scale(r1.seconds_scoring, sp1), "cpu_r1_rebuild_s": scale(r1.seconds_rebuild, sp1),
+                "cpu_r1io_s": scale(rio.seconds_scoring, spio), "cpu_r2_s": scale(r2.seconds, sp2),
+                "cpu_threads": threads, "cpu_sample_pods": {"r1": sp1, "r1io": spio, "r2": sp2},
+            }
+            line = json.dumps(cell)
+            print(line, flush=True)
+            if out:
+                out.write(line + "\n")
+        ctx.close()
+    if out:
+        out.close()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -162,9 +232,15 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--check", action="store_true",
                     help="rank 0 re-checks a sample of pods against the oracle over ALL shards (not timed)")
+    ap.add_argument("--sweep", action="store_true", help="CPU/GPU crossover grid instead of the bench line")
+    ap.add_argument("--sweep-nodes", default="64,512,4096,32768,100000,1000000")
+    ap.add_argument("--sweep-pods", default="1,16,256,4096")
+    ap.add_argument("--sweep-out", default="")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
+    if args.sweep:
+        return run_sweep(args)
     args.warmup = max(args.warmup, 3)
 
     import numpy as np
