@@ -66,6 +66,7 @@ struct vgs_ctx {
     int32_t n_pods = 0, n_reqs = 0, nA = 0, nB = 0, nC = 0, nG = 0, n_picks = 0;
     // pod-sliced classes (A: Nums == 1, B: Nums == 2): bit tables, see SliceTab
     uint32_t *h_slice[2] = {}, *d_slice[2] = {};
+    unsigned char *d_prep[2] = {}; // K1p products: SliceDev tiles, pair classes, score set, classes
     size_t slice_words = 0;
     SliceTab tab[2] = {};
     bool slice_on[2] = {false, false};
@@ -160,6 +161,7 @@ void free_all(vgs_ctx *c) {
     for (int k = 0; k < 2; k++) {
         cudaFree(c->d_slice[k]);
         cudaFreeHost(c->h_slice[k]);
+        cudaFree(c->d_prep[k]);
     }
     cudaFree(c->d_stage);
     cudaFreeHost(c->h_stage);
@@ -265,9 +267,16 @@ int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
         const size_t wp = align_up((P + 31) / 32, 32);
         const size_t rows = VGS_MAX_TYPES + 5 * (kSliceMaxDistinct + 1) + (kSliceMaxPct + 1);
         c->slice_words = rows * wp + 2 * kSliceMaxDistinct + kSliceMaxPct + P + 64;
+        const size_t dinfo_b = max_tiles * 32 * 8 * sizeof(SliceDev), pcls_b = max_tiles * 32 * 32;
+        const size_t hset_b = kSliceHash * sizeof(uint32_t), gvals_b = (kSliceDict + 4) * sizeof(uint32_t);
         for (int k = 0; k < 2; k++) {
             CUI(cudaMalloc(&c->d_slice[k], c->slice_words * sizeof(uint32_t)));
             CUI(cudaMallocHost(&c->h_slice[k], c->slice_words * sizeof(uint32_t)));
+            CUI(cudaMalloc(&c->d_prep[k], dinfo_b + pcls_b + hset_b + gvals_b));
+            c->tab[k].dinfo = reinterpret_cast<uint4 *>(c->d_prep[k]);
+            c->tab[k].pcls = c->d_prep[k] + dinfo_b;
+            c->tab[k].hset = reinterpret_cast<uint32_t *>(c->d_prep[k] + dinfo_b + pcls_b);
+            c->tab[k].gvals = reinterpret_cast<uint32_t *>(c->d_prep[k] + dinfo_b + pcls_b + hset_b);
         }
         if (const char *e = getenv("VGS_SLICE_MIN")) c->slice_min = atoi(e);
     }
@@ -654,18 +663,20 @@ static int score_locked(vgs_ctx *c) {
     const DevReq *dreq = reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqs);
     const bool sliced = c->snap_slice_ok && c->dm == 8;
     if (c->nA) {
-        if (sliced && c->slice_on[0])
-            CU(launch_score_sliced(1, c->cfg.device, a, c->tab[0], c->n_types_used, c->st));
-        else
+        if (sliced && c->slice_on[0]) {
+            CU(launch_score_sliced(1, c->cfg.device, a, c->tab[0], c->n_types_used, c->d_status, c->st));
+            c->launches += c->n_tiles ? kSlicedLaunches - 1 : 0;
+        } else
             CU(launch_score_single(c->dm, true, c->cfg.device, a,
                                    reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqsA),
                                    reinterpret_cast<const int32_t *>(c->d_stage + c->off_origA), c->nA, c->st));
         if (c->n_tiles) c->launches++;
     }
     if (c->nB) {
-        if (sliced && c->slice_on[1])
-            CU(launch_score_sliced(2, c->cfg.device, a, c->tab[1], c->n_types_used, c->st));
-        else
+        if (sliced && c->slice_on[1]) {
+            CU(launch_score_sliced(2, c->cfg.device, a, c->tab[1], c->n_types_used, c->d_status, c->st));
+            c->launches += c->n_tiles ? kSlicedLaunches - 1 : 0;
+        } else
             CU(launch_score_single(c->dm, false, c->cfg.device, a,
                                    reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqsB),
                                    reinterpret_cast<const int32_t *>(c->d_stage + c->off_origB), c->nB, c->st));

@@ -519,44 +519,14 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t by
 }
 
 constexpr int kTileInt4 = kWalkWords * 2 * kWarp; // DM = 8: 512 int4 = 8 KB per 32-node tile
-constexpr int kTileBytes = kTileInt4 * 16;
-constexpr int kDict = 32;   // distinct candidate scores a CTA tracks exactly (more: still correct, slower)
-constexpr int kPend = 256;  // new scores queued per tile
+constexpr int kDict = kSliceDict;
 constexpr int kPairs = 28;  // device pairs (a < b) of an 8-device node
+constexpr int kDevTileBytes = 32 * 8 * (int)sizeof(SliceDev); // 4 KB: the SliceDev records of 32 nodes
+constexpr int kPclsTileBytes = 32 * 32;                       // 1 KB: pair classes of 32 nodes
 
 __constant__ uint8_t kPairA[kPairs] = {0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 1, 1, 2, 2, 2, 2, 2, 3, 3, 3, 3, 4, 4, 4, 5, 5, 6};
 __constant__ uint8_t kPairB[kPairs] = {1, 2, 3, 4, 5, 6, 7, 2, 3, 4, 5, 6, 7, 3, 4, 5, 6, 7, 4, 5, 6, 7, 5, 6, 7, 6, 7, 7};
 __host__ __device__ constexpr int pair_index(int a, int b) { return a * 7 - a * (a - 1) / 2 + (b - a - 1); }
-
-// per device of the current tile, filled once per tile: word offsets of its table rows, word
-// offset of its score class's row in below[], and its score
-struct __align__(16) DevInfo {
-    uint32_t o_type, o_mem, o_pct, o_core;
-    uint32_t o_flag, o_below, score, pad;
-};
-
-// shared-memory carve-up of k1_score_sliced (bytes); T = threads per CTA
-struct SliceSmem {
-    int tile, bar, dev, pscore, pbelow, vals, meta, pend, below, best, row, tab, total;
-};
-__host__ __device__ inline SliceSmem slice_smem(int T, int nums, int tab_rows) {
-    SliceSmem m;
-    int o = 0;
-    m.tile = o, o += kTileBytes;
-    m.bar = o, o += 16;
-    m.dev = o, o += 256 * (int)sizeof(DevInfo);
-    m.pscore = o, o += nums == 2 ? 32 * kPairs * 4 : 0;
-    m.pbelow = o, o += nums == 2 ? 32 * kPairs * 2 : 0;
-    m.vals = o, o += kDict * 4;
-    m.meta = o, o += 16; // nvals, npend
-    m.pend = o, o += kPend * 4;
-    m.below = o, o += (kDict + 1) * T * 4;
-    m.best = o, o += 32 * T * 4;
-    m.row = o, o += 32 * T * 2;
-    m.tab = o, o += tab_rows * T * 4;
-    m.total = o;
-    return m;
-}
 
 // number of sorted values v[0..n) that satisfy the monotone predicate (true prefix); the
 // iteration count depends on n only, so a warp never diverges here
@@ -576,28 +546,215 @@ __device__ __forceinline__ void csa(uint32_t &carry, uint32_t &sum, uint32_t a, 
     carry = (a & b) | (a & c) | (b & c);
 }
 
+__device__ __forceinline__ void hset_insert(uint32_t *__restrict__ hset, uint32_t key, uint32_t *status) {
+    uint32_t h = (key * 2654435761u) >> 20; // 12 bits
+    for (int probe = 0; probe < kSliceHash; probe++) {
+        const uint32_t cur = hset[h];
+        if (cur == key) return;
+        if (cur == 0u) {
+            const uint32_t old = atomicCAS(&hset[h], 0u, key);
+            if (old == 0u || old == key) return;
+        }
+        h = (h + 1) & (kSliceHash - 1);
+    }
+    atomicOr(status, S_DICTFULL); // cannot happen below kSliceHash distinct scores
+}
+
+// ------------------------------------------------------------------------------------
+// K1p: per batch and per sliced class, everything that depends on (device, class) but not on
+// the pod: which table rows the device selects (binary searches over the class's distinct
+// thresholds) and its candidate scores.  Thread = node; the searches of 800k devices run in
+// parallel here instead of serially inside every score CTA.
+// ------------------------------------------------------------------------------------
+template <int NUMS>
+__global__ void __launch_bounds__(128)
+    k1p_collect(const int4 *__restrict__ walk, int32_t n_tiles, SliceTab tb, uint32_t *__restrict__ status) {
+    const int node = blockIdx.x * blockDim.x + threadIdx.x;
+    if (node >= n_tiles * kWarp) return;
+    const int tile = node >> 5, lane = node & 31;
+    const int4 *tp = walk + (size_t)tile * kTileInt4;
+    int32_t totalmem[8], freemem[8], freecores[8], meta[8], wa[8], wb[8];
+    load_word<8>(tp, W_TOTALMEM, lane, totalmem);
+    load_word<8>(tp, W_FREEMEM, lane, freemem);
+    load_word<8>(tp, W_FREECORES, lane, freecores);
+    load_word<8>(tp, W_META, lane, meta);
+    if (NUMS == 1) {
+        load_word<8>(tp, W_SCORE1, lane, wa);
+    } else {
+        load_word<8>(tp, W_COUNT, lane, wa);
+        load_word<8>(tp, W_FREESLOTS, lane, wb);
+    }
+    const int r_mem = VGS_MAX_TYPES, r_pct = r_mem + tb.km + 1, r_core = r_pct + tb.kp + 1;
+    const uint32_t ndev = ((uint32_t)meta[0] >> M_NDEV_SHIFT) & 15u;
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        const uint32_t m = (uint32_t)meta[j];
+        SliceDev d;
+        if (m & (M_NOFREE | M_PAD)) { // Count <= Used (score.go:107) or not a device: never fits
+            d.r_type = d.r_mem = d.r_pct = d.r_core = (uint16_t)r_mem; // memle row 0 is all zero
+            d.a = 0u;
+            d.b = NUMS == 1 ? (uint32_t)kDict : 0u;
+        } else {
+            const int32_t fm = freemem[j], fc = freecores[j], tm = totalmem[j];
+            d.r_type = (uint16_t)(m & M_TYPE_MASK);
+            d.r_mem = (uint16_t)(r_mem + count_prefix(tb.memv, tb.km, [&](int32_t v) { return v <= fm; }));
+            d.r_pct = (uint16_t)(r_pct + count_prefix(tb.pctv, tb.kp, [&](int32_t v) { return pct_mem(tm, v) <= fm; }));
+            // cores x flags table: row = cut * 4 + (excl | full << 1)
+            d.r_core = (uint16_t)(r_core + 4 * count_prefix(tb.corev, tb.kc, [&](int32_t v) { return v <= fc; }) +
+                                  ((m & M_EXCL) ? 1 : 0) + ((m & M_FULL) ? 2 : 0));
+            if (NUMS == 1) {
+                d.a = (uint32_t)wa[j];
+                d.b = (uint32_t)kDict;
+                hset_insert(tb.hset, d.a, status);
+            } else {
+                d.a = (uint32_t)wa[j];
+                d.b = (uint32_t)wb[j] | (ndev << 24);
+            }
+        }
+        reinterpret_cast<SliceDev *>(tb.dinfo)[(size_t)node * 8 + j] = d;
+    }
+    if (NUMS == 2) {
+#pragma unroll
+        for (int a = 0; a < 7; a++)
+#pragma unroll
+            for (int b = a + 1; b < 8; b++)
+                if (!(((uint32_t)meta[a] | (uint32_t)meta[b]) & (M_NOFREE | M_PAD)))
+                    hset_insert(tb.hset,
+                                __float_as_uint(container_score(wrap_add(wa[a], wa[b]), wrap_add(wb[a], wb[b]),
+                                                                (int32_t)ndev - 2)),
+                                status);
+    }
+}
+
+// one CTA: sort the distinct scores; keep the kSliceDict largest, ascending, in gvals
+__global__ void __launch_bounds__(1024) k1p_sort(SliceTab tb) {
+    __shared__ uint32_t v[kSliceHash];
+    for (int i = threadIdx.x; i < kSliceHash; i += blockDim.x) v[i] = tb.hset[i];
+    __syncthreads();
+    for (int k = 2; k <= kSliceHash; k <<= 1)       // bitonic sort, ascending (zeros = empty slots first)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = threadIdx.x; i < kSliceHash; i += blockDim.x) {
+                const int x = i ^ j;
+                if (x > i) {
+                    const uint32_t a = v[i], b = v[x];
+                    const bool up = (i & k) == 0;
+                    if ((a > b) == up) {
+                        v[i] = b;
+                        v[x] = a;
+                    }
+                }
+            }
+            __syncthreads();
+        }
+    __shared__ int nz;
+    if (threadIdx.x == 0) {
+        int z = 0;
+        while (z < kSliceHash && v[z] == 0u) z++;
+        nz = kSliceHash - z; // distinct scores
+    }
+    __syncthreads();
+    const int keep = min(nz, kDict);
+    for (int i = threadIdx.x; i < kDict; i += blockDim.x) tb.gvals[i] = i < keep ? v[kSliceHash - keep + i] : 0xffffffffu;
+    if (threadIdx.x == 0) tb.gvals[kDict] = (uint32_t)keep;
+}
+
+__device__ __forceinline__ uint32_t class_of(const uint32_t *__restrict__ gvals, int nv, uint32_t sb) {
+    int lo = 0, hi = nv;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldg(&gvals[mid]) < sb) lo = mid + 1;
+        else hi = mid;
+    }
+    return (lo < nv && __ldg(&gvals[lo]) == sb) ? (uint32_t)lo : (uint32_t)kDict;
+}
+
+template <int NUMS>
+__global__ void __launch_bounds__(128) k1p_classify(int32_t n_tiles, SliceTab tb) {
+    const int node = blockIdx.x * blockDim.x + threadIdx.x;
+    if (node >= n_tiles * kWarp) return;
+    const int nv = (int)__ldg(&tb.gvals[kDict]);
+    SliceDev *dv = reinterpret_cast<SliceDev *>(tb.dinfo) + (size_t)node * 8;
+    if (NUMS == 1) {
+#pragma unroll
+        for (int j = 0; j < 8; j++)
+            if (dv[j].r_type != dv[j].r_mem || dv[j].a) dv[j].b = dv[j].a ? class_of(tb.gvals, nv, dv[j].a) : (uint32_t)kDict;
+    } else {
+        SliceDev d[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) d[j] = dv[j];
+        uint32_t packed[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+        for (int a = 0; a < 7; a++)
+#pragma unroll
+            for (int b = a + 1; b < 8; b++) {
+                uint32_t cl = (uint32_t)kDict;
+                const bool off = (d[a].r_type == d[a].r_mem) || (d[b].r_type == d[b].r_mem);
+                if (!off) {
+                    const int32_t nd = (int32_t)(d[a].b >> 24);
+                    cl = class_of(tb.gvals, nv,
+                                  __float_as_uint(container_score(wrap_add((int32_t)d[a].a, (int32_t)d[b].a),
+                                                                  wrap_add((int32_t)(d[a].b & 0xffffffu),
+                                                                           (int32_t)(d[b].b & 0xffffffu)),
+                                                                  nd - 2)));
+                }
+                const int q = pair_index(a, b);
+                packed[q >> 2] |= cl << ((q & 3) * 8);
+            }
+        uint4 *dst = reinterpret_cast<uint4 *>(tb.pcls + (size_t)node * 32);
+        dst[0] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+        dst[1] = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+    }
+}
+
+// shared-memory carve-up of k1_score_sliced (bytes); T = threads per CTA
+struct SliceSmem {
+    int tile, ptile, bar, vals, below, best, row, tab, total;
+};
+__host__ __device__ inline SliceSmem slice_smem(int T, int nums, int tab_rows) {
+    SliceSmem m;
+    int o = 0;
+    m.tile = o, o += 2 * kDevTileBytes;
+    m.ptile = o, o += nums == 2 ? 2 * kPclsTileBytes : 0;
+    m.bar = o, o += 16;
+    m.vals = o, o += (kDict + 4) * 4;
+    m.below = o, o += (kDict + 1) * T * 4;
+    m.best = o, o += 32 * T * 4;
+    m.row = o, o += 32 * T * 2;
+    m.tab = o, o += tab_rows * T * 4;
+    m.total = o;
+    return m;
+}
+
+// ------------------------------------------------------------------------------------
+// K1 (pod-sliced): single-request pods with Nums == 1 or Nums == 2, 32 pods per register.
+//
+// The whole CTA works on ONE node at a time; thread t owns pod word w = 32 pods of the class.
+// A device's fit word is four table rows ANDed (type, memory = fixed-MB | percentage pods,
+// cores x flags) -- the rows were chosen by K1p.  The reverse walk becomes word algebra:
+// first = fit & ~seen, second = fit & seen & ~seen2.  A candidate score is a scalar of the node
+// (a device, or a device pair) and belongs to one of the kSliceDict score classes; below[k]
+// holds my pods whose best is still under class k, so "can anybody improve here" is one AND.
+// Nodes are visited in DESCENDING row order, so "strictly greater" keeps the highest row among
+// equal scores inside a CTA; across CTAs the 64-bit key max does.  The 4 KB SliceDev tiles are
+// staged with cp.async.bulk + mbarrier (double buffered) and shared by every pod word of the CTA.
+// ------------------------------------------------------------------------------------
 template <int NUMS, bool TABSMEM, bool VERIFY>
 __global__ void __launch_bounds__(128)
-    k1_score_sliced(const int4 *__restrict__ walk, int32_t n_tiles, int32_t n_nodes, int32_t row_base,
-                    SliceTab tb, int32_t n_types, int32_t tiles_per_cta, unsigned long long *__restrict__ keys,
-                    int32_t *__restrict__ counts, uint32_t *__restrict__ vfit, float *__restrict__ vscore,
-                    int32_t vwords) {
+    k1_score_sliced(int32_t n_tiles, int32_t n_nodes, int32_t row_base, SliceTab tb, int32_t n_types,
+                    int32_t tiles_per_cta, unsigned long long *__restrict__ keys, int32_t *__restrict__ counts,
+                    uint32_t *__restrict__ vfit, float *__restrict__ vscore, int32_t vwords) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int T = blockDim.x, tid = threadIdx.x;
     // table rows, global numbering: [type 0..63][mem 0..km][pct 0..kp][cores x flags: 4 * (kc + 1)]
-    const int r_mem = VGS_MAX_TYPES, r_pct = r_mem + tb.km + 1, r_core = r_pct + tb.kp + 1;
+    const int r_core = VGS_MAX_TYPES + tb.km + 1 + tb.kp + 1;
     const int rows_g = r_core + 4 * (tb.kc + 1);
     // the shared copy keeps only the type rows that can occur (ids < n_types)
     const int drop = TABSMEM ? VGS_MAX_TYPES - n_types : 0;
     const SliceSmem L = slice_smem(T, NUMS, TABSMEM ? rows_g - drop : 0);
-    int4 *tilebuf = reinterpret_cast<int4 *>(smem_raw + L.tile);
+    unsigned char *tilebuf = smem_raw + L.tile;   // [2][kDevTileBytes]
+    unsigned char *ptilebuf = smem_raw + L.ptile; // [2][kPclsTileBytes]
     uint64_t *bar = reinterpret_cast<uint64_t *>(smem_raw + L.bar);
-    DevInfo *dev = reinterpret_cast<DevInfo *>(smem_raw + L.dev);
-    uint32_t *pscore = reinterpret_cast<uint32_t *>(smem_raw + L.pscore);
-    uint16_t *pbelow = reinterpret_cast<uint16_t *>(smem_raw + L.pbelow);
     uint32_t *vals = reinterpret_cast<uint32_t *>(smem_raw + L.vals);
-    int *s_meta = reinterpret_cast<int *>(smem_raw + L.meta); // [0] nvals, [1] npend
-    uint32_t *pend = reinterpret_cast<uint32_t *>(smem_raw + L.pend);
     // below[k][t]: my pods whose best is < vals[k] (may over-approximate, never under); row kDict = all ones
     uint32_t *below = reinterpret_cast<uint32_t *>(smem_raw + L.below);
     uint32_t *s_best = reinterpret_cast<uint32_t *>(smem_raw + L.best); // [32][T] raw score bits, 0 = none
@@ -607,18 +764,29 @@ __global__ void __launch_bounds__(128)
     const int w = blockIdx.y * T + tid;
     const bool active = w < tb.W;
     const int wc = min(w, tb.Wp - 1); // clamped column: inactive threads compute garbage, never publish
-    const int stride = TABSMEM ? T : tb.Wp;
+    const uint32_t stride = TABSMEM ? (uint32_t)T : (uint32_t)tb.Wp;
+    const uint32_t col = TABSMEM ? (uint32_t)tid : (uint32_t)wc;
     const int t_hi = n_tiles - (int)blockIdx.x * tiles_per_cta;
     const int t_lo = max(0, t_hi - tiles_per_cta);
     if (t_hi <= 0) return;
     const int n_my = t_hi - t_lo;
     const int node_lo = t_lo * kWarp;
+    constexpr uint32_t kTx = kDevTileBytes + (NUMS == 2 ? kPclsTileBytes : 0);
+
+    auto fetch = [&](int tile, int buf) { // one thread: stage the records of 32 nodes
+        mbar_expect_tx(&bar[buf], kTx);
+        bulk_g2s(tilebuf + buf * kDevTileBytes, reinterpret_cast<const unsigned char *>(tb.dinfo) + (size_t)tile * kDevTileBytes,
+                 kDevTileBytes, &bar[buf]);
+        if (NUMS == 2)
+            bulk_g2s(ptilebuf + buf * kPclsTileBytes, tb.pcls + (size_t)tile * kPclsTileBytes, kPclsTileBytes, &bar[buf]);
+    };
 
     for (int b = 0; b < 32; b++) {
         s_best[b * T + tid] = 0u;
         s_row[b * T + tid] = 0;
     }
     for (int k = 0; k <= kDict; k++) below[k * T + tid] = 0xffffffffu;
+    for (int k = tid; k <= kDict; k += T) vals[k] = __ldg(&tb.gvals[k]);
     if (TABSMEM) {
         uint32_t *tw = reinterpret_cast<uint32_t *>(smem_raw + L.tab);
         for (int r = 0; r < rows_g - drop; r++) {
@@ -627,33 +795,20 @@ __global__ void __launch_bounds__(128)
         }
     }
     if (tid == 0) {
-        s_meta[0] = 0;
-        s_meta[1] = 0;
         mbar_init(&bar[0], 1);
+        mbar_init(&bar[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
-    if (tid == 0) {
-        mbar_expect_tx(&bar[0], kTileBytes);
-        bulk_g2s(tilebuf, walk + (size_t)(t_hi - 1) * kTileInt4, kTileBytes, &bar[0]);
-    }
+    if (tid == 0) fetch(t_hi - 1, 0);
+    const int nv = (int)vals[kDict];
 
-    auto TAB = [&](uint32_t off) -> uint32_t {
-        if (TABSMEM) return tabs[off + tid];
-        return __ldg(&tb.base[off + wc]);
+    auto TAB = [&](uint32_t row) -> uint32_t {
+        if (TABSMEM) return tabs[(row >= (uint32_t)VGS_MAX_TYPES ? row - (uint32_t)drop : row) * stride + col];
+        return __ldg(&tb.base[row * stride + col]);
     };
-    auto row_off = [&](int rg) -> uint32_t { // global row number -> word offset in the table in use
-        const int r = (TABSMEM && rg >= VGS_MAX_TYPES) ? rg - drop : rg;
-        return (uint32_t)r * (uint32_t)stride;
-    };
-    auto find_class = [&](uint32_t sb, int nv) -> int { // index of sb in vals[0..nv) or kDict
-        int lo = 0, hi = nv;
-        while (lo < hi) {
-            int mid = (lo + hi) >> 1;
-            if (vals[mid] < sb) lo = mid + 1;
-            else hi = mid;
-        }
-        return (lo < nv && vals[lo] == sb) ? lo : kDict;
+    auto fit_of = [&](const uint4 &d) -> uint32_t {
+        return TAB(d.x & 0xffffu) & (TAB(d.x >> 16) | TAB(d.y & 0xffffu)) & TAB(d.y >> 16);
     };
     // pods in `word` get candidate (sb, node); nodes only ever decrease, so equal scores keep
     // the earlier (higher) row.  A pod whose best reaches sb leaves every below[k] with vals[k] <= sb.
@@ -667,51 +822,12 @@ __global__ void __launch_bounds__(128)
                 imp |= 1u << b;
             }
         }
-        const int nv = s_meta[0];
         for (int k = 0; k < nv && vals[k] <= sb; k++) below[k * T + tid] &= ~imp;
     };
-    // Exact ordered replay of one node whose detection word was non-zero.  NUMS == 1: nw[j] =
-    // pods whose first fitting device is j.  NUMS == 2: first/second fitting device words.
-    auto replay1 = [&](const uint32_t (&nw)[8], int l, int node) {
-#pragma unroll
-        for (int j = 0; j < 8; j++) {
-            const int d = l * 8 + j;
-            if (VERIFY && active) {
-                for (uint32_t mth = nw[j]; mth; mth &= mth - 1) {
-                    const int p = tb.orig[w * 32 + __ffs((int)mth) - 1];
-                    vscore[(size_t)p * n_nodes + node] = __uint_as_float(dev[d].score);
-                }
-            }
-            const uint32_t h = nw[j] & below[dev[d].o_below + tid];
-            if (h) raise(h, dev[d].score, node);
-        }
-    };
-    auto replay2 = [&](const uint32_t (&first)[8], const uint32_t (&second)[8], int l, int node) {
-#pragma unroll
-        for (int a = 0; a < 7; a++) {
-            if (first[a] == 0u) continue;
-#pragma unroll
-            for (int b = a + 1; b < 8; b++) {
-                const uint32_t wab = first[a] & second[b]; // pods taking exactly devices a and b
-                if (wab == 0u) continue;
-                const int q = l * kPairs + pair_index(a, b);
-                if (VERIFY && active) {
-                    for (uint32_t mth = wab; mth; mth &= mth - 1) {
-                        const int p = tb.orig[w * 32 + __ffs((int)mth) - 1];
-                        vscore[(size_t)p * n_nodes + node] = __uint_as_float(pscore[q]);
-                    }
-                }
-                const uint32_t h = wab & below[pbelow[q] + tid];
-                if (h) raise(h, pscore[q], node);
-            }
-        }
-    };
-    auto mark_fit = [&](uint32_t anyfit, int node) { // verify mode: the pod x node fit bitmap
-        if (VERIFY && active) {
-            for (uint32_t mth = anyfit; mth; mth &= mth - 1) {
-                const int p = tb.orig[w * 32 + __ffs((int)mth) - 1];
-                atomicOr(&vfit[(size_t)p * vwords + (node >> 5)], 1u << (node & 31));
-            }
+    auto mark = [&](uint32_t word, int node, uint32_t sb) { // verify mode: score of every fitting pair
+        for (uint32_t mth = word; mth; mth &= mth - 1) {
+            const int p = tb.orig[w * 32 + __ffs((int)mth) - 1];
+            vscore[(size_t)p * n_nodes + node] = __uint_as_float(sb);
         }
     };
 
@@ -720,112 +836,17 @@ __global__ void __launch_bounds__(128)
     for (int k = 0; k < kSliceCountPlanes; k++) cnt[k] = 0u;
 
     for (int it = 0; it < n_my; it++) {
-        const int tile = t_hi - 1 - it;
-        mbar_wait(&bar[0], (uint32_t)(it & 1));
+        const int tile = t_hi - 1 - it, buf = it & 1;
+        if (tid == 0 && it + 1 < n_my) fetch(tile - 1, buf ^ 1); // that buffer was released by the last sync
+        mbar_wait(&bar[buf], (uint32_t)((it >> 1) & 1));
+        const uint4 *dv = reinterpret_cast<const uint4 *>(tilebuf + buf * kDevTileBytes); // [32 nodes][8]
+        const uint8_t *pc = ptilebuf + buf * kPclsTileBytes;                              // [32 nodes][32]
 
-        // ---- per-tile pre-pass: everything that depends on the node only -------------------
-        const int32_t *ti = reinterpret_cast<const int32_t *>(tilebuf);
-        auto tile_word = [&](int wd, int l, int j) { return ti[(((wd * 2 + (j >> 2)) * kWarp + l) << 2) + (j & 3)]; };
-        int nv = s_meta[0];
-        for (int d = tid; d < 256; d += T) {
-            const int l = d >> 3, j = d & 7;
-            const uint32_t m = (uint32_t)tile_word(W_META, l, j);
-            DevInfo di;
-            di.pad = 0;
-            di.o_flag = 0;
-            di.o_below = (uint32_t)(kDict * T);
-            if (m & (M_NOFREE | M_PAD)) { // Count <= Used (score.go:107) or not a device: never fits
-                di.o_type = di.o_mem = di.o_pct = di.o_core = row_off(r_mem); // memle row 0: all zero
-                di.score = 0;
-            } else {
-                const int32_t fm = tile_word(W_FREEMEM, l, j), fc = tile_word(W_FREECORES, l, j);
-                const int32_t tm = tile_word(W_TOTALMEM, l, j);
-                di.o_type = row_off((int)(m & M_TYPE_MASK));
-                di.o_mem = row_off(r_mem + count_prefix(tb.memv, tb.km, [&](int32_t v) { return v <= fm; }));
-                di.o_pct = row_off(r_pct + count_prefix(tb.pctv, tb.kp, [&](int32_t v) { return pct_mem(tm, v) <= fm; }));
-                // cores x flags table: row = cut * 4 + (excl | full << 1)
-                di.o_core = row_off(r_core + 4 * count_prefix(tb.corev, tb.kc, [&](int32_t v) { return v <= fc; }) +
-                                    ((m & M_EXCL) ? 1 : 0) + ((m & M_FULL) ? 2 : 0));
-                di.score = (uint32_t)tile_word(W_SCORE1, l, j);
-                if (NUMS == 1) {
-                    const int cl = find_class(di.score, nv);
-                    di.o_below = (uint32_t)(cl * T);
-                    if (cl == kDict) {
-                        const int slot = atomicAdd(&s_meta[1], 1);
-                        if (slot < kPend) pend[slot] = di.score;
-                    }
-                }
-            }
-            dev[d] = di;
-        }
-        if (NUMS == 2) {
-            for (int q = tid; q < 32 * kPairs; q += T) {
-                const int l = q / kPairs, pr = q - l * kPairs;
-                const int a = kPairA[pr], b = kPairB[pr];
-                const uint32_t ma = (uint32_t)tile_word(W_META, l, a), mb = (uint32_t)tile_word(W_META, l, b);
-                uint32_t sb = 0u;
-                int cl = kDict;
-                if (!((ma | mb) & (M_NOFREE | M_PAD))) {
-                    const int32_t nd = (int32_t)((ma >> M_NDEV_SHIFT) & 15u);
-                    sb = __float_as_uint(container_score(
-                        wrap_add(tile_word(W_COUNT, l, a), tile_word(W_COUNT, l, b)),
-                        wrap_add(tile_word(W_FREESLOTS, l, a), tile_word(W_FREESLOTS, l, b)), nd - 2));
-                    cl = find_class(sb, nv);
-                    if (cl == kDict) {
-                        const int slot = atomicAdd(&s_meta[1], 1);
-                        if (slot < kPend) pend[slot] = sb;
-                    }
-                }
-                pscore[q] = sb;
-                pbelow[q] = (uint16_t)(cl * T);
-            }
-        }
-        __syncthreads(); // tile fully consumed: dev[] / pair tables are complete
-        if (tid == 0 && it + 1 < n_my) { // the tile buffer is free during the node loop: prefetch
-            mbar_expect_tx(&bar[0], kTileBytes);
-            bulk_g2s(tilebuf, walk + (size_t)(tile - 1) * kTileInt4, kTileBytes, &bar[0]);
-        }
-        const int npend = min(s_meta[1], kPend);
-        if (npend > 0) { // uniform: new score values -> insert into the sorted dictionary
-            for (int i = 0; i < npend; i++) {
-                const uint32_t x = pend[i];
-                int lo = 0, hi = nv;
-                while (lo < hi) {
-                    int mid = (lo + hi) >> 1;
-                    if (vals[mid] < x) lo = mid + 1;
-                    else hi = mid;
-                }
-                if ((lo < nv && vals[lo] == x) || nv >= kDict) continue; // known, or dictionary full
-                __syncthreads();
-                // below[] of the new value = below[] of the next larger value (no best lies between)
-                for (int k = nv; k > lo; k--) below[k * T + tid] = below[(k - 1) * T + tid];
-                if (lo == nv) below[lo * T + tid] = 0xffffffffu; // larger than every best so far
-                if (tid == 0) {
-                    for (int k = nv; k > lo; k--) vals[k] = vals[k - 1];
-                    vals[lo] = x;
-                    s_meta[0] = nv + 1;
-                }
-                nv++;
-                __syncthreads();
-            }
-            __syncthreads();
-            if (tid == 0) s_meta[1] = 0;
-            // classes again, now that (almost always) every value is known
-            if (NUMS == 1) {
-                for (int d = tid; d < 256; d += T)
-                    if (dev[d].score) dev[d].o_below = (uint32_t)(find_class(dev[d].score, nv) * T);
-            } else {
-                for (int q = tid; q < 32 * kPairs; q += T)
-                    if (pscore[q]) pbelow[q] = (uint16_t)(find_class(pscore[q], nv) * T);
-            }
-            __syncthreads();
-        }
-
-        // ---- 32 nodes, descending, in groups of four.  Phase 1 is branch-free word algebra for
-        // all four nodes (independent chains for the scheduler to interleave): fit words from the
-        // table rows, the walk as masks, and a detection word "could any pod of mine improve
-        // here?" against below[] as it stands (stale = larger = safe).  Phase 2 replays, in
-        // order and against the live below[], only the nodes whose detection word is non-zero.
+        // 32 nodes, descending, in groups of four.  Phase 1 is branch-free word algebra for all
+        // four nodes (independent chains): fit words, the walk as masks, and a detection word
+        // "could any pod of mine improve here?" against below[] as it stands (stale = larger =
+        // safe).  Phase 2 replays, in order and against the live below[], only the nodes whose
+        // detection word is non-zero.
         for (int lq = 7; lq >= 0; lq--) {
             uint32_t xs[4], hit[4];
             if (NUMS == 1) {
@@ -836,20 +857,27 @@ __global__ void __launch_bounds__(128)
                     uint32_t rem = 0xffffffffu, h = VERIFY ? 0xffffffffu : 0u;
 #pragma unroll
                     for (int j = 0; j < 8; j++) { // walk order: the first fitting device is taken
-                        const int4 o = *reinterpret_cast<const int4 *>(&dev[l * 8 + j]);
-                        const uint32_t f = TAB((uint32_t)o.x) & (TAB((uint32_t)o.y) | TAB((uint32_t)o.z)) & TAB((uint32_t)o.w);
+                        const uint4 d = dv[l * 8 + j];
+                        const uint32_t f = fit_of(d);
                         nw[u][j] = f & rem;
                         rem &= ~f;
-                        h |= nw[u][j] & below[dev[l * 8 + j].o_below + tid];
+                        h |= nw[u][j] & below[d.w * T + tid];
                     }
                     xs[u] = ~rem;
                     hit[u] = h;
                 }
 #pragma unroll
                 for (int u = 3; u >= 0; u--) {
-                    const int l = lq * 4 + u;
-                    if (hit[u]) replay1(nw[u], l, tile * kWarp + l);
-                    mark_fit(xs[u], tile * kWarp + l);
+                    const int l = lq * 4 + u, node = tile * kWarp + l;
+                    if (hit[u]) {
+#pragma unroll
+                        for (int j = 0; j < 8; j++) {
+                            const uint4 d = dv[l * 8 + j];
+                            if (VERIFY && active) mark(nw[u][j], node, d.z);
+                            const uint32_t h = nw[u][j] & below[d.w * T + tid];
+                            if (h) raise(h, d.z, node);
+                        }
+                    }
                 }
             } else {
                 uint32_t first[4][8], second[4][8];
@@ -859,26 +887,58 @@ __global__ void __launch_bounds__(128)
                     uint32_t seen = 0u, seen2 = 0u, h = VERIFY ? 0xffffffffu : 0u;
 #pragma unroll
                     for (int j = 0; j < 8; j++) {
-                        const int4 o = *reinterpret_cast<const int4 *>(&dev[l * 8 + j]);
-                        const uint32_t f = TAB((uint32_t)o.x) & (TAB((uint32_t)o.y) | TAB((uint32_t)o.z)) & TAB((uint32_t)o.w);
+                        const uint32_t f = fit_of(dv[l * 8 + j]);
                         first[u][j] = f & ~seen;
                         second[u][j] = f & seen & ~seen2;
                         seen2 |= seen & f;
                         seen |= f;
                     }
+                    const uint4 c0 = *reinterpret_cast<const uint4 *>(pc + l * 32);
+                    const uint4 c1 = *reinterpret_cast<const uint4 *>(pc + l * 32 + 16);
+                    const uint32_t cw[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
 #pragma unroll
                     for (int a = 0; a < 7; a++)
 #pragma unroll
-                        for (int b = a + 1; b < 8; b++)
-                            h |= first[u][a] & second[u][b] & below[pbelow[l * kPairs + pair_index(a, b)] + tid];
+                        for (int b = a + 1; b < 8; b++) {
+                            const int q = pair_index(a, b);
+                            const uint32_t cl = (cw[q >> 2] >> ((q & 3) * 8)) & 0xffu;
+                            h |= first[u][a] & second[u][b] & below[cl * T + tid];
+                        }
                     xs[u] = seen2; // the node fits a pod iff two devices fit
                     hit[u] = h;
                 }
 #pragma unroll
                 for (int u = 3; u >= 0; u--) {
-                    const int l = lq * 4 + u;
-                    if (hit[u]) replay2(first[u], second[u], l, tile * kWarp + l);
-                    mark_fit(xs[u], tile * kWarp + l);
+                    const int l = lq * 4 + u, node = tile * kWarp + l;
+                    if (hit[u]) {
+#pragma unroll
+                        for (int a = 0; a < 7; a++) {
+                            if (first[u][a] == 0u) continue;
+#pragma unroll
+                            for (int b = a + 1; b < 8; b++) {
+                                const uint32_t wab = first[u][a] & second[u][b]; // pods taking exactly a and b
+                                if (wab == 0u) continue;
+                                const uint4 da = dv[l * 8 + a], db = dv[l * 8 + b];
+                                const uint32_t sb = __float_as_uint(container_score(
+                                    wrap_add((int32_t)da.z, (int32_t)db.z),
+                                    wrap_add((int32_t)(da.w & 0xffffffu), (int32_t)(db.w & 0xffffffu)),
+                                    (int32_t)(da.w >> 24) - 2));
+                                if (VERIFY && active) mark(wab, node, sb);
+                                const uint32_t h = wab & below[(uint32_t)pc[l * 32 + pair_index(a, b)] * T + tid];
+                                if (h) raise(h, sb, node);
+                            }
+                        }
+                    }
+                }
+            }
+            if (VERIFY && active) {
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const int node = tile * kWarp + lq * 4 + u;
+                    for (uint32_t mth = xs[u]; mth; mth &= mth - 1) {
+                        const int p = tb.orig[w * 32 + __ffs((int)mth) - 1];
+                        atomicOr(&vfit[(size_t)p * vwords + (node >> 5)], 1u << (node & 31));
+                    }
                 }
             }
             // counter += xs[0] + xs[1] + xs[2] + xs[3] (bit-sliced, carry-save)
@@ -893,7 +953,7 @@ __global__ void __launch_bounds__(128)
                 cf = t2;
             }
         }
-        __syncthreads(); // everyone is done with dev[] and the pair tables
+        __syncthreads(); // everyone is done with this tile buffer
     }
 
     if (!active) return;
@@ -1208,8 +1268,18 @@ cudaError_t launch_score_general(int dm, int dev, const ScoreArgs &a, const DevR
 
 
 template <int NUMS>
-static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &tb, int n_types, cudaStream_t st) {
+static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &tb, int n_types, uint32_t *status,
+                                   cudaStream_t st) {
     const int sms = sm_count(dev);
+    // K1p: table rows + candidate scores per device, distinct scores -> classes
+    cudaError_t e;
+    if ((e = cudaMemsetAsync(tb.hset, 0, kSliceHash * sizeof(uint32_t), st)) != cudaSuccess) return e;
+    const int nthreads = a.n_tiles * kWarp;
+    k1p_collect<NUMS><<<(nthreads + 127) / 128, 128, 0, st>>>(a.walk, a.n_tiles, tb, status);
+    k1p_sort<<<1, 1024, 0, st>>>(tb);
+    k1p_classify<NUMS><<<(nthreads + 127) / 128, 128, 0, st>>>(a.n_tiles, tb);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+
     int warps = (tb.W + 31) / 32;
     if (warps > 4) warps = 4;
     const int T = warps * 32;
@@ -1219,13 +1289,12 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
     const int rows_s = n_types + (tb.km + 1) + (tb.kp + 1) + 4 * (tb.kc + 1);
     static int force_tab = -2;
     if (force_tab == -2) {
-        const char *e = getenv("VGS_SLICE_TABSMEM");
-        force_tab = e ? atoi(e) : -1;
+        const char *ev = getenv("VGS_SLICE_TABSMEM");
+        force_tab = ev ? atoi(ev) : -1;
     }
     // tables in shared memory when small (else global / L1)
     const bool tabsmem = force_tab >= 0 ? force_tab != 0 : (size_t)rows_s * T * 4 <= 8 * 1024;
     const int smem = slice_smem(T, NUMS, tabsmem ? rows_s : 0).total;
-    cudaError_t e;
     auto go = [&](auto kernel) -> cudaError_t {
         if ((e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)) != cudaSuccess) return e;
         int occ = 1;
@@ -1240,7 +1309,7 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
         const int cap = ((1 << kSliceCountPlanes) - 1) / kWarp;
         if (tiles_per > cap) tiles_per = cap;
         const int gx = (a.n_tiles + tiles_per - 1) / tiles_per;
-        kernel<<<dim3(gx, gy), T, smem, st>>>(a.walk, a.n_tiles, a.n_nodes, a.row_base, tb, n_types, tiles_per, a.keys,
+        kernel<<<dim3(gx, gy), T, smem, st>>>(a.n_tiles, a.n_nodes, a.row_base, tb, n_types, tiles_per, a.keys,
                                               a.counts, a.vfit, a.vscore, a.vwords);
         return cudaGetLastError();
     };
@@ -1249,9 +1318,10 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
 }
 
 cudaError_t launch_score_sliced(int nums, int dev, const ScoreArgs &a, const SliceTab &tb, int n_types,
-                                cudaStream_t st) {
+                                uint32_t *status, cudaStream_t st) {
     if (tb.n_pods <= 0 || a.n_tiles <= 0) return cudaSuccess;
-    return nums == 1 ? launch_sliced_t<1>(dev, a, tb, n_types, st) : launch_sliced_t<2>(dev, a, tb, n_types, st);
+    return nums == 1 ? launch_sliced_t<1>(dev, a, tb, n_types, status, st)
+                     : launch_sliced_t<2>(dev, a, tb, n_types, status, st);
 }
 
 cudaError_t launch_merge(const unsigned long long *gk, const int32_t *gc, int32_t n_shards, int32_t stride,

@@ -15,6 +15,7 @@
 //          and a warp reads 512 contiguous bytes per instruction.
 #pragma once
 #include <stdint.h>
+#include <vector_types.h>
 
 namespace vgs {
 
@@ -89,7 +90,20 @@ struct SliceTab {
     const int32_t *orig;                // class position -> pod index of the batch
     int32_t km, kp, kc;
     int32_t n_pods, W, Wp;
+    // per-batch products of the preparation kernels (K1p), all in device memory
+    uint4 *dinfo;      // [n_tiles*32*8] SliceDev, node-major, walk order
+    uint8_t *pcls;     // [n_tiles*32][32] score class of each device pair (Nums == 2 class only)
+    uint32_t *hset;    // [kSliceHash] open-addressing set of the distinct candidate scores
+    uint32_t *gvals;   // [kSliceDict] the largest distinct scores, ascending; gvals[kSliceDict] = count
 };
+// what the sliced score kernel needs to know about one device, 16 bytes
+struct __align__(16) SliceDev {
+    uint16_t r_type, r_mem, r_pct, r_core; // table rows this device selects (r_type == r_mem: never fits)
+    uint32_t a;                            // Nums == 1: score bits if picked alone; Nums == 2: Count
+    uint32_t b;                            // Nums == 1: score class; Nums == 2: free slots | ndev << 24
+};
+constexpr int kSliceDict = 32;    // distinct candidate scores tracked exactly (the largest ones)
+constexpr int kSliceHash = 4096;  // capacity of the distinct-score set (power of two)
 constexpr int kSliceMaxDistinct = 1024; // distinct Memreq / Coresreq values per class
 constexpr int kSliceMaxPct = 101;       // MemPercentagereq in [0, 100]
 constexpr int kSliceCountPlanes = 13;   // bit-sliced fit counter: < 8192 nodes per CTA
@@ -102,6 +116,7 @@ constexpr uint32_t S_NDEV = 4u;     // ndev out of range
 constexpr uint32_t S_MISMATCH = 8u; // resolve kernel disagrees with score kernel
 constexpr uint32_t S_DELTA = 16u;   // delta names a row/slot outside the shard
 constexpr uint32_t S_BIGMEM = 32u;  // (not an error) some Totalmem outside [0, kSliceMaxTotalmem]
+constexpr uint32_t S_DICTFULL = 64u; // more than kSliceHash distinct candidate scores in one class
 
 __host__ __device__ inline uint32_t order_bits(uint32_t fbits) {
     // monotone map float bits -> unsigned, never 0 for a finite float
