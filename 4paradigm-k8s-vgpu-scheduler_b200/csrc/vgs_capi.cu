@@ -84,6 +84,10 @@ struct vgs_ctx {
     float *d_vscore = nullptr;
     int32_t vwords = 0;
 
+    // the pod classes of one batch are independent: their kernel chains run on side streams
+    // forked from / joined to `st` with events
+    cudaStream_t side[2] = {};
+    cudaEvent_t ev_fork = nullptr, ev_join[2] = {};
     cudaEvent_t ev[EV_N] = {};
     bool ev_set[EV_N] = {};
     long long launches = 0;
@@ -175,6 +179,11 @@ void free_all(vgs_ctx *c) {
     cudaFree(c->d_vscore);
     for (int i = 0; i < EV_N; i++)
         if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+    for (int k = 0; k < 2; k++) {
+        if (c->side[k]) cudaStreamDestroy(c->side[k]);
+        if (c->ev_join[k]) cudaEventDestroy(c->ev_join[k]);
+    }
+    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     if (c->own_stream && c->st) cudaStreamDestroy(c->st);
 }
 
@@ -233,6 +242,11 @@ int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
         c->own_stream = true;
     }
     for (int i = 0; i < EV_N; i++) CUI(cudaEventCreate(&c->ev[i]));
+    CUI(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+    for (int k = 0; k < 2; k++) {
+        CUI(cudaStreamCreateWithFlags(&c->side[k], cudaStreamNonBlocking));
+        CUI(cudaEventCreateWithFlags(&c->ev_join[k], cudaEventDisableTiming));
+    }
     const size_t cells = (size_t)cfg->max_nodes * cfg->max_devices;
     for (int f = 0; f < VGS_NUM_PLANES; f++) CUI(cudaMalloc(&c->d_raw[f], cells * sizeof(int32_t)));
     CUI(cudaMalloc(&c->d_ndev, (size_t)cfg->max_nodes * sizeof(int32_t)));
@@ -662,24 +676,27 @@ static int score_locked(vgs_ctx *c) {
     }
     const DevReq *dreq = reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqs);
     const bool sliced = c->snap_slice_ok && c->dm == 8;
+    // fork: class A and class B chains on side streams, the rest on `st`
+    CU(cudaEventRecord(c->ev_fork, c->st));
+    for (int k = 0; k < 2; k++) CU(cudaStreamWaitEvent(c->side[k], c->ev_fork, 0));
     if (c->nA) {
         if (sliced && c->slice_on[0]) {
-            CU(launch_score_sliced(1, c->cfg.device, a, c->tab[0], c->n_types_used, c->d_status, c->st));
+            CU(launch_score_sliced(1, c->cfg.device, a, c->tab[0], c->n_types_used, c->d_status, c->side[0]));
             c->launches += c->n_tiles ? kSlicedLaunches - 1 : 0;
         } else
             CU(launch_score_single(c->dm, true, c->cfg.device, a,
                                    reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqsA),
-                                   reinterpret_cast<const int32_t *>(c->d_stage + c->off_origA), c->nA, c->st));
+                                   reinterpret_cast<const int32_t *>(c->d_stage + c->off_origA), c->nA, c->side[0]));
         if (c->n_tiles) c->launches++;
     }
     if (c->nB) {
         if (sliced && c->slice_on[1]) {
-            CU(launch_score_sliced(2, c->cfg.device, a, c->tab[1], c->n_types_used, c->d_status, c->st));
+            CU(launch_score_sliced(2, c->cfg.device, a, c->tab[1], c->n_types_used, c->d_status, c->side[1]));
             c->launches += c->n_tiles ? kSlicedLaunches - 1 : 0;
         } else
             CU(launch_score_single(c->dm, false, c->cfg.device, a,
                                    reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqsB),
-                                   reinterpret_cast<const int32_t *>(c->d_stage + c->off_origB), c->nB, c->st));
+                                   reinterpret_cast<const int32_t *>(c->d_stage + c->off_origB), c->nB, c->side[1]));
         if (c->n_tiles) c->launches++;
     }
     if (c->nC) {
@@ -692,6 +709,10 @@ static int score_locked(vgs_ctx *c) {
         CU(launch_score_general(c->dm, c->cfg.device, a, dreq,
                                 reinterpret_cast<const GenPod *>(c->d_stage + c->off_podsG), c->nG, c->st));
         if (c->n_tiles) c->launches++;
+    }
+    for (int k = 0; k < 2; k++) { // join
+        CU(cudaEventRecord(c->ev_join[k], c->side[k]));
+        CU(cudaStreamWaitEvent(c->st, c->ev_join[k], 0));
     }
     rec(c, EV_SC1);
     c->scored = true;

@@ -626,14 +626,26 @@ __global__ void __launch_bounds__(128)
     }
 }
 
-// one CTA: sort the distinct scores; keep the kSliceDict largest, ascending, in gvals
+// one CTA: compact the distinct scores out of the hash set, sort them, keep the kSliceDict
+// largest (ascending) in gvals, their count in gvals[kSliceDict]
 __global__ void __launch_bounds__(1024) k1p_sort(SliceTab tb) {
     __shared__ uint32_t v[kSliceHash];
-    for (int i = threadIdx.x; i < kSliceHash; i += blockDim.x) v[i] = tb.hset[i];
+    __shared__ int n_s;
+    if (threadIdx.x == 0) n_s = 0;
     __syncthreads();
-    for (int k = 2; k <= kSliceHash; k <<= 1)       // bitonic sort, ascending (zeros = empty slots first)
+    for (int i = threadIdx.x; i < kSliceHash; i += blockDim.x) {
+        const uint32_t x = tb.hset[i];
+        if (x) v[atomicAdd(&n_s, 1)] = x;
+    }
+    __syncthreads();
+    const int n = n_s;
+    int m = 2; // sort size: next power of two, zero padded (zeros sort first)
+    while (m < n) m <<= 1;
+    for (int i = n + threadIdx.x; i < m; i += blockDim.x) v[i] = 0u;
+    __syncthreads();
+    for (int k = 2; k <= m; k <<= 1)
         for (int j = k >> 1; j > 0; j >>= 1) {
-            for (int i = threadIdx.x; i < kSliceHash; i += blockDim.x) {
+            for (int i = threadIdx.x; i < m; i += blockDim.x) {
                 const int x = i ^ j;
                 if (x > i) {
                     const uint32_t a = v[i], b = v[x];
@@ -646,15 +658,8 @@ __global__ void __launch_bounds__(1024) k1p_sort(SliceTab tb) {
             }
             __syncthreads();
         }
-    __shared__ int nz;
-    if (threadIdx.x == 0) {
-        int z = 0;
-        while (z < kSliceHash && v[z] == 0u) z++;
-        nz = kSliceHash - z; // distinct scores
-    }
-    __syncthreads();
-    const int keep = min(nz, kDict);
-    for (int i = threadIdx.x; i < kDict; i += blockDim.x) tb.gvals[i] = i < keep ? v[kSliceHash - keep + i] : 0xffffffffu;
+    const int keep = min(n, kDict);
+    for (int i = threadIdx.x; i < kDict; i += blockDim.x) tb.gvals[i] = i < keep ? v[m - keep + i] : 0xffffffffu;
     if (threadIdx.x == 0) tb.gvals[kDict] = (uint32_t)keep;
 }
 
@@ -1300,12 +1305,12 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
         int occ = 1;
         if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, T, smem)) != cudaSuccess) return e;
         if (occ < 1) occ = 1;
-        // one wave of CTAs; at least 4 tiles each so the per-CTA set-up and flush stay small, at
+        // one wave of CTAs; at least 2 tiles each so the per-CTA set-up and flush stay small, at
         // most (2^planes - 1) nodes each so the bit-sliced counter cannot overflow
         long long want = (long long)sms * occ / gy;
         if (want < 1) want = 1;
         int tiles_per = (int)((a.n_tiles + want - 1) / want);
-        if (tiles_per < 4) tiles_per = 4;
+        if (tiles_per < 2) tiles_per = 2;
         const int cap = ((1 << kSliceCountPlanes) - 1) / kWarp;
         if (tiles_per > cap) tiles_per = cap;
         const int gx = (a.n_tiles + tiles_per - 1) / tiles_per;
