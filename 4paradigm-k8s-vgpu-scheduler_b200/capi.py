@@ -10,7 +10,7 @@ from typing import Dict, List, Optional, Tuple
 
 import numpy as np
 
-from .model import ANNO_NOUSE, ANNO_NUMA, ANNO_USE, BatchResult, PodBatch, Snapshot
+from .model import ANNO_DCU_NOUSE, ANNO_DCU_USE, ANNO_NOUSE, ANNO_NUMA, ANNO_USE, BatchResult, PodBatch, Snapshot
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "csrc", "libvgpuscore.so")
@@ -28,7 +28,7 @@ EXPORTS = (
     "vgs_score_batch", "vgs_pods_upload", "vgs_score_resident", "vgs_resolve_resident",
     "vgs_results_download", "vgs_sync", "vgs_keys_device", "vgs_keys_merge", "vgs_results_device",
     "vgs_verify_download", "vgs_last_timing", "vgs_host_typemask", "vgs_host_numa_bind",
-    "vgs_host_encode_pod_devices", "vgs_score_batch_noalloc",
+    "vgs_host_encode_pod_devices", "vgs_host_decode_node_devices", "vgs_score_batch_noalloc",
 )
 
 
@@ -115,12 +115,27 @@ def _b(s: Optional[str]) -> Optional[bytes]:
 def host_typemask(req_type: str, annos: Dict[str, str], type_names: List[str]) -> int:
     lib = load_library()
     arr = (C.c_char_p * len(type_names))(*[t.encode("utf-8") for t in type_names])
-    return int(lib.vgs_host_typemask(_b(req_type), _b(annos.get(ANNO_USE)), _b(annos.get(ANNO_NOUSE)), arr,
-                                     len(type_names)))
+    use, nouse = (ANNO_DCU_USE, ANNO_DCU_NOUSE) if req_type == "DCU" else (ANNO_USE, ANNO_NOUSE)
+    return int(lib.vgs_host_typemask(_b(req_type), _b(annos.get(use)), _b(annos.get(nouse)), arr, len(type_names)))
 
 
 def host_numa_bind(annos: Dict[str, str]) -> int:
     return int(load_library().vgs_host_numa_bind(_b(annos.get(ANNO_NUMA))))
+
+
+def decode_node_devices(anno: str, max_dev: int = 64):
+    """util.DecodeNodeDevices -> list of dicts (ID, Count, Devmem, Devcore, Type, Numa, Health); raises on
+    what the reference rejects"""
+    lib = load_library()
+    raw = anno.encode("utf-8")
+    cols = [np.zeros(max_dev, dtype=np.int32) for _ in range(9)]
+    lib.vgs_host_decode_node_devices.restype = C.c_int32
+    n = lib.vgs_host_decode_node_devices(C.c_char_p(raw), max_dev, *[C.c_void_p(c.ctypes.data) for c in cols])
+    if n < 0:
+        raise VgsError(n, "node annotations not decode successfully")
+    cnt, mem, core, numa, health, io, il, to, tl = cols
+    return [dict(ID=raw[io[i]:io[i] + il[i]].decode(), Count=int(cnt[i]), Devmem=int(mem[i]), Devcore=int(core[i]),
+                 Type=raw[to[i]:to[i] + tl[i]].decode(), Numa=int(numa[i]), Health=bool(health[i])) for i in range(n)]
 
 
 def encode_pod_devices(ctrs: List[List[Tuple[str, str, int, int]]]) -> str:
@@ -165,7 +180,7 @@ def pack_batch(batch: PodBatch, type_names: List[str]):
         reqs["ctr"] = ctr_of_req - first_ctr[pod_of_req]
         for r in range(batch.n_reqs):
             an = batch.annos[int(pod_of_req[r])]
-            key = (batch.req_type[r], an.get(ANNO_USE), an.get(ANNO_NOUSE))
+            key = (batch.req_type[r], an.get(ANNO_USE), an.get(ANNO_NOUSE), an.get(ANNO_DCU_USE), an.get(ANNO_DCU_NOUSE))
             m = cache.get(key)
             if m is None:
                 m = host_typemask(batch.req_type[r], an, type_names)

@@ -60,6 +60,28 @@ bool gpu_type_allowed(const char *use, const char *nouse, const std::string &car
     return true;
 }
 
+// strconv.Atoi with the error ignored, as util.DecodeNodeDevices does (`count, _ := ...`):
+// a syntax error yields 0, a range error the clamped int64; then Go converts with int32(x).
+int32_t atoi_go_i32(const std::string &t) {
+    size_t i = 0;
+    bool neg = false;
+    if (i < t.size() && (t[i] == '+' || t[i] == '-')) neg = t[i++] == '-';
+    if (i >= t.size()) return 0;
+    unsigned long long acc = 0;
+    bool over = false;
+    for (; i < t.size(); i++) {
+        if (t[i] < '0' || t[i] > '9') return 0;
+        if (acc > (0xffffffffffffffffull - 9) / 10) over = true;
+        if (!over) acc = acc * 10 + (unsigned long long)(t[i] - '0');
+    }
+    long long v;
+    if (over || acc > (neg ? 0x8000000000000000ull : 0x7fffffffffffffffull))
+        v = neg ? (long long)0x8000000000000000ull : 0x7fffffffffffffffll;
+    else
+        v = neg ? -(long long)acc : (long long)acc;
+    return (int32_t)(uint32_t)(unsigned long long)v;
+}
+
 } // namespace
 
 extern "C" {
@@ -74,9 +96,12 @@ uint64_t vgs_host_typemask(const char *req_type, const char *use_gputype, const 
         if (!types[t]) continue;
         const std::string card(types[t]);
         if (!contains(card, rt)) continue; // score.go:73  d.Type must contain the request type
-        // vendor lookup (score.go:76-81): only the NVIDIA policy is implemented; any other
-        // request type is "Unrecognized device" -> no device passes.
-        if (rt != "NVIDIA") continue;
+        // vendor lookup (score.go:76-81).  NVIDIA (nvidia/device.go:107-112) and Hygon DCU
+        // (hygon/device.go:79-84) share the same use/nouse list logic -- the caller passes the
+        // vendor's own annotation values (nvidia.com/{use,nouse}-gputype or
+        // hygon.com/{use,nouse}-dcutype).  Cambricon's CheckType depends on d.Used and
+        // n.Memreq, so it cannot be a static mask; any other type is "Unrecognized device".
+        if (rt != "NVIDIA" && rt != "DCU") continue;
         if (gpu_type_allowed(use_gputype, nouse_gputype, card)) mask |= 1ull << t;
     }
     return mask;
@@ -90,6 +115,44 @@ int32_t vgs_host_numa_bind(const char *v) {
     for (const char *y : yes)
         if (s == y) return 1;
     return 0;
+}
+
+int32_t vgs_host_decode_node_devices(const char *str, int32_t max_dev, int32_t *count, int32_t *devmem,
+                                     int32_t *devcore, int32_t *numa, int32_t *health, int32_t *id_off,
+                                     int32_t *id_len, int32_t *type_off, int32_t *type_len) {
+    if (!str || max_dev < 0) return VGS_EINVAL;
+    const std::string s(str);
+    if (s.find(':') == std::string::npos) return VGS_EINVAL; // util.go:69-71
+    int32_t n = 0;
+    size_t start = 0;
+    for (;;) { // strings.Split(str, ":")
+        size_t colon = s.find(':', start);
+        const size_t end = colon == std::string::npos ? s.size() : colon;
+        const std::string val = s.substr(start, end - start);
+        if (val.find(',') != std::string::npos) { // :75
+            std::vector<size_t> cut; // item boundaries inside val
+            cut.push_back(0);
+            for (size_t i = 0; i < val.size(); i++)
+                if (val[i] == ',') cut.push_back(i + 1);
+            if (cut.size() != 7) return VGS_EINVAL; // :77, :93-95
+            auto item = [&](int k) {
+                const size_t b = cut[k], e = k + 1 < 7 ? cut[k + 1] - 1 : val.size();
+                return val.substr(b, e - b);
+            };
+            if (n >= max_dev) return VGS_ETOOBIG;
+            count[n] = atoi_go_i32(item(1));
+            devmem[n] = atoi_go_i32(item(2));
+            devcore[n] = atoi_go_i32(item(3));
+            numa[n] = atoi_go_i32(item(5));
+            health[n] = vgs_host_numa_bind(item(6).c_str()); // strconv.ParseBool, error -> false
+            id_off[n] = (int32_t)(start + cut[0]), id_len[n] = (int32_t)item(0).size();
+            type_off[n] = (int32_t)(start + cut[4]), type_len[n] = (int32_t)item(4).size();
+            n++;
+        }
+        if (colon == std::string::npos) break;
+        start = colon + 1;
+    }
+    return n;
 }
 
 int32_t vgs_host_encode_pod_devices(int32_t n_ctrs, const int32_t *picks_per_ctr, const char *const *uuids,

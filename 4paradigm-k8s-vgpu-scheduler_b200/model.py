@@ -20,6 +20,8 @@ MEMPCT_UNSET = 101  # pkg/device/nvidia/device.go:136
 ANNO_USE = "nvidia.com/use-gputype"  # nvidia/device.go:20
 ANNO_NOUSE = "nvidia.com/nouse-gputype"  # :21
 ANNO_NUMA = "nvidia.com/numa-bind"  # :22
+ANNO_DCU_USE = "hygon.com/use-dcutype"  # pkg/device/hygon/device.go:20
+ANNO_DCU_NOUSE = "hygon.com/nouse-dcutype"  # :21
 
 
 @dataclass

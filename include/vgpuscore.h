@@ -248,12 +248,23 @@ int vgs_last_timing(vgs_ctx *ctx, vgs_timing *out);
 
 /* ---- host-side policy helpers (what the Go shim keeps in Go) ----------------
  * bit t = checkType pass for device type string types[t] under the pod's
- * annotations; NULL annotation = key absent.  Mirrors score.go:71-84 with the
- * NVIDIA vendor (nvidia/device.go:62-94,107-112). */
+ * annotations; NULL annotation = key absent.  Mirrors score.go:71-84 for the
+ * NVIDIA vendor (nvidia/device.go:62-94,107-112; pass nvidia.com/use-gputype /
+ * nouse-gputype) and the Hygon vendor (hygon/device.go:45-84; req_type "DCU",
+ * pass hygon.com/use-dcutype / nouse-dcutype).  Other request types: mask 0. */
 uint64_t vgs_host_typemask(const char *req_type, const char *use_gputype,
                            const char *nouse_gputype, const char *const *types, int32_t n_types);
 /* nvidia/device.go:96-105 assertNuma */
 int32_t vgs_host_numa_bind(const char *numa_bind_anno);
+/* util.DecodeNodeDevices (pkg/util/util.go:68-99): the node registration
+ * annotation "id,count,devmem,devcore,type,numa,health:" per device, decoded
+ * straight into the columns the snapshot planes are filled from.  Id and Type
+ * come back as (offset, length) into str.  Returns the device count,
+ * VGS_EINVAL for what the reference rejects (no ':' at all, or an entry that
+ * does not have exactly 7 fields), VGS_ETOOBIG beyond max_dev. */
+int32_t vgs_host_decode_node_devices(const char *str, int32_t max_dev, int32_t *count, int32_t *devmem,
+                                     int32_t *devcore, int32_t *numa, int32_t *health, int32_t *id_off,
+                                     int32_t *id_len, int32_t *type_off, int32_t *type_len);
 /* util.EncodePodDevices (pkg/util/util.go:110-126): "UUID,Type,mem,cores:" per
  * pick, ';' between containers.  Returns length or VGS_ETOOBIG. */
 int32_t vgs_host_encode_pod_devices(int32_t n_ctrs, const int32_t *picks_per_ctr,

@@ -27,7 +27,8 @@ PICK_DTYPE = np.dtype([("slot", "<i4"), ("usedmem", "<i4"), ("usedcores", "<i4")
 
 
 class _Annos(C.Structure):
-    _fields_ = [("use", C.c_char_p), ("nouse", C.c_char_p), ("numa", C.c_char_p)]
+    _fields_ = [("use", C.c_char_p), ("nouse", C.c_char_p), ("numa", C.c_char_p), ("dcu_use", C.c_char_p),
+                ("dcu_nouse", C.c_char_p)]
 
 
 class _Snap(C.Structure):
@@ -91,7 +92,8 @@ def _snap_struct(snap):
 
 
 def _annos_struct(an):
-    return _Annos(_b(an.get(ANNO_USE)), _b(an.get(ANNO_NOUSE)), _b(an.get(ANNO_NUMA)))
+    return _Annos(_b(an.get(ANNO_USE)), _b(an.get(ANNO_NOUSE)), _b(an.get(ANNO_NUMA)),
+                  _b(an.get("hygon.com/use-dcutype")), _b(an.get("hygon.com/nouse-dcutype")))
 
 
 def typemask(annos: dict, req_type: str, type_names) -> tuple:
@@ -160,7 +162,8 @@ def score_packed(snap, batch, full: bool = False, threads: Optional[int] = None)
     ctr_of_req = np.repeat(np.arange(len(batch.req_begin) - 1), np.diff(batch.req_begin))
     for r in range(R):
         a = batch.annos[int(pod_of_ctr[ctr_of_req[r]])]
-        key = (batch.req_type[r], a.get(ANNO_USE), a.get(ANNO_NOUSE), a.get(ANNO_NUMA))
+        key = (batch.req_type[r], a.get(ANNO_USE), a.get(ANNO_NOUSE), a.get(ANNO_NUMA),
+               a.get("hygon.com/use-dcutype"), a.get("hygon.com/nouse-dcutype"))
         if key not in cache:
             cache[key] = typemask(a, batch.req_type[r], snap.type_names)
         masks[r], numa[r] = cache[key]

@@ -128,10 +128,18 @@ int ref_assertNuma(const ref_Annos *annos) {
     return 0;
 }
 
-/* pkg/scheduler/score.go:71-84 checkType, with device.GetDevices() restricted
- * to the NVIDIA vendor (nvidia/device.go:107-112).  The Cambricon and Hygon
- * vendors answer found=false for req.Type "NVIDIA"; any other request type is
- * "Unrecognized device" here (out of scope). */
+/* pkg/device/hygon/device.go:45-77 checkDCUtype: the same list logic on the
+ * hygon.com/{use,nouse}-dcutype annotations */
+static int ref_checkDCUtype(const ref_Annos *annos, const char *cardtype) {
+    if (annos->use_dcutype) return any_token_matches(annos->use_dcutype, cardtype) ? 1 : 0;
+    if (annos->nouse_dcutype) return any_token_matches(annos->nouse_dcutype, cardtype) ? 0 : 1;
+    return 1;
+}
+
+/* pkg/scheduler/score.go:71-84 checkType over device.GetDevices(): NVIDIA
+ * (nvidia/device.go:107-112) and Hygon (hygon/device.go:79-84).  Cambricon
+ * (cambricon/device.go:93-104, depends on d.Used / n.Memreq) is not restated:
+ * a request type neither vendor claims is "Unrecognized device". */
 int ref_checkType(const ref_Annos *annos, const ref_DeviceUsage *d,
                   const ref_ContainerDeviceRequest *n, int *numa) {
     *numa = 0;
@@ -140,6 +148,7 @@ int ref_checkType(const ref_Annos *annos, const ref_DeviceUsage *d,
         *numa = ref_assertNuma(annos);
         return ref_checkGPUtype(annos, d->Type);
     }
+    if (strcmp(n->Type, "DCU") == 0) return ref_checkDCUtype(annos, d->Type); /* hygon: numaAssert false */
     return 0; /* :82-83 */
 }
 

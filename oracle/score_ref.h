@@ -66,6 +66,9 @@ typedef struct {
     const char *use_gputype;
     const char *nouse_gputype;
     const char *numa_bind;
+    /* Hygon vendor (pkg/device/hygon/device.go:20-21) */
+    const char *use_dcutype;
+    const char *nouse_dcutype;
 } ref_Annos;
 
 /* One result record per pod / per pick: same shape the product's C ABI uses

@@ -79,3 +79,26 @@ def test_pack_batch_layout(built):
         assert ctr[0] == 0 and (np.diff(ctr) >= 0).all()
     numa = np.array([1 if a else 0 for a in batch.annos])
     assert numa.sum() > 0
+
+
+def test_decode_node_devices(built):
+    """util.DecodeNodeDevices (util.go:68-99) on strings in util.EncodeNodeDevices' format (:101-108)"""
+    anno = "GPU-aa,10,32768,100,NVIDIA-Tesla V100-PCIE-32GB,0,true:GPU-bb,4,16160,100,NVIDIA-Tesla T4,1,false:"
+    devs = v.capi.decode_node_devices(anno)
+    assert devs == [
+        dict(ID="GPU-aa", Count=10, Devmem=32768, Devcore=100, Type="NVIDIA-Tesla V100-PCIE-32GB", Numa=0, Health=True),
+        dict(ID="GPU-bb", Count=4, Devmem=16160, Devcore=100, Type="NVIDIA-Tesla T4", Numa=1, Health=False)]
+    # Atoi errors are ignored by the reference (-> 0); entries without ',' are skipped
+    devs = v.capi.decode_node_devices("x,abc,-5,+7,T,,maybe::junk:")
+    assert devs == [dict(ID="x", Count=0, Devmem=-5, Devcore=7, Type="T", Numa=0, Health=False)]
+    for bad in ("no separators", "a,b,c:", "a,1,2,3,T,0,true,extra:"):
+        try:
+            v.capi.decode_node_devices(bad)
+        except v.VgsError as e:
+            assert e.code == v.capi.VGS_EINVAL
+        else:
+            raise AssertionError(bad)
+    # decoded columns are exactly what the snapshot packer consumes
+    snap = v.Snapshot.from_nodes([[dict(Count=d["Count"], Totalmem=d["Devmem"], Totalcore=d["Devcore"], Type=d["Type"],
+                                        Numa=d["Numa"]) for d in v.capi.decode_node_devices(anno)]])
+    assert snap.planes[:, 0, 1].tolist() == [0, 4, 0, 16160, 0, 100, 1, 1]

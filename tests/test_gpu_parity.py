@@ -321,3 +321,36 @@ def test_sliced_falls_back_when_preconditions_fail(built, monkeypatch):
         b = ctx.score(batch)
     assert_same(a, oracle.score_packed(wrapped, batch, full=True), "ctx bigmem")
     assert_same(b, oracle.score_packed(snap, batch, full=True), "ctx normal")
+
+
+def test_mixed_vendor_cluster_nvidia_and_hygon(built):
+    """NVIDIA and Hygon DCU devices in one snapshot: a DCU request only sees
+    DCU cards and honours hygon.com/use-dcutype / nouse-dcutype; numa-bind is an NVIDIA-only notion"""
+    rng = np.random.default_rng(8)
+    nodes = []
+    for i in range(600):
+        t = ["NVIDIA-Tesla V100", "DCU-Z100", "DCU-Z100L", "NVIDIA-NVIDIA A100"][i % 4]
+        nodes.append([dict(Used=int(rng.integers(0, 4)), Count=4, Usedmem=int(rng.integers(0, 8000)), Totalmem=16384,
+                           Usedcores=int(rng.choice([0, 30, 60])), Totalcore=100, Numa=s // 4, Type=t) for s in range(8)])
+    snap = v.Snapshot.from_nodes(nodes)
+    pods = []
+    for i in range(120):
+        typ = "DCU" if i % 2 else "NVIDIA"
+        annos = {}
+        if i % 3 == 0:
+            annos["hygon.com/use-dcutype"] = "z100l"
+        if i % 5 == 0:
+            annos["hygon.com/nouse-dcutype"] = "Z100L"
+        if i % 7 == 0:
+            annos["nvidia.com/use-gputype"] = "a100"
+        if i % 4 == 0:
+            annos["nvidia.com/numa-bind"] = "true"
+        pods.append({"containers": [[(int(rng.choice([1, 2])), int(rng.choice([0, 2000])), 101, 10, typ)]], "annos": annos})
+    batch = v.PodBatch.from_pods(pods)
+    got = gpu_score(snap, batch)
+    assert_same(got, oracle.score_faithful(snap, batch, full=True), "hygon R1")
+    assert_same(got, oracle.score_packed(snap, batch, full=True), "hygon R2")
+    # a DCU pod never lands on an NVIDIA node
+    for p in range(batch.n_pods):
+        if got.best_row[p] >= 0:
+            assert ("DCU" in nodes[got.best_row[p]][0]["Type"]) == (batch.req_type[p] == "DCU")
