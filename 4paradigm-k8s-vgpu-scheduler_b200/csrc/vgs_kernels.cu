@@ -746,8 +746,9 @@ __host__ __device__ inline SliceSmem slice_smem(int T, int nums, int tab_rows) {
 template <int NUMS, bool TABSMEM, bool VERIFY>
 __global__ void __launch_bounds__(128)
     k1_score_sliced(int32_t n_tiles, int32_t n_nodes, int32_t row_base, SliceTab tb, int32_t n_types,
-                    int32_t tiles_per_cta, unsigned long long *__restrict__ keys, int32_t *__restrict__ counts,
-                    uint32_t *__restrict__ vfit, float *__restrict__ vscore, int32_t vwords) {
+                    int32_t tiles_per_cta, int32_t phase, unsigned long long *__restrict__ keys,
+                    int32_t *__restrict__ counts, uint32_t *__restrict__ vfit, float *__restrict__ vscore,
+                    int32_t vwords) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int T = blockDim.x, tid = threadIdx.x;
     // table rows, global numbering: [type 0..63][mem 0..km][pct 0..kp][cores x flags: 4 * (kc + 1)]
@@ -771,12 +772,27 @@ __global__ void __launch_bounds__(128)
     const int wc = min(w, tb.Wp - 1); // clamped column: inactive threads compute garbage, never publish
     const uint32_t stride = TABSMEM ? (uint32_t)T : (uint32_t)tb.Wp;
     const uint32_t col = TABSMEM ? (uint32_t)tid : (uint32_t)wc;
-    const int t_hi = n_tiles - (int)blockIdx.x * tiles_per_cta;
+    // Two launches per class.  phase 0 ("scouts") walks every kScout-th tile with cold pruning
+    // state and publishes its bests; phase 1 walks all the other tiles and starts from those
+    // published bests, so that its detection words are almost always zero from the first node.
+    // phase -1 = single launch over all tiles (small snapshots).  v = virtual tile index.
+    constexpr int kScout = 8;
+    auto tile_of = [&](int v) -> int {
+        if (phase < 0) return v;
+        if (phase == 0) return v * kScout;
+        return (v / (kScout - 1)) * kScout + (v % (kScout - 1)) + 1;
+    };
+    const int n_virtual = phase < 0 ? n_tiles
+                          : phase == 0 ? (n_tiles + kScout - 1) / kScout
+                                       : n_tiles - (n_tiles + kScout - 1) / kScout;
+    const int t_hi = n_virtual - (int)blockIdx.x * tiles_per_cta;
     const int t_lo = max(0, t_hi - tiles_per_cta);
     if (t_hi <= 0) return;
     const int n_my = t_hi - t_lo;
-    const int node_lo = t_lo * kWarp;
+    const int node_lo = tile_of(t_lo) * kWarp;
+    const int node_hi = (tile_of(t_hi - 1) + 1) * kWarp;
     constexpr uint32_t kTx = kDevTileBytes + (NUMS == 2 ? kPclsTileBytes : 0);
+    constexpr uint16_t kNotMine = 0xffffu; // s_row of a pod whose best was inherited, not found here
 
     auto fetch = [&](int tile, int buf) { // one thread: stage the records of 32 nodes
         mbar_expect_tx(&bar[buf], kTx);
@@ -786,12 +802,13 @@ __global__ void __launch_bounds__(128)
             bulk_g2s(ptilebuf + buf * kPclsTileBytes, tb.pcls + (size_t)tile * kPclsTileBytes, kPclsTileBytes, &bar[buf]);
     };
 
+    for (int k = tid; k <= kDict; k += T) vals[k] = __ldg(&tb.gvals[k]);
+    for (int k = 0; k <= kDict; k++) below[k * T + tid] = phase == 1 ? 0u : 0xffffffffu;
+    below[kDict * T + tid] = 0xffffffffu;
     for (int b = 0; b < 32; b++) {
         s_best[b * T + tid] = 0u;
-        s_row[b * T + tid] = 0;
+        s_row[b * T + tid] = kNotMine;
     }
-    for (int k = 0; k <= kDict; k++) below[k * T + tid] = 0xffffffffu;
-    for (int k = tid; k <= kDict; k += T) vals[k] = __ldg(&tb.gvals[k]);
     if (TABSMEM) {
         uint32_t *tw = reinterpret_cast<uint32_t *>(smem_raw + L.tab);
         for (int r = 0; r < rows_g - drop; r++) {
@@ -805,8 +822,31 @@ __global__ void __launch_bounds__(128)
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
-    if (tid == 0) fetch(t_hi - 1, 0);
+    if (tid == 0) fetch(tile_of(t_hi - 1), 0);
     const int nv = (int)vals[kDict];
+    if (phase == 1) {
+        // inherit the scouts' bests.  A holder above all my rows can only be beaten by a strictly
+        // larger score; one below some of my rows also by an equal score, so its score is
+        // inherited one ulp lower (a local tie on a lower row is harmless: keys only grow).
+        for (int b = 0; b < 32; b++) {
+            const int i = w * 32 + b;
+            uint32_t init = 0u;
+            if (active && i < tb.n_pods) {
+                const unsigned long long key = keys[__ldg(&tb.orig[i])];
+                if (key) {
+                    const uint32_t gs = (uint32_t)(key >> 32) ^ 0x80000000u; // positive scores
+                    const int grow = (int)(uint32_t)key - row_base;
+                    init = grow >= node_hi ? gs : gs - 1u;
+                }
+            }
+            s_best[b * T + tid] = init;
+            int c = 0; // classes with vals[k] <= init
+            for (int step = 32; step > 0; step >>= 1)
+                if (c + step <= nv && vals[c + step - 1] <= init) c += step;
+            if (c < nv) below[c * T + tid] |= 1u << b; // the pod is under every class from c upward
+        }
+        for (int k = 1; k < nv; k++) below[k * T + tid] |= below[(k - 1) * T + tid];
+    }
 
     auto TAB = [&](uint32_t row) -> uint32_t {
         if (TABSMEM) return tabs[(row >= (uint32_t)VGS_MAX_TYPES ? row - (uint32_t)drop : row) * stride + col];
@@ -841,8 +881,8 @@ __global__ void __launch_bounds__(128)
     for (int k = 0; k < kSliceCountPlanes; k++) cnt[k] = 0u;
 
     for (int it = 0; it < n_my; it++) {
-        const int tile = t_hi - 1 - it, buf = it & 1;
-        if (tid == 0 && it + 1 < n_my) fetch(tile - 1, buf ^ 1); // that buffer was released by the last sync
+        const int tile = tile_of(t_hi - 1 - it), buf = it & 1;
+        if (tid == 0 && it + 1 < n_my) fetch(tile_of(t_hi - 2 - it), buf ^ 1); // released by the last sync
         mbar_wait(&bar[buf], (uint32_t)((it >> 1) & 1));
         const uint4 *dv = reinterpret_cast<const uint4 *>(tilebuf + buf * kDevTileBytes); // [32 nodes][8]
         const uint8_t *pc = ptilebuf + buf * kPclsTileBytes;                              // [32 nodes][32]
@@ -965,17 +1005,18 @@ __global__ void __launch_bounds__(128)
     for (int b = 0; b < 32; b++) {
         const int i = w * 32 + b;
         if (i >= tb.n_pods) break;
-        const uint32_t sb = s_best[b * T + tid];
-        if (sb == 0u) continue;
         int32_t c = (int32_t)((ones >> b) & 1u) | ((int32_t)((twos >> b) & 1u) << 1);
 #pragma unroll
         for (int k = 2; k < kSliceCountPlanes; k++) c |= (int32_t)((cnt[k] >> b) & 1u) << k;
+        if (c == 0) continue; // none of my nodes fits this pod
         const int p = __ldg(&tb.orig[i]);
-        // scores of single-request pods are positive: ordered bits = bits | sign bit
-        const unsigned long long key = ((unsigned long long)(sb | 0x80000000u) << 32) |
-                                       (unsigned long long)(uint32_t)(row_base + node_lo + (int)s_row[b * T + tid]);
-        atomicMax(&keys[p], key);
         atomicAdd(&counts[p], c);
+        const uint16_t r = s_row[b * T + tid];
+        if (r == kNotMine) continue; // nothing here beat the inherited best
+        // scores of single-request pods are positive: ordered bits = bits | sign bit
+        const unsigned long long key = ((unsigned long long)(s_best[b * T + tid] | 0x80000000u) << 32) |
+                                       (unsigned long long)(uint32_t)(row_base + node_lo + (int)r);
+        atomicMax(&keys[p], key);
     }
 }
 
@@ -1305,18 +1346,25 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
         int occ = 1;
         if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, T, smem)) != cudaSuccess) return e;
         if (occ < 1) occ = 1;
-        // one wave of CTAs; at least 2 tiles each so the per-CTA set-up and flush stay small, at
-        // most (2^planes - 1) nodes each so the bit-sliced counter cannot overflow
-        long long want = (long long)sms * occ / gy;
-        if (want < 1) want = 1;
-        int tiles_per = (int)((a.n_tiles + want - 1) / want);
-        if (tiles_per < 2) tiles_per = 2;
-        const int cap = ((1 << kSliceCountPlanes) - 1) / kWarp;
-        if (tiles_per > cap) tiles_per = cap;
-        const int gx = (a.n_tiles + tiles_per - 1) / tiles_per;
-        kernel<<<dim3(gx, gy), T, smem, st>>>(a.n_tiles, a.n_nodes, a.row_base, tb, n_types, tiles_per, a.keys,
-                                              a.counts, a.vfit, a.vscore, a.vwords);
-        return cudaGetLastError();
+        // CTAs of one launch: one wave; at least 2 tiles each so the per-CTA set-up and flush stay
+        // small, at most (2^planes - 1) nodes (and a 16-bit row span) each
+        auto launch = [&](int n_virtual, int phase, int min_tiles) -> cudaError_t {
+            if (n_virtual <= 0) return cudaSuccess;
+            long long want = (long long)sms * occ / gy;
+            if (want < 1) want = 1;
+            int tiles_per = (int)((n_virtual + want - 1) / want);
+            if (tiles_per < min_tiles) tiles_per = min_tiles;
+            const int cap = ((1 << kSliceCountPlanes) - 1) / kWarp;
+            if (tiles_per > cap) tiles_per = cap;
+            const int gx = (n_virtual + tiles_per - 1) / tiles_per;
+            kernel<<<dim3(gx, gy), T, smem, st>>>(a.n_tiles, a.n_nodes, a.row_base, tb, n_types, tiles_per, phase,
+                                                  a.keys, a.counts, a.vfit, a.vscore, a.vwords);
+            return cudaGetLastError();
+        };
+        if (a.n_tiles < 64 * 8) return launch(a.n_tiles, -1, 2); // small snapshot: one launch
+        const int scouts = (a.n_tiles + 7) / 8;
+        if ((e = launch(scouts, 0, 1)) != cudaSuccess) return e;
+        return launch(a.n_tiles - scouts, 1, 2);
     };
     if (a.vfit) return tabsmem ? go(k1_score_sliced<NUMS, true, true>) : go(k1_score_sliced<NUMS, false, true>);
     return tabsmem ? go(k1_score_sliced<NUMS, true, false>) : go(k1_score_sliced<NUMS, false, false>);

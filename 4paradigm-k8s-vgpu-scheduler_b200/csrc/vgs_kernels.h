@@ -38,10 +38,10 @@ cudaError_t launch_score_single(int dm, bool nums1, int dev, const ScoreArgs &a,
 cudaError_t launch_score_general(int dm, int dev, const ScoreArgs &a, const DevReq *reqs,
                                  const GenPod *pods, int32_t n_pods, cudaStream_t st);
 // pod-sliced K1 for one class (all pods: one request, Nums == nums in {1,2}, walk DM == 8)
-// (4 launches: K1p collect / sort / classify, then the score kernel)
+// (up to 5 launches: K1p collect / sort / classify, then the score kernel: scouts + main pass)
 cudaError_t launch_score_sliced(int nums, int dev, const ScoreArgs &a, const SliceTab &tb, int n_types,
                                 uint32_t *status, cudaStream_t st);
-constexpr int kSlicedLaunches = 4;
+constexpr int kSlicedLaunches = 5;
 cudaError_t launch_merge(const unsigned long long *gk, const int32_t *gc, int32_t n_shards,
                          int32_t stride, int32_t n_pods, unsigned long long *keys, int32_t *counts,
                          cudaStream_t st);
