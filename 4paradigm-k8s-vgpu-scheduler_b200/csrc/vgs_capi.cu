@@ -73,6 +73,7 @@ struct vgs_ctx {
     int32_t slice_min = 512;     // classes smaller than this use the per-pair kernels
     bool snap_slice_ok = false;  // snapshot satisfies the sliced kernel's preconditions
     int32_t n_types_used = VGS_MAX_TYPES; // largest type id of the snapshot + 1
+    bool zero_copy_ok = true;             // VGS_ZERO_COPY=0 disables the kernel-driven upload
     bool have_pods = false, scored = false, resolved = false;
 
     // results
@@ -293,6 +294,7 @@ int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
             c->tab[k].gvals = reinterpret_cast<uint32_t *>(c->d_prep[k] + dinfo_b + pcls_b + hset_b);
         }
         if (const char *e = getenv("VGS_SLICE_MIN")) c->slice_min = atoi(e);
+        if (const char *e = getenv("VGS_ZERO_COPY")) c->zero_copy_ok = atoi(e) != 0;
     }
     CUI(cudaMalloc(&c->d_keys, P * sizeof(unsigned long long)));
     CUI(cudaMalloc(&c->d_counts, P * sizeof(int32_t)));
@@ -336,9 +338,24 @@ static int snapshot_common(vgs_ctx *c, int32_t n_nodes, int32_t dmax,
     CU(cudaMemsetAsync(c->d_status, 0, 2 * sizeof(uint32_t), c->st));
     rec(c, EV_UP0);
     if (cells) {
-        for (int f = 0; f < VGS_NUM_PLANES; f++)
-            CU(cudaMemcpyAsync(c->d_raw[f], planes[f], cells * sizeof(int32_t), kind, c->st));
-        CU(cudaMemcpyAsync(c->d_ndev, ndev, (size_t)n_nodes * sizeof(int32_t), kind, c->st));
+        // pinned, 16-byte aligned host planes are read by a kernel straight over PCIe (faster
+        // than the copy engine for this size); anything else goes through cudaMemcpyAsync
+        bool zero_copy = kind == cudaMemcpyHostToDevice && c->zero_copy_ok;
+        for (int f = 0; f <= VGS_NUM_PLANES && zero_copy; f++) {
+            const void *p = f < VGS_NUM_PLANES ? (const void *)planes[f] : (const void *)ndev;
+            cudaPointerAttributes at;
+            if (((uintptr_t)p & 15) || cudaPointerGetAttributes(&at, p) != cudaSuccess || at.type != cudaMemoryTypeHost)
+                zero_copy = false;
+        }
+        cudaGetLastError(); // cudaPointerGetAttributes on pageable memory may leave an error behind
+        if (zero_copy) {
+            CU(launch_copy_planes(planes, ndev, c->d_raw, c->d_ndev, cells, (size_t)n_nodes, c->st));
+            c->launches++;
+        } else {
+            for (int f = 0; f < VGS_NUM_PLANES; f++)
+                CU(cudaMemcpyAsync(c->d_raw[f], planes[f], cells * sizeof(int32_t), kind, c->st));
+            CU(cudaMemcpyAsync(c->d_ndev, ndev, (size_t)n_nodes * sizeof(int32_t), kind, c->st));
+        }
     }
     rec(c, EV_UP1);
     c->n_nodes = n_nodes;

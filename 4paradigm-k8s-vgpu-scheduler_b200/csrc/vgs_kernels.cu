@@ -1196,6 +1196,47 @@ __global__ void k4_apply_delta(RawPlanesMut raw, int32_t n_nodes, int32_t dmax, 
 }
 
 // ------------------------------------------------------------------------------------
+// Host-pinned planes -> device planes, read straight over PCIe by the SMs (zero-copy).  On some
+// boxes of the pool a 26 MB cudaMemcpyAsync from pinned memory ran at only ~15 GB/s (43-51 GB/s
+// for 256 MB); many warps with 16-byte loads in flight reach ~50 GB/s at this size everywhere.
+// ------------------------------------------------------------------------------------
+struct PlaneCopy {
+    const int4 *src[VGS_NUM_PLANES + 1];
+    int4 *dst[VGS_NUM_PLANES + 1];
+    int32_t n16[VGS_NUM_PLANES + 1]; // int4 elements per plane
+    int32_t tail[VGS_NUM_PLANES + 1]; // leftover int32 elements
+};
+__global__ void __launch_bounds__(256) k_copy_planes(PlaneCopy pc) {
+    const int f = blockIdx.y;
+    const int4 *__restrict__ s = pc.src[f];
+    int4 *__restrict__ d = pc.dst[f];
+    const int n = pc.n16[f];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) d[i] = s[i];
+    if (blockIdx.x == 0 && threadIdx.x < pc.tail[f]) {
+        const int32_t *s32 = reinterpret_cast<const int32_t *>(s + n);
+        reinterpret_cast<int32_t *>(d + n)[threadIdx.x] = s32[threadIdx.x];
+    }
+}
+
+cudaError_t launch_copy_planes(const int32_t *const src[VGS_NUM_PLANES], const int32_t *src_ndev,
+                               int32_t *const dst[VGS_NUM_PLANES], int32_t *dst_ndev, size_t cells, size_t n_nodes,
+                               cudaStream_t st) {
+    PlaneCopy pc;
+    for (int f = 0; f <= VGS_NUM_PLANES; f++) {
+        const int32_t *s = f < VGS_NUM_PLANES ? src[f] : src_ndev;
+        int32_t *d = f < VGS_NUM_PLANES ? dst[f] : dst_ndev;
+        const size_t n = f < VGS_NUM_PLANES ? cells : n_nodes;
+        if (((uintptr_t)s | (uintptr_t)d) & 15) return cudaErrorMisalignedAddress;
+        pc.src[f] = reinterpret_cast<const int4 *>(s);
+        pc.dst[f] = reinterpret_cast<int4 *>(d);
+        pc.n16[f] = (int32_t)(n / 4);
+        pc.tail[f] = (int32_t)(n % 4);
+    }
+    k_copy_planes<<<dim3(148 * 2, VGS_NUM_PLANES + 1), 256, 0, st>>>(pc);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------
 // launchers
 // ------------------------------------------------------------------------------------
 static int g_sm_count[64];

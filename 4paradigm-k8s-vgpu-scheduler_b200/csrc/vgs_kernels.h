@@ -30,6 +30,10 @@ struct ScoreArgs {
 inline int walk_dm(int dmax) { return dmax <= 8 ? 8 : 12; }
 inline size_t walk_int4_per_tile(int dm) { return (size_t)kWalkWords * (dm / 4) * kWarp; }
 
+// zero-copy upload: src planes are host-pinned (device-accessible) memory, 16-byte aligned
+cudaError_t launch_copy_planes(const int32_t *const src[VGS_NUM_PLANES], const int32_t *src_ndev,
+                               int32_t *const dst[VGS_NUM_PLANES], int32_t *dst_ndev, size_t cells, size_t n_nodes,
+                               cudaStream_t st);
 cudaError_t launch_prepare(int dm, const RawPlanes &raw, int32_t n_nodes, int32_t dmax, int4 *walk,
                            int32_t n_tiles, uint32_t *status, const int32_t *rowlist,
                            int32_t n_list, cudaStream_t st);

@@ -354,3 +354,23 @@ def test_mixed_vendor_cluster_nvidia_and_hygon(built):
     for p in range(batch.n_pods):
         if got.best_row[p] >= 0:
             assert ("DCU" in nodes[got.best_row[p]][0]["Type"]) == (batch.req_type[p] == "DCU")
+
+
+def test_pinned_planes_take_the_zero_copy_upload(built, monkeypatch):
+    """pinned, aligned host planes are pulled over PCIe by a kernel; pageable ones by cudaMemcpy:
+    same resident snapshot either way"""
+    import torch
+    snap, batch = v.workload.make_config("cfg3", 3001, 64)  # odd size: exercises the int32 tail
+    pin = torch.from_numpy(snap.planes).pin_memory()
+    pnd = torch.from_numpy(snap.ndev).pin_memory()
+    with v.Context(max_nodes=3001, max_pods=64) as ctx:
+        ctx.upload_ptrs(snap.n_nodes, snap.dmax, [pin[f].data_ptr() for f in range(8)], pnd.data_ptr(), device=False)
+        ctx.type_names = snap.type_names
+        planes, ndev = ctx.download_snapshot()
+        assert np.array_equal(planes, snap.planes) and np.array_equal(ndev, snap.ndev)
+        assert_same(ctx.score(batch), oracle.score_packed(snap, batch), "pinned upload")
+    monkeypatch.setenv("VGS_ZERO_COPY", "0")
+    with v.Context(max_nodes=3001, max_pods=64) as ctx:
+        ctx.upload_ptrs(snap.n_nodes, snap.dmax, [pin[f].data_ptr() for f in range(8)], pnd.data_ptr(), device=False)
+        planes, _ = ctx.download_snapshot()
+        assert np.array_equal(planes, snap.planes)
