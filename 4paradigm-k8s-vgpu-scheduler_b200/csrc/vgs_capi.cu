@@ -264,16 +264,11 @@ int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
     // pod staging block: [reqs][pods][pick_begin][reqsA][origA][reqsB][origB][podsG]
     const size_t P = cfg->max_pods, R = cfg->max_reqs;
     size_t o = 0;
-    c->off_reqs = o, o = align_up(o + R * sizeof(DevReq), 256);
-    c->off_pods = o, o = align_up(o + P * sizeof(vgs_pod), 256);
-    c->off_pick = o, o = align_up(o + (R + 1) * sizeof(int32_t), 256);
-    c->off_reqsA = o, o = align_up(o + P * sizeof(DevReq), 256);
-    c->off_origA = o, o = align_up(o + P * sizeof(int32_t), 256);
-    c->off_reqsB = o, o = align_up(o + P * sizeof(DevReq), 256);
-    c->off_origB = o, o = align_up(o + P * sizeof(int32_t), 256);
-    c->off_podsG = o, o = align_up(o + P * sizeof(GenPod), 256);
-    c->off_reqsC = o, o = align_up(o + P * sizeof(DevReq), 256);
-    c->off_origC = o, o = align_up(o + P * sizeof(int32_t), 256);
+    // worst-case size of the staging block; the offsets inside it are laid out per batch
+    // (stage_layout) so that one batch is ONE host-to-device copy of its used prefix
+    o = align_up(R * sizeof(DevReq), 256) + align_up(P * sizeof(vgs_pod), 256) +
+        align_up((R + 1) * sizeof(int32_t), 256) + 3 * align_up(P * sizeof(DevReq), 256) +
+        3 * align_up(P * sizeof(int32_t), 256) + align_up(P * sizeof(GenPod), 256);
     c->stage_bytes = o;
     CUI(cudaMalloc(&c->d_stage, o));
     CUI(cudaMallocHost(&c->h_stage, o));
@@ -451,6 +446,22 @@ int vgs_snapshot_download(vgs_ctx *c, int32_t *const planes[VGS_NUM_PLANES], int
 
 // ---- pod batch ---------------------------------------------------------------------
 
+// lay the staging block out for a batch of n_pods / n_reqs; returns the bytes in use
+static size_t stage_layout(vgs_ctx *c, size_t P, size_t R) {
+    size_t o = 0;
+    c->off_reqs = o, o = align_up(o + R * sizeof(DevReq), 256);
+    c->off_pods = o, o = align_up(o + P * sizeof(vgs_pod), 256);
+    c->off_pick = o, o = align_up(o + (R + 1) * sizeof(int32_t), 256);
+    c->off_reqsA = o, o = align_up(o + P * sizeof(DevReq), 256);
+    c->off_origA = o, o = align_up(o + P * sizeof(int32_t), 256);
+    c->off_reqsB = o, o = align_up(o + P * sizeof(DevReq), 256);
+    c->off_origB = o, o = align_up(o + P * sizeof(int32_t), 256);
+    c->off_podsG = o, o = align_up(o + P * sizeof(GenPod), 256);
+    c->off_reqsC = o, o = align_up(o + P * sizeof(DevReq), 256);
+    c->off_origC = o, o = align_up(o + P * sizeof(int32_t), 256);
+    return o;
+}
+
 // Build the bit tables of one pod-sliced class (see SliceTab) into pinned staging and queue the
 // upload.  Returns false when the class does not qualify (then the per-pair kernel runs).
 static bool build_slice_class(vgs_ctx *c, int k, const DevReq *req, const int32_t *orig, int32_t n,
@@ -458,25 +469,22 @@ static bool build_slice_class(vgs_ctx *c, int k, const DevReq *req, const int32_
     *err = cudaSuccess;
     c->slice_on[k] = false;
     if (n < c->slice_min || n < 1) return false;
-    std::vector<int32_t> mv, pv, cv;
-    mv.reserve(n), cv.reserve(n);
+    std::vector<int32_t> mv, pv, cv; // sorted distinct thresholds (few in practice)
+    auto add = [](std::vector<int32_t> &v, int32_t x) {
+        auto it = std::lower_bound(v.begin(), v.end(), x);
+        if (it == v.end() || *it != x) v.insert(it, x);
+    };
     for (int32_t i = 0; i < n; i++) {
         const DevReq &d = req[i];
         if (d.flags & R_USEPCT) {
             if (d.pct < 0 || d.pct > 100) return false; // monotone in pct only on [0,100]
-            pv.push_back(d.pct);
+            add(pv, d.pct);
         } else {
-            mv.push_back(d.memfix);
+            add(mv, d.memfix);
         }
-        cv.push_back(d.coresreq);
+        add(cv, d.coresreq);
+        if ((int)mv.size() > kSliceMaxDistinct || (int)cv.size() > kSliceMaxDistinct) return false;
     }
-    auto uniq = [](std::vector<int32_t> &v) {
-        std::sort(v.begin(), v.end());
-        v.erase(std::unique(v.begin(), v.end()), v.end());
-    };
-    uniq(mv), uniq(pv), uniq(cv);
-    if ((int)mv.size() > kSliceMaxDistinct || (int)cv.size() > kSliceMaxDistinct || (int)pv.size() > kSliceMaxPct)
-        return false;
     const int32_t km = (int32_t)mv.size(), kp = (int32_t)pv.size(), kc = (int32_t)cv.size();
     const int32_t W = (n + 31) / 32, Wp = (int32_t)align_up((size_t)W, 32);
     uint32_t *h = c->h_slice[k];
@@ -547,6 +555,7 @@ static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, i
     c->scored = c->resolved = false;
     // the staging block may still be the source of an earlier async copy
     CU(cudaStreamSynchronize(c->st));
+    const size_t stage_used = stage_layout(c, (size_t)n_pods, (size_t)n_reqs);
     DevReq *hreq = reinterpret_cast<DevReq *>(c->h_stage + c->off_reqs);
     vgs_pod *hpod = reinterpret_cast<vgs_pod *>(c->h_stage + c->off_pods);
     int32_t *hpick = reinterpret_cast<int32_t *>(c->h_stage + c->off_pick);
@@ -638,20 +647,7 @@ static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, i
     c->nG = nG;
     c->n_picks = (int32_t)picks;
     rec(c, EV_PH0);
-    auto up = [&](size_t off, size_t bytes) -> cudaError_t {
-        if (!bytes) return cudaSuccess;
-        return cudaMemcpyAsync(c->d_stage + off, c->h_stage + off, bytes, cudaMemcpyHostToDevice, c->st);
-    };
-    CU(up(c->off_reqs, (size_t)n_reqs * sizeof(DevReq)));
-    CU(up(c->off_pods, (size_t)n_pods * sizeof(vgs_pod)));
-    CU(up(c->off_pick, (size_t)(n_reqs + 1) * sizeof(int32_t)));
-    CU(up(c->off_reqsA, (size_t)nA * sizeof(DevReq)));
-    CU(up(c->off_origA, (size_t)nA * sizeof(int32_t)));
-    CU(up(c->off_reqsB, (size_t)nB * sizeof(DevReq)));
-    CU(up(c->off_origB, (size_t)nB * sizeof(int32_t)));
-    CU(up(c->off_podsG, (size_t)nG * sizeof(GenPod)));
-    CU(up(c->off_reqsC, (size_t)nC * sizeof(DevReq)));
-    CU(up(c->off_origC, (size_t)nC * sizeof(int32_t)));
+    if (stage_used) CU(cudaMemcpyAsync(c->d_stage, c->h_stage, stage_used, cudaMemcpyHostToDevice, c->st));
     {
         cudaError_t e;
         build_slice_class(c, 0, hA, hoA, nA, &e);
