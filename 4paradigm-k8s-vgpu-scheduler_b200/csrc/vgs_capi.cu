@@ -278,19 +278,11 @@ int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
         const size_t rows = VGS_MAX_TYPES + 5 * (kSliceMaxDistinct + 1) + (kSliceMaxPct + 1);
         c->slice_words = rows * wp + 2 * kSliceMaxDistinct + kSliceMaxPct + P + 64;
         const size_t dinfo_b = max_tiles * 32 * 8 * sizeof(SliceDev), pcls_b = max_tiles * 32 * 32;
-        const size_t hset_b = kSliceHash * sizeof(uint32_t), gvals_b = align_up((kSliceDict + 4) * sizeof(uint32_t), 256);
-        int sms = 148;
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, cfg->device);
-        // result slabs of the sliced kernel: one per CTA, never more CTAs than can be resident
-        const size_t gy_max = (wp + 127) / 128;
-        const size_t best_ctas = std::min<size_t>((size_t)sms * 32, std::max<size_t>(max_tiles, 1) * gy_max);
-        const size_t best_b = best_ctas * 32 * 128 * (sizeof(uint32_t) + sizeof(uint16_t));
+        const size_t hset_b = kSliceHash * sizeof(uint32_t), gvals_b = (kSliceDict + 4) * sizeof(uint32_t);
         for (int k = 0; k < 2; k++) {
             CUI(cudaMalloc(&c->d_slice[k], c->slice_words * sizeof(uint32_t)));
             CUI(cudaMallocHost(&c->h_slice[k], c->slice_words * sizeof(uint32_t)));
-            CUI(cudaMalloc(&c->d_prep[k], dinfo_b + pcls_b + hset_b + gvals_b + best_b));
-            c->tab[k].best = reinterpret_cast<uint32_t *>(c->d_prep[k] + dinfo_b + pcls_b + hset_b + gvals_b);
-            c->tab[k].best_ctas = best_ctas;
+            CUI(cudaMalloc(&c->d_prep[k], dinfo_b + pcls_b + hset_b + gvals_b));
             c->tab[k].dinfo = reinterpret_cast<uint4 *>(c->d_prep[k]);
             c->tab[k].pcls = c->d_prep[k] + dinfo_b;
             c->tab[k].hset = reinterpret_cast<uint32_t *>(c->d_prep[k] + dinfo_b + pcls_b);

@@ -713,7 +713,7 @@ __global__ void __launch_bounds__(128) k1p_classify(int32_t n_tiles, SliceTab tb
 
 // shared-memory carve-up of k1_score_sliced (bytes); T = threads per CTA
 struct SliceSmem {
-    int tile, ptile, bar, vals, below, tab, total;
+    int tile, ptile, bar, vals, below, best, row, tab, total;
 };
 __host__ __device__ inline SliceSmem slice_smem(int T, int nums, int tab_rows) {
     SliceSmem m;
@@ -723,6 +723,8 @@ __host__ __device__ inline SliceSmem slice_smem(int T, int nums, int tab_rows) {
     m.bar = o, o += 16;
     m.vals = o, o += (kDict + 4) * 4;
     m.below = o, o += (kDict + 1) * T * 4;
+    m.best = o, o += 32 * T * 4;
+    m.row = o, o += 32 * T * 2;
     m.tab = o, o += tab_rows * T * 4;
     m.total = o;
     return m;
@@ -761,12 +763,8 @@ __global__ void __launch_bounds__(128)
     uint32_t *vals = reinterpret_cast<uint32_t *>(smem_raw + L.vals);
     // below[k][t]: my pods whose best is < vals[k] (may over-approximate, never under); row kDict = all ones
     uint32_t *below = reinterpret_cast<uint32_t *>(smem_raw + L.below);
-    // per-pod best (raw score bits, 0 = none) and its row (relative to this CTA's first row):
-    // touched only at set-up, on the rare improvement and at the flush, so they live in a
-    // per-CTA slab of global memory and leave the shared memory to resident warps
-    const size_t cta = (size_t)blockIdx.y * gridDim.x + blockIdx.x;
-    uint32_t *s_best = tb.best + cta * 32 * T;                                        // [32][T]
-    uint16_t *s_row = reinterpret_cast<uint16_t *>(tb.best + tb.best_ctas * 32 * 128) + cta * 32 * T; // [32][T]
+    uint32_t *s_best = reinterpret_cast<uint32_t *>(smem_raw + L.best); // [32][T] raw score bits, 0 = none
+    uint16_t *s_row = reinterpret_cast<uint16_t *>(smem_raw + L.row);   // [32][T] row - first row of this CTA
     const uint32_t *tabs = reinterpret_cast<const uint32_t *>(smem_raw + L.tab);
 
     const int w = blockIdx.y * T + tid;
@@ -1397,13 +1395,8 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
             if (want < 1) want = 1;
             int tiles_per = (int)((n_virtual + want - 1) / want);
             if (tiles_per < min_tiles) tiles_per = min_tiles;
-            // per CTA: the bit-sliced fit counter holds 2^planes - 1 nodes, rows are 16-bit offsets
-            // over a span of up to 8/7 of its tiles, and there are tb.best_ctas result slabs
-            const int cap = min(((1 << kSliceCountPlanes) - 1) / kWarp, 1700);
-            const long long slabs = (long long)tb.best_ctas / gy;
-            if (slabs < 1) return cudaErrorInvalidConfiguration;
-            if ((n_virtual + tiles_per - 1) / tiles_per > slabs) tiles_per = (int)((n_virtual + slabs - 1) / slabs);
-            if (tiles_per > cap) return cudaErrorInvalidConfiguration; // > 1700 * best_ctas tiles: not reachable
+            const int cap = ((1 << kSliceCountPlanes) - 1) / kWarp;
+            if (tiles_per > cap) tiles_per = cap;
             const int gx = (n_virtual + tiles_per - 1) / tiles_per;
             kernel<<<dim3(gx, gy), T, smem, st>>>(a.n_tiles, a.n_nodes, a.row_base, tb, n_types, tiles_per, phase,
                                                   a.keys, a.counts, a.vfit, a.vscore, a.vwords);

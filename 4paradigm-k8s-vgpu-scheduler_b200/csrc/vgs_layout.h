@@ -95,8 +95,6 @@ struct SliceTab {
     uint8_t *pcls;     // [n_tiles*32][32] score class of each device pair (Nums == 2 class only)
     uint32_t *hset;    // [kSliceHash] open-addressing set of the distinct candidate scores
     uint32_t *gvals;   // [kSliceDict] the largest distinct scores, ascending; gvals[kSliceDict] = count
-    uint32_t *best;    // per-CTA slabs: best_ctas x [32][128] u32 scores, then best_ctas x [32][128] u16 rows
-    size_t best_ctas;  // number of slabs allocated
 };
 // what the sliced score kernel needs to know about one device, 16 bytes
 struct __align__(16) SliceDev {
@@ -108,7 +106,7 @@ constexpr int kSliceDict = 32;    // distinct candidate scores tracked exactly (
 constexpr int kSliceHash = 4096;  // capacity of the distinct-score set (power of two)
 constexpr int kSliceMaxDistinct = 1024; // distinct Memreq / Coresreq values per class
 constexpr int kSliceMaxPct = 101;       // MemPercentagereq in [0, 100]
-constexpr int kSliceCountPlanes = 16;   // bit-sliced fit counter: < 65536 nodes per CTA
+constexpr int kSliceCountPlanes = 13;   // bit-sliced fit counter: < 8192 nodes per CTA
 constexpr int32_t kSliceMaxTotalmem = 21474836; // Totalmem * 100 must not wrap int32
 
 // status word bits (device -> host)
