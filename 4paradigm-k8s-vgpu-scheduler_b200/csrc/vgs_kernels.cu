@@ -15,6 +15,7 @@
 #include <stdint.h>
 
 #include <cstdlib>
+#include <type_traits>
 
 #include "../../include/vgpuscore.h"
 #include "vgs_kernels.h"
@@ -374,8 +375,10 @@ __global__ void __launch_bounds__(128)
                 bool alive = true, in_ctr = false;
                 float score = 0.0f;
                 int32_t total = 0, free_ = 0, sums = 0;
-                for (int r = 0; r < pod.n_reqs; r++) {
-                    const DevReq rq = load_req(&reqs[pod.req_begin + r]);
+                // one request.  FIRST: the devices still stand in K0's walk order, so "fitting
+                // devices ahead of me" is a prefix count and no keys are compared.  NUMA: numa-bind
+                // grouping.  LAST: nothing follows, the re-sorted positions are not needed.
+                auto request = [&](auto FIRST, auto NUMA, auto LAST, const DevReq &rq) {
                     if (rq.flags & R_NEWCTR) {
                         if (in_ctr) score = __fadd_rn(score, container_score(total, free_, ndev - sums));
                         total = 0;
@@ -385,7 +388,6 @@ __global__ void __launch_bounds__(128)
                     }
                     sums += rq.nums;
                     const bool usepct = rq.flags & R_USEPCT;
-                    const bool numa = rq.flags & R_NUMA;
                     int32_t mem[DM], key[DM], nr[DM];
                     bool fit[DM];
                     int nfit = 0;
@@ -399,34 +401,50 @@ __global__ void __launch_bounds__(128)
                                  ((fs[j] + kKeyFreeBias) << kKeyPosBits) | pos[j];
                         nfit += fit[j] ? 1 : 0;
                     }
-                    // pairwise order: ahead[j] = fitting devices visited before j (same numa
-                    // group only when numa-bound); npos[j] = ascending position after this sort
+                    // ahead[j] = fitting devices visited before j (same numa group only when
+                    // numa-bound); npos[j] = ascending position after this request's sort
                     int ahead[DM], npos[DM], same[DM];
+                    if constexpr (decltype(FIRST)::value && !decltype(NUMA)::value) {
+                        int run = 0;
 #pragma unroll
-                    for (int j = 0; j < DM; j++) {
-                        ahead[j] = 0;
-                        npos[j] = 0;
-                        same[j] = fit[j] ? 1 : 0;
-                    }
+                        for (int j = 0; j < DM; j++) {
+                            ahead[j] = run;
+                            run += fit[j] ? 1 : 0;
+                            npos[j] = pos[j];
+                            same[j] = 0;
+                        }
+                    } else {
 #pragma unroll
-                    for (int i = 0; i < DM; i++) {
+                        for (int j = 0; j < DM; j++) {
+                            ahead[j] = 0;
+                            npos[j] = 0;
+                            same[j] = fit[j] ? 1 : 0;
+                        }
 #pragma unroll
-                        for (int j = i + 1; j < DM; j++) {
-                            bool igtj = key[i] > key[j]; // keys are distinct (pos is a permutation)
-                            bool grp = !numa || nr[i] == nr[j];
-                            ahead[j] += (igtj && fit[i] && grp) ? 1 : 0;
-                            ahead[i] += (!igtj && fit[j] && grp) ? 1 : 0;
-                            npos[i] += igtj ? 1 : 0;
-                            npos[j] += igtj ? 0 : 1;
-                            if (numa) {
-                                same[i] += (fit[j] && nr[i] == nr[j]) ? 1 : 0;
-                                same[j] += (fit[i] && nr[i] == nr[j]) ? 1 : 0;
+                        for (int i = 0; i < DM; i++) {
+#pragma unroll
+                            for (int j = i + 1; j < DM; j++) {
+                                const bool igtj = key[i] > key[j]; // keys are distinct (pos is a permutation)
+                                if constexpr (decltype(NUMA)::value) {
+                                    const bool grp = nr[i] == nr[j];
+                                    ahead[j] += (igtj && fit[i] && grp) ? 1 : 0;
+                                    ahead[i] += (!igtj && fit[j] && grp) ? 1 : 0;
+                                    same[i] += (fit[j] && grp) ? 1 : 0;
+                                    same[j] += (fit[i] && grp) ? 1 : 0;
+                                } else {
+                                    ahead[j] += (igtj && fit[i]) ? 1 : 0;
+                                    ahead[i] += (!igtj && fit[j]) ? 1 : 0;
+                                }
+                                if constexpr (!decltype(LAST)::value) {
+                                    npos[i] += igtj ? 1 : 0;
+                                    npos[j] += igtj ? 0 : 1;
+                                }
                             }
                         }
                     }
                     bool ok;
                     int gstar = -1;
-                    if (numa) {
+                    if constexpr (decltype(NUMA)::value) {
                         // the walk restarts its picks at every numa change (score.go:99-104):
                         // the first numa group (descending) holding >= Nums fitting devices wins
 #pragma unroll
@@ -439,7 +457,7 @@ __global__ void __launch_bounds__(128)
                     alive = alive && ok;
 #pragma unroll
                     for (int j = 0; j < DM; j++) {
-                        bool take = ok && fit[j] && ahead[j] < rq.nums && (!numa || nr[j] == gstar);
+                        const bool take = ok && fit[j] && ahead[j] < rq.nums && (!decltype(NUMA)::value || nr[j] == gstar);
                         if (take) { // score.go:168-174
                             total = wrap_add(total, count[j]);
                             free_ = wrap_add(free_, fs[j]);
@@ -452,7 +470,23 @@ __global__ void __launch_bounds__(128)
                             if ((m & M_CORENZ) && fc[j] == 0) m |= M_FULL;
                             mt[j] = m;
                         }
-                        pos[j] = npos[j];
+                        if constexpr (!decltype(LAST)::value) pos[j] = npos[j];
+                    }
+                };
+                using T_ = std::true_type;
+                using F_ = std::false_type;
+                for (int r = 0; r < pod.n_reqs; r++) {
+                    const DevReq rq = load_req(&reqs[pod.req_begin + r]);
+                    const bool numa = rq.flags & R_NUMA, last = r + 1 == pod.n_reqs;
+                    if (numa) { // rare: one generic variant
+                        if (last) request(F_{}, T_{}, T_{}, rq);
+                        else request(F_{}, T_{}, F_{}, rq);
+                    } else if (r == 0) {
+                        request(T_{}, F_{}, F_{}, rq); // positions stay as they are
+                    } else if (last) {
+                        request(F_{}, F_{}, T_{}, rq);
+                    } else {
+                        request(F_{}, F_{}, F_{}, rq);
                     }
                     if (!__any_sync(0xffffffffu, alive)) break;
                 }
