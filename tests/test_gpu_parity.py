@@ -374,3 +374,22 @@ def test_pinned_planes_take_the_zero_copy_upload(built, monkeypatch):
         ctx.upload_ptrs(snap.n_nodes, snap.dmax, [pin[f].data_ptr() for f in range(8)], pnd.data_ptr(), device=False)
         planes, _ = ctx.download_snapshot()
         assert np.array_equal(planes, snap.planes)
+
+
+def test_refresh_and_phased_calls(built):
+    """the phased entry points (pods_upload / score_resident / resolve_resident / results_download) and
+    vgs_snapshot_refresh give the same answer as the one-shot vgs_score_batch"""
+    snap, batch = v.workload.make_config("cfg3", 4000, 700)
+    pods, reqs = v.capi.pack_batch(batch, snap.type_names)
+    with v.Context(max_nodes=4000, max_pods=700) as ctx:
+        ctx.upload(snap)
+        want_r, want_p = ctx.score_packed(pods, reqs)
+        ctx.pods_upload(pods, reqs)
+        for _ in range(2):
+            ctx.refresh()
+            ctx.score_resident()
+            ctx.resolve_resident()
+            got_r, got_p = ctx.results_download()
+            assert np.array_equal(got_r, want_r) and np.array_equal(got_p, want_p)
+        t = ctx.timing()
+        assert t.score_ms > 0 and t.derive_ms > 0 and t.kernel_launches > 0
