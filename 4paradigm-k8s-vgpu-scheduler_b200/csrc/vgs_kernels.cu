@@ -780,7 +780,7 @@ __host__ __device__ inline SliceSmem slice_smem(int T, int nums, int tab_rows) {
 template <int NUMS, bool TABSMEM, bool VERIFY>
 __global__ void __launch_bounds__(128)
     k1_score_sliced(int32_t n_tiles, int32_t n_nodes, int32_t row_base, SliceTab tb, int32_t n_types,
-                    int32_t tiles_per_cta, int32_t phase, unsigned long long *__restrict__ keys,
+                    int32_t tiles_per_cta, int32_t phase, int32_t kScout, unsigned long long *__restrict__ keys,
                     int32_t *__restrict__ counts, uint32_t *__restrict__ vfit, float *__restrict__ vscore,
                     int32_t vwords) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -810,7 +810,6 @@ __global__ void __launch_bounds__(128)
     // state and publishes its bests; phase 1 walks all the other tiles and starts from those
     // published bests, so that its detection words are almost always zero from the first node.
     // phase -1 = single launch over all tiles (small snapshots).  v = virtual tile index.
-    constexpr int kScout = 8;
     auto tile_of = [&](int v) -> int {
         if (phase < 0) return v;
         if (phase == 0) return v * kScout;
@@ -1408,6 +1407,16 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
     if (n_types < 1) n_types = 1;
     if (n_types > VGS_MAX_TYPES) n_types = VGS_MAX_TYPES;
     const int rows_s = n_types + (tb.km + 1) + (tb.kp + 1) + 4 * (tb.kc + 1);
+    // every scout-th tile is walked by the scout launch: about a hundred scout tiles (measured
+    // optimum on 100k nodes: stride 24-48), VGS_SCOUT overrides
+    static int scout_env = -1;
+    if (scout_env < 0) {
+        const char *ev = getenv("VGS_SCOUT");
+        scout_env = ev ? atoi(ev) : 0;
+    }
+    int scout = scout_env >= 2 ? scout_env : a.n_tiles / 96;
+    if (scout < 4) scout = 4;
+    if (scout > 32 && scout_env < 2) scout = 32;
     static int force_tab = -2;
     if (force_tab == -2) {
         const char *ev = getenv("VGS_SLICE_TABSMEM");
@@ -1433,11 +1442,11 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
             if (tiles_per > cap) tiles_per = cap;
             const int gx = (n_virtual + tiles_per - 1) / tiles_per;
             kernel<<<dim3(gx, gy), T, smem, st>>>(a.n_tiles, a.n_nodes, a.row_base, tb, n_types, tiles_per, phase,
-                                                  a.keys, a.counts, a.vfit, a.vscore, a.vwords);
+                                                  scout, a.keys, a.counts, a.vfit, a.vscore, a.vwords);
             return cudaGetLastError();
         };
-        if (a.n_tiles < 64 * 8) return launch(a.n_tiles, -1, 2); // small snapshot: one launch
-        const int scouts = (a.n_tiles + 7) / 8;
+        if (a.n_tiles < 256) return launch(a.n_tiles, -1, 2); // small snapshot (< 8k nodes): one launch
+        const int scouts = (a.n_tiles + scout - 1) / scout;
         if ((e = launch(scouts, 0, 1)) != cudaSuccess) return e;
         return launch(a.n_tiles - scouts, 1, 2);
     };
