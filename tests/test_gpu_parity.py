@@ -232,17 +232,19 @@ def test_shards_on_one_gpu_equal_single(built):
     assert np.array_equal(picks, single.picks)
 
 
-def test_full_size_properties(built):
-    """BASELINE config 3 at full size (100k nodes x 4096 pods): properties that do not need
-    the oracle over all 4e8 pairs -- determinism, a sampled-pod oracle check over all
+@pytest.mark.parametrize("cfg", ["cfg3", "cfg4"])
+def test_full_size_properties(built, cfg):
+    """BASELINE configs 3 and 4 at full size (100k nodes x 4096 pods): properties that do not
+    need the oracle over all 4e8 pairs -- determinism, a sampled-pod oracle check over all
     nodes, and every winner re-checked by the oracle on its own node."""
-    snap, batch = v.workload.make_config("cfg3")
-    with v.Context(max_nodes=snap.n_nodes, max_pods=batch.n_pods) as ctx:
+    snap, batch = v.workload.make_config(cfg)
+    with v.Context(max_nodes=snap.n_nodes, max_pods=batch.n_pods, max_reqs=batch.n_reqs,
+                   max_picks=int(batch.nums.sum())) as ctx:
         ctx.upload(snap)
         a = ctx.score(batch)
         b = ctx.score(batch)
     assert_same(a, b, "idempotence")
-    assert (a.best_row >= 0).mean() > 0.9
+    assert (a.best_row >= 0).mean() > 0.8
     idx = list(range(0, batch.n_pods, 64))
     sub = batch.select(idx)
     want = oracle.score_packed(snap, sub)
