@@ -267,7 +267,8 @@ def test_full_size_properties(built, cfg):
 
 def test_sliced_default_threshold(built):
     """classes >= 512 pods take the pod-sliced kernels; whole fit/score matrix vs the oracle"""
-    for cfg, n, p in (("cfg3", 3000, 2600), ("cfg2", 5000, 1024), ("cfg3", 40, 4096)):
+    # 9000 nodes: enough tiles for the two-launch (scouts + main) path of the sliced kernel
+    for cfg, n, p in (("cfg3", 3000, 2600), ("cfg2", 5000, 1024), ("cfg3", 40, 4096), ("cfg3", 9000, 1400)):
         snap, batch = v.workload.make_config(cfg, n, p)
         assert_same(gpu_score(snap, batch), oracle.score_packed(snap, batch, full=True), f"sliced {cfg}")
 
