@@ -464,8 +464,8 @@ static size_t stage_layout(vgs_ctx *c, size_t P, size_t R) {
 
 // Build the bit tables of one pod-sliced class (see SliceTab) into pinned staging and queue the
 // upload.  Returns false when the class does not qualify (then the per-pair kernel runs).
-static bool build_slice_class(vgs_ctx *c, int k, const DevReq *req, const int32_t *orig, int32_t n,
-                              cudaError_t *err) {
+static bool build_slice_class(vgs_ctx *c, int k, const DevReq *req, const DevReq *dreq_class,
+                              const int32_t *orig, int32_t n, cudaError_t *err) {
     *err = cudaSuccess;
     c->slice_on[k] = false;
     if (n < c->slice_min || n < 1) return false;
@@ -498,39 +498,18 @@ static bool build_slice_class(vgs_ctx *c, int k, const DevReq *req, const int32_
     const size_t o_corev = o; o += kc;
     const size_t o_orig = o; o += n;
     if (o > c->slice_words) return false;
-    memset(h, 0, o_memv * sizeof(uint32_t));
-    auto idx_of = [](const std::vector<int32_t> &v, int32_t x) {
-        return (int32_t)(std::lower_bound(v.begin(), v.end(), x) - v.begin());
-    };
-    for (int32_t i = 0; i < n; i++) {
-        const DevReq &d = req[i];
-        const uint32_t bit = 1u << (i & 31);
-        const size_t wd = (size_t)(i >> 5);
-        uint64_t mask = ((uint64_t)d.mask_hi << 32) | d.mask_lo;
-        while (mask) {
-            int t = __builtin_ctzll(mask);
-            mask &= mask - 1;
-            h[o_type + (size_t)t * Wp + wd] |= bit;
-        }
-        if (d.flags & R_USEPCT) h[o_pct + (size_t)(idx_of(pv, d.pct) + 1) * Wp + wd] |= bit;
-        else h[o_mem + (size_t)(idx_of(mv, d.memfix) + 1) * Wp + wd] |= bit;
-        // cores x flags: cumulative over the Coresreq cut, one row per flag combination f
-        for (int f = 0; f < 4; f++) {
-            const bool lose = d.coresreq > 100 || ((f & 1) && d.coresreq == 100) || ((f & 2) && d.coresreq == 0);
-            if (!lose) h[o_core + ((size_t)(idx_of(cv, d.coresreq) + 1) * 4 + f) * Wp + wd] |= bit;
-        }
-    }
-    auto prefix_or = [&](size_t base, int32_t rows, int32_t step) { // row r |= row r - step
-        for (int32_t r = step; r < (rows + 1) * step; r++)
-            for (int32_t x = 0; x < W; x++) h[base + (size_t)r * Wp + x] |= h[base + (size_t)(r - step) * Wp + x];
-    };
-    prefix_or(o_mem, km, 1), prefix_or(o_pct, kp, 1), prefix_or(o_core, kc, 4);
+    // host: only the small value arrays; the bit tables are filled on the GPU (K1t) from the
+    // request records that are already on their way to the device
     int32_t *hi = reinterpret_cast<int32_t *>(h);
     std::copy(mv.begin(), mv.end(), hi + o_memv);
     std::copy(pv.begin(), pv.end(), hi + o_pctv);
     std::copy(cv.begin(), cv.end(), hi + o_corev);
     std::copy(orig, orig + n, hi + o_orig);
-    *err = cudaMemcpyAsync(c->d_slice[k], h, o * sizeof(uint32_t), cudaMemcpyHostToDevice, c->st);
+    (void)o_mem, (void)o_pct, (void)o_core;
+    *err = cudaMemcpyAsync(c->d_slice[k] + o_memv, h + o_memv, (o - o_memv) * sizeof(uint32_t),
+                           cudaMemcpyHostToDevice, c->st);
+    if (*err != cudaSuccess) return false;
+    *err = cudaMemsetAsync(c->d_slice[k], 0, o_memv * sizeof(uint32_t), c->st);
     if (*err != cudaSuccess) return false;
     const uint32_t *d = c->d_slice[k];
     SliceTab &t = c->tab[k];
@@ -541,6 +520,9 @@ static bool build_slice_class(vgs_ctx *c, int k, const DevReq *req, const int32_
     t.corev = reinterpret_cast<const int32_t *>(d + o_corev);
     t.orig = reinterpret_cast<const int32_t *>(d + o_orig);
     t.km = km, t.kp = kp, t.kc = kc, t.n_pods = n, t.W = W, t.Wp = Wp;
+    *err = launch_slice_tables(t, dreq_class, c->st);
+    if (*err != cudaSuccess) return false;
+    c->launches += 2;
     c->slice_on[k] = true;
     return true;
 }
@@ -650,9 +632,9 @@ static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, i
     if (stage_used) CU(cudaMemcpyAsync(c->d_stage, c->h_stage, stage_used, cudaMemcpyHostToDevice, c->st));
     {
         cudaError_t e;
-        build_slice_class(c, 0, hA, hoA, nA, &e);
+        build_slice_class(c, 0, hA, reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqsA), hoA, nA, &e);
         CU(e);
-        build_slice_class(c, 1, hB, hoB, nB, &e);
+        build_slice_class(c, 1, hB, reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqsB), hoB, nB, &e);
         CU(e);
     }
     rec(c, EV_PH1);

@@ -595,6 +595,64 @@ __device__ __forceinline__ void hset_insert(uint32_t *__restrict__ hset, uint32_
 }
 
 // ------------------------------------------------------------------------------------
+// K1t: the bit tables of a sliced class (layout: SliceTab), filled from the class's request
+// records.  fill: thread = pod, one atomicOr per table the pod belongs to; prefix: thread =
+// pod word, turns the per-value rows into cumulative ("threshold admitted") rows.
+// ------------------------------------------------------------------------------------
+__device__ __forceinline__ int lower_bound_i32(const int32_t *__restrict__ v, int n, int32_t x) {
+    int lo = 0, hi = n;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldg(&v[mid]) < x) lo = mid + 1;
+        else hi = mid;
+    }
+    return lo;
+}
+__global__ void __launch_bounds__(128) k1t_fill(SliceTab tb, const DevReq *__restrict__ req) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= tb.n_pods) return;
+    uint32_t *base = const_cast<uint32_t *>(tb.base);
+    const DevReq d = load_req(&req[i]);
+    const uint32_t bit = 1u << (i & 31);
+    const size_t wd = (size_t)(i >> 5), Wp = (size_t)tb.Wp;
+    const int r_mem = VGS_MAX_TYPES, r_pct = r_mem + tb.km + 1, r_core = r_pct + tb.kp + 1;
+    for (uint32_t m = d.mask_lo; m; m &= m - 1) atomicOr(&base[(size_t)(__ffs((int)m) - 1) * Wp + wd], bit);
+    for (uint32_t m = d.mask_hi; m; m &= m - 1) atomicOr(&base[(size_t)(32 + __ffs((int)m) - 1) * Wp + wd], bit);
+    if (d.flags & R_USEPCT) atomicOr(&base[(size_t)(r_pct + lower_bound_i32(tb.pctv, tb.kp, d.pct) + 1) * Wp + wd], bit);
+    else atomicOr(&base[(size_t)(r_mem + lower_bound_i32(tb.memv, tb.km, d.memfix) + 1) * Wp + wd], bit);
+    // cores x flags: one row per flag combination f = excl | full << 1; Coresreq == 100 loses on
+    // excl (score.go:128), == 0 on full (:132), > 100 always (:110)
+    const int cut = lower_bound_i32(tb.corev, tb.kc, d.coresreq) + 1;
+    for (int f = 0; f < 4; f++) {
+        const bool lose = d.coresreq > 100 || ((f & 1) && d.coresreq == 100) || ((f & 2) && d.coresreq == 0);
+        if (!lose) atomicOr(&base[(size_t)(r_core + cut * 4 + f) * Wp + wd], bit);
+    }
+}
+__global__ void __launch_bounds__(128) k1t_prefix(SliceTab tb) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= tb.W) return;
+    uint32_t *base = const_cast<uint32_t *>(tb.base);
+    const size_t Wp = (size_t)tb.Wp;
+    const int r_mem = VGS_MAX_TYPES, r_pct = r_mem + tb.km + 1, r_core = r_pct + tb.kp + 1;
+    uint32_t acc = 0u;
+    for (int r = 0; r <= tb.km; r++) base[(size_t)(r_mem + r) * Wp + x] = acc |= base[(size_t)(r_mem + r) * Wp + x];
+    acc = 0u;
+    for (int r = 0; r <= tb.kp; r++) base[(size_t)(r_pct + r) * Wp + x] = acc |= base[(size_t)(r_pct + r) * Wp + x];
+    uint32_t a4[4] = {0u, 0u, 0u, 0u};
+    for (int r = 0; r <= tb.kc; r++)
+        for (int f = 0; f < 4; f++) {
+            const size_t o = (size_t)(r_core + r * 4 + f) * Wp + x;
+            base[o] = a4[f] |= base[o];
+        }
+}
+cudaError_t launch_slice_tables(const SliceTab &tb, const DevReq *dreq, cudaStream_t st) {
+    if (tb.n_pods <= 0) return cudaSuccess;
+    k1t_fill<<<(tb.n_pods + 127) / 128, 128, 0, st>>>(tb, dreq);
+    k1t_prefix<<<(tb.W + 127) / 128, 128, 0, st>>>(tb);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------
 // K1p: per batch and per sliced class, everything that depends on (device, class) but not on
 // the pod: which table rows the device selects (binary searches over the class's distinct
 // thresholds) and its candidate scores.  Thread = node; the searches of 800k devices run in

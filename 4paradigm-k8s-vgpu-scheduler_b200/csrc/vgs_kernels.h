@@ -41,6 +41,8 @@ cudaError_t launch_score_single(int dm, bool nums1, int dev, const ScoreArgs &a,
                                 const int32_t *orig, int32_t n_pods, cudaStream_t st);
 cudaError_t launch_score_general(int dm, int dev, const ScoreArgs &a, const DevReq *reqs,
                                  const GenPod *pods, int32_t n_pods, cudaStream_t st);
+// K1t: fill the bit tables of a sliced class on the device (table region zeroed, value arrays uploaded)
+cudaError_t launch_slice_tables(const SliceTab &tb, const DevReq *dreq_class, cudaStream_t st);
 // pod-sliced K1 for one class (all pods: one request, Nums == nums in {1,2}, walk DM == 8)
 // (up to 5 launches: K1p collect / sort / classify, then the score kernel: scouts + main pass)
 cudaError_t launch_score_sliced(int nums, int dev, const ScoreArgs &a, const SliceTab &tb, int n_types,
