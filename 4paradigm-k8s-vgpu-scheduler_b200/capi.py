@@ -92,7 +92,7 @@ def load_library() -> C.CDLL:
     lib.vgs_results_download.argtypes = [vp, vp, vp]
     lib.vgs_sync.argtypes = [vp]
     lib.vgs_keys_device.argtypes = [vp, C.POINTER(vp), C.POINTER(vp)]
-    lib.vgs_keys_merge.argtypes = [vp, vp, vp, i32, i32]
+    lib.vgs_keys_merge.argtypes = [vp, vp, vp, i32, i32, i32]
     lib.vgs_results_device.argtypes = [vp, C.POINTER(vp), C.POINTER(vp)]
     lib.vgs_verify_download.argtypes = [vp, vp, vp]
     lib.vgs_last_timing.argtypes = [vp, C.POINTER(VgsTiming)]
@@ -345,8 +345,9 @@ class Context:
         self._check(self.lib.vgs_results_device(self.h, C.byref(r), C.byref(p)))
         return r.value, p.value
 
-    def keys_merge(self, keys_ptr: int, counts_ptr: int, n_shards: int, stride: int):
-        self._check(self.lib.vgs_keys_merge(self.h, C.c_void_p(keys_ptr), C.c_void_p(counts_ptr), n_shards, stride))
+    def keys_merge(self, keys_ptr: int, counts_ptr: int, n_shards: int, stride: int, count_stride: int = 0):
+        self._check(self.lib.vgs_keys_merge(self.h, C.c_void_p(keys_ptr), C.c_void_p(counts_ptr), n_shards, stride,
+                                            count_stride))
 
     def timing(self) -> VgsTiming:
         t = VgsTiming()

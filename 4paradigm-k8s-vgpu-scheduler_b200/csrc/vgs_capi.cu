@@ -171,7 +171,6 @@ void free_all(vgs_ctx *c) {
     cudaFree(c->d_stage);
     cudaFreeHost(c->h_stage);
     cudaFree(c->d_keys);
-    cudaFree(c->d_counts);
     cudaFree(c->d_results);
     cudaFreeHost(c->h_results);
     cudaFree(c->d_picks);
@@ -291,8 +290,10 @@ int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
         if (const char *e = getenv("VGS_SLICE_MIN")) c->slice_min = atoi(e);
         if (const char *e = getenv("VGS_ZERO_COPY")) c->zero_copy_ok = atoi(e) != 0;
     }
-    CUI(cudaMalloc(&c->d_keys, P * sizeof(unsigned long long)));
-    CUI(cudaMalloc(&c->d_counts, P * sizeof(int32_t)));
+    // keys and counts are one allocation ("candidate block": max_pods u64 keys, then max_pods
+    // int32 counts) so that shards can exchange both with a single all-gather
+    CUI(cudaMalloc(&c->d_keys, P * (sizeof(unsigned long long) + sizeof(int32_t)) + 8));
+    c->d_counts = reinterpret_cast<int32_t *>(c->d_keys + P);
     CUI(cudaMalloc(&c->d_results, P * sizeof(vgs_result)));
     CUI(cudaMallocHost(&c->h_results, P * sizeof(vgs_result)));
     CUI(cudaMalloc(&c->d_picks, (size_t)cfg->max_picks * sizeof(vgs_pick)));
@@ -815,14 +816,17 @@ int vgs_results_device(vgs_ctx *c, vgs_result **dev_results, vgs_pick **dev_pick
     return VGS_OK;
 }
 
-int vgs_keys_merge(vgs_ctx *c, const uint64_t *gk, const int32_t *gc, int32_t n_shards, int32_t stride) {
+int vgs_keys_merge(vgs_ctx *c, const uint64_t *gk, const int32_t *gc, int32_t n_shards, int32_t stride,
+                   int32_t count_stride) {
     if (!c || !gk || n_shards < 1 || stride < 0) return VGS_EINVAL;
+    if (count_stride <= 0) count_stride = stride;
     std::lock_guard<std::mutex> lk(c->mu);
     DeviceGuard g(c->cfg.device);
     if (!c->scored) return fail(c, VGS_ESTATE, "merge before score");
     if (stride < c->n_pods) return fail(c, VGS_EINVAL, "stride < n_pods");
-    CU(launch_merge(reinterpret_cast<const unsigned long long *>(gk), gc, n_shards, stride, c->n_pods,
-                    c->d_keys, c->d_counts, c->st));
+    if (gc && count_stride < c->n_pods) return fail(c, VGS_EINVAL, "count_stride < n_pods");
+    CU(launch_merge(reinterpret_cast<const unsigned long long *>(gk), gc, n_shards, stride, count_stride,
+                    c->n_pods, c->d_keys, c->d_counts, c->st));
     if (c->n_pods) c->launches++;
     return VGS_OK;
 }

@@ -1115,7 +1115,7 @@ __global__ void __launch_bounds__(128)
 // K2: merge shard candidates (after the allgather)
 // ------------------------------------------------------------------------------------
 __global__ void k2_merge(const unsigned long long *__restrict__ gk, const int32_t *__restrict__ gc,
-                         int32_t n_shards, int32_t stride, int32_t n_pods,
+                         int32_t n_shards, int32_t stride, int32_t cstride, int32_t n_pods,
                          unsigned long long *__restrict__ keys, int32_t *__restrict__ counts) {
     int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n_pods) return;
@@ -1124,7 +1124,7 @@ __global__ void k2_merge(const unsigned long long *__restrict__ gk, const int32_
     for (int g = 0; g < n_shards; g++) {
         unsigned long long k = gk[(size_t)g * stride + p];
         best = k > best ? k : best;
-        if (gc) c += gc[(size_t)g * stride + p];
+        if (gc) c += gc[(size_t)g * cstride + p];
     }
     keys[p] = best;
     if (gc) counts[p] = c;
@@ -1520,9 +1520,10 @@ cudaError_t launch_score_sliced(int nums, int dev, const ScoreArgs &a, const Sli
 }
 
 cudaError_t launch_merge(const unsigned long long *gk, const int32_t *gc, int32_t n_shards, int32_t stride,
-                         int32_t n_pods, unsigned long long *keys, int32_t *counts, cudaStream_t st) {
+                         int32_t cstride, int32_t n_pods, unsigned long long *keys, int32_t *counts,
+                         cudaStream_t st) {
     if (n_pods <= 0) return cudaSuccess;
-    k2_merge<<<(n_pods + 127) / 128, 128, 0, st>>>(gk, gc, n_shards, stride, n_pods, keys, counts);
+    k2_merge<<<(n_pods + 127) / 128, 128, 0, st>>>(gk, gc, n_shards, stride, cstride, n_pods, keys, counts);
     return cudaGetLastError();
 }
 

@@ -49,8 +49,8 @@ cudaError_t launch_score_sliced(int nums, int dev, const ScoreArgs &a, const Sli
                                 uint32_t *status, cudaStream_t st);
 constexpr int kSlicedLaunches = 5;
 cudaError_t launch_merge(const unsigned long long *gk, const int32_t *gc, int32_t n_shards,
-                         int32_t stride, int32_t n_pods, unsigned long long *keys, int32_t *counts,
-                         cudaStream_t st);
+                         int32_t stride, int32_t cstride, int32_t n_pods, unsigned long long *keys,
+                         int32_t *counts, cudaStream_t st);
 cudaError_t launch_resolve(const RawPlanes &raw, int32_t n_nodes, int32_t dmax, int32_t row_base,
                            const vgs_pod *pods, const DevReq *reqs, const int32_t *pick_begin,
                            int32_t n_pods, const unsigned long long *keys, const int32_t *counts,

@@ -93,6 +93,7 @@ class ShardedScorer:
         from .capi import Context
 
         self.rank, self.world, self.group = rank, world, group
+        max_pods += max_pods & 1  # the 12-byte-per-pod candidate block is exchanged in 8-byte units
         self.lo, self.hi = shard_range(n_nodes_total, world, rank)
         self.device = torch.device("cuda", device)
         torch.cuda.set_device(self.device)
@@ -107,12 +108,13 @@ class ShardedScorer:
         self.max_picks = self.ctx.cfg.max_picks
         kp, cp = self.ctx.keys_device()
         rp, pp = self.ctx.results_device()
-        self.keys = device_view(kp, max_pods, torch.int64, self.device)
-        self.counts = device_view(cp, max_pods, torch.int32, self.device)
+        assert cp == kp + 8 * max_pods  # candidate block: keys then counts, one allocation
+        # the block as int32 words (3 per pod): one all-gather moves keys and counts together
+        self.block_words = 3 * max_pods
+        self.block = device_view(kp, self.block_words, torch.int32, self.device)
         self.picks = device_view(pp, self.max_picks * 3, torch.int32, self.device)
         if world > 1:
-            self.gk = torch.empty((world, max_pods), dtype=torch.int64, device=self.device)
-            self.gc = torch.empty((world, max_pods), dtype=torch.int32, device=self.device)
+            self.gathered = torch.empty((world, self.block_words), dtype=torch.int32, device=self.device)
 
     def upload(self, snap_shard):
         assert snap_shard.n_nodes == self.hi - self.lo
@@ -126,9 +128,12 @@ class ShardedScorer:
         with torch.cuda.stream(self.stream):
             self.ctx.score_resident()
             if self.world > 1:
-                dist.all_gather_into_tensor(self.gk, self.keys, group=self.group)
-                dist.all_gather_into_tensor(self.gc, self.counts, group=self.group)
-                self.ctx.keys_merge(self.gk.data_ptr(), self.gc.data_ptr(), self.world, self.max_pods)
+                dist.all_gather_into_tensor(self.gathered, self.block, group=self.group)
+                base = self.gathered.data_ptr()
+                # shard g: keys at base + g*12P bytes (stride 1.5 P uint64), counts 8P bytes further
+                assert self.max_pods % 2 == 0
+                self.ctx.keys_merge(base, base + 8 * self.max_pods, self.world, self.block_words // 2,
+                                    self.block_words)
             self.ctx.resolve_resident()
             if self.world > 1 and n_picks:
                 # picks are written by the owner of each winner row only (zero elsewhere)

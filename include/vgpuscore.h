@@ -194,12 +194,17 @@ int vgs_sync(vgs_ctx *ctx);
 
 /* node sharding: per-pod candidate key = (ordered score bits << 32) | global
  * row, 0 = none; max over shards = the global winner under the canonical tie
- * rule.  keys_device returns this GPU's array of max_pods uint64 (allgather
- * it), keys_merge takes the gathered [n_shards][stride] array (device memory)
- * and reduces it back into the context; counts_* likewise for fit_count. */
+ * rule.  keys_device returns this GPU's candidate block: max_pods uint64 keys
+ * immediately followed by max_pods int32 fit counts (one allocation, so one
+ * all-gather of max_pods * 12 bytes moves both).  keys_merge takes the
+ * gathered blocks (device memory) and reduces them back into the context:
+ * shard g's keys start at dev_gathered_keys + g * key_stride (uint64 units),
+ * its counts at dev_gathered_counts + g * count_stride (int32 units;
+ * <= 0 means "same as key_stride"). */
 int vgs_keys_device(vgs_ctx *ctx, uint64_t **dev_keys, int32_t **dev_counts);
 int vgs_keys_merge(vgs_ctx *ctx, const uint64_t *dev_gathered_keys,
-                   const int32_t *dev_gathered_counts, int32_t n_shards, int32_t stride);
+                   const int32_t *dev_gathered_counts, int32_t n_shards, int32_t key_stride,
+                   int32_t count_stride);
 /* device arrays behind vgs_results_download (shard combine of results/picks) */
 int vgs_results_device(vgs_ctx *ctx, vgs_result **dev_results, vgs_pick **dev_picks);
 
