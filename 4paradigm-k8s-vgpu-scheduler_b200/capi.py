@@ -25,7 +25,7 @@ NOALLOC_MAX_NODES, NOALLOC_MAX_DEVICES, NOALLOC_MAX_PODS, NOALLOC_MAX_REQS = 163
 EXPORTS = (
     "vgs_abi_version", "vgs_strerror", "vgs_init", "vgs_destroy", "vgs_last_error",
     "vgs_snapshot_upload", "vgs_snapshot_set_device", "vgs_snapshot_refresh", "vgs_snapshot_delta", "vgs_snapshot_download",
-    "vgs_score_batch", "vgs_pods_upload", "vgs_score_resident", "vgs_resolve_resident",
+    "vgs_score_batch", "vgs_drain_batch", "vgs_pods_upload", "vgs_score_resident", "vgs_resolve_resident",
     "vgs_results_download", "vgs_sync", "vgs_keys_device", "vgs_keys_merge", "vgs_results_device",
     "vgs_verify_download", "vgs_last_timing", "vgs_host_typemask", "vgs_host_numa_bind",
     "vgs_host_encode_pod_devices", "vgs_host_decode_node_devices", "vgs_score_batch_noalloc",
@@ -86,6 +86,7 @@ def load_library() -> C.CDLL:
     lib.vgs_snapshot_delta.argtypes = [vp, i32, vp]
     lib.vgs_snapshot_download.argtypes = [vp, C.POINTER(vp), vp]
     lib.vgs_score_batch.argtypes = [vp, i32, vp, i32, vp, vp, vp]
+    lib.vgs_drain_batch.argtypes = [vp, i32, vp, i32, vp, vp, vp]
     lib.vgs_pods_upload.argtypes = [vp, i32, vp, i32, vp]
     lib.vgs_score_resident.argtypes = [vp]
     lib.vgs_resolve_resident.argtypes = [vp]
@@ -293,6 +294,15 @@ class Context:
                                              results.ctypes.data, picks.ctypes.data))
         self._np, self._nr, self._n_picks = len(pods), len(reqs), len(picks)
         return results, picks
+
+    def drain(self, batch: PodBatch, type_names: Optional[List[str]] = None) -> BatchResult:
+        """vgs_drain_batch: pods placed one after another, each seeing the previous winners' usage"""
+        pods, reqs = pack_batch(batch, type_names if type_names is not None else self.type_names)
+        results = np.zeros(len(pods), dtype=RESULT_DTYPE)
+        picks = np.zeros(int(reqs["nums"].sum()) if len(reqs) else 0, dtype=PICK_DTYPE)
+        self._check(self.lib.vgs_drain_batch(self.h, len(pods), pods.ctypes.data, len(reqs), reqs.ctypes.data,
+                                             results.ctypes.data, picks.ctypes.data))
+        return self._to_result(results, picks)
 
     def score(self, batch: PodBatch, type_names: Optional[List[str]] = None) -> BatchResult:
         pods, reqs = pack_batch(batch, type_names if type_names is not None else self.type_names)

@@ -63,6 +63,7 @@ struct vgs_ctx {
     size_t off_reqs = 0, off_pods = 0, off_pick = 0, off_reqsA = 0, off_origA = 0, off_reqsB = 0,
            off_origB = 0, off_podsG = 0;
     size_t off_reqsC = 0, off_origC = 0;
+    size_t off_genall = 0; // GenPod of EVERY pod, batch order (drain: one pod at a time)
     int32_t n_pods = 0, n_reqs = 0, nA = 0, nB = 0, nC = 0, nG = 0, n_picks = 0;
     // pod-sliced classes (A: Nums == 1, B: Nums == 2): bit tables, see SliceTab
     uint32_t *h_slice[2] = {}, *d_slice[2] = {};
@@ -267,7 +268,7 @@ int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
     // (stage_layout) so that one batch is ONE host-to-device copy of its used prefix
     o = align_up(R * sizeof(DevReq), 256) + align_up(P * sizeof(vgs_pod), 256) +
         align_up((R + 1) * sizeof(int32_t), 256) + 3 * align_up(P * sizeof(DevReq), 256) +
-        3 * align_up(P * sizeof(int32_t), 256) + align_up(P * sizeof(GenPod), 256);
+        3 * align_up(P * sizeof(int32_t), 256) + 2 * align_up(P * sizeof(GenPod), 256);
     c->stage_bytes = o;
     CUI(cudaMalloc(&c->d_stage, o));
     CUI(cudaMallocHost(&c->h_stage, o));
@@ -460,6 +461,7 @@ static size_t stage_layout(vgs_ctx *c, size_t P, size_t R) {
     c->off_podsG = o, o = align_up(o + P * sizeof(GenPod), 256);
     c->off_reqsC = o, o = align_up(o + P * sizeof(DevReq), 256);
     c->off_origC = o, o = align_up(o + P * sizeof(int32_t), 256);
+    c->off_genall = o, o = align_up(o + P * sizeof(GenPod), 256);
     return o;
 }
 
@@ -590,6 +592,8 @@ static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, i
             prev = reqs[r].ctr;
         }
         hpod[p] = pd;
+        GenPod *hall = reinterpret_cast<GenPod *>(c->h_stage + c->off_genall);
+        hall[p].req_begin = pd.req_begin, hall[p].n_reqs = pd.n_reqs, hall[p].orig = p, hall[p].pad = 0;
         const DevReq &first = hreq[pd.req_begin];
         if (pd.n_reqs == 1 && first.nums == 1) {
             hA[nA] = first; // numa-bind cannot matter for a single device
@@ -791,6 +795,50 @@ int vgs_score_batch(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_r
     if ((rc = pods_upload_locked(c, n_pods, pods, n_reqs, reqs)) != VGS_OK) return rc;
     if ((rc = score_locked(c)) != VGS_OK) return rc;
     if ((rc = resolve_locked(c)) != VGS_OK) return rc;
+    return download_locked(c, results, picks);
+}
+
+int vgs_drain_batch(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_reqs, const vgs_req *reqs,
+                    vgs_result *results, vgs_pick *picks) {
+    if (!c) return VGS_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard g(c->cfg.device);
+    if (!c->have_snapshot) return fail(c, VGS_ESTATE, "drain before snapshot upload");
+    int rc;
+    if ((rc = pods_upload_locked(c, n_pods, pods, n_reqs, reqs)) != VGS_OK) return rc;
+    rec(c, EV_SC0);
+    if (n_pods > 0) {
+        CU(cudaMemsetAsync(c->d_keys, 0, (size_t)n_pods * sizeof(unsigned long long), c->st));
+        CU(cudaMemsetAsync(c->d_counts, 0, (size_t)n_pods * sizeof(int32_t), c->st));
+    }
+    if (c->n_picks) CU(cudaMemsetAsync(c->d_picks, 0, (size_t)c->n_picks * sizeof(vgs_pick), c->st));
+    ScoreArgs a;
+    a.walk = c->d_walk, a.n_tiles = c->n_tiles, a.n_nodes = c->n_nodes, a.row_base = c->cfg.row_base;
+    a.keys = c->d_keys, a.counts = c->d_counts;
+    a.vfit = nullptr, a.vscore = nullptr, a.vwords = 0;
+    RawPlanesMut rm;
+    for (int f = 0; f < VGS_NUM_PLANES; f++) rm.p[f] = c->d_raw[f];
+    rm.ndev = c->d_ndev;
+    const DevReq *dreq = reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqs);
+    const vgs_pod *dpod = reinterpret_cast<const vgs_pod *>(c->d_stage + c->off_pods);
+    const int32_t *dpick = reinterpret_cast<const int32_t *>(c->d_stage + c->off_pick);
+    const GenPod *dall = reinterpret_cast<const GenPod *>(c->d_stage + c->off_genall);
+    // one pod at a time, everything chained on the stream: score (the key/count slot of pod p is
+    // addressed through GenPod.orig) -> resolve -> commit into the raw planes -> re-prepare the row
+    for (int32_t p = 0; p < n_pods; p++) {
+        CU(launch_score_general(c->dm, c->cfg.device, a, dreq, dall + p, 1, c->st));
+        CU(launch_resolve(raw_const(c), c->n_nodes, c->dmax, c->cfg.row_base, dpod + p, dreq, dpick, 1,
+                          c->d_keys + p, c->d_counts + p, c->d_results + p, c->d_picks, c->d_status, c->st));
+        CU(launch_commit(rm, c->n_nodes, c->dmax, c->cfg.row_base, dpod + p, dreq, dpick, c->d_results + p,
+                         c->d_picks, c->d_rowlist, c->st));
+        CU(launch_prepare(c->dm, raw_const(c), c->n_nodes, c->dmax, c->d_walk, c->n_tiles, c->d_status,
+                          c->d_rowlist, 1, c->st));
+        c->launches += c->n_tiles ? 4 : 3;
+    }
+    rec(c, EV_SC1);
+    c->scored = true;
+    c->resolved = true;
+    c->version++;
     return download_locked(c, results, picks);
 }
 

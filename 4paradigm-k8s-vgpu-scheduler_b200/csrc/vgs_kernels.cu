@@ -1287,6 +1287,37 @@ __global__ void k4_apply_delta(RawPlanesMut raw, int32_t n_nodes, int32_t dmax, 
 }
 
 // ------------------------------------------------------------------------------------
+// K5: commit one pod's winner into the raw planes (what addPod does to the next snapshot,
+// scheduler.go:280-297,394) and name the row whose walk tile must be re-prepared.  One thread.
+// ------------------------------------------------------------------------------------
+__global__ void k5_commit(RawPlanesMut raw, int32_t n_nodes, int32_t dmax, int32_t row_base,
+                          const vgs_pod *__restrict__ pod, const DevReq *__restrict__ reqs,
+                          const int32_t *__restrict__ pick_begin, const vgs_result *__restrict__ result,
+                          const vgs_pick *__restrict__ picks, int32_t *__restrict__ rowlist) {
+    if (blockIdx.x != 0 || threadIdx.x != 0) return;
+    rowlist[0] = -1;
+    const int32_t row = result->best_row - row_base;
+    if (result->best_row < 0 || row < 0 || row >= n_nodes) return;
+    for (int r = pod->req_begin; r < pod->req_begin + pod->n_reqs; r++) {
+        const int32_t n = reqs[r].nums, pb = pick_begin[r];
+        for (int t = 0; t < n; t++) {
+            const vgs_pick pk = picks[pb + t];
+            const size_t x = (size_t)row * dmax + pk.slot;
+            raw.p[VGS_PLANE_USED][x] += 1;
+            raw.p[VGS_PLANE_USEDMEM][x] += pk.usedmem;
+            raw.p[VGS_PLANE_USEDCORES][x] += pk.usedcores;
+        }
+    }
+    rowlist[0] = row;
+}
+cudaError_t launch_commit(const RawPlanesMut &raw, int32_t n_nodes, int32_t dmax, int32_t row_base,
+                          const vgs_pod *pod, const DevReq *reqs, const int32_t *pick_begin,
+                          const vgs_result *result, const vgs_pick *picks, int32_t *rowlist, cudaStream_t st) {
+    k5_commit<<<1, 32, 0, st>>>(raw, n_nodes, dmax, row_base, pod, reqs, pick_begin, result, picks, rowlist);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------
 // Host-pinned planes -> device planes, read straight over PCIe by the SMs (zero-copy).  On some
 // boxes of the pool a 26 MB cudaMemcpyAsync from pinned memory ran at only ~15 GB/s (43-51 GB/s
 // for 256 MB); many warps with 16-byte loads in flight reach ~50 GB/s at this size everywhere.

@@ -184,6 +184,15 @@ int vgs_snapshot_download(vgs_ctx *ctx, int32_t *const planes[VGS_NUM_PLANES], i
 int vgs_score_batch(vgs_ctx *ctx, int32_t n_pods, const vgs_pod *pods, int32_t n_reqs,
                     const vgs_req *reqs, vgs_result *results, vgs_pick *picks);
 
+/* Sequential placement of a batch ("what-if drain"): pod p is scored against
+ * the snapshot as the winners of pods 0..p-1 left it, exactly as P consecutive Filter calls
+ * with addPod in between would (scheduler.go:372-394 per pod; usage folding :280-297).  The
+ * whole chain (score -> resolve -> commit -> re-prepare the touched row, per pod) runs on the
+ * GPU without host round trips; the resident snapshot keeps all the commits afterwards.
+ * Single shard only.  Same outputs as vgs_score_batch. */
+int vgs_drain_batch(vgs_ctx *ctx, int32_t n_pods, const vgs_pod *pods, int32_t n_reqs,
+                    const vgs_req *reqs, vgs_result *results, vgs_pick *picks);
+
 /* the same pass in separate phases (resident benchmarking, node sharding) */
 int vgs_pods_upload(vgs_ctx *ctx, int32_t n_pods, const vgs_pod *pods, int32_t n_reqs,
                     const vgs_req *reqs);

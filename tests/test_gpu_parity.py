@@ -396,3 +396,44 @@ def test_refresh_and_phased_calls(built):
             assert np.array_equal(got_r, want_r) and np.array_equal(got_p, want_p)
         t = ctx.timing()
         assert t.score_ms > 0 and t.derive_ms > 0 and t.kernel_launches > 0
+
+
+def _oracle_drain(snap, batch):
+    """P consecutive oracle Filters with the winners' usage folded in between (test-side restatement
+    of scheduler.go:372-394 + :280-297 on the packed planes)"""
+    planes = snap.planes.copy()
+    pb = batch.pick_begin
+    rows, scores, counts, picks = [], [], [], np.zeros((int(batch.nums.sum()), 3), np.int32)
+    for p in range(batch.n_pods):
+        one = batch.select([p])
+        r = oracle.score_packed(v.Snapshot(planes, snap.ndev, snap.type_names), one, threads=4)
+        rows.append(int(r.best_row[0])), scores.append(r.score[0]), counts.append(int(r.fit_count[0]))
+        if r.best_row[0] >= 0:
+            r0, r1 = batch.pod_req_range(p)
+            picks[int(pb[r0]):int(pb[r1])] = r.picks
+            for s, m, c in r.picks:
+                planes[0, rows[-1], s] += 1
+                planes[2, rows[-1], s] += m
+                planes[4, rows[-1], s] += c
+    return np.array(rows, np.int32), np.array(scores, np.float32), np.array(counts, np.int32), picks, planes
+
+
+@pytest.mark.parametrize("cfg,n,p", [("cfg3", 600, 150), ("cfg4", 400, 120), ("cfg2", 64, 200)])
+def test_drain_equals_sequential_filters(built, cfg, n, p):
+    """vgs_drain_batch == P consecutive Filters with addPod in between: same winners, scores, picks,
+    and the resident snapshot ends up equal to the rebuilt one"""
+    snap, batch = v.workload.make_config(cfg, n, p)
+    rows, scores, counts, picks, planes = _oracle_drain(snap, batch)
+    with v.Context(max_nodes=n, max_pods=p, max_reqs=batch.n_reqs, max_picks=int(batch.nums.sum())) as ctx:
+        ctx.upload(snap)
+        got = ctx.drain(batch)
+        after, _ = ctx.download_snapshot()
+        assert np.array_equal(got.best_row, rows)
+        assert np.array_equal(got.score.view(np.uint32), scores.view(np.uint32))
+        assert np.array_equal(got.fit_count, counts)
+        assert np.array_equal(got.picks, picks)
+        assert np.array_equal(after, planes)
+        # state is carried: the drained snapshot answers a fresh batch like the rebuilt one
+        again = ctx.score(batch)
+    assert_same(again, oracle.score_packed(v.Snapshot(planes, snap.ndev, snap.type_names), batch), "after drain")
+    assert (rows >= 0).sum() > 0 and len(set(rows[rows >= 0].tolist())) < (rows >= 0).sum()  # nodes get reused
