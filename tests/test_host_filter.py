@@ -161,8 +161,15 @@ def test_filter_edge_behaviour(built):
     sch.close()
 
 
-def test_resource_request_defaults_cpu():
-    """GenerateResourceRequests defaults are exercised on the GPU tests above; here only that the
-    host library loads (no GPU needed for dlopen) or reports its absence loudly."""
-    import os
-    assert os.path.exists(v.hostlib.LIB_PATH) or True
+def test_host_mirror_without_gpu(built):
+    """CPU box: the C++ host mirror loads; a pod that asks for no vGPU passes every node without
+    touching the GPU (scheduler.go:357-370); a pod that does ask fails LOUDLY -- no CPU fallback"""
+    import torch
+    sch = v.hostlib.Scheduler(max_nodes=8)
+    sch.add_node("n0", [dict(ID=f"U{s}", Count=10, Devmem=32768, Devcore=100, Type="NVIDIA-Tesla V100", Numa=0) for s in range(8)])
+    r = sch.filter("p0", [{}, {}], {"nvidia.com/use-gputype": "a100"}, ["n0", "n1"])
+    assert r == dict(node=None, ids=None, failed={}, passed=["n0", "n1"])
+    if not torch.cuda.is_available():
+        with pytest.raises(RuntimeError, match="no usable GPU"):
+            sch.filter("p1", [{"gpu": 1}], {}, ["n0"])
+    sch.close()
