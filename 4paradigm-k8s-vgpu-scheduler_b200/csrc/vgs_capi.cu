@@ -681,23 +681,27 @@ static int score_locked(vgs_ctx *c) {
     for (int k = 0; k < 2; k++) CU(cudaStreamWaitEvent(c->side[k], c->ev_fork, 0));
     if (c->nA) {
         if (sliced && c->slice_on[0]) {
-            CU(launch_score_sliced(1, c->cfg.device, a, c->tab[0], c->n_types_used, c->d_status, c->side[0]));
-            c->launches += c->n_tiles ? kSlicedLaunches - 1 : 0;
-        } else
+            int nl = 0;
+            CU(launch_score_sliced(1, c->cfg.device, a, c->tab[0], c->n_types_used, c->d_status, c->side[0], &nl));
+            c->launches += nl;
+        } else {
             CU(launch_score_single(c->dm, true, c->cfg.device, a,
                                    reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqsA),
                                    reinterpret_cast<const int32_t *>(c->d_stage + c->off_origA), c->nA, c->side[0]));
-        if (c->n_tiles) c->launches++;
+            if (c->n_tiles) c->launches++;
+        }
     }
     if (c->nB) {
         if (sliced && c->slice_on[1]) {
-            CU(launch_score_sliced(2, c->cfg.device, a, c->tab[1], c->n_types_used, c->d_status, c->side[1]));
-            c->launches += c->n_tiles ? kSlicedLaunches - 1 : 0;
-        } else
+            int nl = 0;
+            CU(launch_score_sliced(2, c->cfg.device, a, c->tab[1], c->n_types_used, c->d_status, c->side[1], &nl));
+            c->launches += nl;
+        } else {
             CU(launch_score_single(c->dm, false, c->cfg.device, a,
                                    reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqsB),
                                    reinterpret_cast<const int32_t *>(c->d_stage + c->off_origB), c->nB, c->side[1]));
-        if (c->n_tiles) c->launches++;
+            if (c->n_tiles) c->launches++;
+        }
     }
     if (c->nC) {
         CU(launch_score_single(c->dm, false, c->cfg.device, a,

@@ -1478,7 +1478,7 @@ cudaError_t launch_score_general(int dm, int dev, const ScoreArgs &a, const DevR
 
 template <int NUMS>
 static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &tb, int n_types, uint32_t *status,
-                                   cudaStream_t st) {
+                                   cudaStream_t st, int *n_launched) {
     const int sms = sm_count(dev);
     // K1p: table rows + candidate scores per device, distinct scores -> classes
     cudaError_t e;
@@ -1488,6 +1488,7 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
     k1p_sort<<<1, 1024, 0, st>>>(tb);
     k1p_classify<NUMS><<<(nthreads + 127) / 128, 128, 0, st>>>(a.n_tiles, tb);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    *n_launched += 3;
 
     int warps = (tb.W + 31) / 32;
     if (warps > 4) warps = 4;
@@ -1532,6 +1533,7 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
             const int gx = (n_virtual + tiles_per - 1) / tiles_per;
             kernel<<<dim3(gx, gy), T, smem, st>>>(a.n_tiles, a.n_nodes, a.row_base, tb, n_types, tiles_per, phase,
                                                   scout, a.keys, a.counts, a.vfit, a.vscore, a.vwords);
+            *n_launched += 1;
             return cudaGetLastError();
         };
         if (a.n_tiles < 256) return launch(a.n_tiles, -1, 2); // small snapshot (< 8k nodes): one launch
@@ -1544,10 +1546,11 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
 }
 
 cudaError_t launch_score_sliced(int nums, int dev, const ScoreArgs &a, const SliceTab &tb, int n_types,
-                                uint32_t *status, cudaStream_t st) {
+                                uint32_t *status, cudaStream_t st, int *n_launched) {
+    *n_launched = 0;
     if (tb.n_pods <= 0 || a.n_tiles <= 0) return cudaSuccess;
-    return nums == 1 ? launch_sliced_t<1>(dev, a, tb, n_types, status, st)
-                     : launch_sliced_t<2>(dev, a, tb, n_types, status, st);
+    return nums == 1 ? launch_sliced_t<1>(dev, a, tb, n_types, status, st, n_launched)
+                     : launch_sliced_t<2>(dev, a, tb, n_types, status, st, n_launched);
 }
 
 cudaError_t launch_merge(const unsigned long long *gk, const int32_t *gc, int32_t n_shards, int32_t stride,

@@ -48,10 +48,10 @@ cudaError_t launch_score_general(int dm, int dev, const ScoreArgs &a, const DevR
 // K1t: fill the bit tables of a sliced class on the device (table region zeroed, value arrays uploaded)
 cudaError_t launch_slice_tables(const SliceTab &tb, const DevReq *dreq_class, cudaStream_t st);
 // pod-sliced K1 for one class (all pods: one request, Nums == nums in {1,2}, walk DM == 8)
-// (up to 5 launches: K1p collect / sort / classify, then the score kernel: scouts + main pass)
+// (K1p collect / sort / classify, then the score kernel as scouts + main pass, or one pass on a small
+// snapshot; *n_launched receives the number of kernels launched)
 cudaError_t launch_score_sliced(int nums, int dev, const ScoreArgs &a, const SliceTab &tb, int n_types,
-                                uint32_t *status, cudaStream_t st);
-constexpr int kSlicedLaunches = 5;
+                                uint32_t *status, cudaStream_t st, int *n_launched);
 cudaError_t launch_merge(const unsigned long long *gk, const int32_t *gc, int32_t n_shards,
                          int32_t stride, int32_t cstride, int32_t n_pods, unsigned long long *keys,
                          int32_t *counts, cudaStream_t st);
