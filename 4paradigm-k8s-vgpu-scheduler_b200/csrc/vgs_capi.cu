@@ -676,30 +676,35 @@ static int score_locked(vgs_ctx *c) {
     }
     const DevReq *dreq = reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqs);
     const bool sliced = c->snap_slice_ok && c->dm == 8;
-    // fork: class A and class B chains on side streams, the rest on `st`
-    CU(cudaEventRecord(c->ev_fork, c->st));
-    for (int k = 0; k < 2; k++) CU(cudaStreamWaitEvent(c->side[k], c->ev_fork, 0));
+    // fork: class A and class B chains on side streams, the rest on `st` -- only when there is
+    // more than one chain worth overlapping (a single-pod Filter stays on one stream)
+    const bool fork = (c->nA > 0) + (c->nB > 0) + (c->nC + c->nG > 0) > 1 && P >= 64;
+    cudaStream_t sA = fork ? c->side[0] : c->st, sB = fork ? c->side[1] : c->st;
+    if (fork) {
+        CU(cudaEventRecord(c->ev_fork, c->st));
+        for (int k = 0; k < 2; k++) CU(cudaStreamWaitEvent(c->side[k], c->ev_fork, 0));
+    }
     if (c->nA) {
         if (sliced && c->slice_on[0]) {
             int nl = 0;
-            CU(launch_score_sliced(1, c->cfg.device, a, c->tab[0], c->n_types_used, c->d_status, c->side[0], &nl));
+            CU(launch_score_sliced(1, c->cfg.device, a, c->tab[0], c->n_types_used, c->d_status, sA, &nl));
             c->launches += nl;
         } else {
             CU(launch_score_single(c->dm, true, c->cfg.device, a,
                                    reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqsA),
-                                   reinterpret_cast<const int32_t *>(c->d_stage + c->off_origA), c->nA, c->side[0]));
+                                   reinterpret_cast<const int32_t *>(c->d_stage + c->off_origA), c->nA, sA));
             if (c->n_tiles) c->launches++;
         }
     }
     if (c->nB) {
         if (sliced && c->slice_on[1]) {
             int nl = 0;
-            CU(launch_score_sliced(2, c->cfg.device, a, c->tab[1], c->n_types_used, c->d_status, c->side[1], &nl));
+            CU(launch_score_sliced(2, c->cfg.device, a, c->tab[1], c->n_types_used, c->d_status, sB, &nl));
             c->launches += nl;
         } else {
             CU(launch_score_single(c->dm, false, c->cfg.device, a,
                                    reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqsB),
-                                   reinterpret_cast<const int32_t *>(c->d_stage + c->off_origB), c->nB, c->side[1]));
+                                   reinterpret_cast<const int32_t *>(c->d_stage + c->off_origB), c->nB, sB));
             if (c->n_tiles) c->launches++;
         }
     }
@@ -714,7 +719,7 @@ static int score_locked(vgs_ctx *c) {
                                 reinterpret_cast<const GenPod *>(c->d_stage + c->off_podsG), c->nG, c->st));
         if (c->n_tiles) c->launches++;
     }
-    for (int k = 0; k < 2; k++) { // join
+    for (int k = 0; k < 2 && fork; k++) { // join
         CU(cudaEventRecord(c->ev_join[k], c->side[k]));
         CU(cudaStreamWaitEvent(c->st, c->ev_join[k], 0));
     }
