@@ -825,24 +825,20 @@ int vgs_drain_batch(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_r
     a.walk = c->d_walk, a.n_tiles = c->n_tiles, a.n_nodes = c->n_nodes, a.row_base = c->cfg.row_base;
     a.keys = c->d_keys, a.counts = c->d_counts;
     a.vfit = nullptr, a.vscore = nullptr, a.vwords = 0;
-    RawPlanesMut rm;
-    for (int f = 0; f < VGS_NUM_PLANES; f++) rm.p[f] = c->d_raw[f];
-    rm.ndev = c->d_ndev;
     const DevReq *dreq = reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqs);
     const vgs_pod *dpod = reinterpret_cast<const vgs_pod *>(c->d_stage + c->off_pods);
     const int32_t *dpick = reinterpret_cast<const int32_t *>(c->d_stage + c->off_pick);
     const GenPod *dall = reinterpret_cast<const GenPod *>(c->d_stage + c->off_genall);
     // one pod at a time, everything chained on the stream: score (the key/count slot of pod p is
-    // addressed through GenPod.orig) -> resolve -> commit into the raw planes -> re-prepare the row
+    // addressed through GenPod.orig) -> resolve + commit into the raw planes -> re-prepare the row
     for (int32_t p = 0; p < n_pods; p++) {
         CU(launch_score_general(c->dm, c->cfg.device, a, dreq, dall + p, 1, c->st));
         CU(launch_resolve(raw_const(c), c->n_nodes, c->dmax, c->cfg.row_base, dpod + p, dreq, dpick, 1,
-                          c->d_keys + p, c->d_counts + p, c->d_results + p, c->d_picks, c->d_status, c->st));
-        CU(launch_commit(rm, c->n_nodes, c->dmax, c->cfg.row_base, dpod + p, dreq, dpick, c->d_results + p,
-                         c->d_picks, c->d_rowlist, c->st));
+                          c->d_keys + p, c->d_counts + p, c->d_results + p, c->d_picks, c->d_status, c->st,
+                          c->d_rowlist)); // resolve + commit into the raw planes
         CU(launch_prepare(c->dm, raw_const(c), c->n_nodes, c->dmax, c->d_walk, c->n_tiles, c->d_status,
                           c->d_rowlist, 1, c->st));
-        c->launches += c->n_tiles ? 4 : 3;
+        c->launches += c->n_tiles ? 3 : 2;
     }
     rec(c, EV_SC1);
     c->scored = true;

@@ -1141,9 +1141,13 @@ __global__ void __launch_bounds__(64)
                const int32_t *__restrict__ pick_begin, int32_t n_pods,
                const unsigned long long *__restrict__ keys, const int32_t *__restrict__ counts,
                vgs_result *__restrict__ results, vgs_pick *__restrict__ picks,
-               uint32_t *__restrict__ status) {
+               uint32_t *__restrict__ status, int32_t *__restrict__ commit_rowlist) {
+    // commit_rowlist != nullptr (sequential drain, one pod per launch): the winner's picks are
+    // also folded into the raw planes (addPod, scheduler.go:280-297,394) and the touched row is
+    // named for re-preparation
     int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n_pods) return;
+    if (commit_rowlist) commit_rowlist[p] = -1;
     const unsigned long long key = keys[p];
     vgs_result res;
     res.fit_count = counts[p];
@@ -1167,18 +1171,21 @@ __global__ void __launch_bounds__(64)
     const int32_t nd = raw.ndev[row];
     const size_t base = (size_t)row * dmax;
     int32_t used[VGS_MAX_DEVICES], usedmem[VGS_MAX_DEVICES], usedcores[VGS_MAX_DEVICES];
-    int32_t ord[VGS_MAX_DEVICES];
-    for (int d = 0; d < nd; d++) {
-        used[d] = raw.p[VGS_PLANE_USED][base + d];
-        usedmem[d] = raw.p[VGS_PLANE_USEDMEM][base + d];
-        usedcores[d] = raw.p[VGS_PLANE_USEDCORES][base + d];
+    int32_t count[VGS_MAX_DEVICES], totalmem[VGS_MAX_DEVICES], totalcore[VGS_MAX_DEVICES];
+    int32_t numa[VGS_MAX_DEVICES], type[VGS_MAX_DEVICES], ord[VGS_MAX_DEVICES];
+#pragma unroll
+    for (int d = 0; d < VGS_MAX_DEVICES; d++) { // all loads issued at once: this thread is latency-bound
+        const bool on = d < nd;
+        used[d] = on ? raw.p[VGS_PLANE_USED][base + d] : 0;
+        usedmem[d] = on ? raw.p[VGS_PLANE_USEDMEM][base + d] : 0;
+        usedcores[d] = on ? raw.p[VGS_PLANE_USEDCORES][base + d] : 0;
+        count[d] = on ? raw.p[VGS_PLANE_COUNT][base + d] : 0;
+        totalmem[d] = on ? raw.p[VGS_PLANE_TOTALMEM][base + d] : 0;
+        totalcore[d] = on ? raw.p[VGS_PLANE_TOTALCORE][base + d] : 0;
+        numa[d] = on ? raw.p[VGS_PLANE_NUMA][base + d] : 0;
+        type[d] = on ? raw.p[VGS_PLANE_TYPEID][base + d] : 0;
         ord[d] = d;
     }
-    const int32_t *count = raw.p[VGS_PLANE_COUNT] + base;
-    const int32_t *totalmem = raw.p[VGS_PLANE_TOTALMEM] + base;
-    const int32_t *totalcore = raw.p[VGS_PLANE_TOTALCORE] + base;
-    const int32_t *numa = raw.p[VGS_PLANE_NUMA] + base;
-    const int32_t *type = raw.p[VGS_PLANE_TYPEID] + base;
 
     float score = 0.0f;
     bool alive = true, in_ctr = false;
@@ -1256,6 +1263,14 @@ __global__ void __launch_bounds__(64)
             picks[pb + t] = pk;
         }
     }
+    if (commit_rowlist && alive) {
+        for (int d = 0; d < nd; d++) { // the mutated copies ARE the committed state
+            const_cast<int32_t *>(raw.p[VGS_PLANE_USED])[base + d] = used[d];
+            const_cast<int32_t *>(raw.p[VGS_PLANE_USEDMEM])[base + d] = usedmem[d];
+            const_cast<int32_t *>(raw.p[VGS_PLANE_USEDCORES])[base + d] = usedcores[d];
+        }
+        commit_rowlist[p] = row;
+    }
     if (alive && in_ctr) score = __fadd_rn(score, container_score(total, free_, nd - sums));
     if (!alive || __float_as_uint(score) != kbits) atomicOr(status, S_MISMATCH);
 }
@@ -1284,37 +1299,6 @@ __global__ void k4_apply_delta(RawPlanesMut raw, int32_t n_nodes, int32_t dmax, 
     atomicAdd(&raw.p[VGS_PLANE_USEDMEM][x], d.d_usedmem);
     atomicAdd(&raw.p[VGS_PLANE_USEDCORES][x], d.d_usedcores);
     rowlist[i] = row;
-}
-
-// ------------------------------------------------------------------------------------
-// K5: commit one pod's winner into the raw planes (what addPod does to the next snapshot,
-// scheduler.go:280-297,394) and name the row whose walk tile must be re-prepared.  One thread.
-// ------------------------------------------------------------------------------------
-__global__ void k5_commit(RawPlanesMut raw, int32_t n_nodes, int32_t dmax, int32_t row_base,
-                          const vgs_pod *__restrict__ pod, const DevReq *__restrict__ reqs,
-                          const int32_t *__restrict__ pick_begin, const vgs_result *__restrict__ result,
-                          const vgs_pick *__restrict__ picks, int32_t *__restrict__ rowlist) {
-    if (blockIdx.x != 0 || threadIdx.x != 0) return;
-    rowlist[0] = -1;
-    const int32_t row = result->best_row - row_base;
-    if (result->best_row < 0 || row < 0 || row >= n_nodes) return;
-    for (int r = pod->req_begin; r < pod->req_begin + pod->n_reqs; r++) {
-        const int32_t n = reqs[r].nums, pb = pick_begin[r];
-        for (int t = 0; t < n; t++) {
-            const vgs_pick pk = picks[pb + t];
-            const size_t x = (size_t)row * dmax + pk.slot;
-            raw.p[VGS_PLANE_USED][x] += 1;
-            raw.p[VGS_PLANE_USEDMEM][x] += pk.usedmem;
-            raw.p[VGS_PLANE_USEDCORES][x] += pk.usedcores;
-        }
-    }
-    rowlist[0] = row;
-}
-cudaError_t launch_commit(const RawPlanesMut &raw, int32_t n_nodes, int32_t dmax, int32_t row_base,
-                          const vgs_pod *pod, const DevReq *reqs, const int32_t *pick_begin,
-                          const vgs_result *result, const vgs_pick *picks, int32_t *rowlist, cudaStream_t st) {
-    k5_commit<<<1, 32, 0, st>>>(raw, n_nodes, dmax, row_base, pod, reqs, pick_begin, result, picks, rowlist);
-    return cudaGetLastError();
 }
 
 // ------------------------------------------------------------------------------------
@@ -1564,10 +1548,11 @@ cudaError_t launch_merge(const unsigned long long *gk, const int32_t *gc, int32_
 cudaError_t launch_resolve(const RawPlanes &raw, int32_t n_nodes, int32_t dmax, int32_t row_base,
                            const vgs_pod *pods, const DevReq *reqs, const int32_t *pick_begin,
                            int32_t n_pods, const unsigned long long *keys, const int32_t *counts,
-                           vgs_result *results, vgs_pick *picks, uint32_t *status, cudaStream_t st) {
+                           vgs_result *results, vgs_pick *picks, uint32_t *status, cudaStream_t st,
+                           int32_t *commit_rowlist) {
     if (n_pods <= 0) return cudaSuccess;
     k3_resolve<<<(n_pods + 63) / 64, 64, 0, st>>>(raw, n_nodes, dmax, row_base, pods, reqs, pick_begin,
-                                                 n_pods, keys, counts, results, picks, status);
+                                                 n_pods, keys, counts, results, picks, status, commit_rowlist);
     return cudaGetLastError();
 }
 

@@ -30,10 +30,6 @@ struct ScoreArgs {
 inline int walk_dm(int dmax) { return dmax <= 8 ? 8 : 12; }
 inline size_t walk_int4_per_tile(int dm) { return (size_t)kWalkWords * (dm / 4) * kWarp; }
 
-// K5: fold one pod's winner (its vgs_result + picks) into the raw planes; rowlist[0] = touched row or -1
-cudaError_t launch_commit(const RawPlanesMut &raw, int32_t n_nodes, int32_t dmax, int32_t row_base,
-                          const vgs_pod *pod, const DevReq *reqs, const int32_t *pick_begin,
-                          const vgs_result *result, const vgs_pick *picks, int32_t *rowlist, cudaStream_t st);
 // zero-copy upload: src planes are host-pinned (device-accessible) memory, 16-byte aligned
 cudaError_t launch_copy_planes(const int32_t *const src[VGS_NUM_PLANES], const int32_t *src_ndev,
                                int32_t *const dst[VGS_NUM_PLANES], int32_t *dst_ndev, size_t cells, size_t n_nodes,
@@ -58,7 +54,8 @@ cudaError_t launch_merge(const unsigned long long *gk, const int32_t *gc, int32_
 cudaError_t launch_resolve(const RawPlanes &raw, int32_t n_nodes, int32_t dmax, int32_t row_base,
                            const vgs_pod *pods, const DevReq *reqs, const int32_t *pick_begin,
                            int32_t n_pods, const unsigned long long *keys, const int32_t *counts,
-                           vgs_result *results, vgs_pick *picks, uint32_t *status, cudaStream_t st);
+                           vgs_result *results, vgs_pick *picks, uint32_t *status, cudaStream_t st,
+                           int32_t *commit_rowlist = nullptr);
 cudaError_t launch_delta(const RawPlanesMut &raw, int32_t n_nodes, int32_t dmax, int32_t row_base,
                          const vgs_delta *deltas, int32_t n, int32_t *rowlist, uint32_t *status,
                          cudaStream_t st);
