@@ -653,8 +653,12 @@ static int score_locked(vgs_ctx *c) {
     const int32_t P = c->n_pods;
     rec(c, EV_SC0);
     if (P > 0) {
-        CU(cudaMemsetAsync(c->d_keys, 0, (size_t)P * sizeof(unsigned long long), c->st));
-        CU(cudaMemsetAsync(c->d_counts, 0, (size_t)P * sizeof(int32_t), c->st));
+        if (P * 4 >= c->cfg.max_pods) { // keys and counts are one block: clear it in one go
+            CU(cudaMemsetAsync(c->d_keys, 0, (size_t)c->cfg.max_pods * 12, c->st));
+        } else {
+            CU(cudaMemsetAsync(c->d_keys, 0, (size_t)P * sizeof(unsigned long long), c->st));
+            CU(cudaMemsetAsync(c->d_counts, 0, (size_t)P * sizeof(int32_t), c->st));
+        }
     }
     ScoreArgs a;
     a.walk = c->d_walk;
