@@ -437,3 +437,38 @@ def test_drain_equals_sequential_filters(built, cfg, n, p):
         again = ctx.score(batch)
     assert_same(again, oracle.score_packed(v.Snapshot(planes, snap.ndev, snap.type_names), batch), "after drain")
     assert (rows >= 0).sum() > 0 and len(set(rows[rows >= 0].tolist())) < (rows >= 0).sum()  # nodes get reused
+
+
+def test_empty_batch_and_concurrent_callers(built):
+    """n_pods = 0 is a no-op; calls on one context from several host threads are serialised by the
+    library (net/http runs each /filter in its own goroutine) and all get the right answer"""
+    import threading
+    snap, batch = v.workload.make_config("cfg3", 2000, 96)
+    want = oracle.score_packed(snap, batch)
+    with v.Context(max_nodes=2000, max_pods=96) as ctx:
+        ctx.upload(snap)
+        r, p = ctx.score_packed(np.zeros(0, v.capi.POD_DTYPE), np.zeros(0, v.capi.REQ_DTYPE))
+        assert len(r) == 0 and len(p) == 0
+        pods, reqs = v.capi.pack_batch(batch, snap.type_names)
+        out, errs = {}, []
+
+        def worker(i):
+            try:
+                for _ in range(5):
+                    res = np.zeros(len(pods), dtype=v.capi.RESULT_DTYPE)
+                    pk = np.zeros(int(reqs["nums"].sum()), dtype=v.capi.PICK_DTYPE)
+                    rc = ctx.lib.vgs_score_batch(ctx.h, len(pods), pods.ctypes.data, len(reqs), reqs.ctypes.data,
+                                                 res.ctypes.data, pk.ctypes.data)
+                    assert rc == 0
+                    out[i] = (res, pk)
+            except Exception as e:  # pragma: no cover
+                errs.append(e)
+
+        ts = [threading.Thread(target=worker, args=(i,)) for i in range(4)]
+        [t.start() for t in ts]
+        [t.join() for t in ts]
+        assert not errs
+        for res, pk in out.values():
+            assert np.array_equal(res["best_row"], want.best_row)
+            assert np.array_equal(res["score"].view(np.uint32), want.score.view(np.uint32))
+            assert np.array_equal(np.stack([pk["slot"], pk["usedmem"], pk["usedcores"]], 1), want.picks)
