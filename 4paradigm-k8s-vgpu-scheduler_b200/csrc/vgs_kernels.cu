@@ -1,12 +1,18 @@
 // vgs_kernels.cu -- sm_100a kernels of libvgpuscore.so
 //
-//   K0 k0_prepare      raw planes -> walk-ordered warp tiles (+ validation)
-//   K1 k1_score_single pods with ONE request: thread = node (state in registers),
-//                      loop over a pod chunk staged in shared memory
-//      k1_score_general pods with several requests / numa-bind multi-device requests
-//   K2 k2_merge        max over shards of the per-pod candidate keys
-//   K3 k3_resolve      re-run the winner node of every pod, emit the picks
-//   K4 k4_apply_delta  scatter usage deltas into the raw planes
+//   K0  k0_prepare        raw planes -> walk-ordered warp tiles (+ validation)
+//   K1t k1t_fill/prefix   bit tables of a pod-sliced class (one bit per pod)
+//   K1p k1p_collect/sort/classify   per device: table rows it selects, candidate scores, score class
+//   K1  k1_score_sliced   classes of >= 512 single-request pods asking for 1 or 2 devices:
+//                         32 pods per register, the CTA walks one node at a time, SliceDev tiles
+//                         staged with cp.async.bulk + mbarrier; scout launch + main launch
+//       k1_score_single   per (pod, node) pair: thread = node (state in registers), loop over a
+//                         pod chunk staged in shared memory
+//       k1_score_general  any number of containers / requests, numa-bind
+//   K2  k2_merge          max over shards of the per-pod candidate keys
+//   K3  k3_resolve        re-run the winner node of every pod, emit the picks (drain: also commit)
+//   K4  k4_apply_delta    scatter usage deltas into the raw planes
+//       k_copy_planes     pinned host planes -> device planes over PCIe (zero-copy upload)
 //
 // Reference semantics restated (never copied): pkg/scheduler/score.go:45-50 (device
 // order), :86-152 (fitInCertainDevice), :154-181 (fitInDevices), :183-214 (calcScore),
