@@ -351,14 +351,12 @@ __global__ void __launch_bounds__(128)
         if (tile >= n_tiles) continue;
 
         const int4 *tp = walk + (size_t)tile * kWalkWords * (DM / 4) * kWarp;
-        int32_t totalmem[DM], freemem0[DM], freecores0[DM], meta0[DM], count[DM], freeslots0[DM];
+        // immutable per node: stays in registers for the whole item
+        int32_t totalmem[DM], count[DM];
         load_word<DM>(tp, W_TOTALMEM, lane, totalmem);
-        load_word<DM>(tp, W_FREEMEM, lane, freemem0);
-        load_word<DM>(tp, W_FREECORES, lane, freecores0);
-        load_word<DM>(tp, W_META, lane, meta0);
         load_word<DM>(tp, W_COUNT, lane, count);
-        load_word<DM>(tp, W_FREESLOTS, lane, freeslots0);
-        const int32_t ndev = (meta0[0] >> M_NDEV_SHIFT) & 15;
+        const int32_t ndev = (__ldg(reinterpret_cast<const int32_t *>(&tp[(W_META * (DM / 4)) * kWarp + lane])) >>
+                              M_NDEV_SHIFT) & 15;
         const uint32_t row0 = (uint32_t)(row_base + tile * kWarp);
         const int row = tile * kWarp + lane;
 
@@ -368,14 +366,17 @@ __global__ void __launch_bounds__(128)
             const int kend = min(kWarp, npod - pp);
             for (int k = 0; k < kend; k++) {
                 const GenPod pod = pods[pod0 + pp + k];
-                int32_t fm[DM], fc[DM], fs[DM], pos[DM];
+                // the pod's private, mutable copy of the node: re-read from the (L1-resident) walk
+                // tile instead of being kept twice in registers
+                int32_t fm[DM], fc[DM], fs[DM], pos[DM], mt_[DM];
                 uint32_t mt[DM];
+                load_word<DM>(tp, W_FREEMEM, lane, fm);
+                load_word<DM>(tp, W_FREECORES, lane, fc);
+                load_word<DM>(tp, W_FREESLOTS, lane, fs);
+                load_word<DM>(tp, W_META, lane, mt_);
 #pragma unroll
                 for (int j = 0; j < DM; j++) {
-                    fm[j] = freemem0[j];
-                    fc[j] = freecores0[j];
-                    fs[j] = freeslots0[j];
-                    mt[j] = (uint32_t)meta0[j];
+                    mt[j] = (uint32_t)mt_[j];
                     pos[j] = DM - 1 - j;
                 }
                 bool alive = true, in_ctr = false;
