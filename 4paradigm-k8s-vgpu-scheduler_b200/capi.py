@@ -10,7 +10,7 @@ from typing import Dict, List, Optional, Tuple
 
 import numpy as np
 
-from .model import ANNO_DCU_NOUSE, ANNO_DCU_USE, ANNO_NOUSE, ANNO_NUMA, ANNO_USE, BatchResult, PodBatch, Snapshot
+from .model import ANNO_DCU_NOUSE, ANNO_DCU_USE, ANNO_MLU_NOUSE, ANNO_MLU_USE, ANNO_NOUSE, ANNO_NUMA, ANNO_USE, BatchResult, PodBatch, Snapshot
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "csrc", "libvgpuscore.so")
@@ -19,12 +19,15 @@ VGS_OK = 0
 VGS_EINVAL, VGS_ECUDA, VGS_ETOOBIG, VGS_EDMAX, VGS_ERANGE, VGS_ESTATE, VGS_EINTERNAL = range(-1, -8, -1)
 VGS_ELIMIT = -8
 VGS_REQ_NUMA_BIND = 1
+VGS_REQ_IDLE_SHARE = 2
+VGS_TYPE_IDLE_SHARE = 1
 NOALLOC_MAX_NODES, NOALLOC_MAX_DEVICES, NOALLOC_MAX_PODS, NOALLOC_MAX_REQS = 16384, 8, 256, 1024
 
 # every symbol include/vgpuscore.h declares
 EXPORTS = (
     "vgs_abi_version", "vgs_strerror", "vgs_init", "vgs_destroy", "vgs_last_error",
     "vgs_snapshot_upload", "vgs_snapshot_set_device", "vgs_snapshot_refresh", "vgs_snapshot_delta", "vgs_snapshot_download",
+    "vgs_snapshot_type_flags", "vgs_host_typemask_mlu", "vgs_host_type_flags",
     "vgs_score_batch", "vgs_drain_batch", "vgs_pods_upload", "vgs_score_resident", "vgs_resolve_resident",
     "vgs_results_download", "vgs_sync", "vgs_keys_device", "vgs_keys_merge", "vgs_results_device",
     "vgs_verify_download", "vgs_last_timing", "vgs_host_typemask", "vgs_host_numa_bind",
@@ -83,6 +86,12 @@ def load_library() -> C.CDLL:
     lib.vgs_snapshot_upload.argtypes = [vp, i32, i32, C.POINTER(vp), vp, u64p]
     lib.vgs_snapshot_set_device.argtypes = [vp, i32, i32, C.POINTER(vp), vp, u64p]
     lib.vgs_snapshot_refresh.argtypes = [vp]
+    lib.vgs_snapshot_type_flags.argtypes = [vp, i32, vp]
+    lib.vgs_host_typemask_mlu.argtypes = [i32, C.c_char_p, C.c_char_p, C.POINTER(C.c_char_p), i32,
+                                          C.POINTER(C.c_uint32)]
+    lib.vgs_host_typemask_mlu.restype = C.c_uint64
+    lib.vgs_host_type_flags.argtypes = [C.c_char_p]
+    lib.vgs_host_type_flags.restype = C.c_uint32
     lib.vgs_snapshot_delta.argtypes = [vp, i32, vp]
     lib.vgs_snapshot_download.argtypes = [vp, C.POINTER(vp), vp]
     lib.vgs_score_batch.argtypes = [vp, i32, vp, i32, vp, vp, vp]
@@ -118,6 +127,20 @@ def host_typemask(req_type: str, annos: Dict[str, str], type_names: List[str]) -
     arr = (C.c_char_p * len(type_names))(*[t.encode("utf-8") for t in type_names])
     use, nouse = (ANNO_DCU_USE, ANNO_DCU_NOUSE) if req_type == "DCU" else (ANNO_USE, ANNO_NOUSE)
     return int(lib.vgs_host_typemask(_b(req_type), _b(annos.get(use)), _b(annos.get(nouse)), arr, len(type_names)))
+
+
+def host_typemask_mlu(memreq: int, annos: Dict[str, str], type_names: List[str]) -> Tuple[int, int]:
+    """Cambricon request -> (typemask, request flags)"""
+    lib = load_library()
+    arr = (C.c_char_p * len(type_names))(*[t.encode("utf-8") for t in type_names])
+    fl = C.c_uint32()
+    m = lib.vgs_host_typemask_mlu(int(memreq), _b(annos.get(ANNO_MLU_USE)), _b(annos.get(ANNO_MLU_NOUSE)), arr,
+                                  len(type_names), C.byref(fl))
+    return int(m), int(fl.value)
+
+
+def host_type_flags(type_name: str) -> int:
+    return int(load_library().vgs_host_type_flags(type_name.encode("utf-8")))
 
 
 def host_numa_bind(annos: Dict[str, str]) -> int:
@@ -181,6 +204,14 @@ def pack_batch(batch: PodBatch, type_names: List[str]):
         reqs["ctr"] = ctr_of_req - first_ctr[pod_of_req]
         for r in range(batch.n_reqs):
             an = batch.annos[int(pod_of_req[r])]
+            if batch.req_type[r] == "MLU":  # the mask depends on Memreq (cambricon/device.go:94-99)
+                key = ("MLU", int(batch.memreq[r]) != 0, an.get(ANNO_MLU_USE), an.get(ANNO_MLU_NOUSE))
+                mf = cache.get(key)
+                if mf is None:
+                    mf = host_typemask_mlu(int(batch.memreq[r]), an, type_names)
+                    cache[key] = mf
+                reqs["typemask"][r], reqs["flags"][r] = mf
+                continue
             key = (batch.req_type[r], an.get(ANNO_USE), an.get(ANNO_NOUSE), an.get(ANNO_DCU_USE), an.get(ANNO_DCU_NOUSE))
             m = cache.get(key)
             if m is None:
@@ -255,6 +286,7 @@ class Context:
 
     # -- snapshot -------------------------------------------------------------------
     def upload(self, snap: Snapshot) -> int:
+        self.set_type_flags([host_type_flags(t) for t in snap.type_names])
         ptrs = (C.c_void_p * 8)(*[snap.planes[f].ctypes.data for f in range(8)])
         ver = C.c_uint64()
         self._check(self.lib.vgs_snapshot_upload(self.h, snap.n_nodes, snap.dmax, ptrs, snap.ndev.ctypes.data,
@@ -273,6 +305,11 @@ class Context:
 
     def refresh(self):
         self._check(self.lib.vgs_snapshot_refresh(self.h))
+
+    def set_type_flags(self, flags: List[int]):
+        """vgs_snapshot_type_flags: VGS_TYPE_* per type id"""
+        arr = np.ascontiguousarray(flags, dtype=np.uint32)
+        self._check(self.lib.vgs_snapshot_type_flags(self.h, len(arr), arr.ctypes.data if len(arr) else None))
 
     def delta(self, deltas: np.ndarray):
         deltas = np.ascontiguousarray(deltas, dtype=DELTA_DTYPE)

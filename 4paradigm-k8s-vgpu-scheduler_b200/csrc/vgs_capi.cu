@@ -53,6 +53,7 @@ struct vgs_ctx {
     int32_t n_nodes = 0, dmax = 0, n_tiles = 0;
     bool have_snapshot = false;
     uint64_t version = 0;
+    uint64_t idle_types = 0; // vgs_snapshot_type_flags: types carrying VGS_TYPE_IDLE_SHARE
     vgs_delta *d_deltas = nullptr, *h_deltas = nullptr;
     int32_t *d_rowlist = nullptr;
     int32_t max_deltas = 0;
@@ -124,6 +125,7 @@ RawPlanes raw_const(const vgs_ctx *c) {
     RawPlanes r;
     for (int f = 0; f < VGS_NUM_PLANES; f++) r.p[f] = c->d_raw[f];
     r.ndev = c->d_ndev;
+    r.idle_types = c->idle_types;
     return r;
 }
 
@@ -387,6 +389,22 @@ int vgs_snapshot_set_device(vgs_ctx *c, int32_t n_nodes, int32_t dmax,
     return snapshot_common(c, n_nodes, dmax, dev_planes, dev_ndev, cudaMemcpyDeviceToDevice, out_version);
 }
 
+int vgs_snapshot_type_flags(vgs_ctx *c, int32_t n_types, const uint32_t *flags) {
+    if (!c) return VGS_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard g(c->cfg.device);
+    if (n_types < 0 || n_types > VGS_MAX_TYPES || (n_types > 0 && !flags))
+        return fail(c, VGS_EINVAL, "type flags: n_types outside [0, VGS_MAX_TYPES]");
+    uint64_t m = 0;
+    for (int32_t t = 0; t < n_types; t++)
+        if (flags[t] & VGS_TYPE_IDLE_SHARE) m |= 1ull << t;
+    if (m == c->idle_types) return VGS_OK;
+    c->idle_types = m;
+    if (!c->have_snapshot) return VGS_OK;
+    c->scored = c->resolved = false; // the walk copy changes under a resident batch
+    return prepare_all(c);
+}
+
 int vgs_snapshot_refresh(vgs_ctx *c) {
     if (!c) return VGS_EINVAL;
     std::lock_guard<std::mutex> lk(c->mu);
@@ -565,6 +583,10 @@ static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, i
         if (q.mempct != VGS_MEMPCT_UNSET && q.memreq == 0) d.flags |= R_USEPCT; // score.go:117
         if (q.flags & VGS_REQ_NUMA_BIND) d.flags |= R_NUMA;
         d.blockmask = M_NOFREE | M_PAD;
+        if (q.flags & VGS_REQ_IDLE_SHARE) { // cambricon/device.go:97-99
+            d.flags |= R_IDLE;
+            d.blockmask |= M_BUSY370;
+        }
         if (q.coresreq == 100) d.blockmask |= M_EXCL; // score.go:128
         if (q.coresreq == 0) d.blockmask |= M_FULL;   // score.go:132
         if (q.coresreq > 100) d.blockmask |= M_ALWAYS; // score.go:110-113: never fits
@@ -595,13 +617,16 @@ static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, i
         GenPod *hall = reinterpret_cast<GenPod *>(c->h_stage + c->off_genall);
         hall[p].req_begin = pd.req_begin, hall[p].n_reqs = pd.n_reqs, hall[p].orig = p, hall[p].pad = 0;
         const DevReq &first = hreq[pd.req_begin];
-        if (pd.n_reqs == 1 && first.nums == 1) {
+        // the bit tables of the sliced classes know nothing of M_BUSY370: idle-share requests
+        // take the per-pair kernel, which tests the whole blockmask
+        const bool idle = first.flags & R_IDLE;
+        if (pd.n_reqs == 1 && first.nums == 1 && !idle) {
             hA[nA] = first; // numa-bind cannot matter for a single device
             hoA[nA++] = p;
-        } else if (pd.n_reqs == 1 && !(first.flags & R_NUMA) && first.nums == 2) {
+        } else if (pd.n_reqs == 1 && !(first.flags & R_NUMA) && first.nums == 2 && !idle) {
             hB[nB] = first;
             hoB[nB++] = p;
-        } else if (pd.n_reqs == 1 && !(first.flags & R_NUMA)) {
+        } else if (pd.n_reqs == 1 && (!(first.flags & R_NUMA) || first.nums == 1)) {
             hC[nC] = first;
             hoC[nC++] = p;
         } else {

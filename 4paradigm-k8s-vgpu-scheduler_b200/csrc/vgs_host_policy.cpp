@@ -100,11 +100,32 @@ uint64_t vgs_host_typemask(const char *req_type, const char *use_gputype, const 
         // (hygon/device.go:79-84) share the same use/nouse list logic -- the caller passes the
         // vendor's own annotation values (nvidia.com/{use,nouse}-gputype or
         // hygon.com/{use,nouse}-dcutype).  Cambricon's CheckType depends on d.Used and
-        // n.Memreq, so it cannot be a static mask; any other type is "Unrecognized device".
+        // n.Memreq: vgs_host_typemask_mlu below.  Any other type is "Unrecognized device".
         if (rt != "NVIDIA" && rt != "DCU") continue;
         if (gpu_type_allowed(use_gputype, nouse_gputype, card)) mask |= 1ull << t;
     }
     return mask;
+}
+
+uint64_t vgs_host_typemask_mlu(int32_t memreq, const char *use_mlutype, const char *nouse_mlutype,
+                               const char *const *types, int32_t n_types, uint32_t *req_flags) {
+    if (req_flags) *req_flags = memreq == 0 ? VGS_REQ_IDLE_SHARE : 0u; // cambricon/device.go:97-99
+    uint64_t mask = 0;
+    if (!types) return 0;
+    if (n_types > VGS_MAX_TYPES) n_types = VGS_MAX_TYPES;
+    for (int32_t t = 0; t < n_types; t++) {
+        if (!types[t]) continue;
+        const std::string card(types[t]);
+        if (!contains(card, "MLU")) continue;                     // score.go:73 with n.Type == "MLU"
+        if (!contains(card, "370") && memreq != 0) continue;      // cambricon/device.go:94-96
+        if (gpu_type_allowed(use_mlutype, nouse_mlutype, card)) mask |= 1ull << t; // checkMLUtype :60-91
+    }
+    return mask;
+}
+
+uint32_t vgs_host_type_flags(const char *type_name) {
+    if (!type_name) return 0;
+    return contains(std::string(type_name), "370") ? VGS_TYPE_IDLE_SHARE : 0u;
 }
 
 int32_t vgs_host_numa_bind(const char *v) {

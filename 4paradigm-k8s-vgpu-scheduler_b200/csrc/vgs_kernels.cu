@@ -169,6 +169,7 @@ __global__ void __launch_bounds__(128)
             if (totalcore[j] != 0) meta |= M_CORENZ;
             if (totalcore[j] == 100 && used[j] > 0) meta |= M_EXCL;
             if (totalcore[j] != 0 && usedcores[j] == totalcore[j]) meta |= M_FULL;
+            if (raw.idle_types >> type[j] & 1ull) meta |= used[j] > 0 ? (M_T370 | M_BUSY370) : M_T370;
             float s1 = fj > 0 ? container_score(count[j], fj, nd - 1) : 0.0f;
             put(W_TOTALMEM, w, totalmem[j]);
             put(W_FREEMEM, w, wrap_sub(totalmem[j], usedmem[j]));
@@ -475,6 +476,7 @@ __global__ void __launch_bounds__(128)
                             if (fs[j] <= 0) m |= M_NOFREE;
                             if (m & M_IS100) m |= M_EXCL;
                             if ((m & M_CORENZ) && fc[j] == 0) m |= M_FULL;
+                            m |= (m >> 1) & M_BUSY370; // Used > 0 from here on
                             mt[j] = m;
                         }
                         if constexpr (!decltype(LAST)::value) pos[j] = npos[j];
@@ -1228,6 +1230,8 @@ __global__ void __launch_bounds__(64)
             const int d = ord[i];
             uint32_t t = (uint32_t)type[d];
             if (!(((t & 32u) ? rq.mask_hi : rq.mask_lo) >> (t & 31u) & 1u)) continue;
+            if ((rq.flags & R_IDLE) && (raw.idle_types >> t & 1ull) && used[d] > 0)
+                continue; // cambricon/device.go:97-99, part of the type check
             if ((rq.flags & R_NUMA) && prevnuma != numa[d]) { // :99-104
                 left = rq.nums;
                 prevnuma = numa[d];

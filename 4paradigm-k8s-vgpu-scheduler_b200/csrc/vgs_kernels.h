@@ -11,6 +11,7 @@ namespace vgs {
 struct RawPlanes {
     const int32_t *p[VGS_NUM_PLANES];
     const int32_t *ndev;
+    uint64_t idle_types; // bit t: type id t carries VGS_TYPE_IDLE_SHARE
 };
 struct RawPlanesMut {
     int32_t *p[VGS_NUM_PLANES];

@@ -46,6 +46,9 @@ constexpr uint32_t M_FULL = 1u << 20;     // Totalcore != 0 && Usedcores == Tota
 constexpr uint32_t M_PAD = 1u << 21;      // slot >= len(node.Devices): not a device
 constexpr uint32_t M_IS100 = 1u << 22;    // Totalcore == 100
 constexpr uint32_t M_CORENZ = 1u << 23;   // Totalcore != 0
+constexpr uint32_t M_BUSY370 = 1u << 24;  // M_T370 && Used > 0            (cambricon/device.go:97)
+constexpr uint32_t M_T370 = 1u << 25;     // type flagged VGS_TYPE_IDLE_SHARE ("370" in d.Type)
+static_assert(M_BUSY370 == (M_T370 >> 1), "the general kernel derives one from the other by a shift");
 constexpr uint32_t M_ALWAYS = 1u << 31;   // always set (lets a request block every device)
 
 // ordering key of a device inside one node: (numa rank, free share slots, previous position)
@@ -66,6 +69,7 @@ struct __align__(16) DevReq {
 constexpr uint32_t R_NUMA = 1u;   // numa-bind asserted
 constexpr uint32_t R_USEPCT = 2u; // memreq = Totalmem * pct / 100 per device
 constexpr uint32_t R_NEWCTR = 4u; // first request of a container
+constexpr uint32_t R_IDLE = 8u;   // VGS_REQ_IDLE_SHARE (K3's plain restatement; the score kernels see M_BUSY370 in blockmask)
 
 // pod of the general (multi-request) class
 struct GenPod {

@@ -109,6 +109,7 @@ extern "C" int vgs_score_batch_noalloc(int32_t device, void *stream, int32_t n_n
     int64_t total_picks = 0;
     for (int32_t r = 0; r < n_reqs; r++) {
         if (reqs[r].nums < 1) return VGS_EINVAL;
+        if (reqs[r].flags & VGS_REQ_IDLE_SHARE) return VGS_EINVAL; // no type-flag input on this entry
         hreq[r] = to_dev_req(reqs[r]);
         hpick[r] = (int32_t)total_picks;
         total_picks += reqs[r].nums;
@@ -182,6 +183,7 @@ extern "C" int vgs_score_batch_noalloc(int32_t device, void *stream, int32_t n_n
     RawPlanes raw;
     for (int f = 0; f < VGS_NUM_PLANES; f++) raw.p[f] = dev_planes[f];
     raw.ndev = dev_ndev;
+    raw.idle_types = 0;
     const int32_t n_tiles = (n_nodes + kWarp - 1) / kWarp;
     NA(launch_prepare(8, raw, n_nodes, dmax, d_walk, n_tiles, d_status, nullptr, 0, st));
     ScoreArgs a;

@@ -59,12 +59,47 @@ ContainerDeviceRequest GenerateResourceRequests(const Container &ctr, const Conf
     return r;
 }
 
-// ---- pkg/k8sutil/pod.go:26-40 (vendors: NVIDIA) --------------------------------------------
+// ---- pkg/device/cambricon/device.go:106-137 ---------------------------------------------------
+ContainerDeviceRequest GenerateResourceRequestsMLU(const Container &ctr, const Config &cfg) {
+    int64_t n;
+    if (!lookup(ctr, cfg.MLUResourceCount, &n)) return ContainerDeviceRequest{};
+    int64_t v;
+    int memnum = 0;
+    if (lookup(ctr, cfg.MLUResourceMemory, &v)) memnum = (int)v;
+    ContainerDeviceRequest r; // MemPercentagereq and Coresreq stay at Go's zero value
+    r.Nums = (int32_t)n;
+    r.Type = "MLU";
+    r.Memreq = (int32_t)memnum;
+    return r;
+}
+
+// ---- pkg/device/hygon/device.go:86-135 -----------------------------------------------------------
+ContainerDeviceRequest GenerateResourceRequestsDCU(const Container &ctr, const Config &cfg) {
+    int64_t n;
+    if (!lookup(ctr, cfg.DCUResourceCount, &n)) return ContainerDeviceRequest{};
+    int64_t v;
+    int memnum = 0;
+    if (lookup(ctr, cfg.DCUResourceMemory, &v)) memnum = (int)v;
+    int32_t corenum = 0;
+    if (lookup(ctr, cfg.DCUResourceCores, &v)) corenum = (int32_t)v;
+    ContainerDeviceRequest r;
+    r.Nums = (int32_t)n;
+    r.Type = "DCU";
+    r.Memreq = (int32_t)memnum;
+    r.MemPercentagereq = memnum == 0 ? 100 : 0; // :121-124
+    r.Coresreq = corenum;
+    return r;
+}
+
+// ---- pkg/k8sutil/pod.go:26-40 -------------------------------------------------------------------
 std::vector<std::vector<ContainerDeviceRequest>> Resourcereqs(const Pod &pod, const Config &cfg) {
     std::vector<std::vector<ContainerDeviceRequest>> counts(pod.Containers.size());
     for (size_t i = 0; i < pod.Containers.size(); i++) {
-        ContainerDeviceRequest request = GenerateResourceRequests(pod.Containers[i], cfg);
-        if (request.Nums > 0) counts[i].push_back(request); // :33
+        const ContainerDeviceRequest vendors[3] = {GenerateResourceRequestsMLU(pod.Containers[i], cfg),
+                                                   GenerateResourceRequests(pod.Containers[i], cfg),
+                                                   GenerateResourceRequestsDCU(pod.Containers[i], cfg)};
+        for (const ContainerDeviceRequest &request : vendors)
+            if (request.Nums > 0) counts[i].push_back(request); // :33
     }
     return counts;
 }
@@ -189,7 +224,10 @@ bool Scheduler::uploadSnapshot(const std::vector<std::string> &order, const std:
     }
     const int32_t *ptrs[VGS_NUM_PLANES];
     for (int f = 0; f < VGS_NUM_PLANES; f++) ptrs[f] = planes[f].data();
-    int rc = vgs_snapshot_upload(ctx_, (int32_t)n, (int32_t)dmax, ptrs, ndev.data(), nullptr);
+    std::vector<uint32_t> tflags;
+    for (const std::string &t : types_) tflags.push_back(vgs_host_type_flags(t.c_str()));
+    int rc = vgs_snapshot_type_flags(ctx_, (int32_t)tflags.size(), tflags.data());
+    if (rc == VGS_OK) rc = vgs_snapshot_upload(ctx_, (int32_t)n, (int32_t)dmax, ptrs, ndev.data(), nullptr);
     if (rc != VGS_OK) {
         *err = std::string(vgs_strerror(rc)) + ": " + vgs_last_error(ctx_);
         return false;
@@ -245,8 +283,17 @@ bool Scheduler::calcScoreGPU(const std::vector<std::string> &order, const std::m
             memset(&r, 0, sizeof r);
             r.ctr = (int32_t)ctr, r.nums = k.Nums, r.memreq = k.Memreq, r.mempct = k.MemPercentagereq;
             r.coresreq = k.Coresreq;
-            r.typemask = vgs_host_typemask(k.Type.c_str(), anno("nvidia.com/use-gputype"),
-                                           anno("nvidia.com/nouse-gputype"), type_c.data(), (int32_t)type_c.size());
+            if (k.Type == "MLU") {
+                r.typemask = vgs_host_typemask_mlu(k.Memreq, anno("cambricon.com/use-mlutype"),
+                                                   anno("cambricon.com/nouse-mlutype"), type_c.data(),
+                                                   (int32_t)type_c.size(), &r.flags);
+            } else if (k.Type == "DCU") {
+                r.typemask = vgs_host_typemask("DCU", anno("hygon.com/use-dcutype"), anno("hygon.com/nouse-dcutype"),
+                                               type_c.data(), (int32_t)type_c.size());
+            } else {
+                r.typemask = vgs_host_typemask(k.Type.c_str(), anno("nvidia.com/use-gputype"),
+                                               anno("nvidia.com/nouse-gputype"), type_c.data(), (int32_t)type_c.size());
+            }
             if (k.Type == "NVIDIA" && vgs_host_numa_bind(anno("nvidia.com/numa-bind"))) r.flags |= VGS_REQ_NUMA_BIND;
             reqs.push_back(r);
             total += k.Nums;
@@ -352,12 +399,14 @@ int vgh_filter(void *s, const char *ns, const char *name, const char *uid, int n
     vgpu::ExtenderArgs args;
     args.pod.Namespace = ns, args.pod.Name = name, args.pod.UID = uid;
     for (int i = 0; i < n_annos; i++) args.pod.Annotations[keys[i]] = vals[i];
-    static const char *rn[4] = {"nvidia.com/gpu", "nvidia.com/gpumem", "nvidia.com/gpumem-percentage",
-                                "nvidia.com/gpucores"};
+    // res[c][9]: the container's limits in this order, INT64_MIN = absent
+    static const char *rn[9] = {"nvidia.com/gpu",       "nvidia.com/gpumem",    "nvidia.com/gpumem-percentage",
+                                "nvidia.com/gpucores",  "cambricon.com/mlunum", "cambricon.com/mlumem",
+                                "hygon.com/dcunum",     "hygon.com/dcumem",     "hygon.com/dcucores"};
     for (int c = 0; c < n_ctrs; c++) {
         vgpu::Container ctr;
-        for (int k = 0; k < 4; k++)
-            if (res[c * 4 + k] != INT64_MIN) ctr.Limits[rn[k]] = res[c * 4 + k];
+        for (int k = 0; k < 9; k++)
+            if (res[c * 9 + k] != INT64_MIN) ctr.Limits[rn[k]] = res[c * 9 + k];
         args.pod.Containers.push_back(ctr);
     }
     for (int i = 0; i < n_nodes; i++) args.NodeNames.push_back(node_names[i]);

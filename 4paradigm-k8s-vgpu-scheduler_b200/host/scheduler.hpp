@@ -6,7 +6,8 @@
 // else here is what stays on the host in the Go extender too.
 //
 //   types            pkg/util/types.go:85-117, pkg/scheduler/nodes.go:28-48, score.go:29-33
-//   Resourcereqs     pkg/k8sutil/pod.go:26-40 + pkg/device/nvidia/device.go:114-175
+//   Resourcereqs     pkg/k8sutil/pod.go:26-40 + the vendors' GenerateResourceRequests (nvidia/device.go:114-175,
+//                    cambricon/device.go:106-137, hygon/device.go:86-135)
 //   getNodesUsage    pkg/scheduler/scheduler.go:249-310
 //   Filter           pkg/scheduler/scheduler.go:354-402
 //   EncodePodDevices pkg/util/util.go:110-126
@@ -96,6 +97,10 @@ struct Config {
     int32_t DefaultMem = 0, DefaultCores = 0;
     std::string ResourceName = "nvidia.com/gpu", ResourceMem = "nvidia.com/gpumem",
                 ResourceMemPercentage = "nvidia.com/gpumem-percentage", ResourceCores = "nvidia.com/gpucores";
+    // cambricon/device.go:40-43, hygon/device.go:34-38
+    std::string MLUResourceCount = "cambricon.com/mlunum", MLUResourceMemory = "cambricon.com/mlumem";
+    std::string DCUResourceCount = "hygon.com/dcunum", DCUResourceMemory = "hygon.com/dcumem",
+                DCUResourceCores = "hygon.com/dcucores";
 };
 
 // annotation keys, pkg/util/types.go:26-31
@@ -109,7 +114,10 @@ std::string EncodePodDevices(const PodDevices &pd);             // util.go:120-1
 
 // nvidia/device.go:114-175; a zero-valued request (Nums == 0) means "this vendor is not asked for"
 ContainerDeviceRequest GenerateResourceRequests(const Container &ctr, const Config &cfg);
-// k8sutil/pod.go:26-40 (NVIDIA vendor only)
+ContainerDeviceRequest GenerateResourceRequestsMLU(const Container &ctr, const Config &cfg); // cambricon/device.go:106-137
+ContainerDeviceRequest GenerateResourceRequestsDCU(const Container &ctr, const Config &cfg); // hygon/device.go:86-135
+// k8sutil/pod.go:26-40.  The reference walks the Go map device.GetDevices() (devices.go:43-52), whose
+// order is random per call; here the vendors come in the fixed order Cambricon, Nvidia, Hygon.
 std::vector<std::vector<ContainerDeviceRequest>> Resourcereqs(const Pod &pod, const Config &cfg);
 
 class Scheduler {

@@ -65,11 +65,13 @@ class Scheduler:
         self.lib.vgh_del_pod(self.h, uid.encode())
 
     def filter(self, uid: str, containers: List[Dict[str, int]], annos: Dict[str, str], node_names: List[str]):
-        """containers[i]: {"gpu":, "gpumem":, "gpumem-percentage":, "gpucores":} (absent keys allowed).
+        """containers[i]: {"gpu":, "gpumem":, "gpumem-percentage":, "gpucores":, "mlunum":, "mlumem":, "dcunum":,
+        "dcumem":, "dcucores":} (absent keys allowed).
         Returns dict(node, ids, failed{}, passed[]) ; raises RuntimeError for the reference's (nil, err)."""
-        res = np.full((max(len(containers), 1), 4), ABSENT, dtype=np.int64)
+        res = np.full((max(len(containers), 1), 9), ABSENT, dtype=np.int64)
         for i, c in enumerate(containers):
-            for k, key in enumerate(("gpu", "gpumem", "gpumem-percentage", "gpucores")):
+            for k, key in enumerate(("gpu", "gpumem", "gpumem-percentage", "gpucores", "mlunum", "mlumem", "dcunum",
+                                     "dcumem", "dcucores")):
                 if key in c:
                     res[i, k] = c[key]
         cap = 1 << 16

@@ -22,6 +22,8 @@ ANNO_NOUSE = "nvidia.com/nouse-gputype"  # :21
 ANNO_NUMA = "nvidia.com/numa-bind"  # :22
 ANNO_DCU_USE = "hygon.com/use-dcutype"  # pkg/device/hygon/device.go:20
 ANNO_DCU_NOUSE = "hygon.com/nouse-dcutype"  # :21
+ANNO_MLU_USE = "cambricon.com/use-mlutype"  # pkg/device/cambricon/device.go:19
+ANNO_MLU_NOUSE = "cambricon.com/nouse-mlutype"  # :20
 
 
 @dataclass

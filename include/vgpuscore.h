@@ -93,6 +93,13 @@ typedef struct {
  * bit t of typemask = checkType(annos, DeviceUsage{Type: types[t]}, req).pass
  * (score.go:71-84, nvidia/device.go:62-94,107-112). */
 #define VGS_REQ_NUMA_BIND 1u /* checkType's numaAssert (nvidia/device.go:96-105) */
+/* Cambricon request without memory (cambricon/device.go:97-99: Type "MLU", Memreq == 0): a
+ * device whose type carries VGS_TYPE_IDLE_SHARE fails the type check while Used > 0 -- Used as
+ * it stands when the request is examined, earlier requests of the same pod included.  The rule
+ * of :94-96 (Memreq != 0 on a non-370 card) does not depend on usage and lives in typemask. */
+#define VGS_REQ_IDLE_SHARE 2u
+/* per device type (vgs_snapshot_type_flags): strings.Contains(d.Type, "370"), cambricon/device.go:94,97 */
+#define VGS_TYPE_IDLE_SHARE 1u
 typedef struct {
     int32_t ctr;      /* container index inside the pod, non-decreasing */
     int32_t nums;     /* Nums  (>= 1: k8sutil/pod.go:33 drops the rest) */
@@ -170,6 +177,9 @@ int vgs_snapshot_upload(vgs_ctx *ctx, int32_t n_nodes, int32_t dmax,
 int vgs_snapshot_set_device(vgs_ctx *ctx, int32_t n_nodes, int32_t dmax,
                             const int32_t *const dev_planes[VGS_NUM_PLANES],
                             const int32_t *dev_ndev, uint64_t *out_version);
+/* flags[t] = VGS_TYPE_* of type id t (all zero until called; types >= n_types get 0).  The
+ * preparation kernel folds them into the walk copy; with a snapshot resident it re-runs. */
+int vgs_snapshot_type_flags(vgs_ctx *ctx, int32_t n_types, const uint32_t *flags);
 /* re-run the preparation kernel over the resident planes (asynchronous; a range
  * error surfaces at the next vgs_results_download) */
 int vgs_snapshot_refresh(vgs_ctx *ctx);
@@ -268,6 +278,14 @@ int vgs_last_timing(vgs_ctx *ctx, vgs_timing *out);
  * pass hygon.com/use-dcutype / nouse-dcutype).  Other request types: mask 0. */
 uint64_t vgs_host_typemask(const char *req_type, const char *use_gputype,
                            const char *nouse_gputype, const char *const *types, int32_t n_types);
+/* the Cambricon vendor (cambricon/device.go:60-104; req_type "MLU", pass
+ * cambricon.com/use-mlutype / nouse-mlutype): bit t = the card contains "MLU", survives
+ * checkMLUtype, and is not ruled out by ":94-96 Memreq != 0 on a card that is not a 370".
+ * *req_flags receives VGS_REQ_IDLE_SHARE when memreq == 0 (:97-99), else 0. */
+uint64_t vgs_host_typemask_mlu(int32_t memreq, const char *use_mlutype, const char *nouse_mlutype,
+                               const char *const *types, int32_t n_types, uint32_t *req_flags);
+/* VGS_TYPE_* of one device type string */
+uint32_t vgs_host_type_flags(const char *type_name);
 /* nvidia/device.go:96-105 assertNuma */
 int32_t vgs_host_numa_bind(const char *numa_bind_anno);
 /* util.DecodeNodeDevices (pkg/util/util.go:68-99): the node registration

@@ -28,7 +28,7 @@ PICK_DTYPE = np.dtype([("slot", "<i4"), ("usedmem", "<i4"), ("usedcores", "<i4")
 
 class _Annos(C.Structure):
     _fields_ = [("use", C.c_char_p), ("nouse", C.c_char_p), ("numa", C.c_char_p), ("dcu_use", C.c_char_p),
-                ("dcu_nouse", C.c_char_p)]
+                ("dcu_nouse", C.c_char_p), ("mlu_use", C.c_char_p), ("mlu_nouse", C.c_char_p)]
 
 
 class _Snap(C.Structure):
@@ -69,8 +69,8 @@ def _load():
                                         C.POINTER(C.c_double)]
         lib.ref_score_batch_packed.argtypes = [C.POINTER(_Snap), C.POINTER(_PodsPacked), C.c_void_p, C.c_void_p,
                                                C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_double)]
-        lib.ref_typemask.argtypes = [C.POINTER(_Annos), C.c_char_p, C.POINTER(C.c_char_p), C.c_int,
-                                     C.POINTER(C.c_int)]
+        lib.ref_typemask.argtypes = [C.POINTER(_Annos), C.c_char_p, C.c_int32, C.POINTER(C.c_char_p), C.c_int,
+                                     C.POINTER(C.c_int), C.POINTER(C.c_int)]
         lib.ref_typemask.restype = C.c_uint64
         lib.ref_encode_pod_devices.argtypes = [C.c_int, C.c_void_p, C.POINTER(C.c_char_p), C.POINTER(C.c_char_p),
                                                C.c_void_p, C.c_void_p, C.c_char_p, C.c_int]
@@ -93,16 +93,19 @@ def _snap_struct(snap):
 
 def _annos_struct(an):
     return _Annos(_b(an.get(ANNO_USE)), _b(an.get(ANNO_NOUSE)), _b(an.get(ANNO_NUMA)),
-                  _b(an.get("hygon.com/use-dcutype")), _b(an.get("hygon.com/nouse-dcutype")))
+                  _b(an.get("hygon.com/use-dcutype")), _b(an.get("hygon.com/nouse-dcutype")),
+                  _b(an.get("cambricon.com/use-mlutype")), _b(an.get("cambricon.com/nouse-mlutype")))
 
 
-def typemask(annos: dict, req_type: str, type_names) -> tuple:
+def typemask(annos: dict, req_type: str, type_names, memreq: int = 0) -> tuple:
+    """(mask, flags): flags bit 0 = numaAssert, bit 1 = in-use "370" cards fail (Cambricon, Memreq == 0)"""
     lib = _load()
     names = (C.c_char_p * max(len(type_names), 1))(*[t.encode() for t in type_names])
     a = _annos_struct(annos)
-    numa = C.c_int(0)
-    m = lib.ref_typemask(C.byref(a), req_type.encode(), names, len(type_names), C.byref(numa))
-    return int(m), int(numa.value)
+    numa, idle = C.c_int(0), C.c_int(0)
+    m = lib.ref_typemask(C.byref(a), req_type.encode(), int(memreq), names, len(type_names), C.byref(numa),
+                         C.byref(idle))
+    return int(m), int(numa.value) | (int(idle.value) << 1)
 
 
 def _outputs(batch, n_nodes, full):
@@ -163,9 +166,11 @@ def score_packed(snap, batch, full: bool = False, threads: Optional[int] = None)
     for r in range(R):
         a = batch.annos[int(pod_of_ctr[ctr_of_req[r]])]
         key = (batch.req_type[r], a.get(ANNO_USE), a.get(ANNO_NOUSE), a.get(ANNO_NUMA),
-               a.get("hygon.com/use-dcutype"), a.get("hygon.com/nouse-dcutype"))
+               a.get("hygon.com/use-dcutype"), a.get("hygon.com/nouse-dcutype"),
+               a.get("cambricon.com/use-mlutype"), a.get("cambricon.com/nouse-mlutype"),
+               int(batch.memreq[r]) != 0 if "MLU" in batch.req_type[r] else None)
         if key not in cache:
-            cache[key] = typemask(a, batch.req_type[r], snap.type_names)
+            cache[key] = typemask(a, batch.req_type[r], snap.type_names, int(batch.memreq[r]))
         masks[r], numa[r] = cache[key]
     arrs = [np.ascontiguousarray(getattr(batch, k), dtype=np.int32)
             for k in ("ctr_begin", "req_begin", "nums", "memreq", "mempct", "coresreq")]

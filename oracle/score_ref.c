@@ -136,10 +136,28 @@ static int ref_checkDCUtype(const ref_Annos *annos, const char *cardtype) {
     return 1;
 }
 
+/* pkg/device/cambricon/device.go:60-91 checkMLUtype: the same list logic on the
+ * cambricon.com/{use,nouse}-mlutype annotations */
+static int ref_checkMLUtype(const ref_Annos *annos, const char *cardtype) {
+    if (annos->use_mlutype) return any_token_matches(annos->use_mlutype, cardtype) ? 1 : 0;
+    if (annos->nouse_mlutype) return any_token_matches(annos->nouse_mlutype, cardtype) ? 0 : 1;
+    return 1;
+}
+
+/* pkg/device/cambricon/device.go:93-104 CheckType (found iff n.Type contains "MLU";
+ * numaAssert always false) */
+static int ref_checkTypeMLU(const ref_Annos *annos, const ref_DeviceUsage *d,
+                            const ref_ContainerDeviceRequest *n) {
+    if (!ref_strings_contains(d->Type, "370") && n->Memreq != 0) return 0;               /* :94-96 */
+    if (ref_strings_contains(d->Type, "370") && n->Memreq == 0 && d->Used > 0) return 0; /* :97-99 */
+    return ref_checkMLUtype(annos, d->Type);                                             /* :100 */
+}
+
 /* pkg/scheduler/score.go:71-84 checkType over device.GetDevices(): NVIDIA
- * (nvidia/device.go:107-112) and Hygon (hygon/device.go:79-84).  Cambricon
- * (cambricon/device.go:93-104, depends on d.Used / n.Memreq) is not restated:
- * a request type neither vendor claims is "Unrecognized device". */
+ * (nvidia/device.go:107-112), Hygon (hygon/device.go:79-84), Cambricon
+ * (cambricon/device.go:93-104).  The three "found" conditions are mutually
+ * exclusive, so the map order of GetDevices() does not matter.  A request type
+ * no vendor claims is "Unrecognized device". */
 int ref_checkType(const ref_Annos *annos, const ref_DeviceUsage *d,
                   const ref_ContainerDeviceRequest *n, int *numa) {
     *numa = 0;
@@ -149,18 +167,23 @@ int ref_checkType(const ref_Annos *annos, const ref_DeviceUsage *d,
         return ref_checkGPUtype(annos, d->Type);
     }
     if (strcmp(n->Type, "DCU") == 0) return ref_checkDCUtype(annos, d->Type); /* hygon: numaAssert false */
+    if (ref_strings_contains(n->Type, "MLU")) return ref_checkTypeMLU(annos, d, n);
     return 0; /* :82-83 */
 }
 
-/* type mask for the packed (R2) arm: bit t = checkType pass for type_names[t];
- * *numa = numaAssert.  Built from the oracle's own string policy above. */
-uint64_t ref_typemask(const ref_Annos *annos, const char *req_type, const char *const *type_names,
-                      int n_types, int *numa) {
+/* type mask for the packed (R2) arm: bit t = checkType pass for an UNUSED device of
+ * type_names[t] and a request of this type and Memreq; *numa = numaAssert; *idle = the
+ * request additionally loses "370" cards that are in use (cambricon/device.go:97-99,
+ * applied per device by the packed arm).  Built from the oracle's own string policy above. */
+uint64_t ref_typemask(const ref_Annos *annos, const char *req_type, int32_t memreq,
+                      const char *const *type_names, int n_types, int *numa, int *idle) {
     uint64_t m = 0;
     ref_ContainerDeviceRequest rq;
     memset(&rq, 0, sizeof rq);
     rq.Type = req_type;
+    rq.Memreq = memreq;
     *numa = 0;
+    if (idle) *idle = ref_strings_contains(req_type, "MLU") && memreq == 0;
     for (int t = 0; t < n_types && t < 64; t++) {
         ref_DeviceUsage d;
         memset(&d, 0, sizeof d);
@@ -517,7 +540,10 @@ static int packed_eval_node(const ref_Snapshot *s, int row, const ref_PodBatchPa
                 int d = st.ord[i];
                 size_t x = base + d;
                 if (!((pods->typemask[r] >> s->type_id[x]) & 1)) continue;
-                if (pods->numa_bind[r] && prevnuma != s->numa[x]) {
+                if ((pods->numa_bind[r] & 2) && st.used[d] > 0 &&
+                    ref_strings_contains(s->type_names[s->type_id[x]], "370"))
+                    continue; /* cambricon/device.go:97-99, part of checkType */
+                if ((pods->numa_bind[r] & 1) && prevnuma != s->numa[x]) {
                     left = nums;
                     prevnuma = s->numa[x];
                     nt = 0;

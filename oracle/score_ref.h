@@ -2,7 +2,8 @@
  * oracle/score_ref.h -- TEST INFRASTRUCTURE ONLY.
  *
  * CPU restatement of the reference scheduler extender's Filter scoring pass
- * (pkg/scheduler/score.go, pkg/device/nvidia/device.go, scheduler.go:386-387).
+ * (pkg/scheduler/score.go, the three vendors' CheckType in pkg/device/{nvidia,
+ * hygon,cambricon}/device.go, scheduler.go:386-387).
  * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
  * --impl reference legs may load this library; the product (libvgpuscore.so)
  * never links or calls it.
@@ -10,8 +11,9 @@
  * PARITY UNPINNED: the reference holds no test, golden vector or fixture for
  * pkg/scheduler, and no Go toolchain exists on this image, so this restatement
  * could not be checked against the reference's own outputs.  It is pinned only
- * by the hand-derived known-answer vectors of SURVEY.md section 8(c)
- * (tests/golden/kat.json).
+ * by the hand-derived known-answer vectors of SURVEY.md section 8(c), plus
+ * seven more derived the same way for the Cambricon vendor
+ * (tests/golden/kat.json, tests/golden/make_kat.py).
  */
 #ifndef VGPU_ORACLE_SCORE_REF_H
 #define VGPU_ORACLE_SCORE_REF_H
@@ -69,6 +71,9 @@ typedef struct {
     /* Hygon vendor (pkg/device/hygon/device.go:20-21) */
     const char *use_dcutype;
     const char *nouse_dcutype;
+    /* Cambricon vendor (pkg/device/cambricon/device.go:19-20) */
+    const char *use_mlutype;
+    const char *nouse_mlutype;
 } ref_Annos;
 
 /* One result record per pod / per pick: same shape the product's C ABI uses
@@ -95,8 +100,8 @@ int ref_assertNuma(const ref_Annos *annos);
 int ref_checkType(const ref_Annos *annos, const ref_DeviceUsage *d,
                   const ref_ContainerDeviceRequest *n, int *numa);
 
-uint64_t ref_typemask(const ref_Annos *annos, const char *req_type, const char *const *type_names,
-                      int n_types, int *numa);
+uint64_t ref_typemask(const ref_Annos *annos, const char *req_type, int32_t memreq,
+                      const char *const *type_names, int n_types, int *numa, int *idle);
 
 /* ---- scoring (score.go:45-50, 86-214) ---------------------------------- */
 void ref_sort_devices(ref_NodeUsage *node);
@@ -157,7 +162,7 @@ typedef struct {
     const int32_t *req_begin;
     const int32_t *nums, *memreq, *mempct, *coresreq;
     const uint64_t *typemask; /* n_reqs */
-    const uint8_t *numa_bind; /* n_reqs */
+    const uint8_t *numa_bind; /* n_reqs: bit 0 numaAssert, bit 1 "370 cards must be unused" */
 } ref_PodBatchPacked;
 
 int ref_score_batch_packed(const ref_Snapshot *snap, const ref_PodBatchPacked *pods,

@@ -33,6 +33,7 @@ def kat(name, devices, containers, annos, fit, bits=None, picks=None, n_nodes=1,
 
 
 U = 101
+M370, M370X4, M290 = "MLU370-X8", "MLU370-X4", "MLU290"
 mixed_types = [V100] * 4 + [A100] * 4
 KATS = [
     kat("1_baseline_cfg1_64_idle_nodes", node(), [[(1, 3000, U, 30)]], {}, True, "0x41000000", [[(7, 3000, 30)]],
@@ -64,6 +65,23 @@ KATS = [
     kat("14_cores_over_100", node(), [[(1, 1000, U, 101)]], {}, False, cite="score.go:110-113"),
     kat("15_all_eight", node(Used=[0, 1, 2, 3, 4, 5, 6, 7]), [[(8, 100, U, 5)]], {}, True, "0x3fc4ec4f",
         [[(s, 100, 5) for s in range(8)]], cite="80/52 + 0"),
+    # Cambricon vendor: request = (Nums, Memreq, 0, 0, "MLU") -- cambricon/device.go:106-137 leaves
+    # MemPercentagereq and Coresreq at Go's zero value
+    kat("16_mlu370_share_needs_unused_card", node(Type=M370, Used=[1, 0, 2, 0, 0, 3, 0, 1]), [[(2, 0, 0, 0, "MLU")]], {},
+        True, "0x40e00000", [[(6, 0, 0), (4, 0, 0)]], cite="cambricon/device.go:97-99: Memreq == 0 on a 370 in use fails"),
+    kat("17_mlu370_share_sees_own_pick", node(Type=M370, Used=[1, 1, 1, 0, 1, 1, 1, 1]),
+        [[(1, 0, 0, 0, "MLU")], [(1, 0, 0, 0, "MLU")]], {}, False,
+        cite="container 0 takes slot 3; for container 1 its Used is 1 (score.go:171), so :97-99 rules it out too"),
+    kat("18_mlu370_with_memory_shares_a_card", node(Type=M370, Used=[1, 1, 1, 0, 1, 1, 1, 1]),
+        [[(1, 1000, 0, 0, "MLU")], [(1, 1000, 0, 0, "MLU")]], {}, True, "0x4180e38e",
+        [[(3, 1000, 0)], [(3, 1000, 0)]], cite="8 + (10/9 + 7): Memreq != 0 skips :97-99"),
+    kat("19_mlu290_cannot_split_memory", node(Type=M290), [[(1, 1000, 0, 0, "MLU")]], {}, False,
+        cite="cambricon/device.go:94-96: Memreq != 0 on a card that is not a 370"),
+    kat("20_mlu290_whole_card_in_use_still_passes", node(Type=M290, Used=1), [[(1, 0, 0, 0, "MLU")]], {}, True,
+        "0x4101c71c", [[(7, 0, 0)]], cite="10/9 + 7: the Used > 0 rule is for 370 only"),
+    kat("21_use_mlutype", node(Type=[M370X4] * 4 + [M370] * 4), [[(1, 0, 0, 0, "MLU")]],
+        {"cambricon.com/use-mlutype": "x4"}, True, "0x41000000", [[(3, 0, 0)]], cite="cambricon/device.go:60-75"),
+    kat("22_nvidia_request_on_mlu_node", node(Type=M370), [[(1, 1000, U, 0)]], {}, False, cite="score.go:73"),
 ]
 
 # string-policy truth table (nvidia/device.go:62-105), each line derived by hand

@@ -52,3 +52,38 @@ def assert_same(a, b, what=""):
     if a.fit is not None and b.fit is not None:
         assert np.array_equal(a.fit, b.fit), what + " fit matrix"
         assert np.array_equal(a.scores.view(np.uint32), b.scores.view(np.uint32)), what + " score matrix"
+
+
+def cambricon_cluster(rng, n_nodes, n_pods):
+    """MLU370 / MLU290 / NVIDIA nodes (a few hold two card types) and pods of 1-3 containers asking
+    for MLUs with and without memory, some with cambricon.com/{use,nouse}-mlutype, some NVIDIA"""
+    kinds = ["MLU370-X8", "MLU290", "MLU370-X4", "NVIDIA-Tesla V100"]
+    nodes = []
+    for i in range(n_nodes):
+        t = kinds[i % 4]
+        devs = []
+        for s in range(8):
+            tt = kinds[(i + s // 4) % 4] if i % 9 == 0 else t
+            used = int(rng.choice([0, 0, 0, 1, 2, 4]))
+            devs.append(dict(Used=used, Count=4, Usedmem=int(rng.integers(0, 6000)) * (used > 0), Totalmem=24576,
+                             Usedcores=int(rng.choice([0, 0, 50, 100])) * (used > 0), Totalcore=100, Numa=s // 4, Type=tt))
+        nodes.append(devs[: int(rng.choice([8, 8, 8, 5, 2]))])
+    pods = []
+    for i in range(n_pods):
+        annos = {}
+        if i % 5 == 1:
+            annos["cambricon.com/use-mlutype"] = str(rng.choice(["x8", "MLU290", "x4,x8", "370"]))
+        elif i % 5 == 2:
+            annos["cambricon.com/nouse-mlutype"] = str(rng.choice(["x8", "mlu290,x4"]))
+        if i % 6 == 0:
+            annos["nvidia.com/numa-bind"] = "true"  # Cambricon never asserts numa (cambricon/device.go:36-38)
+        ctrs = []
+        for _ in range(int(rng.choice([1, 1, 2, 3]))):
+            if rng.random() < 0.2:
+                ctrs.append([(int(rng.choice([1, 2])), 2000, 101, 10, "NVIDIA")])
+            else:
+                ctrs.append([(int(rng.choice([1, 1, 2, 3])), int(rng.choice([0, 0, 1000, 8000])), 0, 0, "MLU")])
+        if rng.random() < 0.1:  # both vendors inside one container
+            ctrs[0] = [(1, 0, 0, 0, "MLU"), (1, 1000, 101, 0, "NVIDIA")]
+        pods.append({"containers": ctrs, "annos": annos})
+    return v.Snapshot.from_nodes(nodes, dmax=8), v.PodBatch.from_pods(pods)

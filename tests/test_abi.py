@@ -61,7 +61,15 @@ def test_host_policy_matches_truth_table_and_oracle(built):
     _, batch = v.workload.make_config("cfg3", 8, 512)
     for an in batch.annos:
         assert v.capi.host_typemask("NVIDIA", an, names) == oracle.typemask(an, "NVIDIA", names)[0]
-    assert v.capi.host_typemask("MLU", {}, ["MLU370"]) == 0
+    assert v.capi.host_typemask("MLU", {}, ["MLU370"]) == 0  # Cambricon has its own entry point
+    mlu = ["MLU370-X8", "MLU290", "NVIDIA-x"]
+    for an in ({}, {"cambricon.com/use-mlutype": "mlu290"}, {"cambricon.com/nouse-mlutype": "x8,t4"},
+               {"cambricon.com/use-mlutype": "X8,", "cambricon.com/nouse-mlutype": "x8"}):
+        for memreq in (0, 1000):
+            m, fl = v.capi.host_typemask_mlu(memreq, an, mlu)
+            om, of = oracle.typemask(an, "MLU", mlu, memreq=memreq)
+            assert (m, fl == v.capi.VGS_REQ_IDLE_SHARE) == (om, of == 2), (an, memreq)
+    assert [v.capi.host_type_flags(t) for t in mlu] == [v.capi.VGS_TYPE_IDLE_SHARE, 0, 0]
 
 
 def test_encode_pod_devices_golden(built):

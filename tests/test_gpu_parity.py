@@ -6,7 +6,7 @@ import pytest
 
 import oracle
 import vgpu_b200 as v
-from helpers import assert_same, check_kat, kat_inputs, load_kats
+from helpers import assert_same, cambricon_cluster, check_kat, kat_inputs, load_kats
 
 pytestmark = pytest.mark.gpu
 K = load_kats()
@@ -357,6 +357,60 @@ def test_mixed_vendor_cluster_nvidia_and_hygon(built):
     for p in range(batch.n_pods):
         if got.best_row[p] >= 0:
             assert ("DCU" in nodes[got.best_row[p]][0]["Type"]) == (batch.req_type[p] == "DCU")
+
+
+def test_cambricon_vendor(built):
+    """Cambricon's CheckType (cambricon/device.go:93-104) depends on the request's
+    Memreq and on the device's Used AS THE POD'S EARLIER REQUESTS LEFT IT; full fit/score matrices
+    against both oracle arms, then the same batch sharded and drained"""
+    rng = np.random.default_rng(370)
+    snap, batch = cambricon_cluster(rng, 900, 260)
+    got = gpu_score(snap, batch)
+    assert_same(got, oracle.score_faithful(snap, batch, full=True), "mlu R1")
+    assert_same(got, oracle.score_packed(snap, batch, full=True), "mlu R2")
+    assert 0 < int((got.best_row >= 0).sum()) < batch.n_pods
+    # the rule bites: with the type flags cleared the same pods see more nodes
+    with v.Context(max_nodes=snap.n_nodes, max_pods=batch.n_pods, max_reqs=batch.n_reqs,
+                   max_picks=int(batch.nums.sum()), verify=True) as ctx:
+        ctx.upload(snap)
+        ctx.set_type_flags([0] * len(snap.type_names))
+        loose = ctx.score(batch)
+        assert int(loose.fit_count.sum()) > int(got.fit_count.sum())
+        ctx.set_type_flags([v.capi.host_type_flags(t) for t in snap.type_names])
+        assert_same(ctx.score(batch), got, "flags restored")
+    # single-request pods only, enough of them to reach the pod-sliced kernels' threshold:
+    # idle-share requests must be kept out of those classes
+    pods = [{"containers": [[(int(rng.choice([1, 2])), int(rng.choice([0, 0, 3000])), 0, 0, "MLU")]]} for _ in range(1300)]
+    big = v.PodBatch.from_pods(pods)
+    assert_same(gpu_score(snap, big, verify=False), oracle.score_packed(snap, big), "mlu classes")
+
+
+def test_cambricon_drain_and_shards(built):
+    rng = np.random.default_rng(371)
+    snap, batch = cambricon_cluster(rng, 400, 90)
+    want = oracle.score_packed(snap, batch)
+    halves = []
+    for lo, hi in ((0, 200), (200, 400)):
+        with v.Context(max_nodes=200, max_pods=batch.n_pods, max_reqs=batch.n_reqs,
+                       max_picks=int(batch.nums.sum()), row_base=lo) as ctx:
+            ctx.upload(snap.rows(lo, hi))
+            halves.append(ctx.score(batch))
+    for p in range(batch.n_pods):
+        cand = [(h.score[p], h.best_row[p]) for h in halves if h.best_row[p] >= 0]
+        assert (max(cand)[1] if cand else -1) == want.best_row[p]
+        assert sum(int(h.fit_count[p]) for h in halves) == want.fit_count[p]
+    # sequential placement: pod p sees the cards pods 0..p-1 took (an MLU370 taken once is gone for
+    # every later memory-less request)
+    rows, scores, counts, picks, planes = _oracle_drain(snap, batch)
+    with v.Context(max_nodes=snap.n_nodes, max_pods=batch.n_pods, max_reqs=batch.n_reqs,
+                   max_picks=int(batch.nums.sum())) as ctx:
+        ctx.upload(snap)
+        got = ctx.drain(batch)
+        after, _ = ctx.download_snapshot()
+    assert np.array_equal(got.best_row, rows)
+    assert np.array_equal(got.score.view(np.uint32), scores.view(np.uint32))
+    assert np.array_equal(got.picks, picks)
+    assert np.array_equal(after, planes)
 
 
 def test_pinned_planes_take_the_zero_copy_upload(built, monkeypatch):

@@ -60,13 +60,18 @@ class ReferenceFlow:
     def requests(self, ctrs):
         out = []
         for c in ctrs:
-            if c.get("gpu", 0) <= 0:
-                out.append([])
-                continue
-            mem, pct = c.get("gpumem", 0), c.get("gpumem-percentage", 101)
-            if pct == 101 and mem == 0:
-                pct = 100  # DefaultMem == 0 (nvidia/device.go:147-153)
-            out.append([(c["gpu"], mem, pct, c.get("gpucores", 0))])
+            one = []  # vendor order of the C++ mirror: Cambricon, Nvidia, Hygon (Go's map order is random)
+            if c.get("mlunum", 0) > 0:  # cambricon/device.go:106-137
+                one.append((c["mlunum"], c.get("mlumem", 0), 0, 0, "MLU"))
+            if c.get("gpu", 0) > 0:
+                mem, pct = c.get("gpumem", 0), c.get("gpumem-percentage", 101)
+                if pct == 101 and mem == 0:
+                    pct = 100  # DefaultMem == 0 (nvidia/device.go:147-153)
+                one.append((c["gpu"], mem, pct, c.get("gpucores", 0), "NVIDIA"))
+            if c.get("dcunum", 0) > 0:  # hygon/device.go:86-135
+                mem = c.get("dcumem", 0)
+                one.append((c["dcunum"], mem, 100 if mem == 0 else 0, c.get("dcucores", 0), "DCU"))
+            out.append(one)
         return out
 
     def filter(self, uid, ctrs, annos, node_names):
@@ -103,7 +108,7 @@ class ReferenceFlow:
             for q in range(int(batch.req_begin[c]), int(batch.req_begin[c + 1])):
                 for j in range(int(batch.nums[q])):
                     s, m, k = (int(x) for x in r.picks[int(pb[q]) + j])
-                    cd.append((self.cluster[node][s]["ID"], "NVIDIA", m, k))
+                    cd.append((self.cluster[node][s]["ID"], batch.req_type[q], m, k))
             pd.append(cd)
         self.pods[uid] = (node, pd)
         return dict(node=node, ids=encode_pod_devices(pd), failed={}, passed=[node])
@@ -158,6 +163,61 @@ def test_filter_edge_behaviour(built):
     # two containers, second sees the first's usage; default memory = 100 % (device.go:147-153)
     r = sch.filter("p3", [{"gpu": 1, "gpucores": 100}, {}, {"gpu": 2, "gpumem": 1000}], {}, ["n0"])
     assert r["ids"] == "U6,NVIDIA,32768,100:;;U5,NVIDIA,1000,0:U4,NVIDIA,1000,0:"
+    sch.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("incremental", [False, True])
+def test_filter_mixed_vendors(built, incremental):
+    """Cambricon MLU, Hygon DCU and NVIDIA nodes in one cluster; a sequence of Filters with usage
+    carried over: an MLU370 that holds one memory-less pod is closed to the next one
+    (cambricon/device.go:97-99), while pods that ask for mlumem keep sharing it"""
+    rng = np.random.default_rng(99)
+    kinds = [("MLU370-X8", 24576), ("MLU290", 32768), ("DCU-Z100", 16384), ("NVIDIA-Tesla T4", 15360)]
+    cluster = {}
+    for i in range(24):
+        t, mem = kinds[i % 4]
+        cluster[f"node-{i:02d}"] = [dict(ID=f"DEV-{i:02d}-{s}", Count=4, Devmem=mem, Devcore=100, Type=t, Numa=s // 2)
+                                    for s in range(4)]
+    sch = v.hostlib.Scheduler(max_nodes=64, incremental=incremental)
+    ref = ReferenceFlow(cluster)
+    for n, devs in cluster.items():
+        sch.add_node(n, devs)
+    names = list(cluster)
+    placed = {"MLU": 0, "DCU": 0, "NVIDIA": 0}
+    for i in range(150):
+        r = rng.random()
+        if r < 0.55:
+            c = {"mlunum": int(rng.choice([1, 1, 2]))}
+            if rng.random() < 0.5:
+                c["mlumem"] = int(rng.choice([1000, 4000]))
+            kind = "MLU"
+        elif r < 0.8:
+            c = {"dcunum": 1, "dcucores": int(rng.choice([0, 30, 60]))}
+            if rng.random() < 0.5:
+                c["dcumem"] = 2000
+            kind = "DCU"
+        else:
+            c, kind = {"gpu": 1, "gpumem": 3000}, "NVIDIA"
+        ctrs = [c] if rng.random() < 0.8 else [c, dict(c)]
+        annos = {}
+        if i % 6 == 0:
+            annos["cambricon.com/nouse-mlutype"] = "mlu290"
+        if i % 7 == 0:
+            annos["hygon.com/use-dcutype"] = "z100"
+        uid = f"pod-{i:03d}"
+        if i % 13 == 12:
+            victim = f"pod-{i - 5:03d}"
+            sch.del_pod(victim)
+            ref.pods.pop(victim, None)
+        got = sch.filter(uid, ctrs, annos, names)
+        want = ref.filter(uid, ctrs, annos, names)
+        assert got["node"] == want["node"], (uid, ctrs, annos, got, want)
+        assert got["ids"] == want["ids"], (uid, got, want)
+        if got["node"] is not None:
+            placed[kind] += 1
+            assert kinds[int(got["node"][-2:]) % 4][0].startswith(kind)
+    assert all(n > 5 for n in placed.values()), placed
     sch.close()
 
 

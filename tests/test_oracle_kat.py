@@ -6,7 +6,7 @@ import pytest
 
 import oracle
 import vgpu_b200 as v
-from helpers import check_kat, kat_inputs, load_kats
+from helpers import assert_same, cambricon_cluster, check_kat, kat_inputs, load_kats
 
 K = load_kats()
 
@@ -29,7 +29,14 @@ def test_policy_truth_table():
         assert bool(m & 1) == want, (annos, card)
     # d.Type must contain the request type (score.go:73); unknown vendors never pass
     assert oracle.typemask({}, "NVIDIA", ["MLU370"])[0] == 0
-    assert oracle.typemask({}, "MLU", ["MLU370"])[0] == 0
+    assert oracle.typemask({}, "TPU", ["TPU-v4"])[0] == 0
+    # Cambricon (cambricon/device.go:93-104), by hand: (mask over [MLU370-X8, MLU290, NVIDIA-x], flags)
+    names = ["MLU370-X8", "MLU290", "NVIDIA-x"]
+    assert oracle.typemask({}, "MLU", names, memreq=0) == (0b011, 2)       # flags bit 1: 370 in use fails
+    assert oracle.typemask({}, "MLU", names, memreq=1000) == (0b001, 0)    # :94-96 drops the 290
+    assert oracle.typemask({"cambricon.com/use-mlutype": "mlu290"}, "MLU", names, memreq=0) == (0b010, 2)
+    assert oracle.typemask({"cambricon.com/nouse-mlutype": "x8,t4"}, "MLU", names, memreq=0) == (0b010, 2)
+    assert oracle.typemask({"nvidia.com/use-gputype": "none"}, "MLU", names, memreq=0) == (0b011, 2)
 
 
 def test_numa_parse_bool():
@@ -87,3 +94,15 @@ def test_negative_scores_keep_their_order():
     assert_same(a, b, "negative")
     fs = a.scores[0][a.fit[0]]
     assert fs.min() < 0 and a.score[0] == fs.max()
+
+
+def test_cambricon_faithful_equals_packed():
+    """the string arm evaluates cambricon/device.go:93-104 per device with the CURRENT Used; the packed
+    arm splits it into a static mask + an in-use rule: same fit/score matrices"""
+    rng = np.random.default_rng(370)
+    snap, batch = cambricon_cluster(rng, 500, 200)
+    a = oracle.score_faithful(snap, batch, full=True)
+    b = oracle.score_packed(snap, batch, full=True)
+    assert_same(a, b, "mlu R1 vs R2")
+    mlu_only = [p for p in range(batch.n_pods) if all(t == "MLU" for t in batch.req_type[slice(*batch.pod_req_range(p))])]
+    assert a.fit[mlu_only].any() and not a.fit[mlu_only].all()
