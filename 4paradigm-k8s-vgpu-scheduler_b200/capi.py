@@ -27,7 +27,7 @@ NOALLOC_MAX_NODES, NOALLOC_MAX_DEVICES, NOALLOC_MAX_PODS, NOALLOC_MAX_REQS = 163
 EXPORTS = (
     "vgs_abi_version", "vgs_strerror", "vgs_init", "vgs_destroy", "vgs_last_error",
     "vgs_snapshot_upload", "vgs_snapshot_set_device", "vgs_snapshot_refresh", "vgs_snapshot_delta", "vgs_snapshot_download",
-    "vgs_snapshot_type_flags", "vgs_host_typemask_mlu", "vgs_host_type_flags",
+    "vgs_snapshot_type_flags", "vgs_host_typemask_mlu", "vgs_host_type_flags", "vgs_host_decode_pod_devices",
     "vgs_score_batch", "vgs_drain_batch", "vgs_pods_upload", "vgs_score_resident", "vgs_resolve_resident",
     "vgs_results_download", "vgs_sync", "vgs_keys_device", "vgs_keys_merge", "vgs_results_device",
     "vgs_verify_download", "vgs_last_timing", "vgs_host_typemask", "vgs_host_numa_bind",
@@ -160,6 +160,29 @@ def decode_node_devices(anno: str, max_dev: int = 64):
     cnt, mem, core, numa, health, io, il, to, tl = cols
     return [dict(ID=raw[io[i]:io[i] + il[i]].decode(), Count=int(cnt[i]), Devmem=int(mem[i]), Devcore=int(core[i]),
                  Type=raw[to[i]:to[i] + tl[i]].decode(), Numa=int(numa[i]), Health=bool(health[i])) for i in range(n)]
+
+
+def decode_pod_devices(anno: str, max_ctrs: int = 64, max_dev: int = 1024) -> List[List[Tuple[str, str, int, int]]]:
+    """util.DecodePodDevices: the vgpu-ids-new annotation -> [[(uuid, type, usedmem, usedcores), ...], ...]
+    (a malformed entry gives [] like the reference, which drops the error)"""
+    lib = load_library()
+    raw = anno.encode("utf-8")
+    ctr_n = np.zeros(max(max_ctrs, 1), dtype=np.int32)
+    cols = [np.zeros(max(max_dev, 1), dtype=np.int32) for _ in range(6)]
+    lib.vgs_host_decode_pod_devices.restype = C.c_int32
+    nc = lib.vgs_host_decode_pod_devices(C.c_char_p(raw), max_ctrs, max_dev, C.c_void_p(ctr_n.ctypes.data),
+                                         *[C.c_void_p(c.ctypes.data) for c in cols])
+    if nc < 0:
+        raise VgsError(nc, "decode_pod_devices")
+    uo, ul, to, tl, mem, cores = cols
+    out, d = [], 0
+    for c in range(nc):
+        devs = []
+        for _ in range(int(ctr_n[c])):
+            devs.append((raw[uo[d]:uo[d] + ul[d]].decode(), raw[to[d]:to[d] + tl[d]].decode(), int(mem[d]), int(cores[d])))
+            d += 1
+        out.append(devs)
+    return out
 
 
 def encode_pod_devices(ctrs: List[List[Tuple[str, str, int, int]]]) -> str:

@@ -69,10 +69,11 @@ int32_t atoi_go_i32(const std::string &t) {
     if (i >= t.size()) return 0;
     unsigned long long acc = 0;
     bool over = false;
-    for (; i < t.size(); i++) {
+    for (; i < t.size() && !over; i++) { // ParseUint stops at the first overflow, before any later bad byte
         if (t[i] < '0' || t[i] > '9') return 0;
-        if (acc > (0xffffffffffffffffull - 9) / 10) over = true;
-        if (!over) acc = acc * 10 + (unsigned long long)(t[i] - '0');
+        const unsigned long long d = (unsigned long long)(t[i] - '0');
+        if (acc > (0xffffffffffffffffull - d) / 10) over = true;
+        else acc = acc * 10 + d;
     }
     long long v;
     if (over || acc > (neg ? 0x8000000000000000ull : 0x7fffffffffffffffull))
@@ -80,6 +81,23 @@ int32_t atoi_go_i32(const std::string &t) {
     else
         v = neg ? -(long long)acc : (long long)acc;
     return (int32_t)(uint32_t)(unsigned long long)v;
+}
+
+// strconv.ParseInt(t, 10, 32) with the error ignored: 0 on a syntax error, the nearest int32
+// limit on a range error (util.go:150-153)
+int32_t parse_int32_go(const std::string &t) {
+    size_t i = 0;
+    bool neg = false;
+    if (i < t.size() && (t[i] == '+' || t[i] == '-')) neg = t[i++] == '-';
+    if (i >= t.size()) return 0;
+    unsigned long long acc = 0;
+    for (; i < t.size(); i++) {
+        if (t[i] < '0' || t[i] > '9') return 0;
+        acc = acc * 10 + (unsigned long long)(t[i] - '0');
+        if (acc > 0xffffffffull) return neg ? INT32_MIN : INT32_MAX; // ParseUint(.., 32) stops here with ErrRange
+    }
+    if (neg) return acc > 0x80000000ull ? INT32_MIN : (int32_t)(-(long long)acc);
+    return acc > 0x7fffffffull ? INT32_MAX : (int32_t)acc;
 }
 
 } // namespace
@@ -174,6 +192,48 @@ int32_t vgs_host_decode_node_devices(const char *str, int32_t max_dev, int32_t *
         start = colon + 1;
     }
     return n;
+}
+
+int32_t vgs_host_decode_pod_devices(const char *str, int32_t max_ctrs, int32_t max_dev, int32_t *ctr_n,
+                                    int32_t *uuid_off, int32_t *uuid_len, int32_t *type_off, int32_t *type_len,
+                                    int32_t *usedmem, int32_t *usedcores) {
+    if (!str || max_ctrs < 0 || max_dev < 0) return VGS_EINVAL;
+    const std::string s(str);
+    if (s.empty()) return 0; // util.go:159-161
+    int32_t nc = 0, nd = 0;
+    size_t cstart = 0;
+    for (;;) { // strings.Split(str, ";")
+        const size_t semi = s.find(';', cstart);
+        const size_t cend = semi == std::string::npos ? s.size() : semi;
+        if (nc >= max_ctrs) return VGS_ETOOBIG;
+        ctr_n[nc] = 0;
+        size_t start = cstart; // DecodeContainerDevices (:128-156) on s[cstart, cend); empty -> no devices
+        while (cend > cstart) {  // strings.Split(piece, ":")
+            size_t colon = s.find(':', start);
+            if (colon == std::string::npos || colon > cend) colon = cend;
+            const std::string val = s.substr(start, colon - start);
+            if (val.find(',') != std::string::npos) { // :141
+                std::vector<size_t> cut{0};
+                for (size_t i = 0; i < val.size(); i++)
+                    if (val[i] == ',') cut.push_back(i + 1);
+                if (cut.size() < 4) return 0; // :144-146 error, swallowed by DecodePodDevices (:167-169)
+                auto len = [&](int k) { return (k + 1 < (int)cut.size() ? cut[k + 1] - 1 : val.size()) - cut[k]; };
+                if (nd >= max_dev) return VGS_ETOOBIG;
+                uuid_off[nd] = (int32_t)(start + cut[0]), uuid_len[nd] = (int32_t)len(0);
+                type_off[nd] = (int32_t)(start + cut[1]), type_len[nd] = (int32_t)len(1);
+                usedmem[nd] = parse_int32_go(val.substr(cut[2], len(2)));
+                usedcores[nd] = parse_int32_go(val.substr(cut[3], len(3)));
+                nd++;
+                ctr_n[nc]++;
+            }
+            if (colon >= cend) break;
+            start = colon + 1;
+        }
+        nc++;
+        if (semi == std::string::npos) break;
+        cstart = semi + 1;
+    }
+    return nc;
 }
 
 int32_t vgs_host_encode_pod_devices(int32_t n_ctrs, const int32_t *picks_per_ctr, const char *const *uuids,

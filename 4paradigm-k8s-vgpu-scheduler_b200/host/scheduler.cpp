@@ -26,6 +26,43 @@ std::string EncodePodDevices(const PodDevices &pd) {
     return out;
 }
 
+// ---- pkg/util/util.go:128-172, :68-99 (through the library's decoders) --------------------
+PodDevices DecodePodDevices(const std::string &str) {
+    PodDevices pd;
+    const int32_t cap_c = 64, cap_d = 1024;
+    std::vector<int32_t> ctr_n(cap_c), uo(cap_d), ul(cap_d), to(cap_d), tl(cap_d), mem(cap_d), cores(cap_d);
+    const int32_t nc = vgs_host_decode_pod_devices(str.c_str(), cap_c, cap_d, ctr_n.data(), uo.data(), ul.data(),
+                                                   to.data(), tl.data(), mem.data(), cores.data());
+    int32_t d = 0;
+    for (int32_t c = 0; c < nc; c++) {
+        ContainerDevices cd;
+        for (int32_t j = 0; j < ctr_n[c]; j++, d++) {
+            ContainerDevice x;
+            x.UUID = str.substr((size_t)uo[d], (size_t)ul[d]), x.Type = str.substr((size_t)to[d], (size_t)tl[d]);
+            x.Usedmem = mem[d], x.Usedcores = cores[d];
+            cd.push_back(x);
+        }
+        pd.push_back(cd);
+    }
+    return pd;
+}
+bool DecodeNodeDevices(const std::string &str, std::vector<DeviceInfo> *out) {
+    const int32_t cap = 64;
+    std::vector<int32_t> cnt(cap), mem(cap), core(cap), numa(cap), health(cap), io(cap), il(cap), to(cap), tl(cap);
+    const int32_t n = vgs_host_decode_node_devices(str.c_str(), cap, cnt.data(), mem.data(), core.data(), numa.data(),
+                                                   health.data(), io.data(), il.data(), to.data(), tl.data());
+    if (n < 0) return false;
+    out->clear();
+    for (int32_t i = 0; i < n; i++) {
+        DeviceInfo d;
+        d.ID = str.substr((size_t)io[i], (size_t)il[i]), d.Type = str.substr((size_t)to[i], (size_t)tl[i]);
+        d.Index = (uint32_t)i, d.Count = cnt[i], d.Devmem = mem[i], d.Devcore = core[i], d.Numa = numa[i];
+        d.Health = health[i] != 0;
+        out->push_back(d);
+    }
+    return true;
+}
+
 // ---- pkg/device/nvidia/device.go:114-175 ---------------------------------------------------
 static bool lookup(const Container &ctr, const std::string &name, int64_t *v) {
     auto it = ctr.Limits.find(name); // limits take precedence (:119-122)
@@ -121,9 +158,77 @@ Scheduler::~Scheduler() { vgs_destroy(ctx_); }
 
 void Scheduler::addNode(const std::string &nodeID, const NodeInfo &info) {
     if (info.Devices.empty()) return; // nodes.go:60-62
-    nodes_[nodeID] = info;
-    nodes_[nodeID].ID = nodeID;
+    auto it = nodes_.find(nodeID);
+    if (it != nodes_.end()) { // :65-70 a known node GAINS the devices (another vendor's register annotation)
+        it->second.Devices.insert(it->second.Devices.end(), info.Devices.begin(), info.Devices.end());
+    } else {
+        nodes_[nodeID] = info;
+        nodes_[nodeID].ID = nodeID;
+    }
     node_epoch_++;
+}
+
+void Scheduler::rmNodeDevice(const std::string &nodeID, const NodeInfo &info) {
+    auto it = nodes_.find(nodeID);
+    if (it == nodes_.end() || it->second.Devices.empty()) return; // nodes.go:79-83
+    std::vector<DeviceInfo> tmp;
+    for (const DeviceInfo &val : it->second.Devices) {
+        bool found = false;
+        for (const DeviceInfo &rm : info.Devices)
+            if (val.ID == rm.ID) {
+                found = true;
+                break;
+            }
+        if (!found && !val.ID.empty()) tmp.push_back(val); // :94-96
+    }
+    it->second.Devices = tmp;
+    node_epoch_++;
+}
+
+NodeInfo Scheduler::registerNode(const std::string &nodeID, const std::string &registerAnnotation) {
+    NodeInfo nodeInfo;
+    nodeInfo.ID = nodeID;
+    std::vector<DeviceInfo> nodedevices;
+    if (!DecodeNodeDevices(registerAnnotation, &nodedevices) || nodedevices.empty()) return nodeInfo; // :152-155
+    bool found = false; // declared OUTSIDE the device loop in the reference (:195): once one device of the
+                        // annotation is already registered, none of the following ones is appended
+    for (size_t index = 0; index < nodedevices.size(); index++) {
+        const DeviceInfo &deviceinfo = nodedevices[index];
+        auto it = nodes_.find(nodeID);
+        if (it != nodes_.end()) {
+            for (DeviceInfo &val1 : it->second.Devices)
+                if (val1.ID == deviceinfo.ID) { // :199-205 refresh the capacities of a known device
+                    found = true;
+                    if (val1.Devmem != deviceinfo.Devmem || val1.Devcore != deviceinfo.Devcore) node_epoch_++;
+                    val1.Devmem = deviceinfo.Devmem;
+                    val1.Devcore = deviceinfo.Devcore;
+                    break;
+                }
+        }
+        if (!found) {
+            DeviceInfo d = deviceinfo;
+            d.Index = (uint32_t)index;
+            nodeInfo.Devices.push_back(d);
+        }
+    }
+    addNode(nodeID, nodeInfo);
+    return nodeInfo;
+}
+
+void Scheduler::onAddPod(const Pod &pod, bool terminated) {
+    auto node = pod.Annotations.find(AssignedNodeAnnotations);
+    if (node == pod.Annotations.end()) return; // scheduler.go:78-81
+    auto ids = pod.Annotations.find(AssignedIDsAnnotations);
+    if (ids == pod.Annotations.end()) return; // :82-85
+    if (terminated) {                         // :86-89 k8sutil.IsPodInTerminatedState
+        delPod(pod);
+        return;
+    }
+    addPod(pod, node->second, DecodePodDevices(ids->second)); // :90-91
+}
+void Scheduler::onDelPod(const Pod &pod) {
+    if (!pod.Annotations.count(AssignedNodeAnnotations)) return; // scheduler.go:104-107
+    delPod(pod);
 }
 
 void Scheduler::queueDelta(const std::string &nodeID, const PodDevices &devs, int sign) {
@@ -390,7 +495,26 @@ void vgh_del_pod(void *s, const char *uid) {
     static_cast<vgpu::Scheduler *>(s)->delPod(p);
 }
 
-// res: [n_ctrs][4] = nvidia.com/gpu, gpumem, gpumem-percentage, gpucores; INT64_MIN = absent.
+// one vendor's register annotation of one node; returns how many devices were new
+int vgh_register_node(void *s, const char *node_id, const char *anno) {
+    return (int)static_cast<vgpu::Scheduler *>(s)->registerNode(node_id, anno).Devices.size();
+}
+// drop the devices named in a register annotation (a vendor's devices leaving, scheduler.go:166)
+void vgh_rm_node_devices(void *s, const char *node_id, const char *anno) {
+    vgpu::NodeInfo info;
+    if (!vgpu::DecodeNodeDevices(anno, &info.Devices)) return;
+    static_cast<vgpu::Scheduler *>(s)->rmNodeDevice(node_id, info);
+}
+// pod informer event: node_anno / ids_anno NULL = annotation absent
+void vgh_on_add_pod(void *s, const char *ns, const char *name, const char *uid, const char *node_anno,
+                    const char *ids_anno, int terminated) {
+    vgpu::Pod pod;
+    pod.Namespace = ns, pod.Name = name, pod.UID = uid;
+    if (node_anno) pod.Annotations[vgpu::AssignedNodeAnnotations] = node_anno;
+    if (ids_anno) pod.Annotations[vgpu::AssignedIDsAnnotations] = ids_anno;
+    static_cast<vgpu::Scheduler *>(s)->onAddPod(pod, terminated != 0);
+}
+// res: [n_ctrs][9] container limits (order below), INT64_MIN = absent.
 // out: "node=<id>\nids=<vgpu-ids-new>\nfailed=<id>:<why>;...\npass=<id>,<id>...\n" ; returns 0, or -1 with
 // out = error text (the reference's `return nil, err`).
 int vgh_filter(void *s, const char *ns, const char *name, const char *uid, int n_annos, const char *const *keys,

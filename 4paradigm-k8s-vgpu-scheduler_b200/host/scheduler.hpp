@@ -111,6 +111,9 @@ constexpr const char *AssignedNodeAnnotations = "4pd.io/vgpu-node";
 
 std::string EncodeContainerDevices(const ContainerDevices &cd); // util.go:110-118
 std::string EncodePodDevices(const PodDevices &pd);             // util.go:120-126
+PodDevices DecodePodDevices(const std::string &str);           // util.go:158-172 (errors come back as an empty list)
+// util.go:68-99; false for what the reference rejects
+bool DecodeNodeDevices(const std::string &str, std::vector<DeviceInfo> *out);
 
 // nvidia/device.go:114-175; a zero-valued request (Nums == 0) means "this vendor is not asked for"
 ContainerDeviceRequest GenerateResourceRequests(const Container &ctr, const Config &cfg);
@@ -129,7 +132,15 @@ class Scheduler {
     Scheduler(const Scheduler &) = delete;
     Scheduler &operator=(const Scheduler &) = delete;
 
-    void addNode(const std::string &nodeID, const NodeInfo &info); // nodes.go:59-74
+    void addNode(const std::string &nodeID, const NodeInfo &info);      // nodes.go:59-74
+    void rmNodeDevice(const std::string &nodeID, const NodeInfo &info); // nodes.go:76-101
+    // the data half of RegisterFromNodeAnnotatons for one node and one vendor's register annotation
+    // (scheduler.go:152-155, 192-222; the handshake patches :157-191 are control plane).  Returns the
+    // NodeInfo handed to addNode (the devices that were new).
+    NodeInfo registerNode(const std::string &nodeID, const std::string &registerAnnotation);
+    // pod informer callbacks (scheduler.go:72-108): the usage source of getNodesUsage
+    void onAddPod(const Pod &pod, bool terminated);
+    void onDelPod(const Pod &pod);
     void addPod(const Pod &pod, const std::string &nodeID, const PodDevices &devices); // pods.go:46-60
     void delPod(const Pod &pod);                                                        // pods.go:62-70
 

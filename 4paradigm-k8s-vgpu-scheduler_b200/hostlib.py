@@ -29,6 +29,9 @@ def load():
         lib.vgh_add_node.argtypes = [C.c_void_p, C.c_char_p, C.c_int, C.POINTER(C.c_char_p), C.c_void_p, C.c_void_p,
                                      C.c_void_p, C.POINTER(C.c_char_p), C.c_void_p]
         lib.vgh_del_pod.argtypes = [C.c_void_p, C.c_char_p]
+        lib.vgh_register_node.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p]
+        lib.vgh_rm_node_devices.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p]
+        lib.vgh_on_add_pod.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int]
         lib.vgh_filter.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int, C.POINTER(C.c_char_p),
                                    C.POINTER(C.c_char_p), C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_char_p),
                                    C.c_char_p, C.c_int]
@@ -63,6 +66,19 @@ class Scheduler:
 
     def del_pod(self, uid: str):
         self.lib.vgh_del_pod(self.h, uid.encode())
+
+    def register_node(self, node_id: str, register_anno: str) -> int:
+        """one vendor's node register annotation (scheduler.go:152-222, data half) -> devices that were new"""
+        return int(self.lib.vgh_register_node(self.h, node_id.encode(), register_anno.encode()))
+
+    def rm_node_devices(self, node_id: str, register_anno: str):
+        self.lib.vgh_rm_node_devices(self.h, node_id.encode(), register_anno.encode())
+
+    def on_add_pod(self, uid: str, node_anno: Optional[str], ids_anno: Optional[str], terminated: bool = False):
+        """pod informer add/update event (scheduler.go:72-96)"""
+        enc = lambda x: None if x is None else x.encode()
+        self.lib.vgh_on_add_pod(self.h, b"default", uid.encode(), uid.encode(), enc(node_anno), enc(ids_anno),
+                                int(terminated))
 
     def filter(self, uid: str, containers: List[Dict[str, int]], annos: Dict[str, str], node_names: List[str]):
         """containers[i]: {"gpu":, "gpumem":, "gpumem-percentage":, "gpucores":, "mlunum":, "mlumem":, "dcunum":,

@@ -297,6 +297,17 @@ int32_t vgs_host_numa_bind(const char *numa_bind_anno);
 int32_t vgs_host_decode_node_devices(const char *str, int32_t max_dev, int32_t *count, int32_t *devmem,
                                      int32_t *devcore, int32_t *numa, int32_t *health, int32_t *id_off,
                                      int32_t *id_len, int32_t *type_off, int32_t *type_len);
+/* util.DecodePodDevices (pkg/util/util.go:128-172): the 4pd.io/vgpu-ids-new annotation back into
+ * per-container device lists -- what the pod informer feeds addPod with (scheduler.go:72-92).
+ * Containers are the ';' pieces; ctr_n[c] = devices of container c, the devices themselves
+ * container-major in the flat columns; UUID and Type as (offset, length) into str; Usedmem /
+ * Usedcores through strconv.ParseInt(s, 10, 32) with the error dropped (0 on a syntax error, the
+ * int32 limit on overflow).  Returns the container count; 0 for the empty string AND for a
+ * malformed entry (fewer than 4 fields), which the reference turns into an empty PodDevices with a
+ * nil error (:167-169); VGS_ETOOBIG beyond max_ctrs / max_dev. */
+int32_t vgs_host_decode_pod_devices(const char *str, int32_t max_ctrs, int32_t max_dev, int32_t *ctr_n,
+                                    int32_t *uuid_off, int32_t *uuid_len, int32_t *type_off,
+                                    int32_t *type_len, int32_t *usedmem, int32_t *usedcores);
 /* util.EncodePodDevices (pkg/util/util.go:110-126): "UUID,Type,mem,cores:" per
  * pick, ';' between containers.  Returns length or VGS_ETOOBIG. */
 int32_t vgs_host_encode_pod_devices(int32_t n_ctrs, const int32_t *picks_per_ctr,

@@ -4,6 +4,7 @@ import os
 import re
 
 import numpy as np
+import pytest
 
 import vgpu_b200 as v
 from helpers import load_kats
@@ -110,3 +111,37 @@ def test_decode_node_devices(built):
     snap = v.Snapshot.from_nodes([[dict(Count=d["Count"], Totalmem=d["Devmem"], Totalcore=d["Devcore"], Type=d["Type"],
                                         Numa=d["Numa"]) for d in v.capi.decode_node_devices(anno)]])
     assert snap.planes[:, 0, 1].tolist() == [0, 4, 0, 16160, 0, 100, 1, 1]
+
+
+def test_pod_devices_coding_round_trips(built):
+    """pkg/util/util_test.go:26-56 (TestEmptyContainerDevicesCoding, TestEmptyPodDeviceCoding,
+    TestPodDevicesCoding): Encode then Decode gives the value back"""
+    enc, dec = v.capi.encode_pod_devices, v.capi.decode_pod_devices
+    assert dec(enc([])) == []  # TestEmptyPodDeviceCoding (and the empty ContainerDevices of :26-32)
+    pd1 = [[("UUID1", "Type1", 1000, 30)], [], [("UUID1", "Type1", 1000, 30)]]  # TestPodDevicesCoding
+    assert enc(pd1) == "UUID1,Type1,1000,30:;;UUID1,Type1,1000,30:"
+    assert dec(enc(pd1)) == pd1
+    rng = np.random.default_rng(5)
+    for _ in range(50):
+        pd = [[(f"GPU-{rng.integers(1 << 30):x}", str(rng.choice(["NVIDIA", "MLU", "DCU"])), int(rng.integers(0, 1 << 20)),
+                int(rng.integers(0, 101))) for _ in range(int(rng.integers(0, 5)))] for _ in range(int(rng.integers(1, 6)))]
+        if any(pd):  # a pod of only empty containers encodes to ";;" pieces and still round-trips...
+            assert dec(enc(pd)) == pd
+    assert dec(enc([[], []])) == [[], []]
+    assert dec(enc([[]])) == []  # ... except the single empty container: "" decodes to no containers (util.go:159-161)
+
+
+def test_decode_pod_devices_follows_the_go_parser(built):
+    dec = v.capi.decode_pod_devices
+    # fewer than 4 fields: DecodeContainerDevices errors, DecodePodDevices returns an EMPTY list and nil (util.go:144-146,167-169)
+    assert dec("a,b,1:") == [] and dec("u,t,1,2:;x,y:") == []
+    # pieces without a comma are skipped (:141); extra fields are ignored
+    assert dec("junk:u,t,5,6,extra,more:") == [[("u", "t", 5, 6)]]
+    # strconv.ParseInt(s, 10, 32) with the error dropped: syntax error -> 0, range error -> the int32 limit,
+    # and the scan stops at the overflow before it can see a later bad byte
+    assert dec("u,t,12x,-:") == [[("u", "t", 0, 0)]]
+    assert dec("u,t,2147483648,-2147483649:") == [[("u", "t", 2147483647, -2147483648)]]
+    assert dec("u,t,99999999999x,2147483648x:") == [[("u", "t", 2147483647, 0)]]
+    assert dec("u,t,+7,-0:") == [[("u", "t", 7, 0)]]
+    with pytest.raises(v.VgsError):
+        dec("a,b,1,2:" * 5, max_dev=4)

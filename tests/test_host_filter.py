@@ -221,6 +221,58 @@ def test_filter_mixed_vendors(built, incremental):
     sch.close()
 
 
+def _encode_node_devices(devs):
+    """util.EncodeNodeDevices (util.go:101-108): what the device plugin writes into the register annotation"""
+    return "".join(f"{d['ID']},{d['Count']},{d['Devmem']},{d['Devcore']},{d['Type']},{d['Numa']},true:" for d in devs)
+
+
+@pytest.mark.gpu
+def test_restarted_extender_rebuilds_state_from_annotations(built):
+    """A second extender that has only seen the cluster's ANNOTATIONS -- node register strings
+    (DecodeNodeDevices, scheduler.go:152-222) and the scheduled pods' vgpu-node / vgpu-ids-new
+    (DecodePodDevices via onAddPod, scheduler.go:72-92) -- answers every further Filter like the one
+    that made the placements"""
+    rng = np.random.default_rng(21)
+    cluster = make_cluster(rng, 30)
+    pods = make_pods(rng, 90)
+    first = v.hostlib.Scheduler(max_nodes=64)
+    for n, devs in cluster.items():
+        first.add_node(n, devs)
+    names = list(cluster)
+    placed = {}
+    for uid, ctrs, annos in pods[:50]:
+        r = first.filter(uid, ctrs, annos, names)
+        if r["node"] is not None:
+            placed[uid] = (r["node"], r["ids"])
+    assert len(placed) > 20
+    second = v.hostlib.Scheduler(max_nodes=64, incremental=True)
+    for n, devs in cluster.items():
+        half = len(devs) // 2  # two register annotations per node (two vendors' plugins): the node GAINS devices
+        assert second.register_node(n, _encode_node_devices(devs[:half])) == half
+        assert second.register_node(n, _encode_node_devices(devs[half:])) == len(devs) - half
+        assert second.register_node(n, _encode_node_devices(devs[half:])) == 0  # seen again 15 s later: nothing new
+    second.register_node("bogus", "no-colon-here")  # rejected by DecodeNodeDevices, not registered
+    for uid, (node, ids) in placed.items():
+        second.on_add_pod(uid, node, ids)
+    second.on_add_pod("half-annotated", "node-000", None)  # no ids annotation: ignored (:82-85)
+    gone = list(placed)[3]
+    second.on_add_pod(gone, *placed[gone], terminated=True)  # Succeeded/Failed pod: its usage is released (:86-89)
+    first.del_pod(gone)
+    for uid, ctrs, annos in pods[50:]:
+        a = first.filter(uid, ctrs, annos, names + ["bogus"])
+        b = second.filter(uid, ctrs, annos, names + ["bogus"])
+        assert a == b, (uid, a, b)
+    # a vendor's devices leave a node (rmNodeDevice, nodes.go:76-101)
+    n0 = names[0]
+    for sch in (first, second):
+        sch.rm_node_devices(n0, _encode_node_devices(cluster[n0][:2]))
+    a = first.filter("after-rm", [{"gpu": len(cluster[n0]) - 1}], {}, [n0])
+    b = second.filter("after-rm", [{"gpu": len(cluster[n0]) - 1}], {}, [n0])
+    assert a == b and a["node"] is None  # only len-2 devices are left
+    first.close()
+    second.close()
+
+
 def test_host_mirror_without_gpu(built):
     """CPU box: the C++ host mirror loads; a pod that asks for no vGPU passes every node without
     touching the GPU (scheduler.go:357-370); a pod that does ask fails LOUDLY -- no CPU fallback"""
