@@ -213,6 +213,36 @@ __device__ __forceinline__ void publish(bool fit, float score, int k, int lane, 
     }
 }
 
+// Small batches (one pod chunk of <= 32 pods, e.g. the single pod of a Filter call): every warp
+// of every item would hit the same few keys[] words with atomics -- 31250 same-address pairs at
+// 1M nodes.  Instead lane k keeps pod k's candidate across all the CTA's items and the CTA
+// publishes once.
+template <int WARPS>
+__device__ __forceinline__ void flush_small(unsigned long long acckey, int32_t acccnt, int lane, int warp,
+                                            int n_pods, const int32_t *__restrict__ orig_or_null,
+                                            const GenPod *__restrict__ pods_or_null,
+                                            unsigned long long *__restrict__ keys, int32_t *__restrict__ counts) {
+    __shared__ unsigned long long s_k[WARPS][kWarp];
+    __shared__ int32_t s_c[WARPS][kWarp];
+    s_k[warp][lane] = acckey;
+    s_c[warp][lane] = acccnt;
+    __syncthreads();
+    if (warp == 0 && lane < n_pods) {
+        unsigned long long kk = 0ull;
+        int32_t cc = 0;
+        const int nw = (int)(blockDim.x >> 5); // <= WARPS: small snapshots run fewer warps per CTA
+        for (int w = 0; w < nw; w++) {
+            kk = s_k[w][lane] > kk ? s_k[w][lane] : kk;
+            cc += s_c[w][lane];
+        }
+        if (kk != 0ull) {
+            const int op = orig_or_null ? orig_or_null[lane] : pods_or_null[lane].orig;
+            atomicMax(&keys[op], kk);
+            atomicAdd(&counts[op], cc);
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------------
 // K1 (single-request pods).  CTA item = (group of warps_per_cta node tiles, pod chunk).
 // NUMS1: Nums == 1 -> the first fitting device in walk order decides, its score was
@@ -229,25 +259,42 @@ __global__ void __launch_bounds__(256)
     DevReq *s_req = reinterpret_cast<DevReq *>(smem_raw);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int n_items = L.n_chunks * L.n_tile_groups;
+    const bool small = n_pods <= kWarp; // one chunk, one group of pods: see flush_small
+    const bool one_chunk = L.n_chunks == 1;
+    bool need_totalmem = true;
+    unsigned long long acckey = 0ull;
+    int32_t acccnt = 0;
 
     for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
         const int chunk = item / L.n_tile_groups, tg = item - chunk * L.n_tile_groups;
         const int pod0 = chunk * L.chunk_len;
         const int npod = min(L.chunk_len, n_pods - pod0);
-        __syncthreads(); // previous item's readers are done
-        {
+        if (!one_chunk || item == (int)blockIdx.x) {
+            // stage the chunk's requests; with a single chunk once per CTA, and the warps then
+            // stream their node tiles without meeting at a barrier again
+            __syncthreads(); // previous item's readers are done
             const int4 *src = reinterpret_cast<const int4 *>(reqs + pod0);
             int4 *dst = reinterpret_cast<int4 *>(s_req);
-            for (int i = threadIdx.x; i < npod * 2; i += blockDim.x) dst[i] = __ldg(&src[i]);
+            int pct = 0;
+            for (int i = threadIdx.x; i < npod * 2; i += blockDim.x) {
+                const int4 x = __ldg(&src[i]);
+                dst[i] = x;
+                if (i & 1) pct |= (uint32_t)x.y & R_USEPCT; // second half of a DevReq: .y = flags
+            }
+            need_totalmem = __syncthreads_or(pct) != 0;
         }
-        __syncthreads();
         const int tile = tg * L.warps_per_cta + warp;
         if (tile >= n_tiles) continue;
 
         const int4 *tp = walk + (size_t)tile * kWalkWords * (DM / 4) * kWarp;
         int32_t totalmem[DM], freemem[DM], freecores[DM], meta[DM];
         int32_t count[DM], freeslots[DM], score1[DM];
-        load_word<DM>(tp, W_TOTALMEM, lane, totalmem);
+        if (need_totalmem) { // Totalmem only enters through memory percentages (score.go:117-120)
+            load_word<DM>(tp, W_TOTALMEM, lane, totalmem);
+        } else {
+#pragma unroll
+            for (int j = 0; j < DM; j++) totalmem[j] = 0;
+        }
         load_word<DM>(tp, W_FREEMEM, lane, freemem);
         load_word<DM>(tp, W_FREECORES, lane, freecores);
         load_word<DM>(tp, W_META, lane, meta);
@@ -316,13 +363,17 @@ __global__ void __launch_bounds__(256)
                 }
                 publish(fit, score, k, lane, row0, mykey, mycnt);
             }
-            if (lane < kend && mykey != 0ull) {
+            if (small) {
+                acckey = mykey > acckey ? mykey : acckey;
+                acccnt += mycnt;
+            } else if (lane < kend && mykey != 0ull) {
                 int op = orig[pod0 + pp + lane];
                 atomicMax(&keys[op], mykey);
                 atomicAdd(&counts[op], mycnt);
             }
         }
     }
+    if (small) flush_small<8>(acckey, acccnt, lane, warp, n_pods, orig, nullptr, keys, counts);
 }
 
 // ------------------------------------------------------------------------------------
@@ -343,6 +394,9 @@ __global__ void __launch_bounds__(128)
                      uint32_t *__restrict__ vfit, float *__restrict__ vscore, int32_t vwords) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int n_items = L.n_chunks * L.n_tile_groups;
+    const bool small = n_pods <= kWarp; // see flush_small
+    unsigned long long acckey = 0ull;
+    int32_t acccnt = 0;
 
     for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
         const int chunk = item / L.n_tile_groups, tg = item - chunk * L.n_tile_groups;
@@ -508,13 +562,17 @@ __global__ void __launch_bounds__(128)
                 }
                 publish(fitn, score, k, lane, row0, mykey, mycnt);
             }
-            if (lane < kend && mykey != 0ull) {
+            if (small) {
+                acckey = mykey > acckey ? mykey : acckey;
+                acccnt += mycnt;
+            } else if (lane < kend && mykey != 0ull) {
                 int op = pods[pod0 + pp + lane].orig;
                 atomicMax(&keys[op], mykey);
                 atomicAdd(&counts[op], mycnt);
             }
         }
     }
+    if (small) flush_small<4>(acckey, acccnt, lane, warp, n_pods, nullptr, pods, keys, counts);
 }
 
 

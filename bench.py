@@ -230,6 +230,7 @@ def main():
     ap.add_argument("--config", default="cfg3")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-hbm-leg", action="store_true", help="skip the single-pod 1M-node (HBM-bound regime) leg")
     ap.add_argument("--check", action="store_true",
                     help="rank 0 re-checks a sample of pods against the oracle over ALL shards (not timed)")
     ap.add_argument("--sweep", action="store_true", help="CPU/GPU crossover grid instead of the bench line")
@@ -370,6 +371,28 @@ def main():
                    "k1_us": 1e6 * k1, "k1_algorithmic_GBps": b1 / k1 / 1e9}
         ctx.pods_upload(pods, reqs)  # restore the batch for anything that follows
 
+    # ---- the regime where the pass IS HBM-bound (P <= ~6): one pod, 1M nodes, snapshot
+    # (256 MB) larger than L2, so every call streams it from HBM ----------------------------------
+    hbm_regime = None
+    if world == 1 and not args.no_hbm_leg and args.config == "cfg3":
+        reps = max(1, 1_000_000 // npg)
+        big = v.Snapshot(np.tile(snap.planes, (1, reps, 1)), np.tile(snap.ndev, reps), snap.type_names)
+        with v.Context(max_nodes=big.n_nodes, max_devices=D, max_pods=1, device=local) as c1:
+            c1.upload(big)
+            one = batch.select([0])
+            p1, r1 = v.capi.pack_batch(one, snap.type_names)
+            ks = []
+            for i in range(40):
+                c1.score_packed(p1, r1)
+                ks.append(c1.timing().score_ms)
+            k = sorted(ks[10:])[len(ks[10:]) // 2] * 1e-3
+            b = algorithmic_bytes(big.n_nodes, D, 1, 1)
+            pk, pk_src = measured_peak()
+            hbm_regime = {"workload": f"{big.n_nodes} nodes x {D} devices x 1 pod, snapshot resident (256 MB > L2)",
+                          "bound": "hbm", "kernel": "k1_score_single<8,true> (+ memset, merge: the whole score phase)",
+                          "achieved": b / k / 1e9, "peak": pk, "unit": "GB/s", "frac": b / k / 1e9 / pk,
+                          "algorithmic_bytes": int(b), "kernel_us": 1e6 * k, "peak_source": pk_src}
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -426,6 +449,8 @@ def main():
         line["check"] = check
     if latency:
         line["filter_latency"] = latency
+    if hbm_regime:
+        line["roofline_hbm_regime"] = hbm_regime
     if not args.no_cpu:
         val, th, dt, sp = cpu_arm(snap, batch, 64)   # calibrate
         sample = max(64, min(P, int(64 * 12.0 / max(dt, 1e-3))))

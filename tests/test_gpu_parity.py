@@ -27,7 +27,9 @@ def test_kat_gpu(built, k):
 
 
 @pytest.mark.parametrize("cfg,n,p", [("cfg1", 64, 1), ("cfg2", 10_000, 256), ("cfg3", 5000, 400),
-                                     ("cfg3", 33, 31), ("cfg4", 4000, 300), ("cfg4", 1000, 33)])
+                                     ("cfg3", 33, 31), ("cfg4", 4000, 300), ("cfg4", 1000, 33),
+                                     # <= 32 pods: candidates are kept per CTA across its node tiles
+                                     ("cfg3", 70_000, 1), ("cfg3", 9000, 32), ("cfg4", 40_000, 7)])
 def test_differential_full_matrix(built, cfg, n, p):
     snap, batch = v.workload.make_config(cfg, n, p)
     got = gpu_score(snap, batch)
