@@ -388,10 +388,18 @@ def main():
             k = sorted(ks[10:])[len(ks[10:]) // 2] * 1e-3
             b = algorithmic_bytes(big.n_nodes, D, 1, 1)
             pk, pk_src = measured_peak()
+            tr = None
+            try:
+                with open(os.path.join(ROOT, "profiles", "k1_traffic.json")) as f:
+                    tr = json.load(f).get("p1_dram_bytes_per_launch")
+            except Exception:
+                pass
             hbm_regime = {"workload": f"{big.n_nodes} nodes x {D} devices x 1 pod, snapshot resident (256 MB > L2)",
                           "bound": "hbm", "kernel": "k1_score_single<8,true> (+ memset, merge: the whole score phase)",
                           "achieved": b / k / 1e9, "peak": pk, "unit": "GB/s", "frac": b / k / 1e9 / pk,
-                          "algorithmic_bytes": int(b), "kernel_us": 1e6 * k, "peak_source": pk_src}
+                          "algorithmic_bytes": int(b), "kernel_us": 1e6 * k, "peak_source": pk_src, "traffic": tr,
+                          "note": "frac can exceed 1: the algorithmic bytes charge all 8 prepared words per device, "
+                                  "the kernel reads 4-6 of them (traffic = ncu DRAM bytes per launch)"}
 
     if rank != 0:
         if world > 1:
