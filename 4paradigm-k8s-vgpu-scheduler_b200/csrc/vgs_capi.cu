@@ -27,7 +27,12 @@ struct DeviceGuard {
     bool ok = false;
     explicit DeviceGuard(int dev) {
         if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
-        ok = cudaSetDevice(dev) == cudaSuccess;
+        if (prev == dev) { // the usual case: nothing to switch, nothing to restore
+            ok = true;
+            prev = -1;
+        } else {
+            ok = cudaSetDevice(dev) == cudaSuccess;
+        }
     }
     ~DeviceGuard() {
         if (prev >= 0) cudaSetDevice(prev);
@@ -35,6 +40,8 @@ struct DeviceGuard {
 };
 
 } // namespace
+
+constexpr int32_t kDirectOutPods = 64;
 
 struct vgs_ctx {
     vgs_config cfg{};
@@ -77,6 +84,8 @@ struct vgs_ctx {
     int32_t n_types_used = VGS_MAX_TYPES; // largest type id of the snapshot + 1
     bool zero_copy_ok = true;             // VGS_ZERO_COPY=0 disables the kernel-driven upload
     bool have_pods = false, scored = false, resolved = false;
+    bool direct_out = false; // K3 of the current batch wrote h_results / h_picks itself
+    int32_t dirty_pods = 0; // leading slots of d_keys / d_counts that may be non-zero (K3 clears behind itself)
 
     // results
     unsigned long long *d_keys = nullptr;
@@ -297,6 +306,8 @@ int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
     // int32 counts) so that shards can exchange both with a single all-gather
     CUI(cudaMalloc(&c->d_keys, P * (sizeof(unsigned long long) + sizeof(int32_t)) + 8));
     c->d_counts = reinterpret_cast<int32_t *>(c->d_keys + P);
+    CUI(cudaMemset(c->d_keys, 0, P * (sizeof(unsigned long long) + sizeof(int32_t)) + 8));
+    c->dirty_pods = 0;
     CUI(cudaMalloc(&c->d_results, P * sizeof(vgs_result)));
     CUI(cudaMallocHost(&c->h_results, P * sizeof(vgs_result)));
     CUI(cudaMalloc(&c->d_picks, (size_t)cfg->max_picks * sizeof(vgs_pick)));
@@ -677,14 +688,18 @@ static int score_locked(vgs_ctx *c) {
     if (!c->have_pods) return fail(c, VGS_ESTATE, "score before pod upload");
     const int32_t P = c->n_pods;
     rec(c, EV_SC0);
-    if (P > 0) {
-        if (P * 4 >= c->cfg.max_pods) { // keys and counts are one block: clear it in one go
+    // the candidate block is zero at rest: allocated zeroed, and K3 clears what it reads.  Only a pass
+    // that was scored but never resolved leaves slots dirty.
+    if (c->dirty_pods > 0) {
+        const int32_t n = c->dirty_pods > P ? c->dirty_pods : P;
+        if (n * 4 >= c->cfg.max_pods) { // keys and counts are one block: clear it in one go
             CU(cudaMemsetAsync(c->d_keys, 0, (size_t)c->cfg.max_pods * 12, c->st));
         } else {
-            CU(cudaMemsetAsync(c->d_keys, 0, (size_t)P * sizeof(unsigned long long), c->st));
-            CU(cudaMemsetAsync(c->d_counts, 0, (size_t)P * sizeof(int32_t), c->st));
+            CU(cudaMemsetAsync(c->d_keys, 0, (size_t)n * sizeof(unsigned long long), c->st));
+            CU(cudaMemsetAsync(c->d_counts, 0, (size_t)n * sizeof(int32_t), c->st));
         }
     }
+    c->dirty_pods = P;
     ScoreArgs a;
     a.walk = c->d_walk;
     a.n_tiles = c->n_tiles;
@@ -761,14 +776,18 @@ static int score_locked(vgs_ctx *c) {
 static int resolve_locked(vgs_ctx *c) {
     if (!c->scored) return fail(c, VGS_ESTATE, "resolve before score");
     rec(c, EV_RS0);
-    if (c->n_picks) CU(cudaMemsetAsync(c->d_picks, 0, (size_t)c->n_picks * sizeof(vgs_pick), c->st));
+    // a Filter-sized batch: K3 stores its records into the pinned host mirrors as well (the pinned
+    // allocations are device-accessible under unified addressing), so the download is one status word
+    c->direct_out = c->n_pods <= kDirectOutPods;
     CU(launch_resolve(raw_const(c), c->n_nodes, c->dmax, c->cfg.row_base,
                       reinterpret_cast<const vgs_pod *>(c->d_stage + c->off_pods),
                       reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqs),
                       reinterpret_cast<const int32_t *>(c->d_stage + c->off_pick), c->n_pods, c->d_keys,
-                      c->d_counts, c->d_results, c->d_picks, c->d_status, c->st));
+                      c->d_counts, c->d_results, c->d_picks, c->d_status, c->st, nullptr,
+                      c->direct_out ? c->h_results : nullptr, c->direct_out ? c->h_picks : nullptr));
     if (c->n_pods) c->launches++;
     rec(c, EV_RS1);
+    c->dirty_pods = 0;
     c->resolved = true;
     return VGS_OK;
 }
@@ -777,10 +796,10 @@ static int download_locked(vgs_ctx *c, vgs_result *results, vgs_pick *picks) {
     if (!c->resolved) return fail(c, VGS_ESTATE, "download before resolve");
     if (c->n_pods > 0 && !results) return fail(c, VGS_EINVAL, "null results");
     rec(c, EV_DH0);
-    if (c->n_pods)
+    if (c->n_pods && !c->direct_out)
         CU(cudaMemcpyAsync(c->h_results, c->d_results, (size_t)c->n_pods * sizeof(vgs_result),
                            cudaMemcpyDeviceToHost, c->st));
-    if (c->n_picks && picks)
+    if (c->n_picks && picks && !c->direct_out)
         CU(cudaMemcpyAsync(c->h_picks, c->d_picks, (size_t)c->n_picks * sizeof(vgs_pick),
                            cudaMemcpyDeviceToHost, c->st));
     CU(cudaMemcpyAsync(c->h_status, c->d_status, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->st));
@@ -845,11 +864,8 @@ int vgs_drain_batch(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_r
     int rc;
     if ((rc = pods_upload_locked(c, n_pods, pods, n_reqs, reqs)) != VGS_OK) return rc;
     rec(c, EV_SC0);
-    if (n_pods > 0) {
-        CU(cudaMemsetAsync(c->d_keys, 0, (size_t)n_pods * sizeof(unsigned long long), c->st));
-        CU(cudaMemsetAsync(c->d_counts, 0, (size_t)n_pods * sizeof(int32_t), c->st));
-    }
-    if (c->n_picks) CU(cudaMemsetAsync(c->d_picks, 0, (size_t)c->n_picks * sizeof(vgs_pick), c->st));
+    if (c->dirty_pods > 0) CU(cudaMemsetAsync(c->d_keys, 0, (size_t)c->cfg.max_pods * 12, c->st));
+    c->dirty_pods = n_pods;
     ScoreArgs a;
     a.walk = c->d_walk, a.n_tiles = c->n_tiles, a.n_nodes = c->n_nodes, a.row_base = c->cfg.row_base;
     a.keys = c->d_keys, a.counts = c->d_counts;
@@ -872,6 +888,8 @@ int vgs_drain_batch(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_r
     rec(c, EV_SC1);
     c->scored = true;
     c->resolved = true;
+    c->dirty_pods = 0; // every pod's K3 cleared its slot
+    c->direct_out = false;
     c->version++;
     return download_locked(c, results, picks);
 }

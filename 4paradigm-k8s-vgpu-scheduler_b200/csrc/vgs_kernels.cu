@@ -21,7 +21,9 @@
 #include <stdint.h>
 
 #include <cstdlib>
+#include <mutex>
 #include <type_traits>
+#include <vector>
 
 #include "../../include/vgpuscore.h"
 #include "vgs_kernels.h"
@@ -1206,9 +1208,12 @@ __global__ void __launch_bounds__(64)
     k3_resolve(RawPlanes raw, int32_t n_nodes, int32_t dmax, int32_t row_base,
                const vgs_pod *__restrict__ pods, const DevReq *__restrict__ reqs,
                const int32_t *__restrict__ pick_begin, int32_t n_pods,
-               const unsigned long long *__restrict__ keys, const int32_t *__restrict__ counts,
+               unsigned long long *__restrict__ keys, int32_t *__restrict__ counts,
                vgs_result *__restrict__ results, vgs_pick *__restrict__ picks,
-               uint32_t *__restrict__ status, int32_t *__restrict__ commit_rowlist) {
+               uint32_t *__restrict__ status, int32_t *__restrict__ commit_rowlist,
+               vgs_result *__restrict__ host_results, vgs_pick *__restrict__ host_picks) {
+    // host_results / host_picks != nullptr (small batches): the records are ALSO stored straight into
+    // the caller-facing pinned host buffers (posted PCIe writes), which spares the two D2H copies
     // commit_rowlist != nullptr (sequential drain, one pod per launch): the winner's picks are
     // also folded into the raw planes (addPod, scheduler.go:280-297,394) and the touched row is
     // named for re-preparation
@@ -1218,22 +1223,41 @@ __global__ void __launch_bounds__(64)
     const unsigned long long key = keys[p];
     vgs_result res;
     res.fit_count = counts[p];
+    // K3 is the last reader of the candidate block: leave it zero for the next score pass
+    keys[p] = 0ull;
+    counts[p] = 0;
+    const vgs_pod pod = pods[p];
+    const int32_t pick_lo = pick_begin[pod.req_begin], pick_hi = pick_begin[pod.req_begin + pod.n_reqs];
+    // picks of a pod without a winner on this shard are all zero
+    auto zero_picks = [&]() {
+        vgs_pick z;
+        z.slot = z.usedmem = z.usedcores = 0;
+        for (int32_t i = pick_lo; i < pick_hi; i++) {
+            picks[i] = z;
+            if (host_picks) host_picks[i] = z;
+        }
+    };
     if (key == 0ull) {
         res.best_row = -1;
         res.score = 0.0f;
         res.n_picks = 0;
         results[p] = res;
+        if (host_results) host_results[p] = res;
+        zero_picks();
         return;
     }
-    const vgs_pod pod = pods[p];
     const int32_t grow = (int32_t)(uint32_t)key;
     const uint32_t kbits = unorder_bits((uint32_t)(key >> 32));
     res.best_row = grow;
     res.score = __uint_as_float(kbits);
-    res.n_picks = pick_begin[pod.req_begin + pod.n_reqs] - pick_begin[pod.req_begin];
+    res.n_picks = pick_hi - pick_lo;
     results[p] = res;
+    if (host_results) host_results[p] = res;
     const int32_t row = grow - row_base;
-    if (row < 0 || row >= n_nodes) return; // another shard owns the winner
+    if (row < 0 || row >= n_nodes) { // another shard owns the winner
+        zero_picks();
+        return;
+    }
 
     const int32_t nd = raw.ndev[row];
     const size_t base = (size_t)row * dmax;
@@ -1330,6 +1354,7 @@ __global__ void __launch_bounds__(64)
             pk.usedmem = tmem[t];
             pk.usedcores = rq.coresreq;
             picks[pb + t] = pk;
+            if (host_picks) host_picks[pb + t] = pk;
         }
     }
     if (commit_rowlist && alive) {
@@ -1439,6 +1464,32 @@ cudaError_t launch_prepare(int dm, const RawPlanes &raw, int32_t n_nodes, int32_
     return cudaGetLastError();
 }
 
+// cudaOccupancyMaxActiveBlocksPerMultiprocessor costs microseconds and plan() asks several times
+// per launch; the answer only depends on (kernel, device, block, dynamic smem)
+template <typename K>
+static cudaError_t cached_occupancy(int *occ, K kernel, int dev, int block, int smem) {
+    struct Entry {
+        const void *k;
+        int dev, block, smem, occ;
+    };
+    static std::mutex mu;
+    static std::vector<Entry> cache;
+    const void *kp = reinterpret_cast<const void *>(kernel);
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        for (const Entry &e : cache)
+            if (e.k == kp && e.dev == dev && e.block == block && e.smem == smem) {
+                *occ = e.occ;
+                return cudaSuccess;
+            }
+    }
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, kernel, block, smem);
+    if (e != cudaSuccess) return e;
+    std::lock_guard<std::mutex> lk(mu);
+    cache.push_back(Entry{kp, dev, block, smem, *occ});
+    return cudaSuccess;
+}
+
 template <typename K>
 static cudaError_t plan(K kernel, int dev, int32_t n_tiles, int32_t n_pods, int max_warps,
                         int smem_per_pod, ScoreLaunch *L) {
@@ -1454,7 +1505,7 @@ static cudaError_t plan(K kernel, int dev, int32_t n_tiles, int32_t n_pods, int 
     int chunk = 512;
     for (;;) {
         L->smem = chunk * smem_per_pod;
-        cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, L->block, L->smem);
+        cudaError_t e = cached_occupancy(&occ, kernel, dev, L->block, L->smem);
         if (e != cudaSuccess) return e;
         if (occ < 1) occ = 1;
         long long resident = (long long)sms * occ;
@@ -1616,12 +1667,13 @@ cudaError_t launch_merge(const unsigned long long *gk, const int32_t *gc, int32_
 
 cudaError_t launch_resolve(const RawPlanes &raw, int32_t n_nodes, int32_t dmax, int32_t row_base,
                            const vgs_pod *pods, const DevReq *reqs, const int32_t *pick_begin,
-                           int32_t n_pods, const unsigned long long *keys, const int32_t *counts,
+                           int32_t n_pods, unsigned long long *keys, int32_t *counts,
                            vgs_result *results, vgs_pick *picks, uint32_t *status, cudaStream_t st,
-                           int32_t *commit_rowlist) {
+                           int32_t *commit_rowlist, vgs_result *host_results, vgs_pick *host_picks) {
     if (n_pods <= 0) return cudaSuccess;
     k3_resolve<<<(n_pods + 63) / 64, 64, 0, st>>>(raw, n_nodes, dmax, row_base, pods, reqs, pick_begin,
-                                                 n_pods, keys, counts, results, picks, status, commit_rowlist);
+                                                 n_pods, keys, counts, results, picks, status, commit_rowlist,
+                                                 host_results, host_picks);
     return cudaGetLastError();
 }
 

@@ -52,11 +52,14 @@ cudaError_t launch_score_sliced(int nums, int dev, const ScoreArgs &a, const Sli
 cudaError_t launch_merge(const unsigned long long *gk, const int32_t *gc, int32_t n_shards,
                          int32_t stride, int32_t cstride, int32_t n_pods, unsigned long long *keys,
                          int32_t *counts, cudaStream_t st);
+// K3 also clears keys[p] / counts[p] (it is their last reader) and writes every pick of every pod,
+// zeros where the pod has no winner on this shard: neither needs a memset before the next pass
 cudaError_t launch_resolve(const RawPlanes &raw, int32_t n_nodes, int32_t dmax, int32_t row_base,
                            const vgs_pod *pods, const DevReq *reqs, const int32_t *pick_begin,
-                           int32_t n_pods, const unsigned long long *keys, const int32_t *counts,
+                           int32_t n_pods, unsigned long long *keys, int32_t *counts,
                            vgs_result *results, vgs_pick *picks, uint32_t *status, cudaStream_t st,
-                           int32_t *commit_rowlist = nullptr);
+                           int32_t *commit_rowlist = nullptr, vgs_result *host_results = nullptr,
+                           vgs_pick *host_picks = nullptr);
 cudaError_t launch_delta(const RawPlanesMut &raw, int32_t n_nodes, int32_t dmax, int32_t row_base,
                          const vgs_delta *deltas, int32_t n, int32_t *rowlist, uint32_t *status,
                          cudaStream_t st);

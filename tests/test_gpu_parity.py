@@ -415,6 +415,35 @@ def test_cambricon_drain_and_shards(built):
     assert np.array_equal(after, planes)
 
 
+def test_candidate_block_is_clean_between_passes(built):
+    """K3 clears the candidate keys/counts it reads and writes every pick itself, so a pass needs no
+    memset -- unless an earlier pass was scored and never resolved, possibly for MORE pods than the next one"""
+    snap, batch = v.workload.make_config("cfg3", 3000, 200)
+    want = oracle.score_packed(snap, batch)
+    small = batch.select(list(range(10)))
+    want_small = oracle.score_packed(snap, small)
+    with v.Context(max_nodes=3000, max_pods=256, max_reqs=512, max_picks=1024) as ctx:
+        ctx.upload(snap)
+        pods, reqs = v.capi.pack_batch(batch, snap.type_names)
+        sp, sr = v.capi.pack_batch(small, snap.type_names)
+        for _ in range(3):  # back-to-back passes, no clearing in between
+            assert_same(ctx.score(batch), want, "repeat")
+        ctx.pods_upload(pods, reqs)
+        ctx.score_resident()  # 200 dirty slots, never resolved
+        ctx.score_resident()  # ... and scored again: counts must not double
+        ctx.resolve_resident()
+        res, picks = ctx.results_download()
+        assert np.array_equal(res["fit_count"], want.fit_count) and np.array_equal(res["best_row"], want.best_row)
+        ctx.pods_upload(pods, reqs)
+        ctx.score_resident()  # dirty again, abandoned for a SMALLER batch
+        assert_same(ctx.score(small), want_small, "small after abandoned pass")
+        assert_same(ctx.score(batch), want, "big after small")  # slots 10..199 must have been cleared too
+        # a pod that fits nowhere gets zero picks even when the slots held another pod's picks before
+        nofit = v.PodBatch.from_pods([{"containers": [[(2, 10**9, 101, 0)]]}] * 3)
+        got = ctx.score(nofit)
+        assert (got.best_row == -1).all() and not got.picks.any()
+
+
 def test_pinned_planes_take_the_zero_copy_upload(built, monkeypatch):
     """pinned, aligned host planes are pulled over PCIe by a kernel; pageable ones by cudaMemcpy:
     same resident snapshot either way"""
