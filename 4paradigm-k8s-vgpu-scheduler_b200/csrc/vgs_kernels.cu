@@ -745,7 +745,8 @@ __global__ void __launch_bounds__(128)
         load_word<8>(tp, W_COUNT, lane, wa);
         load_word<8>(tp, W_FREESLOTS, lane, wb);
     }
-    const int r_mem = VGS_MAX_TYPES, r_pct = r_mem + tb.km + 1, r_core = r_pct + tb.kp + 1;
+    // rows as the score kernel indexes them (see SliceTab::row_shift)
+    const int r_mem = VGS_MAX_TYPES - tb.row_shift, r_pct = r_mem + tb.km + 1, r_core = r_pct + tb.kp + 1;
     const uint32_t ndev = ((uint32_t)meta[0] >> M_NDEV_SHIFT) & 15u;
 #pragma unroll
     for (int j = 0; j < 8; j++) {
@@ -1008,9 +1009,20 @@ __global__ void __launch_bounds__(128)
         for (int k = 1; k < nv; k++) below[k * T + tid] |= below[(k - 1) * T + tid];
     }
 
+    // K1p stored the rows already in this kernel's numbering: one multiply-add per table access
+    const uint32_t stride_b = stride * 4u;
+    const unsigned char *tab_col = reinterpret_cast<const unsigned char *>(TABSMEM ? tabs : tb.base) + (size_t)col * 4u;
+    // the column address as an opaque 64-bit value: one IMAD.WIDE (row * stride + column) feeds the load
+    unsigned long long tab_col_g = reinterpret_cast<unsigned long long>(tab_col);
+    asm volatile("" : "+l"(tab_col_g));
     auto TAB = [&](uint32_t row) -> uint32_t {
-        if (TABSMEM) return tabs[(row >= (uint32_t)VGS_MAX_TYPES ? row - (uint32_t)drop : row) * stride + col];
-        return __ldg(&tb.base[row * stride + col]);
+        if (TABSMEM) return *reinterpret_cast<const uint32_t *>(tab_col + row * stride_b);
+        return __ldg(reinterpret_cast<const uint32_t *>(tab_col_g + (unsigned long long)row * stride_b));
+    };
+    const unsigned char *below_tid = reinterpret_cast<const unsigned char *>(below + tid);
+    const uint32_t tstride_b = (uint32_t)T * 4u;
+    auto BELOW = [&](uint32_t cls) -> uint32_t { // below[cls * T + tid]
+        return *reinterpret_cast<const uint32_t *>(below_tid + cls * tstride_b);
     };
     auto fit_of = [&](const uint4 &d) -> uint32_t {
         return TAB(d.x & 0xffffu) & (TAB(d.x >> 16) | TAB(d.y & 0xffffu)) & TAB(d.y >> 16);
@@ -1066,7 +1078,7 @@ __global__ void __launch_bounds__(128)
                         const uint32_t f = fit_of(d);
                         nw[u][j] = f & rem;
                         rem &= ~f;
-                        h |= nw[u][j] & below[d.w * T + tid];
+                        h |= nw[u][j] & BELOW(d.w);
                     }
                     xs[u] = ~rem;
                     hit[u] = h;
@@ -1079,7 +1091,7 @@ __global__ void __launch_bounds__(128)
                         for (int j = 0; j < 8; j++) {
                             const uint4 d = dv[l * 8 + j];
                             if (VERIFY && active) mark(nw[u][j], node, d.z);
-                            const uint32_t h = nw[u][j] & below[d.w * T + tid];
+                            const uint32_t h = nw[u][j] & BELOW(d.w);
                             if (h) raise(h, d.z, node);
                         }
                     }
@@ -1107,7 +1119,7 @@ __global__ void __launch_bounds__(128)
                         for (int b = a + 1; b < 8; b++) {
                             const int q = pair_index(a, b);
                             const uint32_t cl = (cw[q >> 2] >> ((q & 3) * 8)) & 0xffu;
-                            h |= first[u][a] & second[u][b] & below[cl * T + tid];
+                            h |= first[u][a] & second[u][b] & BELOW(cl);
                         }
                     xs[u] = seen2; // the node fits a pod iff two devices fit
                     hit[u] = h;
@@ -1129,7 +1141,7 @@ __global__ void __launch_bounds__(128)
                                     wrap_add((int32_t)(da.w & 0xffffffu), (int32_t)(db.w & 0xffffffu)),
                                     (int32_t)(da.w >> 24) - 2));
                                 if (VERIFY && active) mark(wab, node, sb);
-                                const uint32_t h = wab & below[(uint32_t)pc[l * 32 + pair_index(a, b)] * T + tid];
+                                const uint32_t h = wab & BELOW((uint32_t)pc[l * 32 + pair_index(a, b)]);
                                 if (h) raise(h, sb, node);
                             }
                         }
@@ -1581,11 +1593,33 @@ cudaError_t launch_score_general(int dm, int dev, const ScoreArgs &a, const DevR
 
 
 template <int NUMS>
-static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &tb, int n_types, uint32_t *status,
+static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &tb_in, int n_types, uint32_t *status,
                                    cudaStream_t st, int *n_launched) {
     const int sms = sm_count(dev);
-    // K1p: table rows + candidate scores per device, distinct scores -> classes
     cudaError_t e;
+    SliceTab tb = tb_in;
+    int warps = (tb.W + 31) / 32;
+    if (warps > 4) warps = 4;
+    const int T = warps * 32;
+    const int gy = (tb.W + T - 1) / T;
+    if (n_types < 1) n_types = 1;
+    if (n_types > VGS_MAX_TYPES) n_types = VGS_MAX_TYPES;
+    const int rows_s = n_types + (tb.km + 1) + (tb.kp + 1) + 4 * (tb.kc + 1);
+    static int force_tab = -2;
+    if (force_tab == -2) {
+        const char *ev = getenv("VGS_SLICE_TABSMEM");
+        force_tab = ev ? atoi(ev) : -1;
+    }
+    // tables in shared memory when small (else global / L1)
+    static int tab_kb = -1;
+    if (tab_kb < 0) {
+        const char *ev = getenv("VGS_SLICE_TABSMEM_KB");
+        tab_kb = ev ? atoi(ev) : 8;
+    }
+    const bool tabsmem = force_tab >= 0 ? force_tab != 0 : (size_t)rows_s * T * 4 <= (size_t)tab_kb * 1024;
+    tb.row_shift = tabsmem ? VGS_MAX_TYPES - n_types : 0;
+
+    // K1p: table rows + candidate scores per device, distinct scores -> classes
     if ((e = cudaMemsetAsync(tb.hset, 0, kSliceHash * sizeof(uint32_t), st)) != cudaSuccess) return e;
     const int nthreads = a.n_tiles * kWarp;
     k1p_collect<NUMS><<<(nthreads + 127) / 128, 128, 0, st>>>(a.walk, a.n_tiles, tb, status);
@@ -1594,13 +1628,6 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     *n_launched += 3;
 
-    int warps = (tb.W + 31) / 32;
-    if (warps > 4) warps = 4;
-    const int T = warps * 32;
-    const int gy = (tb.W + T - 1) / T;
-    if (n_types < 1) n_types = 1;
-    if (n_types > VGS_MAX_TYPES) n_types = VGS_MAX_TYPES;
-    const int rows_s = n_types + (tb.km + 1) + (tb.kp + 1) + 4 * (tb.kc + 1);
     // every scout-th tile is walked by the scout launch: about a hundred scout tiles (measured
     // optimum on 100k nodes: stride 24-48), VGS_SCOUT overrides
     static int scout_env = -1;
@@ -1611,13 +1638,6 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
     int scout = scout_env >= 2 ? scout_env : a.n_tiles / 96;
     if (scout < 4) scout = 4;
     if (scout > 32 && scout_env < 2) scout = 32;
-    static int force_tab = -2;
-    if (force_tab == -2) {
-        const char *ev = getenv("VGS_SLICE_TABSMEM");
-        force_tab = ev ? atoi(ev) : -1;
-    }
-    // tables in shared memory when small (else global / L1)
-    const bool tabsmem = force_tab >= 0 ? force_tab != 0 : (size_t)rows_s * T * 4 <= 8 * 1024;
     const int smem = slice_smem(T, NUMS, tabsmem ? rows_s : 0).total;
     auto go = [&](auto kernel) -> cudaError_t {
         if ((e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)) != cudaSuccess) return e;

@@ -94,6 +94,8 @@ struct SliceTab {
     const int32_t *orig;                // class position -> pod index of the batch
     int32_t km, kp, kc;
     int32_t n_pods, W, Wp;
+    int32_t row_shift; // SliceDev rows >= VGS_MAX_TYPES are stored minus this (the score kernel's shared
+                       // copy of the tables drops the type rows that cannot occur); set by the launcher
     // per-batch products of the preparation kernels (K1p), all in device memory
     uint4 *dinfo;      // [n_tiles*32*8] SliceDev, node-major, walk order
     uint8_t *pcls;     // [n_tiles*32][32] score class of each device pair (Nums == 2 class only)
