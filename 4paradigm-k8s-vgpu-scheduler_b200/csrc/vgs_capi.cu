@@ -79,7 +79,9 @@ struct vgs_ctx {
     size_t slice_words = 0;
     SliceTab tab[2] = {};
     bool slice_on[2] = {false, false};
-    int32_t slice_min = 512;     // classes smaller than this use the per-pair kernels
+    int32_t slice_min = 512;     // classes smaller than this use the per-pair kernels ...
+    int32_t slice_small = 64;    // ... unless they have this many pods and pods x nodes >= slice_small_pairs
+    int64_t slice_small_pairs = 16000000;
     bool snap_slice_ok = false;  // snapshot satisfies the sliced kernel's preconditions
     int32_t n_types_used = VGS_MAX_TYPES; // largest type id of the snapshot + 1
     bool zero_copy_ok = true;             // VGS_ZERO_COPY=0 disables the kernel-driven upload
@@ -299,7 +301,7 @@ int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
             c->tab[k].hset = reinterpret_cast<uint32_t *>(c->d_prep[k] + dinfo_b + pcls_b);
             c->tab[k].gvals = reinterpret_cast<uint32_t *>(c->d_prep[k] + dinfo_b + pcls_b + hset_b);
         }
-        if (const char *e = getenv("VGS_SLICE_MIN")) c->slice_min = atoi(e);
+        if (const char *e = getenv("VGS_SLICE_MIN")) c->slice_min = c->slice_small = atoi(e);
         if (const char *e = getenv("VGS_ZERO_COPY")) c->zero_copy_ok = atoi(e) != 0;
     }
     // keys and counts are one allocation ("candidate block": max_pods u64 keys, then max_pods
@@ -500,7 +502,12 @@ static bool build_slice_class(vgs_ctx *c, int k, const DevReq *req, const DevReq
                               const int32_t *orig, int32_t n, cudaError_t *err) {
     *err = cudaSuccess;
     c->slice_on[k] = false;
-    if (n < c->slice_min || n < 1) return false;
+    // >= slice_min pods: always.  From slice_small pods upward when the pass is big enough for the
+    // class set-up (tables, K1p) to pay: measured 100k nodes x 256 pods 0.224 -> 0.176 ms through the
+    // node-sliced kernel, but 100k x 64 and 10k x 256 lose to the per-pair kernel.
+    const bool big = n >= c->slice_min;
+    const bool mid = n >= c->slice_small && (int64_t)n * c->n_nodes >= c->slice_small_pairs;
+    if (n < 1 || !(big || mid)) return false;
     std::vector<int32_t> mv, pv, cv; // sorted distinct thresholds (few in practice)
     auto add = [](std::vector<int32_t> &v, int32_t x) {
         auto it = std::lower_bound(v.begin(), v.end(), x);
@@ -648,20 +655,8 @@ static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, i
             nG++;
         }
     }
-    // The pod-sliced kernels cost the same per warp whether 32 or 1 of its pod words are in
-    // use, so a small remainder beyond a multiple of 1024 pods goes to the per-pair kernel.
-    auto trim_tail = [&](DevReq *h, int32_t *ho, int32_t &n) {
-        if (n < c->slice_min || n < 1024) return;
-        const int32_t rem = n % 1024;
-        if (rem == 0 || rem >= 512) return;
-        for (int32_t i = n - rem; i < n; i++) {
-            hC[nC] = h[i];
-            hoC[nC++] = ho[i];
-        }
-        n -= rem;
-    };
-    trim_tail(hA, hoA, nA);
-    trim_tail(hB, hoB, nB);
+    // (a sliced class keeps all its pods: the launcher gives the words beyond a multiple of 32 to the
+    // node-sliced kernel)
     c->n_pods = n_pods;
     c->n_reqs = n_reqs;
     c->nA = nA;

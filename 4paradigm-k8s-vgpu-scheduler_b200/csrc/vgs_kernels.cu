@@ -729,7 +729,8 @@ cudaError_t launch_slice_tables(const SliceTab &tb, const DevReq *dreq, cudaStre
 // ------------------------------------------------------------------------------------
 template <int NUMS>
 __global__ void __launch_bounds__(128)
-    k1p_collect(const int4 *__restrict__ walk, int32_t n_tiles, SliceTab tb, uint32_t *__restrict__ status) {
+    k1p_collect(const int4 *__restrict__ walk, int32_t n_tiles, SliceTab tb, uint32_t *__restrict__ status,
+                bool want_scores) { // want_scores: feed the distinct-score set (the pod-sliced kernel's classes)
     const int node = blockIdx.x * blockDim.x + threadIdx.x;
     if (node >= n_tiles * kWarp) return;
     const int tile = node >> 5, lane = node & 31;
@@ -767,7 +768,7 @@ __global__ void __launch_bounds__(128)
             if (NUMS == 1) {
                 d.a = (uint32_t)wa[j];
                 d.b = (uint32_t)kDict;
-                hset_insert(tb.hset, d.a, status);
+                if (want_scores) hset_insert(tb.hset, d.a, status);
             } else {
                 d.a = (uint32_t)wa[j];
                 d.b = (uint32_t)wb[j] | (ndev << 24);
@@ -775,7 +776,7 @@ __global__ void __launch_bounds__(128)
         }
         reinterpret_cast<SliceDev *>(tb.dinfo)[(size_t)node * 8 + j] = d;
     }
-    if (NUMS == 2) {
+    if (NUMS == 2 && want_scores) {
 #pragma unroll
         for (int a = 0; a < 7; a++)
 #pragma unroll
@@ -908,7 +909,8 @@ __host__ __device__ inline SliceSmem slice_smem(int T, int nums, int tab_rows) {
 template <int NUMS, bool TABSMEM, bool VERIFY>
 __global__ void __launch_bounds__(128)
     k1_score_sliced(int32_t n_tiles, int32_t n_nodes, int32_t row_base, SliceTab tb, int32_t n_types,
-                    int32_t tiles_per_cta, int32_t phase, int32_t kScout, unsigned long long *__restrict__ keys,
+                    int32_t tiles_per_cta, int32_t phase, int32_t kScout, int32_t sub,
+                    unsigned long long *__restrict__ keys,
                     int32_t *__restrict__ counts, uint32_t *__restrict__ vfit, float *__restrict__ vscore,
                     int32_t vwords) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -946,7 +948,11 @@ __global__ void __launch_bounds__(128)
     const int n_virtual = phase < 0 ? n_tiles
                           : phase == 0 ? (n_tiles + kScout - 1) / kScout
                                        : n_tiles - (n_tiles + kScout - 1) / kScout;
-    const int t_hi = n_virtual - (int)blockIdx.x * tiles_per_cta;
+    // scouts start cold (every node replays) and there are only ~100 scout tiles: `sub` CTAs share
+    // each tile, one slice of its 8 four-node groups apiece, so that the launch fills the machine
+    const int bx = (int)blockIdx.x / sub, lq_hi = ((int)blockIdx.x % sub + 1) * (8 / sub) - 1,
+              lq_lo = ((int)blockIdx.x % sub) * (8 / sub);
+    const int t_hi = n_virtual - bx * tiles_per_cta;
     const int t_lo = max(0, t_hi - tiles_per_cta);
     if (t_hi <= 0) return;
     const int n_my = t_hi - t_lo;
@@ -1064,7 +1070,7 @@ __global__ void __launch_bounds__(128)
         // "could any pod of mine improve here?" against below[] as it stands (stale = larger =
         // safe).  Phase 2 replays, in order and against the live below[], only the nodes whose
         // detection word is non-zero.
-        for (int lq = 7; lq >= 0; lq--) {
+        for (int lq = lq_hi; lq >= lq_lo; lq--) {
             uint32_t xs[4], hit[4];
             if (NUMS == 1) {
                 uint32_t nw[4][8];
@@ -1190,6 +1196,105 @@ __global__ void __launch_bounds__(128)
                                        (unsigned long long)(uint32_t)(row_base + node_lo + (int)r);
         atomicMax(&keys[p], key);
     }
+}
+
+// ------------------------------------------------------------------------------------
+// K1 (node-sliced): ONE pod word (<= 32 pods) of a sliced class, lane = node.  The transposed use of
+// the same word algebra: every lane builds the fit words of its own node's 8 devices from the
+// word's table column (a few hundred bytes, kept in shared memory) and the K1p records, then the
+// warp settles each pod of the word with one ballot + max-reduction over its 32 nodes.  About
+// 1 warp instruction per (pod, node) -- 3x the pod-sliced kernel, 15x below the per-pair one -- which
+// makes it the home of the words a class has beyond a multiple of 32 (a pod-sliced warp costs the
+// same whether 1 or 32 of its words are in use) and of classes of a few words.
+// ------------------------------------------------------------------------------------
+template <int NUMS, bool VERIFY>
+__global__ void __launch_bounds__(128)
+    k1_score_nodesliced(int32_t n_tiles, int32_t n_nodes, int32_t row_base, SliceTab tb, int32_t word0,
+                        unsigned long long *__restrict__ keys, int32_t *__restrict__ counts,
+                        uint32_t *__restrict__ vfit, float *__restrict__ vscore, int32_t vwords) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint32_t *tcol = reinterpret_cast<uint32_t *>(smem_raw); // the word's column, rows in K1p's numbering
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int word = word0 + (int)blockIdx.y;
+    const int rows_g = VGS_MAX_TYPES + tb.km + 1 + tb.kp + 1 + 4 * (tb.kc + 1);
+    const int drop = tb.row_shift, kept_types = VGS_MAX_TYPES - drop;
+    for (int r = threadIdx.x; r < rows_g - drop; r += blockDim.x)
+        tcol[r] = __ldg(&tb.base[(size_t)(r < kept_types ? r : r + drop) * tb.Wp + word]);
+    __syncthreads();
+    const int npw = min(kWarp, tb.n_pods - word * kWarp); // pods of this word
+    const int32_t *orig = tb.orig + word * kWarp;
+    unsigned long long acckey = 0ull; // lane k: pod k of the word, over all this CTA's tiles
+    int32_t acccnt = 0;
+
+    for (int tile = (int)blockIdx.x * (int)(blockDim.x >> 5) + warp; tile < n_tiles;
+         tile += (int)gridDim.x * (int)(blockDim.x >> 5)) {
+        const int row = tile * kWarp + lane;
+        const uint4 *dv = tb.dinfo + (size_t)row * 8;
+        uint4 d[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) d[j] = __ldg(&dv[j]);
+        uint32_t f[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++)
+            f[j] = tcol[d[j].x & 0xffffu] & (tcol[d[j].x >> 16] | tcol[d[j].y & 0xffffu]) & tcol[d[j].y >> 16];
+        uint32_t fitw; // pods this node fits
+        uint32_t t1[8], t2[8];
+        if (NUMS == 1) {
+            uint32_t rem = 0xffffffffu;
+#pragma unroll
+            for (int j = 0; j < 8; j++) { // walk order: the first fitting device is taken
+                t1[j] = f[j] & rem;
+                rem &= ~f[j];
+            }
+            fitw = ~rem;
+        } else {
+            uint32_t seen = 0u, seen2 = 0u;
+#pragma unroll
+            for (int j = 0; j < 8; j++) { // the first two fitting devices are taken
+                t1[j] = f[j] & ~seen;
+                t2[j] = f[j] & seen & ~seen2;
+                seen2 |= seen & f[j];
+                seen |= f[j];
+            }
+            fitw = seen2;
+#pragma unroll
+            for (int j = 0; j < 8; j++) t1[j] = (t1[j] | t2[j]) & fitw; // taken by the pods that fit
+        }
+        const uint32_t row0 = (uint32_t)(row_base + tile * kWarp);
+        unsigned long long mykey = 0ull;
+        int32_t mycnt = 0;
+        for (int b = 0; b < npw; b++) {
+            const uint32_t bit = 1u << b;
+            const bool fit = fitw & bit;
+            float score;
+            if (NUMS == 1) {
+                uint32_t sb = 0u;
+#pragma unroll
+                for (int j = 0; j < 8; j++) sb = (t1[j] & bit) ? d[j].z : sb; // K0's score of that device alone
+                score = __uint_as_float(sb);
+            } else {
+                int32_t total = 0, free_ = 0, nd = 2;
+#pragma unroll
+                for (int j = 0; j < 8; j++)
+                    if (t1[j] & bit) { // score.go:168-170
+                        total = wrap_add(total, (int32_t)d[j].z);
+                        free_ = wrap_add(free_, (int32_t)(d[j].w & 0xffffffu));
+                        nd = (int32_t)(d[j].w >> 24);
+                    }
+                score = fit ? container_score(total, free_, nd - 2) : 0.0f;
+            }
+            if (VERIFY) {
+                const int op = orig[b];
+                const unsigned bal = __ballot_sync(0xffffffffu, fit);
+                if (lane == 0) vfit[(size_t)op * vwords + tile] = bal;
+                if (row < n_nodes) vscore[(size_t)op * n_nodes + row] = fit ? score : 0.0f;
+            }
+            publish(fit, score, b, lane, row0, mykey, mycnt);
+        }
+        acckey = mykey > acckey ? mykey : acckey;
+        acccnt += mycnt;
+    }
+    flush_small<4>(acckey, acccnt, lane, warp, npw, orig, nullptr, keys, counts);
 }
 
 // ------------------------------------------------------------------------------------
@@ -1598,8 +1703,31 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
     const int sms = sm_count(dev);
     cudaError_t e;
     SliceTab tb = tb_in;
+    // Split the class's pod words between the two kernels.  A pod-sliced warp costs ~0.37 warp
+    // instructions per (pod, node) when all its 32 words are in use and the same total when only one is;
+    // a node-sliced word costs ~1 per (pod, node).  So a few words beyond a multiple of 32 (or a class of
+    // few words) go to the node-sliced kernel, the rest to pod-sliced warps.
+    // Measured at 100k nodes: ~9 us per node-sliced word; a whole pod-sliced chain (sort, classify, scouts,
+    // main) ~200 us, one more warp in an existing chain ~50 us.  VGS_NODE_WORDS overrides both limits.
+    static int node_words_env = -2;
+    if (node_words_env == -2) {
+        const char *ev = getenv("VGS_NODE_WORDS");
+        node_words_env = ev ? atoi(ev) : -1;
+    }
+    const int W_all = tb.W, n_pods_all = tb.n_pods;
+    // a class of its own (< 32 words): chain ~ (155 + 44 n) us against ~6.2 n us per node-sliced word,
+    // n = nodes / 100k (measured at 100k and 400k nodes) -> break-even 7 + 25 / n words
+    int small_limit = 7 + (int)(2500000ll / (a.n_nodes > 0 ? a.n_nodes : 1));
+    if (small_limit > 24) small_limit = 24;
+    const int node_words_max = node_words_env >= 0 ? node_words_env : (W_all < 32 ? small_limit : 6);
+    int ns_words = W_all % 32;
+    if (ns_words > node_words_max) ns_words = 0;
+    const int W_main = W_all - ns_words;
+    tb.W = W_main;
+    tb.n_pods = n_pods_all < W_main * 32 ? n_pods_all : W_main * 32;
     int warps = (tb.W + 31) / 32;
     if (warps > 4) warps = 4;
+    if (warps < 1) warps = 1;
     const int T = warps * 32;
     const int gy = (tb.W + T - 1) / T;
     if (n_types < 1) n_types = 1;
@@ -1620,13 +1748,18 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
     tb.row_shift = tabsmem ? VGS_MAX_TYPES - n_types : 0;
 
     // K1p: table rows + candidate scores per device, distinct scores -> classes
-    if ((e = cudaMemsetAsync(tb.hset, 0, kSliceHash * sizeof(uint32_t), st)) != cudaSuccess) return e;
     const int nthreads = a.n_tiles * kWarp;
-    k1p_collect<NUMS><<<(nthreads + 127) / 128, 128, 0, st>>>(a.walk, a.n_tiles, tb, status);
-    k1p_sort<<<1, 1024, 0, st>>>(tb);
-    k1p_classify<NUMS><<<(nthreads + 127) / 128, 128, 0, st>>>(a.n_tiles, tb);
+    if (W_main > 0) {
+        if ((e = cudaMemsetAsync(tb.hset, 0, kSliceHash * sizeof(uint32_t), st)) != cudaSuccess) return e;
+        k1p_collect<NUMS><<<(nthreads + 127) / 128, 128, 0, st>>>(a.walk, a.n_tiles, tb, status, true);
+        k1p_sort<<<1, 1024, 0, st>>>(tb);
+        k1p_classify<NUMS><<<(nthreads + 127) / 128, 128, 0, st>>>(a.n_tiles, tb);
+        *n_launched += 3;
+    } else { // a class of a few words: the node-sliced kernel needs the records only
+        k1p_collect<NUMS><<<(nthreads + 127) / 128, 128, 0, st>>>(a.walk, a.n_tiles, tb, status, false);
+        *n_launched += 1;
+    }
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
-    *n_launched += 3;
 
     // every scout-th tile is walked by the scout launch: about a hundred scout tiles (measured
     // optimum on 100k nodes: stride 24-48), VGS_SCOUT overrides
@@ -1638,6 +1771,12 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
     int scout = scout_env >= 2 ? scout_env : a.n_tiles / 96;
     if (scout < 4) scout = 4;
     if (scout > 32 && scout_env < 2) scout = 32;
+    static int scout_sub_max = -1;
+    if (scout_sub_max < 0) {
+        const char *ev = getenv("VGS_SCOUT_SUB");
+        scout_sub_max = ev ? atoi(ev) : 2; // cfg3: 1 -> 0.459 ms, 2 -> 0.449, 4 -> 0.472, 8 -> 0.477 (set-up per CTA)
+        if (scout_sub_max != 1 && scout_sub_max != 2 && scout_sub_max != 4 && scout_sub_max != 8) scout_sub_max = 2;
+    }
     const int smem = slice_smem(T, NUMS, tabsmem ? rows_s : 0).total;
     auto go = [&](auto kernel) -> cudaError_t {
         if ((e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)) != cudaSuccess) return e;
@@ -1654,9 +1793,13 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
             if (tiles_per < min_tiles) tiles_per = min_tiles;
             const int cap = ((1 << kSliceCountPlanes) - 1) / kWarp;
             if (tiles_per > cap) tiles_per = cap;
-            const int gx = (n_virtual + tiles_per - 1) / tiles_per;
+            int gx = (n_virtual + tiles_per - 1) / tiles_per;
+            int sub = 1; // scouts: split each tile over a few CTAs while the launch is under one wave
+            if (phase == 0)
+                while (sub < scout_sub_max && (long long)gx * sub * 2 <= want) sub *= 2;
+            gx *= sub;
             kernel<<<dim3(gx, gy), T, smem, st>>>(a.n_tiles, a.n_nodes, a.row_base, tb, n_types, tiles_per, phase,
-                                                  scout, a.keys, a.counts, a.vfit, a.vscore, a.vwords);
+                                                  scout, sub, a.keys, a.counts, a.vfit, a.vscore, a.vwords);
             *n_launched += 1;
             return cudaGetLastError();
         };
@@ -1665,8 +1808,37 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
         if ((e = launch(scouts, 0, 1)) != cudaSuccess) return e;
         return launch(a.n_tiles - scouts, 1, 2);
     };
-    if (a.vfit) return tabsmem ? go(k1_score_sliced<NUMS, true, true>) : go(k1_score_sliced<NUMS, false, true>);
-    return tabsmem ? go(k1_score_sliced<NUMS, true, false>) : go(k1_score_sliced<NUMS, false, false>);
+    if (W_main > 0) {
+        if (a.vfit) e = tabsmem ? go(k1_score_sliced<NUMS, true, true>) : go(k1_score_sliced<NUMS, false, true>);
+        else e = tabsmem ? go(k1_score_sliced<NUMS, true, false>) : go(k1_score_sliced<NUMS, false, false>);
+        if (e != cudaSuccess) return e;
+    }
+    if (ns_words > 0) { // needs K1p's records (row numbering included), not its score classes
+        SliceTab tn = tb;
+        tn.W = W_all;
+        tn.n_pods = n_pods_all;
+        const int rows_all = VGS_MAX_TYPES - tn.row_shift + (tn.km + 1) + (tn.kp + 1) + 4 * (tn.kc + 1);
+        const int nsmem = rows_all * 4;
+        auto gon = [&](auto kernel) -> cudaError_t {
+            if (nsmem > 48 * 1024 &&
+                (e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, nsmem)) != cudaSuccess)
+                return e;
+            int occ = 1;
+            if ((e = cached_occupancy(&occ, kernel, dev, 128, nsmem)) != cudaSuccess) return e;
+            if (occ < 1) occ = 1;
+            long long gx = ((long long)sms * occ + ns_words - 1) / ns_words; // one wave over all words
+            const long long need = (a.n_tiles + 3) / 4;
+            if (gx > need) gx = need;
+            if (gx < 1) gx = 1;
+            kernel<<<dim3((unsigned)gx, (unsigned)ns_words), 128, nsmem, st>>>(a.n_tiles, a.n_nodes, a.row_base, tn, W_main,
+                                                                             a.keys, a.counts, a.vfit, a.vscore, a.vwords);
+            *n_launched += 1;
+            return cudaGetLastError();
+        };
+        e = a.vfit ? gon(k1_score_nodesliced<NUMS, true>) : gon(k1_score_nodesliced<NUMS, false>);
+        if (e != cudaSuccess) return e;
+    }
+    return cudaSuccess;
 }
 
 cudaError_t launch_score_sliced(int nums, int dev, const ScoreArgs &a, const SliceTab &tb, int n_types,

@@ -275,6 +275,33 @@ def test_sliced_default_threshold(built):
         assert_same(gpu_score(snap, batch), oracle.score_packed(snap, batch, full=True), f"sliced {cfg}")
 
 
+@pytest.mark.parametrize("node_words", ["10", "0", "31"])
+def test_sliced_word_split_between_kernels(built, monkeypatch, node_words):
+    """a class's pod words beyond a multiple of 32 go to the node-sliced kernel (lane = node), the rest to
+    pod-sliced warps (lane = pod word); VGS_NODE_WORDS moves the split.  Same answers wherever a word runs."""
+    monkeypatch.setenv("VGS_NODE_WORDS", node_words)
+    monkeypatch.setenv("VGS_SLICE_MIN", "64")
+    rng = np.random.default_rng(77)
+    snap, _ = v.workload.make_config("cfg3", 9000, 1)
+    def pods_of(n1, n2):
+        out = []
+        for i in range(n1 + n2):
+            nums = 1 if i < n1 else 2
+            if rng.random() < 0.5:
+                mem, pct = int(rng.choice([1000, 4000, 16000, 30000])), 101
+            else:
+                mem, pct = 0, int(rng.choice([10, 25, 50, 100]))
+            an = {"nvidia.com/use-gputype": "a100,t4"} if rng.random() < 0.2 else {}
+            out.append({"containers": [[(nums, mem, pct, int(rng.choice([0, 10, 30, 100])))]], "annos": an})
+        return v.PodBatch.from_pods(out)
+    # (Nums 1 pods, Nums 2 pods): 33 + 3 words / 40 + 35 words, a few-word class next to a big one, exact multiples
+    for n1, n2 in ((1040, 70), (1270, 1100), (200, 2048), (1024, 1024 + 5)):
+        batch = pods_of(n1, n2)
+        want = oracle.score_packed(snap, batch, full=True)
+        assert_same(gpu_score(snap, batch), want, f"verify {n1}+{n2} words={node_words}")
+        assert_same(gpu_score(snap, batch, verify=False), oracle.score_packed(snap, batch), f"{n1}+{n2} words={node_words}")
+
+
 @pytest.mark.parametrize("k", K["kats"], ids=[k["name"] for k in K["kats"]])
 def test_sliced_forced_kats(built, monkeypatch, k):
     monkeypatch.setenv("VGS_SLICE_MIN", "1")
