@@ -6,6 +6,8 @@
 //   K1  k1_score_sliced   classes of >= 512 single-request pods asking for 1 or 2 devices:
 //                         32 pods per register, the CTA walks one node at a time, SliceDev tiles
 //                         staged with cp.async.bulk + mbarrier; scout launch + main launch
+//       k1_score_nodesliced  one pod word of such a class, lane = node: the words beyond a multiple
+//                         of 32 and classes of few words
 //       k1_score_single   per (pod, node) pair: thread = node (state in registers), loop over a
 //                         pod chunk staged in shared memory
 //       k1_score_general  any number of containers / requests, numa-bind
