@@ -978,11 +978,19 @@ __global__ void __launch_bounds__(128)
         s_best[b * T + tid] = 0u;
         s_row[b * T + tid] = kNotMine;
     }
-    if (TABSMEM) {
+    if (TABSMEM) { // eight independent loads in flight per thread: the copy is latency-, not bandwidth-bound
         uint32_t *tw = reinterpret_cast<uint32_t *>(smem_raw + L.tab);
-        for (int r = 0; r < rows_g - drop; r++) {
-            const int rg = r < n_types ? r : r + drop;
-            tw[r * T + tid] = __ldg(&tb.base[(size_t)rg * tb.Wp + wc]);
+        const int rows_s = rows_g - drop;
+        for (int r0 = 0; r0 < rows_s; r0 += 8) {
+            uint32_t v[8];
+#pragma unroll
+            for (int u = 0; u < 8; u++) {
+                const int r = min(r0 + u, rows_s - 1);
+                v[u] = __ldg(&tb.base[(size_t)(r < n_types ? r : r + drop) * tb.Wp + wc]);
+            }
+#pragma unroll
+            for (int u = 0; u < 8; u++)
+                if (r0 + u < rows_s) tw[(r0 + u) * T + tid] = v[u];
         }
     }
     if (tid == 0) {
@@ -997,22 +1005,32 @@ __global__ void __launch_bounds__(128)
         // inherit the scouts' bests.  A holder above all my rows can only be beaten by a strictly
         // larger score; one below some of my rows also by an equal score, so its score is
         // inherited one ulp lower (a local tie on a lower row is harmless: keys only grow).
-        for (int b = 0; b < 32; b++) {
-            const int i = w * 32 + b;
+        for (int b0 = 0; b0 < 32; b0 += 8) { // two rounds of 8 independent loads, not 16 dependent ones
+            int op[8];
+            unsigned long long kk[8];
+#pragma unroll
+            for (int u = 0; u < 8; u++) {
+                const int i = w * 32 + b0 + u;
+                op[u] = (active && i < tb.n_pods) ? __ldg(&tb.orig[i]) : -1;
+            }
+#pragma unroll
+            for (int u = 0; u < 8; u++) kk[u] = op[u] >= 0 ? keys[op[u]] : 0ull;
+#pragma unroll
+            for (int u = 0; u < 8; u++) {
+            const int b = b0 + u;
+            const unsigned long long key = kk[u];
             uint32_t init = 0u;
-            if (active && i < tb.n_pods) {
-                const unsigned long long key = keys[__ldg(&tb.orig[i])];
-                if (key) {
-                    const uint32_t gs = (uint32_t)(key >> 32) ^ 0x80000000u; // positive scores
-                    const int grow = (int)(uint32_t)key - row_base;
-                    init = grow >= node_hi ? gs : gs - 1u;
-                }
+            if (key) {
+                const uint32_t gs = (uint32_t)(key >> 32) ^ 0x80000000u; // positive scores
+                const int grow = (int)(uint32_t)key - row_base;
+                init = grow >= node_hi ? gs : gs - 1u;
             }
             s_best[b * T + tid] = init;
             int c = 0; // classes with vals[k] <= init
             for (int step = 32; step > 0; step >>= 1)
                 if (c + step <= nv && vals[c + step - 1] <= init) c += step;
             if (c < nv) below[c * T + tid] |= 1u << b; // the pod is under every class from c upward
+            }
         }
         for (int k = 1; k < nv; k++) below[k * T + tid] |= below[(k - 1) * T + tid];
     }
