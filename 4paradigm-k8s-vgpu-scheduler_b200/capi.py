@@ -28,6 +28,7 @@ EXPORTS = (
     "vgs_abi_version", "vgs_strerror", "vgs_init", "vgs_destroy", "vgs_last_error",
     "vgs_snapshot_upload", "vgs_snapshot_set_device", "vgs_snapshot_refresh", "vgs_snapshot_delta", "vgs_snapshot_download",
     "vgs_snapshot_type_flags", "vgs_host_typemask_mlu", "vgs_host_type_flags", "vgs_host_decode_pod_devices",
+    "vgs_exchange_block", "vgs_resolve_local", "vgs_exchange_merge",
     "vgs_score_batch", "vgs_drain_batch", "vgs_pods_upload", "vgs_score_resident", "vgs_resolve_resident",
     "vgs_results_download", "vgs_sync", "vgs_keys_device", "vgs_keys_merge", "vgs_results_device",
     "vgs_verify_download", "vgs_last_timing", "vgs_host_typemask", "vgs_host_numa_bind",
@@ -104,6 +105,9 @@ def load_library() -> C.CDLL:
     lib.vgs_keys_device.argtypes = [vp, C.POINTER(vp), C.POINTER(vp)]
     lib.vgs_keys_merge.argtypes = [vp, vp, vp, i32, i32, i32]
     lib.vgs_results_device.argtypes = [vp, C.POINTER(vp), C.POINTER(vp)]
+    lib.vgs_exchange_block.argtypes = [vp, C.POINTER(vp), u64p]
+    lib.vgs_resolve_local.argtypes = [vp]
+    lib.vgs_exchange_merge.argtypes = [vp, vp, i32, C.c_uint64]
     lib.vgs_verify_download.argtypes = [vp, vp, vp]
     lib.vgs_last_timing.argtypes = [vp, C.POINTER(VgsTiming)]
     lib.vgs_score_batch_noalloc.argtypes = [i32, vp, i32, i32, i32, C.POINTER(vp), vp, i32, vp, i32, vp, vp, vp]
@@ -401,6 +405,18 @@ class Context:
         picks = np.zeros(self._n_picks, dtype=PICK_DTYPE)
         self._check(self.lib.vgs_results_download(self.h, results.ctypes.data, picks.ctypes.data))
         return results, picks
+
+    def exchange_block(self) -> Tuple[int, int]:
+        """(device address, bytes) of the [keys | counts | picks] block a shard ships in one collective"""
+        ptr, n = C.c_void_p(), C.c_uint64()
+        self._check(self.lib.vgs_exchange_block(self.h, C.byref(ptr), C.byref(n)))
+        return int(ptr.value), int(n.value)
+
+    def resolve_local(self):
+        self._check(self.lib.vgs_resolve_local(self.h))
+
+    def exchange_merge(self, gathered_ptr: int, n_shards: int, stride_bytes: int):
+        self._check(self.lib.vgs_exchange_merge(self.h, C.c_void_p(gathered_ptr), n_shards, stride_bytes))
 
     def sync(self):
         self._check(self.lib.vgs_sync(self.h))

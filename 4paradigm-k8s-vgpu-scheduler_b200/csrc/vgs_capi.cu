@@ -87,6 +87,7 @@ struct vgs_ctx {
     bool zero_copy_ok = true;             // VGS_ZERO_COPY=0 disables the kernel-driven upload
     bool have_pods = false, scored = false, resolved = false;
     bool direct_out = false; // K3 of the current batch wrote h_results / h_picks itself
+    size_t picks_off = 0, xblock_bytes = 0; // exchange block = [keys | counts | pad | picks], one allocation
     int32_t dirty_pods = 0; // leading slots of d_keys / d_counts that may be non-zero (K3 clears behind itself)
 
     // results
@@ -187,7 +188,6 @@ void free_all(vgs_ctx *c) {
     cudaFree(c->d_keys);
     cudaFree(c->d_results);
     cudaFreeHost(c->h_results);
-    cudaFree(c->d_picks);
     cudaFreeHost(c->h_picks);
     cudaFree(c->d_vfit);
     cudaFree(c->d_vscore);
@@ -306,13 +306,17 @@ int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
     }
     // keys and counts are one allocation ("candidate block": max_pods u64 keys, then max_pods
     // int32 counts) so that shards can exchange both with a single all-gather
-    CUI(cudaMalloc(&c->d_keys, P * (sizeof(unsigned long long) + sizeof(int32_t)) + 8));
+    // ... and the picks follow in the same allocation ("exchange block"), so that a shard can also ship
+    // the picks of its own best nodes in that one collective (vgs_exchange_block / vgs_exchange_merge)
+    c->picks_off = align_up(P * (sizeof(unsigned long long) + sizeof(int32_t)) + 8, 16);
+    c->xblock_bytes = align_up(c->picks_off + (size_t)cfg->max_picks * sizeof(vgs_pick), 16);
+    CUI(cudaMalloc(&c->d_keys, c->xblock_bytes));
     c->d_counts = reinterpret_cast<int32_t *>(c->d_keys + P);
-    CUI(cudaMemset(c->d_keys, 0, P * (sizeof(unsigned long long) + sizeof(int32_t)) + 8));
+    CUI(cudaMemset(c->d_keys, 0, c->xblock_bytes));
     c->dirty_pods = 0;
     CUI(cudaMalloc(&c->d_results, P * sizeof(vgs_result)));
     CUI(cudaMallocHost(&c->h_results, P * sizeof(vgs_result)));
-    CUI(cudaMalloc(&c->d_picks, (size_t)cfg->max_picks * sizeof(vgs_pick)));
+    c->d_picks = reinterpret_cast<vgs_pick *>(reinterpret_cast<unsigned char *>(c->d_keys) + c->picks_off);
     CUI(cudaMallocHost(&c->h_picks, (size_t)cfg->max_picks * sizeof(vgs_pick)));
     if (cfg->verify) {
         c->vwords = (int32_t)max_tiles;
@@ -908,6 +912,47 @@ int vgs_results_device(vgs_ctx *c, vgs_result **dev_results, vgs_pick **dev_pick
     if (!c) return VGS_EINVAL;
     if (dev_results) *dev_results = c->d_results;
     if (dev_picks) *dev_picks = c->d_picks;
+    return VGS_OK;
+}
+
+int vgs_exchange_block(vgs_ctx *c, void **dev_block, uint64_t *bytes) {
+    if (!c) return VGS_EINVAL;
+    if (dev_block) *dev_block = c->d_keys;
+    if (bytes) *bytes = (uint64_t)c->xblock_bytes;
+    return VGS_OK;
+}
+
+int vgs_resolve_local(vgs_ctx *c) {
+    if (!c) return VGS_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard g(c->cfg.device);
+    if (!c->scored) return fail(c, VGS_ESTATE, "resolve before score");
+    rec(c, EV_RS0);
+    c->direct_out = false;
+    CU(launch_resolve(raw_const(c), c->n_nodes, c->dmax, c->cfg.row_base,
+                      reinterpret_cast<const vgs_pod *>(c->d_stage + c->off_pods),
+                      reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqs),
+                      reinterpret_cast<const int32_t *>(c->d_stage + c->off_pick), c->n_pods, c->d_keys,
+                      c->d_counts, c->d_results, c->d_picks, c->d_status, c->st, nullptr, nullptr, nullptr, true));
+    if (c->n_pods) c->launches++;
+    rec(c, EV_RS1);
+    return VGS_OK; // not "resolved" yet: the results are this shard's own until vgs_exchange_merge
+}
+
+int vgs_exchange_merge(vgs_ctx *c, const void *gathered, int32_t n_shards, uint64_t stride_bytes) {
+    if (!c || !gathered || n_shards < 1) return VGS_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard g(c->cfg.device);
+    if (!c->scored) return fail(c, VGS_ESTATE, "merge before score");
+    if (stride_bytes < c->xblock_bytes) return fail(c, VGS_EINVAL, "stride smaller than the exchange block");
+    CU(launch_exchange_merge(gathered, n_shards, (size_t)stride_bytes, c->cfg.max_pods, c->picks_off,
+                             reinterpret_cast<const vgs_pod *>(c->d_stage + c->off_pods),
+                             reinterpret_cast<const int32_t *>(c->d_stage + c->off_pick), c->n_pods, c->d_keys,
+                             c->d_counts, c->d_results, c->d_picks, c->st));
+    if (c->n_pods) c->launches++;
+    c->dirty_pods = 0;
+    c->direct_out = false;
+    c->resolved = true;
     return VGS_OK;
 }
 

@@ -1348,7 +1348,7 @@ __global__ void __launch_bounds__(64)
                unsigned long long *__restrict__ keys, int32_t *__restrict__ counts,
                vgs_result *__restrict__ results, vgs_pick *__restrict__ picks,
                uint32_t *__restrict__ status, int32_t *__restrict__ commit_rowlist,
-               vgs_result *__restrict__ host_results, vgs_pick *__restrict__ host_picks) {
+               vgs_result *__restrict__ host_results, vgs_pick *__restrict__ host_picks, bool keep_candidates) {
     // host_results / host_picks != nullptr (small batches): the records are ALSO stored straight into
     // the caller-facing pinned host buffers (posted PCIe writes), which spares the two D2H copies
     // commit_rowlist != nullptr (sequential drain, one pod per launch): the winner's picks are
@@ -1361,8 +1361,10 @@ __global__ void __launch_bounds__(64)
     vgs_result res;
     res.fit_count = counts[p];
     // K3 is the last reader of the candidate block: leave it zero for the next score pass
-    keys[p] = 0ull;
-    counts[p] = 0;
+    if (!keep_candidates) { // (kept for the shard exchange: k2x_merge clears them)
+        keys[p] = 0ull;
+        counts[p] = 0;
+    }
     const vgs_pod pod = pods[p];
     const int32_t pick_lo = pick_begin[pod.req_begin], pick_hi = pick_begin[pod.req_begin + pod.n_reqs];
     // picks of a pod without a winner on this shard are all zero
@@ -1869,6 +1871,60 @@ cudaError_t launch_score_sliced(int nums, int dev, const ScoreArgs &a, const Sli
                      : launch_sliced_t<2>(dev, a, tb, n_types, status, st, n_launched);
 }
 
+// K2x: merge of whole exchange blocks.  Every shard has resolved its OWN best node per pod (K3 with
+// keep_candidates) and the shards' blocks [keys | counts | picks] have been all-gathered; thread = pod
+// picks the winning shard (max key = max score, then highest global row), sums the fit counts, writes the
+// result record and copies the winner's picks.  One collective per pass instead of two.
+__global__ void k2x_merge(const unsigned char *__restrict__ gathered, int32_t n_shards, size_t stride_bytes,
+                          int32_t max_pods, size_t picks_off, const vgs_pod *__restrict__ pods,
+                          const int32_t *__restrict__ pick_begin, int32_t n_pods,
+                          unsigned long long *__restrict__ keys, int32_t *__restrict__ counts,
+                          vgs_result *__restrict__ results, vgs_pick *__restrict__ picks) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n_pods) return;
+    unsigned long long best = 0ull;
+    int32_t total = 0, win = 0;
+    for (int g = 0; g < n_shards; g++) {
+        const unsigned char *blk = gathered + (size_t)g * stride_bytes;
+        const unsigned long long k = reinterpret_cast<const unsigned long long *>(blk)[p];
+        total += reinterpret_cast<const int32_t *>(blk + (size_t)max_pods * 8)[p];
+        if (k > best) {
+            best = k;
+            win = g;
+        }
+    }
+    keys[p] = 0ull; // the local block goes back to its resting state
+    counts[p] = 0;
+    const vgs_pod pod = pods[p];
+    const int32_t lo = pick_begin[pod.req_begin], hi = pick_begin[pod.req_begin + pod.n_reqs];
+    vgs_result res;
+    res.fit_count = total;
+    if (best == 0ull) {
+        res.best_row = -1;
+        res.score = 0.0f;
+        res.n_picks = 0;
+    } else {
+        res.best_row = (int32_t)(uint32_t)best;
+        res.score = __uint_as_float(unorder_bits((uint32_t)(best >> 32)));
+        res.n_picks = hi - lo;
+    }
+    results[p] = res;
+    // the winner's picks (all zero when nobody fits: every shard zero-filled its own)
+    const vgs_pick *src = reinterpret_cast<const vgs_pick *>(gathered + (size_t)win * stride_bytes + picks_off);
+    for (int32_t i = lo; i < hi; i++) picks[i] = src[i];
+}
+
+cudaError_t launch_exchange_merge(const void *gathered, int32_t n_shards, size_t stride_bytes, int32_t max_pods,
+                                  size_t picks_off, const vgs_pod *pods, const int32_t *pick_begin, int32_t n_pods,
+                                  unsigned long long *keys, int32_t *counts, vgs_result *results, vgs_pick *picks,
+                                  cudaStream_t st) {
+    if (n_pods <= 0) return cudaSuccess;
+    k2x_merge<<<(n_pods + 127) / 128, 128, 0, st>>>(reinterpret_cast<const unsigned char *>(gathered), n_shards,
+                                                   stride_bytes, max_pods, picks_off, pods, pick_begin, n_pods, keys,
+                                                   counts, results, picks);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_merge(const unsigned long long *gk, const int32_t *gc, int32_t n_shards, int32_t stride,
                          int32_t cstride, int32_t n_pods, unsigned long long *keys, int32_t *counts,
                          cudaStream_t st) {
@@ -1881,11 +1937,12 @@ cudaError_t launch_resolve(const RawPlanes &raw, int32_t n_nodes, int32_t dmax, 
                            const vgs_pod *pods, const DevReq *reqs, const int32_t *pick_begin,
                            int32_t n_pods, unsigned long long *keys, int32_t *counts,
                            vgs_result *results, vgs_pick *picks, uint32_t *status, cudaStream_t st,
-                           int32_t *commit_rowlist, vgs_result *host_results, vgs_pick *host_picks) {
+                           int32_t *commit_rowlist, vgs_result *host_results, vgs_pick *host_picks,
+                           bool keep_candidates) {
     if (n_pods <= 0) return cudaSuccess;
     k3_resolve<<<(n_pods + 63) / 64, 64, 0, st>>>(raw, n_nodes, dmax, row_base, pods, reqs, pick_begin,
                                                  n_pods, keys, counts, results, picks, status, commit_rowlist,
-                                                 host_results, host_picks);
+                                                 host_results, host_picks, keep_candidates);
     return cudaGetLastError();
 }
 

@@ -106,15 +106,14 @@ class ShardedScorer:
                            max_reqs=max_reqs, max_picks=max_picks, device=device, row_base=self.lo, stream=stream)
         self.max_pods = max_pods
         self.max_picks = self.ctx.cfg.max_picks
-        kp, cp = self.ctx.keys_device()
-        rp, pp = self.ctx.results_device()
-        assert cp == kp + 8 * max_pods  # candidate block: keys then counts, one allocation
-        # the block as int32 words (3 per pod): one all-gather moves keys and counts together
-        self.block_words = 3 * max_pods
-        self.block = device_view(kp, self.block_words, torch.int32, self.device)
-        self.picks = device_view(pp, self.max_picks * 3, torch.int32, self.device)
+        # exchange block = [keys | counts | picks] in one allocation: ONE all-gather per pass moves every
+        # shard's candidates together with the picks of its own best nodes
+        bp, nbytes = self.ctx.exchange_block()
+        assert nbytes % 4 == 0
+        self.block_bytes = nbytes
+        self.block = device_view(bp, nbytes // 4, torch.int32, self.device)
         if world > 1:
-            self.gathered = torch.empty((world, self.block_words), dtype=torch.int32, device=self.device)
+            self.gathered = torch.empty((world, nbytes // 4), dtype=torch.int32, device=self.device)
 
     def upload(self, snap_shard):
         assert snap_shard.n_nodes == self.hi - self.lo
@@ -127,17 +126,14 @@ class ShardedScorer:
 
         with torch.cuda.stream(self.stream):
             self.ctx.score_resident()
-            if self.world > 1:
-                dist.all_gather_into_tensor(self.gathered, self.block, group=self.group)
-                base = self.gathered.data_ptr()
-                # shard g: keys at base + g*12P bytes (stride 1.5 P uint64), counts 8P bytes further
-                assert self.max_pods % 2 == 0
-                self.ctx.keys_merge(base, base + 8 * self.max_pods, self.world, self.block_words // 2,
-                                    self.block_words)
-            self.ctx.resolve_resident()
-            if self.world > 1 and n_picks:
-                # picks are written by the owner of each winner row only (zero elsewhere)
-                dist.all_reduce(self.picks[: n_picks * 3], group=self.group)
+            if self.world == 1:
+                self.ctx.resolve_resident()
+                return
+            # every shard resolves its own best node per pod, the blocks travel once, and the merge keeps
+            # the winning shard's result and picks (vgs_exchange_merge)
+            self.ctx.resolve_local()
+            dist.all_gather_into_tensor(self.gathered, self.block, group=self.group)
+            self.ctx.exchange_merge(self.gathered.data_ptr(), self.world, self.block_bytes)
 
     def score(self, pods: np.ndarray, reqs: np.ndarray):
         self.ctx.pods_upload(pods, reqs)

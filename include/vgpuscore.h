@@ -224,6 +224,15 @@ int vgs_keys_device(vgs_ctx *ctx, uint64_t **dev_keys, int32_t **dev_counts);
 int vgs_keys_merge(vgs_ctx *ctx, const uint64_t *dev_gathered_keys,
                    const int32_t *dev_gathered_counts, int32_t n_shards, int32_t key_stride,
                    int32_t count_stride);
+/* The same exchange in ONE collective.  The candidate block is followed, in the same allocation, by
+ * the picks array ("exchange block": max_pods keys, max_pods counts, padding, max_picks picks).  Each
+ * shard resolves its OWN best node per pod (vgs_resolve_local, which keeps the candidates), the blocks
+ * are all-gathered once, and vgs_exchange_merge picks the winning shard per pod out of the gathered
+ * blocks (shard g at dev_gathered + g * stride_bytes), sums the counts, writes results and copies the
+ * winner's picks -- after which vgs_results_download returns the global answer on every shard. */
+int vgs_exchange_block(vgs_ctx *ctx, void **dev_block, uint64_t *bytes);
+int vgs_resolve_local(vgs_ctx *ctx);
+int vgs_exchange_merge(vgs_ctx *ctx, const void *dev_gathered, int32_t n_shards, uint64_t stride_bytes);
 /* device arrays behind vgs_results_download (shard combine of results/picks) */
 int vgs_results_device(vgs_ctx *ctx, vgs_result **dev_results, vgs_pick **dev_picks);
 

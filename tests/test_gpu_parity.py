@@ -442,6 +442,46 @@ def test_cambricon_drain_and_shards(built):
     assert np.array_equal(after, planes)
 
 
+@pytest.mark.parametrize("cfg,n,p", [("cfg4", 5000, 96), ("cfg3", 9000, 1500)])
+def test_shards_exchange_in_one_collective(built, cfg, n, p):
+    """vgs_resolve_local + one gather of the [keys | counts | picks] blocks + vgs_exchange_merge: every
+    shard ends up with the single-context answer (winner, score bits, summed counts, the winner's picks)"""
+    import torch
+    snap, batch = v.workload.make_config(cfg, n, p)
+    single = gpu_score(snap, batch, verify=False)
+    pods, reqs = v.capi.pack_batch(batch, snap.type_names)
+    G, P = 3, batch.n_pods
+    n_picks = int(reqs["nums"].sum())
+    dev = torch.device("cuda", 0)
+    ctxs, blocks = [], []
+    for g in range(G):
+        lo, hi = v.sharding.shard_range(snap.n_nodes, G, g)
+        c = v.Context(max_nodes=hi - lo, max_pods=P, max_reqs=len(reqs), max_picks=n_picks, row_base=lo)
+        c.upload(snap.rows(lo, hi))
+        ctxs.append(c)
+    for rep in range(2):  # twice: the merge must leave every block clean for the next pass
+        blocks = []
+        for c in ctxs:
+            c.pods_upload(pods, reqs)
+            c.score_resident()
+            c.resolve_local()
+            c.sync()
+            bp, nb = c.exchange_block()
+            blocks.append(v.sharding.device_view(bp, nb // 4, torch.int32, dev).clone())
+        gathered = torch.stack(blocks).contiguous()
+        torch.cuda.synchronize()
+        for c in ctxs:
+            c.exchange_merge(gathered.data_ptr(), G, gathered.stride(0) * 4)
+            r, pk = c.results_download()
+            assert np.array_equal(r["best_row"], single.best_row)
+            assert np.array_equal(r["score"].view(np.uint32), single.score.view(np.uint32))
+            assert np.array_equal(r["fit_count"], single.fit_count)
+            assert np.array_equal(r["n_picks"], single.n_picks)
+            assert np.array_equal(np.stack([pk["slot"], pk["usedmem"], pk["usedcores"]], axis=1), single.picks)
+    for c in ctxs:
+        c.close()
+
+
 def test_candidate_block_is_clean_between_passes(built):
     """K3 clears the candidate keys/counts it reads and writes every pick itself, so a pass needs no
     memset -- unless an earlier pass was scored and never resolved, possibly for MORE pods than the next one"""
