@@ -28,7 +28,7 @@ EXPORTS = (
     "vgs_abi_version", "vgs_strerror", "vgs_init", "vgs_destroy", "vgs_last_error",
     "vgs_snapshot_upload", "vgs_snapshot_set_device", "vgs_snapshot_refresh", "vgs_snapshot_delta", "vgs_snapshot_download",
     "vgs_snapshot_type_flags", "vgs_host_typemask_mlu", "vgs_host_type_flags", "vgs_host_decode_pod_devices",
-    "vgs_exchange_block", "vgs_resolve_local", "vgs_exchange_merge",
+    "vgs_exchange_block", "vgs_resolve_local", "vgs_exchange_merge", "vgs_snapshot_upload_async",
     "vgs_score_batch", "vgs_drain_batch", "vgs_pods_upload", "vgs_score_resident", "vgs_resolve_resident",
     "vgs_results_download", "vgs_sync", "vgs_keys_device", "vgs_keys_merge", "vgs_results_device",
     "vgs_verify_download", "vgs_last_timing", "vgs_host_typemask", "vgs_host_numa_bind",
@@ -86,6 +86,7 @@ def load_library() -> C.CDLL:
     lib.vgs_last_error.restype = C.c_char_p
     lib.vgs_snapshot_upload.argtypes = [vp, i32, i32, C.POINTER(vp), vp, u64p]
     lib.vgs_snapshot_set_device.argtypes = [vp, i32, i32, C.POINTER(vp), vp, u64p]
+    lib.vgs_snapshot_upload_async.argtypes = [vp, i32, i32, C.POINTER(vp), vp, u64p]
     lib.vgs_snapshot_refresh.argtypes = [vp]
     lib.vgs_snapshot_type_flags.argtypes = [vp, i32, vp]
     lib.vgs_host_typemask_mlu.argtypes = [i32, C.c_char_p, C.c_char_p, C.POINTER(C.c_char_p), i32,
@@ -321,11 +322,14 @@ class Context:
         self.n_nodes, self.dmax, self.type_names = snap.n_nodes, snap.dmax, snap.type_names
         return ver.value
 
-    def upload_ptrs(self, n_nodes: int, dmax: int, plane_ptrs: List[int], ndev_ptr: int, device: bool) -> int:
-        """planes given as raw addresses (pinned host memory or this GPU's memory)"""
+    def upload_ptrs(self, n_nodes: int, dmax: int, plane_ptrs: List[int], ndev_ptr: int, device: bool,
+                    asynchronous: bool = False) -> int:
+        """planes given as raw addresses (pinned host memory or this GPU's memory); asynchronous: queue the
+        upload and return (vgs_snapshot_upload_async) -- the planes must stay put until the next call"""
         ptrs = (C.c_void_p * 8)(*plane_ptrs)
         ver = C.c_uint64()
-        fn = self.lib.vgs_snapshot_set_device if device else self.lib.vgs_snapshot_upload
+        fn = self.lib.vgs_snapshot_set_device if device else (
+            self.lib.vgs_snapshot_upload_async if asynchronous else self.lib.vgs_snapshot_upload)
         self._check(fn(self.h, n_nodes, dmax, ptrs, C.c_void_p(ndev_ptr), C.byref(ver)))
         self.n_nodes, self.dmax = n_nodes, dmax
         return ver.value

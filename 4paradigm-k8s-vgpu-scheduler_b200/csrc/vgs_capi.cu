@@ -59,6 +59,9 @@ struct vgs_ctx {
     uint32_t *h_status = nullptr; // pinned
     int32_t n_nodes = 0, dmax = 0, n_tiles = 0;
     bool have_snapshot = false;
+    bool snap_pending = false;    // vgs_snapshot_upload_async: copy + K0 queued, status not looked at yet
+    cudaEvent_t ev_snap = nullptr;
+    bool stage_in_flight = false; // the pinned staging block may still be the source of a queued copy
     uint64_t version = 0;
     uint64_t idle_types = 0; // vgs_snapshot_type_flags: types carrying VGS_TYPE_IDLE_SHARE
     vgs_delta *d_deltas = nullptr, *h_deltas = nullptr;
@@ -152,13 +155,31 @@ int check_status(vgs_ctx *c) {
     return VGS_OK;
 }
 
-int pull_status(vgs_ctx *c) {
-    CU(cudaMemcpyAsync(c->h_status, c->d_status, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->st));
-    CU(cudaStreamSynchronize(c->st));
+// h_status holds the two status words of the resident snapshot: errors, and what the score path may assume
+int apply_status(vgs_ctx *c) {
     int rc = check_status(c);
     c->snap_slice_ok = rc == VGS_OK && !(*c->h_status & S_BIGMEM) && c->dm == 8;
     c->n_types_used = (int32_t)c->h_status[1] + 1;
     if (rc != VGS_OK) cudaMemsetAsync(c->d_status, 0, sizeof(uint32_t), c->st);
+    return rc;
+}
+
+// an asynchronous upload is completed by the first call that needs the snapshot
+int finish_snapshot(vgs_ctx *c) {
+    if (!c->snap_pending) return VGS_OK;
+    c->snap_pending = false;
+    CU(cudaEventSynchronize(c->ev_snap));
+    int rc = apply_status(c);
+    if (rc != VGS_OK) return rc;
+    c->have_snapshot = true;
+    return VGS_OK;
+}
+
+int pull_status(vgs_ctx *c) {
+    CU(cudaMemcpyAsync(c->h_status, c->d_status, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->st));
+    CU(cudaStreamSynchronize(c->st));
+    c->stage_in_flight = false;
+    int rc = apply_status(c);
     return rc;
 }
 
@@ -173,6 +194,7 @@ void free_all(vgs_ctx *c) {
     for (int f = 0; f < VGS_NUM_PLANES; f++) cudaFree(c->d_raw[f]);
     cudaFree(c->d_ndev);
     cudaFree(c->d_walk);
+    if (c->ev_snap) cudaEventDestroy(c->ev_snap);
     cudaFree(c->d_status);
     cudaFreeHost(c->h_status);
     cudaFree(c->d_deltas);
@@ -257,6 +279,7 @@ int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
     }
     for (int i = 0; i < EV_N; i++) CUI(cudaEventCreate(&c->ev[i]));
     CUI(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+    CUI(cudaEventCreateWithFlags(&c->ev_snap, cudaEventDisableTiming));
     for (int k = 0; k < 2; k++) {
         CUI(cudaStreamCreateWithFlags(&c->side[k], cudaStreamNonBlocking));
         CUI(cudaEventCreateWithFlags(&c->ev_join[k], cudaEventDisableTiming));
@@ -340,7 +363,7 @@ void vgs_destroy(vgs_ctx *c) {
 
 static int snapshot_common(vgs_ctx *c, int32_t n_nodes, int32_t dmax,
                            const int32_t *const planes[VGS_NUM_PLANES], const int32_t *ndev,
-                           cudaMemcpyKind kind, uint64_t *out_version) {
+                           cudaMemcpyKind kind, uint64_t *out_version, bool async = false) {
     if (!planes || !ndev) return fail(c, VGS_EINVAL, "null planes");
     if (n_nodes < 0 || dmax < 1) return fail(c, VGS_EINVAL, "bad snapshot shape");
     if (dmax > VGS_MAX_DEVICES) return fail(c, VGS_EDMAX, "dmax > VGS_MAX_DEVICES");
@@ -348,6 +371,10 @@ static int snapshot_common(vgs_ctx *c, int32_t n_nodes, int32_t dmax,
         return fail(c, VGS_ETOOBIG, "snapshot larger than vgs_init capacity");
     for (int f = 0; f < VGS_NUM_PLANES; f++)
         if (!planes[f]) return fail(c, VGS_EINVAL, "null plane");
+    if (c->snap_pending) { // superseded before anybody looked at it
+        c->snap_pending = false;
+        CU(cudaEventSynchronize(c->ev_snap));
+    }
     c->have_snapshot = false;
     c->scored = c->resolved = false;
     const size_t cells = (size_t)n_nodes * dmax;
@@ -380,6 +407,14 @@ static int snapshot_common(vgs_ctx *c, int32_t n_nodes, int32_t dmax,
     int rc = prepare_all(c);
     if (rc != VGS_OK) return rc;
     rec(c, EV_DR1);
+    if (async) { // the status words come back behind K0; finish_snapshot looks at them
+        CU(cudaMemcpyAsync(c->h_status, c->d_status, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->st));
+        CU(cudaEventRecord(c->ev_snap, c->st));
+        c->snap_pending = true;
+        c->version++;
+        if (out_version) *out_version = c->version;
+        return VGS_OK;
+    }
     rc = pull_status(c);
     if (rc != VGS_OK) return rc;
     c->have_snapshot = true;
@@ -397,6 +432,15 @@ int vgs_snapshot_upload(vgs_ctx *c, int32_t n_nodes, int32_t dmax,
     return snapshot_common(c, n_nodes, dmax, planes, ndev, cudaMemcpyHostToDevice, out_version);
 }
 
+int vgs_snapshot_upload_async(vgs_ctx *c, int32_t n_nodes, int32_t dmax,
+                              const int32_t *const planes[VGS_NUM_PLANES], const int32_t *ndev,
+                              uint64_t *out_version) {
+    if (!c) return VGS_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard g(c->cfg.device);
+    return snapshot_common(c, n_nodes, dmax, planes, ndev, cudaMemcpyHostToDevice, out_version, true);
+}
+
 int vgs_snapshot_set_device(vgs_ctx *c, int32_t n_nodes, int32_t dmax,
                             const int32_t *const dev_planes[VGS_NUM_PLANES], const int32_t *dev_ndev,
                             uint64_t *out_version) {
@@ -412,6 +456,10 @@ int vgs_snapshot_type_flags(vgs_ctx *c, int32_t n_types, const uint32_t *flags) 
     DeviceGuard g(c->cfg.device);
     if (n_types < 0 || n_types > VGS_MAX_TYPES || (n_types > 0 && !flags))
         return fail(c, VGS_EINVAL, "type flags: n_types outside [0, VGS_MAX_TYPES]");
+    {
+        int frc = finish_snapshot(c);
+        if (frc != VGS_OK) return frc;
+    }
     uint64_t m = 0;
     for (int32_t t = 0; t < n_types; t++)
         if (flags[t] & VGS_TYPE_IDLE_SHARE) m |= 1ull << t;
@@ -426,6 +474,10 @@ int vgs_snapshot_refresh(vgs_ctx *c) {
     if (!c) return VGS_EINVAL;
     std::lock_guard<std::mutex> lk(c->mu);
     DeviceGuard g(c->cfg.device);
+    {
+        int frc = finish_snapshot(c);
+        if (frc != VGS_OK) return frc;
+    }
     if (!c->have_snapshot) return fail(c, VGS_ESTATE, "refresh before snapshot upload");
     rec(c, EV_UP1);
     int rc = prepare_all(c);
@@ -438,6 +490,10 @@ int vgs_snapshot_delta(vgs_ctx *c, int32_t n, const vgs_delta *deltas) {
     if (!c) return VGS_EINVAL;
     std::lock_guard<std::mutex> lk(c->mu);
     DeviceGuard g(c->cfg.device);
+    {
+        int frc = finish_snapshot(c);
+        if (frc != VGS_OK) return frc;
+    }
     if (!c->have_snapshot) return fail(c, VGS_ESTATE, "delta before snapshot upload");
     if (n < 0 || (n > 0 && !deltas)) return fail(c, VGS_EINVAL, "bad delta list");
     c->scored = c->resolved = false;
@@ -470,6 +526,10 @@ int vgs_snapshot_download(vgs_ctx *c, int32_t *const planes[VGS_NUM_PLANES], int
     if (!c || !planes || !ndev) return VGS_EINVAL;
     std::lock_guard<std::mutex> lk(c->mu);
     DeviceGuard g(c->cfg.device);
+    {
+        int frc = finish_snapshot(c);
+        if (frc != VGS_OK) return frc;
+    }
     if (!c->have_snapshot) return fail(c, VGS_ESTATE, "no snapshot");
     const size_t cells = (size_t)c->n_nodes * c->dmax;
     if (cells) {
@@ -579,7 +639,10 @@ static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, i
     c->have_pods = false;
     c->scored = c->resolved = false;
     // the staging block may still be the source of an earlier async copy
-    CU(cudaStreamSynchronize(c->st));
+    if (c->stage_in_flight) {
+        CU(cudaStreamSynchronize(c->st));
+        c->stage_in_flight = false;
+    }
     const size_t stage_used = stage_layout(c, (size_t)n_pods, (size_t)n_reqs);
     DevReq *hreq = reinterpret_cast<DevReq *>(c->h_stage + c->off_reqs);
     vgs_pod *hpod = reinterpret_cast<vgs_pod *>(c->h_stage + c->off_pods);
@@ -668,8 +731,17 @@ static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, i
     c->nC = nC;
     c->nG = nG;
     c->n_picks = (int32_t)picks;
+    // everything above was host work that overlaps an asynchronous snapshot upload; the class set-up
+    // below wants to know what the snapshot allows (sliced kernels, type rows)
+    {
+        int frc = finish_snapshot(c);
+        if (frc != VGS_OK) return frc;
+    }
     rec(c, EV_PH0);
-    if (stage_used) CU(cudaMemcpyAsync(c->d_stage, c->h_stage, stage_used, cudaMemcpyHostToDevice, c->st));
+    if (stage_used) {
+        CU(cudaMemcpyAsync(c->d_stage, c->h_stage, stage_used, cudaMemcpyHostToDevice, c->st));
+        c->stage_in_flight = true;
+    }
     {
         cudaError_t e;
         build_slice_class(c, 0, hA, reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqsA), hoA, nA, &e);
@@ -683,6 +755,10 @@ static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, i
 }
 
 static int score_locked(vgs_ctx *c) {
+    {
+        int frc = finish_snapshot(c);
+        if (frc != VGS_OK) return frc;
+    }
     if (!c->have_snapshot) return fail(c, VGS_ESTATE, "score before snapshot upload");
     if (!c->have_pods) return fail(c, VGS_ESTATE, "score before pod upload");
     const int32_t P = c->n_pods;
@@ -804,6 +880,7 @@ static int download_locked(vgs_ctx *c, vgs_result *results, vgs_pick *picks) {
     CU(cudaMemcpyAsync(c->h_status, c->d_status, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->st));
     rec(c, EV_DH1);
     CU(cudaStreamSynchronize(c->st));
+    c->stage_in_flight = false;
     int rc = check_status(c);
     if (rc != VGS_OK) {
         cudaMemsetAsync(c->d_status, 0, sizeof(uint32_t), c->st);
@@ -859,6 +936,10 @@ int vgs_drain_batch(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_r
     if (!c) return VGS_EINVAL;
     std::lock_guard<std::mutex> lk(c->mu);
     DeviceGuard g(c->cfg.device);
+    {
+        int frc = finish_snapshot(c);
+        if (frc != VGS_OK) return frc;
+    }
     if (!c->have_snapshot) return fail(c, VGS_ESTATE, "drain before snapshot upload");
     int rc;
     if ((rc = pods_upload_locked(c, n_pods, pods, n_reqs, reqs)) != VGS_OK) return rc;
@@ -898,7 +979,8 @@ int vgs_sync(vgs_ctx *c) {
     std::lock_guard<std::mutex> lk(c->mu);
     DeviceGuard g(c->cfg.device);
     CU(cudaStreamSynchronize(c->st));
-    return VGS_OK;
+    c->stage_in_flight = false;
+    return finish_snapshot(c);
 }
 
 int vgs_keys_device(vgs_ctx *c, uint64_t **dev_keys, int32_t **dev_counts) {

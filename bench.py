@@ -331,7 +331,8 @@ def main():
         d2h = results.nbytes + picks.nbytes
 
         def e2e_step():
-            ctx.upload_ptrs(npg, D, plane_ptrs, pin_ndev.data_ptr(), device=False)  # pinned H2D + K0
+            # pinned H2D + K0, queued: the request packing below overlaps the copy
+            ctx.upload_ptrs(npg, D, plane_ptrs, pin_ndev.data_ptr(), device=False, asynchronous=True)
             ctx.pods_upload(pods, reqs)
             sc.step_resident(n_picks)
             return ctx.results_download()
@@ -349,7 +350,7 @@ def main():
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         e2e = {"value": P * n_total / (float(dt.item()) / n_e2e), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * float(dt.item()) / n_e2e, "steps": n_e2e,
-               "api": "vgs_snapshot_upload + vgs_pods_upload/score/resolve/results_download (host buffers)"}
+               "api": "vgs_snapshot_upload_async + vgs_pods_upload/score/resolve/results_download (host buffers)"}
     clocks = sampler.stop()
 
     # ---- metric (ii): single-pod Filter latency through the C ABI, snapshot resident -------------

@@ -173,6 +173,14 @@ const char *vgs_last_error(vgs_ctx *ctx);
 int vgs_snapshot_upload(vgs_ctx *ctx, int32_t n_nodes, int32_t dmax,
                         const int32_t *const planes[VGS_NUM_PLANES], const int32_t *ndev,
                         uint64_t *out_version);
+/* Same, but returns as soon as the copy and the preparation are queued, so that the caller can go on
+ * building the pod batch while the planes cross PCIe.  The planes must stay untouched until the next
+ * call on this context that needs the snapshot (vgs_pods_upload from its table set-up on, vgs_score_*,
+ * vgs_snapshot_delta / _refresh / _download, vgs_sync): that call waits for the upload and returns its
+ * range errors (VGS_EDMAX / VGS_ERANGE) in place of its own result.  No counterpart in the reference. */
+int vgs_snapshot_upload_async(vgs_ctx *ctx, int32_t n_nodes, int32_t dmax,
+                              const int32_t *const planes[VGS_NUM_PLANES], const int32_t *ndev,
+                              uint64_t *out_version);
 /* same, from planes that already live in this GPU's memory */
 int vgs_snapshot_set_device(vgs_ctx *ctx, int32_t n_nodes, int32_t dmax,
                             const int32_t *const dev_planes[VGS_NUM_PLANES],

@@ -531,6 +531,47 @@ def test_pinned_planes_take_the_zero_copy_upload(built, monkeypatch):
         assert np.array_equal(planes, snap.planes)
 
 
+def test_async_snapshot_upload(built):
+    """vgs_snapshot_upload_async returns with the copy queued; the next call that needs the snapshot waits
+    for it and gets its range errors; results equal the blocking upload's, pass after pass"""
+    import torch
+    snap, batch = v.workload.make_config("cfg3", 6001, 700)
+    want = oracle.score_packed(snap, batch)
+    pods, reqs = v.capi.pack_batch(batch, snap.type_names)
+    pin = torch.from_numpy(snap.planes.copy()).pin_memory()
+    pnd = torch.from_numpy(snap.ndev.copy()).pin_memory()
+    ptrs = [pin[f].data_ptr() for f in range(8)]
+    with v.Context(max_nodes=6001, max_pods=700) as ctx:
+        ctx.type_names = snap.type_names
+        for _ in range(3):  # the bench's end-to-end step
+            ctx.upload_ptrs(snap.n_nodes, snap.dmax, ptrs, pnd.data_ptr(), device=False, asynchronous=True)
+            ctx.pods_upload(pods, reqs)
+            ctx.score_resident()
+            ctx.resolve_resident()
+            r, pk = ctx.results_download()
+            assert np.array_equal(r["best_row"], want.best_row) and np.array_equal(r["fit_count"], want.fit_count)
+            assert np.array_equal(np.stack([pk["slot"], pk["usedmem"], pk["usedcores"]], axis=1), want.picks)
+        # completed by other entry points too
+        ctx.upload_ptrs(snap.n_nodes, snap.dmax, ptrs, pnd.data_ptr(), device=False, asynchronous=True)
+        planes, ndev = ctx.download_snapshot()
+        assert np.array_equal(planes, snap.planes) and np.array_equal(ndev, snap.ndev)
+        ctx.upload_ptrs(snap.n_nodes, snap.dmax, ptrs, pnd.data_ptr(), device=False, asynchronous=True)
+        ctx.sync()
+        assert_same(ctx.score(batch), want, "after sync")
+        # a bad snapshot: the error belongs to the upload and comes out of the next call
+        pin[v.model.P_COUNT][5, 3] = 1 << 21
+        ctx.upload_ptrs(snap.n_nodes, snap.dmax, ptrs, pnd.data_ptr(), device=False, asynchronous=True)
+        with pytest.raises(v.VgsError) as e:
+            ctx.pods_upload(pods, reqs)
+        assert e.value.code == v.capi.VGS_ERANGE
+        with pytest.raises(v.VgsError) as e:
+            ctx.score_resident()  # still no snapshot
+        assert e.value.code == v.capi.VGS_ESTATE
+        pin[v.model.P_COUNT][5, 3] = int(snap.planes[v.model.P_COUNT][5, 3])
+        ctx.upload_ptrs(snap.n_nodes, snap.dmax, ptrs, pnd.data_ptr(), device=False, asynchronous=True)
+        assert_same(ctx.score(batch), want, "recovered")
+
+
 def test_refresh_and_phased_calls(built):
     """the phased entry points (pods_upload / score_resident / resolve_resident / results_download) and
     vgs_snapshot_refresh give the same answer as the one-shot vgs_score_batch"""
