@@ -447,7 +447,7 @@ def main():
         "e2e": e2e,
         "gpu_launches": int(launches),
         "clocks": clocks,
-        "roofline": {"bound": "hbm", "kernel": "K1 score kernels of one step (k1_score_sliced<1>, <2>, k1_score_single tails)",
+        "roofline": {"bound": "hbm", "kernel": "K1 phase of one step (K1p collect/sort/classify, k1_score_sliced<1>, <2> scouts + main, k1_score_nodesliced)",
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes": int(abytes),
                      "kernel_ms": k1_ms,
