@@ -108,6 +108,8 @@ struct vgs_ctx {
     cudaEvent_t ev_fork = nullptr, ev_join[2] = {};
     cudaEvent_t ev[EV_N] = {};
     bool ev_set[EV_N] = {};
+    int ev_alias[EV_N] = {};  // which recorded event stands for this boundary (see rec)
+    bool chained = false;     // inside vgs_score_batch: one phase's end IS the next one's start
     long long launches = 0;
 };
 
@@ -130,7 +132,14 @@ int fail(vgs_ctx *c, int code, const char *what) {
     } while (0)
 
 void rec(vgs_ctx *c, int which) {
+    // back-to-back phases of one call share their boundary event (nothing is queued in between)
+    if (c->chained && (which == EV_SC0 || which == EV_RS0 || which == EV_DH0) && c->ev_set[which - 1]) {
+        c->ev_alias[which] = c->ev_alias[which - 1];
+        c->ev_set[which] = true;
+        return;
+    }
     cudaEventRecord(c->ev[which], c->st);
+    c->ev_alias[which] = which;
     c->ev_set[which] = true;
 }
 
@@ -925,10 +934,12 @@ int vgs_score_batch(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_r
     std::lock_guard<std::mutex> lk(c->mu);
     DeviceGuard g(c->cfg.device);
     int rc;
-    if ((rc = pods_upload_locked(c, n_pods, pods, n_reqs, reqs)) != VGS_OK) return rc;
-    if ((rc = score_locked(c)) != VGS_OK) return rc;
-    if ((rc = resolve_locked(c)) != VGS_OK) return rc;
-    return download_locked(c, results, picks);
+    c->chained = true;
+    if ((rc = pods_upload_locked(c, n_pods, pods, n_reqs, reqs)) == VGS_OK && (rc = score_locked(c)) == VGS_OK &&
+        (rc = resolve_locked(c)) == VGS_OK)
+        rc = download_locked(c, results, picks);
+    c->chained = false;
+    return rc;
 }
 
 int vgs_drain_batch(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_reqs, const vgs_req *reqs,
@@ -1079,7 +1090,8 @@ int vgs_last_timing(vgs_ctx *c, vgs_timing *out) {
     memset(out, 0, sizeof *out);
     auto span = [&](int a, int b) -> float {
         float ms = 0.f;
-        if (c->ev_set[a] && c->ev_set[b] && cudaEventElapsedTime(&ms, c->ev[a], c->ev[b]) == cudaSuccess)
+        if (c->ev_set[a] && c->ev_set[b] &&
+            cudaEventElapsedTime(&ms, c->ev[c->ev_alias[a]], c->ev[c->ev_alias[b]]) == cudaSuccess)
             return ms;
         return 0.f;
     };
