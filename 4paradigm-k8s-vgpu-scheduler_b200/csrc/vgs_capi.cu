@@ -868,7 +868,8 @@ static int resolve_locked(vgs_ctx *c) {
                       reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqs),
                       reinterpret_cast<const int32_t *>(c->d_stage + c->off_pick), c->n_pods, c->d_keys,
                       c->d_counts, c->d_results, c->d_picks, c->d_status, c->st, nullptr,
-                      c->direct_out ? c->h_results : nullptr, c->direct_out ? c->h_picks : nullptr));
+                      c->direct_out ? c->h_results : nullptr, c->direct_out ? c->h_picks : nullptr, false,
+                      c->direct_out ? c->h_status : nullptr));
     if (c->n_pods) c->launches++;
     rec(c, EV_RS1);
     c->dirty_pods = 0;
@@ -886,7 +887,8 @@ static int download_locked(vgs_ctx *c, vgs_result *results, vgs_pick *picks) {
     if (c->n_picks && picks && !c->direct_out)
         CU(cudaMemcpyAsync(c->h_picks, c->d_picks, (size_t)c->n_picks * sizeof(vgs_pick),
                            cudaMemcpyDeviceToHost, c->st));
-    CU(cudaMemcpyAsync(c->h_status, c->d_status, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->st));
+    if (!(c->direct_out && c->n_pods > 0)) // (K3 of a Filter-sized batch forwarded the status word itself)
+        CU(cudaMemcpyAsync(c->h_status, c->d_status, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->st));
     rec(c, EV_DH1);
     CU(cudaStreamSynchronize(c->st));
     c->stage_in_flight = false;

@@ -1348,14 +1348,26 @@ __global__ void __launch_bounds__(64)
                unsigned long long *__restrict__ keys, int32_t *__restrict__ counts,
                vgs_result *__restrict__ results, vgs_pick *__restrict__ picks,
                uint32_t *__restrict__ status, int32_t *__restrict__ commit_rowlist,
-               vgs_result *__restrict__ host_results, vgs_pick *__restrict__ host_picks, bool keep_candidates) {
+               vgs_result *__restrict__ host_results, vgs_pick *__restrict__ host_picks, bool keep_candidates,
+               uint32_t *__restrict__ host_status) {
     // host_results / host_picks != nullptr (small batches): the records are ALSO stored straight into
     // the caller-facing pinned host buffers (posted PCIe writes), which spares the two D2H copies
     // commit_rowlist != nullptr (sequential drain, one pod per launch): the winner's picks are
     // also folded into the raw planes (addPod, scheduler.go:280-297,394) and the touched row is
     // named for re-preparation
+    // host_status != nullptr (single-CTA launches only): the last pod to finish also forwards the status
+    // word to the host mirror, so that the download of such a batch is a stream synchronisation and nothing else
+    __shared__ int s_left;
+    if (threadIdx.x == 0) s_left = min((int)blockDim.x, n_pods - (int)(blockIdx.x * blockDim.x));
+    __syncthreads();
     int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n_pods) return;
+    auto leave = [&]() {
+        if (host_status) {
+            __threadfence(); // my status bits (if any) are out before I count myself done
+            if (atomicSub(&s_left, 1) == 1) host_status[0] = *reinterpret_cast<volatile uint32_t *>(status);
+        }
+    };
     if (commit_rowlist) commit_rowlist[p] = -1;
     const unsigned long long key = keys[p];
     vgs_result res;
@@ -1383,6 +1395,7 @@ __global__ void __launch_bounds__(64)
         results[p] = res;
         if (host_results) host_results[p] = res;
         zero_picks();
+        leave();
         return;
     }
     const int32_t grow = (int32_t)(uint32_t)key;
@@ -1395,6 +1408,7 @@ __global__ void __launch_bounds__(64)
     const int32_t row = grow - row_base;
     if (row < 0 || row >= n_nodes) { // another shard owns the winner
         zero_picks();
+        leave();
         return;
     }
 
@@ -1506,6 +1520,7 @@ __global__ void __launch_bounds__(64)
     }
     if (alive && in_ctr) score = __fadd_rn(score, container_score(total, free_, nd - sums));
     if (!alive || __float_as_uint(score) != kbits) atomicOr(status, S_MISMATCH);
+    leave();
 }
 
 // ------------------------------------------------------------------------------------
@@ -1938,11 +1953,12 @@ cudaError_t launch_resolve(const RawPlanes &raw, int32_t n_nodes, int32_t dmax, 
                            int32_t n_pods, unsigned long long *keys, int32_t *counts,
                            vgs_result *results, vgs_pick *picks, uint32_t *status, cudaStream_t st,
                            int32_t *commit_rowlist, vgs_result *host_results, vgs_pick *host_picks,
-                           bool keep_candidates) {
+                           bool keep_candidates, uint32_t *host_status) {
     if (n_pods <= 0) return cudaSuccess;
+    if (n_pods > 64) host_status = nullptr; // one CTA only (see k3_resolve)
     k3_resolve<<<(n_pods + 63) / 64, 64, 0, st>>>(raw, n_nodes, dmax, row_base, pods, reqs, pick_begin,
                                                  n_pods, keys, counts, results, picks, status, commit_rowlist,
-                                                 host_results, host_picks, keep_candidates);
+                                                 host_results, host_picks, keep_candidates, host_status);
     return cudaGetLastError();
 }
 
