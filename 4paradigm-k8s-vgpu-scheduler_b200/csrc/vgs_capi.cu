@@ -968,15 +968,14 @@ int vgs_drain_batch(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_r
     const int32_t *dpick = reinterpret_cast<const int32_t *>(c->d_stage + c->off_pick);
     const GenPod *dall = reinterpret_cast<const GenPod *>(c->d_stage + c->off_genall);
     // one pod at a time, everything chained on the stream: score (the key/count slot of pod p is
-    // addressed through GenPod.orig) -> resolve + commit into the raw planes -> re-prepare the row
+    // addressed through GenPod.orig) -> resolve + commit into the raw planes + re-prepare the row (K3)
     for (int32_t p = 0; p < n_pods; p++) {
         CU(launch_score_general(c->dm, c->cfg.device, a, dreq, dall + p, 1, c->st));
         CU(launch_resolve(raw_const(c), c->n_nodes, c->dmax, c->cfg.row_base, dpod + p, dreq, dpick, 1,
                           c->d_keys + p, c->d_counts + p, c->d_results + p, c->d_picks, c->d_status, c->st,
-                          c->d_rowlist)); // resolve + commit into the raw planes
-        CU(launch_prepare(c->dm, raw_const(c), c->n_nodes, c->dmax, c->d_walk, c->n_tiles, c->d_status,
-                          c->d_rowlist, 1, c->st));
-        c->launches += c->n_tiles ? 3 : 2;
+                          c->d_rowlist, nullptr, nullptr, false, nullptr, c->d_walk,
+                          c->dm)); // resolve + commit into the raw planes + re-prepare the touched row
+        c->launches += c->n_tiles ? 2 : 1;
     }
     rec(c, EV_SC1);
     c->scored = true;

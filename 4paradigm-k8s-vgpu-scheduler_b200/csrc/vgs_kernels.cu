@@ -89,21 +89,10 @@ __device__ __forceinline__ void load_word(const int4 *__restrict__ tile, int wor
 // ------------------------------------------------------------------------------------
 // K0: prepare the walk-ordered copy.  One thread per node.
 // ------------------------------------------------------------------------------------
+// one node: raw planes -> its slot of the walk-ordered tile (also called by K3 when a drain commits a pod)
 template <int DM>
-__global__ void __launch_bounds__(128)
-    k0_prepare(RawPlanes raw, int32_t n_nodes, int32_t dmax, int4 *__restrict__ walk,
-               int32_t n_tiles, uint32_t *__restrict__ status, const int32_t *__restrict__ rowlist,
-               int32_t n_list) {
-    int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    int row;
-    if (rowlist) {
-        if (idx >= n_list) return;
-        row = rowlist[idx];
-        if (row < 0) return;
-    } else {
-        row = idx;
-    }
-    if (row >= n_tiles * kWarp) return;
+__device__ __forceinline__ void prepare_node(const RawPlanes &raw, int row, int32_t n_nodes, int32_t dmax,
+                                             int4 *__restrict__ walk, uint32_t *__restrict__ status) {
     const bool valid = row < n_nodes;
     int32_t nd = valid ? raw.ndev[row] : 0;
     uint32_t bad = 0;
@@ -196,6 +185,24 @@ __global__ void __launch_bounds__(128)
             put(W_SPARE, j, 0);
         }
     }
+}
+
+template <int DM>
+__global__ void __launch_bounds__(128)
+    k0_prepare(RawPlanes raw, int32_t n_nodes, int32_t dmax, int4 *__restrict__ walk,
+               int32_t n_tiles, uint32_t *__restrict__ status, const int32_t *__restrict__ rowlist,
+               int32_t n_list) {
+    int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    int row;
+    if (rowlist) {
+        if (idx >= n_list) return;
+        row = rowlist[idx];
+        if (row < 0) return;
+    } else {
+        row = idx;
+    }
+    if (row >= n_tiles * kWarp) return;
+    prepare_node<DM>(raw, row, n_nodes, dmax, walk, status);
 }
 
 // ------------------------------------------------------------------------------------
@@ -1349,7 +1356,7 @@ __global__ void __launch_bounds__(64)
                vgs_result *__restrict__ results, vgs_pick *__restrict__ picks,
                uint32_t *__restrict__ status, int32_t *__restrict__ commit_rowlist,
                vgs_result *__restrict__ host_results, vgs_pick *__restrict__ host_picks, bool keep_candidates,
-               uint32_t *__restrict__ host_status) {
+               uint32_t *__restrict__ host_status, int4 *__restrict__ commit_walk, int32_t commit_dm) {
     // host_results / host_picks != nullptr (small batches): the records are ALSO stored straight into
     // the caller-facing pinned host buffers (posted PCIe writes), which spares the two D2H copies
     // commit_rowlist != nullptr (sequential drain, one pod per launch): the winner's picks are
@@ -1517,6 +1524,10 @@ __global__ void __launch_bounds__(64)
             const_cast<int32_t *>(raw.p[VGS_PLANE_USEDCORES])[base + d] = usedcores[d];
         }
         commit_rowlist[p] = row;
+        if (commit_walk) { // re-prepare the touched row right here: the next pod's score kernel reads it
+            if (commit_dm == 8) prepare_node<8>(raw, row, n_nodes, dmax, commit_walk, status);
+            else prepare_node<12>(raw, row, n_nodes, dmax, commit_walk, status);
+        }
     }
     if (alive && in_ctr) score = __fadd_rn(score, container_score(total, free_, nd - sums));
     if (!alive || __float_as_uint(score) != kbits) atomicOr(status, S_MISMATCH);
@@ -1953,12 +1964,13 @@ cudaError_t launch_resolve(const RawPlanes &raw, int32_t n_nodes, int32_t dmax, 
                            int32_t n_pods, unsigned long long *keys, int32_t *counts,
                            vgs_result *results, vgs_pick *picks, uint32_t *status, cudaStream_t st,
                            int32_t *commit_rowlist, vgs_result *host_results, vgs_pick *host_picks,
-                           bool keep_candidates, uint32_t *host_status) {
+                           bool keep_candidates, uint32_t *host_status, int4 *commit_walk, int commit_dm) {
     if (n_pods <= 0) return cudaSuccess;
     if (n_pods > 64) host_status = nullptr; // one CTA only (see k3_resolve)
     k3_resolve<<<(n_pods + 63) / 64, 64, 0, st>>>(raw, n_nodes, dmax, row_base, pods, reqs, pick_begin,
                                                  n_pods, keys, counts, results, picks, status, commit_rowlist,
-                                                 host_results, host_picks, keep_candidates, host_status);
+                                                 host_results, host_picks, keep_candidates, host_status,
+                                                 commit_walk, commit_dm);
     return cudaGetLastError();
 }
 

@@ -60,7 +60,7 @@ cudaError_t launch_resolve(const RawPlanes &raw, int32_t n_nodes, int32_t dmax, 
                            vgs_result *results, vgs_pick *picks, uint32_t *status, cudaStream_t st,
                            int32_t *commit_rowlist = nullptr, vgs_result *host_results = nullptr,
                            vgs_pick *host_picks = nullptr, bool keep_candidates = false,
-                           uint32_t *host_status = nullptr);
+                           uint32_t *host_status = nullptr, int4 *commit_walk = nullptr, int commit_dm = 8);
 // K2x: winner shard per pod out of all-gathered exchange blocks [keys | counts | picks] (see k2x_merge)
 cudaError_t launch_exchange_merge(const void *gathered, int32_t n_shards, size_t stride_bytes, int32_t max_pods,
                                   size_t picks_off, const vgs_pod *pods, const int32_t *pick_begin, int32_t n_pods,
