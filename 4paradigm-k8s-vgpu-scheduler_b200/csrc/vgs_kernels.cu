@@ -448,10 +448,12 @@ __global__ void __launch_bounds__(128)
                 bool alive = true, in_ctr = false;
                 float score = 0.0f;
                 int32_t total = 0, free_ = 0, sums = 0;
-                // one request.  FIRST: the devices still stand in K0's walk order, so "fitting
-                // devices ahead of me" is a prefix count and no keys are compared.  NUMA: numa-bind
-                // grouping.  LAST: nothing follows, the re-sorted positions are not needed.
-                auto request = [&](auto FIRST, auto NUMA, auto LAST, const DevReq &rq) {
+                // One request.  The order of the walk is kept as bit masks: gt[j] = devices visited before
+                // j (descending key).  FIRST: the devices still stand in K0's walk order, device i < j is
+                // simply ahead of j and no keys are compared.  NUMA: numa-bind grouping (rare).
+                // "First Nums fitting devices" = fitting devices with fewer than Nums fitting devices ahead
+                // = popc(gt & fitmask) < Nums; the position after this request's sort = 7 - popc(gt).
+                auto request = [&](auto FIRST, auto NUMA, const DevReq &rq) {
                     if (rq.flags & R_NEWCTR) {
                         if (in_ctr) score = __fadd_rn(score, container_score(total, free_, ndev - sums));
                         total = 0;
@@ -461,77 +463,72 @@ __global__ void __launch_bounds__(128)
                     }
                     sums += rq.nums;
                     const bool usepct = rq.flags & R_USEPCT;
-                    int32_t mem[DM], key[DM], nr[DM];
-                    bool fit[DM];
-                    int nfit = 0;
+                    int32_t mem[DM];
+                    uint32_t gt[DM], fitmask = 0u;
 #pragma unroll
                     for (int j = 0; j < DM; j++) {
                         mem[j] = usepct ? pct_mem(totalmem[j], rq.pct) : rq.memfix;
-                        fit[j] = !(mt[j] & rq.blockmask) && type_ok(rq.mask_lo, rq.mask_hi, mt[j]) &&
-                                 fm[j] >= mem[j] && fc[j] >= rq.coresreq;
-                        nr[j] = (mt[j] >> M_NUMA_SHIFT) & 15;
-                        key[j] = (nr[j] << (kKeyFreeBits + kKeyPosBits)) |
-                                 ((fs[j] + kKeyFreeBias) << kKeyPosBits) | pos[j];
-                        nfit += fit[j] ? 1 : 0;
+                        const bool f = !(mt[j] & rq.blockmask) && type_ok(rq.mask_lo, rq.mask_hi, mt[j]) &&
+                                       fm[j] >= mem[j] && fc[j] >= rq.coresreq;
+                        fitmask |= f ? (1u << j) : 0u;
                     }
-                    // ahead[j] = fitting devices visited before j (same numa group only when
-                    // numa-bound); npos[j] = ascending position after this request's sort
-                    int ahead[DM], npos[DM], same[DM];
-                    if constexpr (decltype(FIRST)::value && !decltype(NUMA)::value) {
-                        int run = 0;
+                    if constexpr (decltype(FIRST)::value) {
 #pragma unroll
-                        for (int j = 0; j < DM; j++) {
-                            ahead[j] = run;
-                            run += fit[j] ? 1 : 0;
-                            npos[j] = pos[j];
-                            same[j] = 0;
-                        }
+                        for (int j = 0; j < DM; j++) gt[j] = (1u << j) - 1u;
                     } else {
+                        int32_t key[DM];
 #pragma unroll
                         for (int j = 0; j < DM; j++) {
-                            ahead[j] = 0;
-                            npos[j] = 0;
-                            same[j] = fit[j] ? 1 : 0;
+                            key[j] = (int32_t)(((mt[j] >> M_NUMA_SHIFT) & 15u) << (kKeyFreeBits + kKeyPosBits)) |
+                                     ((fs[j] + kKeyFreeBias) << kKeyPosBits) | pos[j];
+                            gt[j] = 0u;
                         }
 #pragma unroll
                         for (int i = 0; i < DM; i++) {
 #pragma unroll
-                            for (int j = i + 1; j < DM; j++) {
-                                const bool igtj = key[i] > key[j]; // keys are distinct (pos is a permutation)
-                                if constexpr (decltype(NUMA)::value) {
-                                    const bool grp = nr[i] == nr[j];
-                                    ahead[j] += (igtj && fit[i] && grp) ? 1 : 0;
-                                    ahead[i] += (!igtj && fit[j] && grp) ? 1 : 0;
-                                    same[i] += (fit[j] && grp) ? 1 : 0;
-                                    same[j] += (fit[i] && grp) ? 1 : 0;
-                                } else {
-                                    ahead[j] += (igtj && fit[i]) ? 1 : 0;
-                                    ahead[i] += (!igtj && fit[j]) ? 1 : 0;
-                                }
-                                if constexpr (!decltype(LAST)::value) {
-                                    npos[i] += igtj ? 1 : 0;
-                                    npos[j] += igtj ? 0 : 1;
-                                }
+                            for (int j = i + 1; j < DM; j++) { // keys are distinct (pos is a permutation)
+                                const bool igtj = key[i] > key[j];
+                                gt[j] |= igtj ? (1u << i) : 0u;
+                                gt[i] |= igtj ? 0u : (1u << j);
                             }
                         }
                     }
                     bool ok;
-                    int gstar = -1;
+                    uint32_t takemask; // fitting devices the walk takes
                     if constexpr (decltype(NUMA)::value) {
-                        // the walk restarts its picks at every numa change (score.go:99-104):
-                        // the first numa group (descending) holding >= Nums fitting devices wins
+                        // the walk restarts its picks at every numa change (score.go:99-104): the first numa
+                        // group (descending) holding >= Nums fitting devices wins
+                        uint32_t grp[DM]; // devices of my numa group
+                        int gstar = -1;
 #pragma unroll
-                        for (int j = 0; j < DM; j++)
-                            if (fit[j] && same[j] >= rq.nums) gstar = max(gstar, nr[j]);
+                        for (int j = 0; j < DM; j++) {
+                            const uint32_t nj = (mt[j] >> M_NUMA_SHIFT) & 15u;
+                            grp[j] = 0u;
+#pragma unroll
+                            for (int i = 0; i < DM; i++) grp[j] |= (((mt[i] >> M_NUMA_SHIFT) & 15u) == nj) ? (1u << i) : 0u;
+                            if ((fitmask >> j & 1u) && __popc(fitmask & grp[j]) >= rq.nums) gstar = max(gstar, (int)nj);
+                        }
                         ok = gstar >= 0;
+                        takemask = 0u;
+#pragma unroll
+                        for (int j = 0; j < DM; j++) {
+                            const bool t = ok && (fitmask >> j & 1u) && (int)((mt[j] >> M_NUMA_SHIFT) & 15u) == gstar &&
+                                           __popc(gt[j] & fitmask & grp[j]) < rq.nums;
+                            takemask |= t ? (1u << j) : 0u;
+                        }
                     } else {
-                        ok = nfit >= rq.nums;
+                        ok = __popc(fitmask) >= rq.nums;
+                        takemask = 0u;
+#pragma unroll
+                        for (int j = 0; j < DM; j++) {
+                            const bool t = ok && (fitmask >> j & 1u) && __popc(gt[j] & fitmask) < rq.nums;
+                            takemask |= t ? (1u << j) : 0u;
+                        }
                     }
                     alive = alive && ok;
 #pragma unroll
                     for (int j = 0; j < DM; j++) {
-                        const bool take = ok && fit[j] && ahead[j] < rq.nums && (!decltype(NUMA)::value || nr[j] == gstar);
-                        if (take) { // score.go:168-174
+                        if (takemask >> j & 1u) { // score.go:168-174
                             total = wrap_add(total, count[j]);
                             free_ = wrap_add(free_, fs[j]);
                             fs[j] -= 1;
@@ -544,23 +541,22 @@ __global__ void __launch_bounds__(128)
                             m |= (m >> 1) & M_BUSY370; // Used > 0 from here on
                             mt[j] = m;
                         }
-                        if constexpr (!decltype(LAST)::value) pos[j] = npos[j];
+                        // ascending position under the keys this request sorted by = devices with a smaller key
+                        if constexpr (!decltype(FIRST)::value) pos[j] = DM - 1 - __popc(gt[j]);
                     }
                 };
                 using T_ = std::true_type;
                 using F_ = std::false_type;
                 for (int r = 0; r < pod.n_reqs; r++) {
                     const DevReq rq = load_req(&reqs[pod.req_begin + r]);
-                    const bool numa = rq.flags & R_NUMA, last = r + 1 == pod.n_reqs;
-                    if (numa) { // rare: one generic variant
-                        if (last) request(F_{}, T_{}, T_{}, rq);
-                        else request(F_{}, T_{}, F_{}, rq);
+                    const bool numa = rq.flags & R_NUMA;
+                    if (numa) { // rare
+                        if (r == 0) request(T_{}, T_{}, rq);
+                        else request(F_{}, T_{}, rq);
                     } else if (r == 0) {
-                        request(T_{}, F_{}, F_{}, rq); // positions stay as they are
-                    } else if (last) {
-                        request(F_{}, F_{}, T_{}, rq);
+                        request(T_{}, F_{}, rq); // positions stay as they are
                     } else {
-                        request(F_{}, F_{}, F_{}, rq);
+                        request(F_{}, F_{}, rq);
                     }
                     if (!__any_sync(0xffffffffu, alive)) break;
                 }
