@@ -465,9 +465,15 @@ __global__ void __launch_bounds__(128)
                     const bool usepct = rq.flags & R_USEPCT;
                     int32_t mem[DM];
                     uint32_t gt[DM], fitmask = 0u;
+                    if (usepct) { // warp-uniform: the multiply + divide only where the request asks for it
+#pragma unroll
+                        for (int j = 0; j < DM; j++) mem[j] = pct_mem(totalmem[j], rq.pct);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < DM; j++) mem[j] = rq.memfix;
+                    }
 #pragma unroll
                     for (int j = 0; j < DM; j++) {
-                        mem[j] = usepct ? pct_mem(totalmem[j], rq.pct) : rq.memfix;
                         const bool f = !(mt[j] & rq.blockmask) && type_ok(rq.mask_lo, rq.mask_hi, mt[j]) &&
                                        fm[j] >= mem[j] && fc[j] >= rq.coresreq;
                         fitmask |= f ? (1u << j) : 0u;
@@ -498,16 +504,23 @@ __global__ void __launch_bounds__(128)
                     if constexpr (decltype(NUMA)::value) {
                         // the walk restarts its picks at every numa change (score.go:99-104): the first numa
                         // group (descending) holding >= Nums fitting devices wins
-                        uint32_t grp[DM]; // devices of my numa group
+                        uint32_t grp[DM]; // devices of my numa group (me included)
                         int gstar = -1;
 #pragma unroll
-                        for (int j = 0; j < DM; j++) {
-                            const uint32_t nj = (mt[j] >> M_NUMA_SHIFT) & 15u;
-                            grp[j] = 0u;
+                        for (int j = 0; j < DM; j++) grp[j] = 1u << j;
 #pragma unroll
-                            for (int i = 0; i < DM; i++) grp[j] |= (((mt[i] >> M_NUMA_SHIFT) & 15u) == nj) ? (1u << i) : 0u;
-                            if ((fitmask >> j & 1u) && __popc(fitmask & grp[j]) >= rq.nums) gstar = max(gstar, (int)nj);
+                        for (int i = 0; i < DM; i++) {
+#pragma unroll
+                            for (int j = i + 1; j < DM; j++) {
+                                const bool eq = ((mt[i] ^ mt[j]) & (15u << M_NUMA_SHIFT)) == 0u;
+                                grp[i] |= eq ? (1u << j) : 0u;
+                                grp[j] |= eq ? (1u << i) : 0u;
+                            }
                         }
+#pragma unroll
+                        for (int j = 0; j < DM; j++)
+                            if ((fitmask >> j & 1u) && __popc(fitmask & grp[j]) >= rq.nums)
+                                gstar = max(gstar, (int)((mt[j] >> M_NUMA_SHIFT) & 15u));
                         ok = gstar >= 0;
                         takemask = 0u;
 #pragma unroll
@@ -550,9 +563,8 @@ __global__ void __launch_bounds__(128)
                 for (int r = 0; r < pod.n_reqs; r++) {
                     const DevReq rq = load_req(&reqs[pod.req_begin + r]);
                     const bool numa = rq.flags & R_NUMA;
-                    if (numa) { // rare
-                        if (r == 0) request(T_{}, T_{}, rq);
-                        else request(F_{}, T_{}, rq);
+                    if (numa) { // rare: one variant, keys compared even for the first request
+                        request(F_{}, T_{}, rq);
                     } else if (r == 0) {
                         request(T_{}, F_{}, rq); // positions stay as they are
                     } else {
