@@ -529,6 +529,15 @@ __global__ void __launch_bounds__(128)
                                            __popc(gt[j] & fitmask & grp[j]) < rq.nums;
                             takemask |= t ? (1u << j) : 0u;
                         }
+                    } else if constexpr (decltype(FIRST)::value) {
+                        // K0's order: device i < j is ahead of j, so the walk takes the lowest Nums set bits
+                        ok = __popc(fitmask) >= rq.nums;
+                        takemask = 0u;
+                        uint32_t m = ok ? fitmask : 0u;
+                        for (int n = 0; n < rq.nums && n < DM; n++) { // warp-uniform trip count
+                            takemask |= m & (0u - m);
+                            m &= m - 1u;
+                        }
                     } else {
                         ok = __popc(fitmask) >= rq.nums;
                         takemask = 0u;
