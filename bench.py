@@ -5,19 +5,22 @@
   python bench.py --impl reference ...                   CPU arm: the oracle restatement
 
 Step = one pass of the hot path over one pod batch against the resident snapshot:
-K0 prepare (raw planes -> walk-ordered tiles) + K1 score + [all-gather + K2 merge for
-N > 1] + K3 resolve.  Workload at N=1 = BASELINE config 3 (100k nodes x 8 devices x
+K0 prepare (raw planes -> walk-ordered tiles) + K1 score + K3 resolve; for N > 1 every shard
+resolves its own best node, the [keys | counts | picks] blocks are all-gathered once (NCCL) and
+merged (K2x).  Workload at N=1 = BASELINE config 3 (100k nodes x 8 devices x
 4096 mixed pods); for N > 1 every rank holds its own 100k-node shard (weak scaling,
 N x 100k nodes in total) and the same 4096 pods.
 
 `value`   : device-timed (CUDA events per step on the launching stream, max over ranks),
             inputs resident in HBM, L2 flushed between steps.
 `e2e`     : the same metric through the host-buffer C ABI calls the Go shim makes
-            (vgs_snapshot_upload + vgs_score_batch): pinned host planes and request
-            records in, results out, every step.
+            (vgs_snapshot_upload_async + pods upload / score / resolve / download): pinned
+            host planes and request records in, results out, every step.
 `roofline`: the score kernels (K1) against the measured HBM peak, with the
             algorithmic bytes of SURVEY 8(d).  The batch regime is integer-issue bound,
             so this fraction is tiny by construction; see DESIGN.md.
+`roofline_hbm_regime` (N = 1): one pod against 1M resident nodes, where the pass IS HBM-bound.
+`filter_latency` (N = 1): wall clock of the single-pod vgs_score_batch call, snapshot resident.
 The reference (Go) cannot be built or run here; its CPU arm is the oracle's packed
 multi-threaded restatement ("port"), timed on this box's host cores.
 """
@@ -466,7 +469,7 @@ def main():
         line["filter_latency"] = latency
     if hbm_regime:
         line["roofline_hbm_regime"] = hbm_regime
-    if not args.no_cpu:
+    if not args.no_cpu and world == 1:  # a reported baseline, measured once (N = 1)
         val, th, dt, sp = cpu_arm(snap, batch, 64)   # calibrate
         sample = max(64, min(P, int(64 * 12.0 / max(dt, 1e-3))))
         val, th, dt, sp = cpu_arm(snap, batch, sample)
