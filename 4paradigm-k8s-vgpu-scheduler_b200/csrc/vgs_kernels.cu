@@ -1002,26 +1002,22 @@ __global__ void __launch_bounds__(128)
         s_best[b * T + tid] = 0u;
         s_row[b * T + tid] = kNotMine;
     }
-    if (TABSMEM) { // eight independent loads in flight per thread: the copy is latency-, not bandwidth-bound
+    if (TABSMEM) { // every row of my column with one asynchronous 4-byte copy each: one round trip, no registers
         uint32_t *tw = reinterpret_cast<uint32_t *>(smem_raw + L.tab);
         const int rows_s = rows_g - drop;
-        for (int r0 = 0; r0 < rows_s; r0 += 8) {
-            uint32_t v[8];
-#pragma unroll
-            for (int u = 0; u < 8; u++) {
-                const int r = min(r0 + u, rows_s - 1);
-                v[u] = __ldg(&tb.base[(size_t)(r < n_types ? r : r + drop) * tb.Wp + wc]);
-            }
-#pragma unroll
-            for (int u = 0; u < 8; u++)
-                if (r0 + u < rows_s) tw[(r0 + u) * T + tid] = v[u];
+        for (int r = 0; r < rows_s; r++) {
+            const uint32_t *src = &tb.base[(size_t)(r < n_types ? r : r + drop) * tb.Wp + wc];
+            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(&tw[r * T + tid]);
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
         }
+        asm volatile("cp.async.commit_group;" ::: "memory");
     }
     if (tid == 0) {
         mbar_init(&bar[0], 1);
         mbar_init(&bar[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    if (TABSMEM) asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();
     if (tid == 0) fetch(tile_of(t_hi - 1), 0);
     const int nv = (int)vals[kDict];
@@ -1029,18 +1025,18 @@ __global__ void __launch_bounds__(128)
         // inherit the scouts' bests.  A holder above all my rows can only be beaten by a strictly
         // larger score; one below some of my rows also by an equal score, so its score is
         // inherited one ulp lower (a local tie on a lower row is harmless: keys only grow).
-        for (int b0 = 0; b0 < 32; b0 += 8) { // two rounds of 8 independent loads, not 16 dependent ones
-            int op[8];
-            unsigned long long kk[8];
+        for (int b0 = 0; b0 < 32; b0 += 16) { // two rounds of 16 independent loads, not 32 dependent ones
+            int op[16];
+            unsigned long long kk[16];
 #pragma unroll
-            for (int u = 0; u < 8; u++) {
+            for (int u = 0; u < 16; u++) {
                 const int i = w * 32 + b0 + u;
                 op[u] = (active && i < tb.n_pods) ? __ldg(&tb.orig[i]) : -1;
             }
 #pragma unroll
-            for (int u = 0; u < 8; u++) kk[u] = op[u] >= 0 ? keys[op[u]] : 0ull;
+            for (int u = 0; u < 16; u++) kk[u] = op[u] >= 0 ? keys[op[u]] : 0ull;
 #pragma unroll
-            for (int u = 0; u < 8; u++) {
+            for (int u = 0; u < 16; u++) {
             const int b = b0 + u;
             const unsigned long long key = kk[u];
             uint32_t init = 0u;
