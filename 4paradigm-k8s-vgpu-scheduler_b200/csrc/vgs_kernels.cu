@@ -900,22 +900,6 @@ __global__ void __launch_bounds__(128) k1p_classify(int32_t n_tiles, SliceTab tb
     }
 }
 
-// the replay step of k1_score_sliced for one candidate: see the `raise` lambda there.  Kept out of line: it is
-// inlined at 32 (Nums 1) / 112 (Nums 2) sites otherwise, and the kernels are bound by instruction fetch.
-__device__ __noinline__ void slice_raise(uint32_t word, uint32_t sb, uint32_t row_off, uint32_t *best_t,
-                                         uint16_t *row_t, uint32_t *below_t, const uint32_t *vals, int nv, int T) {
-    uint32_t imp = 0u;
-    for (uint32_t m = word; m; m &= m - 1) {
-        const int b = __ffs((int)m) - 1;
-        if (sb > best_t[b * T]) {
-            best_t[b * T] = sb;
-            row_t[b * T] = (uint16_t)row_off;
-            imp |= 1u << b;
-        }
-    }
-    for (int k = 0; k < nv && vals[k] <= sb; k++) below_t[k * T] &= ~imp;
-}
-
 // shared-memory carve-up of k1_score_sliced (bytes); T = threads per CTA
 struct SliceSmem {
     int tile, ptile, bar, vals, below, best, row, tab, total;
@@ -1091,8 +1075,17 @@ __global__ void __launch_bounds__(128)
     };
     // pods in `word` get candidate (sb, node); nodes only ever decrease, so equal scores keep
     // the earlier (higher) row.  A pod whose best reaches sb leaves every below[k] with vals[k] <= sb.
-    auto raise = [&](uint32_t word, uint32_t sb, int node) { // one out-of-line copy: the call sites are many
-        slice_raise(word, sb, (uint32_t)(node - node_lo), s_best + tid, s_row + tid, below + tid, vals, nv, T);
+    auto raise = [&](uint32_t word, uint32_t sb, int node) {
+        uint32_t imp = 0u;
+        for (uint32_t m = word; m; m &= m - 1) {
+            const int b = __ffs((int)m) - 1;
+            if (sb > s_best[b * T + tid]) {
+                s_best[b * T + tid] = sb;
+                s_row[b * T + tid] = (uint16_t)(node - node_lo);
+                imp |= 1u << b;
+            }
+        }
+        for (int k = 0; k < nv && vals[k] <= sb; k++) below[k * T + tid] &= ~imp;
     };
     auto mark = [&](uint32_t word, int node, uint32_t sb) { // verify mode: score of every fitting pair
         for (uint32_t mth = word; mth; mth &= mth - 1) {
