@@ -105,7 +105,7 @@ struct vgs_ctx {
     // the pod classes of one batch are independent: their kernel chains run on side streams
     // forked from / joined to `st` with events
     cudaStream_t side[2] = {};
-    cudaEvent_t ev_fork = nullptr, ev_join[2] = {};
+    cudaEvent_t ev_fork = nullptr, ev_join[2] = {}, ev_ns[2] = {};
     cudaEvent_t ev[EV_N] = {};
     bool ev_set[EV_N] = {};
     int ev_alias[EV_N] = {};  // which recorded event stands for this boundary (see rec)
@@ -227,6 +227,7 @@ void free_all(vgs_ctx *c) {
     for (int k = 0; k < 2; k++) {
         if (c->side[k]) cudaStreamDestroy(c->side[k]);
         if (c->ev_join[k]) cudaEventDestroy(c->ev_join[k]);
+        if (c->ev_ns[k]) cudaEventDestroy(c->ev_ns[k]);
     }
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     if (c->own_stream && c->st) cudaStreamDestroy(c->st);
@@ -292,6 +293,7 @@ int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
     for (int k = 0; k < 2; k++) {
         CUI(cudaStreamCreateWithFlags(&c->side[k], cudaStreamNonBlocking));
         CUI(cudaEventCreateWithFlags(&c->ev_join[k], cudaEventDisableTiming));
+        CUI(cudaEventCreateWithFlags(&c->ev_ns[k], cudaEventDisableTiming));
     }
     const size_t cells = (size_t)cfg->max_nodes * cfg->max_devices;
     for (int f = 0; f < VGS_NUM_PLANES; f++) CUI(cudaMalloc(&c->d_raw[f], cells * sizeof(int32_t)));
@@ -815,7 +817,8 @@ static int score_locked(vgs_ctx *c) {
     if (c->nA) {
         if (sliced && c->slice_on[0]) {
             int nl = 0;
-            CU(launch_score_sliced(1, c->cfg.device, a, c->tab[0], c->n_types_used, c->d_status, sA, &nl));
+            CU(launch_score_sliced(1, c->cfg.device, a, c->tab[0], c->n_types_used, c->d_status, sA, &nl,
+                                   fork ? c->st : nullptr, c->ev_ns[0]));
             c->launches += nl;
         } else {
             CU(launch_score_single(c->dm, true, c->cfg.device, a,
@@ -827,7 +830,8 @@ static int score_locked(vgs_ctx *c) {
     if (c->nB) {
         if (sliced && c->slice_on[1]) {
             int nl = 0;
-            CU(launch_score_sliced(2, c->cfg.device, a, c->tab[1], c->n_types_used, c->d_status, sB, &nl));
+            CU(launch_score_sliced(2, c->cfg.device, a, c->tab[1], c->n_types_used, c->d_status, sB, &nl,
+                                   fork ? c->st : nullptr, c->ev_ns[1]));
             c->launches += nl;
         } else {
             CU(launch_score_single(c->dm, false, c->cfg.device, a,

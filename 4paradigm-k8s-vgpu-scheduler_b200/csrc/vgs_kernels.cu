@@ -1760,7 +1760,7 @@ cudaError_t launch_score_general(int dm, int dev, const ScoreArgs &a, const DevR
 
 template <int NUMS>
 static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &tb_in, int n_types, uint32_t *status,
-                                   cudaStream_t st, int *n_launched) {
+                                   cudaStream_t st, int *n_launched, cudaStream_t st_ns, cudaEvent_t ev_ns) {
     const int sms = sm_count(dev);
     cudaError_t e;
     SliceTab tb = tb_in;
@@ -1813,6 +1813,12 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
     if (W_main > 0) {
         if ((e = cudaMemsetAsync(tb.hset, 0, kSliceHash * sizeof(uint32_t), st)) != cudaSuccess) return e;
         k1p_collect<NUMS><<<(nthreads + 127) / 128, 128, 0, st>>>(a.walk, a.n_tiles, tb, status, true);
+        // the node-sliced words need the records only (not the score classes): they can start now, on
+        // another stream, instead of queueing behind the class's sort / classify / scout / main launches
+        if (ns_words > 0 && st_ns != st && ev_ns) {
+            if ((e = cudaEventRecord(ev_ns, st)) != cudaSuccess) return e;
+            if ((e = cudaStreamWaitEvent(st_ns, ev_ns, 0)) != cudaSuccess) return e;
+        }
         k1p_sort<<<1, 1024, 0, st>>>(tb);
         k1p_classify<NUMS><<<(nthreads + 127) / 128, 128, 0, st>>>(a.n_tiles, tb);
         *n_launched += 3;
@@ -1891,7 +1897,8 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
             const long long need = (a.n_tiles + 3) / 4;
             if (gx > need) gx = need;
             if (gx < 1) gx = 1;
-            kernel<<<dim3((unsigned)gx, (unsigned)ns_words), 128, nsmem, st>>>(a.n_tiles, a.n_nodes, a.row_base, tn, W_main,
+            cudaStream_t sn = (W_main > 0 && st_ns != st && ev_ns) ? st_ns : st;
+            kernel<<<dim3((unsigned)gx, (unsigned)ns_words), 128, nsmem, sn>>>(a.n_tiles, a.n_nodes, a.row_base, tn, W_main,
                                                                              a.keys, a.counts, a.vfit, a.vscore, a.vwords);
             *n_launched += 1;
             return cudaGetLastError();
@@ -1903,11 +1910,13 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
 }
 
 cudaError_t launch_score_sliced(int nums, int dev, const ScoreArgs &a, const SliceTab &tb, int n_types,
-                                uint32_t *status, cudaStream_t st, int *n_launched) {
+                                uint32_t *status, cudaStream_t st, int *n_launched, cudaStream_t st_ns,
+                                cudaEvent_t ev_ns) {
     *n_launched = 0;
     if (tb.n_pods <= 0 || a.n_tiles <= 0) return cudaSuccess;
-    return nums == 1 ? launch_sliced_t<1>(dev, a, tb, n_types, status, st, n_launched)
-                     : launch_sliced_t<2>(dev, a, tb, n_types, status, st, n_launched);
+    if (!st_ns) st_ns = st;
+    return nums == 1 ? launch_sliced_t<1>(dev, a, tb, n_types, status, st, n_launched, st_ns, ev_ns)
+                     : launch_sliced_t<2>(dev, a, tb, n_types, status, st, n_launched, st_ns, ev_ns);
 }
 
 // K2x: merge of whole exchange blocks.  Every shard has resolved its OWN best node per pod (K3 with

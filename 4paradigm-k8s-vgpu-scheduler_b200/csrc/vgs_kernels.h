@@ -48,7 +48,10 @@ cudaError_t launch_slice_tables(const SliceTab &tb, const DevReq *dreq_class, cu
 // (K1p collect / sort / classify, then the score kernel as scouts + main pass, or one pass on a small
 // snapshot; *n_launched receives the number of kernels launched)
 cudaError_t launch_score_sliced(int nums, int dev, const ScoreArgs &a, const SliceTab &tb, int n_types,
-                                uint32_t *status, cudaStream_t st, int *n_launched);
+                                uint32_t *status, cudaStream_t st, int *n_launched,
+                                cudaStream_t st_ns = nullptr, cudaEvent_t ev_ns = nullptr);
+// (st_ns / ev_ns: optional second stream + event on which the node-sliced words of the class may run as soon
+// as K1p's records exist; the caller joins st_ns with whatever consumes the keys)
 cudaError_t launch_merge(const unsigned long long *gk, const int32_t *gc, int32_t n_shards,
                          int32_t stride, int32_t cstride, int32_t n_pods, unsigned long long *keys,
                          int32_t *counts, cudaStream_t st);
