@@ -1432,14 +1432,14 @@ __global__ void __launch_bounds__(64)
         return;
     }
 
-    const int32_t nd = raw.ndev[row];
+    int32_t nd = raw.ndev[row];
     const size_t base = (size_t)row * dmax;
     int32_t used[VGS_MAX_DEVICES], usedmem[VGS_MAX_DEVICES], usedcores[VGS_MAX_DEVICES];
     int32_t count[VGS_MAX_DEVICES], totalmem[VGS_MAX_DEVICES], totalcore[VGS_MAX_DEVICES];
     int32_t numa[VGS_MAX_DEVICES], type[VGS_MAX_DEVICES], ord[VGS_MAX_DEVICES];
 #pragma unroll
     for (int d = 0; d < VGS_MAX_DEVICES; d++) { // all loads issued at once: this thread is latency-bound
-        const bool on = d < nd;
+        const bool on = d < dmax; // (not d < ndev: that would put ndev's own load in front of all of these)
         used[d] = on ? raw.p[VGS_PLANE_USED][base + d] : 0;
         usedmem[d] = on ? raw.p[VGS_PLANE_USEDMEM][base + d] : 0;
         usedcores[d] = on ? raw.p[VGS_PLANE_USEDCORES][base + d] : 0;
@@ -1450,6 +1450,7 @@ __global__ void __launch_bounds__(64)
         type[d] = on ? raw.p[VGS_PLANE_TYPEID][base + d] : 0;
         ord[d] = d;
     }
+    nd = min(max(nd, 0), dmax);
 
     float score = 0.0f;
     bool alive = true, in_ctr = false;
