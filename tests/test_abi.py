@@ -100,6 +100,10 @@ def test_decode_node_devices(built):
     # Atoi errors are ignored by the reference (-> 0); entries without ',' are skipped
     devs = v.capi.decode_node_devices("x,abc,-5,+7,T,,maybe::junk:")
     assert devs == [dict(ID="x", Count=0, Devmem=-5, Devcore=7, Type="T", Numa=0, Health=False)]
+    # strconv.Atoi = ParseInt(s, 10, 0): a range error clamps to the int64 limit, which int32(x) then truncates
+    # (max int64 -> -1, min int64 -> 0); the scan stops at the overflow, before it can see a later bad byte
+    devs = v.capi.decode_node_devices("y,99999999999999999999,-99999999999999999999,99999999999999999999x,T,4294967297,1:")
+    assert devs == [dict(ID="y", Count=-1, Devmem=0, Devcore=-1, Type="T", Numa=1, Health=True)]
     for bad in ("no separators", "a,b,c:", "a,1,2,3,T,0,true,extra:"):
         try:
             v.capi.decode_node_devices(bad)
