@@ -149,3 +149,24 @@ def test_decode_pod_devices_follows_the_go_parser(built):
     assert dec("u,t,+7,-0:") == [[("u", "t", 7, 0)]]
     with pytest.raises(v.VgsError):
         dec("a,b,1,2:" * 5, max_dev=4)
+
+
+def test_header_is_plain_c99_and_links(built, tmp_path):
+    """the cgo shim includes vgpuscore.h as C: the header must compile as C99 with no C++ leaking in, and a
+    C program that names every declared entry point must link against the in-tree library"""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    hdr = os.path.join(root, "include", "vgpuscore.h")
+    names = sorted(set(re.findall(r"\b(vgs_[a-z0-9_]+)\s*\(", open(hdr).read())))
+    assert set(names) == set(v.capi.EXPORTS)
+    src = tmp_path / "abi.c"
+    body = "\n".join(f"    p[{i}] = (fn){n};" for i, n in enumerate(names))
+    src.write_text(f'#include "vgpuscore.h"\n#include <stdio.h>\ntypedef void (*fn)(void);\nint main(void) {{\n    fn p[{len(names)}];\n{body}\n'
+                   f'    printf("%d %d %d\\n", vgs_abi_version(), (int)sizeof(vgs_req), (int)sizeof(vgs_result));\n'
+                   f'    return p[0] == 0;\n}}\n')
+    exe = tmp_path / "abi"
+    libdir = os.path.dirname(v.capi.LIB_PATH)
+    subprocess.check_call(["gcc", "-std=c99", "-pedantic", "-Wall", "-Werror", "-I", os.path.join(root, "include"),
+                           str(src), "-o", str(exe), "-L", libdir, "-lvgpuscore", f"-Wl,-rpath,{libdir}"])
+    out = subprocess.check_output([str(exe)]).decode().split()
+    assert int(out[0]) >= 1 and out[1:] == ["32", "16"]
