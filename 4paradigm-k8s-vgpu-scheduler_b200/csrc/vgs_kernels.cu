@@ -102,18 +102,30 @@ __device__ __forceinline__ void prepare_node(const RawPlanes &raw, int row, int3
     }
     int32_t used[DM], count[DM], usedmem[DM], totalmem[DM], usedcores[DM], totalcore[DM],
         numa[DM], type[DM];
+    // the slots are loaded for j < dmax, not j < ndev (ndev's own load would sit in front of all of them),
+    // as two 128-bit loads per plane where the rows are 32 bytes, and masked afterwards
+    int32_t *const dst[VGS_NUM_PLANES] = {used, count, usedmem, totalmem, usedcores, totalcore, numa, type};
+    unsigned long long all_ptrs = 0ull; // caller-owned planes (vgs_score_batch_noalloc) may be 4-byte aligned only
+#pragma unroll
+    for (int f = 0; f < VGS_NUM_PLANES; f++) all_ptrs |= reinterpret_cast<unsigned long long>(raw.p[f]);
+    if (DM == 8 && dmax == 8 && valid && (all_ptrs & 15ull) == 0ull) {
+#pragma unroll
+        for (int f = 0; f < VGS_NUM_PLANES; f++) {
+            const int4 *q = reinterpret_cast<const int4 *>(raw.p[f] + (size_t)row * 8);
+            const int4 lo = q[0], hi = q[1];
+            dst[f][0] = lo.x, dst[f][1] = lo.y, dst[f][2] = lo.z, dst[f][3] = lo.w;
+            dst[f][4] = hi.x, dst[f][5] = hi.y, dst[f][6] = hi.z, dst[f][7] = hi.w;
+        }
+    } else {
+#pragma unroll
+        for (int f = 0; f < VGS_NUM_PLANES; f++)
+#pragma unroll
+            for (int j = 0; j < DM; j++) dst[f][j] = (valid && j < dmax) ? raw.p[f][(size_t)row * dmax + j] : 0;
+    }
 #pragma unroll
     for (int j = 0; j < DM; j++) {
         bool on = j < nd;
-        size_t x = (size_t)row * dmax + j;
-        used[j] = on ? raw.p[VGS_PLANE_USED][x] : 0;
-        count[j] = on ? raw.p[VGS_PLANE_COUNT][x] : 0;
-        usedmem[j] = on ? raw.p[VGS_PLANE_USEDMEM][x] : 0;
-        totalmem[j] = on ? raw.p[VGS_PLANE_TOTALMEM][x] : 0;
-        usedcores[j] = on ? raw.p[VGS_PLANE_USEDCORES][x] : 0;
-        totalcore[j] = on ? raw.p[VGS_PLANE_TOTALCORE][x] : 0;
-        numa[j] = on ? raw.p[VGS_PLANE_NUMA][x] : 0;
-        type[j] = on ? raw.p[VGS_PLANE_TYPEID][x] : 0;
+        if (!on) used[j] = count[j] = usedmem[j] = totalmem[j] = usedcores[j] = totalcore[j] = numa[j] = type[j] = 0;
         if (on) {
             if (used[j] < 0 || used[j] >= VGS_MAX_SHARE || count[j] < 0 || count[j] >= VGS_MAX_SHARE)
                 bad |= S_RANGE;
