@@ -814,6 +814,14 @@ static int score_locked(vgs_ctx *c) {
         CU(cudaEventRecord(c->ev_fork, c->st));
         for (int k = 0; k < 2; k++) CU(cudaStreamWaitEvent(c->side[k], c->ev_fork, 0));
     }
+    // The Nums 2 chain is issued first: it is the longer one on the mixes measured (pair enumeration in its
+    // scouts), and whichever chain is issued first gets the SMs first (cfg3, alternating runs on one box:
+    // 0.4123 ms with class A first, 0.4083 ms with class B first).  VGS_ORDER=0 issues class A first.
+    static int order_env = -1;
+    if (order_env < 0) order_env = getenv("VGS_ORDER") ? atoi(getenv("VGS_ORDER")) : 1;
+    for (int turn = 0; turn < 2; turn++) {
+    const bool doA = (turn == 0) != (order_env == 1);
+    if (doA) {
     if (c->nA) {
         if (sliced && c->slice_on[0]) {
             int nl = 0;
@@ -827,6 +835,7 @@ static int score_locked(vgs_ctx *c) {
             if (c->n_tiles) c->launches++;
         }
     }
+    } else {
     if (c->nB) {
         if (sliced && c->slice_on[1]) {
             int nl = 0;
@@ -839,6 +848,8 @@ static int score_locked(vgs_ctx *c) {
                                    reinterpret_cast<const int32_t *>(c->d_stage + c->off_origB), c->nB, sB));
             if (c->n_tiles) c->launches++;
         }
+    }
+    }
     }
     if (c->nC) {
         CU(launch_score_single(c->dm, false, c->cfg.device, a,
