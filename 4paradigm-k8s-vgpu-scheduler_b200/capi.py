@@ -33,13 +33,37 @@ EXPORTS = (
     "vgs_results_download", "vgs_sync", "vgs_keys_device", "vgs_keys_merge", "vgs_results_device",
     "vgs_verify_download", "vgs_last_timing", "vgs_host_typemask", "vgs_host_numa_bind",
     "vgs_host_encode_pod_devices", "vgs_host_decode_node_devices", "vgs_score_batch_noalloc",
+    "vgs_tuning_defaults", "vgs_last_plan",
 )
+
+
+class VgsTuning(C.Structure):
+    _fields_ = [("slice_min", C.c_int32), ("slice_small", C.c_int32), ("slice_small_pairs", C.c_int64),
+                ("node_words", C.c_int32), ("tables_in_smem", C.c_int32), ("tables_smem_kb", C.c_int32),
+                ("scout_stride", C.c_int32), ("scout_split", C.c_int32), ("class_order", C.c_int32),
+                ("zero_copy_upload", C.c_int32), ("general_legacy", C.c_int32), ("max_ctas", C.c_int32),
+                ("reserved", C.c_int32 * 5)]
 
 
 class VgsConfig(C.Structure):
     _fields_ = [("device", C.c_int32), ("max_nodes", C.c_int32), ("max_devices", C.c_int32),
                 ("max_pods", C.c_int32), ("max_reqs", C.c_int32), ("max_picks", C.c_int32),
-                ("row_base", C.c_int32), ("verify", C.c_int32), ("stream", C.c_void_p)]
+                ("row_base", C.c_int32), ("verify", C.c_int32), ("stream", C.c_void_p),
+                ("tuning", C.POINTER(VgsTuning))]
+
+
+class VgsClassPlan(C.Structure):
+    _fields_ = [("pods", C.c_int32), ("kernel", C.c_int32), ("words_pod_sliced", C.c_int32),
+                ("words_node_sliced", C.c_int32), ("tables_in_smem", C.c_int32), ("scout_stride", C.c_int32),
+                ("scout_split", C.c_int32), ("tiles_per_cta_scout", C.c_int32), ("tiles_per_cta_main", C.c_int32),
+                ("launches", C.c_int32)]
+
+
+class VgsPlan(C.Structure):
+    _fields_ = [("cls", VgsClassPlan * 4), ("dict_full", C.c_int32), ("reserved", C.c_int32 * 3)]
+
+
+KERNEL_NONE, KERNEL_PAIR, KERNEL_SLICED, KERNEL_GENERAL = range(4)
 
 
 class VgsTiming(C.Structure):
@@ -111,6 +135,9 @@ def load_library() -> C.CDLL:
     lib.vgs_exchange_merge.argtypes = [vp, vp, i32, C.c_uint64]
     lib.vgs_verify_download.argtypes = [vp, vp, vp]
     lib.vgs_last_timing.argtypes = [vp, C.POINTER(VgsTiming)]
+    lib.vgs_last_plan.argtypes = [vp, C.POINTER(VgsPlan)]
+    lib.vgs_tuning_defaults.argtypes = [C.POINTER(VgsTuning)]
+    lib.vgs_tuning_defaults.restype = None
     lib.vgs_score_batch_noalloc.argtypes = [i32, vp, i32, i32, i32, C.POINTER(vp), vp, i32, vp, i32, vp, vp, vp]
     lib.vgs_host_typemask.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.POINTER(C.c_char_p), i32]
     lib.vgs_host_typemask.restype = C.c_uint64
@@ -274,12 +301,20 @@ class Context:
 
     def __init__(self, max_nodes: int, max_devices: int = 8, max_pods: int = 4096, max_reqs: Optional[int] = None,
                  max_picks: Optional[int] = None, device: int = 0, row_base: int = 0, verify: bool = False,
-                 stream: int = 0):
+                 stream: int = 0, tuning: Optional[Dict[str, int]] = None):
+        """tuning: vgs_tuning fields to change from their defaults, e.g. {"slice_min": 1, "node_words": 0}"""
         self.lib = load_library()
         max_reqs = max_reqs or max_pods * 4
         max_picks = max_picks or max_reqs * 4
+        tune = VgsTuning()
+        self.lib.vgs_tuning_defaults(C.byref(tune))
+        for k, val in (tuning or {}).items():
+            if k not in dict((f[0], 1) for f in VgsTuning._fields_):
+                raise KeyError(f"vgs_tuning has no field {k!r}")
+            setattr(tune, k, int(val))
+        self.tuning = tune
         cfg = VgsConfig(device, max(max_nodes, 1), max_devices, max_pods, max_reqs, max_picks, row_base,
-                        1 if verify else 0, C.c_void_p(stream) if stream else None)
+                        1 if verify else 0, C.c_void_p(stream) if stream else None, C.pointer(tune))
         self.cfg = cfg
         self.h = C.c_void_p()
         rc = self.lib.vgs_init(C.byref(cfg), C.byref(self.h))
@@ -438,6 +473,12 @@ class Context:
     def keys_merge(self, keys_ptr: int, counts_ptr: int, n_shards: int, stride: int, count_stride: int = 0):
         self._check(self.lib.vgs_keys_merge(self.h, C.c_void_p(keys_ptr), C.c_void_p(counts_ptr), n_shards, stride,
                                             count_stride))
+
+    def plan(self) -> VgsPlan:
+        """vgs_last_plan: which kernels the last score pass used, and their launch geometry"""
+        pl = VgsPlan()
+        self._check(self.lib.vgs_last_plan(self.h, C.byref(pl)))
+        return pl
 
     def timing(self) -> VgsTiming:
         t = VgsTiming()

@@ -82,12 +82,12 @@ struct vgs_ctx {
     size_t slice_words = 0;
     SliceTab tab[2] = {};
     bool slice_on[2] = {false, false};
-    int32_t slice_min = 512;     // classes smaller than this use the per-pair kernels ...
-    int32_t slice_small = 64;    // ... unless they have this many pods and pods x nodes >= slice_small_pairs
-    int64_t slice_small_pairs = 16000000;
+    vgs_tuning tune{};           // copied from vgs_config.tuning at vgs_init (defaults when NULL)
+    vgs_plan plan{};             // how the last score pass ran (vgs_last_plan)
     bool snap_slice_ok = false;  // snapshot satisfies the sliced kernel's preconditions
+    bool snap_bigmem = false;    // some Totalmem of the resident snapshot is outside the sliced kernels' range;
+                                 // sticky until the next full upload (deltas never touch Totalmem)
     int32_t n_types_used = VGS_MAX_TYPES; // largest type id of the snapshot + 1
-    bool zero_copy_ok = true;             // VGS_ZERO_COPY=0 disables the kernel-driven upload
     bool have_pods = false, scored = false, resolved = false;
     bool direct_out = false; // K3 of the current batch wrote h_results / h_picks itself
     size_t picks_off = 0, xblock_bytes = 0; // exchange block = [keys | counts | pad | picks], one allocation
@@ -167,7 +167,12 @@ int check_status(vgs_ctx *c) {
 // h_status holds the two status words of the resident snapshot: errors, and what the score path may assume
 int apply_status(vgs_ctx *c) {
     int rc = check_status(c);
-    c->snap_slice_ok = rc == VGS_OK && !(*c->h_status & S_BIGMEM) && c->dm == 8;
+    // S_BIGMEM is a property of the planes, not an error: K0 raises it only for rows it prepares, so it is
+    // remembered on the host -- clearing the error bits below (or a delta that re-prepares other rows) must
+    // not make the sliced kernels believe Totalmem * pct cannot wrap
+    if (*c->h_status & S_BIGMEM) c->snap_bigmem = true;
+    if (*c->h_status & S_DICTFULL) c->plan.dict_full = 1;
+    c->snap_slice_ok = rc == VGS_OK && !c->snap_bigmem && c->dm == 8;
     c->n_types_used = (int32_t)c->h_status[1] + 1;
     if (rc != VGS_OK) cudaMemsetAsync(c->d_status, 0, sizeof(uint32_t), c->st);
     return rc;
@@ -269,6 +274,11 @@ int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
     vgs_ctx *c = new (std::nothrow) vgs_ctx();
     if (!c) return VGS_EINVAL;
     c->cfg = *cfg;
+    vgs_tuning_defaults(&c->tune);
+    if (cfg->tuning) c->tune = *cfg->tuning;
+    c->cfg.tuning = nullptr; // the caller's struct is not kept
+    if (c->tune.slice_min < 1) c->tune.slice_min = 1;
+    if (c->tune.slice_small < 1) c->tune.slice_small = 1;
     c->dm = walk_dm(cfg->max_devices);
     DeviceGuard g(cfg->device);
     auto bail = [&](int rc) {
@@ -335,8 +345,6 @@ int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
             c->tab[k].hset = reinterpret_cast<uint32_t *>(c->d_prep[k] + dinfo_b + pcls_b);
             c->tab[k].gvals = reinterpret_cast<uint32_t *>(c->d_prep[k] + dinfo_b + pcls_b + hset_b);
         }
-        if (const char *e = getenv("VGS_SLICE_MIN")) c->slice_min = c->slice_small = atoi(e);
-        if (const char *e = getenv("VGS_ZERO_COPY")) c->zero_copy_ok = atoi(e) != 0;
     }
     // keys and counts are one allocation ("candidate block": max_pods u64 keys, then max_pods
     // int32 counts) so that shards can exchange both with a single all-gather
@@ -387,6 +395,7 @@ static int snapshot_common(vgs_ctx *c, int32_t n_nodes, int32_t dmax,
         CU(cudaEventSynchronize(c->ev_snap));
     }
     c->have_snapshot = false;
+    c->snap_bigmem = false; // every row is prepared again below
     c->scored = c->resolved = false;
     const size_t cells = (size_t)n_nodes * dmax;
     CU(cudaMemsetAsync(c->d_status, 0, 2 * sizeof(uint32_t), c->st));
@@ -394,7 +403,7 @@ static int snapshot_common(vgs_ctx *c, int32_t n_nodes, int32_t dmax,
     if (cells) {
         // pinned, 16-byte aligned host planes are read by a kernel straight over PCIe (faster
         // than the copy engine for this size); anything else goes through cudaMemcpyAsync
-        bool zero_copy = kind == cudaMemcpyHostToDevice && c->zero_copy_ok;
+        bool zero_copy = kind == cudaMemcpyHostToDevice && c->tune.zero_copy_upload != 0;
         for (int f = 0; f <= VGS_NUM_PLANES && zero_copy; f++) {
             const void *p = f < VGS_NUM_PLANES ? (const void *)planes[f] : (const void *)ndev;
             cudaPointerAttributes at;
@@ -580,8 +589,8 @@ static bool build_slice_class(vgs_ctx *c, int k, const DevReq *req, const DevReq
     // >= slice_min pods: always.  From slice_small pods upward when the pass is big enough for the
     // class set-up (tables, K1p) to pay: measured 100k nodes x 256 pods 0.224 -> 0.176 ms through the
     // node-sliced kernel, but 100k x 64 and 10k x 256 lose to the per-pair kernel.
-    const bool big = n >= c->slice_min;
-    const bool mid = n >= c->slice_small && (int64_t)n * c->n_nodes >= c->slice_small_pairs;
+    const bool big = n >= c->tune.slice_min;
+    const bool mid = n >= c->tune.slice_small && (int64_t)n * c->n_nodes >= c->tune.slice_small_pairs;
     if (n < 1 || !(big || mid)) return false;
     std::vector<int32_t> mv, pv, cv; // sorted distinct thresholds (few in practice)
     auto add = [](std::vector<int32_t> &v, int32_t x) {
@@ -816,19 +825,25 @@ static int score_locked(vgs_ctx *c) {
     }
     // The Nums 2 chain is issued first: it is the longer one on the mixes measured (pair enumeration in its
     // scouts), and whichever chain is issued first gets the SMs first (cfg3, alternating runs on one box:
-    // 0.4123 ms with class A first, 0.4083 ms with class B first).  VGS_ORDER=0 issues class A first.
-    static int order_env = -1;
-    if (order_env < 0) order_env = getenv("VGS_ORDER") ? atoi(getenv("VGS_ORDER")) : 1;
+    // 0.4123 ms with class A first, 0.4083 ms with class B first).  vgs_tuning.class_order = 0 issues class A first.
+    const int order_env = c->tune.class_order != 0 ? 1 : 0;
+    {
+        const int32_t df = c->plan.dict_full;
+        memset(&c->plan, 0, sizeof c->plan);
+        c->plan.dict_full = df;
+        c->plan.cls[0].pods = c->nA, c->plan.cls[1].pods = c->nB, c->plan.cls[2].pods = c->nC, c->plan.cls[3].pods = c->nG;
+    }
     for (int turn = 0; turn < 2; turn++) {
     const bool doA = (turn == 0) != (order_env == 1);
     if (doA) {
     if (c->nA) {
         if (sliced && c->slice_on[0]) {
-            int nl = 0;
-            CU(launch_score_sliced(1, c->cfg.device, a, c->tab[0], c->n_types_used, c->d_status, sA, &nl,
-                                   fork ? c->st : nullptr, c->ev_ns[0]));
-            c->launches += nl;
+            c->plan.cls[0].kernel = VGS_KERNEL_SLICED;
+            CU(launch_score_sliced(1, c->cfg.device, a, c->tab[0], c->n_types_used, c->d_status, sA, c->tune,
+                                   &c->plan.cls[0], fork ? c->st : nullptr, c->ev_ns[0]));
+            c->launches += c->plan.cls[0].launches;
         } else {
+            c->plan.cls[0].kernel = VGS_KERNEL_PAIR, c->plan.cls[0].launches = c->n_tiles ? 1 : 0;
             CU(launch_score_single(c->dm, true, c->cfg.device, a,
                                    reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqsA),
                                    reinterpret_cast<const int32_t *>(c->d_stage + c->off_origA), c->nA, sA));
@@ -838,11 +853,12 @@ static int score_locked(vgs_ctx *c) {
     } else {
     if (c->nB) {
         if (sliced && c->slice_on[1]) {
-            int nl = 0;
-            CU(launch_score_sliced(2, c->cfg.device, a, c->tab[1], c->n_types_used, c->d_status, sB, &nl,
-                                   fork ? c->st : nullptr, c->ev_ns[1]));
-            c->launches += nl;
+            c->plan.cls[1].kernel = VGS_KERNEL_SLICED;
+            CU(launch_score_sliced(2, c->cfg.device, a, c->tab[1], c->n_types_used, c->d_status, sB, c->tune,
+                                   &c->plan.cls[1], fork ? c->st : nullptr, c->ev_ns[1]));
+            c->launches += c->plan.cls[1].launches;
         } else {
+            c->plan.cls[1].kernel = VGS_KERNEL_PAIR, c->plan.cls[1].launches = c->n_tiles ? 1 : 0;
             CU(launch_score_single(c->dm, false, c->cfg.device, a,
                                    reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqsB),
                                    reinterpret_cast<const int32_t *>(c->d_stage + c->off_origB), c->nB, sB));
@@ -855,11 +871,13 @@ static int score_locked(vgs_ctx *c) {
         CU(launch_score_single(c->dm, false, c->cfg.device, a,
                                reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqsC),
                                reinterpret_cast<const int32_t *>(c->d_stage + c->off_origC), c->nC, c->st));
+        c->plan.cls[2].kernel = VGS_KERNEL_PAIR, c->plan.cls[2].launches = c->n_tiles ? 1 : 0;
         if (c->n_tiles) c->launches++;
     }
     if (c->nG) {
         CU(launch_score_general(c->dm, c->cfg.device, a, dreq,
                                 reinterpret_cast<const GenPod *>(c->d_stage + c->off_podsG), c->nG, c->st));
+        c->plan.cls[3].kernel = VGS_KERNEL_GENERAL, c->plan.cls[3].launches = c->n_tiles ? 1 : 0;
         if (c->n_tiles) c->launches++;
     }
     for (int k = 0; k < 2 && fork; k++) { // join
@@ -907,6 +925,7 @@ static int download_locked(vgs_ctx *c, vgs_result *results, vgs_pick *picks) {
     rec(c, EV_DH1);
     CU(cudaStreamSynchronize(c->st));
     c->stage_in_flight = false;
+    if (*c->h_status & S_DICTFULL) c->plan.dict_full = 1;
     int rc = check_status(c);
     if (rc != VGS_OK) {
         cudaMemsetAsync(c->d_status, 0, sizeof(uint32_t), c->st);
@@ -1095,6 +1114,29 @@ int vgs_verify_download(vgs_ctx *c, uint32_t *fit_bitmap, float *scores) {
         CU(cudaMemcpyAsync(scores, c->d_vscore, (size_t)c->n_pods * c->n_nodes * sizeof(float),
                            cudaMemcpyDeviceToHost, c->st));
     CU(cudaStreamSynchronize(c->st));
+    return VGS_OK;
+}
+
+void vgs_tuning_defaults(vgs_tuning *t) {
+    if (!t) return;
+    memset(t, 0, sizeof *t);
+    t->slice_min = 512;
+    t->slice_small = 64;
+    t->slice_small_pairs = 16000000;
+    t->node_words = -1;
+    t->tables_in_smem = -1;
+    t->tables_smem_kb = 48;
+    t->scout_stride = 0;
+    t->scout_split = 2;
+    t->class_order = 1;
+    t->zero_copy_upload = 1;
+    t->general_legacy = 0;
+}
+
+int vgs_last_plan(vgs_ctx *c, vgs_plan *out) {
+    if (!c || !out) return VGS_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    *out = c->plan;
     return VGS_OK;
 }
 

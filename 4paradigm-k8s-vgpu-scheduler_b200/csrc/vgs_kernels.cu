@@ -28,63 +28,11 @@
 #include <vector>
 
 #include "../../include/vgpuscore.h"
+#include "vgs_device.cuh"
 #include "vgs_kernels.h"
 #include "vgs_layout.h"
 
 namespace vgs {
-
-// ------------------------------------------------------------------------------------
-// small helpers
-// ------------------------------------------------------------------------------------
-__device__ __forceinline__ int32_t wrap_sub(int32_t a, int32_t b) {
-    return (int32_t)((uint32_t)a - (uint32_t)b);
-}
-__device__ __forceinline__ int32_t wrap_add(int32_t a, int32_t b) {
-    return (int32_t)((uint32_t)a + (uint32_t)b);
-}
-// Go: Totalmem * MemPercentagereq / 100 in int32 (score.go:119): wrapping multiply,
-// then division truncating toward zero.
-__device__ __forceinline__ int32_t pct_mem(int32_t totalmem, int32_t pct) {
-    return (int32_t)((uint32_t)totalmem * (uint32_t)pct) / 100;
-}
-// score.go:180  float32(total)/float32(free) + float32(len(node.Devices)-sums)
-__device__ __forceinline__ float container_score(int32_t total, int32_t free_, int32_t rest) {
-    return __fadd_rn(__fdiv_rn(__int2float_rn(total), __int2float_rn(free_)),
-                     __int2float_rn(rest));
-}
-__device__ __forceinline__ bool type_ok(uint32_t lo, uint32_t hi, uint32_t meta) {
-    uint32_t t = meta & M_TYPE_MASK;
-    uint32_t w = (t & 32u) ? hi : lo;
-    return (w >> (t & 31u)) & 1u;
-}
-
-__device__ __forceinline__ DevReq load_req(const DevReq *__restrict__ p) {
-    const int4 *q = reinterpret_cast<const int4 *>(p);
-    int4 a = __ldg(q), b = __ldg(q + 1);
-    DevReq r;
-    r.nums = a.x;
-    r.memfix = a.y;
-    r.pct = a.z;
-    r.coresreq = a.w;
-    r.blockmask = (uint32_t)b.x;
-    r.flags = (uint32_t)b.y;
-    r.mask_lo = (uint32_t)b.z;
-    r.mask_hi = (uint32_t)b.w;
-    return r;
-}
-
-template <int DM>
-__device__ __forceinline__ void load_word(const int4 *__restrict__ tile, int word, int lane,
-                                          int32_t (&dst)[DM]) {
-#pragma unroll
-    for (int q = 0; q < DM / 4; q++) {
-        int4 x = __ldg(&tile[(word * (DM / 4) + q) * kWarp + lane]);
-        dst[4 * q + 0] = x.x;
-        dst[4 * q + 1] = x.y;
-        dst[4 * q + 2] = x.z;
-        dst[4 * q + 3] = x.w;
-    }
-}
 
 // ------------------------------------------------------------------------------------
 // K0: prepare the walk-ordered copy.  One thread per node.
@@ -215,55 +163,6 @@ __global__ void __launch_bounds__(128)
     }
     if (row >= n_tiles * kWarp) return;
     prepare_node<DM>(raw, row, n_nodes, dmax, walk, status);
-}
-
-// ------------------------------------------------------------------------------------
-// warp-level publication of one pod's candidates: lane k keeps the result of the k-th
-// pod of a group of 32 so that the flush is one coalesced atomic per 32 pods.
-// ------------------------------------------------------------------------------------
-__device__ __forceinline__ void publish(bool fit, float score, int k, int lane, uint32_t row0,
-                                        unsigned long long &mykey, int32_t &mycnt) {
-    unsigned bal = __ballot_sync(0xffffffffu, fit);
-    if (bal) {
-        uint32_t sb = fit ? order_bits(__float_as_uint(score)) : 0u;
-        uint32_t m = __reduce_max_sync(0xffffffffu, sb);
-        unsigned who = __ballot_sync(0xffffffffu, sb == m);
-        uint32_t hl = 31u - (uint32_t)__clz((int)who); // ties -> highest row
-        if (lane == k) {
-            mykey = ((unsigned long long)m << 32) | (unsigned long long)(row0 + hl);
-            mycnt = __popc(bal);
-        }
-    }
-}
-
-// Small batches (one pod chunk of <= 32 pods, e.g. the single pod of a Filter call): every warp
-// of every item would hit the same few keys[] words with atomics -- 31250 same-address pairs at
-// 1M nodes.  Instead lane k keeps pod k's candidate across all the CTA's items and the CTA
-// publishes once.
-template <int WARPS>
-__device__ __forceinline__ void flush_small(unsigned long long acckey, int32_t acccnt, int lane, int warp,
-                                            int n_pods, const int32_t *__restrict__ orig_or_null,
-                                            const GenPod *__restrict__ pods_or_null,
-                                            unsigned long long *__restrict__ keys, int32_t *__restrict__ counts) {
-    __shared__ unsigned long long s_k[WARPS][kWarp];
-    __shared__ int32_t s_c[WARPS][kWarp];
-    s_k[warp][lane] = acckey;
-    s_c[warp][lane] = acccnt;
-    __syncthreads();
-    if (warp == 0 && lane < n_pods) {
-        unsigned long long kk = 0ull;
-        int32_t cc = 0;
-        const int nw = (int)(blockDim.x >> 5); // <= WARPS: small snapshots run fewer warps per CTA
-        for (int w = 0; w < nw; w++) {
-            kk = s_k[w][lane] > kk ? s_k[w][lane] : kk;
-            cc += s_c[w][lane];
-        }
-        if (kk != 0ull) {
-            const int op = orig_or_null ? orig_or_null[lane] : pods_or_null[lane].orig;
-            atomicMax(&keys[op], kk);
-            atomicAdd(&counts[op], cc);
-        }
-    }
 }
 
 // ------------------------------------------------------------------------------------
@@ -966,7 +865,7 @@ __global__ void __launch_bounds__(128)
     // below[k][t]: my pods whose best is < vals[k] (may over-approximate, never under); row kDict = all ones
     uint32_t *below = reinterpret_cast<uint32_t *>(smem_raw + L.below);
     uint32_t *s_best = reinterpret_cast<uint32_t *>(smem_raw + L.best); // [32][T] raw score bits, 0 = none
-    uint16_t *s_row = reinterpret_cast<uint16_t *>(smem_raw + L.row);   // [32][T] row - first row of this CTA
+    uint16_t *s_row = reinterpret_cast<uint16_t *>(smem_raw + L.row);   // [32][T] (virtual tile - t_lo) * 32 + lane: < 8192 by the counter cap
     const uint32_t *tabs = reinterpret_cast<const uint32_t *>(smem_raw + L.tab);
 
     const int w = blockIdx.y * T + tid;
@@ -994,7 +893,6 @@ __global__ void __launch_bounds__(128)
     const int t_lo = max(0, t_hi - tiles_per_cta);
     if (t_hi <= 0) return;
     const int n_my = t_hi - t_lo;
-    const int node_lo = tile_of(t_lo) * kWarp;
     const int node_hi = (tile_of(t_hi - 1) + 1) * kWarp;
     constexpr uint32_t kTx = kDevTileBytes + (NUMS == 2 ? kPclsTileBytes : 0);
     constexpr uint16_t kNotMine = 0xffffu; // s_row of a pod whose best was inherited, not found here
@@ -1087,13 +985,13 @@ __global__ void __launch_bounds__(128)
     };
     // pods in `word` get candidate (sb, node); nodes only ever decrease, so equal scores keep
     // the earlier (higher) row.  A pod whose best reaches sb leaves every below[k] with vals[k] <= sb.
-    auto raise = [&](uint32_t word, uint32_t sb, int node) {
+    auto raise = [&](uint32_t word, uint32_t sb, int vrow) { // vrow: the node's position among this CTA's virtual tiles
         uint32_t imp = 0u;
         for (uint32_t m = word; m; m &= m - 1) {
             const int b = __ffs((int)m) - 1;
             if (sb > s_best[b * T + tid]) {
                 s_best[b * T + tid] = sb;
-                s_row[b * T + tid] = (uint16_t)(node - node_lo);
+                s_row[b * T + tid] = (uint16_t)vrow;
                 imp |= 1u << b;
             }
         }
@@ -1112,6 +1010,7 @@ __global__ void __launch_bounds__(128)
 
     for (int it = 0; it < n_my; it++) {
         const int tile = tile_of(t_hi - 1 - it), buf = it & 1;
+        const int vbase = (n_my - 1 - it) * kWarp; // 16-bit row of the tile's first node (s_row): independent of the scout stride
         if (tid == 0 && it + 1 < n_my) fetch(tile_of(t_hi - 2 - it), buf ^ 1); // released by the last sync
         mbar_wait(&bar[buf], (uint32_t)((it >> 1) & 1));
         const uint4 *dv = reinterpret_cast<const uint4 *>(tilebuf + buf * kDevTileBytes); // [32 nodes][8]
@@ -1150,7 +1049,7 @@ __global__ void __launch_bounds__(128)
                             const uint4 d = dv[l * 8 + j];
                             if (VERIFY && active) mark(nw[u][j], node, d.z);
                             const uint32_t h = nw[u][j] & BELOW(d.w);
-                            if (h) raise(h, d.z, node);
+                            if (h) raise(h, d.z, vbase + l);
                         }
                     }
                 }
@@ -1200,7 +1099,7 @@ __global__ void __launch_bounds__(128)
                                     (int32_t)(da.w >> 24) - 2));
                                 if (VERIFY && active) mark(wab, node, sb);
                                 const uint32_t h = wab & BELOW((uint32_t)pc[l * 32 + pair_index(a, b)]);
-                                if (h) raise(h, sb, node);
+                                if (h) raise(h, sb, vbase + l);
                             }
                         }
                     }
@@ -1245,7 +1144,7 @@ __global__ void __launch_bounds__(128)
         if (r == kNotMine) continue; // nothing here beat the inherited best
         // scores of single-request pods are positive: ordered bits = bits | sign bit
         const unsigned long long key = ((unsigned long long)(s_best[b * T + tid] | 0x80000000u) << 32) |
-                                       (unsigned long long)(uint32_t)(row_base + node_lo + (int)r);
+                                       (unsigned long long)(uint32_t)(row_base + tile_of(t_lo + (int)(r >> 5)) * kWarp + (int)(r & 31u));
         atomicMax(&keys[p], key);
     }
 }
@@ -1771,9 +1670,32 @@ cudaError_t launch_score_general(int dm, int dev, const ScoreArgs &a, const DevR
 }
 
 
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) once per (kernel, device), to the opt-in limit: the
+// attribute never has to follow the batch, and two contexts on one GPU cannot lower it under each other
+template <typename K>
+static cudaError_t allow_big_smem(K kernel, int dev) {
+    struct Entry {
+        const void *k;
+        int dev;
+    };
+    static std::mutex mu;
+    static std::vector<Entry> done;
+    const void *kp = reinterpret_cast<const void *>(kernel);
+    std::lock_guard<std::mutex> lk(mu);
+    for (const Entry &e : done)
+        if (e.k == kp && e.dev == dev) return cudaSuccess;
+    int optin = 0;
+    cudaError_t e = cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+    if (e != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, optin)) != cudaSuccess) return e;
+    done.push_back(Entry{kp, dev});
+    return cudaSuccess;
+}
+
 template <int NUMS>
 static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &tb_in, int n_types, uint32_t *status,
-                                   cudaStream_t st, int *n_launched, cudaStream_t st_ns, cudaEvent_t ev_ns) {
+                                   cudaStream_t st, const vgs_tuning &tune, vgs_class_plan *plan, cudaStream_t st_ns,
+                                   cudaEvent_t ev_ns) {
     const int sms = sm_count(dev);
     cudaError_t e;
     SliceTab tb = tb_in;
@@ -1782,18 +1704,13 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
     // a node-sliced word costs ~1 per (pod, node).  So a few words beyond a multiple of 32 (or a class of
     // few words) go to the node-sliced kernel, the rest to pod-sliced warps.
     // Measured at 100k nodes: ~9 us per node-sliced word; a whole pod-sliced chain (sort, classify, scouts,
-    // main) ~200 us, one more warp in an existing chain ~50 us.  VGS_NODE_WORDS overrides both limits.
-    static int node_words_env = -2;
-    if (node_words_env == -2) {
-        const char *ev = getenv("VGS_NODE_WORDS");
-        node_words_env = ev ? atoi(ev) : -1;
-    }
+    // main) ~200 us, one more warp in an existing chain ~50 us.  vgs_tuning.node_words overrides both limits.
     const int W_all = tb.W, n_pods_all = tb.n_pods;
     // a class of its own (< 32 words): chain ~ (155 + 44 n) us against ~6.2 n us per node-sliced word,
     // n = nodes / 100k (measured at 100k and 400k nodes) -> break-even 7 + 25 / n words
     int small_limit = 7 + (int)(2500000ll / (a.n_nodes > 0 ? a.n_nodes : 1));
     if (small_limit > 24) small_limit = 24;
-    const int node_words_max = node_words_env >= 0 ? node_words_env : (W_all < 32 ? small_limit : 6);
+    const int node_words_max = tune.node_words >= 0 ? tune.node_words : (W_all < 32 ? small_limit : 6);
     int ns_words = W_all % 32;
     if (ns_words > node_words_max) ns_words = 0;
     const int W_main = W_all - ns_words;
@@ -1807,19 +1724,15 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
     if (n_types < 1) n_types = 1;
     if (n_types > VGS_MAX_TYPES) n_types = VGS_MAX_TYPES;
     const int rows_s = n_types + (tb.km + 1) + (tb.kp + 1) + 4 * (tb.kc + 1);
-    static int force_tab = -2;
-    if (force_tab == -2) {
-        const char *ev = getenv("VGS_SLICE_TABSMEM");
-        force_tab = ev ? atoi(ev) : -1;
-    }
-    // tables in shared memory up to 48 KB per CTA (else global / L1)
-    static int tab_kb = -1;
-    if (tab_kb < 0) {
-        const char *ev = getenv("VGS_SLICE_TABSMEM_KB");
-        tab_kb = ev ? atoi(ev) : 48; // measured on cfg3: 8 KB 0.498 ms, 16-24 KB 0.472, 32-64 KB 0.461
-    }
-    const bool tabsmem = force_tab >= 0 ? force_tab != 0 : (size_t)rows_s * T * 4 <= (size_t)tab_kb * 1024;
+    // tables in shared memory up to tables_smem_kb per CTA (else global / L1); measured on cfg3:
+    // 8 KB 0.498 ms, 16-24 KB 0.472, 32-64 KB 0.461
+    const int tab_kb = tune.tables_smem_kb > 0 ? tune.tables_smem_kb : 48;
+    bool tabsmem = tune.tables_in_smem >= 0 ? tune.tables_in_smem != 0 : (size_t)rows_s * T * 4 <= (size_t)tab_kb * 1024;
+    if (slice_smem(T, NUMS, rows_s).total > 200 * 1024) tabsmem = false; // forced on, but it cannot fit
     tb.row_shift = tabsmem ? VGS_MAX_TYPES - n_types : 0;
+    plan->words_pod_sliced = W_main;
+    plan->words_node_sliced = ns_words;
+    plan->tables_in_smem = W_main > 0 ? (tabsmem ? 1 : 0) : 0;
 
     // K1p: table rows + candidate scores per device, distinct scores -> classes
     const int nthreads = a.n_tiles * kWarp;
@@ -1834,40 +1747,33 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
         }
         k1p_sort<<<1, 1024, 0, st>>>(tb);
         k1p_classify<NUMS><<<(nthreads + 127) / 128, 128, 0, st>>>(a.n_tiles, tb);
-        *n_launched += 3;
+        plan->launches += 3;
     } else { // a class of a few words: the node-sliced kernel needs the records only
         k1p_collect<NUMS><<<(nthreads + 127) / 128, 128, 0, st>>>(a.walk, a.n_tiles, tb, status, false);
-        *n_launched += 1;
+        plan->launches += 1;
     }
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
 
     // every scout-th tile is walked by the scout launch: about a hundred scout tiles (measured
-    // optimum on 100k nodes: stride 24-48), VGS_SCOUT overrides
-    static int scout_env = -1;
-    if (scout_env < 0) {
-        const char *ev = getenv("VGS_SCOUT");
-        scout_env = ev ? atoi(ev) : 0;
-    }
-    int scout = scout_env >= 2 ? scout_env : a.n_tiles / 96;
-    if (scout < 4) scout = 4;
-    if (scout > 32 && scout_env < 2) scout = 32;
-    static int scout_sub_max = -1;
-    if (scout_sub_max < 0) {
-        const char *ev = getenv("VGS_SCOUT_SUB");
-        scout_sub_max = ev ? atoi(ev) : 2; // cfg3: 1 -> 0.459 ms, 2 -> 0.449, 4 -> 0.472, 8 -> 0.477 (set-up per CTA)
-        if (scout_sub_max != 1 && scout_sub_max != 2 && scout_sub_max != 4 && scout_sub_max != 8) scout_sub_max = 2;
-    }
+    // optimum on 100k nodes: stride 24-48), vgs_tuning.scout_stride overrides
+    int scout = tune.scout_stride >= 2 ? tune.scout_stride : a.n_tiles / 96;
+    if (scout < 4 && tune.scout_stride < 2) scout = 4;
+    if (scout > 32 && tune.scout_stride < 2) scout = 32;
+    // cfg3: 1 -> 0.459 ms, 2 -> 0.449, 4 -> 0.472, 8 -> 0.477 (set-up per CTA)
+    int scout_sub_max = tune.scout_split;
+    if (scout_sub_max != 1 && scout_sub_max != 2 && scout_sub_max != 4 && scout_sub_max != 8) scout_sub_max = 2;
     const int smem = slice_smem(T, NUMS, tabsmem ? rows_s : 0).total;
     auto go = [&](auto kernel) -> cudaError_t {
-        if ((e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)) != cudaSuccess) return e;
+        if ((e = allow_big_smem(kernel, dev)) != cudaSuccess) return e;
         int occ = 1;
-        if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, T, smem)) != cudaSuccess) return e;
+        if ((e = cached_occupancy(&occ, kernel, dev, T, smem)) != cudaSuccess) return e;
         if (occ < 1) occ = 1;
         // CTAs of one launch: one wave; at least 2 tiles each so the per-CTA set-up and flush stay
-        // small, at most (2^planes - 1) nodes (and a 16-bit row span) each
-        auto launch = [&](int n_virtual, int phase, int min_tiles) -> cudaError_t {
+        // small, at most (2^planes - 1) nodes each (the bit-sliced fit counter)
+        auto launch = [&](int n_virtual, int phase, int min_tiles, int32_t *tiles_out) -> cudaError_t {
             if (n_virtual <= 0) return cudaSuccess;
             long long want = (long long)sms * occ / gy;
+            if (tune.max_ctas > 0 && want > tune.max_ctas) want = tune.max_ctas;
             if (want < 1) want = 1;
             int tiles_per = (int)((n_virtual + want - 1) / want);
             if (tiles_per < min_tiles) tiles_per = min_tiles;
@@ -1878,15 +1784,18 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
             if (phase == 0)
                 while (sub < scout_sub_max && (long long)gx * sub * 2 <= want) sub *= 2;
             gx *= sub;
+            if (phase == 0) plan->scout_split = sub;
+            *tiles_out = tiles_per;
             kernel<<<dim3(gx, gy), T, smem, st>>>(a.n_tiles, a.n_nodes, a.row_base, tb, n_types, tiles_per, phase,
                                                   scout, sub, a.keys, a.counts, a.vfit, a.vscore, a.vwords);
-            *n_launched += 1;
+            plan->launches += 1;
             return cudaGetLastError();
         };
-        if (a.n_tiles < 256) return launch(a.n_tiles, -1, 2); // small snapshot (< 8k nodes): one launch
+        if (a.n_tiles < 256) return launch(a.n_tiles, -1, 2, &plan->tiles_per_cta_main); // small snapshot (< 8k nodes): one launch
         const int scouts = (a.n_tiles + scout - 1) / scout;
-        if ((e = launch(scouts, 0, 1)) != cudaSuccess) return e;
-        return launch(a.n_tiles - scouts, 1, 2);
+        plan->scout_stride = scout;
+        if ((e = launch(scouts, 0, 1, &plan->tiles_per_cta_scout)) != cudaSuccess) return e;
+        return launch(a.n_tiles - scouts, 1, 2, &plan->tiles_per_cta_main);
     };
     if (W_main > 0) {
         if (a.vfit) e = tabsmem ? go(k1_score_sliced<NUMS, true, true>) : go(k1_score_sliced<NUMS, false, true>);
@@ -1900,9 +1809,7 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
         const int rows_all = VGS_MAX_TYPES - tn.row_shift + (tn.km + 1) + (tn.kp + 1) + 4 * (tn.kc + 1);
         const int nsmem = rows_all * 4;
         auto gon = [&](auto kernel) -> cudaError_t {
-            if (nsmem > 48 * 1024 &&
-                (e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, nsmem)) != cudaSuccess)
-                return e;
+            if (nsmem > 48 * 1024 && (e = allow_big_smem(kernel, dev)) != cudaSuccess) return e;
             int occ = 1;
             if ((e = cached_occupancy(&occ, kernel, dev, 128, nsmem)) != cudaSuccess) return e;
             if (occ < 1) occ = 1;
@@ -1913,7 +1820,7 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
             cudaStream_t sn = (W_main > 0 && st_ns != st && ev_ns) ? st_ns : st;
             kernel<<<dim3((unsigned)gx, (unsigned)ns_words), 128, nsmem, sn>>>(a.n_tiles, a.n_nodes, a.row_base, tn, W_main,
                                                                              a.keys, a.counts, a.vfit, a.vscore, a.vwords);
-            *n_launched += 1;
+            plan->launches += 1;
             return cudaGetLastError();
         };
         e = a.vfit ? gon(k1_score_nodesliced<NUMS, true>) : gon(k1_score_nodesliced<NUMS, false>);
@@ -1923,13 +1830,13 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
 }
 
 cudaError_t launch_score_sliced(int nums, int dev, const ScoreArgs &a, const SliceTab &tb, int n_types,
-                                uint32_t *status, cudaStream_t st, int *n_launched, cudaStream_t st_ns,
-                                cudaEvent_t ev_ns) {
-    *n_launched = 0;
+                                uint32_t *status, cudaStream_t st, const vgs_tuning &tune, vgs_class_plan *plan,
+                                cudaStream_t st_ns, cudaEvent_t ev_ns) {
+    plan->launches = 0;
     if (tb.n_pods <= 0 || a.n_tiles <= 0) return cudaSuccess;
     if (!st_ns) st_ns = st;
-    return nums == 1 ? launch_sliced_t<1>(dev, a, tb, n_types, status, st, n_launched, st_ns, ev_ns)
-                     : launch_sliced_t<2>(dev, a, tb, n_types, status, st, n_launched, st_ns, ev_ns);
+    return nums == 1 ? launch_sliced_t<1>(dev, a, tb, n_types, status, st, tune, plan, st_ns, ev_ns)
+                     : launch_sliced_t<2>(dev, a, tb, n_types, status, st, tune, plan, st_ns, ev_ns);
 }
 
 // K2x: merge of whole exchange blocks.  Every shard has resolved its OWN best node per pod (K3 with

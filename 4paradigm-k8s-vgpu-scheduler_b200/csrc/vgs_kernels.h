@@ -46,9 +46,9 @@ cudaError_t launch_score_general(int dm, int dev, const ScoreArgs &a, const DevR
 cudaError_t launch_slice_tables(const SliceTab &tb, const DevReq *dreq_class, cudaStream_t st);
 // pod-sliced K1 for one class (all pods: one request, Nums == nums in {1,2}, walk DM == 8)
 // (K1p collect / sort / classify, then the score kernel as scouts + main pass, or one pass on a small
-// snapshot; *n_launched receives the number of kernels launched)
+// snapshot; *plan receives the split of the class's words, the launch geometry and the number of kernels launched)
 cudaError_t launch_score_sliced(int nums, int dev, const ScoreArgs &a, const SliceTab &tb, int n_types,
-                                uint32_t *status, cudaStream_t st, int *n_launched,
+                                uint32_t *status, cudaStream_t st, const vgs_tuning &tune, vgs_class_plan *plan,
                                 cudaStream_t st_ns = nullptr, cudaEvent_t ev_ns = nullptr);
 // (st_ns / ev_ns: optional second stream + event on which the node-sliced words of the class may run as soon
 // as K1p's records exist; the caller joins st_ns with whatever consumes the keys)

@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define VGS_ABI_VERSION 1
+#define VGS_ABI_VERSION 2
 
 /* Go 1.19 sort.Sort is a stable insertion sort only for n <= 12
  * (score.go:165); more devices per node would need pdqsort semantics. */
@@ -76,6 +76,29 @@ typedef enum {
 
 typedef struct vgs_ctx vgs_ctx;
 
+/* Tuning of the score path (no counterpart in the reference).  Every field has a default that
+ * vgs_tuning_defaults() writes; a context is configured once, at vgs_init, through
+ * vgs_config.tuning (NULL = all defaults).  The library reads no environment variable.
+ * None of these changes a result, only which kernel computes it. */
+typedef struct {
+    int32_t slice_min;        /* a single-request class (Nums 1 / Nums 2) runs on the pod-sliced kernels from this many pods (512) */
+    int32_t slice_small;      /* ... or from this many when pods x nodes >= slice_small_pairs (64) */
+    int64_t slice_small_pairs;/* (16000000) */
+    int32_t node_words;       /* pod words (32 pods) of a sliced class handed to the node-sliced kernel:
+                               * -1 = measured break-even (default), 0 = none, n = up to n words beyond a multiple of 32 */
+    int32_t tables_in_smem;   /* bit tables of the pod-sliced kernel in shared memory: -1 = when they fit
+                               * tables_smem_kb (default), 0 = never, 1 = always */
+    int32_t tables_smem_kb;   /* (48) */
+    int32_t scout_stride;     /* every scout_stride-th node tile is walked by the scout launch: 0 = auto (n_tiles / 96 in [4, 32]) */
+    int32_t scout_split;      /* CTAs sharing one scout tile: 1, 2, 4 or 8 (2) */
+    int32_t class_order;      /* 1 = issue the Nums 2 class chain first (default), 0 = the Nums 1 chain */
+    int32_t zero_copy_upload; /* 1 = pinned host planes are pulled over PCIe by a copy kernel (default), 0 = cudaMemcpyAsync */
+    int32_t general_legacy;   /* 1 = multi-request pods run on the round-1 all-pairs kernel (A/B and fallback testing), 0 = default */
+    int32_t max_ctas;         /* upper bound on the CTAs of one pod-sliced score launch (sharing the GPU, tests): 0 = one wave */
+    int32_t reserved[5];
+} vgs_tuning;
+void vgs_tuning_defaults(vgs_tuning *out);
+
 typedef struct {
     int32_t device;      /* CUDA ordinal */
     int32_t max_nodes;   /* rows this context can hold */
@@ -86,6 +109,7 @@ typedef struct {
     int32_t row_base;    /* global row index of local row 0 (node sharding) */
     int32_t verify;      /* !=0: also keep the full pod x node fit bitmap and scores */
     void *stream;        /* cudaStream_t to run on; NULL = library creates one */
+    const vgs_tuning *tuning; /* NULL = defaults; copied by vgs_init */
 } vgs_config;
 
 /* One container x vendor request = util.ContainerDeviceRequest
@@ -286,6 +310,28 @@ int vgs_score_batch_noalloc(int32_t device, void *stream, int32_t n_nodes, int32
 int vgs_verify_download(vgs_ctx *ctx, uint32_t *fit_bitmap, float *scores);
 
 int vgs_last_timing(vgs_ctx *ctx, vgs_timing *out);
+
+/* How the most recent vgs_score_resident / vgs_score_batch ran: which kernel family took each pod class
+ * and with what launch geometry (what vgs_tuning steers).  Classes: 0 = one request, Nums 1; 1 = one
+ * request, Nums 2; 2 = one request, Nums >= 3; 3 = everything else (several requests, numa-bind). */
+enum { VGS_KERNEL_NONE = 0, VGS_KERNEL_PAIR = 1, VGS_KERNEL_SLICED = 2, VGS_KERNEL_GENERAL = 3 };
+typedef struct {
+    int32_t pods;             /* pods of the class in the batch */
+    int32_t kernel;           /* VGS_KERNEL_* */
+    int32_t words_pod_sliced; /* pod words (32 pods) on the pod-sliced kernel */
+    int32_t words_node_sliced;/* pod words on the node-sliced kernel */
+    int32_t tables_in_smem;
+    int32_t scout_stride, scout_split;
+    int32_t tiles_per_cta_scout, tiles_per_cta_main;
+    int32_t launches;         /* kernels launched for the class */
+} vgs_class_plan;
+typedef struct {
+    vgs_class_plan cls[4];
+    int32_t dict_full;        /* a sliced class met more distinct candidate scores than its hash set holds since
+                               * vgs_init: results stay exact (such scores are compared one by one), pruning is lost */
+    int32_t reserved[3];
+} vgs_plan;
+int vgs_last_plan(vgs_ctx *ctx, vgs_plan *out);
 
 /* ---- host-side policy helpers (what the Go shim keeps in Go) ----------------
  * bit t = checkType pass for device type string types[t] under the pod's

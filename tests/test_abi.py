@@ -25,12 +25,13 @@ def test_exports(built):
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/vgpuscore.h but not exported"
     assert set(names) == set(v.capi.EXPORTS)
-    assert lib.vgs_abi_version() == 1
+    assert lib.vgs_abi_version() == 2
     assert lib.vgs_strerror(0) == b"ok"
 
 
 def test_struct_layouts(built):
-    assert ctypes.sizeof(v.capi.VgsConfig) == 40
+    assert ctypes.sizeof(v.capi.VgsConfig) == 48
+    assert ctypes.sizeof(v.capi.VgsTuning) == 72 and ctypes.sizeof(v.capi.VgsPlan) == 176
     assert ctypes.sizeof(v.capi.VgsTiming) == 32
     assert v.capi.REQ_DTYPE.itemsize == 32 and v.capi.REQ_DTYPE.fields["typemask"][1] == 24
     assert v.capi.DELTA_DTYPE.itemsize == 20

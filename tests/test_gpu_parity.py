@@ -10,6 +10,7 @@ from helpers import assert_same, cambricon_cluster, check_kat, kat_inputs, load_
 
 pytestmark = pytest.mark.gpu
 K = load_kats()
+FORCE_SLICED = {"slice_min": 1, "slice_small": 1}  # vgs_tuning: every Nums 1 / Nums 2 class on the sliced kernels
 
 
 def gpu_score(snap, batch, verify=True, **kw):
@@ -275,12 +276,14 @@ def test_sliced_default_threshold(built):
         assert_same(gpu_score(snap, batch), oracle.score_packed(snap, batch, full=True), f"sliced {cfg}")
 
 
-@pytest.mark.parametrize("node_words", ["10", "0", "31"])
-def test_sliced_word_split_between_kernels(built, monkeypatch, node_words):
+@pytest.mark.parametrize("node_words,tabsmem,scout", [(10, -1, 0), (0, 0, 5), (31, 1, 17), (-1, -1, 64)])
+def test_sliced_word_split_between_kernels(built, node_words, tabsmem, scout):
     """a class's pod words beyond a multiple of 32 go to the node-sliced kernel (lane = node), the rest to
-    pod-sliced warps (lane = pod word); VGS_NODE_WORDS moves the split.  Same answers wherever a word runs."""
-    monkeypatch.setenv("VGS_NODE_WORDS", node_words)
-    monkeypatch.setenv("VGS_SLICE_MIN", "64")
+    pod-sliced warps (lane = pod word); vgs_tuning.node_words moves the split, tables_in_smem / scout_stride
+    the pod-sliced kernel's variant and launch geometry.  Same answers wherever a word runs -- and
+    vgs_last_plan shows that the knobs really moved the split."""
+    tune = {"node_words": node_words, "slice_min": 64, "slice_small": 64, "tables_in_smem": tabsmem,
+            "scout_stride": scout, "scout_split": 4 if scout == 17 else 2}
     rng = np.random.default_rng(77)
     snap, _ = v.workload.make_config("cfg3", 9000, 1)
     def pods_of(n1, n2):
@@ -298,31 +301,74 @@ def test_sliced_word_split_between_kernels(built, monkeypatch, node_words):
     for n1, n2 in ((1040, 70), (1270, 1100), (200, 2048), (1024, 1024 + 5)):
         batch = pods_of(n1, n2)
         want = oracle.score_packed(snap, batch, full=True)
-        assert_same(gpu_score(snap, batch), want, f"verify {n1}+{n2} words={node_words}")
-        assert_same(gpu_score(snap, batch, verify=False), oracle.score_packed(snap, batch), f"{n1}+{n2} words={node_words}")
+        assert_same(gpu_score(snap, batch, tuning=tune), want, f"verify {n1}+{n2} words={node_words}")
+        with v.Context(max_nodes=snap.n_nodes, max_pods=batch.n_pods, tuning=tune) as ctx:
+            ctx.upload(snap)
+            assert_same(ctx.score(batch), oracle.score_packed(snap, batch), f"{n1}+{n2} words={node_words}")
+            plan = ctx.plan()
+        for k, n in ((0, n1), (1, n2)):
+            cp, W = plan.cls[k], (n + 31) // 32
+            assert cp.pods == n and cp.kernel == v.capi.KERNEL_SLICED, (k, cp.pods, cp.kernel)
+            assert cp.words_pod_sliced + cp.words_node_sliced == W
+            extra = W % 32
+            if node_words == 0:
+                assert cp.words_node_sliced == 0
+            elif node_words == 31:
+                assert cp.words_node_sliced == extra  # every word beyond a multiple of 32
+            elif node_words == 10:
+                assert cp.words_node_sliced == (extra if extra <= 10 else 0)
+            if cp.words_pod_sliced:
+                if tabsmem >= 0:
+                    assert cp.tables_in_smem == tabsmem
+                if scout >= 2:  # 9000 nodes = 282 tiles: scouts + main launch
+                    assert cp.scout_stride == scout and cp.tiles_per_cta_main >= 2
+                    assert cp.scout_split in (1, 2, 4)
+
+
+def test_sliced_long_scout_span_keeps_rows(built):
+    """a scout CTA whose tiles lie far apart (large stride x many tiles per CTA, forced by many pod-word
+    columns and a big stride) still names the right winner row: the per-pod row inside a CTA is kept as
+    (virtual tile, lane), not as a 16-bit node offset"""
+    snap, batch = v.workload.make_config("cfg3", 140_000, 1)
+    rng = np.random.default_rng(3)
+    pods = [{"containers": [[(int(rng.choice([1, 2])), int(rng.choice([1000, 3000, 9000])), 101, int(rng.choice([0, 10, 30])))]]}
+            for _ in range(2048)]
+    batch = v.PodBatch.from_pods(pods)
+    # 4375 tiles, stride 32 -> 137 scout tiles on 2 CTAs = 69 tiles each, 2177 tiles (69664 nodes) apart
+    tune = {"scout_stride": 32, "scout_split": 1, "slice_min": 64, "max_ctas": 2}
+    with v.Context(max_nodes=snap.n_nodes, max_pods=batch.n_pods, tuning=tune) as ctx:
+        ctx.upload(snap)
+        got = ctx.score(batch)
+        plan = ctx.plan()
+    idx = list(range(0, batch.n_pods, 97))
+    want = oracle.score_packed(snap, batch.select(idx))
+    assert np.array_equal(got.best_row[idx], want.best_row)
+    assert np.array_equal(got.score[idx].view(np.uint32), want.score.view(np.uint32))
+    assert np.array_equal(got.fit_count[idx], want.fit_count)
+    # the geometry this test is about: ((tiles_per - 1) * stride + 1) * 32 nodes per scout CTA
+    for cp in (plan.cls[0], plan.cls[1]):
+        assert cp.kernel == v.capi.KERNEL_SLICED and cp.scout_stride == 32
+        assert ((cp.tiles_per_cta_scout - 1) * cp.scout_stride + 1) * 32 > 65535
 
 
 @pytest.mark.parametrize("k", K["kats"], ids=[k["name"] for k in K["kats"]])
-def test_sliced_forced_kats(built, monkeypatch, k):
-    monkeypatch.setenv("VGS_SLICE_MIN", "1")
+def test_sliced_forced_kats(built, k):
     snap, batch = kat_inputs(k)
-    check_kat(k, gpu_score(snap, batch), batch)
+    check_kat(k, gpu_score(snap, batch, tuning=FORCE_SLICED), batch)
 
 
 @pytest.mark.parametrize("dmax,seed", [(8, 21), (8, 22), (7, 23), (4, 24), (1, 25), (2, 26)])
-def test_sliced_forced_random(built, monkeypatch, dmax, seed):
-    monkeypatch.setenv("VGS_SLICE_MIN", "1")
+def test_sliced_forced_random(built, dmax, seed):
     rng = np.random.default_rng(seed)
     snap = _random_snapshot(rng, 1000 + seed, dmax)
     batch = _random_pods(rng, 300, dmax, max_ctrs=1)  # single-container pods -> classes A/B/C
-    got = gpu_score(snap, batch)
+    got = gpu_score(snap, batch, tuning=FORCE_SLICED)
     assert_same(got, oracle.score_packed(snap, batch, full=True), f"sliced dmax={dmax}")
     assert_same(got, oracle.score_faithful(snap, batch, full=True), f"sliced dmax={dmax} R1")
 
 
-def test_sliced_many_distinct_thresholds(built, monkeypatch):
+def test_sliced_many_distinct_thresholds(built):
     """every pod its own Memreq / Coresreq value: long cumulative tables, binary search cut-offs"""
-    monkeypatch.setenv("VGS_SLICE_MIN", "1")
     rng = np.random.default_rng(5)
     snap, _ = v.workload.make_config("cfg3", 2000, 1)
     pods = [{"containers": [[(int(rng.choice([1, 2])), int(rng.integers(0, 40000)), 101, int(rng.integers(0, 101)))]]}
@@ -330,27 +376,33 @@ def test_sliced_many_distinct_thresholds(built, monkeypatch):
     pods += [{"containers": [[(int(rng.choice([1, 2])), 0, int(rng.integers(0, 101)), int(rng.integers(0, 101)))]]}
              for _ in range(300)]
     batch = v.PodBatch.from_pods(pods)
-    assert_same(gpu_score(snap, batch), oracle.score_packed(snap, batch, full=True), "distinct")
+    assert_same(gpu_score(snap, batch, tuning=FORCE_SLICED), oracle.score_packed(snap, batch, full=True), "distinct")
 
 
-def test_sliced_falls_back_when_preconditions_fail(built, monkeypatch):
+def test_sliced_falls_back_when_preconditions_fail(built):
     """Totalmem * pct wrapping int32 (score.go:119) and pct outside [0,100] are only handled by
     the per-pair kernels: the library must route there and still match the oracle"""
-    monkeypatch.setenv("VGS_SLICE_MIN", "1")
     snap, batch = v.workload.make_config("cfg3", 1500, 600)
     big = snap.planes.copy()
     big[3] = 30_000_000       # * 100 wraps int32
     big[2] = big[2] * 900
     wrapped = v.Snapshot(big, snap.ndev, snap.type_names)
-    assert_same(gpu_score(wrapped, batch), oracle.score_packed(wrapped, batch, full=True), "bigmem")
+    assert_same(gpu_score(wrapped, batch, tuning=FORCE_SLICED), oracle.score_packed(wrapped, batch, full=True), "bigmem")
     odd = v.PodBatch.from_pods([{"containers": [[(1, 0, pct, 0)]]} for pct in (150, -5, 100, 0, 250)] * 20)
-    assert_same(gpu_score(snap, odd), oracle.score_packed(snap, odd, full=True), "odd pct")
+    assert_same(gpu_score(snap, odd, tuning=FORCE_SLICED), oracle.score_packed(snap, odd, full=True), "odd pct")
     # and the same context flips back to the sliced path when a normal snapshot returns
-    with v.Context(max_nodes=1500, max_pods=600, verify=True) as ctx:
+    with v.Context(max_nodes=1500, max_pods=600, verify=True, tuning=FORCE_SLICED) as ctx:
         ctx.upload(wrapped)
         a = ctx.score(batch)
+        assert ctx.plan().cls[0].kernel == v.capi.KERNEL_PAIR
+        # a usage delta re-prepares one row only: the snapshot must stay off the sliced kernels
+        ctx.delta(np.array([(7, 0, 0, 0, 0)], dtype=v.capi.DELTA_DTYPE))
+        a2 = ctx.score(batch)
+        assert ctx.plan().cls[0].kernel == v.capi.KERNEL_PAIR
+        assert_same(a2, a, "bigmem stays sticky across a delta")
         ctx.upload(snap)
         b = ctx.score(batch)
+        assert ctx.plan().cls[0].kernel == v.capi.KERNEL_SLICED
     assert_same(a, oracle.score_packed(wrapped, batch, full=True), "ctx bigmem")
     assert_same(b, oracle.score_packed(snap, batch, full=True), "ctx normal")
 
@@ -511,7 +563,7 @@ def test_candidate_block_is_clean_between_passes(built):
         assert (got.best_row == -1).all() and not got.picks.any()
 
 
-def test_pinned_planes_take_the_zero_copy_upload(built, monkeypatch):
+def test_pinned_planes_take_the_zero_copy_upload(built):
     """pinned, aligned host planes are pulled over PCIe by a kernel; pageable ones by cudaMemcpy:
     same resident snapshot either way"""
     import torch
@@ -524,8 +576,7 @@ def test_pinned_planes_take_the_zero_copy_upload(built, monkeypatch):
         planes, ndev = ctx.download_snapshot()
         assert np.array_equal(planes, snap.planes) and np.array_equal(ndev, snap.ndev)
         assert_same(ctx.score(batch), oracle.score_packed(snap, batch), "pinned upload")
-    monkeypatch.setenv("VGS_ZERO_COPY", "0")
-    with v.Context(max_nodes=3001, max_pods=64) as ctx:
+    with v.Context(max_nodes=3001, max_pods=64, tuning={"zero_copy_upload": 0}) as ctx:
         ctx.upload_ptrs(snap.n_nodes, snap.dmax, [pin[f].data_ptr() for f in range(8)], pnd.data_ptr(), device=False)
         planes, _ = ctx.download_snapshot()
         assert np.array_equal(planes, snap.planes)
