@@ -76,6 +76,7 @@ struct vgs_ctx {
     size_t off_reqsC = 0, off_origC = 0;
     size_t off_genall = 0; // GenPod of EVERY pod, batch order (drain: one pod at a time)
     int32_t n_pods = 0, n_reqs = 0, nA = 0, nB = 0, nC = 0, nG = 0, n_picks = 0;
+    int32_t nGL = 0; // of the nG general pods, those on the all-pairs kernel (stored from the END of the podsG region)
     // pod-sliced classes (A: Nums == 1, B: Nums == 2): bit tables, see SliceTab
     uint32_t *h_slice[2] = {}, *d_slice[2] = {};
     unsigned char *d_prep[2] = {}; // K1p products: SliceDev tiles, pair classes, score set, classes
@@ -704,7 +705,7 @@ static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, i
     }
     hpick[n_reqs] = (int32_t)picks;
 
-    int32_t nA = 0, nB = 0, nC = 0, nG = 0;
+    int32_t nA = 0, nB = 0, nC = 0, nG = 0, nGL = 0;
     for (int32_t p = 0; p < n_pods; p++) {
         const vgs_pod &pd = pods[p];
         if (pd.n_reqs < 1 || pd.n_reqs > VGS_MAX_REQS_PER_POD || pd.req_begin < 0 ||
@@ -720,7 +721,9 @@ static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, i
         }
         hpod[p] = pd;
         GenPod *hall = reinterpret_cast<GenPod *>(c->h_stage + c->off_genall);
-        hall[p].req_begin = pd.req_begin, hall[p].n_reqs = pd.n_reqs, hall[p].orig = p, hall[p].pad = 0;
+        hall[p].req_begin = pd.req_begin, hall[p].n_reqs = pd.n_reqs, hall[p].orig = p;
+        hall[p].flags = gen_pod_flags(&hreq[pd.req_begin], pd.n_reqs);
+        if (c->tune.general_legacy) hall[p].flags |= G_LEGACY;
         const DevReq &first = hreq[pd.req_begin];
         // the bit tables of the sliced classes know nothing of M_BUSY370: idle-share requests
         // take the per-pair kernel, which tests the whole blockmask
@@ -734,11 +737,9 @@ static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, i
         } else if (pd.n_reqs == 1 && (!(first.flags & R_NUMA) || first.nums == 1)) {
             hC[nC] = first;
             hoC[nC++] = p;
-        } else {
-            hG[nG].req_begin = pd.req_begin;
-            hG[nG].n_reqs = pd.n_reqs;
-            hG[nG].orig = p;
-            hG[nG].pad = 0;
+        } else { // walk-kernel pods from the front of the region, all-pairs pods from its end
+            GenPod &g = (hall[p].flags & G_LEGACY) ? hG[n_pods - 1 - nGL++] : hG[nG - nGL];
+            g = hall[p];
             nG++;
         }
     }
@@ -750,6 +751,7 @@ static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, i
     c->nB = nB;
     c->nC = nC;
     c->nG = nG;
+    c->nGL = nGL;
     c->n_picks = (int32_t)picks;
     // everything above was host work that overlaps an asynchronous snapshot upload; the class set-up
     // below wants to know what the snapshot allows (sliced kernels, type rows)
@@ -875,10 +877,13 @@ static int score_locked(vgs_ctx *c) {
         if (c->n_tiles) c->launches++;
     }
     if (c->nG) {
-        CU(launch_score_general(c->dm, c->cfg.device, a, dreq,
-                                reinterpret_cast<const GenPod *>(c->d_stage + c->off_podsG), c->nG, c->st));
-        c->plan.cls[3].kernel = VGS_KERNEL_GENERAL, c->plan.cls[3].launches = c->n_tiles ? 1 : 0;
-        if (c->n_tiles) c->launches++;
+        const GenPod *gp = reinterpret_cast<const GenPod *>(c->d_stage + c->off_podsG);
+        const int32_t n_walk = c->nG - c->nGL;
+        CU(launch_score_walk(c->dm, c->cfg.device, a, dreq, gp, n_walk, c->st));
+        CU(launch_score_general(c->dm, c->cfg.device, a, dreq, gp + c->n_pods - c->nGL, c->nGL, c->st));
+        c->plan.cls[3].kernel = VGS_KERNEL_GENERAL;
+        c->plan.cls[3].launches = c->n_tiles ? (n_walk > 0) + (c->nGL > 0) : 0;
+        c->launches += c->plan.cls[3].launches;
     }
     for (int k = 0; k < 2 && fork; k++) { // join
         CU(cudaEventRecord(c->ev_join[k], c->side[k]));
@@ -1004,7 +1009,10 @@ int vgs_drain_batch(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_r
     // one pod at a time, everything chained on the stream: score (the key/count slot of pod p is
     // addressed through GenPod.orig) -> resolve + commit into the raw planes + re-prepare the row (K3)
     for (int32_t p = 0; p < n_pods; p++) {
-        CU(launch_score_general(c->dm, c->cfg.device, a, dreq, dall + p, 1, c->st));
+        if (reinterpret_cast<const GenPod *>(c->h_stage + c->off_genall)[p].flags & G_LEGACY)
+            CU(launch_score_general(c->dm, c->cfg.device, a, dreq, dall + p, 1, c->st));
+        else
+            CU(launch_score_walk(c->dm, c->cfg.device, a, dreq, dall + p, 1, c->st));
         CU(launch_resolve(raw_const(c), c->n_nodes, c->dmax, c->cfg.row_base, dpod + p, dreq, dpick, 1,
                           c->d_keys + p, c->d_counts + p, c->d_results + p, c->d_picks, c->d_status, c->st,
                           c->d_rowlist, nullptr, nullptr, false, nullptr, c->d_walk,

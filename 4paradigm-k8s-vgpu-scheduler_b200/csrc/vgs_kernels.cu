@@ -1614,6 +1614,11 @@ static cudaError_t plan(K kernel, int dev, int32_t n_tiles, int32_t n_pods, int 
     return cudaSuccess;
 }
 
+cudaError_t plan_score_launch(const void *kernel, int dev, int32_t n_tiles, int32_t n_pods, int max_warps,
+                              int smem_per_pod, ScoreLaunch *L) {
+    return plan(kernel, dev, n_tiles, n_pods, max_warps, smem_per_pod, L);
+}
+
 template <int DM, bool NUMS1>
 static cudaError_t launch_single_t(int dev, const ScoreArgs &a, const DevReq *reqs, const int32_t *orig,
                                    int32_t n_pods, cudaStream_t st) {

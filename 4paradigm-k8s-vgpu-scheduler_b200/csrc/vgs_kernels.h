@@ -42,6 +42,12 @@ cudaError_t launch_score_single(int dm, bool nums1, int dev, const ScoreArgs &a,
                                 const int32_t *orig, int32_t n_pods, cudaStream_t st);
 cudaError_t launch_score_general(int dm, int dev, const ScoreArgs &a, const DevReq *reqs,
                                  const GenPod *pods, int32_t n_pods, cudaStream_t st);
+// the walk kernel (vgs_general.cu): multi-request pods by ordering keys; pods flagged G_LEGACY must not come here
+cudaError_t launch_score_walk(int dm, int dev, const ScoreArgs &a, const DevReq *reqs, const GenPod *pods,
+                              int32_t n_pods, cudaStream_t st);
+// launch geometry of a thread-per-node score kernel (persistent grid over (tile group, pod chunk) items)
+cudaError_t plan_score_launch(const void *kernel, int dev, int32_t n_tiles, int32_t n_pods, int max_warps,
+                              int smem_per_pod, ScoreLaunch *L);
 // K1t: fill the bit tables of a sliced class on the device (table region zeroed, value arrays uploaded)
 cudaError_t launch_slice_tables(const SliceTab &tb, const DevReq *dreq_class, cudaStream_t st);
 // pod-sliced K1 for one class (all pods: one request, Nums == nums in {1,2}, walk DM == 8)

@@ -71,10 +71,33 @@ constexpr uint32_t R_USEPCT = 2u; // memreq = Totalmem * pct / 100 per device
 constexpr uint32_t R_NEWCTR = 4u; // first request of a container
 constexpr uint32_t R_IDLE = 8u;   // VGS_REQ_IDLE_SHARE (K3's plain restatement; the score kernels see M_BUSY370 in blockmask)
 
+// ordering key of the walk kernel (vgs_general.cu): [numa rank 4][free share slots + bias 21][arrival stamp 7]
+constexpr int kStampBits = 7;
+constexpr uint32_t kStampMask = (1u << kStampBits) - 1u;
+constexpr int kFsBits = 21;
+constexpr uint32_t kFsBias = 1u << 20; // |Count - Used| < VGS_MAX_SHARE = 2^20
+constexpr int kNumaShift = kStampBits + kFsBits; // 28
+
 // pod of the general (multi-request) class
 struct GenPod {
-    int32_t req_begin, n_reqs, orig, pad;
+    int32_t req_begin, n_reqs, orig, flags; // flags: G_*, 0 = nothing known (always correct)
 };
+constexpr int32_t G_UNIFORM_TYPE = 1;  // every request of the pod carries the same type mask and no R_IDLE
+constexpr int32_t G_NO_USED_TRACK = 2; // no request's blockmask tests a "Used > 0" bit (M_EXCL, M_BUSY370)
+constexpr int32_t G_LEGACY = 4;        // host routing only: more picks than the walk kernel's arrival stamps hold
+constexpr int kWalkMaxPicks = 100;     // sum of Nums per pod the walk kernel accepts (7-bit stamps, 12 initial)
+
+inline int32_t gen_pod_flags(const DevReq *r, int n) {
+    int32_t f = G_UNIFORM_TYPE | G_NO_USED_TRACK;
+    long long picks = 0;
+    for (int i = 0; i < n; i++) {
+        if (r[i].mask_lo != r[0].mask_lo || r[i].mask_hi != r[0].mask_hi || (r[i].flags & R_IDLE)) f &= ~G_UNIFORM_TYPE;
+        if (r[i].blockmask & (M_EXCL | M_BUSY370)) f &= ~G_NO_USED_TRACK;
+        picks += r[i].nums;
+    }
+    if (picks > kWalkMaxPicks) f |= G_LEGACY;
+    return f;
+}
 
 // Pod-sliced score kernel: per-class bit tables over the pods of one class (bit i of word
 // i/32 = pod i of the class).  Row stride Wp words.  "LE" tables are cumulative: row c holds

@@ -132,7 +132,7 @@ extern "C" int vgs_score_batch_noalloc(int32_t device, void *stream, int32_t n_n
         hgen[p].req_begin = pd.req_begin;
         hgen[p].n_reqs = pd.n_reqs;
         hgen[p].orig = p;
-        hgen[p].pad = 0;
+        hgen[p].flags = gen_pod_flags(&hreq[pd.req_begin], pd.n_reqs);
     }
 
     std::lock_guard<std::mutex> lk(g_lock);
@@ -196,7 +196,12 @@ extern "C" int vgs_score_batch_noalloc(int32_t device, void *stream, int32_t n_n
     a.vfit = nullptr;
     a.vscore = nullptr;
     a.vwords = 0;
-    NA(launch_score_general(8, device, a, d_reqs, d_gen, n_pods, st));
+    // (pods with more picks than the walk kernel's stamps hold cannot occur here: <= 1024 requests, but a
+    // single pod may still carry > 100 picks -- those take the all-pairs kernel)
+    bool any_legacy = false;
+    for (int32_t p = 0; p < n_pods; p++) any_legacy = any_legacy || (hgen[p].flags & G_LEGACY);
+    if (any_legacy) NA(launch_score_general(8, device, a, d_reqs, d_gen, n_pods, st));
+    else NA(launch_score_walk(8, device, a, d_reqs, d_gen, n_pods, st));
     NA(launch_resolve(raw, n_nodes, dmax, row_base, d_pods, d_reqs, d_pick, n_pods, d_keys, d_counts, dev_results,
                       dev_picks, d_status, st));
     uint32_t hstatus = 0;
