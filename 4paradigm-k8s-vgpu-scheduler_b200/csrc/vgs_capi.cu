@@ -752,6 +752,34 @@ static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, i
     c->nC = nC;
     c->nG = nG;
     c->nGL = nGL;
+    // The walk kernel shares the work of a common first request between consecutive pods: order its class by
+    // (pod flags, first request) and mark the runs.  Results are scattered by GenPod.orig, so the order is free.
+    if (nG - nGL > 1) {
+        GenPod *w = hG;
+        const int32_t nw = nG - nGL;
+        auto first_key = [&](const GenPod &g, int32_t (&k)[9]) {
+            const DevReq &d = hreq[g.req_begin];
+            k[0] = g.flags & ~(G_SAME_FIRST | G_SAVE_FIRST), k[1] = d.nums, k[2] = d.memfix, k[3] = d.pct, k[4] = d.coresreq, k[5] = (int32_t)d.blockmask;
+            k[6] = (int32_t)d.flags, k[7] = (int32_t)d.mask_lo, k[8] = (int32_t)d.mask_hi;
+        };
+        std::sort(w, w + nw, [&](const GenPod &a, const GenPod &b) {
+            int32_t ka[9], kb[9];
+            first_key(a, ka), first_key(b, kb);
+            for (int i = 0; i < 9; i++)
+                if (ka[i] != kb[i]) return ka[i] < kb[i];
+            return a.orig < b.orig;
+        });
+        for (int32_t i = 1; i < nw; i++) {
+            int32_t ka[9], kb[9];
+            first_key(w[i - 1], ka), first_key(w[i], kb);
+            bool same = (w[i].flags & G_NO_USED_TRACK) && w[i].n_reqs > 1; // (the parked state has no usage flags)
+            for (int q = 0; q < 9 && same; q++) same = ka[q] == kb[q];
+            if (same) {
+                w[i].flags |= G_SAME_FIRST;
+                w[i - 1].flags |= G_SAVE_FIRST;
+            }
+        }
+    }
     c->n_picks = (int32_t)picks;
     // everything above was host work that overlaps an asynchronous snapshot upload; the class set-up
     // below wants to know what the snapshot allows (sliced kernels, type rows)

@@ -131,6 +131,10 @@ __global__ void __launch_bounds__(128)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int n_items = L.n_chunks * L.n_tile_groups;
     const bool small = n_pods <= kWarp; // see flush_small
+    // Consecutive pods with the same first request (the host sorts the class by it, G_SAME_FIRST / G_SAVE_FIRST)
+    // share everything up to and including that request: the node state it leaves is parked here, per
+    // thread, and the followers start from it at their second request.
+    __shared__ int4 s_save[3 * (DM / 4) + 1][128];
     uint32_t one = 1u;
     asm volatile("" : "+r"(one)); // opaque 1 (see take_if)
     unsigned long long acckey = 0ull;
@@ -164,47 +168,67 @@ __global__ void __launch_bounds__(128)
             const int kend = min(kWarp, npod - pp);
             for (int k = 0; k < kend; k++) {
                 const GenPod pod = pods[pod0 + pp + k];
-                // the pod's private, mutable view of the node: free memory and cores re-read from the
-                // (L1-resident) tile, keys and meta from the registers above
+                // the pod's private, mutable view of the node
                 int32_t fm[DM], fc[DM];
                 uint32_t key[DM], mt[DM];
-                load_word<DM>(tp, W_FREEMEM, lane, fm);
-                load_word<DM>(tp, W_FREECORES, lane, fc);
-#pragma unroll
-                for (int j = 0; j < DM; j++) {
-                    key[j] = key0[j];
-                    mt[j] = (uint32_t)meta0[j];
-                }
                 const bool uniform_type = pod.flags & G_UNIFORM_TYPE;
                 const bool track_used = !(pod.flags & G_NO_USED_TRACK);
-                if (uniform_type) {
-                    // one type mask for the whole pod: a device that fails it never fits, whatever the
-                    // request -- it gets a free memory no request is small enough for
-                    const DevReq r0 = load_req(&reqs[pod.req_begin]);
-#pragma unroll
-                    for (int j = 0; j < DM; j++)
-                        fm[j] = type_ok(r0.mask_lo, r0.mask_hi, mt[j]) ? fm[j] : INT32_MIN;
-                }
                 bool alive = true, in_ctr = false;
                 float score = 0.0f;
                 uint32_t total = 0u, free_ = 0u; // wrapping, like Go's int32
                 int32_t sums = 0;
                 uint32_t stamp = (uint32_t)DM; // next arrival stamp
+                int r_first = 0;
+#pragma unroll
+                for (int j = 0; j < DM; j++) mt[j] = (uint32_t)meta0[j];
+                // (item == first pod of this warp's run over the tile: nothing parked yet)
+                if ((pod.flags & G_SAME_FIRST) && (pp + k) > 0) {
+#pragma unroll
+                    for (int q = 0; q < DM / 4; q++) {
+                        const int4 a = s_save[q][threadIdx.x], b = s_save[DM / 4 + q][threadIdx.x],
+                                   c = s_save[2 * (DM / 4) + q][threadIdx.x];
+                        fm[4 * q] = a.x, fm[4 * q + 1] = a.y, fm[4 * q + 2] = a.z, fm[4 * q + 3] = a.w;
+                        fc[4 * q] = b.x, fc[4 * q + 1] = b.y, fc[4 * q + 2] = b.z, fc[4 * q + 3] = b.w;
+                        key[4 * q] = (uint32_t)c.x, key[4 * q + 1] = (uint32_t)c.y, key[4 * q + 2] = (uint32_t)c.z,
+                                key[4 * q + 3] = (uint32_t)c.w;
+                    }
+                    const int4 sc = s_save[3 * (DM / 4)][threadIdx.x];
+                    total = (uint32_t)sc.x, free_ = (uint32_t)sc.y, sums = sc.z;
+                    stamp = (uint32_t)sc.w & 0xffffu;
+                    alive = (sc.w >> 16) & 1;
+                    in_ctr = true;
+                    r_first = 1;
+                } else {
+                    // free memory and cores re-read from the (L1-resident) tile, keys from the registers above
+                    load_word<DM>(tp, W_FREEMEM, lane, fm);
+                    load_word<DM>(tp, W_FREECORES, lane, fc);
+#pragma unroll
+                    for (int j = 0; j < DM; j++) key[j] = key0[j];
+                    if (uniform_type) {
+                        // one type mask for the whole pod: a device that fails it never fits, whatever the
+                        // request -- it gets a free memory no request is small enough for
+                        const DevReq r0 = load_req(&reqs[pod.req_begin]);
+#pragma unroll
+                        for (int j = 0; j < DM; j++)
+                            fm[j] = type_ok(r0.mask_lo, r0.mask_hi, mt[j]) ? fm[j] : INT32_MIN;
+                    }
+                }
 
-                for (int r = 0; r < pod.n_reqs; r++) {
+                for (int r = r_first; r < pod.n_reqs; r++) {
                     const DevReq rq = load_req(&reqs[pod.req_begin + r]);
                     if (rq.flags & R_NEWCTR) { // score.go:180,203: one container done
-                        if (in_ctr) score = __fadd_rn(score, container_score((int32_t)total, (int32_t)free_, ndev - sums));
+                        // (a lane that is out has taken nothing: free = 0 would send the whole warp through the
+                        // division's slow path)
+                        if (in_ctr) score = __fadd_rn(score, container_score((int32_t)total, alive ? (int32_t)free_ : 1, ndev - sums));
                         total = 0u;
                         free_ = 0u;
                         sums = 0;
                         in_ctr = true;
                     }
                     sums += rq.nums;
-                    if (rq.nums > DM) { // score.go:162 (Nums > len(node.Devices)) on every node
-                        alive = false;
-                        break;
-                    }
+                    // (Nums > len(node.Devices), score.go:162: the rounds below run out of candidates; the trip
+                    // count is capped so that an absurd Nums costs nothing)
+                    const int32_t rounds = min(rq.nums, DM + 1);
                     // ---- which devices fit (score.go:94-134), all against the state before this request
                     uint32_t cand[DM];
                     // the bits of the blockmask that are not arithmetic here
@@ -243,7 +267,7 @@ __global__ void __launch_bounds__(128)
                         // it.  One compare per device, the updates predicated on it and placed on the multiply-add
                         // unit (take_if), beside the compare / select unit that the fit tests keep busy.
                         const uint32_t ncores = 0u - (uint32_t)rq.coresreq;
-                        for (int i = 0; i < rq.nums; i++) { // warp-uniform trip count
+                        for (int i = 0; i < rounds; i++) { // warp-uniform trip count
                             uint32_t m = 0u;
 #pragma unroll
                             for (int j = 0; j < DM; j++) m = max(m, cand[j]);
@@ -253,7 +277,7 @@ __global__ void __launch_bounds__(128)
                             const uint32_t mm = m != 0u ? m : 0xffffffffu; // keys never reach this value
                             // one level down and stamped as the newest arrival there; devices taken by one request
                             // keep their relative order: the first taken gets the request's highest stamp
-                            const uint32_t nrestamp = (stamp + (uint32_t)(rq.nums - 1 - i)) - (0x80u + kStampMask);
+                            const uint32_t nrestamp = (stamp + (uint32_t)(rounds - 1 - i)) - (0x80u + kStampMask);
                             if (track_used) { // Used > 0 from here on: exclusive cards, busy 370s
 #pragma unroll
                                 for (int j = 0; j < DM; j++)
@@ -267,10 +291,21 @@ __global__ void __launch_bounds__(128)
                     };
                     if (rq.flags & R_USEPCT) body(std::true_type{}); // warp-uniform
                     else body(std::false_type{});
-                    stamp += (uint32_t)rq.nums;
+                    stamp += (uint32_t)rounds;
+                    if (r == 0 && (pod.flags & G_SAVE_FIRST)) { // the next pod starts from here
+#pragma unroll
+                        for (int q = 0; q < DM / 4; q++) {
+                            s_save[q][threadIdx.x] = make_int4(fm[4 * q], fm[4 * q + 1], fm[4 * q + 2], fm[4 * q + 3]);
+                            s_save[DM / 4 + q][threadIdx.x] = make_int4(fc[4 * q], fc[4 * q + 1], fc[4 * q + 2], fc[4 * q + 3]);
+                            s_save[2 * (DM / 4) + q][threadIdx.x] = make_int4((int32_t)key[4 * q], (int32_t)key[4 * q + 1],
+                                                                           (int32_t)key[4 * q + 2], (int32_t)key[4 * q + 3]);
+                        }
+                        s_save[3 * (DM / 4)][threadIdx.x] =
+                            make_int4((int32_t)total, (int32_t)free_, sums, (int32_t)(stamp | (alive ? 0x10000u : 0u)));
+                    }
                     if (!__any_sync(0xffffffffu, alive)) break;
                 }
-                if (alive && in_ctr) score = __fadd_rn(score, container_score((int32_t)total, (int32_t)free_, ndev - sums));
+                if (in_ctr) score = __fadd_rn(score, container_score((int32_t)total, alive ? (int32_t)free_ : 1, ndev - sums));
                 const bool fitn = alive;
                 if (VERIFY) {
                     unsigned b = __ballot_sync(0xffffffffu, fitn);
