@@ -13,7 +13,11 @@
 // fixed array that is part of the library image.
 //
 // The price is a hard size limit (VGS_NOALLOC_MAX_*) and about 4 MiB of device memory held
-// by every GPU that loads the library, from the first CUDA call of the process until exit.
+// by every GPU that loads the library until the process exits.  With CUDA's default lazy
+// module loading that memory (and the kernels' code) is committed by the FIRST call on a GPU,
+// not when the library is loaded: a caller that runs under a memory quota should make one
+// small warm-up call at start-up, while memory is still free, or run with
+// CUDA_MODULE_LOADING=EAGER; after that first call no later call can fail for lack of memory.
 #include <cuda_runtime.h>
 
 #include <cstdint>
@@ -145,7 +149,10 @@ extern "C" int vgs_score_batch_noalloc(int32_t device, void *stream, int32_t n_n
     if (!g_base[device]) {
         unsigned char *ptr = nullptr;
         cudaError_t e = cudaGetSymbolAddress((void **)&ptr, g_noalloc_scratch);
-        if (e != cudaSuccess || !ptr) return VGS_ECUDA;
+        if (e != cudaSuccess || !ptr) {
+            cudaGetLastError(); // do not leave the error behind for the caller's next CUDA call
+            return VGS_ECUDA;
+        }
         g_base[device] = ptr;
     }
     unsigned char *base = g_base[device];

@@ -288,7 +288,10 @@ int vgs_results_device(vgs_ctx *ctx, vgs_result **dev_results, vgs_pick **dev_pi
  * the hard limits below; anything larger returns VGS_ELIMIT and touches nothing.
  *
  * The first call on each GPU looks up that array's device address (one-time
- * set-up); make that first call outside of any stream capture.  Every call on a
+ * set-up); make that first call outside of any stream capture.  With CUDA's
+ * default lazy module loading it is also the call that commits the array and the
+ * kernels' code to device memory: make it at start-up (a one-node, one-pod call
+ * will do) while memory is free, or set CUDA_MODULE_LOADING=EAGER.  Every call on a
  * GPU shares the array and finds the previous call's contents in it (the call
  * clears what has to start at zero).  Two calls executing at once on the same GPU
  * would corrupt each other, so the function takes a process-wide lock and does

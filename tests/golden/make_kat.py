@@ -3,7 +3,8 @@
 The expected values are LITERALS transcribed from the survey's table (derived by hand
 from pkg/scheduler/score.go), not outputs of the oracle or of the GPU path.  The
 reference has no test for pkg/scheduler and cannot be run here (no Go toolchain), so
-these vectors are the only pin the oracle has ("parity unpinned").
+these vectors are the only pin the oracle has ("parity unpinned").  Float bit patterns were worked out with
+IEEE binary32 arithmetic on the literal integers named in each `cite` (e.g. float32(20)/float32(19)+float32(6)).
 
 node = 8 device slots, Count=10, Totalmem=32768, Totalcore=100, Numa=0,
 Type "NVIDIA-Tesla V100-PCIE-32GB", idle unless stated.
@@ -82,6 +83,42 @@ KATS = [
     kat("21_use_mlutype", node(Type=[M370X4] * 4 + [M370] * 4), [[(1, 0, 0, 0, "MLU")]],
         {"cambricon.com/use-mlutype": "x4"}, True, "0x41000000", [[(3, 0, 0)]], cite="cambricon/device.go:60-75"),
     kat("22_nvidia_request_on_mlu_node", node(Type=M370), [[(1, 1000, U, 0)]], {}, False, cite="score.go:73"),
+    # ---- request shapes the first 23 vectors never used (derived by hand from score.go, like the rest) ----
+    kat("23_memreq_wins_over_percentage", node(Used=1, Usedmem=20000), [[(1, 3000, 50, 0)]], {}, True, "0x4101c71c",
+        [[(7, 3000, 0)]],
+        cite="score.go:114-120: Memreq > 0 sets memreq = 3000; the percentage branch needs Memreq == 0, so 50% "
+             "(16384 > 12768 free) is never computed. 10/9 + 7"),
+    kat("24_negative_memreq_with_percentage", node(Used=1, Usedmem=32768), [[(1, -5, 50, 0)]], {}, True, "0x4101c71c",
+        [[(7, 0, 0)]],
+        cite="score.go:114-120: Memreq > 0 false and Memreq == 0 false -> memreq stays 0; 0 free >= 0 fits, Usedmem 0"),
+    kat("25_negative_coresreq_then_zero_cores", node(Used=1, Usedcores=100), [[(1, 1000, U, -10)], [(1, 1000, U, 0)]],
+        {}, True, "0x4182e38e", [[(7, 1000, -10)], [(7, 1000, 0)]],
+        cite="score.go:124: 0 free cores >= -10; :172 Usedcores += -10 -> 90. Container 1 (cores 0): slots 0-6 are "
+             "full (:132), slot 7 (now first in the sort, 8 free) is reached last and fits: (10/9 + 7) + (10/8 + 7)"),
+    kat("26_used_exceeds_count", node(Used=[12, 11, 10, 9, 12, 11, 10, 12]), [[(1, 1000, U, 0)]], {}, True, "0x41880000",
+        [[(3, 1000, 0)]], cite="score.go:107 Count <= Used skips seven devices; 10/1 + 7"),
+    kat("27_totalcore_zero_cores_zero", node(Totalcore=0, Used=1), [[(1, 1000, U, 0)]], {}, True, "0x4101c71c",
+        [[(7, 1000, 0)]], cite="score.go:124 0-0 < 0 false; :128 needs Totalcore == 100; :132 needs Totalcore != 0"),
+    kat("27b_totalcore_zero_cores_100", node(Totalcore=0), [[(1, 1000, U, 100)]], {}, False,
+        cite="score.go:124: 0 - 0 < 100 on every device"),
+    kat("28_numa_bind_type_mismatch_inside_group",
+        node(Numa=[0, 0, 0, 0, 1, 1, 1, 1], Type=[V100] * 5 + [A100] + [V100] * 2), [[(3, 1000, U, 0)]],
+        {"nvidia.com/numa-bind": "true", "nvidia.com/use-gputype": "v100"}, True, "0x40c00000",
+        [[(7, 1000, 0), (6, 1000, 0), (4, 1000, 0)]],
+        cite="score.go:94-104: slot 5 fails the type check and is skipped BEFORE the numa test, so the numa-1 group "
+             "is not broken: 7, 6, 4. 30/30 + 5"),
+    kat("29_second_request_sees_first_take", node(Used=[1] * 7 + [0], Usedmem=[32768] * 7 + [0]),
+        [[(1, 1000, U, 0, "NVIDIA"), (1, 1000, U, 100, "NVIDIA")]], {}, False,
+        cite="score.go:168-174: request 0 takes slot 7 (the only one with memory) -> Used 1; request 1 wants a card "
+             "exclusively (:128 Used > 0) -> nothing fits, the container fails"),
+    kat("29b_second_request_shares_the_card", node(Used=[1] * 7 + [0], Usedmem=[32768] * 7 + [0]),
+        [[(1, 1000, U, 0, "NVIDIA"), (1, 1000, U, 50, "NVIDIA")]], {}, True, "0x40e1af28",
+        [[(7, 1000, 0), (7, 1000, 50)]],
+        cite="same, but 50 cores: slot 7 again. total 10 + 10, free 10 + 9 (:170 after the first Used++), sums 2: 20/19 + 6"),
+    kat("30_two_vendors_in_one_container", node(Type=[V100] * 4 + [M370] * 4),
+        [[(1, 0, 0, 0, "MLU"), (1, 1000, U, 0, "NVIDIA")]], {}, True, "0x40e00000", [[(7, 0, 0), (3, 1000, 0)]],
+        cite="MLU request takes slot 7 (Used 1 -> sorts first); the NVIDIA request walks 6, 5, 4 (type mismatch, "
+             "score.go:73) and takes slot 3. 20/20 + 6"),
 ]
 
 # string-policy truth table (nvidia/device.go:62-105), each line derived by hand

@@ -74,11 +74,14 @@ def _random_pods(rng, p, dmax, max_ctrs=4):
                 ctrs.append([])
                 continue
             nums = int(rng.choice([1, 1, 2, 3, dmax, dmax + 1]))
-            if rng.random() < 0.5:
+            u = rng.random()
+            if u < 0.4:
                 mem, pct = int(rng.choice([0, 500, 4000, 20000])), 101
-            else:
+            elif u < 0.8:
                 mem, pct = 0, int(rng.choice([0, 10, 50, 100, 101]))
-            cores = int(rng.choice([0, 0, 10, 50, 100, 101]))
+            else:  # gpumem AND gpumem-percentage set (nvidia/device.go:125-145), negative values: score.go:114-120
+                mem, pct = int(rng.choice([500, 4000, -5, -4000])), int(rng.choice([10, 50, 100, 0]))
+            cores = int(rng.choice([0, 0, 10, 50, 100, 101, -10]))
             ctrs.append([(nums, mem, pct, cores)])
         if not any(ctrs):
             ctrs.append([(1, 0, 101, 0)])
@@ -115,6 +118,53 @@ def test_multi_request_container(built):
             {"containers": [[(1, 100, 101, 0), (1, 100, 101, 0), (1, 100, 101, 0)]], "annos": {"nvidia.com/numa-bind": "true"}}]
     batch = v.PodBatch.from_pods(pods)
     assert_same(gpu_score(snap, batch), oracle.score_packed(snap, batch, full=True), "multi-req")
+
+
+def test_shared_first_request_runs(built):
+    """the walk kernel parks the node state after a first request that consecutive pods share: groups of pods
+    with equal first requests and different continuations -- numa-bind, exclusive (usage-flag tracking, never
+    shared), mixed vendors, a follower with a single request, percentages -- against the whole fit / score matrix"""
+    rng = np.random.default_rng(41)
+    snap = _random_snapshot(rng, 1500, 8, ragged=True, types=5)
+    firsts = [(1, 1000, 101, 0), (2, 0, 50, 10), (1, 4000, 101, 100), (3, 500, 101, 0), (1, 0, 25, 0)]
+    pods = []
+    for i in range(400):
+        f = firsts[int(rng.integers(0, len(firsts)))]
+        ctrs = [[f]]
+        for _ in range(int(rng.integers(0, 4))):
+            if rng.random() < 0.5:
+                ctrs.append([(int(rng.choice([1, 1, 2, 4])), int(rng.choice([500, 4000, 20000])), 101, int(rng.choice([0, 10, 100])))])
+            else:
+                ctrs.append([(int(rng.choice([1, 2])), 0, int(rng.choice([10, 50, 100])), int(rng.choice([0, 30])))])
+        if rng.random() < 0.15:  # a second request inside the FIRST container
+            ctrs[0] = [f, (1, 100, 101, 0)]
+        annos = {}
+        if rng.random() < 0.2:
+            annos["nvidia.com/numa-bind"] = "true"
+        if rng.random() < 0.2:
+            annos["nvidia.com/use-gputype"] = "a100,t4"
+        pods.append({"containers": ctrs, "annos": annos})
+    batch = v.PodBatch.from_pods(pods)
+    want = oracle.score_packed(snap, batch, full=True)
+    assert want.fit.any()
+    assert_same(gpu_score(snap, batch), want, "shared first request")
+    assert_same(gpu_score(snap, batch, verify=False), oracle.score_packed(snap, batch), "shared first request (fast)")
+    # the round-1 all-pairs kernel (vgs_tuning.general_legacy) must agree as well
+    assert_same(gpu_score(snap, batch, tuning={"general_legacy": 1}), want, "all-pairs kernel")
+
+
+def test_walk_kernel_many_picks_fall_back(built):
+    """a pod with more picks than the walk kernel's arrival stamps hold (> 100) runs on the all-pairs kernel;
+    one just below the limit runs on the walk kernel: same oracle"""
+    node = [dict(Used=0, Count=40, Usedmem=0, Totalmem=32768, Usedcores=0, Totalcore=0, Numa=s // 4) for s in range(8)]
+    snap = v.Snapshot.from_nodes([node] * 40)
+    pods = [{"containers": [[(8, 10, 101, 0)] for _ in range(13)]},   # 104 picks
+            {"containers": [[(8, 10, 101, 0)] for _ in range(12)]},   # 96 picks
+            {"containers": [[(4, 10, 101, 0)] for _ in range(25)]}]   # 100 picks
+    batch = v.PodBatch.from_pods(pods)
+    want = oracle.score_packed(snap, batch, full=True)
+    assert want.fit.all()
+    assert_same(gpu_score(snap, batch), want, "many picks")
 
 
 def test_empty_and_tiny(built):
@@ -532,6 +582,55 @@ def test_shards_exchange_in_one_collective(built, cfg, n, p):
             assert np.array_equal(np.stack([pk["slot"], pk["usedmem"], pk["usedcores"]], axis=1), single.picks)
     for c in ctxs:
         c.close()
+
+
+def test_cfg5_shape_eight_shards(built):
+    """BASELINE config 5 at full size: 1M nodes x 8 devices x 16384 pods as 8 row shards of 125k nodes (here: 8
+    contexts on one GPU), every shard resolving its own best node, ONE gather of the exchange blocks, merge.
+    Checked against the oracle over all 1M nodes for a sample of pods, and every shard must hold the same answer."""
+    import torch
+    snap, batch = v.workload.make_config("cfg5")
+    assert snap.n_nodes == 1_000_000 and batch.n_pods == 16384
+    pods, reqs = v.capi.pack_batch(batch, snap.type_names)
+    G, P = 8, batch.n_pods
+    n_picks = int(reqs["nums"].sum())
+    dev = torch.device("cuda", 0)
+    ctxs, blocks = [], []
+    for g in range(G):
+        lo, hi = v.sharding.shard_range(snap.n_nodes, G, g)
+        c = v.Context(max_nodes=hi - lo, max_pods=P, max_reqs=len(reqs), max_picks=n_picks, row_base=lo)
+        c.upload(snap.rows(lo, hi))
+        c.pods_upload(pods, reqs)
+        c.score_resident()
+        c.resolve_local()
+        c.sync()
+        plan = c.plan()
+        assert plan.cls[0].kernel == v.capi.KERNEL_SLICED and plan.cls[1].kernel == v.capi.KERNEL_SLICED
+        bp, nb = c.exchange_block()
+        blocks.append(v.sharding.device_view(bp, nb // 4, torch.int32, dev).clone())
+        ctxs.append(c)
+    gathered = torch.stack(blocks).contiguous()
+    torch.cuda.synchronize()
+    first = None
+    for c in ctxs:
+        c.exchange_merge(gathered.data_ptr(), G, gathered.stride(0) * 4)
+        r, pk = c.results_download()
+        if first is None:
+            first = (r, pk)
+        else:
+            assert np.array_equal(r, first[0]) and np.array_equal(pk, first[1])
+        c.close()
+    r, pk = first
+    idx = list(range(0, P, 256))
+    want = oracle.score_packed(snap, batch.select(idx))
+    assert np.array_equal(r["best_row"][idx], want.best_row)
+    assert np.array_equal(r["score"][idx].view(np.uint32), want.score.view(np.uint32))
+    assert np.array_equal(r["fit_count"][idx], want.fit_count)
+    pb = batch.pick_begin
+    got = np.stack([pk["slot"], pk["usedmem"], pk["usedcores"]], axis=1)
+    got = np.concatenate([got[int(pb[batch.pod_req_range(p)[0]]):int(pb[batch.pod_req_range(p)[1]])] for p in idx])
+    assert np.array_equal(got, want.picks)
+    assert (r["best_row"] >= 0).mean() > 0.8 and r["best_row"].max() > 875_000  # winners come from the last shard too
 
 
 def test_candidate_block_is_clean_between_passes(built):

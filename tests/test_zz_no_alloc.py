@@ -9,6 +9,7 @@ Collected last on purpose (file name), runs alone or after the other GPU tests."
 import numpy as np
 import pytest
 
+import oracle
 import vgpu_b200 as v
 
 pytestmark = pytest.mark.gpu
@@ -53,6 +54,13 @@ def test_noalloc_matches_allocating_entry_point_twice(built):
         assert np.array_equal(got_res["n_picks"], want_res["n_picks"]), f"call {i}"
         assert np.array_equal(got_picks, want_picks), f"call {i}"
         assert (want_res["best_row"] >= 0).any()
+        # ... and a parity test in its own right: the same answers as the CPU oracle
+        ref = oracle.score_packed(snap, batch)
+        assert np.array_equal(got_res["best_row"], ref.best_row), f"call {i} vs oracle"
+        assert np.array_equal(got_res["score"].view(np.uint32), ref.score.view(np.uint32)), f"call {i} vs oracle"
+        assert np.array_equal(got_res["fit_count"], ref.fit_count), f"call {i} vs oracle"
+        assert np.array_equal(np.stack([got_picks["slot"], got_picks["usedmem"], got_picks["usedcores"]], axis=1),
+                              ref.picks), f"call {i} vs oracle"
 
 
 def test_noalloc_rejects_sizes_beyond_its_limits(built):
