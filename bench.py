@@ -7,20 +7,26 @@
 Step = one pass of the hot path over one pod batch against the resident snapshot:
 K0 prepare (raw planes -> walk-ordered tiles) + K1 score + K3 resolve; for N > 1 every shard
 resolves its own best node, the [keys | counts | picks] blocks are all-gathered once (NCCL) and
-merged (K2x).  Workload at N=1 = BASELINE config 3 (100k nodes x 8 devices x
-4096 mixed pods); for N > 1 every rank holds its own 100k-node shard (weak scaling,
-N x 100k nodes in total) and the same 4096 pods.
+merged (K2x).  Headline workload = BASELINE config 3 (100k nodes x 8 devices x 4096 mixed pods);
+for N > 1 every rank holds its own 100k-node shard (weak scaling, N x 100k nodes) and the same pods.
 
 `value`   : device-timed (CUDA events per step on the launching stream, max over ranks),
             inputs resident in HBM, L2 flushed between steps.
 `e2e`     : the same metric through the host-buffer C ABI calls the Go shim makes
             (vgs_snapshot_upload_async + pods upload / score / resolve / download): pinned
             host planes and request records in, results out, every step.
-`roofline`: the score kernels (K1) against the measured HBM peak, with the
-            algorithmic bytes of SURVEY 8(d).  The batch regime is integer-issue bound,
-            so this fraction is tiny by construction; see DESIGN.md.
+`e2e_delta`: the production shape of the same calls: snapshot resident, each step ships the usage deltas of
+            the previous step's placements (vgs_snapshot_delta) + the pod batch.
+`roofline`: the score kernels (K1) against the measured HBM peak with the algorithmic bytes of SURVEY 8(d),
+            and `issue_fraction` = K1 warp instructions (ncu launch list under profiles/) / K1 time of this
+            run / issue slots.  The batch regime is integer-issue bound; see DESIGN.md.
+`configs` : the other BASELINE configs as device-timed legs of their own, each with a sampled oracle check:
+            N = 1: cfg2, cfg4, one cfg5 shard (125k nodes x 16384 pods); N > 1: cfg5 (1M nodes) and cfg4,
+            both strong-scaled over the N shards.
+`check`   : a sample of the headline's pods re-scored by the CPU oracle over all nodes (not timed).
 `roofline_hbm_regime` (N = 1): one pod against 1M resident nodes, where the pass IS HBM-bound.
 `filter_latency` (N = 1): wall clock of the single-pod vgs_score_batch call, snapshot resident.
+`cpu_baseline` (N = 1): oracle R2 (packed, all host cores) + R1 / R1-io (the reference's own shape, one thread).
 The reference (Go) cannot be built or run here; its CPU arm is the oracle's packed
 multi-threaded restatement ("port"), timed on this box's host cores.
 """
@@ -222,6 +228,114 @@ def run_sweep(args):
         out.close()
 
 
+def latest_k1_profile():
+    """profiles/rNN_k1_profile.json of the newest round (tools/make_k1_profile.py writes it from the ncu launch
+    list of this command): warp instructions and DRAM bytes of the K1 phase of one cfg3 step, with the tree it
+    was captured on."""
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_k1_profile.json")))
+    if not files:
+        return None
+    try:
+        with open(files[-1]) as f:
+            d = json.load(f)
+        d["file"] = os.path.relpath(files[-1], ROOT)
+        return d
+    except Exception:
+        return None
+
+
+def sampled_check(v, np, snap_whole, batch, results, picks, n_sample=48):
+    """not timed: a sample of pods re-scored by the CPU oracle over ALL nodes; bit-exact or not"""
+    import oracle
+    P = batch.n_pods
+    idx = list(range(0, P, max(1, P // n_sample)))
+    want = oracle.score_packed(snap_whole, batch.select(idx))
+    pb = batch.pick_begin
+    ok = (np.array_equal(results["best_row"][idx], want.best_row)
+          and np.array_equal(results["score"][idx].view(np.uint32), want.score.view(np.uint32))
+          and np.array_equal(results["fit_count"][idx], want.fit_count))
+    flat = np.stack([picks["slot"], picks["usedmem"], picks["usedcores"]], axis=1)
+    got = [flat[int(pb[batch.pod_req_range(p)[0]]):int(pb[batch.pod_req_range(p)[1]])] for p in idx]
+    got = np.concatenate(got) if got else np.zeros((0, 3), np.int32)
+    ok = ok and np.array_equal(got, want.picks)
+    return {"pods_checked": len(idx), "nodes": snap_whole.n_nodes, "bit_exact_vs_oracle": bool(ok)}
+
+
+class Leg:
+    """one resident workload on this rank's shard: context, pinned planes, device-timed steps"""
+
+    def __init__(self, v, torch, dist, local, rank, world, snap, batch, n_total, row_lo=None):
+        self.v, self.torch, self.dist, self.world, self.rank = v, torch, dist, world, rank
+        self.snap, self.batch = snap, batch
+        self.pods, self.reqs = v.capi.pack_batch(batch, snap.type_names)
+        self.n_picks = int(self.reqs["nums"].sum())
+        P, R = len(self.pods), len(self.reqs)
+        self.sc = v.sharding.ShardedScorer(n_total, snap.dmax, max_pods=P, max_reqs=max(R, P),
+                                           max_picks=max(self.n_picks, R), device=local, rank=rank, world=world)
+        assert self.sc.hi - self.sc.lo == snap.n_nodes, (self.sc.lo, self.sc.hi, snap.n_nodes)
+        self.ctx = self.sc.ctx
+        self.pin_planes = torch.from_numpy(snap.planes).pin_memory()
+        self.pin_ndev = torch.from_numpy(snap.ndev).pin_memory()
+        self.plane_ptrs = [self.pin_planes[f].data_ptr() for f in range(8)]
+        self.ctx.upload_ptrs(snap.n_nodes, snap.dmax, self.plane_ptrs, self.pin_ndev.data_ptr(), device=False)
+        self.ctx.type_names = snap.type_names
+        self.ctx.pods_upload(self.pods, self.reqs)
+        self.dev = torch.device("cuda", local)
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def step(self):
+        self.ctx.refresh()                      # K0
+        self.sc.step_resident(self.n_picks)     # K1 (+ local K3 + all-gather + K2x), else K3
+
+    def timed(self, steps, warmup, flush):
+        """W untimed steps, then K steps bracketed by CUDA events on the library's stream, L2 flushed between
+        steps; returns (ms per step = max over ranks of the summed step times / K, K1 ms, launches)"""
+        torch = self.torch
+        torch.cuda.set_stream(self.sc.stream)
+        for _ in range(warmup):
+            flush.zero_()
+            self.step()
+        self.barrier()
+        l0 = self.ctx.timing().kernel_launches
+        starts = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
+        ends = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
+        score_ms = []
+        self.barrier()
+        for i in range(steps):
+            flush.zero_()          # evict the snapshot from L2 between steps (not timed)
+            starts[i].record()
+            self.step()
+            ends[i].record()
+            if i % 8 == 7 or i == steps - 1:
+                score_ms.append(self.ctx.timing().score_ms)  # syncs; last step's K1 time
+        self.barrier()
+        launches = self.ctx.timing().kernel_launches - l0
+        step_ms = [s.elapsed_time(e) for s, e in zip(starts, ends)]
+        total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device=self.dev)
+        k1_ms = torch.tensor([sum(score_ms) / len(score_ms)], dtype=torch.float64, device=self.dev)
+        if self.world > 1:
+            self.dist.all_reduce(total_ms, op=self.dist.ReduceOp.MAX)
+            self.dist.all_reduce(k1_ms, op=self.dist.ReduceOp.MAX)
+        return float(total_ms.item()) / steps, float(k1_ms.item()), int(launches)
+
+    def close(self):
+        self.sc.close()
+        del self.pin_planes, self.pin_ndev
+
+
+def whole_snapshot(v, np, make_shard, world):
+    shards = [make_shard(r) for r in range(world)]
+    if world == 1:
+        return shards[0]
+    return v.Snapshot(np.concatenate([s_.planes for s_ in shards], axis=1), np.concatenate([s_.ndev for s_ in shards]),
+                      shards[0].type_names)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -234,8 +348,8 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-hbm-leg", action="store_true", help="skip the single-pod 1M-node (HBM-bound regime) leg")
-    ap.add_argument("--check", action="store_true",
-                    help="rank 0 re-checks a sample of pods against the oracle over ALL shards (not timed)")
+    ap.add_argument("--no-configs", action="store_true", help="skip the other BASELINE configs (cfg2 / cfg4 / cfg5)")
+    ap.add_argument("--check", action="store_true", help="(kept for old command lines: the oracle check always runs)")
     ap.add_argument("--sweep", action="store_true", help="CPU/GPU crossover grid instead of the bench line")
     ap.add_argument("--sweep-nodes", default="64,512,4096,32768,100000,1000000")
     ap.add_argument("--sweep-pods", default="1,16,256,4096")
@@ -263,97 +377,102 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     v.load_library()
+    cfg_idx = int(args.config[3:])
 
-    # ---- inputs: every rank builds its own shard (rows [rank*npg, (rank+1)*npg)) -------
+    # ---- headline workload: every rank builds its own shard (rows [rank*npg, (rank+1)*npg)) -------
     npg = args.nodes_per_gpu
     n_total = npg * world
-    snap = v.workload.make_snapshot(npg, v.workload.SEED + int(args.config[3:]) + 1000 * rank)
+    make_shard = lambda r: v.workload.make_snapshot(npg, v.workload.SEED + cfg_idx + 1000 * r)
+    snap = make_shard(rank)
     _, batch = v.workload.make_config(args.config, 8, args.pods)
-    pods, reqs = v.capi.pack_batch(batch, snap.type_names)
-    n_picks = int(reqs["nums"].sum())
+    leg = Leg(v, torch, dist, local, rank, world, snap, batch, n_total)
+    ctx, sc, pods, reqs, n_picks = leg.ctx, leg.sc, leg.pods, leg.reqs, leg.n_picks
     P, R, D = len(pods), len(reqs), snap.dmax
-
-    sc = v.sharding.ShardedScorer(n_total, D, max_pods=P, max_reqs=max(R, P), max_picks=max(n_picks, R),
-                                  device=local, rank=rank, world=world)
-    ctx = sc.ctx
-    # pinned host copies (e2e leg) and the resident upload
-    pin_planes = torch.from_numpy(snap.planes).pin_memory()
-    pin_ndev = torch.from_numpy(snap.ndev).pin_memory()
-    plane_ptrs = [pin_planes[f].data_ptr() for f in range(8)]
-    ctx.upload_ptrs(npg, D, plane_ptrs, pin_ndev.data_ptr(), device=False)
-    ctx.pods_upload(pods, reqs)
     flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=dev)
-    torch.cuda.set_stream(sc.stream)  # library kernels, collectives, flush and events: one stream
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def step():
-        ctx.refresh()          # K0
-        sc.step_resident(n_picks)  # K1 (+ all-gather + K2) + K3
+    barrier = leg.barrier
 
     sampler = ClockSampler(local)
-    # ---- device-timed leg ---------------------------------------------------------------
-    for _ in range(args.warmup):
-        flush.zero_()
-        step()
-    barrier()
-    l0 = ctx.timing().kernel_launches
-    starts = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
-    ends = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
-    score_ms = []
     sampler.start()
-    barrier()
-    for i in range(args.steps):
-        flush.zero_()          # evict the snapshot from L2 between steps (not timed)
-        starts[i].record()
-        step()
-        ends[i].record()
-        if i % 8 == 7 or i == args.steps - 1:
-            score_ms.append(ctx.timing().score_ms)  # syncs; last step's K1 time
-    barrier()
-    launches = ctx.timing().kernel_launches - l0
-    step_ms = [s.elapsed_time(e) for s, e in zip(starts, ends)]
-    total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)
-    k1_ms = torch.tensor([sum(score_ms) / len(score_ms)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
-        dist.all_reduce(k1_ms, op=dist.ReduceOp.MAX)
-    total_ms, k1_ms = float(total_ms.item()), float(k1_ms.item())
-    ms_per_step = total_ms / args.steps
+    ms_per_step, k1_ms, launches = leg.timed(args.steps, args.warmup, flush)
     value = P * n_total / (ms_per_step * 1e-3)
     results, picks = ctx.results_download()
     placed = int((results["best_row"] >= 0).sum())
 
     # ---- end-to-end leg: host buffers through the C ABI, every step -----------------------
-    e2e = None
+    e2e = e2e_delta = None
     if not args.no_e2e:
         h2d = snap.planes.nbytes + snap.ndev.nbytes + pods.nbytes + reqs.nbytes
         d2h = results.nbytes + picks.nbytes
 
         def e2e_step():
             # pinned H2D + K0, queued: the request packing below overlaps the copy
-            ctx.upload_ptrs(npg, D, plane_ptrs, pin_ndev.data_ptr(), device=False, asynchronous=True)
+            ctx.upload_ptrs(npg, D, leg.plane_ptrs, leg.pin_ndev.data_ptr(), device=False, asynchronous=True)
             ctx.pods_upload(pods, reqs)
             sc.step_resident(n_picks)
             return ctx.results_download()
 
-        for _ in range(3):
-            e2e_step()
-        barrier()
-        t0 = time.perf_counter()
+        def run_e2e(fn, n):
+            for _ in range(3):
+                fn()
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(n):
+                fn()
+            barrier()
+            dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+            return float(dt.item()) / n
+
         n_e2e = max(5, min(args.steps, 30))
-        for _ in range(n_e2e):
-            e2e_step()
-        barrier()
-        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-        e2e = {"value": P * n_total / (float(dt.item()) / n_e2e), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
-               "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * float(dt.item()) / n_e2e, "steps": n_e2e,
+        sec = run_e2e(e2e_step, n_e2e)
+        e2e = {"value": P * n_total / sec, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+               "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * sec, "steps": n_e2e,
                "api": "vgs_snapshot_upload_async + vgs_pods_upload/score/resolve/results_download (host buffers)"}
+
+        # the production path (scheduler.go:280-297 folded into deltas): the snapshot stays resident, each step
+        # ships the usage changes of the previous step's placements + the pod batch, and reads the results back
+        pod_of_req = np.repeat(np.arange(P), pods["n_reqs"])
+        pod_of_pick = pod_of_req[np.repeat(np.arange(R), reqs["nums"])]
+        state = {"sign": 1, "deltas": None, "bytes": 0}
+
+        def deltas_of(res, pk):
+            rows = res["best_row"][pod_of_pick]
+            ok = rows >= 0
+            d = np.zeros(int(ok.sum()), dtype=v.capi.DELTA_DTYPE)
+            d["row"], d["slot"] = rows[ok], pk["slot"][ok]
+            d["d_used"], d["d_usedmem"], d["d_usedcores"] = 1, pk["usedmem"][ok], pk["usedcores"][ok]
+            return d
+
+        def e2e_delta_step():
+            if state["sign"] > 0:      # commit the previous winners ...
+                state["deltas"] = deltas_of(*state["last"])
+                d = state["deltas"]
+            else:                      # ... and take them away again next step: the snapshot stays bounded
+                d = state["deltas"].copy()
+                for k in ("d_used", "d_usedmem", "d_usedcores"):
+                    d[k] = -d[k]
+            state["sign"] = -state["sign"]
+            state["bytes"] = d.nbytes
+            ctx.delta(d)
+            ctx.pods_upload(pods, reqs)
+            sc.step_resident(n_picks)
+            state["last"] = ctx.results_download()
+            return state["last"]
+
+        ctx.upload_ptrs(npg, D, leg.plane_ptrs, leg.pin_ndev.data_ptr(), device=False)
+        ctx.pods_upload(pods, reqs)
+        sc.step_resident(n_picks)
+        state["last"] = ctx.results_download()
+        sec = run_e2e(e2e_delta_step, n_e2e + (n_e2e & 1))
+        if state["sign"] < 0:  # leave the snapshot as uploaded
+            e2e_delta_step()
+        e2e_delta = {"value": P * n_total / sec, "unit": UNIT, "ms_per_step": 1e3 * sec,
+                     "h2d_bytes_per_step": int(state["bytes"] + pods.nbytes + reqs.nbytes), "d2h_bytes_per_step": int(d2h),
+                     "api": "vgs_snapshot_delta (previous step's placements) + vgs_pods_upload/score/resolve/"
+                            "results_download; snapshot resident"}
+        ctx.upload_ptrs(npg, D, leg.plane_ptrs, leg.pin_ndev.data_ptr(), device=False)
+        ctx.pods_upload(pods, reqs)
     clocks = sampler.stop()
 
     # ---- metric (ii): single-pod Filter latency through the C ABI, snapshot resident -------------
@@ -381,6 +500,8 @@ def main():
                    "k1_us": 1e6 * k1, "k1_algorithmic_GBps": b1 / k1 / 1e9}
         ctx.pods_upload(pods, reqs)  # restore the batch for anything that follows
 
+    prof = latest_k1_profile()
+    peak, peak_src = measured_peak()
     # ---- the regime where the pass IS HBM-bound (P <= ~6): one pod, 1M nodes, snapshot
     # (256 MB) larger than L2, so every call streams it from HBM ----------------------------------
     hbm_regime = None
@@ -397,85 +518,123 @@ def main():
                 ks.append(c1.timing().score_ms)
             k = sorted(ks[10:])[len(ks[10:]) // 2] * 1e-3
             b = algorithmic_bytes(big.n_nodes, D, 1, 1)
-            pk, pk_src = measured_peak()
-            tr = None
-            try:
-                with open(os.path.join(ROOT, "profiles", "k1_traffic.json")) as f:
-                    tr = json.load(f).get("p1_dram_bytes_per_launch")
-            except Exception:
-                pass
+            tr = (prof or {}).get("p1_dram_bytes_per_launch")
             hbm_regime = {"workload": f"{big.n_nodes} nodes x {D} devices x 1 pod, snapshot resident (256 MB > L2)",
                           "bound": "hbm", "kernel": "k1_score_single<8,true> (+ memset, merge: the whole score phase)",
-                          "achieved": b / k / 1e9, "peak": pk, "unit": "GB/s", "frac": b / k / 1e9 / pk,
-                          "algorithmic_bytes": int(b), "kernel_us": 1e6 * k, "peak_source": pk_src, "traffic": tr,
-                          "note": "frac can exceed 1: the algorithmic bytes charge all 8 prepared words per device, "
-                                  "the kernel reads 4-6 of them (traffic = ncu DRAM bytes per launch)"}
+                          # the fraction that follows from what the kernel moves (ncu DRAM bytes per launch), on this
+                          # run's CUDA-event time; the algorithmic-bytes figure (all 8 prepared words per device,
+                          # of which the kernel reads 4-6) is kept beside it under its own name
+                          "achieved": (tr / k / 1e9) if tr else None, "peak": peak, "unit": "GB/s",
+                          "frac": (tr / k / 1e9 / peak) if tr else None, "traffic": tr,
+                          "algorithmic_bytes": int(b), "algorithmic_GBps": b / k / 1e9,
+                          "kernel_us": 1e6 * k, "peak_source": peak_src,
+                          "traffic_source": (prof or {}).get("file")}
+        del big
+
+    # ---- the other BASELINE configs, each a resident device-timed leg with its own oracle check ------------------
+    configs = {}
+    steps_c, warm_c = max(3, min(args.steps, 10)), 3
+    if not args.no_configs and args.config == "cfg3":
+        leg.close()
+        plan = []
+        if world == 1:
+            plan = [("cfg2", "cfg2", None, None, "10k nodes x 8 devices x 256 single-container pods (Nums 1, MB, cores)"),
+                    ("cfg4", "cfg4", None, None, "100k nodes x 4096 multi-container pods, 2-8 vGPUs, 10% numa-bind"),
+                    ("cfg5_shard", "cfg5", 125_000, 16384, "one of cfg5's eight shards: 125k nodes x 16384 mixed pods")]
+        else:
+            plan = [("cfg5", "cfg5", 1_000_000, 16384, f"1M nodes x 16384 mixed pods, node-sharded x{world} (strong)"),
+                    ("cfg4_strong", "cfg4", None, None, f"100k nodes x 4096 multi-container pods, node-sharded x{world} (strong)")]
+        for name, cfg, n_nodes, n_pods, what in plan:
+            whole, b = v.workload.make_config(cfg, n_nodes, n_pods)
+            lo, hi = v.sharding.shard_range(whole.n_nodes, world, rank)
+            lg = Leg(v, torch, dist, local, rank, world, whole.rows(lo, hi), b, whole.n_nodes)
+            ms, k1c, ln = lg.timed(steps_c, warm_c, flush)
+            rs, pk = lg.ctx.results_download()
+            pl = lg.ctx.plan()
+            rec = {"workload": what, "nodes_total": whole.n_nodes, "pods": b.n_pods, "requests": b.n_reqs,
+                   "ms_per_step": ms, "value": b.n_pods * whole.n_nodes / (ms * 1e-3), "unit": UNIT, "k1_ms": k1c,
+                   "steps": steps_c, "gpu_launches": ln, "scaling": "strong" if world > 1 else "single GPU",
+                   "kernels": [["none", "pair", "sliced", "general"][pl.cls[i].kernel] for i in range(4)],
+                   "class_pods": [pl.cls[i].pods for i in range(4)]}
+            if rank == 0:
+                rec["check"] = sampled_check(v, np, whole, b, rs, pk)
+            configs[name] = rec
+            lg.close()
+            del whole, lg
 
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
 
-    check = None
-    if args.check:
-        import oracle
-        shards = [v.workload.make_snapshot(npg, v.workload.SEED + int(args.config[3:]) + 1000 * r) for r in range(world)]
-        whole = v.Snapshot(np.concatenate([s_.planes for s_ in shards], axis=1),
-                           np.concatenate([s_.ndev for s_ in shards]), snap.type_names)
-        idx = list(range(0, P, max(1, P // 48)))
-        want = oracle.score_packed(whole, batch.select(idx))
-        pb = batch.pick_begin
-        ok = (np.array_equal(results["best_row"][idx], want.best_row)
-              and np.array_equal(results["score"][idx].view(np.uint32), want.score.view(np.uint32))
-              and np.array_equal(results["fit_count"][idx], want.fit_count))
-        got_picks = np.concatenate([np.stack([picks["slot"], picks["usedmem"], picks["usedcores"]], axis=1)
-                                    [int(pb[batch.pod_req_range(p)[0]]):int(pb[batch.pod_req_range(p)[1]])] for p in idx])
-        ok = ok and np.array_equal(got_picks, want.picks)
-        check = {"pods_checked": len(idx), "nodes": whole.n_nodes, "bit_exact_vs_oracle": bool(ok)}
-        if not ok:
-            print(json.dumps({"error": "sharded result differs from the oracle", "check": check}), flush=True)
+    check = sampled_check(v, np, whole_snapshot(v, np, make_shard, world), batch, results, picks)
+    if not check["bit_exact_vs_oracle"]:
+        print(json.dumps({"error": "result differs from the oracle", "check": check}), flush=True)
+        raise SystemExit(3)
+    for name, rec in configs.items():
+        if not rec["check"]["bit_exact_vs_oracle"]:
+            print(json.dumps({"error": f"{name}: result differs from the oracle", "check": rec["check"]}), flush=True)
             raise SystemExit(3)
 
-    peak, peak_src = measured_peak()
     abytes = algorithmic_bytes(npg, D, P, R)
     achieved = abytes / (k1_ms * 1e-3) / 1e9
-    traffic = None
-    try:
-        with open(os.path.join(ROOT, "profiles", "k1_traffic.json")) as f:
-            traffic = json.load(f).get("dram_bytes_per_launch")
-    except Exception:
-        pass
+    props = torch.cuda.get_device_properties(local)
+    sm_hz = 1e6 * float(clocks.get("sm_mhz") or clocks.get("sm_max_mhz") or 1965.0)
+    issue_peak = props.multi_processor_count * 4 * sm_hz
+    winst = (prof or {}).get("k1_warp_instructions_per_step") if (args.config == "cfg3" and npg == NODES_PER_GPU and P == N_PODS) else None
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "int32", "data": "synthetic",
-        "config": {"workload": WORKLOAD if args.config == "cfg3" else args.config, "nodes_per_gpu": npg,
+        "config": {"workload": WORKLOAD if args.config == "cfg3" else f"{args.config}: {npg} nodes per GPU x {P} pods",
+                   "nodes_per_gpu": npg,
                    "nodes_total": n_total, "devices_per_node": D, "pods": P, "requests": R,
                    "parallelism": f"node-shard x{world}", "l2": "256 MiB memset between steps (untimed)",
                    "placed_pods": placed},
         "e2e": e2e,
         "gpu_launches": int(launches),
         "clocks": clocks,
-        "roofline": {"bound": "hbm", "kernel": "K1 phase of one step (K1p collect/sort/classify, k1_score_sliced<1>, <2> scouts + main, k1_score_nodesliced)",
+        "roofline": {"bound": "hbm", "kernel": "K1 phase of one step (every score launch between the K0 and K3 events)",
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes": int(abytes),
+                     "traffic": (prof or {}).get("k1_dram_bytes_per_step") if winst else None,
+                     "peak_source": peak_src, "algorithmic_bytes": int(abytes),
                      "kernel_ms": k1_ms,
+                     # SURVEY 8(d) "always": warp instructions of the K1 phase (ncu launch list of this command,
+                     # file named below) / K1 time of THIS run / (SMs x 4 schedulers x SM clock sampled in this run)
+                     "issue_fraction": (winst / (k1_ms * 1e-3) / issue_peak) if winst else None,
+                     "warp_instructions": winst, "issue_peak_per_s": issue_peak,
+                     "profile": (prof or {}).get("file"), "profile_tree": (prof or {}).get("tree"),
                      "note": "batch regime is instruction-issue bound, not HBM bound (SURVEY F6, DESIGN.md 4)"},
         "device_evals_per_s": P * n_total * D / (ms_per_step * 1e-3),
+        "check": check,
     }
-    if check:
-        line["check"] = check
+    if e2e_delta:
+        line["e2e_delta"] = e2e_delta
+    if configs:
+        line["configs"] = configs
     if latency:
         line["filter_latency"] = latency
     if hbm_regime:
         line["roofline_hbm_regime"] = hbm_regime
-    if not args.no_cpu and world == 1:  # a reported baseline, measured once (N = 1)
+    if not args.no_cpu and world == 1:  # reported baselines, measured once (N = 1), bounded samples
+        import oracle
         val, th, dt, sp = cpu_arm(snap, batch, 64)   # calibrate
         sample = max(64, min(P, int(64 * 12.0 / max(dt, 1e-3))))
         val, th, dt, sp = cpu_arm(snap, batch, sample)
         line["cpu_baseline"] = {"value": val, "unit": UNIT, "cores": th, "kind": "port",
                                 "sample": f"first {sp} of {P} pods x all {npg} nodes ({dt:.1f} s), oracle packed "
-                                          "restatement; reference Go not runnable here"}
+                                          "restatement (R2); reference Go not runnable here"}
+        # R1: the reference's own shape (pointers to structs, string checkType per device, one thread), and
+        # R1-io: the same with the reference's per-device log lines formatted and written to /dev/null
+        rows = {}
+        for key, io, budget in (("r1_faithful_single_thread", False, 4.0), ("r1_io_with_log_lines", True, 4.0)):
+            r = oracle.score_faithful(snap, batch.select([0]), log_io=io)
+            n = max(1, min(32, int(budget / max(r.seconds_scoring, 1e-4))))
+            r = oracle.score_faithful(snap, batch.select(list(range(n))), log_io=io)
+            rows[key] = {"value": n * npg / r.seconds_scoring, "unit": UNIT, "cores": 1,
+                         "sample": f"first {n} pods x all {npg} nodes ({r.seconds_scoring:.1f} s)",
+                         "snapshot_rebuild_s_per_filter": r.seconds_rebuild / n}
+        line["cpu_baseline"]["other_rows"] = rows
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
