@@ -2,6 +2,8 @@
 // it cites; the only call into the GPU library is calcScoreGPU.
 #include "scheduler.hpp"
 
+#include <chrono>
+#include <unordered_set>
 #include <algorithm>
 #include <cstring>
 #include <ctime>
@@ -233,14 +235,23 @@ void Scheduler::onDelPod(const Pod &pod) {
 
 void Scheduler::queueDelta(const std::string &nodeID, const PodDevices &devs, int sign) {
     if (!incremental_) return;
-    auto row = resident_row_.find(nodeID);
     auto node = nodes_.find(nodeID);
-    if (row == resident_row_.end() || node == nodes_.end()) return; // next Filter uploads in full
+    if (node == nodes_.end()) return;
+    auto row = resident_row_.find(nodeID); // not a row of the resident snapshot: only the usage view follows
+    // the resident copy of getNodesUsage's result (what /metrics reads, scheduler.go:232-234) follows the
+    // same events, so that a Filter on the resident path does not have to rebuild it
+    auto ov = overviewstatus_.find(nodeID);
     for (const ContainerDevices &cd : devs)
         for (const ContainerDevice &u : cd)
             for (size_t s = 0; s < node->second.Devices.size(); s++)
-                if (node->second.Devices[s].ID == u.UUID) // same match as scheduler.go:287-293
-                    pending_.push_back({row->second, (int32_t)s, sign, sign * u.Usedmem, sign * u.Usedcores});
+                if (node->second.Devices[s].ID == u.UUID) { // same match as scheduler.go:287-293
+                    if (row != resident_row_.end())
+                        pending_.push_back({row->second, (int32_t)s, sign, sign * u.Usedmem, sign * u.Usedcores});
+                    if (ov != overviewstatus_.end() && s < ov->second.Devices.size()) {
+                        DeviceUsage &d = *ov->second.Devices[s];
+                        d.Used += sign, d.Usedmem += sign * u.Usedmem, d.Usedcores += sign * u.Usedcores;
+                    }
+                }
 }
 
 void Scheduler::addPod(const Pod &pod, const std::string &nodeID, const PodDevices &devices) {
@@ -344,7 +355,11 @@ bool Scheduler::uploadSnapshot(const std::vector<std::string> &order, const std:
 }
 
 // ---- calcScore (score.go:183-214) + pick (scheduler.go:386-387), on the GPU -----------------------
-bool Scheduler::calcScoreGPU(const std::vector<std::string> &order, const std::map<std::string, NodeUsage *> &nodes,
+static double now_us() {
+    return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+bool Scheduler::calcScoreGPU(const std::vector<std::string> &order, const std::map<std::string, NodeUsage *> *nodes,
                              const std::vector<std::vector<ContainerDeviceRequest>> &nums,
                              const std::map<std::string, std::string> &annos, NodeScore *winner, bool *found,
                              std::string *err) {
@@ -358,20 +373,26 @@ bool Scheduler::calcScoreGPU(const std::vector<std::string> &order, const std::m
         return false;
     }
     // snapshot: resident + deltas when nothing but pod usage changed, else a full upload
-    if (incremental_ && resident_epoch_ == node_epoch_ && resident_order_ == order) {
+    double t_gpu = 0.0, t0;
+    if (!nodes || (incremental_ && resident_epoch_ == node_epoch_ && resident_order_ == order)) {
         if (!pending_.empty()) {
+            t0 = now_us();
             std::vector<vgs_delta> d(pending_.size());
             for (size_t i = 0; i < pending_.size(); i++)
                 d[i] = vgs_delta{pending_[i].row, pending_[i].slot, pending_[i].used, pending_[i].mem, pending_[i].cores};
             int rc = vgs_snapshot_delta(ctx_, (int32_t)d.size(), d.data());
+            t_gpu += now_us() - t0;
             if (rc != VGS_OK) {
                 *err = std::string(vgs_strerror(rc)) + ": " + vgs_last_error(ctx_);
                 return false;
             }
             pending_.clear();
         }
-    } else if (!uploadSnapshot(order, nodes, err)) {
-        return false;
+    } else {
+        t0 = now_us();
+        const bool ok = uploadSnapshot(order, *nodes, err);
+        t_gpu += now_us() - t0; // (includes packing the planes)
+        if (!ok) return false;
     }
     // requests: the string policy (checkType, score.go:71-84) evaluated once per distinct type
     auto anno = [&](const char *k) -> const char * {
@@ -406,7 +427,9 @@ bool Scheduler::calcScoreGPU(const std::vector<std::string> &order, const std::m
     vgs_pod pod{0, (int32_t)reqs.size()};
     vgs_result res;
     std::vector<vgs_pick> picks(std::max(total, 1));
+    t0 = now_us();
     int rc = vgs_score_batch(ctx_, 1, &pod, (int32_t)reqs.size(), reqs.data(), &res, picks.data());
+    timing_.gpu_us = t_gpu + (now_us() - t0);
     if (rc != VGS_OK) {
         *err = std::string(vgs_strerror(rc)) + ": " + vgs_last_error(ctx_);
         return false;
@@ -416,14 +439,14 @@ bool Scheduler::calcScoreGPU(const std::vector<std::string> &order, const std::m
     winner->nodeID = order[res.best_row];
     winner->score = res.score;
     winner->devices.clear();
-    const DeviceUsageList &devs = nodes.at(winner->nodeID)->Devices;
+    const std::vector<DeviceInfo> &devs = nodes_.at(winner->nodeID).Devices; // registration order == slot
     size_t i = 0;
     for (size_t ctr = 0; ctr < nums.size(); ctr++) { // util.PodDevices: one list per container (score.go:196,201)
         ContainerDevices cd;
         for (const ContainerDeviceRequest &k : nums[ctr])
             for (int j = 0; j < k.Nums; j++, i++) {
                 ContainerDevice c;
-                c.UUID = devs[picks[i].slot]->Id, c.Type = k.Type;
+                c.UUID = devs[picks[i].slot].ID, c.Type = k.Type;
                 c.Usedmem = picks[i].usedmem, c.Usedcores = picks[i].usedcores;
                 cd.push_back(c);
             }
@@ -443,15 +466,37 @@ bool Scheduler::Filter(const ExtenderArgs &args, ExtenderFilterResult *res, std:
         res->NodeNames = args.NodeNames;
         return true;
     }
+    const double t_begin = now_us();
+    timing_ = FilterTiming();
     delPod(args.pod); // :372
-    std::map<std::string, NodeUsage *> nodeUsage;
-    getNodesUsage(args.NodeNames, &nodeUsage, &res->FailedNodes);
-    std::vector<std::string> order; // rows = args.NodeNames order, registered nodes only
-    for (const std::string &id : args.NodeNames)
-        if (nodeUsage.count(id) && std::find(order.begin(), order.end(), id) == order.end()) order.push_back(id);
     NodeScore m;
     bool found = false;
-    if (!calcScoreGPU(order, nodeUsage, nums, args.pod.Annotations, &m, &found, err)) return false; // :378-380
+    // Resident path: the node registry has not changed since the upload and kube-scheduler
+    // sends the same candidate list -> the packed snapshot on the GPU, its row order, the per-node usage view
+    // and the "unregistered" entries are all still valid; pod events since then are queued deltas.  Nothing of
+    // getNodesUsage (scheduler.go:249-310: N x D allocations + a pods x devices UUID scan) is redone.
+    const bool fast = incremental_ && ctx_ && resident_epoch_ == node_epoch_ && args.NodeNames == resident_names_;
+    timing_.fast = fast;
+    bool ok;
+    if (fast) {
+        res->FailedNodes = resident_failed_;
+        ok = calcScoreGPU(resident_order_, nullptr, nums, args.pod.Annotations, &m, &found, err);
+    } else {
+        std::map<std::string, NodeUsage *> nodeUsage;
+        getNodesUsage(args.NodeNames, &nodeUsage, &res->FailedNodes);
+        std::vector<std::string> order; // rows = args.NodeNames order, registered nodes only, each once
+        std::unordered_set<std::string> seen;
+        order.reserve(args.NodeNames.size());
+        for (const std::string &id : args.NodeNames)
+            if (nodeUsage.count(id) && seen.insert(id).second) order.push_back(id);
+        ok = calcScoreGPU(order, &nodeUsage, nums, args.pod.Annotations, &m, &found, err);
+        if (ok && incremental_) {
+            resident_names_ = args.NodeNames;
+            resident_failed_ = res->FailedNodes;
+        }
+    }
+    timing_.total_us = now_us() - t_begin;
+    if (!ok) return false; // :378-380
     if (!found) return true; // :381-385 ExtenderFilterResult{FailedNodes}
     std::map<std::string, std::string> &a = res->PatchedAnnotations; // :388-393
     a[AssignedNodeAnnotations] = m.nodeID;
@@ -487,6 +532,11 @@ void vgh_add_node(void *s, const char *node_id, int n, const char *const *ids, c
         info.Devices.push_back(d);
     }
     static_cast<vgpu::Scheduler *>(s)->addNode(node_id, info);
+}
+
+void vgh_last_timing(void *s, double *total_us, double *gpu_us, int *fast) {
+    const vgpu::Scheduler::FilterTiming &t = static_cast<vgpu::Scheduler *>(s)->lastTiming();
+    *total_us = t.total_us, *gpu_us = t.gpu_us, *fast = t.fast ? 1 : 0;
 }
 
 void vgh_del_pod(void *s, const char *uid) {

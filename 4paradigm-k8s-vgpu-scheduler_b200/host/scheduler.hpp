@@ -16,6 +16,7 @@
 #include <map>
 #include <memory>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 struct vgs_ctx;
@@ -148,13 +149,18 @@ class Scheduler {
     bool Filter(const ExtenderArgs &args, ExtenderFilterResult *res, std::string *err);
 
     const std::map<std::string, NodeUsage> &InspectAllNodesUsage() const { return overviewstatus_; } // :232-234
+    // wall time of the last Filter: the whole call, and the part spent inside libvgpuscore calls (microseconds);
+    // fast = it took the resident path (no getNodesUsage rebuild, no snapshot upload)
+    struct FilterTiming { double total_us = 0, gpu_us = 0; bool fast = false; };
+    const FilterTiming &lastTiming() const { return timing_; }
 
   private:
     // scheduler.go:249-310
     void getNodesUsage(const std::vector<std::string> &nodes, std::map<std::string, NodeUsage *> *cache,
                        std::map<std::string, std::string> *failedNodes);
     // score.go:183-214 + scheduler.go:386-387 on the GPU: winner or nullptr-equivalent (found = false)
-    bool calcScoreGPU(const std::vector<std::string> &order, const std::map<std::string, NodeUsage *> &nodes,
+    // (nodes == nullptr: the resident path -- snapshot and row order are the ones of the last upload)
+    bool calcScoreGPU(const std::vector<std::string> &order, const std::map<std::string, NodeUsage *> *nodes,
                       const std::vector<std::vector<ContainerDeviceRequest>> &nums,
                       const std::map<std::string, std::string> &annos, NodeScore *winner, bool *found,
                       std::string *err);
@@ -172,7 +178,10 @@ class Scheduler {
     std::vector<std::string> types_;               // distinct DeviceUsage.Type strings
     std::map<std::string, int32_t> type_id_;
     std::vector<std::string> resident_order_;      // rows of the resident snapshot
-    std::map<std::string, int32_t> resident_row_;
+    std::unordered_map<std::string, int32_t> resident_row_;
+    std::vector<std::string> resident_names_;      // args.NodeNames of the Filter that uploaded it, verbatim
+    std::map<std::string, std::string> resident_failed_; // ... and its "node unregisterd" entries
+    FilterTiming timing_;
     uint64_t node_epoch_ = 0, resident_epoch_ = ~0ull;
     struct Delta { int32_t row, slot, used, mem, cores; };
     std::vector<Delta> pending_;                   // usage changes since the last upload

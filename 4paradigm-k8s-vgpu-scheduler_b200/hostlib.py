@@ -35,6 +35,7 @@ def load():
         lib.vgh_filter.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int, C.POINTER(C.c_char_p),
                                    C.POINTER(C.c_char_p), C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_char_p),
                                    C.c_char_p, C.c_int]
+        lib.vgh_last_timing.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_int)]
         _lib = lib
     return _lib
 
@@ -63,6 +64,12 @@ class Scheduler:
         cnt, mem, core, numa = arr("Count"), arr("Devmem"), arr("Devcore"), arr("Numa")
         self.lib.vgh_add_node(self.h, node_id.encode(), n, _strs([d["ID"] for d in devices]), cnt.ctypes.data,
                               mem.ctypes.data, core.ctypes.data, _strs([d["Type"] for d in devices]), numa.ctypes.data)
+
+    def last_timing(self):
+        """(total microseconds of the last Filter, microseconds inside libvgpuscore calls, took the resident path)"""
+        t, g, f = C.c_double(), C.c_double(), C.c_int()
+        self.lib.vgh_last_timing(self.h, C.byref(t), C.byref(g), C.byref(f))
+        return t.value, g.value, bool(f.value)
 
     def del_pod(self, uid: str):
         self.lib.vgh_del_pod(self.h, uid.encode())

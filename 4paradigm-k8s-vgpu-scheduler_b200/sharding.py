@@ -87,7 +87,8 @@ class ShardedScorer:
     extender would do with one context per GPU inside a single process."""
 
     def __init__(self, n_nodes_total: int, dmax: int, max_pods: int, max_reqs: Optional[int] = None,
-                 max_picks: Optional[int] = None, device: int = 0, rank: int = 0, world: int = 1, group=None):
+                 max_picks: Optional[int] = None, device: int = 0, rank: int = 0, world: int = 1, group=None,
+                 tuning=None):
         import torch
 
         from .capi import Context
@@ -103,7 +104,8 @@ class ShardedScorer:
         stream = self.stream.cuda_stream
         assert stream != 0
         self.ctx = Context(max_nodes=max(self.hi - self.lo, 1), max_devices=dmax, max_pods=max_pods,
-                           max_reqs=max_reqs, max_picks=max_picks, device=device, row_base=self.lo, stream=stream)
+                           max_reqs=max_reqs, max_picks=max_picks, device=device, row_base=self.lo, stream=stream,
+                           tuning=tuning)
         self.max_pods = max_pods
         self.max_picks = self.ctx.cfg.max_picks
         # exchange block = [keys | counts | picks] in one allocation: ONE all-gather per pass moves every

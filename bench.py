@@ -265,6 +265,8 @@ def sampled_check(v, np, snap_whole, batch, results, picks, n_sample=48):
 class Leg:
     """one resident workload on this rank's shard: context, pinned planes, device-timed steps"""
 
+    tuning = None  # vgs_tuning overrides (--tuning), A/B runs only
+
     def __init__(self, v, torch, dist, local, rank, world, snap, batch, n_total, row_lo=None):
         self.v, self.torch, self.dist, self.world, self.rank = v, torch, dist, world, rank
         self.snap, self.batch = snap, batch
@@ -272,7 +274,8 @@ class Leg:
         self.n_picks = int(self.reqs["nums"].sum())
         P, R = len(self.pods), len(self.reqs)
         self.sc = v.sharding.ShardedScorer(n_total, snap.dmax, max_pods=P, max_reqs=max(R, P),
-                                           max_picks=max(self.n_picks, R), device=local, rank=rank, world=world)
+                                           max_picks=max(self.n_picks, R), device=local, rank=rank, world=world,
+                                           tuning=Leg.tuning)
         assert self.sc.hi - self.sc.lo == snap.n_nodes, (self.sc.lo, self.sc.hi, snap.n_nodes)
         self.ctx = self.sc.ctx
         self.pin_planes = torch.from_numpy(snap.planes).pin_memory()
@@ -350,6 +353,7 @@ def main():
     ap.add_argument("--no-hbm-leg", action="store_true", help="skip the single-pod 1M-node (HBM-bound regime) leg")
     ap.add_argument("--no-configs", action="store_true", help="skip the other BASELINE configs (cfg2 / cfg4 / cfg5)")
     ap.add_argument("--check", action="store_true", help="(kept for old command lines: the oracle check always runs)")
+    ap.add_argument("--tuning", default="", help="vgs_tuning overrides for A/B runs, e.g. early_scouts=0,scout_split=4")
     ap.add_argument("--sweep", action="store_true", help="CPU/GPU crossover grid instead of the bench line")
     ap.add_argument("--sweep-nodes", default="64,512,4096,32768,100000,1000000")
     ap.add_argument("--sweep-pods", default="1,16,256,4096")
@@ -360,6 +364,8 @@ def main():
     if args.sweep:
         return run_sweep(args)
     args.warmup = max(args.warmup, 3)
+    if args.tuning:
+        Leg.tuning = {k: int(x) for k, x in (kv.split("=") for kv in args.tuning.split(","))}
 
     import numpy as np
     import torch

@@ -145,6 +145,42 @@ def test_filter_sequence_matches_reference_flow(built, incremental):
 
 
 @pytest.mark.gpu
+def test_incremental_filter_skips_the_rebuild_at_100k_nodes(built):
+    """SURVEY 8(f) rank 1 on the host side: with the snapshot resident, a Filter must not redo getNodesUsage
+    (scheduler.go:249-310).  100k registered nodes, a few hundred scheduled pods: the first Filter uploads, every
+    later one takes the resident path (deltas only) and its host time is a small fraction of the rebuild's; both
+    modes place the pods on the same nodes with the same devices."""
+    N = 100_000
+    rng = np.random.default_rng(5)
+    names = [f"node-{i:06d}" for i in range(N)]
+    devs = lambda i: [dict(ID=f"GPU-{i}-{s}", Count=10, Devmem=32768 if i % 3 else 16384, Devcore=100,
+                           Type="NVIDIA-Tesla V100-PCIE-32GB" if i % 3 else "NVIDIA-Tesla T4", Numa=s // 4) for s in range(8)]
+    out = {}
+    for incremental in (False, True):
+        sch = v.hostlib.Scheduler(max_nodes=N, incremental=incremental)
+        for i, n in enumerate(names):
+            sch.add_node(n, devs(i))
+        placed, times = [], []
+        for k in range(12):
+            got = sch.filter(f"pod-{k}", [{"gpu": 1 + k % 2, "gpumem": 3000 + 500 * (k % 5), "gpucores": 10 * (k % 4)}], {}, names)
+            total_us, gpu_us, fast = sch.last_timing()
+            placed.append((got["node"], got["ids"]))
+            times.append((total_us, gpu_us, fast))
+            assert got["node"] is not None
+        sch.close()
+        out[incremental] = (placed, times)
+    assert out[False][0] == out[True][0]                       # same placements either way
+    assert not any(f for _, _, f in out[False][1])             # rebuild mode never takes the resident path
+    assert [f for _, _, f in out[True][1]] == [False] + [True] * 11
+    rebuild = np.median([t - g for t, g, _ in out[False][1][1:]])      # host time outside libvgpuscore
+    resident = np.median([t - g for t, g, _ in out[True][1][1:]])
+    print(f"host us per Filter at {N} nodes: rebuild {rebuild:.0f}, resident {resident:.0f}; "
+          f"total rebuild {np.median([t for t, _, _ in out[False][1][1:]]):.0f}, "
+          f"resident {np.median([t for t, _, _ in out[True][1][1:]]):.0f}")
+    assert resident * 10 < rebuild
+
+
+@pytest.mark.gpu
 def test_filter_edge_behaviour(built):
     sch = v.hostlib.Scheduler(max_nodes=8)
     sch.add_node("n0", [dict(ID=f"U{s}", Count=10, Devmem=32768, Devcore=100, Type="NVIDIA-Tesla V100", Numa=0) for s in range(8)])
