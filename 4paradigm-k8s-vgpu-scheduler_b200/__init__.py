@@ -7,4 +7,4 @@ Python identifier; import it through ``vgpu_b200`` (repo root, ``vgpu_b200.py``)
 """
 from .model import (ANNO_NOUSE, ANNO_NUMA, ANNO_USE, MEMPCT_UNSET, BatchResult, PodBatch, Snapshot)  # noqa: F401
 from . import capi, hostlib, sharding, workload  # noqa: F401
-from .capi import Context, VgsError, load_library  # noqa: F401
+from .capi import Context, Group, VgsError, load_library  # noqa: F401

@@ -34,6 +34,8 @@ EXPORTS = (
     "vgs_verify_download", "vgs_last_timing", "vgs_host_typemask", "vgs_host_numa_bind",
     "vgs_host_encode_pod_devices", "vgs_host_decode_node_devices", "vgs_score_batch_noalloc",
     "vgs_tuning_defaults", "vgs_last_plan",
+    "vgs_group_init", "vgs_group_destroy", "vgs_group_last_error", "vgs_group_snapshot_upload",
+    "vgs_group_snapshot_type_flags", "vgs_group_snapshot_delta", "vgs_group_score_batch", "vgs_group_last_timing",
 )
 
 
@@ -64,6 +66,14 @@ class VgsPlan(C.Structure):
 
 
 KERNEL_NONE, KERNEL_PAIR, KERNEL_SLICED, KERNEL_GENERAL = range(4)
+VGS_ENCCL = -9
+EXCHANGE_NCCL, EXCHANGE_PEER = 0, 1
+
+
+class VgsGroupConfig(C.Structure):
+    _fields_ = [("n_devices", C.c_int32), ("devices", C.c_int32 * 8), ("max_nodes", C.c_int32),
+                ("max_devices", C.c_int32), ("max_pods", C.c_int32), ("max_reqs", C.c_int32), ("max_picks", C.c_int32),
+                ("exchange", C.c_int32), ("tuning", C.POINTER(VgsTuning))]
 
 
 class VgsTiming(C.Structure):
@@ -136,6 +146,16 @@ def load_library() -> C.CDLL:
     lib.vgs_verify_download.argtypes = [vp, vp, vp]
     lib.vgs_last_timing.argtypes = [vp, C.POINTER(VgsTiming)]
     lib.vgs_last_plan.argtypes = [vp, C.POINTER(VgsPlan)]
+    lib.vgs_group_init.argtypes = [C.POINTER(VgsGroupConfig), C.POINTER(vp)]
+    lib.vgs_group_destroy.argtypes = [vp]
+    lib.vgs_group_destroy.restype = None
+    lib.vgs_group_last_error.argtypes = [vp]
+    lib.vgs_group_last_error.restype = C.c_char_p
+    lib.vgs_group_snapshot_upload.argtypes = [vp, i32, i32, C.POINTER(vp), vp]
+    lib.vgs_group_snapshot_type_flags.argtypes = [vp, i32, vp]
+    lib.vgs_group_snapshot_delta.argtypes = [vp, i32, vp]
+    lib.vgs_group_score_batch.argtypes = [vp, i32, vp, i32, vp, vp, vp]
+    lib.vgs_group_last_timing.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     lib.vgs_tuning_defaults.argtypes = [C.POINTER(VgsTuning)]
     lib.vgs_tuning_defaults.restype = None
     lib.vgs_score_batch_noalloc.argtypes = [i32, vp, i32, i32, i32, C.POINTER(vp), vp, i32, vp, i32, vp, vp, vp]
@@ -484,3 +504,71 @@ class Context:
         t = VgsTiming()
         self._check(self.lib.vgs_last_timing(self.h, C.byref(t)))
         return t
+
+
+class Group:
+    """vgs_group_*: the node set sharded over several GPUs of one box inside the library (one process, one host
+    thread), exchange by NCCL all-gather or by peer-mapped stores.  Same calls as a Context."""
+
+    def __init__(self, devices: List[int], max_nodes: int, max_devices: int = 8, max_pods: int = 4096,
+                 max_reqs: Optional[int] = None, max_picks: Optional[int] = None, exchange: int = EXCHANGE_NCCL,
+                 tuning: Optional[Dict[str, int]] = None):
+        self.lib = load_library()
+        max_reqs = max_reqs or max_pods * 4
+        max_picks = max_picks or max_reqs * 4
+        tune = VgsTuning()
+        self.lib.vgs_tuning_defaults(C.byref(tune))
+        for k, val in (tuning or {}).items():
+            setattr(tune, k, int(val))
+        self._tune = tune
+        cfg = VgsGroupConfig(len(devices), (C.c_int32 * 8)(*devices), max(max_nodes, 1), max_devices, max_pods, max_reqs,
+                             max_picks, exchange, C.pointer(tune))
+        self.h = C.c_void_p()
+        rc = self.lib.vgs_group_init(C.byref(cfg), C.byref(self.h))
+        if rc != VGS_OK:
+            raise VgsError(rc, self.lib.vgs_strerror(rc).decode())
+
+    def close(self):
+        if getattr(self, "h", None) and self.h.value:
+            self.lib.vgs_group_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _check(self, rc: int):
+        if rc != VGS_OK:
+            raise VgsError(rc, f"{self.lib.vgs_strerror(rc).decode()}: {self.lib.vgs_group_last_error(self.h).decode()}")
+
+    def upload(self, snap: Snapshot):
+        flags = np.ascontiguousarray([host_type_flags(t) for t in snap.type_names], dtype=np.uint32)
+        self._check(self.lib.vgs_group_snapshot_type_flags(self.h, len(flags), flags.ctypes.data if len(flags) else None))
+        ptrs = (C.c_void_p * 8)(*[snap.planes[f].ctypes.data for f in range(8)])
+        self._check(self.lib.vgs_group_snapshot_upload(self.h, snap.n_nodes, snap.dmax, ptrs, snap.ndev.ctypes.data))
+        self.type_names = snap.type_names
+
+    def delta(self, deltas: np.ndarray):
+        deltas = np.ascontiguousarray(deltas, dtype=DELTA_DTYPE)
+        self._check(self.lib.vgs_group_snapshot_delta(self.h, len(deltas), deltas.ctypes.data))
+
+    def score_packed(self, pods: np.ndarray, reqs: np.ndarray):
+        results = np.zeros(len(pods), dtype=RESULT_DTYPE)
+        picks = np.zeros(int(reqs["nums"].sum()) if len(reqs) else 0, dtype=PICK_DTYPE)
+        self._check(self.lib.vgs_group_score_batch(self.h, len(pods), pods.ctypes.data, len(reqs), reqs.ctypes.data,
+                                                   results.ctypes.data, picks.ctypes.data))
+        return results, picks
+
+    def score(self, batch: PodBatch) -> BatchResult:
+        pods, reqs = pack_batch(batch, self.type_names)
+        r, pk = self.score_packed(pods, reqs)
+        return BatchResult(r["best_row"].copy(), r["score"].copy(), r["fit_count"].copy(), r["n_picks"].copy(),
+                           np.stack([pk["slot"], pk["usedmem"], pk["usedcores"]], axis=1) if len(pk)
+                           else np.zeros((0, 3), np.int32))
+
+    def timing(self):
+        t, x = C.c_double(), C.c_double()
+        self._check(self.lib.vgs_group_last_timing(self.h, C.byref(t), C.byref(x)))
+        return t.value, x.value

@@ -256,6 +256,7 @@ const char *vgs_strerror(int status) {
     case VGS_ESTATE: return "call sequence error";
     case VGS_EINTERNAL: return "internal self-check failed";
     case VGS_ELIMIT: return "larger than the fixed VGS_NOALLOC_MAX_* limits of vgs_score_batch_noalloc";
+    case VGS_ENCCL: return "NCCL unavailable or collective failed";
     default: return "unknown status";
     }
 }

@@ -268,6 +268,45 @@ int vgs_exchange_merge(vgs_ctx *ctx, const void *dev_gathered, int32_t n_shards,
 /* device arrays behind vgs_results_download (shard combine of results/picks) */
 int vgs_results_device(vgs_ctx *ctx, vgs_result **dev_results, vgs_pick **dev_picks);
 
+/* ---- node sharding inside the library: several GPUs of one box behind one handle --------------------
+ * (No counterpart in the reference.)  One process, one host thread, one context per GPU; GPU g owns the
+ * contiguous rows [g * ceil(N/G), (g+1) * ceil(N/G)) of the snapshot.  A pass scores
+ * every shard with no collective, every shard resolves its own best node per pod, and the shards'
+ * [keys | counts | picks] blocks (vgs_exchange_block) are combined by ONE exchange:
+ *   VGS_EXCHANGE_NCCL  ncclAllGather over NVLink (libnccl.so.2 is opened at vgs_group_init; absent
+ *                      library -> VGS_ENCCL).  One communicator per GPU (ncclCommInitAll).
+ *   VGS_EXCHANGE_PEER  every shard copies its block into the first GPU's gather buffer with ordinary
+ *                      peer-mapped stores (cudaDeviceEnablePeerAccess), ordered by events; no collective
+ *                      launch.  Also the mode that works with several shards on ONE GPU (tests).
+ * The first GPU merges (max key = max score, then highest global row: the single-GPU canonical winner) and
+ * holds the results.  Same inputs and outputs as vgs_snapshot_upload / _delta / vgs_score_batch. */
+#define VGS_ENCCL (-9) /* NCCL unavailable or a collective failed (vgs_group_last_error has the text) */
+#define VGS_MAX_GROUP 8
+enum { VGS_EXCHANGE_NCCL = 0, VGS_EXCHANGE_PEER = 1 };
+typedef struct vgs_group vgs_group;
+typedef struct {
+    int32_t n_devices;                  /* 1..VGS_MAX_GROUP shards */
+    int32_t devices[VGS_MAX_GROUP];     /* CUDA ordinal of each shard (repeats allowed with VGS_EXCHANGE_PEER) */
+    int32_t max_nodes;                  /* rows of the WHOLE snapshot */
+    int32_t max_devices, max_pods, max_reqs, max_picks; /* as in vgs_config */
+    int32_t exchange;                   /* VGS_EXCHANGE_* */
+    const vgs_tuning *tuning;           /* NULL = defaults */
+} vgs_group_config;
+int vgs_group_init(const vgs_group_config *cfg, vgs_group **out);
+void vgs_group_destroy(vgs_group *g);
+const char *vgs_group_last_error(vgs_group *g);
+/* planes of the whole node set, as for vgs_snapshot_upload; the library hands every GPU its row range */
+int vgs_group_snapshot_upload(vgs_group *g, int32_t n_nodes, int32_t dmax, const int32_t *const planes[VGS_NUM_PLANES],
+                              const int32_t *ndev);
+int vgs_group_snapshot_type_flags(vgs_group *g, int32_t n_types, const uint32_t *flags);
+/* deltas name GLOBAL rows; every shard applies the ones it owns */
+int vgs_group_snapshot_delta(vgs_group *g, int32_t n, const vgs_delta *deltas);
+int vgs_group_score_batch(vgs_group *g, int32_t n_pods, const vgs_pod *pods, int32_t n_reqs, const vgs_req *reqs,
+                          vgs_result *results, vgs_pick *picks);
+/* wall-clock microseconds of the last vgs_group_score_batch and, of that, the part after the last shard's
+ * score kernels were queued (exchange + merge + download) */
+int vgs_group_last_timing(vgs_group *g, double *total_us, double *exchange_us);
+
 /* ---- scoring without any GPU allocation --------------------------------------
  * (No counterpart in the reference: the Go extender never touches a GPU.)
  *
