@@ -568,12 +568,52 @@ def main():
             lg.close()
             del whole, lg
 
+    # ---- the same sharded pass through vgs_group_* : ONE process (rank 0) driving all N GPUs, exchange by NCCL
+    # all-gather and by peer-mapped stores.  The other ranks wait on the rendezvous store (a CPU wait: an NCCL
+    # barrier would keep their GPUs spinning).  Wall clock per vgs_group_score_batch call, snapshot resident.
+    group = None
+    whole = None
+    if world > 1 and args.config == "cfg3" and not args.no_configs:
+        if not configs:
+            leg.close()
+        torch.cuda.synchronize()
+        store = dist.distributed_c10d._get_default_store()
+        if rank == 0:
+            whole = whole_snapshot(v, np, make_shard, world)
+            group = {}
+            for name, ex in (("nccl", v.capi.EXCHANGE_NCCL), ("peer", v.capi.EXCHANGE_PEER)):
+                try:
+                    with v.Group(list(range(world)), max_nodes=whole.n_nodes, max_devices=D, max_pods=P, max_reqs=max(R, P),
+                                 max_picks=max(n_picks, R), exchange=ex) as g:
+                        g.upload(whole)
+                        for _ in range(3):
+                            rg, pg = g.score_packed(pods, reqs)
+                        ts, xs = [], []
+                        for _ in range(20):
+                            t0 = time.perf_counter()
+                            rg, pg = g.score_packed(pods, reqs)
+                            ts.append(time.perf_counter() - t0)
+                            xs.append(g.timing()[1])
+                        ts.sort(), xs.sort()
+                        group[name] = {"ms_per_call": 1e3 * ts[len(ts) // 2], "value": P * whole.n_nodes / ts[len(ts) // 2],
+                                       "unit": UNIT, "exchange_us": xs[len(xs) // 2],
+                                       "equals_torchrun_result": bool(np.array_equal(rg, results) and np.array_equal(pg, picks))}
+                except Exception as e:  # reported, not fatal: the torchrun path above is the measured headline
+                    group[name] = {"error": str(e)[:300]}
+            group["api"] = ("vgs_group_score_batch: request records H2D to every GPU + score + local resolve + exchange + "
+                            "merge + results D2H, one host thread, snapshot resident; median wall clock of 20 calls")
+            store.set("vgs_group_leg_done", "1")
+        else:
+            store.wait(["vgs_group_leg_done"])
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
 
-    check = sampled_check(v, np, whole_snapshot(v, np, make_shard, world), batch, results, picks)
+    if whole is None:
+        whole = whole_snapshot(v, np, make_shard, world)
+    check = sampled_check(v, np, whole, batch, results, picks)
     if not check["bit_exact_vs_oracle"]:
         print(json.dumps({"error": "result differs from the oracle", "check": check}), flush=True)
         raise SystemExit(3)
@@ -618,6 +658,8 @@ def main():
         line["e2e_delta"] = e2e_delta
     if configs:
         line["configs"] = configs
+    if group:
+        line["group"] = group
     if latency:
         line["filter_latency"] = latency
     if hbm_regime:
