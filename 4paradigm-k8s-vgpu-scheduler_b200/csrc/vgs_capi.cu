@@ -67,6 +67,8 @@ struct vgs_ctx {
     vgs_delta *d_deltas = nullptr, *h_deltas = nullptr;
     int32_t *d_rowlist = nullptr;
     int32_t max_deltas = 0;
+    cudaEvent_t ev_delta = nullptr; // the pinned delta staging buffer has been consumed
+    bool delta_in_flight = false;
 
     // pod batch
     unsigned char *h_stage = nullptr, *d_stage = nullptr; // one block, carved below
@@ -106,6 +108,11 @@ struct vgs_ctx {
     // the pod classes of one batch are independent: their kernel chains run on side streams
     // forked from / joined to `st` with events
     cudaStream_t side[2] = {};
+    // a pod batch that arrives while an asynchronous snapshot upload is still crossing PCIe goes up (and has its
+    // bit tables built) on this stream, beside the copy; the score pass joins the two
+    cudaStream_t st_pods = nullptr;
+    cudaEvent_t ev_idle = nullptr, ev_pods = nullptr; // `st` as it stood before the upload was queued / pod work done
+    bool pods_on_side = false;
     cudaEvent_t ev_fork = nullptr, ev_join[2] = {}, ev_ns[2] = {};
     cudaEvent_t ev[EV_N] = {};
     bool ev_set[EV_N] = {};
@@ -210,6 +217,7 @@ void free_all(vgs_ctx *c) {
     cudaFree(c->d_ndev);
     cudaFree(c->d_walk);
     if (c->ev_snap) cudaEventDestroy(c->ev_snap);
+    if (c->ev_delta) cudaEventDestroy(c->ev_delta);
     cudaFree(c->d_status);
     cudaFreeHost(c->h_status);
     cudaFree(c->d_deltas);
@@ -236,6 +244,9 @@ void free_all(vgs_ctx *c) {
         if (c->ev_ns[k]) cudaEventDestroy(c->ev_ns[k]);
     }
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+    if (c->st_pods) cudaStreamDestroy(c->st_pods);
+    if (c->ev_idle) cudaEventDestroy(c->ev_idle);
+    if (c->ev_pods) cudaEventDestroy(c->ev_pods);
     if (c->own_stream && c->st) cudaStreamDestroy(c->st);
 }
 
@@ -302,6 +313,9 @@ int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
     for (int i = 0; i < EV_N; i++) CUI(cudaEventCreate(&c->ev[i]));
     CUI(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
     CUI(cudaEventCreateWithFlags(&c->ev_snap, cudaEventDisableTiming));
+    CUI(cudaStreamCreateWithFlags(&c->st_pods, cudaStreamNonBlocking));
+    CUI(cudaEventCreateWithFlags(&c->ev_idle, cudaEventDisableTiming));
+    CUI(cudaEventCreateWithFlags(&c->ev_pods, cudaEventDisableTiming));
     for (int k = 0; k < 2; k++) {
         CUI(cudaStreamCreateWithFlags(&c->side[k], cudaStreamNonBlocking));
         CUI(cudaEventCreateWithFlags(&c->ev_join[k], cudaEventDisableTiming));
@@ -315,7 +329,8 @@ int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
     CUI(cudaMalloc(&c->d_status, 2 * sizeof(uint32_t))); // [0] S_* flags, [1] largest type id in use
     CUI(cudaMemset(c->d_status, 0, 2 * sizeof(uint32_t)));
     CUI(cudaMallocHost(&c->h_status, 2 * sizeof(uint32_t)));
-    c->max_deltas = 4096;
+    c->max_deltas = 16384;
+    CUI(cudaEventCreateWithFlags(&c->ev_delta, cudaEventDisableTiming));
     CUI(cudaMalloc(&c->d_deltas, c->max_deltas * sizeof(vgs_delta)));
     CUI(cudaMallocHost(&c->h_deltas, c->max_deltas * sizeof(vgs_delta)));
     CUI(cudaMalloc(&c->d_rowlist, c->max_deltas * sizeof(int32_t)));
@@ -400,6 +415,7 @@ static int snapshot_common(vgs_ctx *c, int32_t n_nodes, int32_t dmax,
     c->snap_bigmem = false; // every row is prepared again below
     c->scored = c->resolved = false;
     const size_t cells = (size_t)n_nodes * dmax;
+    if (async) CU(cudaEventRecord(c->ev_idle, c->st)); // everything queued so far: what a pod upload beside the copy waits for
     CU(cudaMemsetAsync(c->d_status, 0, 2 * sizeof(uint32_t), c->st));
     rec(c, EV_UP0);
     if (cells) {
@@ -524,7 +540,10 @@ int vgs_snapshot_delta(vgs_ctx *c, int32_t n, const vgs_delta *deltas) {
     rm.ndev = c->d_ndev;
     for (int32_t done = 0; done < n;) {
         int32_t m = n - done < c->max_deltas ? n - done : c->max_deltas;
-        CU(cudaStreamSynchronize(c->st)); // staging buffer reuse
+        if (c->delta_in_flight) { // staging buffer reuse: only the previous delta copy has to be through
+            CU(cudaEventSynchronize(c->ev_delta));
+            c->delta_in_flight = false;
+        }
         memcpy(c->h_deltas, deltas + done, (size_t)m * sizeof(vgs_delta));
         CU(cudaMemcpyAsync(c->d_deltas, c->h_deltas, (size_t)m * sizeof(vgs_delta),
                            cudaMemcpyHostToDevice, c->st));
@@ -532,14 +551,14 @@ int vgs_snapshot_delta(vgs_ctx *c, int32_t n, const vgs_delta *deltas) {
                         c->d_status, c->st));
         CU(launch_prepare(c->dm, raw_const(c), c->n_nodes, c->dmax, c->d_walk, c->n_tiles, c->d_status,
                           c->d_rowlist, m, c->st));
+        CU(cudaEventRecord(c->ev_delta, c->st));
+        c->delta_in_flight = true;
         c->launches += 2;
         done += m;
     }
-    int rc = pull_status(c);
-    if (rc != VGS_OK) {
-        c->have_snapshot = false; // planes may hold out-of-range values now
-        return rc;
-    }
+    // Nothing is waited for: a delta is a few microseconds of GPU work in front of the next score pass.  What
+    // the kernels find wrong with it (a slot the node does not have, usage out of range) is in the status word
+    // and comes out of the next call that reads it -- vgs_results_download / vgs_score_batch / vgs_sync.
     c->version++;
     return VGS_OK;
 }
@@ -585,7 +604,7 @@ static size_t stage_layout(vgs_ctx *c, size_t P, size_t R) {
 // Build the bit tables of one pod-sliced class (see SliceTab) into pinned staging and queue the
 // upload.  Returns false when the class does not qualify (then the per-pair kernel runs).
 static bool build_slice_class(vgs_ctx *c, int k, const DevReq *req, const DevReq *dreq_class,
-                              const int32_t *orig, int32_t n, cudaError_t *err) {
+                              const int32_t *orig, int32_t n, cudaError_t *err, cudaStream_t sp) {
     *err = cudaSuccess;
     c->slice_on[k] = false;
     // >= slice_min pods: always.  From slice_small pods upward when the pass is big enough for the
@@ -594,22 +613,30 @@ static bool build_slice_class(vgs_ctx *c, int k, const DevReq *req, const DevReq
     const bool big = n >= c->tune.slice_min;
     const bool mid = n >= c->tune.slice_small && (int64_t)n * c->n_nodes >= c->tune.slice_small_pairs;
     if (n < 1 || !(big || mid)) return false;
-    std::vector<int32_t> mv, pv, cv; // sorted distinct thresholds (few in practice)
-    auto add = [](std::vector<int32_t> &v, int32_t x) {
-        auto it = std::lower_bound(v.begin(), v.end(), x);
-        if (it == v.end() || *it != x) v.insert(it, x);
-    };
+    // sorted distinct thresholds (few in practice): percentages through a 101-bit map, the rest collected with
+    // a "same as the previous pod" shortcut, then sorted and made unique once
+    static thread_local std::vector<int32_t> mv, pv, cv;
+    mv.clear(), pv.clear(), cv.clear();
+    bool pct_seen[kSliceMaxPct] = {};
+    int32_t last_m = INT32_MIN, last_c = INT32_MIN;
     for (int32_t i = 0; i < n; i++) {
         const DevReq &d = req[i];
         if (d.flags & R_USEPCT) {
             if (d.pct < 0 || d.pct > 100) return false; // monotone in pct only on [0,100]
-            add(pv, d.pct);
-        } else {
-            add(mv, d.memfix);
+            pct_seen[d.pct] = true;
+        } else if (d.memfix != last_m) {
+            mv.push_back(last_m = d.memfix);
         }
-        add(cv, d.coresreq);
-        if ((int)mv.size() > kSliceMaxDistinct || (int)cv.size() > kSliceMaxDistinct) return false;
+        if (d.coresreq != last_c) cv.push_back(last_c = d.coresreq);
     }
+    auto uniq = [](std::vector<int32_t> &v) {
+        std::sort(v.begin(), v.end());
+        v.erase(std::unique(v.begin(), v.end()), v.end());
+    };
+    uniq(mv), uniq(cv);
+    for (int32_t q = 0; q < kSliceMaxPct; q++)
+        if (pct_seen[q]) pv.push_back(q);
+    if ((int)mv.size() > kSliceMaxDistinct || (int)cv.size() > kSliceMaxDistinct) return false;
     const int32_t km = (int32_t)mv.size(), kp = (int32_t)pv.size(), kc = (int32_t)cv.size();
     const int32_t W = (n + 31) / 32, Wp = (int32_t)align_up((size_t)W, 32);
     uint32_t *h = c->h_slice[k];
@@ -632,9 +659,9 @@ static bool build_slice_class(vgs_ctx *c, int k, const DevReq *req, const DevReq
     std::copy(orig, orig + n, hi + o_orig);
     (void)o_mem, (void)o_pct, (void)o_core;
     *err = cudaMemcpyAsync(c->d_slice[k] + o_memv, h + o_memv, (o - o_memv) * sizeof(uint32_t),
-                           cudaMemcpyHostToDevice, c->st);
+                           cudaMemcpyHostToDevice, sp);
     if (*err != cudaSuccess) return false;
-    *err = cudaMemsetAsync(c->d_slice[k], 0, o_memv * sizeof(uint32_t), c->st);
+    *err = cudaMemsetAsync(c->d_slice[k], 0, o_memv * sizeof(uint32_t), sp);
     if (*err != cudaSuccess) return false;
     const uint32_t *d = c->d_slice[k];
     SliceTab &t = c->tab[k];
@@ -645,15 +672,16 @@ static bool build_slice_class(vgs_ctx *c, int k, const DevReq *req, const DevReq
     t.corev = reinterpret_cast<const int32_t *>(d + o_corev);
     t.orig = reinterpret_cast<const int32_t *>(d + o_orig);
     t.km = km, t.kp = kp, t.kc = kc, t.n_pods = n, t.W = W, t.Wp = Wp;
-    *err = launch_slice_tables(t, dreq_class, c->st);
+    *err = launch_slice_tables(t, dreq_class, sp);
     if (*err != cudaSuccess) return false;
     c->launches += 2;
     c->slice_on[k] = true;
     return true;
 }
 
+// want_all: also list EVERY pod as a GenPod in batch order (the drain scores one pod at a time)
 static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_reqs,
-                              const vgs_req *reqs) {
+                              const vgs_req *reqs, bool want_all = false) {
     if (n_pods < 0 || n_reqs < 0 || (n_pods > 0 && (!pods || !reqs)))
         return fail(c, VGS_EINVAL, "bad pod batch");
     if (n_pods > c->cfg.max_pods || n_reqs > c->cfg.max_reqs)
@@ -662,7 +690,7 @@ static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, i
     c->scored = c->resolved = false;
     // the staging block may still be the source of an earlier async copy
     if (c->stage_in_flight) {
-        CU(cudaStreamSynchronize(c->st));
+        CU(cudaStreamSynchronize(c->pods_on_side ? c->st_pods : c->st));
         c->stage_in_flight = false;
     }
     const size_t stage_used = stage_layout(c, (size_t)n_pods, (size_t)n_reqs);
@@ -722,9 +750,14 @@ static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, i
         }
         hpod[p] = pd;
         GenPod *hall = reinterpret_cast<GenPod *>(c->h_stage + c->off_genall);
-        hall[p].req_begin = pd.req_begin, hall[p].n_reqs = pd.n_reqs, hall[p].orig = p;
-        hall[p].flags = gen_pod_flags(&hreq[pd.req_begin], pd.n_reqs);
-        if (c->tune.general_legacy) hall[p].flags |= G_LEGACY;
+        auto as_gen = [&]() {
+            GenPod g;
+            g.req_begin = pd.req_begin, g.n_reqs = pd.n_reqs, g.orig = p;
+            g.flags = gen_pod_flags(&hreq[pd.req_begin], pd.n_reqs);
+            if (c->tune.general_legacy) g.flags |= G_LEGACY;
+            return g;
+        };
+        if (want_all) hall[p] = as_gen();
         const DevReq &first = hreq[pd.req_begin];
         // the bit tables of the sliced classes know nothing of M_BUSY370: idle-share requests
         // take the per-pair kernel, which tests the whole blockmask
@@ -739,8 +772,9 @@ static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, i
             hC[nC] = first;
             hoC[nC++] = p;
         } else { // walk-kernel pods from the front of the region, all-pairs pods from its end
-            GenPod &g = (hall[p].flags & G_LEGACY) ? hG[n_pods - 1 - nGL++] : hG[nG - nGL];
-            g = hall[p];
+            const GenPod gp = want_all ? hall[p] : as_gen();
+            GenPod &g = (gp.flags & G_LEGACY) ? hG[n_pods - 1 - nGL++] : hG[nG - nGL];
+            g = gp;
             nG++;
         }
     }
@@ -782,25 +816,39 @@ static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, i
         }
     }
     c->n_picks = (int32_t)picks;
-    // everything above was host work that overlaps an asynchronous snapshot upload; the class set-up
-    // below wants to know what the snapshot allows (sliced kernels, type rows)
-    {
-        int frc = finish_snapshot(c);
-        if (frc != VGS_OK) return frc;
+    // Everything above was host work that overlaps an asynchronous snapshot upload.  So does the device side of
+    // the batch: the request records and the bit tables of the sliced classes depend on the pods alone (what the
+    // snapshot allows -- sliced kernels, type rows -- is looked at when the score pass is queued), so while a
+    // snapshot copy is pending they go up on a stream of their own, behind what `st` held before the copy.
+    cudaStream_t sp = c->st;
+    c->pods_on_side = c->snap_pending;
+    if (c->pods_on_side) {
+        sp = c->st_pods;
+        CU(cudaStreamWaitEvent(sp, c->ev_idle, 0));
+        cudaEventRecord(c->ev[EV_PH0], sp);
+        c->ev_alias[EV_PH0] = EV_PH0, c->ev_set[EV_PH0] = true;
+    } else {
+        rec(c, EV_PH0);
     }
-    rec(c, EV_PH0);
     if (stage_used) {
-        CU(cudaMemcpyAsync(c->d_stage, c->h_stage, stage_used, cudaMemcpyHostToDevice, c->st));
+        CU(cudaMemcpyAsync(c->d_stage, c->h_stage, stage_used, cudaMemcpyHostToDevice, sp));
         c->stage_in_flight = true;
     }
     {
         cudaError_t e;
-        build_slice_class(c, 0, hA, reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqsA), hoA, nA, &e);
+        build_slice_class(c, 0, hA, reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqsA), hoA, nA, &e, sp);
         CU(e);
-        build_slice_class(c, 1, hB, reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqsB), hoB, nB, &e);
+        build_slice_class(c, 1, hB, reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqsB), hoB, nB, &e, sp);
         CU(e);
     }
-    rec(c, EV_PH1);
+    if (c->pods_on_side) {
+        cudaEventRecord(c->ev[EV_PH1], sp);
+        c->ev_alias[EV_PH1] = EV_PH1, c->ev_set[EV_PH1] = true;
+        CU(cudaEventRecord(c->ev_pods, sp));
+        CU(cudaStreamWaitEvent(c->st, c->ev_pods, 0)); // whatever is queued on `st` next sees the batch
+    } else {
+        rec(c, EV_PH1);
+    }
     c->have_pods = true;
     return VGS_OK;
 }
@@ -962,6 +1010,8 @@ static int download_locked(vgs_ctx *c, vgs_result *results, vgs_pick *picks) {
     if (*c->h_status & S_DICTFULL) c->plan.dict_full = 1;
     int rc = check_status(c);
     if (rc != VGS_OK) {
+        // a delta that went wrong leaves planes that may hold out-of-range values: upload again
+        if (*c->h_status & (S_DELTA | S_RANGE | S_TYPE | S_NDEV)) c->have_snapshot = false;
         cudaMemsetAsync(c->d_status, 0, sizeof(uint32_t), c->st);
         return rc;
     }
@@ -1023,7 +1073,7 @@ int vgs_drain_batch(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_r
     }
     if (!c->have_snapshot) return fail(c, VGS_ESTATE, "drain before snapshot upload");
     int rc;
-    if ((rc = pods_upload_locked(c, n_pods, pods, n_reqs, reqs)) != VGS_OK) return rc;
+    if ((rc = pods_upload_locked(c, n_pods, pods, n_reqs, reqs, true)) != VGS_OK) return rc;
     rec(c, EV_SC0);
     if (c->dirty_pods > 0) CU(cudaMemsetAsync(c->d_keys, 0, (size_t)c->cfg.max_pods * 12, c->st));
     c->dirty_pods = n_pods;
@@ -1061,9 +1111,16 @@ int vgs_sync(vgs_ctx *c) {
     if (!c) return VGS_EINVAL;
     std::lock_guard<std::mutex> lk(c->mu);
     DeviceGuard g(c->cfg.device);
-    CU(cudaStreamSynchronize(c->st));
-    c->stage_in_flight = false;
-    return finish_snapshot(c);
+    int frc = finish_snapshot(c);
+    if (frc != VGS_OK) return frc;
+    if (!c->have_snapshot) {
+        CU(cudaStreamSynchronize(c->st));
+        c->stage_in_flight = false;
+        return VGS_OK;
+    }
+    int rc = pull_status(c); // synchronises the stream; reports what asynchronous deltas left in the status word
+    if (rc != VGS_OK && (*c->h_status & (S_DELTA | S_RANGE | S_TYPE | S_NDEV))) c->have_snapshot = false;
+    return rc;
 }
 
 int vgs_keys_device(vgs_ctx *c, uint64_t **dev_keys, int32_t **dev_counts) {

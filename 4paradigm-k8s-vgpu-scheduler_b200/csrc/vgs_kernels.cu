@@ -634,27 +634,35 @@ __global__ void __launch_bounds__(128) k1t_fill(SliceTab tb, const DevReq *__res
         if (!lose) atomicOr(&base[(size_t)(r_core + cut * 4 + f) * Wp + wd], bit);
     }
 }
+// rows [r0, r0 + n) of column x, stride `step` rows apart, turned into their running OR -- eight loads in flight
+// at a time (the naive loop is one dependent L2 round trip per row)
+__device__ __forceinline__ void prefix_or_rows(uint32_t *__restrict__ col, size_t Wp, int r0, int n, int step) {
+    uint32_t acc = 0u;
+    for (int r = 0; r < n; r += 8) {
+        uint32_t v[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++) v[u] = r + u < n ? col[(size_t)(r0 + (r + u) * step) * Wp] : 0u;
+#pragma unroll
+        for (int u = 0; u < 8; u++)
+            if (r + u < n) col[(size_t)(r0 + (r + u) * step) * Wp] = acc |= v[u];
+    }
+}
 __global__ void __launch_bounds__(128) k1t_prefix(SliceTab tb) {
-    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    // thread = (pod word, chain): the memory chain, the percentage chain and the four cores x flags chains of a
+    // column are independent
+    const int x = (blockIdx.x * blockDim.x + threadIdx.x) / 6, chain = (blockIdx.x * blockDim.x + threadIdx.x) % 6;
     if (x >= tb.W) return;
-    uint32_t *base = const_cast<uint32_t *>(tb.base);
+    uint32_t *col = const_cast<uint32_t *>(tb.base) + x;
     const size_t Wp = (size_t)tb.Wp;
     const int r_mem = VGS_MAX_TYPES, r_pct = r_mem + tb.km + 1, r_core = r_pct + tb.kp + 1;
-    uint32_t acc = 0u;
-    for (int r = 0; r <= tb.km; r++) base[(size_t)(r_mem + r) * Wp + x] = acc |= base[(size_t)(r_mem + r) * Wp + x];
-    acc = 0u;
-    for (int r = 0; r <= tb.kp; r++) base[(size_t)(r_pct + r) * Wp + x] = acc |= base[(size_t)(r_pct + r) * Wp + x];
-    uint32_t a4[4] = {0u, 0u, 0u, 0u};
-    for (int r = 0; r <= tb.kc; r++)
-        for (int f = 0; f < 4; f++) {
-            const size_t o = (size_t)(r_core + r * 4 + f) * Wp + x;
-            base[o] = a4[f] |= base[o];
-        }
+    if (chain == 0) prefix_or_rows(col, Wp, r_mem, tb.km + 1, 1);
+    else if (chain == 1) prefix_or_rows(col, Wp, r_pct, tb.kp + 1, 1);
+    else prefix_or_rows(col, Wp, r_core + (chain - 2), tb.kc + 1, 4);
 }
 cudaError_t launch_slice_tables(const SliceTab &tb, const DevReq *dreq, cudaStream_t st) {
     if (tb.n_pods <= 0) return cudaSuccess;
     k1t_fill<<<(tb.n_pods + 127) / 128, 128, 0, st>>>(tb, dreq);
-    k1t_prefix<<<(tb.W + 127) / 128, 128, 0, st>>>(tb);
+    k1t_prefix<<<(tb.W * 6 + 127) / 128, 128, 0, st>>>(tb);
     return cudaGetLastError();
 }
 

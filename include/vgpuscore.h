@@ -199,9 +199,11 @@ int vgs_snapshot_upload(vgs_ctx *ctx, int32_t n_nodes, int32_t dmax,
                         uint64_t *out_version);
 /* Same, but returns as soon as the copy and the preparation are queued, so that the caller can go on
  * building the pod batch while the planes cross PCIe.  The planes must stay untouched until the next
- * call on this context that needs the snapshot (vgs_pods_upload from its table set-up on, vgs_score_*,
- * vgs_snapshot_delta / _refresh / _download, vgs_sync): that call waits for the upload and returns its
- * range errors (VGS_EDMAX / VGS_ERANGE) in place of its own result.  No counterpart in the reference. */
+ * call on this context that needs the snapshot (vgs_score_*, vgs_drain_batch, vgs_snapshot_delta /
+ * _refresh / _download / _type_flags, vgs_sync): that call waits for the upload and returns its
+ * range errors (VGS_EDMAX / VGS_ERANGE) in place of its own result.  vgs_pods_upload does NOT wait: the
+ * request records and the bit tables depend on the pods alone, so a batch uploaded while the copy is
+ * pending goes up on a second stream beside it.  No counterpart in the reference. */
 int vgs_snapshot_upload_async(vgs_ctx *ctx, int32_t n_nodes, int32_t dmax,
                               const int32_t *const planes[VGS_NUM_PLANES], const int32_t *ndev,
                               uint64_t *out_version);
@@ -215,6 +217,10 @@ int vgs_snapshot_type_flags(vgs_ctx *ctx, int32_t n_types, const uint32_t *flags
 /* re-run the preparation kernel over the resident planes (asynchronous; a range
  * error surfaces at the next vgs_results_download) */
 int vgs_snapshot_refresh(vgs_ctx *ctx);
+/* Queues the usage changes (scatter into the resident planes + re-preparation of the touched rows) and returns;
+ * the deltas are copied before it does.  A delta naming a slot the node does not have (VGS_EINVAL) or driving
+ * Used out of range (VGS_ERANGE) is reported by the next vgs_results_download / vgs_score_batch / vgs_sync on
+ * this context, after which the snapshot has to be uploaded again.  Rows outside the shard are ignored. */
 int vgs_snapshot_delta(vgs_ctx *ctx, int32_t n, const vgs_delta *deltas);
 /* read the resident planes back (testing the delta path) */
 int vgs_snapshot_download(vgs_ctx *ctx, int32_t *const planes[VGS_NUM_PLANES], int32_t *ndev);

@@ -244,6 +244,36 @@ def test_delta_equals_rebuild(built):
         assert_same(ctx.score(batch), first, "after undo")
 
 
+def test_delta_errors_surface_at_the_next_status_read(built):
+    """vgs_snapshot_delta only queues work; a delta naming a slot the node does not have is reported by the next
+    call that reads the status word, and the snapshot then has to be uploaded again"""
+    snap, batch = v.workload.make_config("cfg3", 500, 8)
+    pods, reqs = v.capi.pack_batch(batch, snap.type_names)
+    with v.Context(max_nodes=500, max_pods=8) as ctx:
+        ctx.upload(snap)
+        good = ctx.score_packed(pods, reqs)
+        ctx.delta(np.array([(3, 11, 1, 100, 10)], dtype=v.capi.DELTA_DTYPE))  # slot 11 of an 8-device node
+        with pytest.raises(v.VgsError) as e:
+            ctx.score_packed(pods, reqs)
+        assert e.value.code == v.capi.VGS_EINVAL
+        with pytest.raises(v.VgsError) as e:
+            ctx.score_packed(pods, reqs)
+        assert e.value.code == v.capi.VGS_ESTATE
+        ctx.upload(snap)
+        again = ctx.score_packed(pods, reqs)
+        assert np.array_equal(good[0], again[0]) and np.array_equal(good[1], again[1])
+        ctx.delta(np.array([(3, 0, 1 << 21, 0, 0)], dtype=v.capi.DELTA_DTYPE))  # Used out of range
+        with pytest.raises(v.VgsError) as e:
+            ctx.sync()
+        assert e.value.code == v.capi.VGS_ERANGE
+        # a delta for a row of another shard is not an error
+        ctx.upload(snap)
+        ctx.delta(np.array([(100_000, 0, 1, 1, 1)], dtype=v.capi.DELTA_DTYPE))
+        ctx.sync()
+        again = ctx.score_packed(pods, reqs)
+        assert np.array_equal(good[0], again[0])
+
+
 def test_shards_on_one_gpu_equal_single(built):
     """3 row shards (3 contexts on one GPU) + key merge == one context; 1-GPU result is the oracle"""
     import torch
@@ -711,8 +741,9 @@ def test_async_snapshot_upload(built):
         # a bad snapshot: the error belongs to the upload and comes out of the next call
         pin[v.model.P_COUNT][5, 3] = 1 << 21
         ctx.upload_ptrs(snap.n_nodes, snap.dmax, ptrs, pnd.data_ptr(), device=False, asynchronous=True)
+        ctx.pods_upload(pods, reqs)  # depends on the pods alone: goes up beside the copy, does not wait for it
         with pytest.raises(v.VgsError) as e:
-            ctx.pods_upload(pods, reqs)
+            ctx.score_resident()  # the first call that needs the snapshot
         assert e.value.code == v.capi.VGS_ERANGE
         with pytest.raises(v.VgsError) as e:
             ctx.score_resident()  # still no snapshot
