@@ -586,9 +586,13 @@ __device__ __forceinline__ void csa(uint32_t &carry, uint32_t &sum, uint32_t a, 
     carry = (a & b) | (a & c) | (b & c);
 }
 
-__device__ __forceinline__ void hset_insert(uint32_t *__restrict__ hset, uint32_t key, uint32_t *status) {
+__device__ __forceinline__ void hset_insert(uint32_t *__restrict__ hset, uint32_t key, uint32_t *status, bool &full) {
+    // The set only has to hold enough distinct scores to place the class boundaries well: a snapshot with more
+    // distinct candidate scores than it can take (S_DICTFULL) simply stops feeding it -- a score that is not in
+    // the set still gets a valid class (class_of), results stay exact.
+    if (full) return; // (read once per thread at kernel start, set when an own insert gives up)
     uint32_t h = (key * 2654435761u) >> 20; // 12 bits
-    for (int probe = 0; probe < kSliceHash; probe++) {
+    for (int probe = 0; probe < 48; probe++) {
         const uint32_t cur = hset[h];
         if (cur == key) return;
         if (cur == 0u) {
@@ -597,7 +601,8 @@ __device__ __forceinline__ void hset_insert(uint32_t *__restrict__ hset, uint32_
         }
         h = (h + 1) & (kSliceHash - 1);
     }
-    atomicOr(status, S_DICTFULL); // cannot happen below kSliceHash distinct scores
+    atomicOr(status, S_DICTFULL); // a probe run of 48: the table is as good as full
+    full = true;
 }
 
 // ------------------------------------------------------------------------------------
@@ -680,6 +685,7 @@ __global__ void __launch_bounds__(128)
     if (node >= n_tiles * kWarp) return;
     const int tile = node >> 5, lane = node & 31;
     const int4 *tp = walk + (size_t)tile * kTileInt4;
+    bool set_full = want_scores && (*reinterpret_cast<volatile uint32_t *>(status) & S_DICTFULL);
     int32_t totalmem[8], freemem[8], freecores[8], meta[8], wa[8], wb[8];
     load_word<8>(tp, W_TOTALMEM, lane, totalmem);
     load_word<8>(tp, W_FREEMEM, lane, freemem);
@@ -713,7 +719,7 @@ __global__ void __launch_bounds__(128)
             if (NUMS == 1) {
                 d.a = (uint32_t)wa[j];
                 d.b = (uint32_t)kDict;
-                if (want_scores) hset_insert(tb.hset, d.a, status);
+                if (want_scores) hset_insert(tb.hset, d.a, status, set_full);
             } else {
                 d.a = (uint32_t)wa[j];
                 d.b = (uint32_t)wb[j] | (ndev << 24);
@@ -730,7 +736,7 @@ __global__ void __launch_bounds__(128)
                     hset_insert(tb.hset,
                                 __float_as_uint(container_score(wrap_add(wa[a], wa[b]), wrap_add(wb[a], wb[b]),
                                                                 (int32_t)ndev - 2)),
-                                status);
+                                status, set_full);
     }
 }
 
@@ -766,11 +772,28 @@ __global__ void __launch_bounds__(1024) k1p_sort(SliceTab tb) {
             }
             __syncthreads();
         }
+    // <= kDict distinct scores: every one is a class of its own.  More: the class boundaries are the 16 largest
+    // scores (where the per-pod bests end up, so resolution matters) and 16 evenly spaced ranks of the rest.
     const int keep = min(n, kDict);
-    for (int i = threadIdx.x; i < kDict; i += blockDim.x) tb.gvals[i] = i < keep ? v[m - keep + i] : 0xffffffffu;
+    for (int i = threadIdx.x; i < kDict; i += blockDim.x) {
+        uint32_t val = 0xffffffffu;
+        if (n <= kDict) {
+            if (i < keep) val = v[m - keep + i];
+        } else if (i >= kDict / 2) {
+            val = v[m - kDict + i];
+        } else {
+            const int rest = n - kDict / 2; // ranks 0 .. rest-1 of the ascending distinct scores
+            val = v[m - n + (int)(((long long)(i + 1) * rest) / (kDict / 2 + 1))];
+        }
+        tb.gvals[i] = val;
+    }
     if (threadIdx.x == 0) tb.gvals[kDict] = (uint32_t)keep;
 }
 
+// Detection class of a candidate score: the number of class boundaries below it.  below[k] holds the pods whose
+// best is under boundary k, so a candidate of class k can only improve pods in below[k] -- exactly those when the
+// score IS boundary k (few distinct scores: every score is one), a superset when it lies between two boundaries
+// (the replay compares exactly).  Above the last boundary: kDict, the all-ones row.
 __device__ __forceinline__ uint32_t class_of(const uint32_t *__restrict__ gvals, int nv, uint32_t sb) {
     int lo = 0, hi = nv;
     while (lo < hi) {
@@ -778,7 +801,7 @@ __device__ __forceinline__ uint32_t class_of(const uint32_t *__restrict__ gvals,
         if (__ldg(&gvals[mid]) < sb) lo = mid + 1;
         else hi = mid;
     }
-    return (lo < nv && __ldg(&gvals[lo]) == sb) ? (uint32_t)lo : (uint32_t)kDict;
+    return lo < nv ? (uint32_t)lo : (uint32_t)kDict;
 }
 
 template <int NUMS>

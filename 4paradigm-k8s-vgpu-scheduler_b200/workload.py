@@ -169,6 +169,40 @@ def pods_multi(n_pods: int, seed: int) -> PodBatch:
     return PodBatch.from_pods(pods)
 
 
+def make_stress_snapshot(n_nodes: int, seed: int = SEED + 77, dmax: int = 8) -> Snapshot:
+    """A snapshot built against the assumptions the synthetic configs are kind to (robustness number, not a
+    BASELINE config): Count differs per device (1..32), nodes are ragged (0..8 devices), 48 device types mixed
+    INSIDE nodes, two numa nodes in random order, and the fill level falls with the row index -- the kernels walk
+    rows downwards, so candidate scores keep RISING along the walk and there are hundreds of distinct score values
+    (the sliced kernels track the 32 largest exactly)."""
+    rng = SplitMix(seed)
+    D = dmax
+    names, mems = [], []
+    for t, m in GPU_TYPES:
+        for k in range(6):
+            names.append(f"{t}-rev{k}")
+            mems.append(m - 256 * k)
+    mems = np.array(mems, dtype=np.int64)
+    planes = np.zeros((8, n_nodes, D), dtype=np.int32)
+    count = 1 + rng.below(n_nodes * D, 32).astype(np.int64).reshape(n_nodes, D)
+    # free fraction grows with the row: row 0 is nearly full (high scores), the last row nearly idle
+    frac = (np.arange(n_nodes, dtype=np.float64)[:, None] + 1.0) / n_nodes
+    noise = rng.unit(n_nodes * D).reshape(n_nodes, D) * 0.15
+    free = np.clip(np.round(count * np.clip(frac + noise - 0.05, 0.0, 1.0)), 0, count).astype(np.int64)
+    used = count - free
+    tid = rng.below(n_nodes * D, len(names)).astype(np.int64).reshape(n_nodes, D)
+    tm = mems[tid]
+    usedmem = np.minimum(tm, (used * tm) // (count * 2) + rng.below(n_nodes * D, 2000).astype(np.int64).reshape(n_nodes, D) * (used > 0))
+    usedcores = np.minimum(100, (used * 60) // count + 5 * rng.below(n_nodes * D, 5).astype(np.int64).reshape(n_nodes, D) * (used > 0))
+    planes[0], planes[1], planes[2], planes[3] = used, count, usedmem, tm
+    planes[4], planes[5] = usedcores, 100
+    planes[6] = rng.below(n_nodes * D, 2).astype(np.int32).reshape(n_nodes, D)
+    planes[7] = tid
+    ndev = rng.below(n_nodes, D + 1).astype(np.int32)
+    ndev[rng.unit(n_nodes) < 0.6] = D  # most nodes are full-width, the rest ragged (incl. 0 devices)
+    return Snapshot(planes, ndev, names)
+
+
 CONFIGS = {
     # name: (n_nodes, n_pods, pod generator)
     "cfg1": (64, 1, None),
@@ -181,6 +215,8 @@ CONFIGS = {
 
 def make_config(name: str, n_nodes: int = None, n_pods: int = None):
     """(Snapshot, PodBatch) of a BASELINE.json config, optionally resized."""
+    if name == "stress":
+        return make_stress_snapshot(n_nodes or 100_000), pods_mixed(n_pods or 4096, SEED + 177)
     N, P, gen = CONFIGS[name]
     N = n_nodes or N
     P = n_pods or P

@@ -383,12 +383,13 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     v.load_library()
-    cfg_idx = int(args.config[3:])
+    cfg_idx = 77 if args.config == "stress" else int(args.config[3:])
 
     # ---- headline workload: every rank builds its own shard (rows [rank*npg, (rank+1)*npg)) -------
     npg = args.nodes_per_gpu
     n_total = npg * world
-    make_shard = lambda r: v.workload.make_snapshot(npg, v.workload.SEED + cfg_idx + 1000 * r)
+    make_shard = (lambda r: v.workload.make_stress_snapshot(npg, v.workload.SEED + 77 + 1000 * r)) if args.config == "stress" \
+        else (lambda r: v.workload.make_snapshot(npg, v.workload.SEED + cfg_idx + 1000 * r))
     snap = make_shard(rank)
     _, batch = v.workload.make_config(args.config, 8, args.pods)
     leg = Leg(v, torch, dist, local, rank, world, snap, batch, n_total)
@@ -546,7 +547,9 @@ def main():
         if world == 1:
             plan = [("cfg2", "cfg2", None, None, "10k nodes x 8 devices x 256 single-container pods (Nums 1, MB, cores)"),
                     ("cfg4", "cfg4", None, None, "100k nodes x 4096 multi-container pods, 2-8 vGPUs, 10% numa-bind"),
-                    ("cfg5_shard", "cfg5", 125_000, 16384, "one of cfg5's eight shards: 125k nodes x 16384 mixed pods")]
+                    ("cfg5_shard", "cfg5", 125_000, 16384, "one of cfg5's eight shards: 125k nodes x 16384 mixed pods"),
+                    ("stress", "stress", None, None, "robustness, not a BASELINE config: 100k ragged nodes, Count 1..32 per device, 48 "
+                     "types mixed inside nodes, scores rising along the walk; the cfg3 pod mix")]
         else:
             plan = [("cfg5", "cfg5", 1_000_000, 16384, f"1M nodes x 16384 mixed pods, node-sharded x{world} (strong)"),
                     ("cfg4_strong", "cfg4", None, None, f"100k nodes x 4096 multi-container pods, node-sharded x{world} (strong)")]
@@ -561,7 +564,7 @@ def main():
                    "ms_per_step": ms, "value": b.n_pods * whole.n_nodes / (ms * 1e-3), "unit": UNIT, "k1_ms": k1c,
                    "steps": steps_c, "gpu_launches": ln, "scaling": "strong" if world > 1 else "single GPU",
                    "kernels": [["none", "pair", "sliced", "general"][pl.cls[i].kernel] for i in range(4)],
-                   "class_pods": [pl.cls[i].pods for i in range(4)]}
+                   "class_pods": [pl.cls[i].pods for i in range(4)], "score_set_overflow": bool(pl.dict_full)}
             if rank == 0:
                 rec["check"] = sampled_check(v, np, whole, b, rs, pk)
             configs[name] = rec

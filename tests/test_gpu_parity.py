@@ -447,6 +447,20 @@ def test_sliced_forced_random(built, dmax, seed):
     assert_same(got, oracle.score_faithful(snap, batch, full=True), f"sliced dmax={dmax} R1")
 
 
+@pytest.mark.parametrize("n,p,tune", [(3000, 700, None), (9500, 1300, None), (2000, 300, {"slice_min": 1, "slice_small": 1})])
+def test_stress_snapshot_many_score_values(built, n, p, tune):
+    """the robustness workload: Count 1..32 per device, ragged nodes, 48 types mixed inside nodes, scores rising
+    along the walk, thousands of distinct candidate scores (more than the 32 score classes and, at size, more than
+    the sliced kernels' hash set holds): whole fit / score matrix against both oracle arms"""
+    snap, batch = v.workload.make_config("stress", n, p)
+    want = oracle.score_packed(snap, batch, full=True)
+    assert len(np.unique(want.scores[want.fit])) > 500
+    got = gpu_score(snap, batch, tuning=tune)
+    assert_same(got, want, "stress")
+    assert_same(got, oracle.score_faithful(snap, batch, full=True), "stress R1")
+    assert_same(gpu_score(snap, batch, verify=False, tuning=tune), oracle.score_packed(snap, batch), "stress fast")
+
+
 def test_sliced_many_distinct_thresholds(built):
     """every pod its own Memreq / Coresreq value: long cumulative tables, binary search cut-offs"""
     rng = np.random.default_rng(5)
