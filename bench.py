@@ -351,6 +351,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-hbm-leg", action="store_true", help="skip the single-pod 1M-node (HBM-bound regime) leg")
+    ap.add_argument("--no-latency", action="store_true", help="skip the single-pod Filter latency leg")
     ap.add_argument("--no-configs", action="store_true", help="skip the other BASELINE configs (cfg2 / cfg4 / cfg5)")
     ap.add_argument("--check", action="store_true", help="(kept for old command lines: the oracle check always runs)")
     ap.add_argument("--tuning", default="", help="vgs_tuning overrides for A/B runs, e.g. early_scouts=0,scout_split=4")
@@ -484,7 +485,7 @@ def main():
 
     # ---- metric (ii): single-pod Filter latency through the C ABI, snapshot resident -------------
     latency = None
-    if world == 1:
+    if world == 1 and not args.no_latency:
         one = batch.select([0])
         p1, r1 = v.capi.pack_batch(one, snap.type_names)
         ts, k1s = [], []
