@@ -9,8 +9,7 @@
 //   PEER  every shard copies its block into the first GPU's gather buffer with a small kernel doing ordinary
 //         16-byte stores through the peer mapping (cudaDeviceEnablePeerAccess); the first GPU's stream waits for
 //         one event per shard and merges.  No collective launch; only the first GPU needs the gathered blocks,
-//         because only it hands results to the host.  (Loads and stores only -- no bulk-tensor or multicast
-//         copy ever touches another GPU's memory here.)
+//         because only it hands results to the host.
 #include <cuda_runtime.h>
 #include <dlfcn.h>
 
