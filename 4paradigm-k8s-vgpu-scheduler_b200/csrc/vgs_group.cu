@@ -1,5 +1,6 @@
 // vgs_group.cu -- vgs_group_*: the node set sharded over several GPUs of one box behind one handle
-// (include/vgpuscore.h).  One host thread drives every GPU: one vgs_ctx per shard, each on a
+// (include/vgpuscore.h).  One call drives every GPU (the per-shard host work runs on one
+// helper thread per further shard): one vgs_ctx per shard, each on a
 // stream of its own, built only from the public single-shard entry points (pods upload / score / resolve_local
 // / exchange block / exchange merge / download) plus the exchange itself:
 //
@@ -15,6 +16,9 @@
 
 #include <algorithm>
 #include <chrono>
+#include <condition_variable>
+#include <functional>
+#include <thread>
 #include <cstdio>
 #include <cstring>
 #include <mutex>
@@ -81,8 +85,58 @@ struct Dev {
 
 } // namespace
 
+// one helper thread per shard beyond the first: the per-shard host work of a pass (packing the request records
+// into that context's staging block, queueing its copies and launches) runs side by side instead of G times in
+// a row on the caller's thread
+struct Worker {
+    std::thread th;
+    std::mutex mu;
+    std::condition_variable cv;
+    std::function<int()> job;
+    bool has_job = false, stop = false, done = true;
+    int rc = 0;
+    void loop() {
+        std::unique_lock<std::mutex> lk(mu);
+        for (;;) {
+            cv.wait(lk, [&] { return has_job || stop; });
+            if (stop) return;
+            std::function<int()> j = std::move(job);
+            has_job = false;
+            lk.unlock();
+            const int r = j();
+            lk.lock();
+            rc = r;
+            done = true;
+            cv.notify_all();
+        }
+    }
+    void start() { th = std::thread([this] { loop(); }); }
+    void submit(std::function<int()> j) {
+        std::lock_guard<std::mutex> lk(mu);
+        job = std::move(j);
+        has_job = true;
+        done = false;
+        cv.notify_all();
+    }
+    int wait() {
+        std::unique_lock<std::mutex> lk(mu);
+        cv.wait(lk, [&] { return done; });
+        return rc;
+    }
+    void shutdown() {
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            stop = true;
+            cv.notify_all();
+        }
+        if (th.joinable()) th.join();
+    }
+};
+
 struct vgs_group {
     vgs_group_config cfg{};
+    Worker worker[VGS_MAX_GROUP];
+    bool workers_on = false;
     int G = 0;
     std::mutex mu;
     std::string err;
@@ -117,6 +171,8 @@ int gfail_ctx(vgs_group *g, int rc, int shard, const char *what) {
 }
 
 void group_free(vgs_group *g) {
+    if (g->workers_on)
+        for (int i = 1; i < g->G; i++) g->worker[i].shutdown();
     for (int i = 0; i < g->G; i++) {
         Dev d(g->cfg.devices[i]);
         if (g->have_comm && g->comm[i]) g->nccl.CommDestroy(g->comm[i]);
@@ -217,6 +273,8 @@ int vgs_group_init(const vgs_group_config *cfg, vgs_group **out) {
             } // else: cudaMemcpyPeerAsync (the driver stages it)
         }
     }
+    for (int i = 1; i < g->G; i++) g->worker[i].start();
+    g->workers_on = true;
     *out = g;
     return VGS_OK;
 }
@@ -285,13 +343,22 @@ int vgs_group_score_batch(vgs_group *g, int32_t n_pods, const vgs_pod *pods, int
     std::lock_guard<std::mutex> lk(g->mu);
     const double t_begin = now_us();
     int rc;
-    // 1. every shard: request records up, score kernels, own best node per pod -- all queued, nothing waited for
-    for (int i = 0; i < g->G; i++)
-        if ((rc = vgs_pods_upload(g->ctx[i], n_pods, pods, n_reqs, reqs)) != VGS_OK) return gfail_ctx(g, rc, i, "pods upload");
-    for (int i = 0; i < g->G; i++)
-        if ((rc = vgs_score_resident(g->ctx[i])) != VGS_OK) return gfail_ctx(g, rc, i, "score");
-    for (int i = 0; i < g->G; i++)
-        if ((rc = vgs_resolve_local(g->ctx[i])) != VGS_OK) return gfail_ctx(g, rc, i, "resolve");
+    // 1. every shard: request records up, score kernels, own best node per pod -- queued by one helper thread per
+    // shard (the caller's thread takes shard 0), nothing waited for on the GPU side
+    auto shard_pass = [g, n_pods, pods, n_reqs, reqs](int i) -> int {
+        int r;
+        if ((r = vgs_pods_upload(g->ctx[i], n_pods, pods, n_reqs, reqs)) != VGS_OK) return r;
+        if ((r = vgs_score_resident(g->ctx[i])) != VGS_OK) return r;
+        return vgs_resolve_local(g->ctx[i]);
+    };
+    for (int i = 1; i < g->G; i++) g->worker[i].submit([shard_pass, i] { return shard_pass(i); });
+    rc = shard_pass(0);
+    int bad = rc != VGS_OK ? 0 : -1;
+    for (int i = 1; i < g->G; i++) {
+        const int r = g->worker[i].wait();
+        if (r != VGS_OK && bad < 0) bad = i, rc = r;
+    }
+    if (bad >= 0) return gfail_ctx(g, rc, bad, "shard pass");
     {
         Dev d(g->cfg.devices[0]);
         cudaEventRecord(g->ev_t0, g->st[0]);

@@ -605,7 +605,7 @@ def main():
                 except Exception as e:  # reported, not fatal: the torchrun path above is the measured headline
                     group[name] = {"error": str(e)[:300]}
             group["api"] = ("vgs_group_score_batch: request records H2D to every GPU + score + local resolve + exchange + "
-                            "merge + results D2H, one host thread, snapshot resident; median wall clock of 20 calls")
+                            "merge + results D2H, one caller thread + one helper thread per further GPU, snapshot resident; median wall clock of 20 calls")
             store.set("vgs_group_leg_done", "1")
         else:
             store.wait(["vgs_group_leg_done"])

@@ -275,7 +275,8 @@ int vgs_exchange_merge(vgs_ctx *ctx, const void *dev_gathered, int32_t n_shards,
 int vgs_results_device(vgs_ctx *ctx, vgs_result **dev_results, vgs_pick **dev_picks);
 
 /* ---- node sharding inside the library: several GPUs of one box behind one handle --------------------
- * (No counterpart in the reference.)  One process, one host thread, one context per GPU; GPU g owns the
+ * (No counterpart in the reference.)  One process, one call, one context per GPU (the library keeps one helper
+ * thread per GPU beyond the first for the per-shard host work of a pass); GPU g owns the
  * contiguous rows [g * ceil(N/G), (g+1) * ceil(N/G)) of the snapshot.  A pass scores
  * every shard with no collective, every shard resolves its own best node per pod, and the shards'
  * [keys | counts | picks] blocks (vgs_exchange_block) are combined by ONE exchange:
