@@ -57,6 +57,7 @@ struct vgs_ctx {
     int4 *d_walk = nullptr;
     uint32_t *d_status = nullptr;
     uint32_t *h_status = nullptr; // pinned
+    unsigned int *d_done = nullptr; // CTA counter of the single-launch Filter kernel, zero at rest
     int32_t n_nodes = 0, dmax = 0, n_tiles = 0;
     bool have_snapshot = false;
     bool snap_pending = false;    // vgs_snapshot_upload_async: copy + K0 queued, status not looked at yet
@@ -219,6 +220,7 @@ void free_all(vgs_ctx *c) {
     if (c->ev_snap) cudaEventDestroy(c->ev_snap);
     if (c->ev_delta) cudaEventDestroy(c->ev_delta);
     cudaFree(c->d_status);
+    cudaFree(c->d_done);
     cudaFreeHost(c->h_status);
     cudaFree(c->d_deltas);
     cudaFreeHost(c->h_deltas);
@@ -329,6 +331,8 @@ int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
     CUI(cudaMalloc(&c->d_status, 2 * sizeof(uint32_t))); // [0] S_* flags, [1] largest type id in use
     CUI(cudaMemset(c->d_status, 0, 2 * sizeof(uint32_t)));
     CUI(cudaMallocHost(&c->h_status, 2 * sizeof(uint32_t)));
+    CUI(cudaMalloc(&c->d_done, sizeof(unsigned int)));
+    CUI(cudaMemset(c->d_done, 0, sizeof(unsigned int)));
     c->max_deltas = 16384;
     CUI(cudaEventCreateWithFlags(&c->ev_delta, cudaEventDisableTiming));
     CUI(cudaMalloc(&c->d_deltas, c->max_deltas * sizeof(vgs_delta)));
@@ -584,6 +588,29 @@ int vgs_snapshot_download(vgs_ctx *c, int32_t *const planes[VGS_NUM_PLANES], int
 
 // ---- pod batch ---------------------------------------------------------------------
 
+// a ContainerDeviceRequest as the kernels see it
+static DevReq to_dev_req(const vgs_req &q) {
+    DevReq d;
+    d.nums = q.nums;
+    d.memfix = q.memreq > 0 ? q.memreq : 0;                            // score.go:114-116
+    d.pct = q.mempct;
+    d.coresreq = q.coresreq;
+    d.flags = 0;
+    if (q.mempct != VGS_MEMPCT_UNSET && q.memreq == 0) d.flags |= R_USEPCT; // score.go:117
+    if (q.flags & VGS_REQ_NUMA_BIND) d.flags |= R_NUMA;
+    d.blockmask = M_NOFREE | M_PAD;
+    if (q.flags & VGS_REQ_IDLE_SHARE) { // cambricon/device.go:97-99
+        d.flags |= R_IDLE;
+        d.blockmask |= M_BUSY370;
+    }
+    if (q.coresreq == 100) d.blockmask |= M_EXCL; // score.go:128
+    if (q.coresreq == 0) d.blockmask |= M_FULL;   // score.go:132
+    if (q.coresreq > 100) d.blockmask |= M_ALWAYS; // score.go:110-113: never fits
+    d.mask_lo = (uint32_t)q.typemask;
+    d.mask_hi = (uint32_t)(q.typemask >> 32);
+    return d;
+}
+
 // lay the staging block out for a batch of n_pods / n_reqs; returns the bytes in use
 static size_t stage_layout(vgs_ctx *c, size_t P, size_t R) {
     size_t o = 0;
@@ -709,25 +736,7 @@ static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, i
     for (int32_t r = 0; r < n_reqs; r++) {
         const vgs_req &q = reqs[r];
         if (q.nums < 1) return fail(c, VGS_EINVAL, "request with Nums < 1 (k8sutil/pod.go:33 drops those)");
-        DevReq d;
-        d.nums = q.nums;
-        d.memfix = q.memreq > 0 ? q.memreq : 0;                            // score.go:114-116
-        d.pct = q.mempct;
-        d.coresreq = q.coresreq;
-        d.flags = 0;
-        if (q.mempct != VGS_MEMPCT_UNSET && q.memreq == 0) d.flags |= R_USEPCT; // score.go:117
-        if (q.flags & VGS_REQ_NUMA_BIND) d.flags |= R_NUMA;
-        d.blockmask = M_NOFREE | M_PAD;
-        if (q.flags & VGS_REQ_IDLE_SHARE) { // cambricon/device.go:97-99
-            d.flags |= R_IDLE;
-            d.blockmask |= M_BUSY370;
-        }
-        if (q.coresreq == 100) d.blockmask |= M_EXCL; // score.go:128
-        if (q.coresreq == 0) d.blockmask |= M_FULL;   // score.go:132
-        if (q.coresreq > 100) d.blockmask |= M_ALWAYS; // score.go:110-113: never fits
-        d.mask_lo = (uint32_t)q.typemask;
-        d.mask_hi = (uint32_t)(q.typemask >> 32);
-        hreq[r] = d;
+        hreq[r] = to_dev_req(q);
         hpick[r] = (int32_t)picks;
         picks += q.nums;
         if (picks > c->cfg.max_picks) return fail(c, VGS_ETOOBIG, "sum of nums exceeds max_picks");
@@ -1048,12 +1057,81 @@ int vgs_results_download(vgs_ctx *c, vgs_result *results, vgs_pick *picks) {
     return download_locked(c, results, picks);
 }
 
+// The Filter call proper (one pod, a handful of requests, snapshot resident): ONE kernel launch and one stream
+// synchronisation -- the pod travels as launch parameters, the last CTA of the score kernel resolves the winner
+// and writes the pinned host mirrors.  Returns 1 when the call is not of that shape (the phased path takes it).
+static int filter_one_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_reqs, const vgs_req *reqs,
+                             vgs_result *results, vgs_pick *picks) {
+    if (n_pods != 1 || !pods || !reqs || !results || n_reqs < 1 || n_reqs > kFilterMaxReqs || c->cfg.verify ||
+        !c->tune.filter_one_launch || c->n_tiles <= 0)
+        return 1;
+    if (pods[0].req_begin != 0 || pods[0].n_reqs != n_reqs) return 1;
+    FilterOne fo;
+    memset(&fo, 0, sizeof fo);
+    int32_t prev = -1, total = 0;
+    for (int32_t r = 0; r < n_reqs; r++) {
+        if (reqs[r].nums < 1 || reqs[r].ctr < prev || reqs[r].ctr < 0) return 1; // the phased path words the error
+        fo.reqs[r] = to_dev_req(reqs[r]);
+        if (reqs[r].ctr != prev) fo.reqs[r].flags |= R_NEWCTR;
+        prev = reqs[r].ctr;
+        fo.pick_begin[r] = total;
+        total += reqs[r].nums;
+        if (total > c->cfg.max_picks || total > kWalkMaxPicks) return 1;
+    }
+    if (total > 0 && !picks) return 1;
+    fo.pick_begin[n_reqs] = total;
+    fo.pod.req_begin = 0, fo.pod.n_reqs = n_reqs, fo.pod.orig = 0;
+    fo.pod.flags = gen_pod_flags(fo.reqs, n_reqs);
+    fo.raw = raw_const(c);
+    fo.dmax = c->dmax;
+    fo.results = c->d_results, fo.host_results = c->h_results;
+    fo.picks = c->d_picks, fo.host_picks = c->h_picks;
+    fo.status = c->d_status, fo.host_status = c->h_status;
+    fo.done = c->d_done;
+    c->have_pods = false; // the staging block does not hold this pod
+    c->scored = c->resolved = false;
+    if (c->dirty_pods > 0) {
+        CU(cudaMemsetAsync(c->d_keys, 0, (size_t)c->cfg.max_pods * 12, c->st));
+        c->dirty_pods = 0;
+    }
+    ScoreArgs a;
+    a.walk = c->d_walk, a.n_tiles = c->n_tiles, a.n_nodes = c->n_nodes, a.row_base = c->cfg.row_base;
+    a.keys = c->d_keys, a.counts = c->d_counts;
+    a.vfit = nullptr, a.vscore = nullptr, a.vwords = 0;
+    for (int i = 0; i < EV_N; i++) c->ev_set[i] = false;
+    rec(c, EV_SC0);
+    CU(launch_filter_one(c->dm, c->cfg.device, a, fo, c->st));
+    rec(c, EV_SC1);
+    c->launches++;
+    {
+        const int32_t df = c->plan.dict_full;
+        memset(&c->plan, 0, sizeof c->plan);
+        c->plan.dict_full = df;
+        c->plan.cls[3].pods = 1, c->plan.cls[3].kernel = VGS_KERNEL_GENERAL, c->plan.cls[3].launches = 1;
+    }
+    CU(cudaStreamSynchronize(c->st));
+    c->stage_in_flight = false;
+    int rc = check_status(c);
+    if (rc != VGS_OK) {
+        if (*c->h_status & (S_DELTA | S_RANGE | S_TYPE | S_NDEV)) c->have_snapshot = false;
+        cudaMemsetAsync(c->d_status, 0, sizeof(uint32_t), c->st);
+        return rc;
+    }
+    results[0] = c->h_results[0];
+    if (total) memcpy(picks, c->h_picks, (size_t)total * sizeof(vgs_pick));
+    return VGS_OK;
+}
+
 int vgs_score_batch(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_reqs, const vgs_req *reqs,
                     vgs_result *results, vgs_pick *picks) {
     if (!c) return VGS_EINVAL;
     std::lock_guard<std::mutex> lk(c->mu);
     DeviceGuard g(c->cfg.device);
     int rc;
+    if (n_pods == 1) {
+        if ((rc = finish_snapshot(c)) != VGS_OK) return rc;
+        if (c->have_snapshot && (rc = filter_one_locked(c, n_pods, pods, n_reqs, reqs, results, picks)) != 1) return rc;
+    }
     c->chained = true;
     if ((rc = pods_upload_locked(c, n_pods, pods, n_reqs, reqs)) == VGS_OK && (rc = score_locked(c)) == VGS_OK &&
         (rc = resolve_locked(c)) == VGS_OK)
@@ -1225,6 +1303,8 @@ void vgs_tuning_defaults(vgs_tuning *t) {
     t->class_order = 1;
     t->zero_copy_upload = 1;
     t->general_legacy = 0;
+    t->max_ctas = 0;
+    t->filter_one_launch = 1;
 }
 
 int vgs_last_plan(vgs_ctx *c, vgs_plan *out) {

@@ -34,6 +34,7 @@
 #include "vgs_device.cuh"
 #include "vgs_kernels.h"
 #include "vgs_layout.h"
+#include "vgs_resolve.cuh"
 
 namespace vgs {
 
@@ -122,12 +123,18 @@ __device__ __forceinline__ void numa_filter(uint32_t (&cand)[DM], int32_t nums) 
     for (int j = 0; j < DM; j++) cand[j] = (cand[j] >> kNumaShift) == gsel ? cand[j] : 0u;
 }
 
-template <int DM, bool VERIFY>
+// FILTER: the single-pod Filter call in ONE launch.  The pod and its requests arrive as launch parameters (no
+// staging copy in front of the kernel), and the CTA that finishes last resolves the winner (the resolve kernel's
+// body, vgs_resolve.cuh) and stores result, picks and the status word straight into the pinned host mirrors:
+// the call is one launch + one stream synchronisation.
+template <int DM, bool VERIFY, bool FILTER>
 __global__ void __launch_bounds__(128)
     k1_score_walk(const int4 *__restrict__ walk, int32_t n_tiles, int32_t n_nodes, int32_t row_base,
-                  const DevReq *__restrict__ reqs, const GenPod *__restrict__ pods, int32_t n_pods, ScoreLaunch L,
+                  const DevReq *__restrict__ reqs_g, const GenPod *__restrict__ pods_g, int32_t n_pods, ScoreLaunch L,
                   unsigned long long *__restrict__ keys, int32_t *__restrict__ counts, uint32_t *__restrict__ vfit,
-                  float *__restrict__ vscore, int32_t vwords) {
+                  float *__restrict__ vscore, int32_t vwords, const __grid_constant__ FilterOne fo) {
+    const DevReq *reqs = FILTER ? fo.reqs : reqs_g;
+    const GenPod *pods = FILTER ? &fo.pod : pods_g;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int n_items = L.n_chunks * L.n_tile_groups;
     const bool small = n_pods <= kWarp; // see flush_small
@@ -207,7 +214,7 @@ __global__ void __launch_bounds__(128)
                     if (uniform_type) {
                         // one type mask for the whole pod: a device that fails it never fits, whatever the
                         // request -- it gets a free memory no request is small enough for
-                        const DevReq r0 = load_req(&reqs[pod.req_begin]);
+                        const DevReq r0 = FILTER ? reqs[pod.req_begin] : load_req(&reqs[pod.req_begin]);
 #pragma unroll
                         for (int j = 0; j < DM; j++)
                             fm[j] = type_ok(r0.mask_lo, r0.mask_hi, mt[j]) ? fm[j] : INT32_MIN;
@@ -215,7 +222,7 @@ __global__ void __launch_bounds__(128)
                 }
 
                 for (int r = r_first; r < pod.n_reqs; r++) {
-                    const DevReq rq = load_req(&reqs[pod.req_begin + r]);
+                    const DevReq rq = FILTER ? reqs[pod.req_begin + r] : load_req(&reqs[pod.req_begin + r]);
                     if (rq.flags & R_NEWCTR) { // score.go:180,203: one container done
                         // (a lane that is out has taken nothing: free = 0 would send the whole warp through the
                         // division's slow path)
@@ -325,6 +332,59 @@ __global__ void __launch_bounds__(128)
         }
     }
     if (small) flush_small<4>(acckey, acccnt, lane, warp, n_pods, nullptr, pods, keys, counts);
+    if constexpr (FILTER) {
+        // last CTA out resolves the winner (thread 0 published this CTA's candidate just above)
+        __shared__ bool s_last;
+        if (threadIdx.x == 0) {
+            __threadfence();
+            s_last = atomicAdd(fo.done, 1u) == gridDim.x - 1u;
+        }
+        __syncthreads();
+        if (!s_last || threadIdx.x != 0) return;
+        *fo.done = 0u; // zero at rest: the next call counts again
+        __threadfence();
+        const unsigned long long key = atomicMax(&keys[0], 0ull);
+        vgs_result res;
+        res.fit_count = atomicAdd(&counts[0], 0);
+        keys[0] = 0ull; // the candidate block goes back to its resting state
+        counts[0] = 0;
+        const int32_t pick_hi = fo.pick_begin[fo.pod.n_reqs];
+        auto finish = [&](bool zero_picks) {
+            if (zero_picks) {
+                vgs_pick z;
+                z.slot = z.usedmem = z.usedcores = 0;
+                for (int32_t i = 0; i < pick_hi; i++) fo.picks[i] = z, fo.host_picks[i] = z;
+            }
+            fo.results[0] = res;
+            fo.host_results[0] = res;
+            __threadfence();
+            fo.host_status[0] = *reinterpret_cast<volatile uint32_t *>(fo.status);
+        };
+        if (key == 0ull) {
+            res.best_row = -1, res.score = 0.0f, res.n_picks = 0;
+            finish(true);
+            return;
+        }
+        const uint32_t kbits = unorder_bits((uint32_t)(key >> 32));
+        res.best_row = (int32_t)(uint32_t)key;
+        res.score = __uint_as_float(kbits);
+        res.n_picks = pick_hi;
+        const int32_t row = res.best_row - row_base;
+        if (row < 0 || row >= n_nodes) { // cannot happen on a single shard; same answer as the resolve kernel
+            finish(true);
+            return;
+        }
+        ResolveOut ro;
+        resolve_row(
+            fo.raw, row, fo.dmax, fo.pod.n_reqs, [&](int r) { return fo.reqs[r]; },
+            [&](int r, int t, const vgs_pick &pk) {
+                fo.picks[fo.pick_begin[r] + t] = pk;
+                fo.host_picks[fo.pick_begin[r] + t] = pk;
+            },
+            ro);
+        if (!ro.alive || __float_as_uint(ro.score) != kbits) atomicOr(fo.status, S_MISMATCH);
+        finish(false);
+    }
 }
 
 template <int DM>
@@ -332,18 +392,35 @@ static cudaError_t launch_walk_t(int dev, const ScoreArgs &a, const DevReq *reqs
                                  cudaStream_t st) {
     ScoreLaunch L;
     cudaError_t e;
+    static const FilterOne none{};
     if (a.vfit) {
-        auto k = k1_score_walk<DM, true>;
+        auto k = k1_score_walk<DM, true, false>;
         if ((e = plan_score_launch(reinterpret_cast<const void *>(k), dev, a.n_tiles, n_pods, 4, 0, &L)) != cudaSuccess) return e;
         k<<<L.grid, L.block, 0, st>>>(a.walk, a.n_tiles, a.n_nodes, a.row_base, reqs, pods, n_pods, L, a.keys, a.counts,
-                                     a.vfit, a.vscore, a.vwords);
+                                     a.vfit, a.vscore, a.vwords, none);
     } else {
-        auto k = k1_score_walk<DM, false>;
+        auto k = k1_score_walk<DM, false, false>;
         if ((e = plan_score_launch(reinterpret_cast<const void *>(k), dev, a.n_tiles, n_pods, 4, 0, &L)) != cudaSuccess) return e;
         k<<<L.grid, L.block, 0, st>>>(a.walk, a.n_tiles, a.n_nodes, a.row_base, reqs, pods, n_pods, L, a.keys, a.counts,
-                                     nullptr, nullptr, 0);
+                                     nullptr, nullptr, 0, none);
     }
     return cudaGetLastError();
+}
+
+template <int DM>
+static cudaError_t launch_filter_t(int dev, const ScoreArgs &a, const FilterOne &fo, cudaStream_t st) {
+    ScoreLaunch L;
+    cudaError_t e;
+    auto k = k1_score_walk<DM, false, true>;
+    if ((e = plan_score_launch(reinterpret_cast<const void *>(k), dev, a.n_tiles, 1, 4, 0, &L)) != cudaSuccess) return e;
+    k<<<L.grid, L.block, 0, st>>>(a.walk, a.n_tiles, a.n_nodes, a.row_base, nullptr, nullptr, 1, L, a.keys, a.counts,
+                                 nullptr, nullptr, 0, fo);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_filter_one(int dm, int dev, const ScoreArgs &a, const FilterOne &fo, cudaStream_t st) {
+    if (a.n_tiles <= 0) return cudaErrorInvalidValue; // the caller takes the phased path for an empty snapshot
+    return dm == 8 ? launch_filter_t<8>(dev, a, fo, st) : launch_filter_t<12>(dev, a, fo, st);
 }
 
 cudaError_t launch_score_walk(int dm, int dev, const ScoreArgs &a, const DevReq *reqs, const GenPod *pods,

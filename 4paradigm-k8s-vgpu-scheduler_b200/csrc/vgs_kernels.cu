@@ -31,6 +31,7 @@
 #include "vgs_device.cuh"
 #include "vgs_kernels.h"
 #include "vgs_layout.h"
+#include "vgs_resolve.cuh"
 
 namespace vgs {
 
@@ -1374,110 +1375,23 @@ __global__ void __launch_bounds__(64)
         return;
     }
 
-    int32_t nd = raw.ndev[row];
     const size_t base = (size_t)row * dmax;
-    int32_t used[VGS_MAX_DEVICES], usedmem[VGS_MAX_DEVICES], usedcores[VGS_MAX_DEVICES];
-    int32_t count[VGS_MAX_DEVICES], totalmem[VGS_MAX_DEVICES], totalcore[VGS_MAX_DEVICES];
-    int32_t numa[VGS_MAX_DEVICES], type[VGS_MAX_DEVICES], ord[VGS_MAX_DEVICES];
-#pragma unroll
-    for (int d = 0; d < VGS_MAX_DEVICES; d++) { // all loads issued at once: this thread is latency-bound
-        const bool on = d < dmax; // (not d < ndev: that would put ndev's own load in front of all of these)
-        used[d] = on ? raw.p[VGS_PLANE_USED][base + d] : 0;
-        usedmem[d] = on ? raw.p[VGS_PLANE_USEDMEM][base + d] : 0;
-        usedcores[d] = on ? raw.p[VGS_PLANE_USEDCORES][base + d] : 0;
-        count[d] = on ? raw.p[VGS_PLANE_COUNT][base + d] : 0;
-        totalmem[d] = on ? raw.p[VGS_PLANE_TOTALMEM][base + d] : 0;
-        totalcore[d] = on ? raw.p[VGS_PLANE_TOTALCORE][base + d] : 0;
-        numa[d] = on ? raw.p[VGS_PLANE_NUMA][base + d] : 0;
-        type[d] = on ? raw.p[VGS_PLANE_TYPEID][base + d] : 0;
-        ord[d] = d;
-    }
-    nd = min(max(nd, 0), dmax);
-
-    float score = 0.0f;
-    bool alive = true, in_ctr = false;
-    int32_t total = 0, free_ = 0, sums = 0;
-    for (int r = 0; r < pod.n_reqs && alive; r++) {
-        const DevReq rq = reqs[pod.req_begin + r];
-        if (rq.flags & R_NEWCTR) {
-            if (in_ctr) score = __fadd_rn(score, container_score(total, free_, nd - sums));
-            total = free_ = sums = 0;
-            in_ctr = true;
-        }
-        sums += rq.nums;
-        if (rq.nums > nd) { // score.go:162
-            alive = false;
-            break;
-        }
-        // stable insertion sort, ascending (Numa, Count-Used)   score.go:45-50,165
-        for (int i = 1; i < nd; i++) {
-            for (int j = i; j > 0; j--) {
-                int a = ord[j], b = ord[j - 1];
-                bool less = numa[a] == numa[b]
-                                ? wrap_sub(count[a], used[a]) < wrap_sub(count[b], used[b])
-                                : numa[a] < numa[b];
-                if (!less) break;
-                ord[j] = b;
-                ord[j - 1] = a;
-            }
-        }
-        int32_t left = rq.nums, prevnuma = -1, nt = 0;
-        int32_t tdev[VGS_MAX_DEVICES], tmem[VGS_MAX_DEVICES];
-        bool ok = false;
-        for (int i = nd - 1; i >= 0; i--) { // score.go:92
-            const int d = ord[i];
-            uint32_t t = (uint32_t)type[d];
-            if (!(((t & 32u) ? rq.mask_hi : rq.mask_lo) >> (t & 31u) & 1u)) continue;
-            if ((rq.flags & R_IDLE) && (raw.idle_types >> t & 1ull) && used[d] > 0)
-                continue; // cambricon/device.go:97-99, part of the type check
-            if ((rq.flags & R_NUMA) && prevnuma != numa[d]) { // :99-104
-                left = rq.nums;
-                prevnuma = numa[d];
-                nt = 0;
-            }
-            if (count[d] <= used[d]) continue; // :107
-            if (rq.coresreq > 100) break;      // :110
-            int32_t memreq = (rq.flags & R_USEPCT) ? pct_mem(totalmem[d], rq.pct) : rq.memfix;
-            if (wrap_sub(totalmem[d], usedmem[d]) < memreq) continue;
-            if (wrap_sub(totalcore[d], usedcores[d]) < rq.coresreq) continue;
-            if (totalcore[d] == 100 && rq.coresreq == 100 && used[d] > 0) continue;
-            if (totalcore[d] != 0 && usedcores[d] == totalcore[d] && rq.coresreq == 0) continue;
-            if (left > 0) {
-                left--;
-                tdev[nt] = d;
-                tmem[nt] = memreq;
-                nt++;
-            }
-            if (left == 0) {
-                ok = true;
-                break;
-            }
-        }
-        if (!ok) {
-            alive = false;
-            break;
-        }
-        const int32_t pb = pick_begin[pod.req_begin + r];
-        for (int t = 0; t < nt; t++) { // :168-174
-            const int d = tdev[t];
-            total = wrap_add(total, count[d]);
-            free_ = wrap_add(free_, wrap_sub(count[d], used[d]));
-            used[d] = wrap_add(used[d], 1);
-            usedcores[d] = wrap_add(usedcores[d], rq.coresreq);
-            usedmem[d] = wrap_add(usedmem[d], tmem[t]);
-            vgs_pick pk;
-            pk.slot = d;
-            pk.usedmem = tmem[t];
-            pk.usedcores = rq.coresreq;
+    ResolveOut ro;
+    resolve_row(
+        raw, row, dmax, pod.n_reqs, [&](int r) { return reqs[pod.req_begin + r]; },
+        [&](int r, int t, const vgs_pick &pk) {
+            const int32_t pb = pick_begin[pod.req_begin + r];
             picks[pb + t] = pk;
             if (host_picks) host_picks[pb + t] = pk;
-        }
-    }
+        },
+        ro);
+    const bool alive = ro.alive;
+    const float score = ro.score;
     if (commit_rowlist && alive) {
-        for (int d = 0; d < nd; d++) { // the mutated copies ARE the committed state
-            const_cast<int32_t *>(raw.p[VGS_PLANE_USED])[base + d] = used[d];
-            const_cast<int32_t *>(raw.p[VGS_PLANE_USEDMEM])[base + d] = usedmem[d];
-            const_cast<int32_t *>(raw.p[VGS_PLANE_USEDCORES])[base + d] = usedcores[d];
+        for (int d = 0; d < ro.nd; d++) { // the mutated copies ARE the committed state
+            const_cast<int32_t *>(raw.p[VGS_PLANE_USED])[base + d] = ro.used[d];
+            const_cast<int32_t *>(raw.p[VGS_PLANE_USEDMEM])[base + d] = ro.usedmem[d];
+            const_cast<int32_t *>(raw.p[VGS_PLANE_USEDCORES])[base + d] = ro.usedcores[d];
         }
         commit_rowlist[p] = row;
         if (commit_walk) { // re-prepare the touched row right here: the next pod's score kernel reads it
@@ -1485,7 +1399,6 @@ __global__ void __launch_bounds__(64)
             else prepare_node<12>(raw, row, n_nodes, dmax, commit_walk, status);
         }
     }
-    if (alive && in_ctr) score = __fadd_rn(score, container_score(total, free_, nd - sums));
     if (!alive || __float_as_uint(score) != kbits) atomicOr(status, S_MISMATCH);
     leave();
 }

@@ -45,6 +45,21 @@ cudaError_t launch_score_general(int dm, int dev, const ScoreArgs &a, const DevR
 // the walk kernel (vgs_general.cu): multi-request pods by ordering keys; pods flagged G_LEGACY must not come here
 cudaError_t launch_score_walk(int dm, int dev, const ScoreArgs &a, const DevReq *reqs, const GenPod *pods,
                               int32_t n_pods, cudaStream_t st);
+// The single-pod Filter call as ONE launch: the pod by value, the outputs it writes (device arrays and the pinned
+// host mirrors), a CTA counter that is zero at rest.
+constexpr int kFilterMaxReqs = 8;
+struct FilterOne {
+    GenPod pod; // req_begin = 0, orig = 0
+    DevReq reqs[kFilterMaxReqs];
+    int32_t pick_begin[kFilterMaxReqs + 1];
+    RawPlanes raw;
+    int32_t dmax;
+    vgs_result *results, *host_results;
+    vgs_pick *picks, *host_picks;
+    uint32_t *status, *host_status;
+    unsigned int *done;
+};
+cudaError_t launch_filter_one(int dm, int dev, const ScoreArgs &a, const FilterOne &fo, cudaStream_t st);
 // launch geometry of a thread-per-node score kernel (persistent grid over (tile group, pod chunk) items)
 cudaError_t plan_score_launch(const void *kernel, int dev, int32_t n_tiles, int32_t n_pods, int max_warps,
                               int smem_per_pod, ScoreLaunch *L);

@@ -504,7 +504,8 @@ def main():
         k1 = k1s[len(k1s) // 2] * 1e-3
         b1 = algorithmic_bytes(npg, D, 1, 1)
         latency = {"p50_us": 1e6 * ts[len(ts) // 2], "p99_us": 1e6 * ts[int(len(ts) * 0.99)], "nodes": npg, "pods": 1,
-                   "api": "vgs_score_batch (request H2D + kernels + result D2H), snapshot resident",
+                   "api": "vgs_score_batch, snapshot resident: one launch (pod as launch parameters, last CTA resolves into "
+                          "pinned buffers) + one stream synchronisation; k1_us = that kernel",
                    "k1_us": 1e6 * k1, "k1_algorithmic_GBps": b1 / k1 / 1e9}
         ctx.pods_upload(pods, reqs)  # restore the batch for anything that follows
 

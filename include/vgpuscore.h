@@ -95,7 +95,10 @@ typedef struct {
     int32_t zero_copy_upload; /* 1 = pinned host planes are pulled over PCIe by a copy kernel (default), 0 = cudaMemcpyAsync */
     int32_t general_legacy;   /* 1 = multi-request pods run on the round-1 all-pairs kernel (A/B and fallback testing), 0 = default */
     int32_t max_ctas;         /* upper bound on the CTAs of one pod-sliced score launch (sharing the GPU, tests): 0 = one wave */
-    int32_t reserved[5];
+    int32_t filter_one_launch;/* 1 = vgs_score_batch of ONE pod with <= 8 requests runs as a single kernel launch (the pod travels
+                               * as launch parameters, the last CTA resolves the winner into the pinned result buffers);
+                               * 0 = the phased path (copy, score kernel, resolve kernel) */
+    int32_t reserved[4];
 } vgs_tuning;
 void vgs_tuning_defaults(vgs_tuning *out);
 

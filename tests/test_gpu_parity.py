@@ -244,6 +244,48 @@ def test_delta_equals_rebuild(built):
         assert_same(ctx.score(batch), first, "after undo")
 
 
+@pytest.mark.parametrize("k", K["kats"], ids=[k["name"] for k in K["kats"]])
+def test_kat_single_launch_filter(built, k):
+    """the Filter call proper -- one pod, snapshot resident, no verify buffers -- runs as ONE kernel launch (pod as
+    launch parameters, last CTA resolves): every known-answer vector through it, and through the phased path"""
+    snap, batch = kat_inputs(k)
+    for one_launch in (1, 0):
+        with v.Context(max_nodes=snap.n_nodes, max_devices=snap.dmax, max_pods=1, max_reqs=32, max_picks=256,
+                       tuning={"filter_one_launch": one_launch}) as ctx:
+            ctx.upload(snap)
+            l0 = ctx.timing().kernel_launches
+            res = ctx.score(batch)
+            launches = ctx.timing().kernel_launches - l0
+            check_kat(k, res, batch)
+            check_kat(k, ctx.score(batch), batch)  # and again: the candidate block and the CTA counter are back at rest
+        if batch.n_reqs <= 8:
+            assert launches == (1 if one_launch else 2), (one_launch, launches)
+
+
+def test_single_launch_filter_random_pods(built):
+    """random single pods (multi-container, numa-bind, percentages, exclusive, > devices) one call each against a
+    ragged snapshot: winner, score bits, fit count and picks equal the oracle's; 12-slot nodes too"""
+    for dmax, seed in ((8, 31), (12, 32), (3, 33)):
+        rng = np.random.default_rng(seed)
+        snap = _random_snapshot(rng, 3000 + seed, dmax)
+        batch = _random_pods(rng, 60, dmax)
+        want = oracle.score_packed(snap, batch)
+        with v.Context(max_nodes=snap.n_nodes, max_devices=dmax, max_pods=2, max_reqs=64, max_picks=512) as ctx:
+            ctx.upload(snap)
+            pb = batch.pick_begin
+            for p in range(batch.n_pods):
+                got = ctx.score(batch.select([p]))
+                r0, r1 = batch.pod_req_range(p)
+                assert got.best_row[0] == want.best_row[p], (dmax, p)
+                assert got.score.view(np.uint32)[0] == want.score.view(np.uint32)[p], (dmax, p)
+                assert got.fit_count[0] == want.fit_count[p], (dmax, p)
+                assert np.array_equal(got.picks, want.picks[int(pb[r0]):int(pb[r1])]), (dmax, p)
+            # a batch of two goes the phased way and leaves the single-launch path usable afterwards
+            two = ctx.score(batch.select([0, 1]))
+            assert np.array_equal(two.best_row, want.best_row[:2])
+            assert ctx.score(batch.select([5])).best_row[0] == want.best_row[5]
+
+
 def test_delta_errors_surface_at_the_next_status_read(built):
     """vgs_snapshot_delta only queues work; a delta naming a slot the node does not have is reported by the next
     call that reads the status word, and the snapshot then has to be uploaded again"""
