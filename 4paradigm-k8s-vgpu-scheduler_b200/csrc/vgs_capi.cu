@@ -1165,8 +1165,33 @@ int vgs_drain_batch(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_r
     const GenPod *dall = reinterpret_cast<const GenPod *>(c->d_stage + c->off_genall);
     // one pod at a time, everything chained on the stream: score (the key/count slot of pod p is
     // addressed through GenPod.orig) -> resolve + commit into the raw planes + re-prepare the row (K3)
+    const DevReq *hreq_all = reinterpret_cast<const DevReq *>(c->h_stage + c->off_reqs);
+    const int32_t *hpick_all = reinterpret_cast<const int32_t *>(c->h_stage + c->off_pick);
     for (int32_t p = 0; p < n_pods; p++) {
-        if (reinterpret_cast<const GenPod *>(c->h_stage + c->off_genall)[p].flags & G_LEGACY)
+        const GenPod &gp = reinterpret_cast<const GenPod *>(c->h_stage + c->off_genall)[p];
+        if (gp.n_reqs <= kFilterMaxReqs && !(gp.flags & G_LEGACY) && c->n_tiles > 0 && c->tune.filter_one_launch) {
+            // one launch per pod: score, last CTA resolves, commits into the raw planes and re-prepares the row
+            FilterOne fo;
+            memset(&fo, 0, sizeof fo);
+            for (int32_t r = 0; r < gp.n_reqs; r++) {
+                fo.reqs[r] = hreq_all[gp.req_begin + r];
+                fo.pick_begin[r] = hpick_all[gp.req_begin + r];
+            }
+            fo.pick_begin[gp.n_reqs] = hpick_all[gp.req_begin + gp.n_reqs];
+            fo.pod.req_begin = 0, fo.pod.n_reqs = gp.n_reqs, fo.pod.orig = 0, fo.pod.flags = gp.flags;
+            fo.raw = raw_const(c);
+            fo.dmax = c->dmax;
+            // (pick_begin holds batch-wide offsets: the picks arrays are passed whole)
+            fo.results = c->d_results + p, fo.host_results = c->h_results + p;
+            fo.picks = c->d_picks, fo.host_picks = c->h_picks;
+            fo.status = c->d_status, fo.host_status = c->h_status;
+            fo.done = c->d_done;
+            fo.commit_walk = c->d_walk;
+            CU(launch_filter_one(c->dm, c->cfg.device, a, fo, c->st));
+            c->launches++;
+            continue;
+        }
+        if (gp.flags & G_LEGACY)
             CU(launch_score_general(c->dm, c->cfg.device, a, dreq, dall + p, 1, c->st));
         else
             CU(launch_score_walk(c->dm, c->cfg.device, a, dreq, dall + p, 1, c->st));

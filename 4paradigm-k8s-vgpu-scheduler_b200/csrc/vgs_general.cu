@@ -34,6 +34,7 @@
 #include "vgs_device.cuh"
 #include "vgs_kernels.h"
 #include "vgs_layout.h"
+#include "vgs_prepare.cuh"
 #include "vgs_resolve.cuh"
 
 namespace vgs {
@@ -348,12 +349,12 @@ __global__ void __launch_bounds__(128)
         res.fit_count = atomicAdd(&counts[0], 0);
         keys[0] = 0ull; // the candidate block goes back to its resting state
         counts[0] = 0;
-        const int32_t pick_hi = fo.pick_begin[fo.pod.n_reqs];
+        const int32_t pick_lo = fo.pick_begin[0], pick_hi = fo.pick_begin[fo.pod.n_reqs];
         auto finish = [&](bool zero_picks) {
             if (zero_picks) {
                 vgs_pick z;
                 z.slot = z.usedmem = z.usedcores = 0;
-                for (int32_t i = 0; i < pick_hi; i++) fo.picks[i] = z, fo.host_picks[i] = z;
+                for (int32_t i = pick_lo; i < pick_hi; i++) fo.picks[i] = z, fo.host_picks[i] = z;
             }
             fo.results[0] = res;
             fo.host_results[0] = res;
@@ -368,7 +369,7 @@ __global__ void __launch_bounds__(128)
         const uint32_t kbits = unorder_bits((uint32_t)(key >> 32));
         res.best_row = (int32_t)(uint32_t)key;
         res.score = __uint_as_float(kbits);
-        res.n_picks = pick_hi;
+        res.n_picks = pick_hi - pick_lo;
         const int32_t row = res.best_row - row_base;
         if (row < 0 || row >= n_nodes) { // cannot happen on a single shard; same answer as the resolve kernel
             finish(true);
@@ -383,6 +384,15 @@ __global__ void __launch_bounds__(128)
             },
             ro);
         if (!ro.alive || __float_as_uint(ro.score) != kbits) atomicOr(fo.status, S_MISMATCH);
+        if (fo.commit_walk && ro.alive) { // sequential drain: the placement becomes usage (addPod, scheduler.go:280-297,394)
+            const size_t base = (size_t)row * fo.dmax; // and the touched row of the walk copy is prepared again
+            for (int d = 0; d < ro.nd; d++) {
+                const_cast<int32_t *>(fo.raw.p[VGS_PLANE_USED])[base + d] = ro.used[d];
+                const_cast<int32_t *>(fo.raw.p[VGS_PLANE_USEDMEM])[base + d] = ro.usedmem[d];
+                const_cast<int32_t *>(fo.raw.p[VGS_PLANE_USEDCORES])[base + d] = ro.usedcores[d];
+            }
+            prepare_node<DM>(fo.raw, row, n_nodes, fo.dmax, fo.commit_walk, fo.status);
+        }
         finish(false);
     }
 }

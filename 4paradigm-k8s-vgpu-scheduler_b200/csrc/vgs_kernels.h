@@ -58,6 +58,7 @@ struct FilterOne {
     vgs_pick *picks, *host_picks;
     uint32_t *status, *host_status;
     unsigned int *done;
+    int4 *commit_walk; // sequential drain: not null = fold the winner's picks into the raw planes and re-prepare its row
 };
 cudaError_t launch_filter_one(int dm, int dev, const ScoreArgs &a, const FilterOne &fo, cudaStream_t st);
 // launch geometry of a thread-per-node score kernel (persistent grid over (tile group, pod chunk) items)

@@ -1,0 +1,124 @@
+// vgs_prepare.cuh -- prepare_node: one node of the raw planes -> its slot of the walk-ordered tile copy (K0's body;
+// also run by the resolve paths when a drain commits a pod and the touched row has to be prepared again).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/vgpuscore.h"
+#include "vgs_device.cuh"
+#include "vgs_kernels.h"
+#include "vgs_layout.h"
+
+namespace vgs {
+
+// one node: raw planes -> its slot of the walk-ordered tile (also called by K3 when a drain commits a pod)
+template <int DM>
+__device__ __forceinline__ void prepare_node(const RawPlanes &raw, int row, int32_t n_nodes, int32_t dmax,
+                                             int4 *__restrict__ walk, uint32_t *__restrict__ status) {
+    const bool valid = row < n_nodes;
+    int32_t nd = valid ? raw.ndev[row] : 0;
+    uint32_t bad = 0;
+    if (nd < 0 || nd > dmax) {
+        bad |= S_NDEV;
+        nd = 0;
+    }
+    int32_t used[DM], count[DM], usedmem[DM], totalmem[DM], usedcores[DM], totalcore[DM],
+        numa[DM], type[DM];
+    // the slots are loaded for j < dmax, not j < ndev (ndev's own load would sit in front of all of them),
+    // as two 128-bit loads per plane where the rows are 32 bytes, and masked afterwards
+    int32_t *const dst[VGS_NUM_PLANES] = {used, count, usedmem, totalmem, usedcores, totalcore, numa, type};
+    unsigned long long all_ptrs = 0ull; // caller-owned planes (vgs_score_batch_noalloc) may be 4-byte aligned only
+#pragma unroll
+    for (int f = 0; f < VGS_NUM_PLANES; f++) all_ptrs |= reinterpret_cast<unsigned long long>(raw.p[f]);
+    if (DM == 8 && dmax == 8 && valid && (all_ptrs & 15ull) == 0ull) {
+#pragma unroll
+        for (int f = 0; f < VGS_NUM_PLANES; f++) {
+            const int4 *q = reinterpret_cast<const int4 *>(raw.p[f] + (size_t)row * 8);
+            const int4 lo = q[0], hi = q[1];
+            dst[f][0] = lo.x, dst[f][1] = lo.y, dst[f][2] = lo.z, dst[f][3] = lo.w;
+            dst[f][4] = hi.x, dst[f][5] = hi.y, dst[f][6] = hi.z, dst[f][7] = hi.w;
+        }
+    } else {
+#pragma unroll
+        for (int f = 0; f < VGS_NUM_PLANES; f++)
+#pragma unroll
+            for (int j = 0; j < DM; j++) dst[f][j] = (valid && j < dmax) ? raw.p[f][(size_t)row * dmax + j] : 0;
+    }
+#pragma unroll
+    for (int j = 0; j < DM; j++) {
+        bool on = j < nd;
+        if (!on) used[j] = count[j] = usedmem[j] = totalmem[j] = usedcores[j] = totalcore[j] = numa[j] = type[j] = 0;
+        if (on) {
+            if (used[j] < 0 || used[j] >= VGS_MAX_SHARE || count[j] < 0 || count[j] >= VGS_MAX_SHARE)
+                bad |= S_RANGE;
+            if (type[j] < 0 || type[j] >= VGS_MAX_TYPES) {
+                bad |= S_TYPE;
+                type[j] = 0;
+            }
+            if (totalmem[j] < 0 || totalmem[j] > kSliceMaxTotalmem) bad |= S_BIGMEM;
+        }
+    }
+    if (bad) atomicOr(status, bad);
+    {
+        int mt = 0;
+#pragma unroll
+        for (int j = 0; j < DM; j++) mt = max(mt, type[j]);
+        if (mt > 0) atomicMax(status + 1, (uint32_t)mt); // status[1] = largest type id in use
+    }
+
+    const int tile = row / kWarp, lane = row % kWarp;
+    int32_t *wbase = reinterpret_cast<int32_t *>(walk + (size_t)tile * kWalkWords * (DM / 4) * kWarp);
+    auto put = [&](int word, int w, int32_t v) {
+        wbase[((word * (DM / 4) + (w >> 2)) * kWarp + lane) * 4 + (w & 3)] = v;
+    };
+#pragma unroll
+    for (int j = 0; j < DM; j++) {
+        if (j < nd) {
+            // ascending position under score.go:45-50 with insertion-sort stability:
+            // (Numa, Count-Used, registration slot)
+            int rank = 0, nrank = 0;
+            int32_t fj = wrap_sub(count[j], used[j]);
+#pragma unroll
+            for (int i = 0; i < DM; i++) {
+                if (i < nd && i != j) {
+                    int32_t fi = wrap_sub(count[i], used[i]);
+                    bool less = numa[i] < numa[j] ||
+                                (numa[i] == numa[j] && (fi < fj || (fi == fj && i < j)));
+                    rank += less ? 1 : 0;
+                    nrank += numa[i] < numa[j] ? 1 : 0;
+                }
+            }
+            int w = nd - 1 - rank; // the reverse walk (score.go:92) visits the last first
+            uint32_t meta = (uint32_t)type[j] | ((uint32_t)nrank << M_NUMA_SHIFT) |
+                            ((uint32_t)j << M_SLOT_SHIFT) | ((uint32_t)nd << M_NDEV_SHIFT) | M_ALWAYS;
+            if (count[j] <= used[j]) meta |= M_NOFREE;
+            if (totalcore[j] == 100) meta |= M_IS100;
+            if (totalcore[j] != 0) meta |= M_CORENZ;
+            if (totalcore[j] == 100 && used[j] > 0) meta |= M_EXCL;
+            if (totalcore[j] != 0 && usedcores[j] == totalcore[j]) meta |= M_FULL;
+            if (raw.idle_types >> type[j] & 1ull) meta |= used[j] > 0 ? (M_T370 | M_BUSY370) : M_T370;
+            float s1 = fj > 0 ? container_score(count[j], fj, nd - 1) : 0.0f;
+            put(W_TOTALMEM, w, totalmem[j]);
+            put(W_FREEMEM, w, wrap_sub(totalmem[j], usedmem[j]));
+            put(W_FREECORES, w, wrap_sub(totalcore[j], usedcores[j]));
+            put(W_COUNT, w, count[j]);
+            put(W_FREESLOTS, w, fj);
+            put(W_META, w, (int32_t)meta);
+            put(W_SCORE1, w, __float_as_int(s1));
+            put(W_SPARE, w, 0);
+        } else {
+            uint32_t meta = M_PAD | M_NOFREE | M_ALWAYS | ((uint32_t)j << M_SLOT_SHIFT) |
+                            ((uint32_t)nd << M_NDEV_SHIFT);
+            put(W_TOTALMEM, j, 0);
+            put(W_FREEMEM, j, 0);
+            put(W_FREECORES, j, 0);
+            put(W_COUNT, j, 0);
+            put(W_FREESLOTS, j, 0);
+            put(W_META, j, (int32_t)meta);
+            put(W_SCORE1, j, 0);
+            put(W_SPARE, j, 0);
+        }
+    }
+}
+
+} // namespace vgs
