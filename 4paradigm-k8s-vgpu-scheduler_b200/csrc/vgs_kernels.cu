@@ -54,7 +54,13 @@ __global__ void __launch_bounds__(128)
         row = idx;
     }
     if (row >= n_tiles * kWarp) return;
-    prepare_node<DM>(raw, row, n_nodes, dmax, walk, status);
+    if (rowlist) { // scattered rows: straight stores
+        prepare_node<DM>(raw, row, n_nodes, dmax, walk, status);
+        return;
+    }
+    // whole snapshot: warp = tile, the tile's words are collected in shared memory and stored as 512-byte rows
+    extern __shared__ __align__(16) int32_t k0_stage[];
+    prepare_node<DM>(raw, row, n_nodes, dmax, walk, status, k0_stage + (threadIdx.x >> 5) * (kWalkWords * DM * kWarp));
 }
 
 // ------------------------------------------------------------------------------------
@@ -1382,10 +1388,18 @@ cudaError_t launch_prepare(int dm, const RawPlanes &raw, int32_t n_nodes, int32_
     int n = rowlist ? n_list : n_tiles * kWarp;
     if (n <= 0) return cudaSuccess;
     int block = 128, grid = (n + block - 1) / block;
-    if (dm == 8)
-        k0_prepare<8><<<grid, block, 0, st>>>(raw, n_nodes, dmax, walk, n_tiles, status, rowlist, n_list);
-    else
-        k0_prepare<12><<<grid, block, 0, st>>>(raw, n_nodes, dmax, walk, n_tiles, status, rowlist, n_list);
+    const int smem = rowlist ? 0 : (block / kWarp) * kWalkWords * dm * kWarp * (int)sizeof(int32_t); // 32 / 48 KB
+    if (dm == 8) {
+        k0_prepare<8><<<grid, block, smem, st>>>(raw, n_nodes, dmax, walk, n_tiles, status, rowlist, n_list);
+    } else {
+        static std::once_flag once[64];
+        int dev = 0;
+        cudaGetDevice(&dev);
+        std::call_once(once[dev & 63], [] {
+            cudaFuncSetAttribute(k0_prepare<12>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * kWalkWords * 12 * kWarp * 4);
+        });
+        k0_prepare<12><<<grid, block, smem, st>>>(raw, n_nodes, dmax, walk, n_tiles, status, rowlist, n_list);
+    }
     return cudaGetLastError();
 }
 

@@ -13,8 +13,12 @@ namespace vgs {
 
 // one node: raw planes -> its slot of the walk-ordered tile (also called by K3 when a drain commits a pod)
 template <int DM>
+// stage: nullptr = store straight into the tile (single rows: deltas, drain commits); else a shared-memory
+// block of kWalkWords * DM * 32 int32 owned by the calling WARP, which must be working on one whole tile
+// (lane = node): the words are collected there and leave as 512-byte warp stores
 __device__ __forceinline__ void prepare_node(const RawPlanes &raw, int row, int32_t n_nodes, int32_t dmax,
-                                             int4 *__restrict__ walk, uint32_t *__restrict__ status) {
+                                             int4 *__restrict__ walk, uint32_t *__restrict__ status,
+                                             int32_t *__restrict__ stage = nullptr) {
     const bool valid = row < n_nodes;
     int32_t nd = valid ? raw.ndev[row] : 0;
     uint32_t bad = 0;
@@ -69,7 +73,8 @@ __device__ __forceinline__ void prepare_node(const RawPlanes &raw, int row, int3
     const int tile = row / kWarp, lane = row % kWarp;
     int32_t *wbase = reinterpret_cast<int32_t *>(walk + (size_t)tile * kWalkWords * (DM / 4) * kWarp);
     auto put = [&](int word, int w, int32_t v) {
-        wbase[((word * (DM / 4) + (w >> 2)) * kWarp + lane) * 4 + (w & 3)] = v;
+        if (stage) stage[(word * DM + w) * kWarp + lane] = v; // bank = lane: conflict-free whatever w is
+        else wbase[((word * (DM / 4) + (w >> 2)) * kWarp + lane) * 4 + (w & 3)] = v;
     };
 #pragma unroll
     for (int j = 0; j < DM; j++) {
@@ -118,6 +123,18 @@ __device__ __forceinline__ void prepare_node(const RawPlanes &raw, int row, int3
             put(W_SCORE1, j, 0);
             put(W_SPARE, j, 0);
         }
+    }
+    if (stage) {
+        __syncwarp();
+        int4 *tile4 = walk + (size_t)tile * kWalkWords * (DM / 4) * kWarp;
+#pragma unroll
+        for (int word = 0; word < kWalkWords; word++)
+#pragma unroll
+            for (int q = 0; q < DM / 4; q++) {
+                const int32_t *sp = stage + ((word * DM + 4 * q) * kWarp + lane);
+                tile4[(word * (DM / 4) + q) * kWarp + lane] = make_int4(sp[0], sp[kWarp], sp[2 * kWarp], sp[3 * kWarp]);
+            }
+        __syncwarp();
     }
 }
 
