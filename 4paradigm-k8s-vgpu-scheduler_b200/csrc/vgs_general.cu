@@ -341,16 +341,22 @@ __global__ void __launch_bounds__(128)
             s_last = atomicAdd(fo.done, 1u) == gridDim.x - 1u;
         }
         __syncthreads();
-        if (!s_last || threadIdx.x != 0) return;
-        *fo.done = 0u; // zero at rest: the next call counts again
-        __threadfence();
-        const unsigned long long key = atomicMax(&keys[0], 0ull);
+        if (!s_last || warp != 0) return;
+        // warp 0 of the last CTA: lane 0 reads the candidate, the warp resolves it (lane = device slot)
+        unsigned long long key = 0ull;
         vgs_result res;
-        res.fit_count = atomicAdd(&counts[0], 0);
-        keys[0] = 0ull; // the candidate block goes back to its resting state
-        counts[0] = 0;
+        res.fit_count = 0;
+        if (lane == 0) {
+            *fo.done = 0u; // zero at rest: the next call counts again
+            __threadfence();
+            key = atomicMax(&keys[0], 0ull);
+            res.fit_count = atomicAdd(&counts[0], 0);
+            keys[0] = 0ull; // the candidate block goes back to its resting state
+            counts[0] = 0;
+        }
+        key = __shfl_sync(0xffffffffu, key, 0);
         const int32_t pick_lo = fo.pick_begin[0], pick_hi = fo.pick_begin[fo.pod.n_reqs];
-        auto finish = [&](bool zero_picks) {
+        auto finish = [&](bool zero_picks) { // lane 0 only
             if (zero_picks) {
                 vgs_pick z;
                 z.slot = z.usedmem = z.usedcores = 0;
@@ -361,39 +367,48 @@ __global__ void __launch_bounds__(128)
             __threadfence();
             fo.host_status[0] = *reinterpret_cast<volatile uint32_t *>(fo.status);
         };
-        if (key == 0ull) {
-            res.best_row = -1, res.score = 0.0f, res.n_picks = 0;
-            finish(true);
-            return;
-        }
         const uint32_t kbits = unorder_bits((uint32_t)(key >> 32));
-        res.best_row = (int32_t)(uint32_t)key;
-        res.score = __uint_as_float(kbits);
-        res.n_picks = pick_hi - pick_lo;
-        const int32_t row = res.best_row - row_base;
-        if (row < 0 || row >= n_nodes) { // cannot happen on a single shard; same answer as the resolve kernel
-            finish(true);
+        const int32_t row = (int32_t)(uint32_t)key - row_base;
+        if (key == 0ull || row < 0 || row >= n_nodes) { // nobody fits (a foreign row cannot happen on one shard)
+            if (lane == 0) {
+                res.best_row = key == 0ull ? -1 : (int32_t)(uint32_t)key;
+                res.score = key == 0ull ? 0.0f : __uint_as_float(kbits);
+                res.n_picks = key == 0ull ? 0 : pick_hi - pick_lo;
+                finish(true);
+            }
             return;
         }
-        ResolveOut ro;
-        resolve_row(
+        bool alive;
+        float score;
+        int32_t nd, used, usedmem, usedcores;
+        resolve_row_warp(
             fo.raw, row, fo.dmax, fo.pod.n_reqs, [&](int r) { return fo.reqs[r]; },
             [&](int r, int t, const vgs_pick &pk) {
                 fo.picks[fo.pick_begin[r] + t] = pk;
                 fo.host_picks[fo.pick_begin[r] + t] = pk;
             },
-            ro);
-        if (!ro.alive || __float_as_uint(ro.score) != kbits) atomicOr(fo.status, S_MISMATCH);
-        if (fo.commit_walk && ro.alive) { // sequential drain: the placement becomes usage (addPod, scheduler.go:280-297,394)
-            const size_t base = (size_t)row * fo.dmax; // and the touched row of the walk copy is prepared again
-            for (int d = 0; d < ro.nd; d++) {
-                const_cast<int32_t *>(fo.raw.p[VGS_PLANE_USED])[base + d] = ro.used[d];
-                const_cast<int32_t *>(fo.raw.p[VGS_PLANE_USEDMEM])[base + d] = ro.usedmem[d];
-                const_cast<int32_t *>(fo.raw.p[VGS_PLANE_USEDCORES])[base + d] = ro.usedcores[d];
-            }
-            prepare_node<DM>(fo.raw, row, n_nodes, fo.dmax, fo.commit_walk, fo.status);
+            alive, score, nd, used, usedmem, usedcores);
+        if (!alive || __float_as_uint(score) != kbits) {
+            if (lane == 0) atomicOr(fo.status, S_MISMATCH);
         }
-        finish(false);
+        if (fo.commit_walk && alive) { // sequential drain: the placement becomes usage (addPod, scheduler.go:280-297,394)
+            if (lane < nd) {
+                const size_t at = (size_t)row * fo.dmax + lane;
+                const_cast<int32_t *>(fo.raw.p[VGS_PLANE_USED])[at] = used;
+                const_cast<int32_t *>(fo.raw.p[VGS_PLANE_USEDMEM])[at] = usedmem;
+                const_cast<int32_t *>(fo.raw.p[VGS_PLANE_USEDCORES])[at] = usedcores;
+            }
+            __syncwarp();
+            // ... and the touched row of the walk copy is prepared again
+            if (lane == 0) prepare_node<DM>(fo.raw, row, n_nodes, fo.dmax, fo.commit_walk, fo.status);
+        }
+        __syncwarp();
+        if (lane == 0) {
+            res.best_row = (int32_t)(uint32_t)key;
+            res.score = __uint_as_float(kbits);
+            res.n_picks = pick_hi - pick_lo;
+            finish(false);
+        }
     }
 }
 
