@@ -1300,6 +1300,54 @@ __global__ void __launch_bounds__(64)
     leave();
 }
 
+// K3 for whole batches: one WARP per pod (lane = device slot of the winner node, resolve_row_warp) instead of one
+// thread per pod walking local-memory arrays: 4096 pods resolve in one wave of short warps.  Same outputs as
+// k3_resolve without its commit / host-mirror extras (those are for single-CTA batches and the drain).
+__global__ void __launch_bounds__(256)
+    k3_resolve_warp(RawPlanes raw, int32_t n_nodes, int32_t dmax, int32_t row_base, const vgs_pod *__restrict__ pods,
+                    const DevReq *__restrict__ reqs, const int32_t *__restrict__ pick_begin, int32_t n_pods,
+                    unsigned long long *__restrict__ keys, int32_t *__restrict__ counts, vgs_result *__restrict__ results,
+                    vgs_pick *__restrict__ picks, uint32_t *__restrict__ status, bool keep_candidates) {
+    const int p = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = (int)(threadIdx.x & 31u);
+    if (p >= n_pods) return; // whole warps
+    unsigned long long key = 0ull;
+    vgs_result res;
+    res.fit_count = 0;
+    if (lane == 0) {
+        key = keys[p];
+        res.fit_count = counts[p];
+        if (!keep_candidates) { // last reader of the candidate block: leave it zero for the next score pass
+            keys[p] = 0ull;
+            counts[p] = 0;
+        }
+    }
+    key = __shfl_sync(0xffffffffu, key, 0);
+    const vgs_pod pod = pods[p];
+    const int32_t pick_lo = pick_begin[pod.req_begin], pick_hi = pick_begin[pod.req_begin + pod.n_reqs];
+    const uint32_t kbits = unorder_bits((uint32_t)(key >> 32));
+    const int32_t grow = (int32_t)(uint32_t)key, row = grow - row_base;
+    if (lane == 0) {
+        res.best_row = key ? grow : -1;
+        res.score = key ? __uint_as_float(kbits) : 0.0f;
+        res.n_picks = key ? pick_hi - pick_lo : 0;
+        results[p] = res;
+    }
+    if (key == 0ull || row < 0 || row >= n_nodes) { // nobody fits, or another shard owns the winner: zero picks
+        vgs_pick z;
+        z.slot = z.usedmem = z.usedcores = 0;
+        for (int32_t i = pick_lo + lane; i < pick_hi; i += kWarp) picks[i] = z;
+        return;
+    }
+    bool alive;
+    float score;
+    int32_t nd, used, usedmem, usedcores;
+    resolve_row_warp(
+        raw, row, dmax, pod.n_reqs, [&](int r) { return reqs[pod.req_begin + r]; },
+        [&](int r, int t, const vgs_pick &pk) { picks[pick_begin[pod.req_begin + r] + t] = pk; }, alive, score, nd, used,
+        usedmem, usedcores);
+    if ((!alive || __float_as_uint(score) != kbits) && lane == 0) atomicOr(status, S_MISMATCH);
+}
+
 // ------------------------------------------------------------------------------------
 // K4: usage deltas (what addPod/delPod change between two Filters, scheduler.go:280-297)
 // ------------------------------------------------------------------------------------
@@ -1762,6 +1810,11 @@ cudaError_t launch_resolve(const RawPlanes &raw, int32_t n_nodes, int32_t dmax, 
                            int32_t *commit_rowlist, vgs_result *host_results, vgs_pick *host_picks,
                            bool keep_candidates, uint32_t *host_status, int4 *commit_walk, int commit_dm) {
     if (n_pods <= 0) return cudaSuccess;
+    if (n_pods > 64 && !commit_rowlist && !host_results && !host_picks) { // a whole batch: one warp per pod
+        k3_resolve_warp<<<(n_pods + 7) / 8, 256, 0, st>>>(raw, n_nodes, dmax, row_base, pods, reqs, pick_begin, n_pods, keys,
+                                                         counts, results, picks, status, keep_candidates);
+        return cudaGetLastError();
+    }
     if (n_pods > 64) host_status = nullptr; // one CTA only (see k3_resolve)
     k3_resolve<<<(n_pods + 63) / 64, 64, 0, st>>>(raw, n_nodes, dmax, row_base, pods, reqs, pick_begin,
                                                  n_pods, keys, counts, results, picks, status, commit_rowlist,
