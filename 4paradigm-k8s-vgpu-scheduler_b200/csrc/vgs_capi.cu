@@ -1107,7 +1107,12 @@ static int filter_one_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, in
         const int32_t df = c->plan.dict_full;
         memset(&c->plan, 0, sizeof c->plan);
         c->plan.dict_full = df;
-        c->plan.cls[3].pods = 1, c->plan.cls[3].kernel = VGS_KERNEL_GENERAL, c->plan.cls[3].launches = 1;
+        // the same classes as a batch: one request without a numa group to choose takes the per-pair kernel
+        const DevReq &q = fo.reqs[0];
+        const bool pair = n_reqs == 1 && !(fo.pod.flags & G_LEGACY) && (!(q.flags & R_NUMA) || q.nums == 1);
+        const int k = !pair ? 3 : q.nums == 1 ? 0 : q.nums == 2 ? 1 : 2;
+        c->plan.cls[k].pods = 1, c->plan.cls[k].launches = 1;
+        c->plan.cls[k].kernel = pair ? VGS_KERNEL_PAIR : VGS_KERNEL_GENERAL;
     }
     CU(cudaStreamSynchronize(c->st));
     c->stage_in_flight = false;

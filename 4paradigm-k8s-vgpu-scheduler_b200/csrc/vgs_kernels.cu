@@ -28,6 +28,7 @@
 #include <vector>
 
 #include "../../include/vgpuscore.h"
+#include "vgs_filter_tail.cuh"
 #include "vgs_device.cuh"
 #include "vgs_kernels.h"
 #include "vgs_layout.h"
@@ -68,13 +69,16 @@ __global__ void __launch_bounds__(128)
 // NUMS1: Nums == 1 -> the first fitting device in walk order decides, its score was
 // prepared by K0.  Otherwise: first Nums fitting devices, total/free accumulated.
 // ------------------------------------------------------------------------------------
-template <int DM, bool NUMS1, bool VERIFY>
+// FILTER: the launch is a whole Filter call for one pod -- the request travels in the launch parameters and the
+// CTA that finishes last resolves the winner (vgs_filter_tail.cuh).
+template <int DM, bool NUMS1, bool VERIFY, bool FILTER>
 __global__ void __launch_bounds__(256)
     k1_score_single(const int4 *__restrict__ walk, int32_t n_tiles, int32_t n_nodes,
                     int32_t row_base, const DevReq *__restrict__ reqs,
                     const int32_t *__restrict__ orig, int32_t n_pods, ScoreLaunch L,
                     unsigned long long *__restrict__ keys, int32_t *__restrict__ counts,
-                    uint32_t *__restrict__ vfit, float *__restrict__ vscore, int32_t vwords) {
+                    uint32_t *__restrict__ vfit, float *__restrict__ vscore, int32_t vwords,
+                    const __grid_constant__ FilterOne fo) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     DevReq *s_req = reinterpret_cast<DevReq *>(smem_raw);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -89,7 +93,13 @@ __global__ void __launch_bounds__(256)
         const int chunk = item / L.n_tile_groups, tg = item - chunk * L.n_tile_groups;
         const int pod0 = chunk * L.chunk_len;
         const int npod = min(L.chunk_len, n_pods - pod0);
-        if (!one_chunk || item == (int)blockIdx.x) {
+        if constexpr (FILTER) {
+            if (item == (int)blockIdx.x) {
+                if (threadIdx.x == 0) s_req[0] = fo.reqs[0];
+                need_totalmem = (fo.reqs[0].flags & R_USEPCT) != 0;
+                __syncthreads();
+            }
+        } else if (!one_chunk || item == (int)blockIdx.x) {
             // stage the chunk's requests; with a single chunk once per CTA, and the warps then
             // stream their node tiles without meeting at a barrier again
             __syncthreads(); // previous item's readers are done
@@ -193,7 +203,12 @@ __global__ void __launch_bounds__(256)
             }
         }
     }
-    if (small) flush_small<8>(acckey, acccnt, lane, warp, n_pods, orig, nullptr, keys, counts);
+    if constexpr (FILTER) {
+        flush_small<8>(acckey, acccnt, lane, warp, 1, nullptr, &fo.pod, keys, counts);
+        filter_tail<DM>(fo, keys, counts, n_nodes, row_base);
+    } else {
+        if (small) flush_small<8>(acckey, acccnt, lane, warp, n_pods, orig, nullptr, keys, counts);
+    }
 }
 
 // ------------------------------------------------------------------------------------
@@ -1516,23 +1531,45 @@ cudaError_t plan_score_launch(const void *kernel, int dev, int32_t n_tiles, int3
     return plan(kernel, dev, n_tiles, n_pods, max_warps, smem_per_pod, L);
 }
 
+static const FilterOne kNoFilter{};
+
 template <int DM, bool NUMS1>
 static cudaError_t launch_single_t(int dev, const ScoreArgs &a, const DevReq *reqs, const int32_t *orig,
                                    int32_t n_pods, cudaStream_t st) {
     ScoreLaunch L;
     cudaError_t e;
     if (a.vfit) {
-        auto k = k1_score_single<DM, NUMS1, true>;
+        auto k = k1_score_single<DM, NUMS1, true, false>;
         if ((e = plan(k, dev, a.n_tiles, n_pods, 8, (int)sizeof(DevReq), &L)) != cudaSuccess) return e;
         k<<<L.grid, L.block, L.smem, st>>>(a.walk, a.n_tiles, a.n_nodes, a.row_base, reqs, orig, n_pods, L,
-                                          a.keys, a.counts, a.vfit, a.vscore, a.vwords);
+                                          a.keys, a.counts, a.vfit, a.vscore, a.vwords, kNoFilter);
     } else {
-        auto k = k1_score_single<DM, NUMS1, false>;
+        auto k = k1_score_single<DM, NUMS1, false, false>;
         if ((e = plan(k, dev, a.n_tiles, n_pods, 8, (int)sizeof(DevReq), &L)) != cudaSuccess) return e;
         k<<<L.grid, L.block, L.smem, st>>>(a.walk, a.n_tiles, a.n_nodes, a.row_base, reqs, orig, n_pods, L,
-                                          a.keys, a.counts, nullptr, nullptr, 0);
+                                          a.keys, a.counts, nullptr, nullptr, 0, kNoFilter);
     }
     return cudaGetLastError();
+}
+
+template <int DM, bool NUMS1>
+static cudaError_t launch_filter_single_t(int dev, const ScoreArgs &a, const FilterOne &fo, cudaStream_t st) {
+    ScoreLaunch L;
+    cudaError_t e;
+    auto k = k1_score_single<DM, NUMS1, false, true>;
+    if ((e = plan(k, dev, a.n_tiles, 1, 8, (int)sizeof(DevReq), &L)) != cudaSuccess) return e;
+    k<<<L.grid, L.block, L.smem, st>>>(a.walk, a.n_tiles, a.n_nodes, a.row_base, nullptr, nullptr, 1, L, a.keys,
+                                      a.counts, nullptr, nullptr, 0, fo);
+    return cudaGetLastError();
+}
+
+// a Filter call whose pod is one request without a numa group to choose: the per-pair kernel streams 4 words per
+// device where the walk kernel streams 6
+cudaError_t launch_filter_single(int dm, bool nums1, int dev, const ScoreArgs &a, const FilterOne &fo,
+                                 cudaStream_t st) {
+    if (dm == 8)
+        return nums1 ? launch_filter_single_t<8, true>(dev, a, fo, st) : launch_filter_single_t<8, false>(dev, a, fo, st);
+    return nums1 ? launch_filter_single_t<12, true>(dev, a, fo, st) : launch_filter_single_t<12, false>(dev, a, fo, st);
 }
 
 cudaError_t launch_score_single(int dm, bool nums1, int dev, const ScoreArgs &a, const DevReq *reqs,

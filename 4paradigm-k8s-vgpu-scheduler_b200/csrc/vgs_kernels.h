@@ -60,6 +60,8 @@ struct FilterOne {
     unsigned int *done;
     int4 *commit_walk; // sequential drain: not null = fold the winner's picks into the raw planes and re-prepare its row
 };
+cudaError_t launch_filter_single(int dm, bool nums1, int dev, const ScoreArgs &a, const FilterOne &fo,
+                                 cudaStream_t st);
 cudaError_t launch_filter_one(int dm, int dev, const ScoreArgs &a, const FilterOne &fo, cudaStream_t st);
 // launch geometry of a thread-per-node score kernel (persistent grid over (tile group, pod chunk) items)
 cudaError_t plan_score_launch(const void *kernel, int dev, int32_t n_tiles, int32_t n_pods, int max_warps,

@@ -529,7 +529,8 @@ def main():
             b = algorithmic_bytes(big.n_nodes, D, 1, 1)
             tr = (prof or {}).get("p1_dram_bytes_per_launch")
             hbm_regime = {"workload": f"{big.n_nodes} nodes x {D} devices x 1 pod, snapshot resident (256 MB > L2)",
-                          "bound": "hbm", "kernel": "k1_score_single<8,true> (+ memset, merge: the whole score phase)",
+                          "bound": "hbm", "kernel": "k1_score_single<8,true,false,true>: the whole call in one launch (score, last CTA "
+                                                    "resolves the winner)",
                           # the fraction that follows from what the kernel moves (ncu DRAM bytes per launch), on this
                           # run's CUDA-event time; the algorithmic-bytes figure (all 8 prepared words per device,
                           # of which the kernel reads 4-6) is kept beside it under its own name
