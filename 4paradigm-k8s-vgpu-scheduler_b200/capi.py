@@ -44,7 +44,7 @@ class VgsTuning(C.Structure):
                 ("node_words", C.c_int32), ("tables_in_smem", C.c_int32), ("tables_smem_kb", C.c_int32),
                 ("scout_stride", C.c_int32), ("scout_split", C.c_int32), ("class_order", C.c_int32),
                 ("zero_copy_upload", C.c_int32), ("general_legacy", C.c_int32), ("max_ctas", C.c_int32),
-                ("filter_one_launch", C.c_int32), ("reserved", C.c_int32 * 4)]
+                ("filter_one_launch", C.c_int32), ("drain_chunk", C.c_int32), ("reserved", C.c_int32 * 3)]
 
 
 class VgsConfig(C.Structure):
@@ -62,7 +62,8 @@ class VgsClassPlan(C.Structure):
 
 
 class VgsPlan(C.Structure):
-    _fields_ = [("cls", VgsClassPlan * 4), ("dict_full", C.c_int32), ("reserved", C.c_int32 * 3)]
+    _fields_ = [("cls", VgsClassPlan * 4), ("dict_full", C.c_int32), ("drain_chunks", C.c_int32),
+                ("drain_rescans", C.c_int32), ("reserved", C.c_int32 * 1)]
 
 
 KERNEL_NONE, KERNEL_PAIR, KERNEL_SLICED, KERNEL_GENERAL = range(4)

@@ -58,6 +58,13 @@ struct vgs_ctx {
     uint32_t *d_status = nullptr;
     uint32_t *h_status = nullptr; // pinned
     unsigned int *d_done = nullptr; // CTA counter of the single-launch Filter kernel, zero at rest
+    // batch-scale drain: per-chunk scratch -- candidate lists, counts, and (allocated by the first chunked drain) the
+    // score bits of every (pod of the chunk, node)
+    unsigned long long *d_topk = nullptr;
+    int32_t *d_dcounts = nullptr;
+    uint32_t *d_drain_ob = nullptr;
+    int32_t *d_drain_stats = nullptr, *h_drain_stats = nullptr;
+    int sms = 0;
     int32_t n_nodes = 0, dmax = 0, n_tiles = 0;
     bool have_snapshot = false;
     bool snap_pending = false;    // vgs_snapshot_upload_async: copy + K0 queued, status not looked at yet
@@ -221,6 +228,11 @@ void free_all(vgs_ctx *c) {
     if (c->ev_delta) cudaEventDestroy(c->ev_delta);
     cudaFree(c->d_status);
     cudaFree(c->d_done);
+    cudaFree(c->d_topk);
+    cudaFree(c->d_dcounts);
+    cudaFree(c->d_drain_ob);
+    cudaFree(c->d_drain_stats);
+    if (c->h_drain_stats) cudaFreeHost(c->h_drain_stats);
     cudaFreeHost(c->h_status);
     cudaFree(c->d_deltas);
     cudaFreeHost(c->h_deltas);
@@ -333,6 +345,11 @@ int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
     CUI(cudaMallocHost(&c->h_status, 2 * sizeof(uint32_t)));
     CUI(cudaMalloc(&c->d_done, sizeof(unsigned int)));
     CUI(cudaMemset(c->d_done, 0, sizeof(unsigned int)));
+    CUI(cudaMalloc(&c->d_topk, (size_t)kDrainChunk * kDrainMaxSegs * kDrainTop * sizeof(unsigned long long)));
+    CUI(cudaMalloc(&c->d_dcounts, (size_t)kDrainChunk * kDrainMaxSegs * sizeof(int32_t)));
+    CUI(cudaMalloc(&c->d_drain_stats, 8 * sizeof(int32_t)));
+    CUI(cudaMallocHost(&c->h_drain_stats, 8 * sizeof(int32_t)));
+    CUI(cudaDeviceGetAttribute(&c->sms, cudaDevAttrMultiProcessorCount, cfg->device));
     c->max_deltas = 16384;
     CUI(cudaEventCreateWithFlags(&c->ev_delta, cudaEventDisableTiming));
     CUI(cudaMalloc(&c->d_deltas, c->max_deltas * sizeof(vgs_delta)));
@@ -1172,6 +1189,45 @@ int vgs_drain_batch(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_r
     // addressed through GenPod.orig) -> resolve + commit into the raw planes + re-prepare the row (K3)
     const DevReq *hreq_all = reinterpret_cast<const DevReq *>(c->h_stage + c->off_reqs);
     const int32_t *hpick_all = reinterpret_cast<const int32_t *>(c->h_stage + c->off_pick);
+    // batch-scale drain (vgs_drain.cu): chunks of pods, each scored against the whole snapshot once and then placed
+    // in order from the rows the chunk has touched
+    int chunk = c->tune.drain_chunk == 0 ? kDrainChunk : c->tune.drain_chunk;
+    if (chunk > kDrainChunk) chunk = kDrainChunk;
+    bool chunked = chunk > 0 && n_pods >= 32 && c->n_tiles > 0;
+    for (int32_t p = 0; p < n_pods && chunked; p++)
+        if (reinterpret_cast<const GenPod *>(c->h_stage + c->off_genall)[p].flags & G_LEGACY) chunked = false;
+    c->plan.drain_chunks = 0, c->plan.drain_rescans = 0;
+    if (chunked && !c->d_drain_ob) { // 4 bytes per (pod of a chunk, node): 26 MB at 100k nodes
+        const size_t max_tiles = ((size_t)c->cfg.max_nodes + kWarp - 1) / kWarp;
+        if (cudaMalloc(&c->d_drain_ob, (size_t)kDrainChunk * max_tiles * kWarp * sizeof(uint32_t)) != cudaSuccess) {
+            cudaGetLastError(); // no room: the per-pod chain needs none
+            c->d_drain_ob = nullptr;
+            chunked = false;
+        }
+    }
+    if (chunked) {
+        CU(cudaMemsetAsync(c->d_drain_stats, 0, 8 * sizeof(int32_t), c->st));
+        for (int32_t p0 = 0; p0 < n_pods; p0 += chunk) {
+            const int32_t n = n_pods - p0 < chunk ? n_pods - p0 : chunk;
+            CU(launch_drain_chunk(c->dm, c->cfg.device, c->sms, raw_const(c), c->d_walk, c->n_tiles, c->n_nodes,
+                                  c->cfg.row_base, c->dmax, dreq, dall + p0, dpick, n,
+                                  c->d_drain_ob, c->d_topk, c->d_dcounts, c->d_results + p0, c->d_picks,
+                                  c->d_status, c->d_drain_stats, c->st));
+            c->launches += 3;
+            c->plan.drain_chunks++;
+        }
+        CU(cudaMemcpyAsync(c->h_drain_stats, c->d_drain_stats, 8 * sizeof(int32_t), cudaMemcpyDeviceToHost, c->st));
+        rec(c, EV_SC1);
+        c->scored = true;
+        c->resolved = true;
+        c->dirty_pods = 0;
+        c->direct_out = false;
+        c->version++;
+        rc = download_locked(c, results, picks);
+        c->plan.drain_rescans = c->h_drain_stats[0];
+        if (getenv("VGS_DRAIN_DEBUG")) fprintf(stderr, "drain cycles/64: A %d B %d C %d D %d E %d\n", c->h_drain_stats[1], c->h_drain_stats[2], c->h_drain_stats[3], c->h_drain_stats[4], c->h_drain_stats[5]);
+        return rc;
+    }
     for (int32_t p = 0; p < n_pods; p++) {
         const GenPod &gp = reinterpret_cast<const GenPod *>(c->h_stage + c->off_genall)[p];
         if (gp.n_reqs <= kFilterMaxReqs && !(gp.flags & G_LEGACY) && c->n_tiles > 0 && c->tune.filter_one_launch) {
@@ -1335,6 +1391,7 @@ void vgs_tuning_defaults(vgs_tuning *t) {
     t->general_legacy = 0;
     t->max_ctas = 0;
     t->filter_one_launch = 1;
+    t->drain_chunk = 0;
 }
 
 int vgs_last_plan(vgs_ctx *c, vgs_plan *out) {

@@ -63,6 +63,15 @@ struct FilterOne {
 cudaError_t launch_filter_single(int dm, bool nums1, int dev, const ScoreArgs &a, const FilterOne &fo,
                                  cudaStream_t st);
 cudaError_t launch_filter_one(int dm, int dev, const ScoreArgs &a, const FilterOne &fo, cudaStream_t st);
+// batch-scale drain (vgs_drain.cu), one chunk of <= kDrainChunk pods: chunk-start pass over the whole snapshot (score
+// bits of every (pod, node) into ob[kDrainChunk][n_tiles * 32], then per pod the fit count and the best keys into
+// counts[kDrainChunk][8] / topk[kDrainChunk][8][kDrainTop]), then the chunk in pod order by one CTA
+constexpr int kDrainMaxSegs = 8;
+cudaError_t launch_drain_chunk(int dm, int dev, int sms, const RawPlanes &raw, int4 *walk, int32_t n_tiles,
+                               int32_t n_nodes, int32_t row_base, int32_t dmax, const DevReq *reqs, const GenPod *pods,
+                               const int32_t *pick_begin, int32_t n_pods, uint32_t *ob, unsigned long long *topk,
+                               int32_t *counts, vgs_result *results, vgs_pick *picks, uint32_t *status, int32_t *stats,
+                               cudaStream_t st);
 // launch geometry of a thread-per-node score kernel (persistent grid over (tile group, pod chunk) items)
 cudaError_t plan_score_launch(const void *kernel, int dev, int32_t n_tiles, int32_t n_pods, int max_warps,
                               int smem_per_pod, ScoreLaunch *L);

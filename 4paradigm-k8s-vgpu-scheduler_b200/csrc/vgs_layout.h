@@ -87,6 +87,8 @@ constexpr int32_t G_NO_USED_TRACK = 2; // no request's blockmask tests a "Used >
 constexpr int32_t G_LEGACY = 4;        // host routing only: more picks than the walk kernel's arrival stamps hold
 constexpr int32_t G_SAME_FIRST = 8;    // same first request (and pod flags) as the pod before it in the class list
 constexpr int32_t G_SAVE_FIRST = 16;   // the pod after it carries G_SAME_FIRST
+constexpr int kDrainChunk = 64;       // pods per chunk of the batch-scale drain (= touched rows a chunk can hold)
+constexpr int kDrainTop = 16;         // candidate keys kept per pod by the chunk-start pass
 constexpr int kWalkMaxPicks = 100;     // sum of Nums per pod the walk kernel accepts (7-bit stamps, 12 initial)
 
 inline int32_t gen_pod_flags(const DevReq *r, int n) {

@@ -138,4 +138,97 @@ __device__ __forceinline__ void prepare_node(const RawPlanes &raw, int row, int3
     }
 }
 
+// The same words for ONE row by a whole warp (lane = device slot): the drain's commits, where the row comes back
+// into play at once and a single thread's run through prepare_node would sit on the critical path.  mirror: a
+// second tile (shared memory, the row at column mirror_lane) that receives the same words; may be null.
+// the core: lane j holds the columns of device slot j (zeros from slot nd on; nd already clamped to [0, dmax])
+template <int DM>
+__device__ __forceinline__ void prepare_lanes(int row, int32_t nd, uint32_t bad, int32_t used, int32_t count,
+                                              int32_t usedmem, int32_t totalmem, int32_t usedcores, int32_t totalcore,
+                                              int32_t numa, int32_t type, uint64_t idle_types, int4 *__restrict__ walk,
+                                              uint32_t *__restrict__ status, int4 *mirror, int mirror_lane) {
+    constexpr unsigned kAll = 0xffffffffu;
+    const int j = (int)(threadIdx.x & 31u);
+    const bool on = j < nd;
+    if (on) {
+        if (used < 0 || used >= VGS_MAX_SHARE || count < 0 || count >= VGS_MAX_SHARE) bad |= S_RANGE;
+        if (type < 0 || type >= VGS_MAX_TYPES) {
+            bad |= S_TYPE;
+            type = 0;
+        }
+        if (totalmem < 0 || totalmem > kSliceMaxTotalmem) bad |= S_BIGMEM;
+    }
+    bad = __reduce_or_sync(kAll, bad);
+    const int32_t mt = __reduce_max_sync(kAll, on ? type : 0);
+    if (j == 0) {
+        if (bad) atomicOr(status, bad);
+        if (mt > 0) atomicMax(status + 1, (uint32_t)mt);
+    }
+    const int32_t fj = wrap_sub(count, used);
+    int rank = 0, nrank = 0;
+#pragma unroll
+    for (int i = 0; i < DM; i++) {
+        const int32_t fi = __shfl_sync(kAll, fj, i), ni = __shfl_sync(kAll, numa, i);
+        if (i < nd && i != j) {
+            const bool less = ni < numa || (ni == numa && (fi < fj || (fi == fj && i < j)));
+            rank += less ? 1 : 0;
+            nrank += ni < numa ? 1 : 0;
+        }
+    }
+    if (j >= DM) return;
+    const int w = on ? nd - 1 - rank : j;
+    uint32_t meta;
+    int32_t words[kWalkWords];
+#pragma unroll
+    for (int k = 0; k < kWalkWords; k++) words[k] = 0;
+    if (on) {
+        meta = (uint32_t)type | ((uint32_t)nrank << M_NUMA_SHIFT) | ((uint32_t)j << M_SLOT_SHIFT) |
+               ((uint32_t)nd << M_NDEV_SHIFT) | M_ALWAYS;
+        if (count <= used) meta |= M_NOFREE;
+        if (totalcore == 100) meta |= M_IS100;
+        if (totalcore != 0) meta |= M_CORENZ;
+        if (totalcore == 100 && used > 0) meta |= M_EXCL;
+        if (totalcore != 0 && usedcores == totalcore) meta |= M_FULL;
+        if (idle_types >> type & 1ull) meta |= used > 0 ? (M_T370 | M_BUSY370) : M_T370;
+        const float s1 = fj > 0 ? container_score(count, fj, nd - 1) : 0.0f;
+        words[W_TOTALMEM] = totalmem;
+        words[W_FREEMEM] = wrap_sub(totalmem, usedmem);
+        words[W_FREECORES] = wrap_sub(totalcore, usedcores);
+        words[W_COUNT] = count;
+        words[W_FREESLOTS] = fj;
+        words[W_SCORE1] = __float_as_int(s1);
+    } else {
+        meta = M_PAD | M_NOFREE | M_ALWAYS | ((uint32_t)j << M_SLOT_SHIFT) | ((uint32_t)nd << M_NDEV_SHIFT);
+    }
+    words[W_META] = (int32_t)meta;
+    const int tile = row / kWarp, lane = row % kWarp;
+    int32_t *wbase = reinterpret_cast<int32_t *>(walk + (size_t)tile * kWalkWords * (DM / 4) * kWarp);
+    int32_t *mbase = reinterpret_cast<int32_t *>(mirror);
+#pragma unroll
+    for (int k = 0; k < kWalkWords; k++) {
+        wbase[((k * (DM / 4) + (w >> 2)) * kWarp + lane) * 4 + (w & 3)] = words[k];
+        if (mbase) mbase[((k * (DM / 4) + (w >> 2)) * kWarp + mirror_lane) * 4 + (w & 3)] = words[k];
+    }
+}
+
+template <int DM>
+__device__ __forceinline__ void prepare_node_warp(const RawPlanes &raw, int row, int32_t dmax, int4 *__restrict__ walk,
+                                                  uint32_t *__restrict__ status, int4 *mirror, int mirror_lane) {
+    const int j = (int)(threadIdx.x & 31u);
+    int32_t nd = raw.ndev[row];
+    uint32_t bad = 0;
+    if (nd < 0 || nd > dmax) {
+        bad |= S_NDEV;
+        nd = 0;
+    }
+    const bool on = j < nd;
+    const size_t at = (size_t)row * dmax + (j < dmax ? j : 0);
+    const int32_t used = on ? raw.p[VGS_PLANE_USED][at] : 0, count = on ? raw.p[VGS_PLANE_COUNT][at] : 0;
+    const int32_t usedmem = on ? raw.p[VGS_PLANE_USEDMEM][at] : 0, totalmem = on ? raw.p[VGS_PLANE_TOTALMEM][at] : 0;
+    const int32_t usedcores = on ? raw.p[VGS_PLANE_USEDCORES][at] : 0, totalcore = on ? raw.p[VGS_PLANE_TOTALCORE][at] : 0;
+    const int32_t numa = on ? raw.p[VGS_PLANE_NUMA][at] : 0, type = on ? raw.p[VGS_PLANE_TYPEID][at] : 0;
+    prepare_lanes<DM>(row, nd, bad, used, count, usedmem, totalmem, usedcores, totalcore, numa, type, raw.idle_types, walk,
+                      status, mirror, mirror_lane);
+}
+
 } // namespace vgs

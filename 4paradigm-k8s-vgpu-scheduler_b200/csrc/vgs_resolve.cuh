@@ -139,10 +139,15 @@ __device__ __forceinline__ void resolve_row(const RawPlanes &raw, int32_t row, i
 // version above, whose local-memory arrays make every step a dependent L1 round trip).
 // All 32 lanes must call it.  emit(r, t, pick) is called by the lane that owns the pick.  On return lane d < nd holds
 // the device's usage as the pod leaves it in (used, usedmem, usedcores).
+// the columns of device slot d = lane that do not change with usage (for a preparation without another load)
+struct RowStatic {
+    int32_t count, totalmem, totalcore, numa, type;
+};
 template <typename ReqAt, typename Emit>
 __device__ __forceinline__ void resolve_row_warp(const RawPlanes &raw, int32_t row, int32_t dmax, int32_t n_reqs,
                                                  ReqAt req_at, Emit emit, bool &alive_out, float &score_out,
-                                                 int32_t &nd_out, int32_t &used, int32_t &usedmem, int32_t &usedcores) {
+                                                 int32_t &nd_out, int32_t &used, int32_t &usedmem, int32_t &usedcores,
+                                                 RowStatic *fixed = nullptr) {
     constexpr unsigned kAll = 0xffffffffu;
     const int d = (int)(threadIdx.x & 31u);
     const bool on = d < dmax;
@@ -154,6 +159,7 @@ __device__ __forceinline__ void resolve_row_warp(const RawPlanes &raw, int32_t r
     const int32_t count = on ? raw.p[VGS_PLANE_COUNT][at] : 0, totalmem = on ? raw.p[VGS_PLANE_TOTALMEM][at] : 0;
     const int32_t totalcore = on ? raw.p[VGS_PLANE_TOTALCORE][at] : 0, numa = on ? raw.p[VGS_PLANE_NUMA][at] : 0;
     const uint32_t type = on ? (uint32_t)raw.p[VGS_PLANE_TYPEID][at] : 0u;
+    if (fixed) fixed->count = count, fixed->totalmem = totalmem, fixed->totalcore = totalcore, fixed->numa = numa, fixed->type = (int32_t)type;
     nd = min(max(nd, 0), dmax);
     nd_out = nd;
     const bool valid = d < nd;

@@ -98,7 +98,9 @@ typedef struct {
     int32_t filter_one_launch;/* 1 = vgs_score_batch of ONE pod with <= 8 requests runs as a single kernel launch (the pod travels
                                * as launch parameters, the last CTA resolves the winner into the pinned result buffers);
                                * 0 = the phased path (copy, score kernel, resolve kernel) */
-    int32_t reserved[4];
+    int32_t drain_chunk;      /* vgs_drain_batch: pods per chunk of the batch-scale drain, 1..64 (0 = default 64); -1 = the
+                               * per-pod chain (one pass over the whole snapshot per pod) */
+    int32_t reserved[3];
 } vgs_tuning;
 void vgs_tuning_defaults(vgs_tuning *out);
 
@@ -238,9 +240,12 @@ int vgs_score_batch(vgs_ctx *ctx, int32_t n_pods, const vgs_pod *pods, int32_t n
 /* Sequential placement of a batch ("what-if drain"): pod p is scored against
  * the snapshot as the winners of pods 0..p-1 left it, exactly as P consecutive Filter calls
  * with addPod in between would (scheduler.go:372-394 per pod; usage folding :280-297).  The
- * whole chain (score -> resolve -> commit -> re-prepare the touched row, per pod) runs on the
- * GPU without host round trips; the resident snapshot keeps all the commits afterwards.
- * Single shard only.  Same outputs as vgs_score_batch. */
+ * whole chain runs on the GPU without host round trips; the resident snapshot keeps all the
+ * commits afterwards.  Batches of 32 pods and more run in chunks (vgs_tuning.drain_chunk): the
+ * chunk's pods are scored against the whole snapshot once, then placed in order by one CTA that
+ * re-evaluates only the rows touched inside the chunk (a commit changes one row); smaller
+ * batches, and pods the walk kernel does not take (more than 100 devices asked for), score the
+ * whole snapshot per pod.  Single shard only.  Same outputs as vgs_score_batch. */
 int vgs_drain_batch(vgs_ctx *ctx, int32_t n_pods, const vgs_pod *pods, int32_t n_reqs,
                     const vgs_req *reqs, vgs_result *results, vgs_pick *picks);
 
@@ -381,7 +386,9 @@ typedef struct {
     vgs_class_plan cls[4];
     int32_t dict_full;        /* a sliced class met more distinct candidate scores than its hash set holds since
                                * vgs_init: results stay exact (such scores are compared one by one), pruning is lost */
-    int32_t reserved[3];
+    int32_t drain_chunks;     /* the most recent vgs_drain_batch: chunks it ran as (0 = the per-pod chain) */
+    int32_t drain_rescans;    /* ... and pods whose candidate list ran dry (a whole-snapshot scan inside the chunk) */
+    int32_t reserved[1];
 } vgs_plan;
 int vgs_last_plan(vgs_ctx *ctx, vgs_plan *out);
 

@@ -869,6 +869,62 @@ def test_drain_equals_sequential_filters(built, cfg, n, p):
     assert (rows >= 0).sum() > 0 and len(set(rows[rows >= 0].tolist())) < (rows >= 0).sum()  # nodes get reused
 
 
+@pytest.mark.parametrize("chunk", [0, 7, 33, -1])
+@pytest.mark.parametrize("cfg,n,p", [("cfg3", 3000, 500), ("cfg4", 700, 150), ("cfg2", 64, 200), ("stress", 900, 130)])
+def test_drain_chunked_equals_per_pod_chain(built, cfg, n, p, chunk):
+    """the batch-scale drain (chunks scored once, placed in order from the touched rows) against the oracle's
+    P sequential Filters, for several chunk lengths and for the per-pod chain (drain_chunk = -1)"""
+    snap, batch = v.workload.make_config(cfg, n, p)
+    rows, scores, counts, picks, planes = _oracle_drain(snap, batch)
+    with v.Context(max_nodes=snap.n_nodes, max_devices=snap.dmax, max_pods=p, max_reqs=batch.n_reqs,
+                   max_picks=int(batch.nums.sum()), tuning={"drain_chunk": chunk}) as ctx:
+        ctx.upload(snap)
+        got = ctx.drain(batch)
+        plan = ctx.plan()
+        after, _ = ctx.download_snapshot()
+        assert np.array_equal(got.best_row, rows)
+        assert np.array_equal(got.score.view(np.uint32), scores.view(np.uint32))
+        assert np.array_equal(got.fit_count, counts)
+        assert np.array_equal(got.picks, picks)
+        assert np.array_equal(after, planes)
+        want_chunks = 0 if chunk < 0 else -(-p // (chunk or 64))
+        assert plan.drain_chunks == want_chunks
+        # the drained snapshot answers a fresh batch like the rebuilt one, and a second drain carries on from it
+        again = ctx.score(batch)
+        assert_same(again, oracle.score_packed(v.Snapshot(planes, snap.ndev, snap.type_names), batch), "after drain")
+        more = ctx.drain(batch)
+    rows2, scores2, counts2, picks2, _ = _oracle_drain(v.Snapshot(planes, snap.ndev, snap.type_names), batch)
+    assert np.array_equal(more.best_row, rows2) and np.array_equal(more.fit_count, counts2)
+    assert np.array_equal(more.score.view(np.uint32), scores2.view(np.uint32)) and np.array_equal(more.picks, picks2)
+
+
+def test_drain_candidate_list_runs_dry(built):
+    """identical pods on nodes that take exactly one of them: inside a chunk every candidate of a pod's list is
+    consumed by the pods before it, and no touched row fits any more -- the commit kernel has to scan the walk
+    copy (vgs_plan.drain_rescans), and still places every pod where sequential Filters would"""
+    n, p = 500, 120
+    planes = np.zeros((8, n, 4), np.int32)
+    USED, COUNT, TOTALMEM, TOTALCORE = 0, 1, 3, 5  # include/vgpuscore.h VGS_PLANE_*
+    planes[COUNT] = 1
+    planes[TOTALMEM] = 16000
+    planes[TOTALCORE] = 100
+    ndev = np.full(n, 4, np.int32)
+    planes[USED, :, 1:] = 1  # one free card per node
+    snap = v.Snapshot(planes, ndev, ["NVIDIA-A100"])
+    batch = v.PodBatch.from_pods([{"containers": [[(1, 1000, 0, 10, "NVIDIA")]]} for _ in range(p)])
+    rows, scores, counts, picks, after_want = _oracle_drain(snap, batch)
+    assert len(set(rows.tolist())) == p and rows.max() == n - 1  # one node each, highest rows first
+    with v.Context(max_nodes=n, max_devices=4, max_pods=p) as ctx:
+        ctx.upload(snap)
+        got = ctx.drain(batch)
+        plan = ctx.plan()
+        after, _ = ctx.download_snapshot()
+    assert np.array_equal(got.best_row, rows) and np.array_equal(got.fit_count, counts)
+    assert np.array_equal(got.score.view(np.uint32), scores.view(np.uint32)) and np.array_equal(got.picks, picks)
+    assert np.array_equal(after, after_want)
+    assert plan.drain_chunks == 2 and plan.drain_rescans > 0
+
+
 def test_empty_batch_and_concurrent_callers(built):
     """n_pods = 0 is a no-op; calls on one context from several host threads are serialised by the
     library (net/http runs each /filter in its own goroutine) and all get the right answer"""

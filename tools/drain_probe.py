@@ -1,20 +1,31 @@
-"""time vgs_drain_batch against P single-pod vgs_score_batch + vgs_snapshot_delta round trips"""
-import os, sys, time, numpy as np
+"""time vgs_drain_batch: the batch-scale drain (chunks) against the per-pod chain, results compared with each other
+usage: python tools/drain_probe.py [cfg] [nodes] [pods] [chunk ...]"""
+import os, sys, time, importlib, numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-import vgpu_b200 as v
-N, P = int(sys.argv[1]) if len(sys.argv) > 1 else 100000, int(sys.argv[2]) if len(sys.argv) > 2 else 1024
-snap, batch = v.workload.make_config("cfg3", N, P)
-with v.Context(max_nodes=N, max_pods=P, max_reqs=P, max_picks=2 * P) as ctx:
-    ctx.upload(snap)
-    t0 = time.perf_counter(); r = ctx.drain(batch); t1 = time.perf_counter()
-    print(f"drain {P} pods x {N} nodes: {1e3*(t1-t0):.1f} ms = {1e6*(t1-t0)/P:.1f} us/pod, placed {(r.best_row>=0).sum()}, distinct nodes {len(set(r.best_row.tolist()))}")
-    ctx.upload(snap)
-    pb = batch.pick_begin
-    t0 = time.perf_counter()
-    for p in range(min(P, 256)):
-        one = batch.select([p]); rr = ctx.score(one, snap.type_names)
-        if rr.best_row[0] >= 0:
-            d = np.array([(int(rr.best_row[0]), int(s), 1, int(m), int(c)) for s, m, c in rr.picks], dtype=v.capi.DELTA_DTYPE)
-            ctx.delta(d)
-    t1 = time.perf_counter()
-    print(f"host loop (score P=1 + delta): {1e6*(t1-t0)/min(P,256):.1f} us/pod")
+v = importlib.import_module("4paradigm-k8s-vgpu-scheduler_b200")
+cfg = sys.argv[1] if len(sys.argv) > 1 else "cfg3"
+N = int(sys.argv[2]) if len(sys.argv) > 2 else 100000
+P = int(sys.argv[3]) if len(sys.argv) > 3 else 4096
+chunks = [int(x) for x in sys.argv[4:]] or [-1, 0, 32]
+snap, batch = v.workload.make_config(cfg, N, P)
+ref = None
+for ch in chunks:
+    with v.Context(max_nodes=N, max_devices=snap.dmax, max_pods=P, max_reqs=batch.n_reqs,
+                   max_picks=int(batch.nums.sum()), tuning={"drain_chunk": ch}) as ctx:
+        best = None
+        for rep in range(3):
+            ctx.upload(snap)
+            t0 = time.perf_counter(); r = ctx.drain(batch); t1 = time.perf_counter()
+            best = min(best or 1e9, t1 - t0)
+        plan = ctx.plan()
+        t = ctx.timing()
+        same = ""
+        if ref is None:
+            ref = r
+        else:
+            same = " same=" + str(bool(np.array_equal(ref.best_row, r.best_row) and np.array_equal(ref.fit_count, r.fit_count)
+                                        and np.array_equal(ref.score.view(np.uint32), r.score.view(np.uint32))
+                                        and np.array_equal(ref.picks, r.picks)))
+        print(f"{cfg} {P} pods x {N} nodes chunk={ch}: {1e3*best:.2f} ms = {1e6*best/P:.2f} us/pod (device {t.score_ms:.2f} ms), "
+              f"chunks {plan.drain_chunks} rescans {plan.drain_rescans}, placed {(r.best_row>=0).sum()}, "
+              f"distinct nodes {len(set(r.best_row.tolist()))}{same}", flush=True)
