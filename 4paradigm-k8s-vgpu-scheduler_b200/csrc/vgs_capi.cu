@@ -14,6 +14,7 @@
 
 #include "../../include/vgpuscore.h"
 #include "vgs_kernels.h"
+#include "vgs_pair_eval.cuh"
 #include "vgs_layout.h"
 
 using namespace vgs;
@@ -60,9 +61,13 @@ struct vgs_ctx {
     unsigned int *d_done = nullptr; // CTA counter of the single-launch Filter kernel, zero at rest
     // batch-scale drain: per-chunk scratch -- candidate lists, counts, and (allocated by the first chunked drain) the
     // score bits of every (pod of the chunk, node)
-    unsigned long long *d_topk = nullptr;
-    int32_t *d_dcounts = nullptr;
-    uint32_t *d_drain_ob = nullptr;
+    unsigned long long *d_topk[2] = {}, *d_seglist = nullptr;
+    int32_t *d_dcounts[2] = {}, *d_segcount = nullptr;
+    unsigned int *d_seldone = nullptr;
+    uint32_t *d_drain_ob[2] = {};
+    void *d_carry[2] = {}; // rows a chunk changed + their words (vgs_drain.cu)
+    int4 *d_carry_words[2] = {};
+    cudaEvent_t ev_pass[2] = {}, ev_commit[2] = {};
     int32_t *d_drain_stats = nullptr, *h_drain_stats = nullptr;
     int sms = 0;
     int32_t n_nodes = 0, dmax = 0, n_tiles = 0;
@@ -228,9 +233,18 @@ void free_all(vgs_ctx *c) {
     if (c->ev_delta) cudaEventDestroy(c->ev_delta);
     cudaFree(c->d_status);
     cudaFree(c->d_done);
-    cudaFree(c->d_topk);
-    cudaFree(c->d_dcounts);
-    cudaFree(c->d_drain_ob);
+    for (int k = 0; k < 2; k++) {
+        cudaFree(c->d_topk[k]);
+        cudaFree(c->d_dcounts[k]);
+        cudaFree(c->d_drain_ob[k]);
+        if (c->ev_pass[k]) cudaEventDestroy(c->ev_pass[k]);
+        if (c->ev_commit[k]) cudaEventDestroy(c->ev_commit[k]);
+        cudaFree(c->d_carry[k]);
+        cudaFree(c->d_carry_words[k]);
+    }
+    cudaFree(c->d_seglist);
+    cudaFree(c->d_segcount);
+    cudaFree(c->d_seldone);
     cudaFree(c->d_drain_stats);
     if (c->h_drain_stats) cudaFreeHost(c->h_drain_stats);
     cudaFreeHost(c->h_status);
@@ -345,8 +359,18 @@ int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
     CUI(cudaMallocHost(&c->h_status, 2 * sizeof(uint32_t)));
     CUI(cudaMalloc(&c->d_done, sizeof(unsigned int)));
     CUI(cudaMemset(c->d_done, 0, sizeof(unsigned int)));
-    CUI(cudaMalloc(&c->d_topk, (size_t)kDrainChunk * kDrainMaxSegs * kDrainTop * sizeof(unsigned long long)));
-    CUI(cudaMalloc(&c->d_dcounts, (size_t)kDrainChunk * kDrainMaxSegs * sizeof(int32_t)));
+    for (int k = 0; k < 2; k++) {
+        CUI(cudaMalloc(&c->d_topk[k], (size_t)kDrainChunk * kDrainListWords * sizeof(unsigned long long)));
+        CUI(cudaMalloc(&c->d_dcounts[k], (size_t)kDrainChunk * sizeof(int32_t)));
+        CUI(cudaEventCreateWithFlags(&c->ev_pass[k], cudaEventDisableTiming));
+        CUI(cudaEventCreateWithFlags(&c->ev_commit[k], cudaEventDisableTiming));
+        CUI(cudaMalloc(&c->d_carry[k], drain_carry_bytes()));
+        CUI(cudaMalloc(&c->d_carry_words[k], (size_t)(kDrainChunk / kWarp) * walk_int4_per_tile(c->dm) * sizeof(int4)));
+    }
+    CUI(cudaMalloc(&c->d_seglist, (size_t)kDrainChunk * kDrainMaxSegs * kDrainListWords * sizeof(unsigned long long)));
+    CUI(cudaMalloc(&c->d_segcount, (size_t)kDrainChunk * kDrainMaxSegs * sizeof(int32_t)));
+    CUI(cudaMalloc(&c->d_seldone, kDrainChunk * sizeof(unsigned int)));
+    CUI(cudaMemset(c->d_seldone, 0, kDrainChunk * sizeof(unsigned int)));
     CUI(cudaMalloc(&c->d_drain_stats, 8 * sizeof(int32_t)));
     CUI(cudaMallocHost(&c->h_drain_stats, 8 * sizeof(int32_t)));
     CUI(cudaDeviceGetAttribute(&c->sms, cudaDevAttrMultiProcessorCount, cfg->device));
@@ -1197,25 +1221,67 @@ int vgs_drain_batch(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_r
     for (int32_t p = 0; p < n_pods && chunked; p++)
         if (reinterpret_cast<const GenPod *>(c->h_stage + c->off_genall)[p].flags & G_LEGACY) chunked = false;
     c->plan.drain_chunks = 0, c->plan.drain_rescans = 0;
-    if (chunked && !c->d_drain_ob) { // 4 bytes per (pod of a chunk, node): 26 MB at 100k nodes
+    if (chunked && !c->d_drain_ob[0]) { // 2 x 4 bytes per (pod of a chunk, node): 51 MB at 100k nodes
         const size_t max_tiles = ((size_t)c->cfg.max_nodes + kWarp - 1) / kWarp;
-        if (cudaMalloc(&c->d_drain_ob, (size_t)kDrainChunk * max_tiles * kWarp * sizeof(uint32_t)) != cudaSuccess) {
-            cudaGetLastError(); // no room: the per-pod chain needs none
-            c->d_drain_ob = nullptr;
-            chunked = false;
-        }
+        for (int k = 0; k < 2 && chunked; k++)
+            if (cudaMalloc(&c->d_drain_ob[k], (size_t)kDrainChunk * max_tiles * kWarp * sizeof(uint32_t)) != cudaSuccess) {
+                cudaGetLastError(); // no room: the per-pod chain needs none
+                cudaFree(c->d_drain_ob[0]);
+                c->d_drain_ob[0] = c->d_drain_ob[1] = nullptr;
+                chunked = false;
+            }
     }
     if (chunked) {
+        // Two streams.  st: chunk k is placed pod by pod (k_drain_commit); it hands the rows it changed to the next
+        // chunk's commit kernel and to k_drain_apply in a carry block and leaves the walk copy alone.  side[0],
+        // meanwhile: the carry block of chunk k-1 goes into the walk copy, then the pass of chunk k+1 runs over it
+        // (score-bit matrix, candidate lists) -- one chunk stale, which the commit kernel of chunk k+1 makes up for
+        // by starting from the rows chunk k changed.
+        cudaStream_t ps = c->side[0];
         CU(cudaMemsetAsync(c->d_drain_stats, 0, 8 * sizeof(int32_t), c->st));
-        for (int32_t p0 = 0; p0 < n_pods; p0 += chunk) {
-            const int32_t n = n_pods - p0 < chunk ? n_pods - p0 : chunk;
-            CU(launch_drain_chunk(c->dm, c->cfg.device, c->sms, raw_const(c), c->d_walk, c->n_tiles, c->n_nodes,
-                                  c->cfg.row_base, c->dmax, dreq, dall + p0, dpick, n,
-                                  c->d_drain_ob, c->d_topk, c->d_dcounts, c->d_results + p0, c->d_picks,
-                                  c->d_status, c->d_drain_stats, c->st));
-            c->launches += 3;
+        CU(cudaEventRecord(c->ev_fork, c->st));
+        CU(cudaStreamWaitEvent(ps, c->ev_fork, 0));
+        const int32_t n_chunks = (n_pods + chunk - 1) / chunk;
+        auto pass_of = [&](int32_t k) {
+            DrainPass dp;
+            dp.walk = c->d_walk, dp.n_tiles = c->n_tiles, dp.row_base = c->cfg.row_base;
+            dp.reqs = dreq, dp.pods = dall + (size_t)k * chunk;
+            dp.n_pods = n_pods - k * chunk < chunk ? n_pods - k * chunk : chunk;
+            dp.any_pair = dp.any_walk = false;
+            for (int32_t p = k * chunk; p < k * chunk + dp.n_pods; p++) {
+                const GenPod &gp = reinterpret_cast<const GenPod *>(c->h_stage + c->off_genall)[p];
+                const bool pr = pair_pod(gp.n_reqs, hreq_all[gp.req_begin]);
+                dp.any_pair |= pr, dp.any_walk |= !pr;
+            }
+            dp.ob = c->d_drain_ob[k & 1], dp.topk = c->d_topk[k & 1], dp.counts = c->d_dcounts[k & 1];
+            dp.seglist = c->d_seglist, dp.segcount = c->d_segcount, dp.done = c->d_seldone; // (passes run one after another)
+            return dp;
+        };
+        CU(launch_drain_pass(c->dm, c->sms, pass_of(0), ps));
+        CU(cudaEventRecord(c->ev_pass[0], ps));
+        for (int32_t k = 0; k < n_chunks; k++) {
+            if (k + 1 < n_chunks) { // side: chunk k-1 into the walk copy (pass k has read it), then pass k+1
+                if (k > 0) {
+                    CU(cudaStreamWaitEvent(ps, c->ev_commit[(k - 1) & 1], 0));
+                    CU(launch_drain_apply(c->dm, c->d_carry[(k - 1) & 1], c->d_carry_words[(k - 1) & 1], c->d_walk, ps));
+                }
+                CU(launch_drain_pass(c->dm, c->sms, pass_of(k + 1), ps));
+                CU(cudaEventRecord(c->ev_pass[(k + 1) & 1], ps));
+            }
+            CU(cudaStreamWaitEvent(c->st, c->ev_pass[k & 1], 0));
+            const DrainPass dp = pass_of(k);
+            CU(launch_drain_commit(c->dm, c->cfg.device, c->sms, raw_const(c), c->n_nodes, c->dmax, dp, dpick, k == 0,
+                                   c->d_carry[(k + 1) & 1], c->d_carry_words[(k + 1) & 1], c->d_carry[k & 1],
+                                   c->d_carry_words[k & 1], c->d_results + (size_t)k * chunk, c->d_picks, c->d_status,
+                                   c->d_drain_stats, c->st));
+            CU(cudaEventRecord(c->ev_commit[k & 1], c->st));
+            c->launches += 4;
             c->plan.drain_chunks++;
         }
+        // the last two chunks' rows (the side stream has applied the others)
+        if (n_chunks > 1)
+            CU(launch_drain_apply(c->dm, c->d_carry[(n_chunks - 2) & 1], c->d_carry_words[(n_chunks - 2) & 1], c->d_walk, c->st));
+        CU(launch_drain_apply(c->dm, c->d_carry[(n_chunks - 1) & 1], c->d_carry_words[(n_chunks - 1) & 1], c->d_walk, c->st));
         CU(cudaMemcpyAsync(c->h_drain_stats, c->d_drain_stats, 8 * sizeof(int32_t), cudaMemcpyDeviceToHost, c->st));
         rec(c, EV_SC1);
         c->scored = true;
@@ -1225,7 +1291,7 @@ int vgs_drain_batch(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_r
         c->version++;
         rc = download_locked(c, results, picks);
         c->plan.drain_rescans = c->h_drain_stats[0];
-        if (getenv("VGS_DRAIN_DEBUG")) fprintf(stderr, "drain cycles/64: A %d B %d C %d D %d E %d\n", c->h_drain_stats[1], c->h_drain_stats[2], c->h_drain_stats[3], c->h_drain_stats[4], c->h_drain_stats[5]);
+        if (getenv("VGS_DRAIN_DEBUG")) fprintf(stderr, "drain cycles/64: A %d B1 %d B2 %d B %d C %d D %d E %d\n", c->h_drain_stats[1], c->h_drain_stats[6], c->h_drain_stats[7], c->h_drain_stats[2], c->h_drain_stats[3], c->h_drain_stats[4], c->h_drain_stats[5]);
         return rc;
     }
     for (int32_t p = 0; p < n_pods; p++) {

@@ -72,16 +72,16 @@ __device__ __forceinline__ unsigned long long warp_max64(unsigned long long v) {
 // chunk-start pass, part 1: the score bits of every (pod, node).  Warp = node tile, item = (tile, part of the pods).
 // ------------------------------------------------------------------------------------
 constexpr int kScoreThreads = 256;
-template <int DM>
-__global__ void __launch_bounds__(kScoreThreads)
+// WALK = false: the chunk's pair pods (fewer registers, three CTAs per SM); true: the others.  A chunk with both kinds
+// launches both; each writes its pods' rows of the matrix.
+template <int DM, bool WALK>
+__global__ void __launch_bounds__(kScoreThreads, WALK ? 2 : 3)
     k_drain_eval(const int4 *__restrict__ walk, int32_t n_tiles, const DevReq *__restrict__ reqs,
                  const GenPod *__restrict__ pods, int32_t n_pods, int32_t psplit, uint32_t *__restrict__ ob) {
     __shared__ ChunkPods cp;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     constexpr int kWarps = kScoreThreads / 32;
     chunk_pods_load(cp, pods, reqs, n_pods);
-    uint32_t one = 1u;
-    asm volatile("" : "+r"(one));
     const size_t stride = (size_t)n_tiles * kWarp;
     const int per = (n_pods + psplit - 1) / psplit;
     const long long n_items = (long long)n_tiles * psplit;
@@ -90,12 +90,7 @@ __global__ void __launch_bounds__(kScoreThreads)
         const int k0 = part * per, k1 = min(n_pods, k0 + per);
         const int4 *tp = walk + (size_t)tile * kWalkWords * (DM / 4) * kWarp;
         uint32_t *out = ob + (size_t)tile * kWarp + lane;
-        bool any_pair = false, any_walk = false;
-        for (int k = k0; k < k1; k++) {
-            const bool pr = (cp.pair[k >> 5] >> (k & 31)) & 1u;
-            any_pair |= pr, any_walk |= !pr;
-        }
-        if (any_pair) {
+        if constexpr (!WALK) {
             PairNode<DM> nd;
             pair_node_load<DM, true>(tp, lane, nd);
             for (int k = k0; k < k1; k++) {
@@ -105,8 +100,9 @@ __global__ void __launch_bounds__(kScoreThreads)
                 pair_eval<DM>(nd, cp.first[k], fit, score);
                 out[k * stride] = fit ? order_bits(__float_as_uint(score)) : 0u;
             }
-        }
-        if (any_walk) {
+        } else {
+            uint32_t one = 1u;
+            asm volatile("" : "+r"(one));
             WalkNode<DM> nd;
             walk_node_load<DM, true>(tp, lane, nd);
             for (int k = k0; k < k1; k++) {
@@ -128,9 +124,10 @@ __global__ void __launch_bounds__(kScoreThreads)
 // ------------------------------------------------------------------------------------
 constexpr int kSelectThreads = 512;
 constexpr int kSelectMine = 4;            // keys a thread keeps (the rows of a thread lie kSelectThreads apart)
-constexpr int kListWords = kDrainTop + 1; // keys + bound
+constexpr int kListWords = kDrainListWords; // keys + bound
 __global__ void __launch_bounds__(kSelectThreads)
     k_drain_select(const uint32_t *__restrict__ ob, int32_t n_tiles, int32_t row_base, int32_t n_segs,
+                   unsigned long long *__restrict__ seglist, int32_t *__restrict__ segcount, unsigned int *__restrict__ done,
                    unsigned long long *__restrict__ topk, int32_t *__restrict__ counts) {
     constexpr int kWarps = kSelectThreads / 32;
     __shared__ unsigned long long s_best[kWarps];
@@ -145,22 +142,33 @@ __global__ void __launch_bounds__(kSelectThreads)
     for (int i = 0; i < kSelectMine; i++) t[i] = 0ull;
     unsigned long long dropped = 0ull; // the largest key this thread has let go
     int32_t cnt = 0;
-    for (int r = r0 + (int)threadIdx.x; r < r1; r += kSelectThreads) {
-        const uint32_t bits = __ldg(&src[r]);
-        if (bits == 0u) continue;
-        cnt++;
-        unsigned long long v = ((unsigned long long)bits << 32) | (uint32_t)(row_base + r);
+    constexpr int kFly = 8; // loads in flight per thread
+    for (int rb = r0 + (int)threadIdx.x; rb < r1; rb += kFly * kSelectThreads) {
+        uint32_t bits[kFly];
 #pragma unroll
-        for (int i = 0; i < kSelectMine; i++) {
-            const unsigned long long hi = v > t[i] ? v : t[i];
-            v = v > t[i] ? t[i] : v;
-            t[i] = hi;
+        for (int u = 0; u < kFly; u++) {
+            const int r = rb + u * kSelectThreads;
+            bits[u] = r < r1 ? __ldg(&src[r]) : 0u;
         }
-        dropped = v > dropped ? v : dropped;
+#pragma unroll
+        for (int u = 0; u < kFly; u++) {
+            if (bits[u] == 0u) continue;
+            cnt++;
+            unsigned long long v = ((unsigned long long)bits[u] << 32) | (uint32_t)(row_base + rb + u * kSelectThreads);
+            if (v > t[kSelectMine - 1]) {
+#pragma unroll
+                for (int i = 0; i < kSelectMine; i++) {
+                    const unsigned long long hi = v > t[i] ? v : t[i];
+                    v = v > t[i] ? t[i] : v;
+                    t[i] = hi;
+                }
+            }
+            dropped = v > dropped ? v : dropped;
+        }
     }
     cnt = __reduce_add_sync(0xffffffffu, cnt);
     if (lane == 0) s_cnt[warp] = cnt;
-    unsigned long long *list = topk + ((size_t)pod * n_segs + seg) * kListWords;
+    unsigned long long *list = seglist + ((size_t)pod * n_segs + seg) * kListWords;
     // kDrainTop rounds of "largest head of all threads" (the owner moves on to its next), one more for the bound
     for (int r = 0; r <= kDrainTop; r++) {
         const unsigned long long mine = r < kDrainTop ? t[0] : (t[0] > dropped ? t[0] : dropped);
@@ -178,88 +186,166 @@ __global__ void __launch_bounds__(kSelectThreads)
             t[kSelectMine - 1] = 0ull;
         }
     }
+    __shared__ bool s_last;
     if (threadIdx.x == 0) {
         int32_t c = 0;
         for (int w = 0; w < kWarps; w++) c += s_cnt[w];
-        counts[pod * n_segs + seg] = c;
+        segcount[pod * n_segs + seg] = c;
+        __threadfence();
+        s_last = atomicAdd(&done[pod], 1u) == (unsigned)n_segs - 1u;
     }
+    __syncthreads();
+    if (!s_last) return;
+    // the pod's last segment merges: a key's place in the pod's list = the number of larger keys among the segments'
+    __threadfence();
+    __shared__ unsigned long long s_keys[kDrainMaxSegs * kDrainTop];
+    const int n_keys = n_segs * kDrainTop;
+    const unsigned long long *mine_list = seglist + (size_t)pod * n_segs * kListWords;
+    for (int i = threadIdx.x; i < n_keys; i += kSelectThreads)
+        s_keys[i] = __ldcg(&mine_list[(i / kDrainTop) * kListWords + i % kDrainTop]);
+    __syncthreads();
+    unsigned long long out_of_list = 0ull; // goes into the bound
+    for (int i = threadIdx.x; i < n_keys; i += kSelectThreads) {
+        const unsigned long long v = s_keys[i];
+        int rank = 0;
+        for (int j = 0; j < n_keys; j++) rank += s_keys[j] > v ? 1 : 0;
+        if (v != 0ull && rank < kDrainTop) topk[(size_t)pod * kListWords + rank] = v;
+        else out_of_list = v;
+    }
+    if (threadIdx.x < n_segs) {
+        const unsigned long long b = __ldcg(&mine_list[threadIdx.x * kListWords + kDrainTop]);
+        out_of_list = b > out_of_list ? b : out_of_list;
+    }
+    // slots no key claimed: zero (fewer than kDrainTop fitting rows)
+    int n_nonzero = 0;
+    for (int j = 0; j < n_keys; j++) n_nonzero += s_keys[j] != 0ull ? 1 : 0;
+    for (int r = n_nonzero + (int)threadIdx.x; r < kDrainTop; r += kSelectThreads) topk[(size_t)pod * kListWords + r] = 0ull;
+    const unsigned long long m = warp_max64(out_of_list);
+    __syncthreads();
+    if (lane == 0) s_best[warp] = m;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long bound = 0ull;
+        for (int w = 0; w < kWarps; w++) bound = s_best[w] > bound ? s_best[w] : bound;
+        topk[(size_t)pod * kListWords + kDrainTop] = bound;
+        int32_t c = 0;
+        for (int g = 0; g < n_segs; g++) c += __ldcg(&segcount[pod * n_segs + g]);
+        counts[pod] = c;
+        done[pod] = 0u; // zero at rest
+    }
+}
+
+// Address of word k of the device at walk position w of column col of a tile (int32 view of the int4 layout)
+template <int DM>
+__device__ __forceinline__ int tile_at(int k, int w, int col) {
+    return ((k * (DM / 4) + (w >> 2)) * kWarp + col) * 4 + (w & 3);
 }
 
 // pull a line towards this SM ahead of its use
 __device__ __forceinline__ void warm(const void *p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 
+// What one chunk's commit kernel hands to the next and to k_drain_apply: the rows it changed, with their words as the
+// chunk leaves them (tile layout, column = index in rows[]).
+constexpr int kDrainSlots = 2 * kDrainChunk; // rows a commit kernel can hold: carried in + touched by its own pods
+struct DrainCarry {
+    int32_t n;
+    int32_t rows[kDrainChunk]; // local rows
+};
+
 struct DrainChunk {
-    int4 *walk;
+    const int4 *walk; // the walk copy: commits up to the previous chunk (k_drain_apply), not this one's
     int32_t n_tiles, n_nodes, row_base, dmax;
     RawPlanes raw;
     const DevReq *reqs;
     const GenPod *pods;        // the chunk's pods, batch order
     const int32_t *pick_begin; // batch-wide, per request
     int32_t n_pods;
-    const uint32_t *ob;             // [pod][n_tiles * 32] chunk-start score bits
-    const unsigned long long *topk; // [pod][n_segs][kListWords]
-    const int32_t *counts;          // [pod][n_segs]
-    int32_t n_segs;
+    const uint32_t *ob;             // [pod][n_tiles * 32] score bits, as of the start of the PREVIOUS chunk
+    const unsigned long long *topk; // [pod][kListWords]: candidate keys descending, then the bound
+    const int32_t *counts;          // [pod]
+    int32_t first; // 1 = first chunk of the drain: nothing carried in, the matrix is as of this chunk's start
+    const DrainCarry *carry_in; // rows the previous chunk changed ...
+    const int4 *words_in;       // ... and their words, kDrainChunk / 32 tiles
+    DrainCarry *carry_out;      // the same for this chunk
+    int4 *words_out;
     vgs_result *results; // the chunk's
     vgs_pick *picks;     // the batch's
     uint32_t *status;
     int32_t *stats; // [0] += pods that needed the full scan
 };
 
-constexpr int kDrainThreads = 256;
+constexpr int kDrainThreads = 512; // (with its registers, nothing of the concurrent pass fits beside it on the SM)
 constexpr int kDrainReqBuf = 384; // requests of the chunk's multi-request pods kept in shared memory
 
 // ------------------------------------------------------------------------------------
-// the chunk in pod order, one CTA
+// the chunk in pod order, one CTA.  T = the rows the previous chunk changed (the matrix and the lists do not know
+// that: they were worked out while that chunk ran) + the rows this chunk has changed so far.
 // ------------------------------------------------------------------------------------
 template <int DM>
 __global__ void __launch_bounds__(kDrainThreads) k_drain_commit(const __grid_constant__ DrainChunk a) {
     constexpr int kTile4 = kWalkWords * (DM / 4) * kWarp; // int4 per tile
-    constexpr int kSlotTiles = kDrainChunk / kWarp;
+    constexpr int kRow4 = kWalkWords * (DM / 4);          // int4 per row
+    constexpr int kSlotTiles = kDrainSlots / kWarp;
     constexpr int kWarps = kDrainThreads / kWarp;
-    extern __shared__ __align__(16) int4 s_cur[]; // the live words of the touched rows, kSlotTiles tiles (slot = column)
+    static_assert(kSlotTiles < kWarps, "helper warps needed");
+    extern __shared__ __align__(16) int4 s_cur[]; // the live words of T's rows, kSlotTiles tiles (slot = column)
     __shared__ ChunkPods cp;
     __shared__ DevReq s_req[kDrainReqBuf];
     __shared__ int32_t s_roff[kDrainChunk]; // pod k's requests start at s_req[s_roff[k]]; -1 = read them from global
-    __shared__ unsigned long long s_list[kDrainChunk][kDrainTop]; // kTouched = the row has been touched since
+    __shared__ unsigned long long s_list[kDrainChunk][kDrainTop]; // kTouched = the row is in T
     __shared__ unsigned long long s_bound[kDrainChunk];           // no row outside pod k's list had a larger key
-    __shared__ int s_newrow; // global row touched for the first time by the previous pod, or -1
+    __shared__ int s_newrow; // global row that entered T with the previous pod, or -1
     __shared__ int32_t s_count0[kDrainChunk], s_pick_lo[kDrainChunk], s_pick_hi[kDrainChunk];
-    __shared__ int32_t s_trow[kDrainChunk];  // local row of slot s
-    __shared__ int32_t s_nt_at[kDrainChunk]; // touched rows when pod k was placed; -1 = its fit count is final
+    __shared__ int32_t s_trow[kDrainSlots];  // local row of slot s
+    __shared__ uint32_t s_mod[kSlotTiles];   // bit: the slot's row was changed by this chunk
+    __shared__ int32_t s_nt_at[kDrainChunk]; // |T| when pod k was placed; -1 = its fit count is final
     __shared__ unsigned long long s_wkey[kWarps];
     __shared__ int32_t s_wcnt[kWarps];
+    constexpr int kHashBits = 8, kHash = 1 << kHashBits; // >= 4 x the carried rows
+    __shared__ int32_t s_hash[kHash];
+    __shared__ uint32_t s_filter[32]; // rescan: bit (tile & 1023) for every tile holding a row of T
     __shared__ int s_nT;
+    // the tile words of the next pod's two likeliest winners outside T, fetched one pod ahead (row-major: kRow4 int4)
+    __shared__ __align__(16) int4 s_cand[2][2][kRow4];
+    __shared__ int32_t s_cand_row[2][2]; // local rows, -1 = none
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // (the last warp) start the copies for pod k into buffer k & 1; `skip` = global row that is about to enter T
+    auto fetch_candidates = [&](int k, int skip) {
+        const unsigned long long e = lane < kDrainTop ? s_list[k][lane] : 0ull;
+        unsigned open_ = __ballot_sync(0xffffffffu, e > kTouched && (int)(uint32_t)e != skip);
+#pragma unroll
+        for (int c = 0; c < 2; c++) {
+            int32_t row = -1;
+            if (open_) {
+                const int at = __ffs((int)open_) - 1;
+                open_ &= open_ - 1u;
+                row = (int32_t)(uint32_t)__shfl_sync(0xffffffffu, e, at) - a.row_base;
+                if (lane < kRow4) {
+                    const unsigned dst = (unsigned)__cvta_generic_to_shared(&s_cand[k & 1][c][lane]);
+                    const int4 *src = a.walk + (size_t)(row / kWarp) * kTile4 + lane * kWarp + row % kWarp;
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+                }
+            }
+            if (lane == 0) s_cand_row[k & 1][c] = row;
+        }
+    };
     for (int i = tid; i < kSlotTiles * kTile4; i += kDrainThreads) s_cur[i] = make_int4(0, 0, 0, 0);
-    if (tid < kDrainChunk) s_trow[tid] = -1;
+    if (tid < kDrainSlots) s_trow[tid] = -1;
+    if (tid < kSlotTiles) s_mod[tid] = 0u;
     chunk_pods_load(cp, a.pods, a.reqs, a.n_pods);
+    const int n_in = a.first ? 0 : a.carry_in->n;
+    // carried in: rows and live words
+    if (tid < n_in) s_trow[tid] = a.carry_in->rows[tid];
+    for (int i = tid; i < ((n_in + kWarp - 1) / kWarp) * kTile4; i += kDrainThreads) s_cur[i] = a.words_in[i];
+    for (int i = tid; i < a.n_pods * kListWords; i += kDrainThreads) {
+        const unsigned long long x = a.topk[i];
+        const int k = i / kListWords, r = i % kListWords;
+        if (r < kDrainTop) s_list[k][r] = x;
+        else s_bound[k] = x;
+    }
     if (tid < a.n_pods) {
         const GenPod p = cp.pod[tid];
-        // the segments' lists merged (what the merge drops goes into the bound), the segments' counts added up
-        const unsigned long long *seg = a.topk + (size_t)tid * a.n_segs * kListWords;
-        int head[kDrainMaxSegs];
-        for (int g = 0; g < kDrainMaxSegs; g++) head[g] = 0;
-        for (int r = 0; r < kDrainTop; r++) {
-            unsigned long long best = 0ull;
-            int from = 0;
-            for (int g = 0; g < a.n_segs; g++) {
-                const unsigned long long e = head[g] < kDrainTop ? seg[g * kListWords + head[g]] : 0ull;
-                if (e > best) best = e, from = g;
-            }
-            head[from]++;
-            s_list[tid][r] = best;
-        }
-        unsigned long long bound = 0ull;
-        int32_t c0 = 0;
-        for (int g = 0; g < a.n_segs; g++) {
-            const unsigned long long rest = seg[g * kListWords + min(head[g], kDrainTop)]; // next key, or the bound
-            const unsigned long long b = seg[g * kListWords + kDrainTop];
-            bound = max(bound, max(rest, b));
-            c0 += a.counts[tid * a.n_segs + g];
-        }
-        s_bound[tid] = bound;
-        s_count0[tid] = c0;
+        s_count0[tid] = a.counts[tid];
         s_pick_lo[tid] = a.pick_begin[p.req_begin];
         s_pick_hi[tid] = a.pick_begin[p.req_begin + p.n_reqs];
     }
@@ -279,11 +365,32 @@ __global__ void __launch_bounds__(kDrainThreads) k_drain_commit(const __grid_con
         if (off >= 0)
             for (int r = lane; r < cp.pod[k].n_reqs; r += kWarp) s_req[off + r] = load_req(&a.reqs[cp.pod[k].req_begin + r]);
     }
+    // the carried rows leave the lists (a small open-addressing set of them)
+    for (int i = tid; i < kHash; i += kDrainThreads) s_hash[i] = -1;
+    __syncthreads();
+    if (tid < n_in) {
+        const int32_t r = s_trow[tid];
+        for (uint32_t h = ((uint32_t)r * 2654435761u) >> (32 - kHashBits);; h = (h + 1) & (kHash - 1))
+            if (atomicCAS(&s_hash[h], -1, r) == -1) break;
+    }
+    __syncthreads();
+    for (int e = tid; e < a.n_pods * kDrainTop; e += kDrainThreads) {
+        const unsigned long long x = (&s_list[0][0])[e];
+        if (x == 0ull) continue;
+        const int32_t r = (int32_t)(uint32_t)x - a.row_base;
+        for (uint32_t h = ((uint32_t)r * 2654435761u) >> (32 - kHashBits); s_hash[h] != -1; h = (h + 1) & (kHash - 1))
+            if (s_hash[h] == r) {
+                (&s_list[0][0])[e] = kTouched;
+                break;
+            }
+    }
+    __syncthreads(); // the lists are final
+    if (warp == kWarps - 1) fetch_candidates(0, -1);
     uint32_t one = 1u;
     asm volatile("" : "+r"(one));
-    int nT = 0;
+    int nT = n_in;
 #ifdef VGS_DRAIN_TIMING
-    long long tA = 0, tB = 0, tC = 0, tD = 0, tE = 0, t0 = 0, t1 = 0;
+    long long tA = 0, tB = 0, tB1 = 0, tB2 = 0, tC = 0, tD = 0, tE = 0, t0 = 0, t1 = 0;
 #define TICK(acc) t1 = clock64(), acc += t1 - t0, t0 = t1
 #else
 #define TICK(acc)
@@ -300,36 +407,7 @@ __global__ void __launch_bounds__(kDrainThreads) k_drain_commit(const __grid_con
         auto req_at = [&](int r) {
             return pod.n_reqs == 1 ? cp.first[q] : roff >= 0 ? s_req[roff + r] : load_req(&a.reqs[pod.req_begin + r]);
         };
-        // the last warp pulls the next pod's likeliest winners (the head of its list) towards this SM: their raw planes
-        if (warp == kWarps - 1 && q + 1 < a.n_pods) {
-#pragma unroll
-            for (int c = 0; c < 2; c++) {
-                const unsigned long long e = s_list[q + 1][c];
-                if (e > kTouched) {
-                    const int32_t row = (int32_t)(uint32_t)e - a.row_base;
-                    if (lane < VGS_NUM_PLANES) warm(a.raw.p[lane] + (size_t)row * a.dmax);
-                    else if (lane == VGS_NUM_PLANES) warm(a.raw.ndev + row);
-                }
-            }
-        }
-        // a row touched for the first time by the previous pod leaves every list (the entries stay, as kTouched)
-        if (s_newrow >= 0) {
-            const uint32_t nr = (uint32_t)s_newrow;
-            for (int e = tid; e < a.n_pods * kDrainTop; e += kDrainThreads) {
-                const unsigned long long x = (&s_list[0][0])[e];
-                if (x > kTouched && (uint32_t)x == nr) (&s_list[0][0])[e] = kTouched;
-            }
-        }
-        TICK(tA);
-
-        // ---- the touched rows, live: warp w on slots [32 w, 32 w + 32)
-        unsigned long long key = 0ull;
-        int32_t dc = 0;
-        if (warp < kSlotTiles && nT > warp * kWarp) { // warp-uniform
-            const int slot = warp * kWarp + lane;
-            const int4 *tp = s_cur + (size_t)warp * kTile4;
-            bool alive;
-            float score;
+        auto eval_on = [&](const int4 *tp, bool &alive, float &score) { // this lane's column of the tile
             if (is_pair) {
                 PairNode<DM> nd;
                 pair_node_load<DM, false>(tp, lane, nd);
@@ -339,46 +417,120 @@ __global__ void __launch_bounds__(kDrainThreads) k_drain_commit(const __grid_con
                 walk_node_load<DM, false>(tp, lane, nd);
                 walk_eval<DM, false, false>(nd, pod, req_at, one, nullptr, false, alive, score);
             }
-            if (slot < nT && alive) key = key_of(score, (uint32_t)(a.row_base + s_trow[slot])), dc = 1;
+        };
+        if (warp >= kSlotTiles) { // the helper warps
+            // this pod's candidates have arrived (started one pod ago); the next pod's are started
+            if (warp == kWarps - 1) {
+                asm volatile("cp.async.wait_all;" ::: "memory");
+                if (q + 1 < a.n_pods) fetch_candidates(q + 1, s_newrow);
+            }
+            // a row that entered T with the previous pod leaves every list (the entries stay, as kTouched)
+            if (s_newrow >= 0) {
+                const uint32_t nr = (uint32_t)s_newrow;
+                for (int e = tid - kSlotTiles * kWarp; e < a.n_pods * kDrainTop; e += kDrainThreads - kSlotTiles * kWarp) {
+                    const unsigned long long x = (&s_list[0][0])[e];
+                    if (x > kTouched && (uint32_t)x == nr) (&s_list[0][0])[e] = kTouched;
+                }
+            }
         }
-        if (warp < kSlotTiles) {
+        TICK(tA);
+
+        // ---- the first candidate outside T (lane k looks at entry k; the row that entered T with the previous pod
+        // is being struck out by the helper warps right now: it is excluded by name)
+        static_assert(kDrainTop <= 32, "one lane per list entry");
+        const unsigned long long mine = lane < kDrainTop ? s_list[q][lane] : 0ull;
+        const unsigned open_ = __ballot_sync(0xffffffffu, mine > kTouched && (int)(uint32_t)mine != s_newrow);
+        const unsigned long long lkey = open_ ? __shfl_sync(0xffffffffu, mine, __ffs((int)open_) - 1) : 0ull;
+        const unsigned long long bound = s_bound[q];
+        // ---- T's rows, live
+        if (is_pair) {
+            // pair pods: lane = (slot, device) -- a group of DM-rounded-to-8/16 lanes per row, the take decided by
+            // ballots and the sums by shuffles inside the group; every warp takes part
+            constexpr int kGrp = DM <= 8 ? 8 : 16, kPerWarp = kWarp / kGrp;
+            const DevReq rq = cp.first[q];
+            const int j = lane % kGrp, g = lane / kGrp;
+            unsigned long long key = 0ull;
+            int32_t dc = 0;
+            constexpr int kRounds = kDrainSlots / (kWarps * kPerWarp);
+            // (the rounds are independent: unrolled, their instruction streams interleave)
+#pragma unroll
+            for (int rd = 0; rd < kRounds; rd++) {
+                const int s0 = rd * kWarps * kPerWarp + warp * kPerWarp;
+                if (rd * kWarps * kPerWarp >= nT) break; // CTA-uniform
+                const int slot = s0 + g;
+                const bool on = slot < nT && j < DM;
+                const int32_t *src = reinterpret_cast<const int32_t *>(s_cur + (size_t)((on ? slot : 0) / kWarp) * kTile4);
+                const int col = (on ? slot : 0) % kWarp, jj = on ? j : 0;
+                const int32_t tm = src[tile_at<DM>(W_TOTALMEM, jj, col)], fm = src[tile_at<DM>(W_FREEMEM, jj, col)];
+                const int32_t fc = src[tile_at<DM>(W_FREECORES, jj, col)], cn = src[tile_at<DM>(W_COUNT, jj, col)];
+                const int32_t fs = src[tile_at<DM>(W_FREESLOTS, jj, col)];
+                const uint32_t mt = (uint32_t)src[tile_at<DM>(W_META, jj, col)];
+                const int32_t mem = (rq.flags & R_USEPCT) ? pct_mem(tm, rq.pct) : rq.memfix;
+                const bool f = on && !(mt & rq.blockmask) && type_ok(rq.mask_lo, rq.mask_hi, mt) && fm >= mem && fc >= rq.coresreq;
+                const unsigned grp = (__ballot_sync(0xffffffffu, f) >> (g * kGrp)) & ((1u << kGrp) - 1u);
+                const bool taken = f && __popc(grp & ((1u << j) - 1u)) < rq.nums;
+                uint32_t total = taken ? (uint32_t)cn : 0u, free_ = taken ? (uint32_t)fs : 0u;
+#pragma unroll
+                for (int d = 1; d < kGrp; d <<= 1) {
+                    total += __shfl_xor_sync(0xffffffffu, total, d);
+                    free_ += __shfl_xor_sync(0xffffffffu, free_, d);
+                }
+                const bool fit = slot < nT && __popc(grp) >= rq.nums;
+                const int32_t ndv = (int32_t)((__shfl_sync(0xffffffffu, mt, g * kGrp) >> M_NDEV_SHIFT) & 15u);
+                const float score = container_score((int32_t)total, fit ? (int32_t)free_ : 1, ndv - rq.nums);
+                if (fit) {
+                    const unsigned long long v = key_of(score, (uint32_t)(a.row_base + s_trow[slot]));
+                    key = v > key ? v : key;
+                    dc += j == 0 ? 1 : 0;
+                }
+            }
             key = warp_max64(key);
             dc = __reduce_add_sync(0xffffffffu, dc);
             if (lane == 0) s_wkey[warp] = key, s_wcnt[warp] = dc;
+        } else {
+            // the others: warp w on slots [32 w, 32 w + 32), lane = row
+            unsigned long long key = 0ull;
+            int32_t dc = 0;
+            if (warp < kSlotTiles && nT > warp * kWarp) { // warp-uniform
+                const int slot = warp * kWarp + lane;
+                bool alive;
+                float score;
+                eval_on(s_cur + (size_t)warp * kTile4, alive, score);
+                if (slot < nT && alive) key = key_of(score, (uint32_t)(a.row_base + s_trow[slot])), dc = 1;
+                key = warp_max64(key);
+                dc = __reduce_add_sync(0xffffffffu, dc);
+            }
+            if (lane == 0) s_wkey[warp] = key, s_wcnt[warp] = dc;
         }
+        TICK(tB1);
         __syncthreads();
+        TICK(tB2);
         unsigned long long tkey = 0ull;
         int32_t live = 0;
-#pragma unroll
-        for (int w = 0; w < kSlotTiles; w++) {
-            tkey = s_wkey[w] > tkey ? s_wkey[w] : tkey;
-            live += s_wcnt[w];
+        { // lane w reads warp w's part
+            static_assert(kWarps <= kWarp, "one lane per warp");
+            tkey = warp_max64(lane < kWarps ? s_wkey[lane] : 0ull);
+            live = __reduce_add_sync(0xffffffffu, lane < kWarps ? s_wcnt[lane] : 0);
         }
-        // ---- the first candidate outside T (lane k looks at entry k)
-        static_assert(kDrainTop <= 32, "one lane per list entry");
-        const unsigned long long mine = lane < kDrainTop ? s_list[q][lane] : 0ull;
-        const unsigned open_ = __ballot_sync(0xffffffffu, mine > kTouched);
-        const unsigned long long lkey = open_ ? __shfl_sync(0xffffffffu, mine, __ffs((int)open_) - 1) : 0ull;
         unsigned long long best = tkey > lkey ? tkey : lkey;
         int32_t fit_count = live, nt_at = nT;
-        if (best < s_bound[q]) {
-            // some row the list does not name had a larger key at chunk start than anything in sight: scan the walk
-            // copy (it holds the commits so far).  CTA-uniform branch.
+        if (best < bound) {
+            // some row the list does not name had a larger key than anything in sight: scan the walk copy for the
+            // rows outside T (T's rows are stale there; their live keys and count are in hand).  CTA-uniform branch.
             __syncthreads(); // s_w* are read above
+            if (tid < 32) s_filter[tid] = 0u;
+            __syncthreads();
+            for (int s = tid; s < nT; s += kDrainThreads) atomicOr(&s_filter[((s_trow[s] / kWarp) & 1023) >> 5], 1u << ((s_trow[s] / kWarp) & 31));
+            __syncthreads();
             unsigned long long sk = 0ull;
             int32_t sc = 0;
             for (int tile = warp; tile < a.n_tiles; tile += kWarps) {
-                const int4 *tp = a.walk + (size_t)tile * kTile4;
                 bool alive;
                 float score;
-                if (is_pair) {
-                    PairNode<DM> nd;
-                    pair_node_load<DM, false>(tp, lane, nd);
-                    pair_eval<DM>(nd, cp.first[q], alive, score);
-                } else {
-                    WalkNode<DM> nd;
-                    walk_node_load<DM, false>(tp, lane, nd);
-                    walk_eval<DM, false, false>(nd, pod, req_at, one, nullptr, false, alive, score);
+                eval_on(a.walk + (size_t)tile * kTile4, alive, score);
+                if ((s_filter[(tile & 1023) >> 5] >> (tile & 31)) & 1u) { // may hold rows of T: they do not count here
+                    const int32_t r = tile * kWarp + lane;
+                    for (int s = 0; s < nT; s++) alive = alive && s_trow[s] != r;
                 }
                 if (alive) {
                     const unsigned long long v = key_of(score, (uint32_t)(a.row_base + tile * kWarp + lane));
@@ -390,7 +542,7 @@ __global__ void __launch_bounds__(kDrainThreads) k_drain_commit(const __grid_con
             sc = __reduce_add_sync(0xffffffffu, sc);
             if (lane == 0) s_wkey[warp] = sk, s_wcnt[warp] = sc;
             __syncthreads();
-            best = 0ull, fit_count = 0, nt_at = -1;
+            best = tkey, nt_at = -1;
 #pragma unroll
             for (int w = 0; w < kWarps; w++) {
                 best = s_wkey[w] > best ? s_wkey[w] : best;
@@ -405,7 +557,7 @@ __global__ void __launch_bounds__(kDrainThreads) k_drain_commit(const __grid_con
             const int32_t pick_lo = s_pick_lo[q], pick_hi = s_pick_hi[q];
             int newrow = -1;
             vgs_result res;
-            res.fit_count = fit_count; // (nt_at >= 0: the live part; the chunk-start part is added when the chunk is done)
+            res.fit_count = fit_count; // (nt_at >= 0: the live part; the rest is added when the chunk is done)
             if (best == 0ull) {
                 vgs_pick z;
                 z.slot = z.usedmem = z.usedcores = 0;
@@ -414,42 +566,120 @@ __global__ void __launch_bounds__(kDrainThreads) k_drain_commit(const __grid_con
             } else {
                 const uint32_t kbits = unorder_bits((uint32_t)(best >> 32));
                 const int32_t row = (int32_t)(uint32_t)best - a.row_base;
-                bool alive;
-                float score;
-                int32_t ndv, used, usedmem, usedcores;
-                RowStatic fx;
-                resolve_row_warp(
-                    a.raw, row, a.dmax, pod.n_reqs, req_at,
-                    [&](int r, int t, const vgs_pick &pk) { a.picks[a.pick_begin[pod.req_begin + r] + t] = pk; }, alive,
-                    score, ndv, used, usedmem, usedcores, &fx);
-                if ((!alive || __float_as_uint(score) != kbits) && lane == 0) atomicOr(a.status, S_MISMATCH);
-                TICK(tC);
-                if (alive) {
-                    if (lane < ndv) { // addPod: the placement becomes usage (scheduler.go:280-297)
-                        const size_t at = (size_t)row * a.dmax + lane;
-                        const_cast<int32_t *>(a.raw.p[VGS_PLANE_USED])[at] = used;
-                        const_cast<int32_t *>(a.raw.p[VGS_PLANE_USEDMEM])[at] = usedmem;
-                        const_cast<int32_t *>(a.raw.p[VGS_PLANE_USEDCORES])[at] = usedcores;
-                    }
-                    // the row's slot among the touched rows
-                    unsigned hit = 0u;
+                // the row's slot in T, a new one if it enters now
+                unsigned hit = 0u;
 #pragma unroll
-                    for (int t = 0; t < kSlotTiles; t++) {
-                        const unsigned b = __ballot_sync(0xffffffffu, t * kWarp + lane < nT && s_trow[t * kWarp + lane] == row);
-                        if (b) hit = (unsigned)(t * kWarp + __ffs((int)b) - 1) + 1u;
-                    }
-                    int slot;
-                    if (hit) {
-                        slot = (int)hit - 1;
-                    } else {
+                for (int t = 0; t < kSlotTiles; t++) {
+                    const unsigned b = __ballot_sync(0xffffffffu, t * kWarp + lane < nT && s_trow[t * kWarp + lane] == row);
+                    if (b) hit = (unsigned)(t * kWarp + __ffs((int)b) - 1) + 1u;
+                }
+                auto take_slot = [&]() {
+                    int slot = (int)hit - 1;
+                    if (!hit) {
                         slot = nT++;
                         if (lane == 0) s_trow[slot] = row, newrow = (int)(uint32_t)best;
                     }
-                    // its words again, from the columns the resolve holds in registers (lane = device slot)
-                    prepare_lanes<DM>(row, ndv, 0u, used, fx.count, usedmem, fx.totalmem, usedcores, fx.totalcore, fx.numa,
-                                      fx.type, a.raw.idle_types, a.walk, a.status, s_cur + (size_t)(slot / kWarp) * kTile4,
-                                      slot % kWarp);
-                    TICK(tD);
+                    if (lane == 0) s_mod[slot / kWarp] |= 1u << (slot % kWarp);
+                    return slot;
+                };
+                if (is_pair) {
+                    // One request, the first Nums fitting devices in walk order: everything comes out of the row's
+                    // tile words (lane = walk position) -- the picks, the usage for the raw planes (Used = Count -
+                    // free slots, ...), and the row's words after the commit, devices re-ranked by (numa rank, free
+                    // slots, slot) as K0 would.  W_SCORE1 is put right when the chunk hands its rows on.
+                    const DevReq rq = cp.first[q];
+                    // its words: from T, from the candidates fetched ahead (row-major), or from the walk copy
+                    const int32_t *src;
+                    int scol, cstride = kWarp;
+                    if (hit) {
+                        src = reinterpret_cast<const int32_t *>(s_cur + (size_t)((hit - 1) / kWarp) * kTile4), scol = (int)((hit - 1) % kWarp);
+                    } else if (row == s_cand_row[q & 1][0] || row == s_cand_row[q & 1][1]) {
+                        src = reinterpret_cast<const int32_t *>(&s_cand[q & 1][row == s_cand_row[q & 1][0] ? 0 : 1][0]);
+                        scol = 0, cstride = 1;
+                    } else {
+                        src = reinterpret_cast<const int32_t *>(a.walk + (size_t)(row / kWarp) * kTile4), scol = row % kWarp;
+                    }
+                    const int j = lane < DM ? lane : 0;
+                    auto word = [&](int k) { return src[((k * (DM / 4) + (j >> 2)) * cstride + scol) * 4 + (j & 3)]; };
+                    int32_t tm = word(W_TOTALMEM), fm = word(W_FREEMEM), fc = word(W_FREECORES), cn = word(W_COUNT);
+                    int32_t fs = word(W_FREESLOTS), tc = word(W_TOTALCORE);
+                    uint32_t mt = (uint32_t)word(W_META);
+                    const int32_t ndv = (int32_t)((mt >> M_NDEV_SHIFT) & 15u);
+                    const int32_t mem = (rq.flags & R_USEPCT) ? pct_mem(tm, rq.pct) : rq.memfix;
+                    const bool f = lane < DM && !(mt & rq.blockmask) && type_ok(rq.mask_lo, rq.mask_hi, mt) && fm >= mem &&
+                                   fc >= rq.coresreq;
+                    const unsigned fits = __ballot_sync(0xffffffffu, f);
+                    const int t = __popc(fits & ((1u << lane) - 1u));
+                    const bool taken = f && t < rq.nums;
+                    const int dslot = (int)((mt >> M_SLOT_SHIFT) & 15u);
+                    if (__popc(fits) < rq.nums) {
+                        if (lane == 0) atomicOr(a.status, S_MISMATCH);
+                    } else {
+                        TICK(tC);
+                        const int slot = take_slot();
+                        if (taken) { // score.go:135-145,168-174
+                            vgs_pick pk;
+                            pk.slot = dslot, pk.usedmem = mem, pk.usedcores = rq.coresreq;
+                            a.picks[pick_lo + t] = pk;
+                            fs = wrap_sub(fs, 1), fm = wrap_sub(fm, mem), fc = wrap_sub(fc, rq.coresreq);
+                            const int32_t used = wrap_sub(cn, fs);
+                            const size_t at = (size_t)row * a.dmax + dslot;
+                            const_cast<int32_t *>(a.raw.p[VGS_PLANE_USED])[at] = used;
+                            const_cast<int32_t *>(a.raw.p[VGS_PLANE_USEDMEM])[at] = wrap_sub(tm, fm);
+                            const_cast<int32_t *>(a.raw.p[VGS_PLANE_USEDCORES])[at] = wrap_sub(tc, fc);
+                            if (used >= VGS_MAX_SHARE) atomicOr(a.status, S_RANGE);
+                            mt &= ~(M_NOFREE | M_EXCL | M_FULL | M_BUSY370);
+                            if (fs <= 0) mt |= M_NOFREE;
+                            if (mt & M_IS100) mt |= M_EXCL;
+                            if ((mt & M_CORENZ) && fc == 0) mt |= M_FULL;
+                            if (mt & M_T370) mt |= M_BUSY370;
+                        }
+                        // the device's place in the walk order now
+                        const bool dev = lane < ndv;
+                        const uint32_t sk = (((mt >> M_NUMA_SHIFT) & 15u) << 25) | ((uint32_t)(fs + (int32_t)kFsBias) << 4) | (uint32_t)dslot;
+                        int rank = 0;
+#pragma unroll
+                        for (int i = 0; i < DM; i++) {
+                            const uint32_t ski = __shfl_sync(0xffffffffu, sk, i);
+                            rank += (i < ndv && ski < sk) ? 1 : 0;
+                        }
+                        const int w = dev ? ndv - 1 - rank : lane;
+                        int32_t *dst = reinterpret_cast<int32_t *>(s_cur + (size_t)(slot / kWarp) * kTile4);
+                        const int dcol = slot % kWarp;
+                        __syncwarp(); // every lane has read its words
+                        if (lane < DM) {
+                            dst[tile_at<DM>(W_TOTALMEM, w, dcol)] = tm, dst[tile_at<DM>(W_FREEMEM, w, dcol)] = fm;
+                            dst[tile_at<DM>(W_FREECORES, w, dcol)] = fc, dst[tile_at<DM>(W_COUNT, w, dcol)] = cn;
+                            dst[tile_at<DM>(W_FREESLOTS, w, dcol)] = fs, dst[tile_at<DM>(W_META, w, dcol)] = (int32_t)mt;
+                            dst[tile_at<DM>(W_TOTALCORE, w, dcol)] = tc;
+                        }
+                        TICK(tD);
+                    }
+                } else {
+                    bool alive;
+                    float score;
+                    int32_t ndv, used, usedmem, usedcores;
+                    RowStatic fx;
+                    resolve_row_warp(
+                        a.raw, row, a.dmax, pod.n_reqs, req_at,
+                        [&](int r, int t, const vgs_pick &pk) { a.picks[a.pick_begin[pod.req_begin + r] + t] = pk; }, alive,
+                        score, ndv, used, usedmem, usedcores, &fx);
+                    if ((!alive || __float_as_uint(score) != kbits) && lane == 0) atomicOr(a.status, S_MISMATCH);
+                    TICK(tC);
+                    if (alive) {
+                        if (lane < ndv) { // addPod: the placement becomes usage (scheduler.go:280-297)
+                            const size_t at = (size_t)row * a.dmax + lane;
+                            const_cast<int32_t *>(a.raw.p[VGS_PLANE_USED])[at] = used;
+                            const_cast<int32_t *>(a.raw.p[VGS_PLANE_USEDMEM])[at] = usedmem;
+                            const_cast<int32_t *>(a.raw.p[VGS_PLANE_USEDCORES])[at] = usedcores;
+                        }
+                        const int slot = take_slot();
+                        // its words again, from the columns the resolve holds in registers (lane = device slot), into T
+                        prepare_lanes<DM>(row, ndv, 0u, used, fx.count, usedmem, fx.totalmem, usedcores, fx.totalcore, fx.numa,
+                                          fx.type, a.raw.idle_types, nullptr, a.status, s_cur + (size_t)(slot / kWarp) * kTile4,
+                                          slot % kWarp);
+                        TICK(tD);
+                    }
                 }
                 res.best_row = (int32_t)(uint32_t)best;
                 res.score = __uint_as_float(kbits);
@@ -466,71 +696,153 @@ __global__ void __launch_bounds__(kDrainThreads) k_drain_commit(const __grid_con
         nT = s_nT;
         TICK(tE);
     }
-    // ---- fit counts: + chunk-start count - the touched rows (as of the pod's turn) that fitted at chunk start
-    for (int k = warp; k < a.n_pods; k += kWarps) {
-        const int n = s_nt_at[k];
-        if (n < 0) continue; // scanned: final
+    // ---- fit counts: + the matrix's count - T's rows (as of the pod's turn) that fitted in the matrix
+    {
+        constexpr int kPer = kDrainThreads / kDrainChunk; // threads per pod
+        const int k = tid / kPer, part = tid % kPer;
+        const int n = k < a.n_pods ? s_nt_at[k] : -1;
         const uint32_t *mine = a.ob + (size_t)k * a.n_tiles * kWarp;
         int32_t was = 0;
-        for (int s = lane; s < n; s += kWarp) was += mine[s_trow[s]] != 0u ? 1 : 0;
-        was = __reduce_add_sync(0xffffffffu, was);
-        if (lane == 0) a.results[k].fit_count += s_count0[k] - was;
+        for (int s = part; s < n; s += kPer) was += mine[s_trow[s]] != 0u ? 1 : 0;
+#pragma unroll
+        for (int d = 1; d < kPer; d <<= 1) was += __shfl_xor_sync(0xffffffffu, was, d);
+        // (n < 0: the pod scanned -- it counted the rows outside T itself, and T live)
+        if (part == 0 && n >= 0) a.results[k].fit_count += s_count0[k] - was;
+    }
+    // ---- the rows this chunk changed go on to k_drain_apply (walk copy) and to the next chunk (its T), W_SCORE1 put right
+    __syncthreads();
+    if (warp == 0) {
+        int n_out = 0;
+        for (int t = 0; t < kSlotTiles; t++) {
+            const uint32_t m = s_mod[t];
+            const bool mine = (m >> lane) & 1u;
+            const int at = n_out + __popc(m & ((1u << lane) - 1u));
+            if (mine) a.carry_out->rows[at] = s_trow[t * kWarp + lane];
+            n_out += __popc(m);
+        }
+        if (lane == 0) a.carry_out->n = n_out;
+    }
+    // word copy: one warp per changed slot in turn
+    {
+        // position of slot s among the changed slots
+        for (int s = warp; s < nT; s += kWarps) {
+            if (!((s_mod[s / kWarp] >> (s % kWarp)) & 1u)) continue;
+            int at = 0;
+            for (int t = 0; t < s / kWarp; t++) at += __popc(s_mod[t]);
+            at += __popc(s_mod[s / kWarp] & ((1u << (s % kWarp)) - 1u));
+            if (lane < DM) {
+                const int32_t *src = reinterpret_cast<const int32_t *>(s_cur + (size_t)(s / kWarp) * kTile4);
+                int32_t *dst = reinterpret_cast<int32_t *>(a.words_out + (size_t)(at / kWarp) * kTile4);
+                int32_t wd[kWalkWords];
+#pragma unroll
+                for (int k = 0; k < kWalkWords; k++) wd[k] = src[tile_at<DM>(k, lane, s % kWarp)];
+                const uint32_t mt = (uint32_t)wd[W_META];
+                const float s1 = (!(mt & M_PAD) && wd[W_FREESLOTS] > 0)
+                                     ? container_score(wd[W_COUNT], wd[W_FREESLOTS], (int32_t)((mt >> M_NDEV_SHIFT) & 15u) - 1)
+                                     : 0.0f;
+                wd[W_SCORE1] = __float_as_int(s1);
+#pragma unroll
+                for (int k = 0; k < kWalkWords; k++) dst[tile_at<DM>(k, lane, at % kWarp)] = wd[k];
+            }
+        }
     }
 #ifdef VGS_DRAIN_TIMING
     if (tid == 0) {
         atomicAdd(&a.stats[1], (int)(tA >> 6)), atomicAdd(&a.stats[2], (int)(tB >> 6)), atomicAdd(&a.stats[3], (int)(tC >> 6));
         atomicAdd(&a.stats[4], (int)(tD >> 6)), atomicAdd(&a.stats[5], (int)(tE >> 6));
+        atomicAdd(&a.stats[6], (int)(tB1 >> 6)), atomicAdd(&a.stats[7], (int)(tB2 >> 6));
     }
 #endif
 }
 
+// the rows a chunk changed, into the walk copy (after the pass that was reading it has finished)
 template <int DM>
-static cudaError_t drain_chunk_t(int dev, DrainChunk &c, uint32_t *ob, unsigned long long *topk, int32_t *counts,
-                                 int sms, cudaStream_t st) {
-    constexpr size_t smem = (size_t)(kDrainChunk / kWarp) * kWalkWords * (DM / 4) * kWarp * sizeof(int4);
-    static bool attr[64] = {}; // (static + dynamic shared memory of the commit kernel passes 48 KB for DM = 12)
+__global__ void __launch_bounds__(256) k_drain_apply(const DrainCarry *__restrict__ carry, const int4 *__restrict__ words,
+                                                     int4 *__restrict__ walk) {
+    constexpr int kTile4 = kWalkWords * (DM / 4) * kWarp, kRow4 = kWalkWords * (DM / 4);
+    const int n = carry->n;
+    for (int i = threadIdx.x; i < n * kRow4; i += blockDim.x) {
+        const int s = i / kRow4, k = i % kRow4, row = carry->rows[s];
+        walk[(size_t)(row / kWarp) * kTile4 + k * kWarp + row % kWarp] = words[(size_t)(s / kWarp) * kTile4 + k * kWarp + s % kWarp];
+    }
+}
+
+// geometry shared by the launchers
+static int drain_segs(int sms, int n_pods, int n_tiles) {
+    // segments per pod: the select CTAs of a chunk fill the GPU about once, a segment is at least 64 tiles
+    int segs = (sms + n_pods - 1) / n_pods;
+    if (segs > kDrainMaxSegs) segs = kDrainMaxSegs;
+    if (segs > (n_tiles + 63) / 64) segs = (n_tiles + 63) / 64;
+    return segs < 1 ? 1 : segs;
+}
+
+template <int DM, bool WALK>
+static cudaError_t drain_eval_launch(int sms, const DrainPass &p, cudaStream_t st) {
+    // one SM is left to the commit kernel of the chunk before (a persistent grid that counted on it would run a
+    // second wave); items = (tile, part of the pods): at least one per resident warp
+    const long long ctas = (long long)(sms > 1 ? sms - 1 : 1) * (WALK ? 2 : 3), warps = ctas * (kScoreThreads / 32);
+    int psplit = (int)((warps + p.n_tiles - 1) / p.n_tiles);
+    if (psplit < 1) psplit = 1;
+    if (psplit > p.n_pods) psplit = p.n_pods;
+    const long long items = (long long)p.n_tiles * psplit;
+    long long grid = (items + kScoreThreads / 32 - 1) / (kScoreThreads / 32);
+    if (grid > ctas) grid = ctas;
+    if (grid < 1) grid = 1;
+    k_drain_eval<DM, WALK><<<(int)grid, kScoreThreads, 0, st>>>(p.walk, p.n_tiles, p.reqs, p.pods, p.n_pods, psplit, p.ob);
+    return cudaGetLastError();
+}
+
+template <int DM>
+static cudaError_t drain_eval_t(int sms, const DrainPass &p, cudaStream_t st) {
+    cudaError_t e;
+    if (p.any_pair && (e = drain_eval_launch<DM, false>(sms, p, st)) != cudaSuccess) return e;
+    if (p.any_walk && (e = drain_eval_launch<DM, true>(sms, p, st)) != cudaSuccess) return e;
+    const int segs = drain_segs(sms, p.n_pods, p.n_tiles);
+    k_drain_select<<<dim3(segs, p.n_pods), kSelectThreads, 0, st>>>(p.ob, p.n_tiles, p.row_base, segs, p.seglist, p.segcount,
+                                                                     p.done, p.topk, p.counts);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_drain_pass(int dm, int sms, const DrainPass &p, cudaStream_t st) {
+    if (p.n_pods <= 0 || p.n_pods > kDrainChunk || p.n_tiles <= 0) return cudaErrorInvalidValue;
+    return dm == 8 ? drain_eval_t<8>(sms, p, st) : drain_eval_t<12>(sms, p, st);
+}
+
+template <int DM>
+static cudaError_t drain_commit_t(int dev, const DrainChunk &c, cudaStream_t st) {
+    constexpr size_t smem = (size_t)(kDrainSlots / kWarp) * kWalkWords * (DM / 4) * kWarp * sizeof(int4);
+    static bool attr[64] = {}; // (static + dynamic shared memory of the commit kernel passes 48 KB)
     if (dev >= 0 && dev < 64 && !attr[dev]) {
         cudaError_t ea = cudaFuncSetAttribute(k_drain_commit<DM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (ea != cudaSuccess) return ea;
         attr[dev] = true;
     }
-    // enough (tile, pod part) items for four rounds of the resident warps (two CTAs of 8 warps per SM)
-    const long long ctas = (long long)sms * 2, warps = ctas * (kScoreThreads / 32);
-    int psplit = (int)((4 * warps + c.n_tiles - 1) / (c.n_tiles > 0 ? c.n_tiles : 1));
-    if (psplit < 1) psplit = 1;
-    if (psplit > c.n_pods) psplit = c.n_pods;
-    const long long items = (long long)c.n_tiles * psplit;
-    long long grid = (items + kScoreThreads / 32 - 1) / (kScoreThreads / 32);
-    if (grid > ctas) grid = ctas;
-    if (grid < 1) grid = 1;
-    k_drain_eval<DM><<<(int)grid, kScoreThreads, 0, st>>>(c.walk, c.n_tiles, c.reqs, c.pods, c.n_pods, psplit, ob);
-    cudaError_t e = cudaGetLastError();
-    if (e != cudaSuccess) return e;
-    // segments per pod: the select CTAs of a chunk fill the GPU about once, a segment is at least 64 tiles
-    int segs = (int)((sms + c.n_pods - 1) / c.n_pods);
-    if (segs > kDrainMaxSegs) segs = kDrainMaxSegs;
-    if (segs > (c.n_tiles + 63) / 64) segs = (c.n_tiles + 63) / 64;
-    if (segs < 1) segs = 1;
-    k_drain_select<<<dim3(segs, c.n_pods), kSelectThreads, 0, st>>>(ob, c.n_tiles, c.row_base, segs, topk, counts);
-    if ((e = cudaGetLastError()) != cudaSuccess) return e;
-    c.n_segs = segs;
     k_drain_commit<DM><<<1, kDrainThreads, smem, st>>>(c);
     return cudaGetLastError();
 }
 
-cudaError_t launch_drain_chunk(int dm, int dev, int sms, const RawPlanes &raw, int4 *walk, int32_t n_tiles,
-                               int32_t n_nodes, int32_t row_base, int32_t dmax, const DevReq *reqs, const GenPod *pods,
-                               const int32_t *pick_begin, int32_t n_pods, uint32_t *ob, unsigned long long *topk,
-                               int32_t *counts, vgs_result *results, vgs_pick *picks, uint32_t *status, int32_t *stats,
-                               cudaStream_t st) {
-    if (n_pods <= 0 || n_pods > kDrainChunk || n_tiles <= 0) return cudaErrorInvalidValue;
+cudaError_t launch_drain_commit(int dm, int dev, int sms, const RawPlanes &raw, int32_t n_nodes, int32_t dmax,
+                                const DrainPass &p, const int32_t *pick_begin, bool first, const void *carry_in,
+                                const int4 *words_in, void *carry_out, int4 *words_out, vgs_result *results, vgs_pick *picks, uint32_t *status, int32_t *stats, cudaStream_t st) {
+    if (p.n_pods <= 0 || p.n_pods > kDrainChunk || p.n_tiles <= 0) return cudaErrorInvalidValue;
     DrainChunk c;
-    c.walk = walk, c.n_tiles = n_tiles, c.n_nodes = n_nodes, c.row_base = row_base, c.dmax = dmax;
+    c.walk = p.walk, c.n_tiles = p.n_tiles, c.n_nodes = n_nodes, c.row_base = p.row_base, c.dmax = dmax;
     c.raw = raw;
-    c.reqs = reqs, c.pods = pods, c.pick_begin = pick_begin, c.n_pods = n_pods;
-    c.ob = ob, c.topk = topk, c.counts = counts, c.n_segs = 1;
+    c.reqs = p.reqs, c.pods = p.pods, c.pick_begin = pick_begin, c.n_pods = p.n_pods;
+    c.ob = p.ob, c.topk = p.topk, c.counts = p.counts;
+    c.first = first ? 1 : 0;
+    c.carry_in = static_cast<const DrainCarry *>(carry_in), c.words_in = words_in;
+    c.carry_out = static_cast<DrainCarry *>(carry_out), c.words_out = words_out;
     c.results = results, c.picks = picks, c.status = status, c.stats = stats;
-    return dm == 8 ? drain_chunk_t<8>(dev, c, ob, topk, counts, sms, st) : drain_chunk_t<12>(dev, c, ob, topk, counts, sms, st);
+    return dm == 8 ? drain_commit_t<8>(dev, c, st) : drain_commit_t<12>(dev, c, st);
 }
+
+cudaError_t launch_drain_apply(int dm, const void *carry, const int4 *carry_words, int4 *walk, cudaStream_t st) {
+    if (dm == 8) k_drain_apply<8><<<1, 256, 0, st>>>(static_cast<const DrainCarry *>(carry), carry_words, walk);
+    else k_drain_apply<12><<<1, 256, 0, st>>>(static_cast<const DrainCarry *>(carry), carry_words, walk);
+    return cudaGetLastError();
+}
+
+size_t drain_carry_bytes() { return sizeof(DrainCarry); }
 
 } // namespace vgs

@@ -63,15 +63,36 @@ struct FilterOne {
 cudaError_t launch_filter_single(int dm, bool nums1, int dev, const ScoreArgs &a, const FilterOne &fo,
                                  cudaStream_t st);
 cudaError_t launch_filter_one(int dm, int dev, const ScoreArgs &a, const FilterOne &fo, cudaStream_t st);
-// batch-scale drain (vgs_drain.cu), one chunk of <= kDrainChunk pods: chunk-start pass over the whole snapshot (score
-// bits of every (pod, node) into ob[kDrainChunk][n_tiles * 32], then per pod the fit count and the best keys into
-// counts[kDrainChunk][8] / topk[kDrainChunk][8][kDrainTop]), then the chunk in pod order by one CTA
+// Batch-scale drain (vgs_drain.cu), one chunk of <= kDrainChunk pods.
+//   launch_drain_pass    the chunk's pods against the whole walk copy: score bits of every (pod, node) into
+//                        ob[kDrainChunk][n_tiles * 32], then per pod the fit count and the best keys into
+//                        counts[kDrainChunk] / topk[kDrainChunk][kDrainListWords]
+//   launch_drain_commit  the chunk in pod order by one CTA: results, picks, usage into the raw planes; the rows it
+//                        changed go into the carry block (and NOT into the walk copy: the next chunk's pass may be
+//                        reading it) -- that pass may therefore be one chunk stale: `first` = it is not
+//   launch_drain_apply   the carry block into the walk copy
 constexpr int kDrainMaxSegs = 8;
-cudaError_t launch_drain_chunk(int dm, int dev, int sms, const RawPlanes &raw, int4 *walk, int32_t n_tiles,
-                               int32_t n_nodes, int32_t row_base, int32_t dmax, const DevReq *reqs, const GenPod *pods,
-                               const int32_t *pick_begin, int32_t n_pods, uint32_t *ob, unsigned long long *topk,
-                               int32_t *counts, vgs_result *results, vgs_pick *picks, uint32_t *status, int32_t *stats,
-                               cudaStream_t st);
+constexpr int kDrainListWords = kDrainTop + 1;
+struct DrainPass {
+    const int4 *walk;
+    int32_t n_tiles, row_base;
+    const DevReq *reqs;
+    const GenPod *pods; // the chunk's, batch order
+    int32_t n_pods;
+    bool any_pair, any_walk; // pods of the chunk that take the pair / the walk evaluation (vgs_pair_eval.cuh)
+    uint32_t *ob;
+    unsigned long long *seglist; // scratch of the select kernel: [pod][kDrainMaxSegs][kDrainListWords]
+    int32_t *segcount;           // [pod][kDrainMaxSegs]
+    unsigned int *done;          // [kDrainChunk], zero at rest
+    unsigned long long *topk;    // [pod][kDrainListWords]
+    int32_t *counts;             // [pod]
+};
+cudaError_t launch_drain_pass(int dm, int sms, const DrainPass &p, cudaStream_t st);
+cudaError_t launch_drain_commit(int dm, int dev, int sms, const RawPlanes &raw, int32_t n_nodes, int32_t dmax,
+                                const DrainPass &p, const int32_t *pick_begin, bool first, const void *carry_in,
+                                const int4 *words_in, void *carry_out, int4 *words_out, vgs_result *results, vgs_pick *picks, uint32_t *status, int32_t *stats, cudaStream_t st);
+cudaError_t launch_drain_apply(int dm, const void *carry, const int4 *carry_words, int4 *walk, cudaStream_t st);
+size_t drain_carry_bytes();
 // launch geometry of a thread-per-node score kernel (persistent grid over (tile group, pod chunk) items)
 cudaError_t plan_score_launch(const void *kernel, int dev, int32_t n_tiles, int32_t n_pods, int max_warps,
                               int smem_per_pod, ScoreLaunch *L);

@@ -31,7 +31,7 @@ enum {
     W_META = 5,      // packed small fields, see M_*
     W_SCORE1 = 6,    // f32 bits of Count/(Count-Used) + (ndev-1): the node score if this
                      // device alone is picked (score.go:180 with Nums == 1)
-    W_SPARE = 7,
+    W_TOTALCORE = 7, // Totalcore (with W_FREECORES: Usedcores; read by the drain only)
     kWalkWords = 8
 };
 
@@ -88,7 +88,7 @@ constexpr int32_t G_LEGACY = 4;        // host routing only: more picks than the
 constexpr int32_t G_SAME_FIRST = 8;    // same first request (and pod flags) as the pod before it in the class list
 constexpr int32_t G_SAVE_FIRST = 16;   // the pod after it carries G_SAME_FIRST
 constexpr int kDrainChunk = 64;       // pods per chunk of the batch-scale drain (= touched rows a chunk can hold)
-constexpr int kDrainTop = 16;         // candidate keys kept per pod by the chunk-start pass
+constexpr int kDrainTop = 32;         // candidate keys kept per pod by the chunk-start pass
 constexpr int kWalkMaxPicks = 100;     // sum of Nums per pod the walk kernel accepts (7-bit stamps, 12 initial)
 
 inline int32_t gen_pod_flags(const DevReq *r, int n) {

@@ -59,7 +59,9 @@ __device__ __forceinline__ void pair_eval(const PairNode<DM> &nd, const DevReq &
         free_ += take ? nd.freeslots[j] : 0;
     }
     fit = cnt >= rq.nums;
-    score = fit ? container_score(total, free_, nd.ndev - rq.nums) : 0.0f;
+    // (a node that is out divides by 1: 0 / 0 would send the whole warp through the division's slow path)
+    score = container_score(total, fit ? free_ : 1, nd.ndev - rq.nums);
+    score = fit ? score : 0.0f;
 }
 
 } // namespace vgs

@@ -110,7 +110,7 @@ __device__ __forceinline__ void prepare_node(const RawPlanes &raw, int row, int3
             put(W_FREESLOTS, w, fj);
             put(W_META, w, (int32_t)meta);
             put(W_SCORE1, w, __float_as_int(s1));
-            put(W_SPARE, w, 0);
+            put(W_TOTALCORE, w, totalcore[j]);
         } else {
             uint32_t meta = M_PAD | M_NOFREE | M_ALWAYS | ((uint32_t)j << M_SLOT_SHIFT) |
                             ((uint32_t)nd << M_NDEV_SHIFT);
@@ -121,7 +121,7 @@ __device__ __forceinline__ void prepare_node(const RawPlanes &raw, int row, int3
             put(W_FREESLOTS, j, 0);
             put(W_META, j, (int32_t)meta);
             put(W_SCORE1, j, 0);
-            put(W_SPARE, j, 0);
+            put(W_TOTALCORE, j, 0);
         }
     }
     if (stage) {
@@ -141,7 +141,7 @@ __device__ __forceinline__ void prepare_node(const RawPlanes &raw, int row, int3
 // The same words for ONE row by a whole warp (lane = device slot): the drain's commits, where the row comes back
 // into play at once and a single thread's run through prepare_node would sit on the critical path.  mirror: a
 // second tile (shared memory, the row at column mirror_lane) that receives the same words; may be null.
-// the core: lane j holds the columns of device slot j (zeros from slot nd on; nd already clamped to [0, dmax])
+// the core: lane j holds the columns of device slot j (nd already clamped to [0, dmax]); walk or mirror may be null
 template <int DM>
 __device__ __forceinline__ void prepare_lanes(int row, int32_t nd, uint32_t bad, int32_t used, int32_t count,
                                               int32_t usedmem, int32_t totalmem, int32_t usedcores, int32_t totalcore,
@@ -197,16 +197,17 @@ __device__ __forceinline__ void prepare_lanes(int row, int32_t nd, uint32_t bad,
         words[W_COUNT] = count;
         words[W_FREESLOTS] = fj;
         words[W_SCORE1] = __float_as_int(s1);
+        words[W_TOTALCORE] = totalcore;
     } else {
         meta = M_PAD | M_NOFREE | M_ALWAYS | ((uint32_t)j << M_SLOT_SHIFT) | ((uint32_t)nd << M_NDEV_SHIFT);
     }
     words[W_META] = (int32_t)meta;
     const int tile = row / kWarp, lane = row % kWarp;
-    int32_t *wbase = reinterpret_cast<int32_t *>(walk + (size_t)tile * kWalkWords * (DM / 4) * kWarp);
+    int32_t *wbase = walk ? reinterpret_cast<int32_t *>(walk + (size_t)tile * kWalkWords * (DM / 4) * kWarp) : nullptr;
     int32_t *mbase = reinterpret_cast<int32_t *>(mirror);
 #pragma unroll
     for (int k = 0; k < kWalkWords; k++) {
-        wbase[((k * (DM / 4) + (w >> 2)) * kWarp + lane) * 4 + (w & 3)] = words[k];
+        if (wbase) wbase[((k * (DM / 4) + (w >> 2)) * kWarp + lane) * 4 + (w & 3)] = words[k];
         if (mbase) mbase[((k * (DM / 4) + (w >> 2)) * kWarp + mirror_lane) * 4 + (w & 3)] = words[k];
     }
 }

@@ -15,7 +15,7 @@ for ln in open(sys.argv[2]):
     if m:
         cur = (m.group(1).split("/")[-1], int(m.group(2)))
         continue
-    if re.match(r"^\s*/\*[0-9a-f]{4}\*/", ln):
+    if re.match(r"^\s*/\*[0-9a-f]{4,}\*/", ln):
         lines.append(cur)
 assert len(lines) == len(counts), (len(lines), len(counts))
 agg = defaultdict(int)
