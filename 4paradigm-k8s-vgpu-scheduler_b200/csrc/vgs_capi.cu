@@ -1291,7 +1291,10 @@ int vgs_drain_batch(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_r
         c->version++;
         rc = download_locked(c, results, picks);
         c->plan.drain_rescans = c->h_drain_stats[0];
-        if (getenv("VGS_DRAIN_DEBUG")) fprintf(stderr, "drain cycles/64: A %d B1 %d B2 %d B %d C %d D %d E %d\n", c->h_drain_stats[1], c->h_drain_stats[6], c->h_drain_stats[7], c->h_drain_stats[2], c->h_drain_stats[3], c->h_drain_stats[4], c->h_drain_stats[5]);
+#ifdef VGS_DRAIN_TIMING // (a build for kernel work only: per-phase clock counts of the commit kernel, in units of 64 cycles)
+        fprintf(stderr, "drain cycles/64: A %d B1 %d B2 %d B %d C %d D %d E %d\n", c->h_drain_stats[1], c->h_drain_stats[6],
+                c->h_drain_stats[7], c->h_drain_stats[2], c->h_drain_stats[3], c->h_drain_stats[4], c->h_drain_stats[5]);
+#endif
         return rc;
     }
     for (int32_t p = 0; p < n_pods; p++) {

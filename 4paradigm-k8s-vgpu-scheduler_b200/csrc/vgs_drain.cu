@@ -466,7 +466,8 @@ __global__ void __launch_bounds__(kDrainThreads) k_drain_commit(const __grid_con
                 const int32_t fs = src[tile_at<DM>(W_FREESLOTS, jj, col)];
                 const uint32_t mt = (uint32_t)src[tile_at<DM>(W_META, jj, col)];
                 const int32_t mem = (rq.flags & R_USEPCT) ? pct_mem(tm, rq.pct) : rq.memfix;
-                const bool f = on && !(mt & rq.blockmask) && type_ok(rq.mask_lo, rq.mask_hi, mt) && fm >= mem && fc >= rq.coresreq;
+                const bool f = (int)on & (int)!(mt & rq.blockmask) & (int)type_ok(rq.mask_lo, rq.mask_hi, mt) & (int)(fm >= mem) &
+                               (int)(fc >= rq.coresreq);
                 const unsigned grp = (__ballot_sync(0xffffffffu, f) >> (g * kGrp)) & ((1u << kGrp) - 1u);
                 const bool taken = f && __popc(grp & ((1u << j) - 1u)) < rq.nums;
                 uint32_t total = taken ? (uint32_t)cn : 0u, free_ = taken ? (uint32_t)fs : 0u;
@@ -477,7 +478,8 @@ __global__ void __launch_bounds__(kDrainThreads) k_drain_commit(const __grid_con
                 }
                 const bool fit = slot < nT && __popc(grp) >= rq.nums;
                 const int32_t ndv = (int32_t)((__shfl_sync(0xffffffffu, mt, g * kGrp) >> M_NDEV_SHIFT) & 15u);
-                const float score = container_score((int32_t)total, fit ? (int32_t)free_ : 1, ndv - rq.nums);
+                // (rows that are out divide 1 by 1: a zero operand would take the whole warp through the division's slow path)
+                const float score = container_score(fit ? (int32_t)total : 1, fit ? (int32_t)free_ : 1, ndv - rq.nums);
                 if (fit) {
                     const unsigned long long v = key_of(score, (uint32_t)(a.row_base + s_trow[slot]));
                     key = v > key ? v : key;
@@ -568,10 +570,12 @@ __global__ void __launch_bounds__(kDrainThreads) k_drain_commit(const __grid_con
                 const int32_t row = (int32_t)(uint32_t)best - a.row_base;
                 // the row's slot in T, a new one if it enters now
                 unsigned hit = 0u;
+                if (best != lkey) { // (a row out of the list is not in T)
 #pragma unroll
-                for (int t = 0; t < kSlotTiles; t++) {
-                    const unsigned b = __ballot_sync(0xffffffffu, t * kWarp + lane < nT && s_trow[t * kWarp + lane] == row);
-                    if (b) hit = (unsigned)(t * kWarp + __ffs((int)b) - 1) + 1u;
+                    for (int t = 0; t < kSlotTiles; t++) {
+                        const unsigned b = __ballot_sync(0xffffffffu, t * kWarp + lane < nT && s_trow[t * kWarp + lane] == row);
+                        if (b) hit = (unsigned)(t * kWarp + __ffs((int)b) - 1) + 1u;
+                    }
                 }
                 auto take_slot = [&]() {
                     int slot = (int)hit - 1;
@@ -606,8 +610,8 @@ __global__ void __launch_bounds__(kDrainThreads) k_drain_commit(const __grid_con
                     uint32_t mt = (uint32_t)word(W_META);
                     const int32_t ndv = (int32_t)((mt >> M_NDEV_SHIFT) & 15u);
                     const int32_t mem = (rq.flags & R_USEPCT) ? pct_mem(tm, rq.pct) : rq.memfix;
-                    const bool f = lane < DM && !(mt & rq.blockmask) && type_ok(rq.mask_lo, rq.mask_hi, mt) && fm >= mem &&
-                                   fc >= rq.coresreq;
+                    const bool f = (int)(lane < DM) & (int)!(mt & rq.blockmask) & (int)type_ok(rq.mask_lo, rq.mask_hi, mt) &
+                                   (int)(fm >= mem) & (int)(fc >= rq.coresreq);
                     const unsigned fits = __ballot_sync(0xffffffffu, f);
                     const int t = __popc(fits & ((1u << lane) - 1u));
                     const bool taken = f && t < rq.nums;

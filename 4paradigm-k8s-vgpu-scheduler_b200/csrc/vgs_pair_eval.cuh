@@ -51,16 +51,17 @@ __device__ __forceinline__ void pair_eval(const PairNode<DM> &nd, const DevReq &
 #pragma unroll
     for (int j = 0; j < DM; j++) {
         const int32_t mem = usepct ? pct_mem(nd.totalmem[j], rq.pct) : rq.memfix;
-        const bool f = !(nd.meta[j] & rq.blockmask) && type_ok(rq.mask_lo, rq.mask_hi, nd.meta[j]) &&
-                       nd.freemem[j] >= mem && nd.freecores[j] >= rq.coresreq;
-        const bool take = f && cnt < rq.nums;
+        // (& on purpose: no short-circuit branches)
+        const bool f = (int)!(nd.meta[j] & rq.blockmask) & (int)type_ok(rq.mask_lo, rq.mask_hi, nd.meta[j]) &
+                       (int)(nd.freemem[j] >= mem) & (int)(nd.freecores[j] >= rq.coresreq);
+        const bool take = (int)f & (int)(cnt < rq.nums);
         cnt += f ? 1 : 0;
         total += take ? nd.count[j] : 0;
         free_ += take ? nd.freeslots[j] : 0;
     }
     fit = cnt >= rq.nums;
-    // (a node that is out divides by 1: 0 / 0 would send the whole warp through the division's slow path)
-    score = container_score(total, fit ? free_ : 1, nd.ndev - rq.nums);
+    // (a node that is out divides 1 by 1: a zero on either side of the division sends the whole warp through its slow path)
+    score = container_score(fit ? total : 1, fit ? free_ : 1, nd.ndev - rq.nums);
     score = fit ? score : 0.0f;
 }
 
