@@ -58,6 +58,10 @@ struct vgs_ctx {
     int4 *d_walk = nullptr;
     uint32_t *d_status = nullptr;
     uint32_t *h_status = nullptr; // pinned
+    // the small arrays every score launch touches (request staging, bit tables of the two sliced classes, candidate
+    // block) are carved from ONE allocation: their addresses relative to each other decide how the K1 phase runs (a
+    // 512 KB shift of this group cost 11 % before), so they must not depend on what else the context allocates
+    unsigned char *d_arena = nullptr;
     unsigned int *d_done = nullptr; // CTA counter of the single-launch Filter kernel, zero at rest
     // batch-scale drain: per-chunk scratch -- candidate lists, counts, and (allocated by the first chunked drain) the
     // score bits of every (pod of the chunk, node)
@@ -233,6 +237,7 @@ void free_all(vgs_ctx *c) {
     if (c->ev_delta) cudaEventDestroy(c->ev_delta);
     cudaFree(c->d_status);
     cudaFree(c->d_done);
+    cudaFree(c->d_arena);
     for (int k = 0; k < 2; k++) {
         cudaFree(c->d_topk[k]);
         cudaFree(c->d_dcounts[k]);
@@ -252,13 +257,10 @@ void free_all(vgs_ctx *c) {
     cudaFreeHost(c->h_deltas);
     cudaFree(c->d_rowlist);
     for (int k = 0; k < 2; k++) {
-        cudaFree(c->d_slice[k]);
         cudaFreeHost(c->h_slice[k]);
         cudaFree(c->d_prep[k]);
     }
-    cudaFree(c->d_stage);
     cudaFreeHost(c->h_stage);
-    cudaFree(c->d_keys);
     cudaFree(c->d_results);
     cudaFreeHost(c->h_results);
     cudaFreeHost(c->h_picks);
@@ -359,20 +361,6 @@ int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
     CUI(cudaMallocHost(&c->h_status, 2 * sizeof(uint32_t)));
     CUI(cudaMalloc(&c->d_done, sizeof(unsigned int)));
     CUI(cudaMemset(c->d_done, 0, sizeof(unsigned int)));
-    for (int k = 0; k < 2; k++) {
-        CUI(cudaMalloc(&c->d_topk[k], (size_t)kDrainChunk * kDrainListWords * sizeof(unsigned long long)));
-        CUI(cudaMalloc(&c->d_dcounts[k], (size_t)kDrainChunk * sizeof(int32_t)));
-        CUI(cudaEventCreateWithFlags(&c->ev_pass[k], cudaEventDisableTiming));
-        CUI(cudaEventCreateWithFlags(&c->ev_commit[k], cudaEventDisableTiming));
-        CUI(cudaMalloc(&c->d_carry[k], drain_carry_bytes()));
-        CUI(cudaMalloc(&c->d_carry_words[k], (size_t)(kDrainChunk / kWarp) * walk_int4_per_tile(c->dm) * sizeof(int4)));
-    }
-    CUI(cudaMalloc(&c->d_seglist, (size_t)kDrainChunk * kDrainMaxSegs * kDrainListWords * sizeof(unsigned long long)));
-    CUI(cudaMalloc(&c->d_segcount, (size_t)kDrainChunk * kDrainMaxSegs * sizeof(int32_t)));
-    CUI(cudaMalloc(&c->d_seldone, kDrainChunk * sizeof(unsigned int)));
-    CUI(cudaMemset(c->d_seldone, 0, kDrainChunk * sizeof(unsigned int)));
-    CUI(cudaMalloc(&c->d_drain_stats, 8 * sizeof(int32_t)));
-    CUI(cudaMallocHost(&c->h_drain_stats, 8 * sizeof(int32_t)));
     CUI(cudaDeviceGetAttribute(&c->sms, cudaDevAttrMultiProcessorCount, cfg->device));
     c->max_deltas = 16384;
     CUI(cudaEventCreateWithFlags(&c->ev_delta, cudaEventDisableTiming));
@@ -389,8 +377,23 @@ int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
         align_up((R + 1) * sizeof(int32_t), 256) + 3 * align_up(P * sizeof(DevReq), 256) +
         3 * align_up(P * sizeof(int32_t), 256) + 2 * align_up(P * sizeof(GenPod), 256);
     c->stage_bytes = o;
-    CUI(cudaMalloc(&c->d_stage, o));
     CUI(cudaMallocHost(&c->h_stage, o));
+    // arena layout: [stage | pad | slice 0 | slice 1 | candidate block], every piece on a 4 KB boundary
+    {
+        const size_t wp0 = align_up((P + 31) / 32, 32);
+        const size_t rows0 = VGS_MAX_TYPES + 5 * (kSliceMaxDistinct + 1) + (kSliceMaxPct + 1);
+        const size_t slice_b = (rows0 * wp0 + 2 * kSliceMaxDistinct + kSliceMaxPct + P + 64) * sizeof(uint32_t);
+        const size_t picks_off0 = align_up(P * (sizeof(unsigned long long) + sizeof(int32_t)) + 8, 16);
+        const size_t xblock_b = align_up(picks_off0 + (size_t)cfg->max_picks * sizeof(vgs_pick), 16);
+        const size_t pad_b = (size_t)(c->tune.alloc_pad_kb > 0 ? c->tune.alloc_pad_kb : 0) * 1024;
+        const size_t o_slice0 = align_up(o, 4096) + pad_b, o_slice1 = o_slice0 + align_up(slice_b, 4096);
+        const size_t o_keys = o_slice1 + align_up(slice_b, 4096);
+        CUI(cudaMalloc(&c->d_arena, o_keys + align_up(xblock_b, 4096)));
+        c->d_stage = c->d_arena;
+        c->d_slice[0] = reinterpret_cast<uint32_t *>(c->d_arena + o_slice0);
+        c->d_slice[1] = reinterpret_cast<uint32_t *>(c->d_arena + o_slice1);
+        c->d_keys = reinterpret_cast<unsigned long long *>(c->d_arena + o_keys);
+    }
 
     {
         const size_t wp = align_up((P + 31) / 32, 32);
@@ -399,7 +402,6 @@ int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
         const size_t dinfo_b = max_tiles * 32 * 8 * sizeof(SliceDev), pcls_b = max_tiles * 32 * 32;
         const size_t hset_b = kSliceHash * sizeof(uint32_t), gvals_b = (kSliceDict + 4) * sizeof(uint32_t);
         for (int k = 0; k < 2; k++) {
-            CUI(cudaMalloc(&c->d_slice[k], c->slice_words * sizeof(uint32_t)));
             CUI(cudaMallocHost(&c->h_slice[k], c->slice_words * sizeof(uint32_t)));
             CUI(cudaMalloc(&c->d_prep[k], dinfo_b + pcls_b + hset_b + gvals_b));
             c->tab[k].dinfo = reinterpret_cast<uint4 *>(c->d_prep[k]);
@@ -414,7 +416,6 @@ int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
     // the picks of its own best nodes in that one collective (vgs_exchange_block / vgs_exchange_merge)
     c->picks_off = align_up(P * (sizeof(unsigned long long) + sizeof(int32_t)) + 8, 16);
     c->xblock_bytes = align_up(c->picks_off + (size_t)cfg->max_picks * sizeof(vgs_pick), 16);
-    CUI(cudaMalloc(&c->d_keys, c->xblock_bytes));
     c->d_counts = reinterpret_cast<int32_t *>(c->d_keys + P);
     CUI(cudaMemset(c->d_keys, 0, c->xblock_bytes));
     c->dirty_pods = 0;
@@ -427,6 +428,21 @@ int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
         CUI(cudaMalloc(&c->d_vfit, P * max_tiles * sizeof(uint32_t)));
         CUI(cudaMalloc(&c->d_vscore, P * (size_t)cfg->max_nodes * sizeof(float)));
     }
+    // the drain's small scratch blocks, after everything the score path uses (their addresses stay what they were)
+    for (int k = 0; k < 2; k++) {
+        CUI(cudaMalloc(&c->d_topk[k], (size_t)kDrainChunk * kDrainListWords * sizeof(unsigned long long)));
+        CUI(cudaMalloc(&c->d_dcounts[k], (size_t)kDrainChunk * sizeof(int32_t)));
+        CUI(cudaEventCreateWithFlags(&c->ev_pass[k], cudaEventDisableTiming));
+        CUI(cudaEventCreateWithFlags(&c->ev_commit[k], cudaEventDisableTiming));
+        CUI(cudaMalloc(&c->d_carry[k], drain_carry_bytes()));
+        CUI(cudaMalloc(&c->d_carry_words[k], (size_t)(kDrainChunk / kWarp) * walk_int4_per_tile(c->dm) * sizeof(int4)));
+    }
+    CUI(cudaMalloc(&c->d_seglist, (size_t)kDrainChunk * kDrainMaxSegs * kDrainListWords * sizeof(unsigned long long)));
+    CUI(cudaMalloc(&c->d_segcount, (size_t)kDrainChunk * kDrainMaxSegs * sizeof(int32_t)));
+    CUI(cudaMalloc(&c->d_seldone, kDrainChunk * sizeof(unsigned int)));
+    CUI(cudaMemset(c->d_seldone, 0, kDrainChunk * sizeof(unsigned int)));
+    CUI(cudaMalloc(&c->d_drain_stats, 8 * sizeof(int32_t)));
+    CUI(cudaMallocHost(&c->h_drain_stats, 8 * sizeof(int32_t)));
 #undef CUI
     *out = c;
     return VGS_OK;

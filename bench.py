@@ -574,6 +574,59 @@ def main():
             lg.close()
             del whole, lg
 
+    # ---- sequential placement of the whole cfg3 batch: vgs_drain_batch, snapshot resident, the C
+    # call with host buffers (request records up, results + picks down); chunked path against the per-pod chain,
+    # pod for pod, and the first pods against P sequential oracle Filters ------------------------------------------
+    drain = None
+    if world == 1 and not args.no_configs and args.config == "cfg3":
+        if not configs:
+            leg.close()
+        import oracle
+        whole_d, bd = v.workload.make_config("cfg3")
+        pd_, rd_ = v.capi.pack_batch(bd, whole_d.type_names)
+        res_d = {k: np.zeros(len(pd_), dtype=v.capi.RESULT_DTYPE) for k in (0, -1)}
+        pk_d = {k: np.zeros(int(rd_["nums"].sum()), dtype=v.capi.PICK_DTYPE) for k in (0, -1)}
+        t_d, plan_d = {}, None
+        for chunk in (0, -1):
+            with v.Context(max_nodes=whole_d.n_nodes, max_devices=D, max_pods=len(pd_), max_reqs=len(rd_),
+                           max_picks=int(rd_["nums"].sum()), device=local, tuning={"drain_chunk": chunk}) as cd:
+                ts = []
+                for _ in range(4 if chunk == 0 else 2):
+                    cd.upload(whole_d)
+                    t0 = time.perf_counter()
+                    rc = cd.lib.vgs_drain_batch(cd.h, len(pd_), pd_.ctypes.data, len(rd_), rd_.ctypes.data,
+                                                res_d[chunk].ctypes.data, pk_d[chunk].ctypes.data)
+                    ts.append(time.perf_counter() - t0)
+                    cd._check(rc)
+                t_d[chunk] = min(ts[1:])
+                if chunk == 0:
+                    plan_d = cd.plan()
+        n_chk = 96
+        planes_o = whole_d.planes.copy()
+        ok_o = True
+        pb = bd.pick_begin
+        for q in range(n_chk):
+            ro = oracle.score_packed(v.Snapshot(planes_o, whole_d.ndev, whole_d.type_names), bd.select([q]))
+            r0, r1 = bd.pod_req_range(q)
+            mine = pk_d[0][int(pb[r0]):int(pb[r1])]
+            ok_o = ok_o and int(ro.best_row[0]) == int(res_d[0]["best_row"][q]) and int(ro.fit_count[0]) == int(res_d[0]["fit_count"][q]) \
+                and ro.score[:1].view(np.uint32)[0] == res_d[0]["score"][q:q + 1].view(np.uint32)[0] \
+                and np.array_equal(ro.picks, np.stack([mine["slot"], mine["usedmem"], mine["usedcores"]], axis=1))
+            if ro.best_row[0] >= 0:
+                for sl, m_, c_ in ro.picks:
+                    planes_o[0, ro.best_row[0], sl] += 1
+                    planes_o[2, ro.best_row[0], sl] += m_
+                    planes_o[4, ro.best_row[0], sl] += c_
+        drain = {"workload": f"the cfg3 batch placed pod after pod: {len(pd_)} pods x {whole_d.n_nodes} nodes, each pod scored "
+                             "against the snapshot as the winners before it left it (P sequential Filters + addPod)",
+                 "api": "vgs_drain_batch, snapshot resident, host buffers; best wall clock of 3 calls",
+                 "ms": 1e3 * t_d[0], "us_per_pod": 1e6 * t_d[0] / len(pd_), "chunks": plan_d.drain_chunks,
+                 "rescans": plan_d.drain_rescans, "per_pod_chain_ms": 1e3 * t_d[-1],
+                 "equals_per_pod_chain": bool(np.array_equal(res_d[0], res_d[-1]) and np.array_equal(pk_d[0], pk_d[-1])),
+                 "check": {"pods_checked": n_chk, "bit_exact_vs_sequential_oracle": bool(ok_o)},
+                 "placed": int((res_d[0]["best_row"] >= 0).sum())}
+        del whole_d
+
     # ---- the same sharded pass through vgs_group_* : ONE process (rank 0) driving all N GPUs, exchange by NCCL
     # all-gather and by peer-mapped stores.  The other ranks wait on the rendezvous store (a CPU wait: an NCCL
     # barrier would keep their GPUs spinning).  Wall clock per vgs_group_score_batch call, snapshot resident.
@@ -664,6 +717,11 @@ def main():
         line["e2e_delta"] = e2e_delta
     if configs:
         line["configs"] = configs
+    if drain:
+        line["drain"] = drain
+        if not (drain["equals_per_pod_chain"] and drain["check"]["bit_exact_vs_sequential_oracle"]):
+            print(json.dumps({"error": "drain: result differs", "drain": drain}), flush=True)
+            raise SystemExit(3)
     if group:
         line["group"] = group
     if latency:

@@ -100,7 +100,9 @@ typedef struct {
                                * 0 = the phased path (copy, score kernel, resolve kernel) */
     int32_t drain_chunk;      /* vgs_drain_batch: pods per chunk of the batch-scale drain, 1..64 (0 = default 64); -1 = the
                                * per-pod chain (one pass over the whole snapshot per pod) */
-    int32_t reserved[3];
+    int32_t alloc_pad_kb;     /* layout experiments: this many KB between the request staging block and the bit tables inside the
+                               * allocation that holds the score path's small arrays (0) */
+    int32_t reserved[2];
 } vgs_tuning;
 void vgs_tuning_defaults(vgs_tuning *out);
 

@@ -898,6 +898,57 @@ def test_drain_chunked_equals_per_pod_chain(built, cfg, n, p, chunk):
     assert np.array_equal(more.score.view(np.uint32), scores2.view(np.uint32)) and np.array_equal(more.picks, picks2)
 
 
+@pytest.mark.parametrize("pods_of", ["mixed", "multi"])
+def test_drain_chunked_wide_nodes(built, pods_of):
+    """nodes with 12 and with ragged device counts (the 12-wide tiles): chunked drain == sequential oracle Filters"""
+    n, p = 1500, 260
+    snap = v.workload.make_snapshot(n, seed=991, dmax=12, count=6)
+    rng = np.random.default_rng(5)
+    snap.ndev[:] = rng.integers(5, 13, n)
+    for f in range(8):
+        snap.planes[f][np.arange(12)[None, :] >= snap.ndev[:, None]] = 0
+    batch = (v.workload.pods_mixed if pods_of == "mixed" else v.workload.pods_multi)(p, 77)
+    rows, scores, counts, picks, planes = _oracle_drain(snap, batch)
+    with v.Context(max_nodes=n, max_devices=12, max_pods=p, max_reqs=batch.n_reqs, max_picks=int(batch.nums.sum())) as ctx:
+        ctx.upload(snap)
+        got = ctx.drain(batch)
+        plan = ctx.plan()
+        after, _ = ctx.download_snapshot()
+    assert plan.drain_chunks == -(-p // 64)
+    assert np.array_equal(got.best_row, rows) and np.array_equal(got.fit_count, counts)
+    assert np.array_equal(got.score.view(np.uint32), scores.view(np.uint32)) and np.array_equal(got.picks, picks)
+    assert np.array_equal(after, planes)
+
+
+@pytest.mark.parametrize("cfg,p", [("cfg3", 4096), ("cfg4", 1024)])
+def test_drain_full_size(built, cfg, p):
+    """the drain at BASELINE's node count: the chunked path and the per-pod chain against each other for every pod,
+    and against sequential oracle Filters for the first 160 pods (two and a half chunks: carried rows included)"""
+    snap, batch = v.workload.make_config(cfg, 100_000, p)
+    out = {}
+    for chunk in (0, -1):
+        with v.Context(max_nodes=snap.n_nodes, max_pods=p, max_reqs=batch.n_reqs, max_picks=int(batch.nums.sum()),
+                       tuning={"drain_chunk": chunk}) as ctx:
+            ctx.upload(snap)
+            out[chunk] = ctx.drain(batch)
+            if chunk == 0:
+                plan = ctx.plan()
+                after, _ = ctx.download_snapshot()
+            else:
+                after_chain, _ = ctx.download_snapshot()
+    a, b = out[0], out[-1]
+    assert plan.drain_chunks == p // 64
+    assert np.array_equal(a.best_row, b.best_row) and np.array_equal(a.fit_count, b.fit_count)
+    assert np.array_equal(a.score.view(np.uint32), b.score.view(np.uint32)) and np.array_equal(a.picks, b.picks)
+    assert np.array_equal(after, after_chain)
+    head = batch.select(list(range(160)))
+    rows, scores, counts, picks, _ = _oracle_drain(snap, head)
+    assert np.array_equal(a.best_row[:160], rows) and np.array_equal(a.fit_count[:160], counts)
+    assert np.array_equal(a.score[:160].view(np.uint32), scores.view(np.uint32))
+    assert np.array_equal(a.picks[:len(picks)], picks)
+    assert (a.best_row >= 0).sum() > 0.9 * p
+
+
 def test_drain_candidate_list_runs_dry(built):
     """identical pods on nodes that take exactly one of them: inside a chunk every candidate of a pod's list is
     consumed by the pods before it, and no touched row fits any more -- the commit kernel has to scan the walk
