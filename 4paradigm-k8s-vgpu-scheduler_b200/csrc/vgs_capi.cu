@@ -124,13 +124,13 @@ struct vgs_ctx {
 
     // the pod classes of one batch are independent: their kernel chains run on side streams
     // forked from / joined to `st` with events
-    cudaStream_t side[2] = {};
+    cudaStream_t side[2] = {}, side_sc[2] = {};
     // a pod batch that arrives while an asynchronous snapshot upload is still crossing PCIe goes up (and has its
     // bit tables built) on this stream, beside the copy; the score pass joins the two
     cudaStream_t st_pods = nullptr;
     cudaEvent_t ev_idle = nullptr, ev_pods = nullptr; // `st` as it stood before the upload was queued / pod work done
     bool pods_on_side = false;
-    cudaEvent_t ev_fork = nullptr, ev_join[2] = {}, ev_ns[2] = {};
+    cudaEvent_t ev_fork = nullptr, ev_join[2] = {}, ev_ns[2] = {}, ev_sc[2] = {};
     cudaEvent_t ev[EV_N] = {};
     bool ev_set[EV_N] = {};
     int ev_alias[EV_N] = {};  // which recorded event stands for this boundary (see rec)
@@ -270,8 +270,10 @@ void free_all(vgs_ctx *c) {
         if (c->ev[i]) cudaEventDestroy(c->ev[i]);
     for (int k = 0; k < 2; k++) {
         if (c->side[k]) cudaStreamDestroy(c->side[k]);
+        if (c->side_sc[k]) cudaStreamDestroy(c->side_sc[k]);
         if (c->ev_join[k]) cudaEventDestroy(c->ev_join[k]);
         if (c->ev_ns[k]) cudaEventDestroy(c->ev_ns[k]);
+        if (c->ev_sc[k]) cudaEventDestroy(c->ev_sc[k]);
     }
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     if (c->st_pods) cudaStreamDestroy(c->st_pods);
@@ -348,8 +350,10 @@ int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
     CUI(cudaEventCreateWithFlags(&c->ev_pods, cudaEventDisableTiming));
     for (int k = 0; k < 2; k++) {
         CUI(cudaStreamCreateWithFlags(&c->side[k], cudaStreamNonBlocking));
+        CUI(cudaStreamCreateWithFlags(&c->side_sc[k], cudaStreamNonBlocking));
         CUI(cudaEventCreateWithFlags(&c->ev_join[k], cudaEventDisableTiming));
         CUI(cudaEventCreateWithFlags(&c->ev_ns[k], cudaEventDisableTiming));
+        CUI(cudaEventCreateWithFlags(&c->ev_sc[k], cudaEventDisableTiming));
     }
     const size_t cells = (size_t)cfg->max_nodes * cfg->max_devices;
     for (int f = 0; f < VGS_NUM_PLANES; f++) CUI(cudaMalloc(&c->d_raw[f], cells * sizeof(int32_t)));
@@ -978,14 +982,25 @@ static int score_locked(vgs_ctx *c) {
         c->plan.dict_full = df;
         c->plan.cls[0].pods = c->nA, c->plan.cls[1].pods = c->nB, c->plan.cls[2].pods = c->nC, c->plan.cls[3].pods = c->nG;
     }
+    // Node-sliced scouts pay for classes of up to ~160 pod words and only when every sliced class of the batch uses
+    // them (measured at 100k-125k nodes: 2 x 64 words 0.402 -> 0.369 ms per step; 385 + 128 words 0.948 -> 0.989 with
+    // both, 0.966 with the smaller class alone; one class of two on cfg3 0.43-0.47): a node-sliced word costs three
+    // times a pod-sliced one, the cold start it avoids does not grow with the words.  Bit 4 lifts the limit.
+    vgs_tuning tune_k = c->tune;
+    if (!(tune_k.scouts_node_sliced & 16)) {
+        const int32_t kScoutNsMaxWords = 160;
+        const bool a_sl = c->nA && sliced && c->slice_on[0], b_sl = c->nB && sliced && c->slice_on[1];
+        if ((a_sl && (c->nA + 31) / 32 > kScoutNsMaxWords) || (b_sl && (c->nB + 31) / 32 > kScoutNsMaxWords))
+            tune_k.scouts_node_sliced &= ~3;
+    }
     for (int turn = 0; turn < 2; turn++) {
     const bool doA = (turn == 0) != (order_env == 1);
     if (doA) {
     if (c->nA) {
         if (sliced && c->slice_on[0]) {
             c->plan.cls[0].kernel = VGS_KERNEL_SLICED;
-            CU(launch_score_sliced(1, c->cfg.device, a, c->tab[0], c->n_types_used, c->d_status, sA, c->tune,
-                                   &c->plan.cls[0], fork ? c->st : nullptr, c->ev_ns[0]));
+            CU(launch_score_sliced(1, c->cfg.device, a, c->tab[0], c->n_types_used, c->d_status, sA, tune_k,
+                                   &c->plan.cls[0], fork ? c->st : nullptr, c->ev_ns[0], c->ev_sc[0], fork ? c->side_sc[0] : nullptr));
             c->launches += c->plan.cls[0].launches;
         } else {
             c->plan.cls[0].kernel = VGS_KERNEL_PAIR, c->plan.cls[0].launches = c->n_tiles ? 1 : 0;
@@ -999,8 +1014,8 @@ static int score_locked(vgs_ctx *c) {
     if (c->nB) {
         if (sliced && c->slice_on[1]) {
             c->plan.cls[1].kernel = VGS_KERNEL_SLICED;
-            CU(launch_score_sliced(2, c->cfg.device, a, c->tab[1], c->n_types_used, c->d_status, sB, c->tune,
-                                   &c->plan.cls[1], fork ? c->st : nullptr, c->ev_ns[1]));
+            CU(launch_score_sliced(2, c->cfg.device, a, c->tab[1], c->n_types_used, c->d_status, sB, tune_k,
+                                   &c->plan.cls[1], fork ? c->st : nullptr, c->ev_ns[1], c->ev_sc[1], fork ? c->side_sc[1] : nullptr));
             c->launches += c->plan.cls[1].launches;
         } else {
             c->plan.cls[1].kernel = VGS_KERNEL_PAIR, c->plan.cls[1].launches = c->n_tiles ? 1 : 0;
@@ -1477,6 +1492,7 @@ void vgs_tuning_defaults(vgs_tuning *t) {
     t->max_ctas = 0;
     t->filter_one_launch = 1;
     t->drain_chunk = 0;
+    t->scouts_node_sliced = 11;
 }
 
 int vgs_last_plan(vgs_ctx *c, vgs_plan *out) {

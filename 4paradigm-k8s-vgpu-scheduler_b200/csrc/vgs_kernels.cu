@@ -1104,7 +1104,7 @@ __global__ void __launch_bounds__(128)
 // ------------------------------------------------------------------------------------
 template <int NUMS, bool VERIFY>
 __global__ void __launch_bounds__(128)
-    k1_score_nodesliced(int32_t n_tiles, int32_t n_nodes, int32_t row_base, SliceTab tb, int32_t word0,
+    k1_score_nodesliced(int32_t n_virtual, int32_t tile_mul, int32_t n_nodes, int32_t row_base, SliceTab tb, int32_t word0,
                         unsigned long long *__restrict__ keys, int32_t *__restrict__ counts,
                         uint32_t *__restrict__ vfit, float *__restrict__ vscore, int32_t vwords) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -1121,8 +1121,9 @@ __global__ void __launch_bounds__(128)
     unsigned long long acckey = 0ull; // lane k: pod k of the word, over all this CTA's tiles
     int32_t acccnt = 0;
 
-    for (int tile = (int)blockIdx.x * (int)(blockDim.x >> 5) + warp; tile < n_tiles;
-         tile += (int)gridDim.x * (int)(blockDim.x >> 5)) {
+    // tiles v * tile_mul, v < n_virtual (tile_mul = 1: every tile; the scout stride: the scout tiles of a pod-sliced class)
+    for (int v = (int)blockIdx.x * (int)(blockDim.x >> 5) + warp; v < n_virtual; v += (int)gridDim.x * (int)(blockDim.x >> 5)) {
+        const int tile = v * tile_mul;
         const int row = tile * kWarp + lane;
         const uint4 *dv = tb.dinfo + (size_t)row * 8;
         uint4 d[8];
@@ -1634,7 +1635,7 @@ static cudaError_t allow_big_smem(K kernel, int dev) {
 template <int NUMS>
 static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &tb_in, int n_types, uint32_t *status,
                                    cudaStream_t st, const vgs_tuning &tune, vgs_class_plan *plan, cudaStream_t st_ns,
-                                   cudaEvent_t ev_ns) {
+                                   cudaEvent_t ev_ns, cudaEvent_t ev_sc, cudaStream_t st_sc) {
     const int sms = sm_count(dev);
     cudaError_t e;
     SliceTab tb = tb_in;
@@ -1673,6 +1674,22 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
     plan->words_node_sliced = ns_words;
     plan->tables_in_smem = W_main > 0 ? (tabsmem ? 1 : 0) : 0;
 
+    // every scout-th tile is walked ahead of the main pass: about a hundred scout tiles (measured
+    // optimum on 100k nodes: stride 24-48), vgs_tuning.scout_stride overrides
+    int scout_stride = tune.scout_stride >= 2 ? tune.scout_stride : a.n_tiles / 96;
+    if (scout_stride < 4 && tune.scout_stride < 2) scout_stride = 4;
+    if (scout_stride > 32 && tune.scout_stride < 2) scout_stride = 32;
+    // who walks them: the node-sliced kernel (default) or a cold pod-sliced launch
+    // (bit 0: the Nums 1 class, bit 1: the Nums 2 class, bit 2: in order on the class's own stream)
+    // (the caller clears the bits for batches with a class of more than kScoutNsMaxWords words: see there)
+    const bool scouts_ns = ((tune.scouts_node_sliced >> (NUMS - 1)) & 1) != 0 && W_main > 0 && a.n_tiles >= 256;
+    // (bit 3: on a stream of the class's own, beside sort / classify; else bit 2 clear: on st_ns)
+    cudaStream_t sc_stream = st;
+    if (scouts_ns && ev_ns && ev_sc) {
+        if ((tune.scouts_node_sliced & 8) && st_sc && st_sc != st) sc_stream = st_sc;
+        else if (!(tune.scouts_node_sliced & 4) && st_ns != st) sc_stream = st_ns;
+    }
+
     // K1p: table rows + candidate scores per device, distinct scores -> classes
     const int nthreads = a.n_tiles * kWarp;
     if (W_main > 0) {
@@ -1680,9 +1697,33 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
         k1p_collect<NUMS><<<(nthreads + 127) / 128, 128, 0, st>>>(a.walk, a.n_tiles, tb, status, true);
         // the node-sliced words need the records only (not the score classes): they can start now, on
         // another stream, instead of queueing behind the class's sort / classify / scout / main launches
-        if (ns_words > 0 && st_ns != st && ev_ns) {
+        if (ns_words > 0 && st_ns != st && ev_ns && !(scouts_ns && sc_stream == st_ns)) { // (else the same wait is queued with the scouts)
             if ((e = cudaEventRecord(ev_ns, st)) != cudaSuccess) return e;
             if ((e = cudaStreamWaitEvent(st_ns, ev_ns, 0)) != cudaSuccess) return e;
+        }
+        if (scouts_ns) {
+            // Scouts: the bests of every scout_stride-th tile, which the main pass starts from.  They need K1p's
+            // records only, so the node-sliced kernel walks those tiles for ALL the class's words while sort and
+            // classify run (a pod-sliced scout launch starts cold -- every node improves for most pods -- and
+            // took 84 us for 3 % of the nodes; this takes ~15)
+            if (sc_stream != st) {
+                if ((e = cudaEventRecord(ev_ns, st)) != cudaSuccess) return e;
+                if ((e = cudaStreamWaitEvent(sc_stream, ev_ns, 0)) != cudaSuccess) return e;
+            }
+            SliceTab ts = tb; // (tb.W / n_pods = the pod-sliced words)
+            const int rows_sc = VGS_MAX_TYPES - ts.row_shift + (ts.km + 1) + (ts.kp + 1) + 4 * (ts.kc + 1);
+            const int scsmem = rows_sc * 4;
+            const int n_scout = (a.n_tiles + scout_stride - 1) / scout_stride;
+            auto gos = [&](auto kernel) -> cudaError_t {
+                if (scsmem > 48 * 1024 && (e = allow_big_smem(kernel, dev)) != cudaSuccess) return e;
+                kernel<<<dim3((unsigned)((n_scout + 3) / 4), (unsigned)W_main), 128, scsmem, sc_stream>>>(
+                    n_scout, scout_stride, a.n_nodes, a.row_base, ts, 0, a.keys, a.counts, a.vfit, a.vscore, a.vwords);
+                return cudaGetLastError();
+            };
+            e = a.vfit ? gos(k1_score_nodesliced<NUMS, true>) : gos(k1_score_nodesliced<NUMS, false>);
+            if (e != cudaSuccess) return e;
+            if (sc_stream != st && (e = cudaEventRecord(ev_sc, sc_stream)) != cudaSuccess) return e;
+            plan->launches += 1;
         }
         k1p_sort<<<1, 1024, 0, st>>>(tb);
         k1p_classify<NUMS><<<(nthreads + 127) / 128, 128, 0, st>>>(a.n_tiles, tb);
@@ -1693,11 +1734,7 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
     }
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
 
-    // every scout-th tile is walked by the scout launch: about a hundred scout tiles (measured
-    // optimum on 100k nodes: stride 24-48), vgs_tuning.scout_stride overrides
-    int scout = tune.scout_stride >= 2 ? tune.scout_stride : a.n_tiles / 96;
-    if (scout < 4 && tune.scout_stride < 2) scout = 4;
-    if (scout > 32 && tune.scout_stride < 2) scout = 32;
+    const int scout = scout_stride;
     // cfg3: 1 -> 0.459 ms, 2 -> 0.449, 4 -> 0.472, 8 -> 0.477 (set-up per CTA)
     int scout_sub_max = tune.scout_split;
     if (scout_sub_max != 1 && scout_sub_max != 2 && scout_sub_max != 4 && scout_sub_max != 8) scout_sub_max = 2;
@@ -1733,7 +1770,11 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
         if (a.n_tiles < 256) return launch(a.n_tiles, -1, 2, &plan->tiles_per_cta_main); // small snapshot (< 8k nodes): one launch
         const int scouts = (a.n_tiles + scout - 1) / scout;
         plan->scout_stride = scout;
-        if ((e = launch(scouts, 0, 1, &plan->tiles_per_cta_scout)) != cudaSuccess) return e;
+        if (scouts_ns) { // the scout tiles were walked by the node-sliced kernel (above): the main pass inherits its bests
+            if (sc_stream != st && (e = cudaStreamWaitEvent(st, ev_sc, 0)) != cudaSuccess) return e;
+        } else if ((e = launch(scouts, 0, 1, &plan->tiles_per_cta_scout)) != cudaSuccess) {
+            return e;
+        }
         return launch(a.n_tiles - scouts, 1, 2, &plan->tiles_per_cta_main);
     };
     if (W_main > 0) {
@@ -1757,7 +1798,7 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
             if (gx > need) gx = need;
             if (gx < 1) gx = 1;
             cudaStream_t sn = (W_main > 0 && st_ns != st && ev_ns) ? st_ns : st;
-            kernel<<<dim3((unsigned)gx, (unsigned)ns_words), 128, nsmem, sn>>>(a.n_tiles, a.n_nodes, a.row_base, tn, W_main,
+            kernel<<<dim3((unsigned)gx, (unsigned)ns_words), 128, nsmem, sn>>>(a.n_tiles, 1, a.n_nodes, a.row_base, tn, W_main,
                                                                              a.keys, a.counts, a.vfit, a.vscore, a.vwords);
             plan->launches += 1;
             return cudaGetLastError();
@@ -1770,12 +1811,12 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
 
 cudaError_t launch_score_sliced(int nums, int dev, const ScoreArgs &a, const SliceTab &tb, int n_types,
                                 uint32_t *status, cudaStream_t st, const vgs_tuning &tune, vgs_class_plan *plan,
-                                cudaStream_t st_ns, cudaEvent_t ev_ns) {
+                                cudaStream_t st_ns, cudaEvent_t ev_ns, cudaEvent_t ev_sc, cudaStream_t st_sc) {
     plan->launches = 0;
     if (tb.n_pods <= 0 || a.n_tiles <= 0) return cudaSuccess;
     if (!st_ns) st_ns = st;
-    return nums == 1 ? launch_sliced_t<1>(dev, a, tb, n_types, status, st, tune, plan, st_ns, ev_ns)
-                     : launch_sliced_t<2>(dev, a, tb, n_types, status, st, tune, plan, st_ns, ev_ns);
+    return nums == 1 ? launch_sliced_t<1>(dev, a, tb, n_types, status, st, tune, plan, st_ns, ev_ns, ev_sc, st_sc)
+                     : launch_sliced_t<2>(dev, a, tb, n_types, status, st, tune, plan, st_ns, ev_ns, ev_sc, st_sc);
 }
 
 // K2x: merge of whole exchange blocks.  Every shard has resolved its OWN best node per pod (K3 with

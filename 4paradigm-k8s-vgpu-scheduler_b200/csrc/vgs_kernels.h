@@ -103,9 +103,11 @@ cudaError_t launch_slice_tables(const SliceTab &tb, const DevReq *dreq_class, cu
 // snapshot; *plan receives the split of the class's words, the launch geometry and the number of kernels launched)
 cudaError_t launch_score_sliced(int nums, int dev, const ScoreArgs &a, const SliceTab &tb, int n_types,
                                 uint32_t *status, cudaStream_t st, const vgs_tuning &tune, vgs_class_plan *plan,
-                                cudaStream_t st_ns = nullptr, cudaEvent_t ev_ns = nullptr);
+                                cudaStream_t st_ns = nullptr, cudaEvent_t ev_ns = nullptr, cudaEvent_t ev_sc = nullptr,
+                                cudaStream_t st_sc = nullptr);
 // (st_ns / ev_ns: optional second stream + event on which the node-sliced words of the class may run as soon
-// as K1p's records exist; the caller joins st_ns with whatever consumes the keys)
+// as K1p's records exist; the caller joins st_ns with whatever consumes the keys.  ev_sc: event for "the node-sliced
+// scout launch on st_ns is done", which the class's main launch on st waits for)
 cudaError_t launch_merge(const unsigned long long *gk, const int32_t *gc, int32_t n_shards,
                          int32_t stride, int32_t cstride, int32_t n_pods, unsigned long long *keys,
                          int32_t *counts, cudaStream_t st);

@@ -102,7 +102,13 @@ typedef struct {
                                * per-pod chain (one pass over the whole snapshot per pod) */
     int32_t alloc_pad_kb;     /* layout experiments: this many KB between the request staging block and the bit tables inside the
                                * allocation that holds the score path's small arrays (0) */
-    int32_t reserved[2];
+    int32_t scouts_node_sliced; /* who walks the scout tiles of a pod-sliced class (the bests the main launch starts from):
+                                 * bit 0 / bit 1 = the node-sliced kernel for the Nums 1 / Nums 2 class (else a cold
+                                 * pod-sliced launch after sort / classify); bit 3 = on a stream of the class's own beside
+                                 * sort / classify, bit 2 = in order on the class's stream (neither: on the stream of the
+                                 * node-sliced words); a batch with a sliced class of more than 160 pod words keeps the
+                                 * pod-sliced launches unless bit 4 is set.  Default 11 */
+    int32_t reserved[1];
 } vgs_tuning;
 void vgs_tuning_defaults(vgs_tuning *out);
 

@@ -404,8 +404,12 @@ def test_sliced_word_split_between_kernels(built, node_words, tabsmem, scout):
     pod-sliced warps (lane = pod word); vgs_tuning.node_words moves the split, tables_in_smem / scout_stride
     the pod-sliced kernel's variant and launch geometry.  Same answers wherever a word runs -- and
     vgs_last_plan shows that the knobs really moved the split."""
+    # (the scout tiles: a cold pod-sliced launch in the two cases that steer its geometry, the node-sliced kernel --
+    # the default -- in the others)
     tune = {"node_words": node_words, "slice_min": 64, "slice_small": 64, "tables_in_smem": tabsmem,
             "scout_stride": scout, "scout_split": 4 if scout == 17 else 2}
+    if scout in (5, 17):
+        tune["scouts_node_sliced"] = 0
     rng = np.random.default_rng(77)
     snap, _ = v.workload.make_config("cfg3", 9000, 1)
     def pods_of(n1, n2):
@@ -444,7 +448,10 @@ def test_sliced_word_split_between_kernels(built, node_words, tabsmem, scout):
                     assert cp.tables_in_smem == tabsmem
                 if scout >= 2:  # 9000 nodes = 282 tiles: scouts + main launch
                     assert cp.scout_stride == scout and cp.tiles_per_cta_main >= 2
-                    assert cp.scout_split in (1, 2, 4)
+                    if tune.get("scouts_node_sliced") == 0:
+                        assert cp.scout_split in (1, 2, 4) and cp.tiles_per_cta_scout >= 1
+                    else:
+                        assert cp.scout_split == 0 and cp.tiles_per_cta_scout == 0  # no pod-sliced scout launch
 
 
 def test_sliced_long_scout_span_keeps_rows(built):
@@ -457,7 +464,7 @@ def test_sliced_long_scout_span_keeps_rows(built):
             for _ in range(2048)]
     batch = v.PodBatch.from_pods(pods)
     # 4375 tiles, stride 32 -> 137 scout tiles on 2 CTAs = 69 tiles each, 2177 tiles (69664 nodes) apart
-    tune = {"scout_stride": 32, "scout_split": 1, "slice_min": 64, "max_ctas": 2}
+    tune = {"scout_stride": 32, "scout_split": 1, "slice_min": 64, "max_ctas": 2, "scouts_node_sliced": 0}
     with v.Context(max_nodes=snap.n_nodes, max_pods=batch.n_pods, tuning=tune) as ctx:
         ctx.upload(snap)
         got = ctx.score(batch)

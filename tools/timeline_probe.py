@@ -3,12 +3,14 @@ every kernel between the K0 launch and K3's end."""
 import json, os, sys, tempfile
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
-import vgpu_b200 as v
+import importlib
+v = importlib.import_module("4paradigm-k8s-vgpu-scheduler_b200")
 cfg = sys.argv[1] if len(sys.argv) > 1 else "cfg3"
+tuning = dict((k, int(x)) for k, x in (kv.split("=") for kv in sys.argv[2].split(","))) if len(sys.argv) > 2 else None
 snap, batch = v.workload.make_config(cfg)
 pods, reqs = v.capi.pack_batch(batch, snap.type_names)
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
-with v.Context(max_nodes=snap.n_nodes, max_pods=len(pods), max_reqs=max(len(reqs), len(pods)), max_picks=int(reqs["nums"].sum())) as ctx:
+with v.Context(max_nodes=snap.n_nodes, max_pods=len(pods), max_reqs=max(len(reqs), len(pods)), max_picks=int(reqs["nums"].sum()), tuning=tuning) as ctx:
     ctx.upload(snap); ctx.pods_upload(pods, reqs)
     for _ in range(5):
         ctx.refresh(); ctx.score_resident(); ctx.resolve_resident(); ctx.sync()
