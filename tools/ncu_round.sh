@@ -16,9 +16,11 @@ ncu --metrics $M --clock-control none -c 80 --csv --log-file gpurun_out/${T}_cfg
     python bench.py --config cfg4 --steps 1 --warmup 3 --no-cpu --no-e2e --no-hbm-leg --no-configs > gpurun_out/${T}_ncu3.log 2>&1
 ncu --set full --import-source on --clock-control none -k regex:k1_score_walk -s 1 -c 1 -o gpurun_out/${T}_walk \
     python bench.py --config cfg4 --steps 1 --warmup 3 --no-cpu --no-e2e --no-hbm-leg --no-configs > gpurun_out/${T}_ncu4.log 2>&1
-# 4. --set full of the two sliced main launches (class A: 2nd k1_score_sliced<1 launch of a step; class B likewise)
-ncu --set full --import-source on --clock-control none -k regex:k1_score_sliced -s 12 -c 4 -o gpurun_out/${T}_sliced \
+# 4. --set full of the sliced launches of the last step: the two pod-sliced mains and the node-sliced launches (scouts, odd words)
+ncu --set full --import-source on --clock-control none -k regex:k1_score_sliced -s 6 -c 2 -o gpurun_out/${T}_sliced \
     python bench.py --steps 1 --warmup 3 --no-cpu --no-e2e --no-hbm-leg --no-configs > gpurun_out/${T}_ncu5.log 2>&1
+ncu --set full --import-source on --clock-control none -k regex:k1_score_nodesliced -s 9 -c 3 -o gpurun_out/${T}_nodesliced \
+    python bench.py --steps 1 --warmup 3 --no-cpu --no-e2e --no-hbm-leg --no-configs > gpurun_out/${T}_ncu5b.log 2>&1
 ls -la gpurun_out/${T}_*
 # 5. the batch-scale drain: launch list of a 1024-pod drain at 100k nodes, --set full of one launch of each kernel
 python tools/drain_probe.py cfg3 100000 1024 0 > gpurun_out/${T}_drain_plain.log 2>&1 || exit 1
