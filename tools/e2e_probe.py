@@ -1,7 +1,8 @@
 """where the end-to-end step (bench.py `e2e`) spends its wall clock: per call and per device phase"""
 import sys, time, numpy as np, torch
 import os; sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-import vgpu_b200 as v
+import importlib
+v = importlib.import_module("4paradigm-k8s-vgpu-scheduler_b200")
 snap, batch = v.workload.make_config("cfg3")
 pods, reqs = v.capi.pack_batch(batch, snap.type_names)
 ctx = v.Context(max_nodes=snap.n_nodes, max_pods=4096, max_reqs=4096, max_picks=8192)
