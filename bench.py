@@ -245,6 +245,28 @@ def latest_k1_profile():
         return None
 
 
+def pin_to_gpu_numa(torch, local):
+    """Run this rank on the cores next to its GPU, so that the pinned planes it allocates (first touch) and the packing
+    of its batches sit on that GPU's NUMA node: with N ranks uploading 26 MB each per e2e step, planes on a remote node
+    go over the inter-socket link.  Best effort: returns the node, or None when the topology cannot be read."""
+    try:
+        pr = torch.cuda.get_device_properties(local)
+        bus = "%04x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        base = "/sys/bus/pci/devices/" + bus
+        cpus = set()
+        for part in open(base + "/local_cpulist").read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        node = int(open(base + "/numa_node").read().strip())
+        return node if node >= 0 else None  # (-1: a single-node host, e.g. the VMs this was measured on -- nothing to gain)
+    except Exception:
+        return None
+
+
 def sampled_check(v, np, snap_whole, batch, results, picks, n_sample=48):
     """not timed: a sample of pods re-scored by the CPU oracle over ALL nodes; bit-exact or not"""
     import oracle
@@ -381,6 +403,7 @@ def main():
         raise SystemExit("bench.py needs a CUDA GPU: the scoring path has no CPU fallback")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa = pin_to_gpu_numa(torch, local) if world > 1 else None  # host buffers next to this rank's GPU (e2e legs)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     v.load_library()
@@ -437,6 +460,8 @@ def main():
         e2e = {"value": P * n_total / sec, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * sec, "steps": n_e2e,
                "api": "vgs_snapshot_upload_async + vgs_pods_upload/score/resolve/results_download (host buffers)"}
+        if numa is not None:
+            e2e["host_numa_node"] = numa  # rank 0's; every rank runs on the cores next to its own GPU
 
         # the production path (scheduler.go:280-297 folded into deltas): the snapshot stays resident, each step
         # ships the usage changes of the previous step's placements + the pod batch, and reads the results back
