@@ -956,6 +956,43 @@ def test_drain_full_size(built, cfg, p):
     assert (a.best_row >= 0).sum() > 0.9 * p
 
 
+@pytest.mark.parametrize("chunk", [0, 7, -1])
+def test_drain_hand_derived_sequence(built, chunk):
+    """A drain worked out by hand from score.go / scheduler.go, no oracle involved.  11 nodes of two cards (Count 2,
+    1000 MB, 100 cores, one numa, one type); node 0 has card 0 in use once (300 MB, 20 cores); 40 identical pods
+    ask for one card with 400 MB and 30 cores.  Per Filter the cards are sorted ascending by Count-Used
+    (score.go:45-50, stable for <= 12) and walked from the END (:92), so the emptier card is met first, and
+    score = Count/(Count-Used) + (2 - 1) with Used as it was before the take (:168-170,180).  An empty node gives
+    2/2 + 1 = 2 through card 1; so does node 0 (card 1 is its emptier one).  Ties go to the highest row (our canonical
+    rule), so node 10 takes the first pod on card 1; then its card 0 is the emptier one (2 again, slot 0); then both
+    cards have one slot left, the stable sort keeps registration order and the walk meets card 1 first: 2/1 + 1 = 3,
+    then card 0 likewise: 3.  Node 10 is full (Used = Count on both cards) and the next four pods do the same to
+    node 9, and so on down to node 1.  Nodes that fit pod 4k+j: rows 0..10-k."""
+    n = 11
+    planes = np.zeros((8, n, 2), np.int32)
+    USED, COUNT, USEDMEM, TOTALMEM, USEDCORES, TOTALCORE = 0, 1, 2, 3, 4, 5
+    planes[COUNT], planes[TOTALMEM], planes[TOTALCORE] = 2, 1000, 100
+    planes[USED, 0, 0], planes[USEDMEM, 0, 0], planes[USEDCORES, 0, 0] = 1, 300, 20
+    snap = v.Snapshot(planes, np.full(n, 2, np.int32), ["NVIDIA-A100"])
+    batch = v.PodBatch.from_pods([{"containers": [[(1, 400, 101, 30, "NVIDIA")]]} for _ in range(40)])
+    want_rows = np.repeat(np.arange(10, 0, -1), 4).astype(np.int32)
+    want_scores = np.tile(np.array([2.0, 2.0, 3.0, 3.0], np.float32), 10)
+    want_slots = np.tile(np.array([1, 0, 1, 0], np.int32), 10)
+    want_fit = np.repeat(np.arange(11, 1, -1), 4).astype(np.int32)
+    with v.Context(max_nodes=n, max_devices=2, max_pods=40, tuning={"drain_chunk": chunk}) as ctx:
+        ctx.upload(snap)
+        got = ctx.drain(batch)
+        after, _ = ctx.download_snapshot()
+        assert ctx.plan().drain_chunks == {0: 1, 7: 6, -1: 0}[chunk]
+    assert np.array_equal(got.best_row, want_rows)
+    assert np.array_equal(got.score, want_scores)
+    assert np.array_equal(got.fit_count, want_fit)
+    assert np.array_equal(got.picks, np.stack([want_slots, np.full(40, 400), np.full(40, 30)], axis=1))
+    end = planes.copy()
+    end[USED, 1:], end[USEDMEM, 1:], end[USEDCORES, 1:] = 2, 800, 60
+    assert np.array_equal(after, end)
+
+
 def test_drain_candidate_list_runs_dry(built):
     """identical pods on nodes that take exactly one of them: inside a chunk every candidate of a pod's list is
     consumed by the pods before it, and no touched row fits any more -- the commit kernel has to scan the walk
