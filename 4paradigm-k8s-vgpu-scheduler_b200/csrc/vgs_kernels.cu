@@ -653,6 +653,51 @@ __global__ void __launch_bounds__(128)
     }
 }
 
+// The Nums 1 class does not need the node as a whole: thread = DEVICE.  Eight times the threads of k1p_collect<1>,
+// an eighth of its serial chain of searches and set probes each -- that kernel was latency bound at a third of the warp
+// slots (thread = node leaves 21 warps per SM at 100k nodes) and heads the chain the cfg3 step waits for.
+__global__ void __launch_bounds__(256)
+    k1p_collect1_dev(const int4 *__restrict__ walk, int32_t n_tiles, SliceTab tb, uint32_t *__restrict__ status,
+                     bool want_scores) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int node = t >> 3, j = t & 7;
+    if (node >= n_tiles * kWarp) return;
+    const int tile = node >> 5, lane = node & 31;
+    const int32_t *tw = reinterpret_cast<const int32_t *>(walk + (size_t)tile * kTileInt4);
+    auto word = [&](int w) { return __ldg(&tw[((w * 2 + (j >> 2)) * kWarp + lane) * 4 + (j & 3)]); };
+    bool set_full = want_scores && (*reinterpret_cast<volatile uint32_t *>(status) & S_DICTFULL);
+    const uint32_t m = (uint32_t)word(W_META);
+    const int r_mem = VGS_MAX_TYPES - tb.row_shift, r_pct = r_mem + tb.km + 1, r_core = r_pct + tb.kp + 1;
+    SliceDev d;
+    if (m & (M_NOFREE | M_PAD)) { // Count <= Used (score.go:107) or not a device: never fits
+        d.r_type = d.r_mem = d.r_pct = d.r_core = (uint16_t)r_mem; // memle row 0 is all zero
+        d.a = 0u;
+        d.b = (uint32_t)kDict;
+    } else {
+        const int32_t fm = word(W_FREEMEM), fc = word(W_FREECORES), tm = word(W_TOTALMEM);
+        d.r_type = (uint16_t)(m & M_TYPE_MASK);
+        d.r_mem = (uint16_t)(r_mem + count_prefix(tb.memv, tb.km, [&](int32_t v) { return v <= fm; }));
+        d.r_pct = (uint16_t)(r_pct + count_prefix(tb.pctv, tb.kp, [&](int32_t v) { return pct_mem(tm, v) <= fm; }));
+        d.r_core = (uint16_t)(r_core + 4 * count_prefix(tb.corev, tb.kc, [&](int32_t v) { return v <= fc; }) +
+                              ((m & M_EXCL) ? 1 : 0) + ((m & M_FULL) ? 2 : 0));
+        d.a = (uint32_t)word(W_SCORE1);
+        d.b = (uint32_t)kDict;
+        if (want_scores) hset_insert(tb.hset, d.a, status, set_full);
+    }
+    reinterpret_cast<SliceDev *>(tb.dinfo)[(size_t)node * 8 + j] = d;
+}
+
+// ... and its classify: the class of the device's own score
+__device__ __forceinline__ uint32_t class_of(const uint32_t *__restrict__ gvals, int nv, uint32_t sb);
+__global__ void __launch_bounds__(256) k1p_classify1_dev(int32_t n_tiles, SliceTab tb) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_tiles * kWarp * 8) return;
+    const int nv = (int)__ldg(&tb.gvals[kDict]);
+    SliceDev *dv = reinterpret_cast<SliceDev *>(tb.dinfo) + t;
+    const SliceDev d = *dv;
+    if (d.r_type != d.r_mem || d.a) dv->b = d.a ? class_of(tb.gvals, nv, d.a) : (uint32_t)kDict;
+}
+
 // one CTA: compact the distinct scores out of the hash set, sort them, keep the kSliceDict
 // largest (ascending) in gvals, their count in gvals[kSliceDict]
 __global__ void __launch_bounds__(1024) k1p_sort(SliceTab tb) {
@@ -1694,7 +1739,8 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
     const int nthreads = a.n_tiles * kWarp;
     if (W_main > 0) {
         if ((e = cudaMemsetAsync(tb.hset, 0, kSliceHash * sizeof(uint32_t), st)) != cudaSuccess) return e;
-        k1p_collect<NUMS><<<(nthreads + 127) / 128, 128, 0, st>>>(a.walk, a.n_tiles, tb, status, true);
+        if (NUMS == 1) k1p_collect1_dev<<<(nthreads * 8 + 255) / 256, 256, 0, st>>>(a.walk, a.n_tiles, tb, status, true);
+        else k1p_collect<NUMS><<<(nthreads + 127) / 128, 128, 0, st>>>(a.walk, a.n_tiles, tb, status, true);
         // the node-sliced words need the records only (not the score classes): they can start now, on
         // another stream, instead of queueing behind the class's sort / classify / scout / main launches
         if (ns_words > 0 && st_ns != st && ev_ns && !(scouts_ns && sc_stream == st_ns)) { // (else the same wait is queued with the scouts)
@@ -1726,10 +1772,12 @@ static cudaError_t launch_sliced_t(int dev, const ScoreArgs &a, const SliceTab &
             plan->launches += 1;
         }
         k1p_sort<<<1, 1024, 0, st>>>(tb);
-        k1p_classify<NUMS><<<(nthreads + 127) / 128, 128, 0, st>>>(a.n_tiles, tb);
+        if (NUMS == 1) k1p_classify1_dev<<<(nthreads * 8 + 255) / 256, 256, 0, st>>>(a.n_tiles, tb);
+        else k1p_classify<NUMS><<<(nthreads + 127) / 128, 128, 0, st>>>(a.n_tiles, tb);
         plan->launches += 3;
     } else { // a class of a few words: the node-sliced kernel needs the records only
-        k1p_collect<NUMS><<<(nthreads + 127) / 128, 128, 0, st>>>(a.walk, a.n_tiles, tb, status, false);
+        if (NUMS == 1) k1p_collect1_dev<<<(nthreads * 8 + 255) / 256, 256, 0, st>>>(a.walk, a.n_tiles, tb, status, false);
+        else k1p_collect<NUMS><<<(nthreads + 127) / 128, 128, 0, st>>>(a.walk, a.n_tiles, tb, status, false);
         plan->launches += 1;
     }
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
