@@ -774,6 +774,32 @@ def test_pinned_planes_take_the_zero_copy_upload(built):
         assert np.array_equal(planes, snap.planes)
 
 
+def test_async_uploads_of_snapshots_with_other_properties(built):
+    """asynchronous uploads one after another of snapshots that allow different things -- more types (other table
+    rows), a Totalmem the bit tables cannot take (per-pair kernels only) -- each scored right after it"""
+    import torch
+    n, p = 6001, 1400
+    snap_a, batch = v.workload.make_config("cfg3", n, p)
+    snap_b = v.workload.make_stress_snapshot(n)          # 48 types instead of a handful
+    snap_c = v.Snapshot(snap_a.planes.copy(), snap_a.ndev.copy(), snap_a.type_names)
+    snap_c.planes[3][11, 0] = 1 << 30                      # Totalmem beyond the sliced tables: per-pair kernels only
+    with v.Context(max_nodes=n, max_pods=p) as ctx:
+        for snap in (snap_a, snap_b, snap_a, snap_c, snap_a, snap_a):
+            want = oracle.score_packed(snap, batch)
+            pods, reqs = v.capi.pack_batch(batch, snap.type_names)
+            pin = torch.from_numpy(snap.planes.copy()).pin_memory()
+            pnd = torch.from_numpy(snap.ndev.copy()).pin_memory()
+            ctx.set_type_flags([v.capi.host_type_flags(t) for t in snap.type_names])
+            ctx.upload_ptrs(n, snap.dmax, [pin[f].data_ptr() for f in range(8)], pnd.data_ptr(), device=False, asynchronous=True)
+            ctx.pods_upload(pods, reqs)
+            ctx.score_resident()
+            ctx.resolve_resident()
+            r, pk = ctx.results_download()
+            assert np.array_equal(r["best_row"], want.best_row) and np.array_equal(r["fit_count"], want.fit_count)
+            assert np.array_equal(r["score"].view(np.uint32), want.score.view(np.uint32))
+            assert np.array_equal(np.stack([pk["slot"], pk["usedmem"], pk["usedcores"]], axis=1), want.picks)
+
+
 def test_async_snapshot_upload(built):
     """vgs_snapshot_upload_async returns with the copy queued; the next call that needs the snapshot waits
     for it and gets its range errors; results equal the blocking upload's, pass after pass"""
