@@ -45,7 +45,7 @@ class VgsTuning(C.Structure):
                 ("scout_stride", C.c_int32), ("scout_split", C.c_int32), ("class_order", C.c_int32),
                 ("zero_copy_upload", C.c_int32), ("general_legacy", C.c_int32), ("max_ctas", C.c_int32),
                 ("filter_one_launch", C.c_int32), ("drain_chunk", C.c_int32), ("alloc_pad_kb", C.c_int32),
-                ("scouts_node_sliced", C.c_int32), ("reserved", C.c_int32 * 1)]
+                ("scouts_node_sliced", C.c_int32), ("slice_min_nodes", C.c_int32)]
 
 
 class VgsConfig(C.Structure):

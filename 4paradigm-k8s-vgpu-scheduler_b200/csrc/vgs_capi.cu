@@ -698,6 +698,10 @@ static bool build_slice_class(vgs_ctx *c, int k, const DevReq *req, const DevReq
     // >= slice_min pods: always.  From slice_small pods upward when the pass is big enough for the
     // class set-up (tables, K1p) to pay: measured 100k nodes x 256 pods 0.224 -> 0.176 ms through the
     // node-sliced kernel, but 100k x 64 and 10k x 256 lose to the per-pair kernel.
+    // Small snapshots stay on the per-pair kernel whatever the class size.  Wall clock of the resident call, 4096 / 1024
+    // pods (tools/small_probe.py): 64-512 nodes 400 / 117 us sliced against 152 / 104 us per pair, 4096 nodes 422 / 127
+    // against 262 / 124, 8192 nodes 379 / 138 against 362 / 149.
+    if (c->n_nodes > 0 && c->n_nodes < c->tune.slice_min_nodes) return false;
     const bool big = n >= c->tune.slice_min;
     const bool mid = n >= c->tune.slice_small && (int64_t)n * c->n_nodes >= c->tune.slice_small_pairs;
     if (n < 1 || !(big || mid)) return false;
@@ -1493,6 +1497,7 @@ void vgs_tuning_defaults(vgs_tuning *t) {
     t->filter_one_launch = 1;
     t->drain_chunk = 0;
     t->scouts_node_sliced = 11;
+    t->slice_min_nodes = 6144;
 }
 
 int vgs_last_plan(vgs_ctx *c, vgs_plan *out) {

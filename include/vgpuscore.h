@@ -108,7 +108,8 @@ typedef struct {
                                  * sort / classify, bit 2 = in order on the class's stream (neither: on the stream of the
                                  * node-sliced words); a batch with a sliced class of more than 160 pod words keeps the
                                  * pod-sliced launches unless bit 4 is set.  Default 11 */
-    int32_t reserved[1];
+    int32_t slice_min_nodes;  /* ... and only on snapshots of at least this many nodes (6144): below, the classes' set-up (bit
+                               * tables, preparation kernels) costs more than the per-pair kernel's whole pass */
 } vgs_tuning;
 void vgs_tuning_defaults(vgs_tuning *out);
 

@@ -10,10 +10,13 @@ from helpers import assert_same, cambricon_cluster, check_kat, kat_inputs, load_
 
 pytestmark = pytest.mark.gpu
 K = load_kats()
-FORCE_SLICED = {"slice_min": 1, "slice_small": 1}  # vgs_tuning: every Nums 1 / Nums 2 class on the sliced kernels
+FORCE_SLICED = {"slice_min": 1, "slice_small": 1, "slice_min_nodes": 0}  # vgs_tuning: every Nums 1 / Nums 2 class on the sliced kernels
 
 
 def gpu_score(snap, batch, verify=True, **kw):
+    # (the small snapshots of these tests keep reaching the sliced kernels: production routes snapshots under 6144
+    # nodes to the per-pair kernel, test_small_snapshots_take_the_per_pair_kernel)
+    kw["tuning"] = dict({"slice_min_nodes": 0}, **(kw.get("tuning") or {}))
     with v.Context(max_nodes=max(snap.n_nodes, 1), max_devices=snap.dmax, max_pods=max(batch.n_pods, 1),
                    max_reqs=max(batch.n_reqs, batch.n_pods, 1), max_picks=max(int(batch.nums.sum()), batch.n_reqs, 1),
                    verify=verify, **kw) as ctx:
@@ -406,7 +409,7 @@ def test_sliced_word_split_between_kernels(built, node_words, tabsmem, scout):
     vgs_last_plan shows that the knobs really moved the split."""
     # (the scout tiles: a cold pod-sliced launch in the two cases that steer its geometry, the node-sliced kernel --
     # the default -- in the others)
-    tune = {"node_words": node_words, "slice_min": 64, "slice_small": 64, "tables_in_smem": tabsmem,
+    tune = {"node_words": node_words, "slice_min": 64, "slice_small": 64, "slice_min_nodes": 0, "tables_in_smem": tabsmem,
             "scout_stride": scout, "scout_split": 4 if scout == 17 else 2}
     if scout in (5, 17):
         tune["scouts_node_sliced"] = 0
@@ -454,6 +457,19 @@ def test_sliced_word_split_between_kernels(built, node_words, tabsmem, scout):
                         assert cp.scout_split == 0 and cp.tiles_per_cta_scout == 0  # no pod-sliced scout launch
 
 
+def test_small_snapshots_take_the_per_pair_kernel(built):
+    """default routing: a big class on a snapshot under vgs_tuning.slice_min_nodes runs on the per-pair kernel, on a
+    larger one on the sliced kernels -- same answers"""
+    for n, kernel in ((3000, v.capi.KERNEL_PAIR), (7000, v.capi.KERNEL_SLICED)):
+        snap, batch = v.workload.make_config("cfg3", n, 2600)  # both single-request classes above slice_min (512) pods
+        with v.Context(max_nodes=n, max_pods=2600) as ctx:
+            ctx.upload(snap)
+            got = ctx.score(batch)
+            plan = ctx.plan()
+        assert plan.cls[0].kernel == kernel and plan.cls[1].kernel == kernel, (n, plan.cls[0].kernel, plan.cls[1].kernel)
+        assert_same(got, oracle.score_packed(snap, batch), f"routing {n}")
+
+
 def test_sliced_long_scout_span_keeps_rows(built):
     """a scout CTA whose tiles lie far apart (large stride x many tiles per CTA, forced by many pod-word
     columns and a big stride) still names the right winner row: the per-pod row inside a CTA is kept as
@@ -496,7 +512,7 @@ def test_sliced_forced_random(built, dmax, seed):
     assert_same(got, oracle.score_faithful(snap, batch, full=True), f"sliced dmax={dmax} R1")
 
 
-@pytest.mark.parametrize("n,p,tune", [(3000, 700, None), (9500, 1300, None), (2000, 300, {"slice_min": 1, "slice_small": 1})])
+@pytest.mark.parametrize("n,p,tune", [(3000, 700, None), (9500, 1300, None), (2000, 300, {"slice_min": 1, "slice_small": 1, "slice_min_nodes": 0})])
 def test_stress_snapshot_many_score_values(built, n, p, tune):
     """the robustness workload: Count 1..32 per device, ragged nodes, 48 types mixed inside nodes, scores rising
     along the walk, thousands of distinct candidate scores (more than the 32 score classes and, at size, more than
