@@ -10,18 +10,24 @@
 //                   candidate keys (score, row) in descending order, and a bound: no row outside the list has a
 //                   larger key than that.  (Every thread keeps its best few, the CTA merges them; what a thread or
 //                   the merge drops only raises the bound.)
-//   k_drain_commit  ONE CTA walks the chunk in pod order.  T = the rows touched inside the chunk so far (<= C).
-//                   For pod q, every row outside T still has its chunk-start key, so
+//   k_drain_commit  ONE CTA walks the chunk in pod order.  T = the rows the previous chunk changed (see below) +
+//                   the rows this chunk has changed so far (<= 2 C), their tile words in shared memory.  For pod q
+//                   every row outside T still has the key the matrix holds, so
 //                       winner(q) = max( best live key over T,  first candidate of q's list outside T )
-//                   provided that maximum reaches the list's bound; the live keys over T are evaluated now (thread =
-//                   touched row, from a copy of the row's tile words in shared memory).  Otherwise the list says
-//                   nothing about the rest of the snapshot and the CTA scans the whole walk copy for that pod (rare:
+//                   provided that maximum reaches the list's bound; the live keys over T are evaluated now (pair
+//                   pods: lane = (row, device); others: lane = row).  Otherwise the list says nothing about the rest
+//                   of the snapshot and the CTA scans the walk copy for the rows outside T (rare:
 //                   vgs_plan.drain_rescans).
-//                       fit_count(q) = chunk-start count - #{T rows fitting at chunk start} + #{T rows fitting now},
+//                       fit_count(q) = matrix count - #{T rows fitting in the matrix} + #{T rows fitting now},
 //                   the middle term read from the matrix when the chunk is done.
-//                   The winner is resolved by one warp from the raw planes (picks), folded into them, and its row
-//                   prepared again -- in the walk copy and in the shared-memory copy.
-// Every result equals what the per-pod chain (score kernel over all nodes per pod) produces.
+//                   The winner is committed by warp 0: a pair pod straight from the row's tile words (picks, usage
+//                   into the raw planes, the row's words after the take, re-ranked as K0 would); other pods by the
+//                   warp resolve from the raw planes + the warp preparation.  The walk copy is NOT written: the rows
+//                   the chunk changed leave in a carry block,
+//   k_drain_apply   which this kernel stores into the walk copy.
+// Two streams: the pass (eval + select) of chunk k+1 runs while chunk k is placed, over a walk copy that holds the
+// chunks up to k-1 -- which is why the rows chunk k changed are carried into T of chunk k+1 (vgs_capi.cu queues it).
+// Every result equals what the per-pod chain (one score kernel over all nodes per pod) produces.
 #include <cuda_runtime.h>
 #include <stdint.h>
 
