@@ -119,6 +119,18 @@ KATS = [
         [[(1, 0, 0, 0, "MLU"), (1, 1000, U, 0, "NVIDIA")]], {}, True, "0x40e00000", [[(7, 0, 0), (3, 1000, 0)]],
         cite="MLU request takes slot 7 (Used 1 -> sorts first); the NVIDIA request walks 6, 5, 4 (type mismatch, "
              "score.go:73) and takes slot 3. 20/20 + 6"),
+    kat("31_three_device_node", [dict(Used=u, Count=4, Usedmem=0, Totalmem=16000, Usedcores=0, Totalcore=100, Numa=0, Type=V100)
+                                 for u in (1, 3, 0)], [[(2, 1000, U, 0)]], {}, True, "0x40092492", [[(2, 1000, 0), (0, 1000, 0)]],
+        cite="len(Devices) = 3. Count-Used = 3, 1, 4 -> ascending order slots 1, 0, 2 (score.go:45-50); the walk from the "
+             "end (:92) takes slot 2 (total 4, free 4) and slot 0 (total 8, free 7): 8/7 + (3 - 2)"),
+    kat("32_second_container_finds_nothing", node(Count=[10] * 7 + [1], Used=[10] * 7 + [0]),
+        [[(1, 1000, U, 0)], [(1, 1000, U, 0)]], {}, False,
+        cite="slots 0-6 have Count <= Used (score.go:107); container 0 takes the one share of slot 7 (:168-174), container "
+             "1 finds no device (:175-177) -> the node is no candidate (:200-206)"),
+    kat("33_percentage_truncates", node(Totalmem=1001, Usedmem=[672, 672, 671, 672, 672, 672, 672, 672]),
+        [[(1, 0, 33, 0)]], {}, True, "0x41000000", [[(2, 330, 0)]],
+        cite="score.go:119: 1001 * 33 / 100 = 330 in integers; free memory is 329 everywhere but on slot 2 (330): the walk "
+             "passes slots 7..3 (:121) and takes slot 2. 10/10 + 7"),
 ]
 
 # string-policy truth table (nvidia/device.go:62-105), each line derived by hand
