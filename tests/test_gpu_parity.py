@@ -1035,6 +1035,30 @@ def test_drain_hand_derived_sequence(built, chunk):
     assert np.array_equal(after, end)
 
 
+@pytest.mark.parametrize("dmax,seed,n,p,chunk", [(8, 31, 260, 140, 0), (8, 32, 90, 200, 0), (12, 33, 400, 100, 0),
+                                                  (4, 34, 150, 130, 9), (1, 35, 500, 70, 0), (7, 36, 40, 96, 33),
+                                                  (8, 37, 3000, 160, 0)])
+def test_drain_random_ragged(built, dmax, seed, n, p, chunk):
+    """the chunked drain on random ragged snapshots (odd Count / Used / Totalcore values, negative numa, 0..dmax devices)
+    with random multi-container pods (numa-bind, type filters, requests that cannot fit): few nodes, so rows are hit
+    again and again, lists run dry, carried rows are hit by the next chunk"""
+    rng = np.random.default_rng(seed)
+    snap = _random_snapshot(rng, n, dmax)
+    batch = _random_pods(rng, p, dmax)
+    rows, scores, counts, picks, planes = _oracle_drain(snap, batch)
+    with v.Context(max_nodes=n, max_devices=dmax, max_pods=p, max_reqs=batch.n_reqs, max_picks=int(batch.nums.sum()),
+                   tuning={"drain_chunk": chunk}) as ctx:
+        ctx.upload(snap)
+        got = ctx.drain(batch)
+        after, _ = ctx.download_snapshot()
+        assert ctx.plan().drain_chunks > 0
+    assert np.array_equal(got.best_row, rows)
+    assert np.array_equal(got.score.view(np.uint32), scores.view(np.uint32))
+    assert np.array_equal(got.fit_count, counts)
+    assert np.array_equal(got.picks, picks)
+    assert np.array_equal(after, planes)
+
+
 def test_drain_candidate_list_runs_dry(built):
     """identical pods on nodes that take exactly one of them: inside a chunk every candidate of a pod's list is
     consumed by the pods before it, and no touched row fits any more -- the commit kernel has to scan the walk
