@@ -1059,6 +1059,31 @@ def test_drain_random_ragged(built, dmax, seed, n, p, chunk):
     assert np.array_equal(after, planes)
 
 
+@pytest.mark.parametrize("seed,n,d,p", [(2050, 2500, 2, 190), (2051, 200, 4, 199), (2055, 700, 4, 142)])
+def test_drain_tight_cluster_rescans(built, seed, n, d, p):
+    """nodes that take one or two pods each, pods that differ little: rows fill up quickly, the candidate lists run dry
+    chunk after chunk (dozens of re-scans, over rows carried in from the chunk before) -- still sequential Filters"""
+    rng = np.random.default_rng(seed)
+    planes = np.zeros((8, n, d), np.int32)
+    planes[1] = rng.integers(1, 3, (n, d))
+    planes[0] = np.where(rng.random((n, d)) < 0.8, planes[1], planes[1] - 1)
+    planes[3], planes[5] = 16000, 100
+    planes[2] = 1000 * planes[0]
+    planes[6] = rng.integers(0, 2, (n, d))
+    snap = v.Snapshot(planes, np.full(n, d, np.int32), ["NVIDIA-A100"])
+    batch = v.PodBatch.from_pods([{"containers": [[(int(rng.choice([1, 1, 1, 2])), int(rng.choice([500, 1000])), 101,
+                                                    int(rng.choice([0, 10])), "NVIDIA")]]} for _ in range(p)])
+    rows, scores, counts, picks, want_planes = _oracle_drain(snap, batch)
+    with v.Context(max_nodes=n, max_devices=d, max_pods=p, max_reqs=batch.n_reqs, max_picks=int(batch.nums.sum())) as ctx:
+        ctx.upload(snap)
+        got = ctx.drain(batch)
+        after, _ = ctx.download_snapshot()
+        assert ctx.plan().drain_rescans > 20
+    assert np.array_equal(got.best_row, rows) and np.array_equal(got.fit_count, counts)
+    assert np.array_equal(got.score.view(np.uint32), scores.view(np.uint32)) and np.array_equal(got.picks, picks)
+    assert np.array_equal(after, want_planes)
+
+
 def test_drain_candidate_list_runs_dry(built):
     """identical pods on nodes that take exactly one of them: inside a chunk every candidate of a pod's list is
     consumed by the pods before it, and no touched row fits any more -- the commit kernel has to scan the walk
