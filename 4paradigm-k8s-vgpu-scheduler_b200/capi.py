@@ -64,7 +64,7 @@ class VgsClassPlan(C.Structure):
 
 class VgsPlan(C.Structure):
     _fields_ = [("cls", VgsClassPlan * 4), ("dict_full", C.c_int32), ("drain_chunks", C.c_int32),
-                ("drain_rescans", C.c_int32), ("reserved", C.c_int32 * 1)]
+                ("drain_rescans", C.c_int32), ("drain_chain_pods", C.c_int32)]
 
 
 KERNEL_NONE, KERNEL_PAIR, KERNEL_SLICED, KERNEL_GENERAL = range(4)

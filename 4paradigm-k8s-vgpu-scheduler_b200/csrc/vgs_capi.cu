@@ -445,8 +445,8 @@ int vgs_init(const vgs_config *cfg, vgs_ctx **out) {
     CUI(cudaMalloc(&c->d_segcount, (size_t)kDrainChunk * kDrainMaxSegs * sizeof(int32_t)));
     CUI(cudaMalloc(&c->d_seldone, kDrainChunk * sizeof(unsigned int)));
     CUI(cudaMemset(c->d_seldone, 0, kDrainChunk * sizeof(unsigned int)));
-    CUI(cudaMalloc(&c->d_drain_stats, 8 * sizeof(int32_t)));
-    CUI(cudaMallocHost(&c->h_drain_stats, 8 * sizeof(int32_t)));
+    CUI(cudaMalloc(&c->d_drain_stats, 12 * sizeof(int32_t)));
+    CUI(cudaMallocHost(&c->h_drain_stats, 12 * sizeof(int32_t)));
 #undef CUI
     *out = c;
     return VGS_OK;
@@ -1255,7 +1255,8 @@ int vgs_drain_batch(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_r
     bool chunked = chunk > 0 && n_pods >= 32 && c->n_tiles > 0;
     for (int32_t p = 0; p < n_pods && chunked; p++)
         if (reinterpret_cast<const GenPod *>(c->h_stage + c->off_genall)[p].flags & G_LEGACY) chunked = false;
-    c->plan.drain_chunks = 0, c->plan.drain_rescans = 0;
+    c->plan.drain_chunks = 0, c->plan.drain_rescans = 0, c->plan.drain_chain_pods = 0;
+    int32_t p_first = 0; // first pod of the per-pod chain (after chunks that gave up)
     if (chunked && !c->d_drain_ob[0]) { // 2 x 4 bytes per (pod of a chunk, node): 51 MB at 100k nodes
         const size_t max_tiles = ((size_t)c->cfg.max_nodes + kWarp - 1) / kWarp;
         for (int k = 0; k < 2 && chunked; k++)
@@ -1273,7 +1274,13 @@ int vgs_drain_batch(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_r
         // (score-bit matrix, candidate lists) -- one chunk stale, which the commit kernel of chunk k+1 makes up for
         // by starting from the rows chunk k changed.
         cudaStream_t ps = c->side[0];
-        CU(cudaMemsetAsync(c->d_drain_stats, 0, 8 * sizeof(int32_t), c->st));
+        CU(cudaMemsetAsync(c->d_drain_stats, 0, 12 * sizeof(int32_t), c->st));
+        CU(cudaMemsetAsync(c->d_seldone, 0, kDrainChunk * sizeof(unsigned int), c->st)); // (a drain that gave up may leave counts)
+        // re-scans a chunk may spend before the drain gives the chunks up: about what its pods would cost pod by pod
+        // (~11 us each) over what one re-scan costs (~0.064 us per tile: 0.2 ms at 100k nodes)
+        int32_t max_rescans = c->n_tiles > 0 ? (int32_t)(11000 / c->n_tiles) : kDrainChunk;
+        if (max_rescans > kDrainChunk) max_rescans = kDrainChunk;
+        const int32_t *d_stop = c->d_drain_stats + 8;
         CU(cudaEventRecord(c->ev_fork, c->st));
         CU(cudaStreamWaitEvent(ps, c->ev_fork, 0));
         const int32_t n_chunks = (n_pods + chunk - 1) / chunk;
@@ -1290,6 +1297,7 @@ int vgs_drain_batch(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_r
             }
             dp.ob = c->d_drain_ob[k & 1], dp.topk = c->d_topk[k & 1], dp.counts = c->d_dcounts[k & 1];
             dp.seglist = c->d_seglist, dp.segcount = c->d_segcount, dp.done = c->d_seldone; // (passes run one after another)
+            dp.stop = c->d_drain_stats + 8;
             return dp;
         };
         CU(launch_drain_pass(c->dm, c->sms, pass_of(0), ps));
@@ -1298,7 +1306,8 @@ int vgs_drain_batch(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_r
             if (k + 1 < n_chunks) { // side: chunk k-1 into the walk copy (pass k has read it), then pass k+1
                 if (k > 0) {
                     CU(cudaStreamWaitEvent(ps, c->ev_commit[(k - 1) & 1], 0));
-                    CU(launch_drain_apply(c->dm, c->d_carry[(k - 1) & 1], c->d_carry_words[(k - 1) & 1], c->d_walk, ps));
+                    CU(launch_drain_apply(c->dm, c->d_carry[(k - 1) & 1], c->d_carry_words[(k - 1) & 1], c->d_walk,
+                                          (k - 1) * chunk, d_stop, ps));
                 }
                 CU(launch_drain_pass(c->dm, c->sms, pass_of(k + 1), ps));
                 CU(cudaEventRecord(c->ev_pass[(k + 1) & 1], ps));
@@ -1307,7 +1316,7 @@ int vgs_drain_batch(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_r
             const DrainPass dp = pass_of(k);
             CU(launch_drain_commit(c->dm, c->cfg.device, c->sms, raw_const(c), c->n_nodes, c->dmax, dp, dpick, k == 0,
                                    c->d_carry[(k + 1) & 1], c->d_carry_words[(k + 1) & 1], c->d_carry[k & 1],
-                                   c->d_carry_words[k & 1], c->d_results + (size_t)k * chunk, c->d_picks, c->d_status,
+                                   c->d_carry_words[k & 1], k * chunk, max_rescans, c->d_results + (size_t)k * chunk, c->d_picks, c->d_status,
                                    c->d_drain_stats, c->st));
             CU(cudaEventRecord(c->ev_commit[k & 1], c->st));
             c->launches += 4;
@@ -1315,9 +1324,18 @@ int vgs_drain_batch(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_r
         }
         // the last two chunks' rows (the side stream has applied the others)
         if (n_chunks > 1)
-            CU(launch_drain_apply(c->dm, c->d_carry[(n_chunks - 2) & 1], c->d_carry_words[(n_chunks - 2) & 1], c->d_walk, c->st));
-        CU(launch_drain_apply(c->dm, c->d_carry[(n_chunks - 1) & 1], c->d_carry_words[(n_chunks - 1) & 1], c->d_walk, c->st));
-        CU(cudaMemcpyAsync(c->h_drain_stats, c->d_drain_stats, 8 * sizeof(int32_t), cudaMemcpyDeviceToHost, c->st));
+            CU(launch_drain_apply(c->dm, c->d_carry[(n_chunks - 2) & 1], c->d_carry_words[(n_chunks - 2) & 1], c->d_walk,
+                                  (n_chunks - 2) * chunk, d_stop, c->st));
+        CU(launch_drain_apply(c->dm, c->d_carry[(n_chunks - 1) & 1], c->d_carry_words[(n_chunks - 1) & 1], c->d_walk,
+                              (n_chunks - 1) * chunk, d_stop, c->st));
+        CU(cudaMemcpyAsync(c->h_drain_stats, c->d_drain_stats, 12 * sizeof(int32_t), cudaMemcpyDeviceToHost, c->st));
+        // did the chunks give up (too many re-scans)?  Then the pods from there on take the per-pod chain below.
+        CU(cudaStreamSynchronize(c->st));
+        c->plan.drain_rescans = c->h_drain_stats[0];
+        if (c->h_drain_stats[8] != 0) p_first = c->h_drain_stats[8];
+        c->plan.drain_chain_pods = p_first ? n_pods - p_first : 0;
+    }
+    if (chunked && p_first == 0) {
         rec(c, EV_SC1);
         c->scored = true;
         c->resolved = true;
@@ -1325,14 +1343,13 @@ int vgs_drain_batch(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_r
         c->direct_out = false;
         c->version++;
         rc = download_locked(c, results, picks);
-        c->plan.drain_rescans = c->h_drain_stats[0];
 #ifdef VGS_DRAIN_TIMING // (a build for kernel work only: per-phase clock counts of the commit kernel, in units of 64 cycles)
         fprintf(stderr, "drain cycles/64: A %d B1 %d B2 %d B %d C %d D %d E %d\n", c->h_drain_stats[1], c->h_drain_stats[6],
                 c->h_drain_stats[7], c->h_drain_stats[2], c->h_drain_stats[3], c->h_drain_stats[4], c->h_drain_stats[5]);
 #endif
         return rc;
     }
-    for (int32_t p = 0; p < n_pods; p++) {
+    for (int32_t p = p_first; p < n_pods; p++) {
         const GenPod &gp = reinterpret_cast<const GenPod *>(c->h_stage + c->off_genall)[p];
         if (gp.n_reqs <= kFilterMaxReqs && !(gp.flags & G_LEGACY) && c->n_tiles > 0 && c->tune.filter_one_launch) {
             // one launch per pod: score, last CTA resolves, commits into the raw planes and re-prepares the row

@@ -83,7 +83,9 @@ constexpr int kScoreThreads = 256;
 template <int DM, bool WALK>
 __global__ void __launch_bounds__(kScoreThreads, WALK ? 2 : 3)
     k_drain_eval(const int4 *__restrict__ walk, int32_t n_tiles, const DevReq *__restrict__ reqs,
-                 const GenPod *__restrict__ pods, int32_t n_pods, int32_t psplit, uint32_t *__restrict__ ob) {
+                 const GenPod *__restrict__ pods, int32_t n_pods, int32_t psplit, uint32_t *__restrict__ ob,
+                 const int32_t *__restrict__ stop) {
+    if (*reinterpret_cast<const volatile int32_t *>(stop) != 0) return; // the commit kernels have given the chunks up (see there)
     __shared__ ChunkPods cp;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     constexpr int kWarps = kScoreThreads / 32;
@@ -134,7 +136,8 @@ constexpr int kListWords = kDrainListWords; // keys + bound
 __global__ void __launch_bounds__(kSelectThreads)
     k_drain_select(const uint32_t *__restrict__ ob, int32_t n_tiles, int32_t row_base, int32_t n_segs,
                    unsigned long long *__restrict__ seglist, int32_t *__restrict__ segcount, unsigned int *__restrict__ done,
-                   unsigned long long *__restrict__ topk, int32_t *__restrict__ counts) {
+                   unsigned long long *__restrict__ topk, int32_t *__restrict__ counts, const int32_t *__restrict__ stop) {
+    if (*reinterpret_cast<const volatile int32_t *>(stop) != 0) return;
     constexpr int kWarps = kSelectThreads / 32;
     __shared__ unsigned long long s_best[kWarps];
     __shared__ int32_t s_cnt[kWarps];
@@ -278,6 +281,12 @@ struct DrainChunk {
     vgs_pick *picks;     // the batch's
     uint32_t *status;
     int32_t *stats; // [0] += pods that needed the full scan
+    // Re-scans are what this scheme cannot afford on a big snapshot (one CTA over the whole walk copy: ~0.2 ms at 100k
+    // nodes).  Near-identical pods on nodes that take one or two of them exhaust each other's lists and need one per
+    // pod.  A chunk that would pass max_rescans stops there: *stop = the first pod not placed (0 = none so far; pod 0
+    // never re-scans), every later kernel of the drain returns at once, and the host places the rest pod by pod.
+    int32_t first_pod, max_rescans;
+    int32_t *stop;
 };
 
 constexpr int kDrainThreads = 512; // (with its registers, nothing of the concurrent pass fits beside it on the SM)
@@ -315,6 +324,11 @@ __global__ void __launch_bounds__(kDrainThreads) k_drain_commit(const __grid_con
     __shared__ __align__(16) int4 s_cand[2][2][kRow4];
     __shared__ int32_t s_cand_row[2][2]; // local rows, -1 = none
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    {
+        const int32_t st0 = *reinterpret_cast<volatile int32_t *>(a.stop);
+        if (st0 != 0 && st0 <= a.first_pod) return; // given up in an earlier chunk
+    }
+    int n_done = a.n_pods, n_rescans = 0;
     // (the last warp) start the copies for pod k into buffer k & 1; `skip` = global row that is about to enter T
     auto fetch_candidates = [&](int k, int skip) {
         const unsigned long long e = lane < kDrainTop ? s_list[k][lane] : 0ull;
@@ -522,7 +536,12 @@ __global__ void __launch_bounds__(kDrainThreads) k_drain_commit(const __grid_con
         }
         unsigned long long best = tkey > lkey ? tkey : lkey;
         int32_t fit_count = live, nt_at = nT;
+        if (best < bound && n_rescans >= a.max_rescans) { // CTA-uniform: stop here, the host goes on pod by pod
+            n_done = q;
+            break;
+        }
         if (best < bound) {
+            n_rescans++;
             // some row the list does not name had a larger key than anything in sight: scan the walk copy for the
             // rows outside T (T's rows are stale there; their live keys and count are in hand).  CTA-uniform branch.
             __syncthreads(); // s_w* are read above
@@ -710,7 +729,7 @@ __global__ void __launch_bounds__(kDrainThreads) k_drain_commit(const __grid_con
     {
         constexpr int kPer = kDrainThreads / kDrainChunk; // threads per pod
         const int k = tid / kPer, part = tid % kPer;
-        const int n = k < a.n_pods ? s_nt_at[k] : -1;
+        const int n = k < n_done ? s_nt_at[k] : -1;
         const uint32_t *mine = a.ob + (size_t)k * a.n_tiles * kWarp;
         int32_t was = 0;
         for (int s = part; s < n; s += kPer) was += mine[s_trow[s]] != 0u ? 1 : 0;
@@ -719,6 +738,8 @@ __global__ void __launch_bounds__(kDrainThreads) k_drain_commit(const __grid_con
         // (n < 0: the pod scanned -- it counted the rows outside T itself, and T live)
         if (part == 0 && n >= 0) a.results[k].fit_count += s_count0[k] - was;
     }
+    if (warp == kWarps - 1) asm volatile("cp.async.wait_all;" ::: "memory"); // (a fetch for a pod that was never reached)
+    if (n_done < a.n_pods && tid == 0) *a.stop = a.first_pod + n_done;
     // ---- the rows this chunk changed go on to k_drain_apply (walk copy) and to the next chunk (its T), W_SCORE1 put right
     __syncthreads();
     if (warp == 0) {
@@ -768,7 +789,12 @@ __global__ void __launch_bounds__(kDrainThreads) k_drain_commit(const __grid_con
 // the rows a chunk changed, into the walk copy (after the pass that was reading it has finished)
 template <int DM>
 __global__ void __launch_bounds__(256) k_drain_apply(const DrainCarry *__restrict__ carry, const int4 *__restrict__ words,
-                                                     int4 *__restrict__ walk) {
+                                                     int4 *__restrict__ walk, int32_t first_pod,
+                                                     const int32_t *__restrict__ stop) {
+    {
+        const int32_t st0 = *reinterpret_cast<const volatile int32_t *>(stop);
+        if (st0 != 0 && st0 <= first_pod) return; // that chunk was never placed: its carry block is an older chunk's
+    }
     constexpr int kTile4 = kWalkWords * (DM / 4) * kWarp, kRow4 = kWalkWords * (DM / 4);
     const int n = carry->n;
     for (int i = threadIdx.x; i < n * kRow4; i += blockDim.x) {
@@ -798,7 +824,7 @@ static cudaError_t drain_eval_launch(int sms, const DrainPass &p, cudaStream_t s
     long long grid = (items + kScoreThreads / 32 - 1) / (kScoreThreads / 32);
     if (grid > ctas) grid = ctas;
     if (grid < 1) grid = 1;
-    k_drain_eval<DM, WALK><<<(int)grid, kScoreThreads, 0, st>>>(p.walk, p.n_tiles, p.reqs, p.pods, p.n_pods, psplit, p.ob);
+    k_drain_eval<DM, WALK><<<(int)grid, kScoreThreads, 0, st>>>(p.walk, p.n_tiles, p.reqs, p.pods, p.n_pods, psplit, p.ob, p.stop);
     return cudaGetLastError();
 }
 
@@ -809,7 +835,7 @@ static cudaError_t drain_eval_t(int sms, const DrainPass &p, cudaStream_t st) {
     if (p.any_walk && (e = drain_eval_launch<DM, true>(sms, p, st)) != cudaSuccess) return e;
     const int segs = drain_segs(sms, p.n_pods, p.n_tiles);
     k_drain_select<<<dim3(segs, p.n_pods), kSelectThreads, 0, st>>>(p.ob, p.n_tiles, p.row_base, segs, p.seglist, p.segcount,
-                                                                     p.done, p.topk, p.counts);
+                                                                     p.done, p.topk, p.counts, p.stop);
     return cudaGetLastError();
 }
 
@@ -833,7 +859,8 @@ static cudaError_t drain_commit_t(int dev, const DrainChunk &c, cudaStream_t st)
 
 cudaError_t launch_drain_commit(int dm, int dev, int sms, const RawPlanes &raw, int32_t n_nodes, int32_t dmax,
                                 const DrainPass &p, const int32_t *pick_begin, bool first, const void *carry_in,
-                                const int4 *words_in, void *carry_out, int4 *words_out, vgs_result *results, vgs_pick *picks, uint32_t *status, int32_t *stats, cudaStream_t st) {
+                                const int4 *words_in, void *carry_out, int4 *words_out, int32_t first_pod,
+                                int32_t max_rescans, vgs_result *results, vgs_pick *picks, uint32_t *status, int32_t *stats, cudaStream_t st) {
     if (p.n_pods <= 0 || p.n_pods > kDrainChunk || p.n_tiles <= 0) return cudaErrorInvalidValue;
     DrainChunk c;
     c.walk = p.walk, c.n_tiles = p.n_tiles, c.n_nodes = n_nodes, c.row_base = p.row_base, c.dmax = dmax;
@@ -844,12 +871,14 @@ cudaError_t launch_drain_commit(int dm, int dev, int sms, const RawPlanes &raw, 
     c.carry_in = static_cast<const DrainCarry *>(carry_in), c.words_in = words_in;
     c.carry_out = static_cast<DrainCarry *>(carry_out), c.words_out = words_out;
     c.results = results, c.picks = picks, c.status = status, c.stats = stats;
+    c.first_pod = first_pod, c.max_rescans = max_rescans, c.stop = p.stop;
     return dm == 8 ? drain_commit_t<8>(dev, c, st) : drain_commit_t<12>(dev, c, st);
 }
 
-cudaError_t launch_drain_apply(int dm, const void *carry, const int4 *carry_words, int4 *walk, cudaStream_t st) {
-    if (dm == 8) k_drain_apply<8><<<1, 256, 0, st>>>(static_cast<const DrainCarry *>(carry), carry_words, walk);
-    else k_drain_apply<12><<<1, 256, 0, st>>>(static_cast<const DrainCarry *>(carry), carry_words, walk);
+cudaError_t launch_drain_apply(int dm, const void *carry, const int4 *carry_words, int4 *walk, int32_t first_pod,
+                               const int32_t *stop, cudaStream_t st) {
+    if (dm == 8) k_drain_apply<8><<<1, 256, 0, st>>>(static_cast<const DrainCarry *>(carry), carry_words, walk, first_pod, stop);
+    else k_drain_apply<12><<<1, 256, 0, st>>>(static_cast<const DrainCarry *>(carry), carry_words, walk, first_pod, stop);
     return cudaGetLastError();
 }
 

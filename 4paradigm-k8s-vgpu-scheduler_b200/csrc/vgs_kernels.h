@@ -86,12 +86,15 @@ struct DrainPass {
     unsigned int *done;          // [kDrainChunk], zero at rest
     unsigned long long *topk;    // [pod][kDrainListWords]
     int32_t *counts;             // [pod]
+    int32_t *stop;               // one word, 0 at the start of a drain: first pod the chunks gave up on (vgs_drain.cu)
 };
 cudaError_t launch_drain_pass(int dm, int sms, const DrainPass &p, cudaStream_t st);
 cudaError_t launch_drain_commit(int dm, int dev, int sms, const RawPlanes &raw, int32_t n_nodes, int32_t dmax,
                                 const DrainPass &p, const int32_t *pick_begin, bool first, const void *carry_in,
-                                const int4 *words_in, void *carry_out, int4 *words_out, vgs_result *results, vgs_pick *picks, uint32_t *status, int32_t *stats, cudaStream_t st);
-cudaError_t launch_drain_apply(int dm, const void *carry, const int4 *carry_words, int4 *walk, cudaStream_t st);
+                                const int4 *words_in, void *carry_out, int4 *words_out, int32_t first_pod,
+                                int32_t max_rescans, vgs_result *results, vgs_pick *picks, uint32_t *status, int32_t *stats, cudaStream_t st);
+cudaError_t launch_drain_apply(int dm, const void *carry, const int4 *carry_words, int4 *walk, int32_t first_pod,
+                               const int32_t *stop, cudaStream_t st);
 size_t drain_carry_bytes();
 // launch geometry of a thread-per-node score kernel (persistent grid over (tile group, pod chunk) items)
 cudaError_t plan_score_launch(const void *kernel, int dev, int32_t n_tiles, int32_t n_pods, int max_warps,

@@ -397,7 +397,8 @@ typedef struct {
                                * vgs_init: results stay exact (such scores are compared one by one), pruning is lost */
     int32_t drain_chunks;     /* the most recent vgs_drain_batch: chunks it ran as (0 = the per-pod chain) */
     int32_t drain_rescans;    /* ... and pods whose candidate list ran dry (a whole-snapshot scan inside the chunk) */
-    int32_t reserved[1];
+    int32_t drain_chain_pods; /* ... and pods placed by the per-pod chain after the chunks gave up (re-scans on a big snapshot
+                               * cost more than that chain: near-identical pods on nodes that take one or two of them) */
 } vgs_plan;
 int vgs_last_plan(vgs_ctx *ctx, vgs_plan *out);
 

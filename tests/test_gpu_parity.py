@@ -1084,6 +1084,35 @@ def test_drain_tight_cluster_rescans(built, seed, n, d, p):
     assert np.array_equal(after, want_planes)
 
 
+def test_drain_gives_the_chunks_up_when_rescans_pile_up(built):
+    """a tight cluster at a size where a re-scan costs more than placing a pod the plain way (40k nodes: 8 re-scans
+    per chunk allowed): the chunked drain stops at the pod that would pass that, the rest goes pod by pod
+    (vgs_plan.drain_chain_pods) -- same answers as sequential Filters throughout"""
+    rng = np.random.default_rng(77)
+    n, d, p = 40_000, 2, 200
+    planes = np.zeros((8, n, d), np.int32)
+    planes[1] = rng.integers(1, 3, (n, d))
+    planes[0] = np.where(rng.random((n, d)) < 0.8, planes[1], planes[1] - 1)
+    planes[3], planes[5] = 16000, 100
+    planes[2] = 1000 * planes[0]
+    snap = v.Snapshot(planes, np.full(n, d, np.int32), ["NVIDIA-A100"])
+    batch = v.PodBatch.from_pods([{"containers": [[(int(rng.choice([1, 1, 1, 2])), int(rng.choice([500, 1000])), 101,
+                                                    int(rng.choice([0, 10])), "NVIDIA")]]} for _ in range(p)])
+    rows, scores, counts, picks, want_planes = _oracle_drain(snap, batch)
+    with v.Context(max_nodes=n, max_devices=d, max_pods=p, max_reqs=batch.n_reqs, max_picks=int(batch.nums.sum())) as ctx:
+        ctx.upload(snap)
+        got = ctx.drain(batch)
+        plan = ctx.plan()
+        after, _ = ctx.download_snapshot()
+        again = ctx.drain(batch)  # and a second drain on top of it starts in chunks again
+    assert 0 < plan.drain_chain_pods < p and plan.drain_rescans <= 8 * plan.drain_chunks
+    assert np.array_equal(got.best_row, rows) and np.array_equal(got.fit_count, counts)
+    assert np.array_equal(got.score.view(np.uint32), scores.view(np.uint32)) and np.array_equal(got.picks, picks)
+    assert np.array_equal(after, want_planes)
+    rows2, scores2, counts2, picks2, _ = _oracle_drain(v.Snapshot(want_planes, snap.ndev, snap.type_names), batch)
+    assert np.array_equal(again.best_row, rows2) and np.array_equal(again.fit_count, counts2) and np.array_equal(again.picks, picks2)
+
+
 def test_drain_candidate_list_runs_dry(built):
     """identical pods on nodes that take exactly one of them: inside a chunk every candidate of a pod's list is
     consumed by the pods before it, and no touched row fits any more -- the commit kernel has to scan the walk
