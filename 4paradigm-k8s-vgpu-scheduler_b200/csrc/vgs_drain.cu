@@ -549,7 +549,13 @@ __global__ void __launch_bounds__(kDrainThreads) k_drain_commit(const __grid_con
             __syncthreads();
             for (int s = tid; s < nT; s += kDrainThreads) atomicOr(&s_filter[((s_trow[s] / kWarp) & 1023) >> 5], 1u << ((s_trow[s] / kWarp) & 31));
             __syncthreads();
-            unsigned long long sk = 0ull;
+            // The scan does not only name the winner: it leaves this pod a fresh candidate list (the kDrainTop best rows
+            // outside T and the bound behind them, selected as k_drain_select does), and the pods after it in the chunk
+            // that ask for exactly the same inherit it -- replicas use up each other's candidates, one scan serves the
+            // next kDrainTop of them.  (Outside T a row's key is the same for every pod with that request.)
+            unsigned long long t4[kSelectMine], dropped = 0ull;
+#pragma unroll
+            for (int i = 0; i < kSelectMine; i++) t4[i] = 0ull;
             int32_t sc = 0;
             for (int tile = warp; tile < a.n_tiles; tile += kWarps) {
                 bool alive;
@@ -560,20 +566,52 @@ __global__ void __launch_bounds__(kDrainThreads) k_drain_commit(const __grid_con
                     for (int s = 0; s < nT; s++) alive = alive && s_trow[s] != r;
                 }
                 if (alive) {
-                    const unsigned long long v = key_of(score, (uint32_t)(a.row_base + tile * kWarp + lane));
-                    sk = v > sk ? v : sk;
+                    unsigned long long v = key_of(score, (uint32_t)(a.row_base + tile * kWarp + lane));
                     sc++;
+#pragma unroll
+                    for (int i = 0; i < kSelectMine; i++) {
+                        const unsigned long long hi = v > t4[i] ? v : t4[i];
+                        v = v > t4[i] ? t4[i] : v;
+                        t4[i] = hi;
+                    }
+                    dropped = v > dropped ? v : dropped;
                 }
             }
-            sk = warp_max64(sk);
             sc = __reduce_add_sync(0xffffffffu, sc);
-            if (lane == 0) s_wkey[warp] = sk, s_wcnt[warp] = sc;
-            __syncthreads();
-            best = tkey, nt_at = -1;
+            if (lane == 0) s_wcnt[warp] = sc;
+            unsigned long long scan_best = 0ull;
+            for (int r = 0; r <= kDrainTop; r++) { // kDrainTop rounds of "largest head of all threads", one for the bound
+                const unsigned long long mine_r = r < kDrainTop ? t4[0] : (t4[0] > dropped ? t4[0] : dropped);
+                const unsigned long long m = warp_max64(mine_r);
+                __syncthreads();
+                if (lane == 0) s_wkey[warp] = m;
+                __syncthreads();
+                unsigned long long top = 0ull;
 #pragma unroll
-            for (int w = 0; w < kWarps; w++) {
-                best = s_wkey[w] > best ? s_wkey[w] : best;
-                fit_count += s_wcnt[w];
+                for (int w = 0; w < kWarps; w++) top = s_wkey[w] > top ? s_wkey[w] : top;
+                if (r == 0) scan_best = top;
+                if (tid == 0) {
+                    if (r < kDrainTop) s_list[q][r] = top;
+                    else s_bound[q] = top;
+                }
+                if (r < kDrainTop && t4[0] == top && top != 0ull) {
+#pragma unroll
+                    for (int i = 0; i + 1 < kSelectMine; i++) t4[i] = t4[i + 1];
+                    t4[kSelectMine - 1] = 0ull;
+                }
+            }
+            best = tkey > scan_best ? tkey : scan_best, nt_at = -1;
+#pragma unroll
+            for (int w = 0; w < kWarps; w++) fit_count += s_wcnt[w];
+            __syncthreads(); // the new list and bound of pod q
+            for (int o = q + 1 + warp; o < a.n_pods; o += kWarps) { // warp per later pod: the same request?
+                const bool both = is_pair && ((cp.pair[o >> 5] >> (o & 31)) & 1u);
+                const uint32_t *x = reinterpret_cast<const uint32_t *>(&cp.first[q]), *y = reinterpret_cast<const uint32_t *>(&cp.first[o]);
+                const bool same = both && __all_sync(0xffffffffu, lane >= (int)(sizeof(DevReq) / 4) || x[lane] == y[lane]);
+                if (same) {
+                    if (lane < kDrainTop) s_list[o][lane] = s_list[q][lane];
+                    if (lane == 0) s_bound[o] = s_bound[q];
+                }
             }
             if (tid == 0) atomicAdd(&a.stats[0], 1);
         }

@@ -1078,7 +1078,7 @@ def test_drain_tight_cluster_rescans(built, seed, n, d, p):
         ctx.upload(snap)
         got = ctx.drain(batch)
         after, _ = ctx.download_snapshot()
-        assert ctx.plan().drain_rescans > 20
+        assert ctx.plan().drain_rescans >= 3  # (a re-scan refills the list of the pod and of its replicas: far fewer than pods)
     assert np.array_equal(got.best_row, rows) and np.array_equal(got.fit_count, counts)
     assert np.array_equal(got.score.view(np.uint32), scores.view(np.uint32)) and np.array_equal(got.picks, picks)
     assert np.array_equal(after, want_planes)
@@ -1111,6 +1111,25 @@ def test_drain_gives_the_chunks_up_when_rescans_pile_up(built):
     assert np.array_equal(after, want_planes)
     rows2, scores2, counts2, picks2, _ = _oracle_drain(v.Snapshot(want_planes, snap.ndev, snap.type_names), batch)
     assert np.array_equal(again.best_row, rows2) and np.array_equal(again.fit_count, counts2) and np.array_equal(again.picks, picks2)
+
+
+@pytest.mark.parametrize("req", [(1, 3000, 101, 30), (2, 8000, 101, 0), (1, 0, 50, 100)])
+def test_drain_replicas_share_the_refilled_list(built, req):
+    """300 identical pods (one Deployment's replicas) and a few others in between: the pods in front use up the
+    candidates all of them share; the re-scan that follows refills the list of its pod AND of the replicas behind it"""
+    snap, other = v.workload.make_config("cfg3", 20_000, 12)
+    pods = [{"containers": [[req + ("NVIDIA",)]]} for _ in range(300)]
+    batch = v.PodBatch.from_pods(pods)
+    rows, scores, counts, picks, want_planes = _oracle_drain(snap, batch)
+    with v.Context(max_nodes=snap.n_nodes, max_pods=300, max_reqs=batch.n_reqs, max_picks=int(batch.nums.sum())) as ctx:
+        ctx.upload(snap)
+        got = ctx.drain(batch)
+        plan = ctx.plan()
+        after, _ = ctx.download_snapshot()
+    assert plan.drain_chain_pods == 0 and 0 < plan.drain_rescans < 40
+    assert np.array_equal(got.best_row, rows) and np.array_equal(got.fit_count, counts)
+    assert np.array_equal(got.score.view(np.uint32), scores.view(np.uint32)) and np.array_equal(got.picks, picks)
+    assert np.array_equal(after, want_planes)
 
 
 def test_drain_candidate_list_runs_dry(built):
