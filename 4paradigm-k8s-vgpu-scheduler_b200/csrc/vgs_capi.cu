@@ -908,12 +908,14 @@ static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, i
         CU(cudaMemcpyAsync(c->d_stage, c->h_stage, stage_used, cudaMemcpyHostToDevice, sp));
         c->stage_in_flight = true;
     }
-    {
+    if (!want_all) {
         cudaError_t e;
         build_slice_class(c, 0, hA, reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqsA), hoA, nA, &e, sp);
         CU(e);
         build_slice_class(c, 1, hB, reinterpret_cast<const DevReq *>(c->d_stage + c->off_reqsB), hoB, nB, &e, sp);
         CU(e);
+    } else { // the drain scores with the pair / walk evaluations: no bit tables (and the batch is not kept for a score pass)
+        c->slice_on[0] = c->slice_on[1] = false;
     }
     if (c->pods_on_side) {
         cudaEventRecord(c->ev[EV_PH1], sp);
@@ -923,7 +925,7 @@ static int pods_upload_locked(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, i
     } else {
         rec(c, EV_PH1);
     }
-    c->have_pods = true;
+    c->have_pods = !want_all;
     return VGS_OK;
 }
 
@@ -1329,25 +1331,26 @@ int vgs_drain_batch(vgs_ctx *c, int32_t n_pods, const vgs_pod *pods, int32_t n_r
         CU(launch_drain_apply(c->dm, c->d_carry[(n_chunks - 1) & 1], c->d_carry_words[(n_chunks - 1) & 1], c->d_walk,
                               (n_chunks - 1) * chunk, d_stop, c->st));
         CU(cudaMemcpyAsync(c->h_drain_stats, c->d_drain_stats, 12 * sizeof(int32_t), cudaMemcpyDeviceToHost, c->st));
-        // did the chunks give up (too many re-scans)?  Then the pods from there on take the per-pod chain below.
-        CU(cudaStreamSynchronize(c->st));
-        c->plan.drain_rescans = c->h_drain_stats[0];
-        if (c->h_drain_stats[8] != 0) p_first = c->h_drain_stats[8];
-        c->plan.drain_chain_pods = p_first ? n_pods - p_first : 0;
-    }
-    if (chunked && p_first == 0) {
+        // results come down with the stop word: did the chunks give up (too many re-scans)?  Then the pods from there
+        // on take the per-pod chain below and the results are read again.
         rec(c, EV_SC1);
         c->scored = true;
         c->resolved = true;
         c->dirty_pods = 0;
         c->direct_out = false;
-        c->version++;
         rc = download_locked(c, results, picks);
+        c->plan.drain_rescans = c->h_drain_stats[0];
 #ifdef VGS_DRAIN_TIMING // (a build for kernel work only: per-phase clock counts of the commit kernel, in units of 64 cycles)
         fprintf(stderr, "drain cycles/64: A %d B1 %d B2 %d B %d C %d D %d E %d\n", c->h_drain_stats[1], c->h_drain_stats[6],
                 c->h_drain_stats[7], c->h_drain_stats[2], c->h_drain_stats[3], c->h_drain_stats[4], c->h_drain_stats[5]);
 #endif
-        return rc;
+        if (rc != VGS_OK) return rc;
+        if (c->h_drain_stats[8] == 0) {
+            c->version++;
+            return VGS_OK;
+        }
+        p_first = c->h_drain_stats[8];
+        c->plan.drain_chain_pods = n_pods - p_first;
     }
     for (int32_t p = p_first; p < n_pods; p++) {
         const GenPod &gp = reinterpret_cast<const GenPod *>(c->h_stage + c->off_genall)[p];

@@ -254,7 +254,8 @@ int vgs_score_batch(vgs_ctx *ctx, int32_t n_pods, const vgs_pod *pods, int32_t n
  * chunk's pods are scored against the whole snapshot once, then placed in order by one CTA that
  * re-evaluates only the rows touched inside the chunk (a commit changes one row); smaller
  * batches, and pods the walk kernel does not take (more than 100 devices asked for), score the
- * whole snapshot per pod.  Single shard only.  Same outputs as vgs_score_batch. */
+ * whole snapshot per pod.  Single shard only.  Same outputs as vgs_score_batch.  The batch does not
+ * stay resident for vgs_score_resident (upload it with vgs_pods_upload first). */
 int vgs_drain_batch(vgs_ctx *ctx, int32_t n_pods, const vgs_pod *pods, int32_t n_reqs,
                     const vgs_req *reqs, vgs_result *results, vgs_pick *picks);
 

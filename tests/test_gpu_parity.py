@@ -1159,6 +1159,24 @@ def test_drain_candidate_list_runs_dry(built):
     assert plan.drain_chunks == 2 and plan.drain_rescans > 0
 
 
+def test_drain_does_not_keep_the_batch_for_a_score_pass(built):
+    """the drain builds none of the score pass's class tables for its batch: vgs_score_resident after it is a sequence
+    error until the pods are uploaded again, and a score of the same batch afterwards sees the drained snapshot"""
+    snap, batch = v.workload.make_config("cfg3", 3000, 700)
+    rows, scores, counts, picks, after_want = _oracle_drain(snap, batch)
+    with v.Context(max_nodes=snap.n_nodes, max_devices=snap.dmax, max_pods=batch.n_pods, max_reqs=batch.n_reqs,
+                   max_picks=int(batch.nums.sum()), tuning={"slice_min_nodes": 0}) as ctx:
+        ctx.upload(snap)
+        got = ctx.drain(batch)
+        assert np.array_equal(got.best_row, rows) and np.array_equal(got.picks, picks)
+        with pytest.raises(v.VgsError) as e:
+            ctx.score_resident()
+        assert e.value.code == v.capi.VGS_ESTATE
+        res = ctx.score(batch)  # uploads the pods (with their tables) again
+    want = oracle.score_packed(v.Snapshot(after_want, snap.ndev, snap.type_names), batch, full=False)
+    assert_same(res, want, "score after drain")
+
+
 def test_empty_batch_and_concurrent_callers(built):
     """n_pods = 0 is a no-op; calls on one context from several host threads are serialised by the
     library (net/http runs each /filter in its own goroutine) and all get the right answer"""
