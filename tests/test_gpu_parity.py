@@ -1177,6 +1177,32 @@ def test_drain_does_not_keep_the_batch_for_a_score_pass(built):
     assert_same(res, want, "score after drain")
 
 
+def test_contexts_give_their_memory_back(built):
+    """vgs_destroy releases everything a context took -- the planes, the arena, the verify matrices, the drain's score
+    matrices (allocated at the first chunked drain): the device's free memory after 12 contexts that scored, drained
+    and were closed is where it was after the first one (which pays for the lazily loaded kernels)"""
+    import torch
+    snap, batch = v.workload.make_config("cfg3", 20_000, 700)
+
+    def cycle(verify):
+        with v.Context(max_nodes=snap.n_nodes, max_devices=snap.dmax, max_pods=batch.n_pods, max_reqs=batch.n_reqs,
+                       max_picks=int(batch.nums.sum()), verify=verify) as ctx:
+            ctx.upload(snap)
+            ctx.score(batch)
+            ctx.score(batch.select([3]))
+            ctx.drain(batch)
+            assert ctx.plan().drain_chunks > 0
+
+    cycle(True)
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info()
+    for i in range(12):
+        cycle(bool(i & 1))
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info()
+    assert free0 - free1 < (4 << 20), (free0, free1)  # one context of this size holds > 60 MB
+
+
 def test_empty_batch_and_concurrent_callers(built):
     """n_pods = 0 is a no-op; calls on one context from several host threads are serialised by the
     library (net/http runs each /filter in its own goroutine) and all get the right answer"""
