@@ -33,7 +33,7 @@ EXPORTS = (
     "vgs_results_download", "vgs_sync", "vgs_keys_device", "vgs_keys_merge", "vgs_results_device",
     "vgs_verify_download", "vgs_last_timing", "vgs_host_typemask", "vgs_host_numa_bind",
     "vgs_host_encode_pod_devices", "vgs_host_decode_node_devices", "vgs_score_batch_noalloc",
-    "vgs_tuning_defaults", "vgs_last_plan",
+    "vgs_tuning_defaults", "vgs_last_plan", "vgs_snapshot_upload_narrow",
     "vgs_group_init", "vgs_group_destroy", "vgs_group_last_error", "vgs_group_snapshot_upload",
     "vgs_group_snapshot_type_flags", "vgs_group_snapshot_delta", "vgs_group_score_batch", "vgs_group_last_timing",
 )
@@ -123,6 +123,7 @@ def load_library() -> C.CDLL:
     lib.vgs_snapshot_upload.argtypes = [vp, i32, i32, C.POINTER(vp), vp, u64p]
     lib.vgs_snapshot_set_device.argtypes = [vp, i32, i32, C.POINTER(vp), vp, u64p]
     lib.vgs_snapshot_upload_async.argtypes = [vp, i32, i32, C.POINTER(vp), vp, u64p]
+    lib.vgs_snapshot_upload_narrow.argtypes = [vp, i32, i32, C.POINTER(vp), vp, vp, i32, u64p]
     lib.vgs_snapshot_refresh.argtypes = [vp]
     lib.vgs_snapshot_type_flags.argtypes = [vp, i32, vp]
     lib.vgs_host_typemask_mlu.argtypes = [i32, C.c_char_p, C.c_char_p, C.POINTER(C.c_char_p), i32,
@@ -318,6 +319,17 @@ def score_batch_noalloc(device: int, stream: int, n_nodes: int, dmax: int, row_b
                                            C.c_void_p(picks_ptr)))
 
 
+def narrow_planes(snap: Snapshot) -> List[np.ndarray]:
+    """[8 planes, ndev] of a snapshot, each in the narrowest of int8 / int16 / int32 that holds its values -- what a
+    host packer filling the planes from the DeviceUsage structs would write for vgs_snapshot_upload_narrow"""
+    out = []
+    for a in [snap.planes[f] for f in range(8)] + [snap.ndev]:
+        lo, hi = (int(a.min()), int(a.max())) if a.size else (0, 0)
+        dt = np.int8 if -128 <= lo and hi <= 127 else (np.int16 if -32768 <= lo and hi <= 32767 else np.int32)
+        out.append(np.ascontiguousarray(a, dtype=dt))
+    return out
+
+
 class Context:
     """One GPU, one shard of the node set.  Thin, 1:1 over the C ABI."""
 
@@ -390,6 +402,28 @@ class Context:
         self._check(fn(self.h, n_nodes, dmax, ptrs, C.c_void_p(ndev_ptr), C.byref(ver)))
         self.n_nodes, self.dmax = n_nodes, dmax
         return ver.value
+
+    def upload_narrow_ptrs(self, n_nodes: int, dmax: int, plane_ptrs: List[int], ndev_ptr: int, widths,
+                           asynchronous: bool = False) -> int:
+        """vgs_snapshot_upload_narrow: planes of 1-, 2- or 4-byte elements (widths[0..7] for the planes, widths[8] for
+        ndev), host memory given as raw addresses"""
+        ptrs = (C.c_void_p * 8)(*plane_ptrs)
+        w = np.ascontiguousarray(widths, dtype=np.uint8)
+        assert len(w) == 9
+        ver = C.c_uint64()
+        self._check(self.lib.vgs_snapshot_upload_narrow(self.h, n_nodes, dmax, ptrs, C.c_void_p(ndev_ptr), w.ctypes.data,
+                                                        1 if asynchronous else 0, C.byref(ver)))
+        self.n_nodes, self.dmax = n_nodes, dmax
+        return ver.value
+
+    def upload_narrow(self, snap: Snapshot) -> int:
+        """the snapshot through the narrow wire format, every plane in the narrowest type its values fit"""
+        self.set_type_flags([host_type_flags(t) for t in snap.type_names])
+        arrs = narrow_planes(snap)
+        ver = self.upload_narrow_ptrs(snap.n_nodes, snap.dmax, [a.ctypes.data for a in arrs[:8]], arrs[8].ctypes.data,
+                                      [a.dtype.itemsize for a in arrs])
+        self.type_names = snap.type_names
+        return ver
 
     def refresh(self):
         self._check(self.lib.vgs_snapshot_refresh(self.h))

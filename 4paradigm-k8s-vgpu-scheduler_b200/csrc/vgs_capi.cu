@@ -56,6 +56,7 @@ struct vgs_ctx {
     int32_t *d_raw[VGS_NUM_PLANES] = {};
     int32_t *d_ndev = nullptr;
     int4 *d_walk = nullptr;
+    char *d_nstage = nullptr;     // narrow planes from pageable memory land here first (allocated at the first such upload)
     uint32_t *d_status = nullptr;
     uint32_t *h_status = nullptr; // pinned
     // the small arrays every score launch touches (request staging, bit tables of the two sliced classes, candidate
@@ -233,6 +234,7 @@ void free_all(vgs_ctx *c) {
     for (int f = 0; f < VGS_NUM_PLANES; f++) cudaFree(c->d_raw[f]);
     cudaFree(c->d_ndev);
     cudaFree(c->d_walk);
+    cudaFree(c->d_nstage);
     if (c->ev_snap) cudaEventDestroy(c->ev_snap);
     if (c->ev_delta) cudaEventDestroy(c->ev_delta);
     cudaFree(c->d_status);
@@ -462,10 +464,15 @@ void vgs_destroy(vgs_ctx *c) {
     delete c;
 }
 
+// widths != nullptr: the narrow wire format -- planes[f] / ndev hold elements of widths[f] / widths[VGS_NUM_PLANES]
+// bytes (host memory only)
 static int snapshot_common(vgs_ctx *c, int32_t n_nodes, int32_t dmax,
                            const int32_t *const planes[VGS_NUM_PLANES], const int32_t *ndev,
-                           cudaMemcpyKind kind, uint64_t *out_version, bool async = false) {
+                           cudaMemcpyKind kind, uint64_t *out_version, bool async = false,
+                           const uint8_t *widths = nullptr) {
     if (!planes || !ndev) return fail(c, VGS_EINVAL, "null planes");
+    for (int f = 0; widths && f <= VGS_NUM_PLANES; f++)
+        if (widths[f] != 1 && widths[f] != 2 && widths[f] != 4) return fail(c, VGS_EINVAL, "plane width must be 1, 2 or 4 bytes");
     if (n_nodes < 0 || dmax < 1) return fail(c, VGS_EINVAL, "bad snapshot shape");
     if (dmax > VGS_MAX_DEVICES) return fail(c, VGS_EDMAX, "dmax > VGS_MAX_DEVICES");
     if (n_nodes > c->cfg.max_nodes || dmax > c->cfg.max_devices)
@@ -494,7 +501,25 @@ static int snapshot_common(vgs_ctx *c, int32_t n_nodes, int32_t dmax,
                 zero_copy = false;
         }
         cudaGetLastError(); // cudaPointerGetAttributes on pageable memory may leave an error behind
-        if (zero_copy) {
+        if (widths) {
+            const void *src[VGS_NUM_PLANES + 1];
+            for (int f = 0; f <= VGS_NUM_PLANES; f++) src[f] = f < VGS_NUM_PLANES ? (const void *)planes[f] : (const void *)ndev;
+            if (!zero_copy) { // pageable or unaligned: the narrow bytes go to a staging block, the kernel widens from there
+                const size_t max_cells = (size_t)c->cfg.max_nodes * c->cfg.max_devices;
+                if (!c->d_nstage)
+                    CU(cudaMalloc(&c->d_nstage, (max_cells * VGS_NUM_PLANES + (size_t)c->cfg.max_nodes) * sizeof(int32_t) +
+                                                    16 * (VGS_NUM_PLANES + 1)));
+                size_t off = 0;
+                for (int f = 0; f <= VGS_NUM_PLANES; f++) {
+                    const size_t b = (f < VGS_NUM_PLANES ? cells : (size_t)n_nodes) * widths[f];
+                    CU(cudaMemcpyAsync(c->d_nstage + off, src[f], b, cudaMemcpyHostToDevice, c->st));
+                    src[f] = c->d_nstage + off;
+                    off += align_up(b, 16);
+                }
+            }
+            CU(launch_copy_planes_narrow(src, widths, c->d_raw, c->d_ndev, cells, (size_t)n_nodes, c->st));
+            c->launches++;
+        } else if (zero_copy) {
             CU(launch_copy_planes(planes, ndev, c->d_raw, c->d_ndev, cells, (size_t)n_nodes, c->st));
             c->launches++;
         } else {
@@ -542,6 +567,17 @@ int vgs_snapshot_upload_async(vgs_ctx *c, int32_t n_nodes, int32_t dmax,
     std::lock_guard<std::mutex> lk(c->mu);
     DeviceGuard g(c->cfg.device);
     return snapshot_common(c, n_nodes, dmax, planes, ndev, cudaMemcpyHostToDevice, out_version, true);
+}
+
+int vgs_snapshot_upload_narrow(vgs_ctx *c, int32_t n_nodes, int32_t dmax, const void *const planes[VGS_NUM_PLANES],
+                               const void *ndev, const uint8_t widths[VGS_NUM_PLANES + 1], int32_t asynchronous,
+                               uint64_t *out_version) {
+    if (!c) return VGS_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    DeviceGuard g(c->cfg.device);
+    if (!widths) return fail(c, VGS_EINVAL, "null widths");
+    return snapshot_common(c, n_nodes, dmax, reinterpret_cast<const int32_t *const *>(planes),
+                           static_cast<const int32_t *>(ndev), cudaMemcpyHostToDevice, out_version, asynchronous != 0, widths);
 }
 
 int vgs_snapshot_set_device(vgs_ctx *c, int32_t n_nodes, int32_t dmax,

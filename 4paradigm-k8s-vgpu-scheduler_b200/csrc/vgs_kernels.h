@@ -35,6 +35,11 @@ inline size_t walk_int4_per_tile(int dm) { return (size_t)kWalkWords * (dm / 4) 
 cudaError_t launch_copy_planes(const int32_t *const src[VGS_NUM_PLANES], const int32_t *src_ndev,
                                int32_t *const dst[VGS_NUM_PLANES], int32_t *dst_ndev, size_t cells, size_t n_nodes,
                                cudaStream_t st);
+// the same from the narrow wire format: src[f] / width[f] for the 8 planes and (index VGS_NUM_PLANES) ndev; elements of
+// 1, 2 or 4 bytes, signed; src in device-accessible memory (pinned host or device), 16-byte aligned
+cudaError_t launch_copy_planes_narrow(const void *const src[VGS_NUM_PLANES + 1], const uint8_t width[VGS_NUM_PLANES + 1],
+                                      int32_t *const dst[VGS_NUM_PLANES], int32_t *dst_ndev, size_t cells, size_t n_nodes,
+                                      cudaStream_t st);
 cudaError_t launch_prepare(int dm, const RawPlanes &raw, int32_t n_nodes, int32_t dmax, int4 *walk,
                            int32_t n_tiles, uint32_t *status, const int32_t *rowlist,
                            int32_t n_list, cudaStream_t st);

@@ -13,8 +13,10 @@ for N > 1 every rank holds its own 100k-node shard (weak scaling, N x 100k nodes
 `value`   : device-timed (CUDA events per step on the launching stream, max over ranks),
             inputs resident in HBM, L2 flushed between steps.
 `e2e`     : the same metric through the host-buffer C ABI calls the Go shim makes
-            (vgs_snapshot_upload_async + pods upload / score / resolve / download): pinned
-            host planes and request records in, results out, every step.
+            (snapshot upload, queued + pods upload / score / resolve / download): pinned
+            host planes and request records in, results out, every step.  The planes travel in the narrow
+            wire format (vgs_snapshot_upload_narrow: int8 where the values fit, widened on the GPU);
+            `e2e_int32_planes` is the same step with int32 planes, the figure of the earlier rounds.
 `e2e_delta`: the production shape of the same calls: snapshot resident, each step ships the usage deltas of
             the previous step's placements (vgs_snapshot_delta) + the pod batch.
 `roofline`: the score kernels (K1) against the measured HBM peak with the algorithmic bytes of SURVEY 8(d),
@@ -457,9 +459,33 @@ def main():
 
         n_e2e = max(5, min(args.steps, 30))
         sec = run_e2e(e2e_step, n_e2e)
-        e2e = {"value": P * n_total / sec, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+        e2e_int32 = {"value": P * n_total / sec, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+                     "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * sec, "steps": n_e2e,
+                     "api": "vgs_snapshot_upload_async + vgs_pods_upload/score/resolve/results_download (host buffers, "
+                            "int32 planes: the e2e figure of the earlier rounds)"}
+        # the same step with the snapshot in the narrow wire format (vgs_snapshot_upload_narrow): every plane in the
+        # narrowest integer type its values fit, widened on the GPU by the kernel that pulls it over PCIe
+        narrow = v.capi.narrow_planes(snap)
+        widths = [a.dtype.itemsize for a in narrow]
+        pin_narrow = [torch.from_numpy(a.reshape(-1)).pin_memory() for a in narrow]
+        nptrs = [t.data_ptr() for t in pin_narrow]
+
+        def e2e_step_narrow():
+            ctx.upload_narrow_ptrs(npg, D, nptrs[:8], nptrs[8], widths, asynchronous=True)
+            ctx.pods_upload(pods, reqs)
+            sc.step_resident(n_picks)
+            return ctx.results_download()
+
+        ra, rb = e2e_step(), e2e_step_narrow()
+        if not all(np.array_equal(x, y) for x, y in zip(ra, rb)):
+            print("bench: narrow-plane upload changed the results", file=sys.stderr)
+            sys.exit(3)
+        sec = run_e2e(e2e_step_narrow, n_e2e)
+        h2d_n = sum(a.nbytes for a in narrow) + pods.nbytes + reqs.nbytes
+        e2e = {"value": P * n_total / sec, "unit": UNIT, "h2d_bytes_per_step": int(h2d_n),
                "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * sec, "steps": n_e2e,
-               "api": "vgs_snapshot_upload_async + vgs_pods_upload/score/resolve/results_download (host buffers)"}
+               "api": "vgs_snapshot_upload_narrow (queued) + vgs_pods_upload/score/resolve/results_download (host buffers)",
+               "plane_bytes_per_element": widths, "results_equal_int32_upload": True}
         if numa is not None:
             e2e["host_numa_node"] = numa  # rank 0's; every rank runs on the cores next to its own GPU
 
@@ -738,6 +764,8 @@ def main():
         "device_evals_per_s": P * n_total * D / (ms_per_step * 1e-3),
         "check": check,
     }
+    if e2e:
+        line["e2e_int32_planes"] = e2e_int32
     if e2e_delta:
         line["e2e_delta"] = e2e_delta
     if configs:

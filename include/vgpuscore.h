@@ -221,6 +221,17 @@ int vgs_snapshot_upload(vgs_ctx *ctx, int32_t n_nodes, int32_t dmax,
 int vgs_snapshot_upload_async(vgs_ctx *ctx, int32_t n_nodes, int32_t dmax,
                               const int32_t *const planes[VGS_NUM_PLANES], const int32_t *ndev,
                               uint64_t *out_version);
+/* The same upload from planes in a NARROW wire format: plane f holds n_nodes * dmax elements of widths[f] bytes,
+ * ndev holds n_nodes elements of widths[VGS_NUM_PLANES] bytes; 1, 2 or 4 bytes each, signed two's complement,
+ * widened to int32 on the GPU by the kernel that reads them.  What the upload costs is the bytes that cross PCIe:
+ * the packer that fills the planes from []*util.DeviceUsage (pkg/util/types.go:105-117) picks, per plane, the
+ * narrowest type its values fit -- Used / Count / Usedcores / Totalcore / Numa / type id are bytes on any real
+ * cluster (split counts, core percentages <= 100, < 64 types), memory stays int32: 14 instead of 32 bytes per
+ * device.  asynchronous != 0: as vgs_snapshot_upload_async.  Pinned, 16-byte aligned planes are read straight
+ * over PCIe; anything else is copied to a device staging block first (allocated at the first such call). */
+int vgs_snapshot_upload_narrow(vgs_ctx *ctx, int32_t n_nodes, int32_t dmax, const void *const planes[VGS_NUM_PLANES],
+                               const void *ndev, const uint8_t widths[VGS_NUM_PLANES + 1], int32_t asynchronous,
+                               uint64_t *out_version);
 /* same, from planes that already live in this GPU's memory */
 int vgs_snapshot_set_device(vgs_ctx *ctx, int32_t n_nodes, int32_t dmax,
                             const int32_t *const dev_planes[VGS_NUM_PLANES],

@@ -1177,6 +1177,59 @@ def test_drain_does_not_keep_the_batch_for_a_score_pass(built):
     assert_same(res, want, "score after drain")
 
 
+@pytest.mark.parametrize("seed,n,dmax", [(1, 3000, 8), (2, 33, 7), (3, 1, 1), (4, 517, 12), (5, 64, 4), (6, 5000, 2)])
+def test_narrow_planes_upload_like_int32_planes(built, seed, n, dmax):
+    """vgs_snapshot_upload_narrow: planes of int8 / int16 / int32 elements (every plane in the narrowest type its values
+    fit: numa -1 and Totalcore 200 of the random snapshots exercise sign extension and the 2-byte path, odd sizes the
+    tails) leave exactly the device planes the int32 upload leaves, from pageable memory (staging copy) and from pinned
+    memory (read over PCIe by the widening kernel), synchronously and queued -- and score the same"""
+    import torch
+    rng = np.random.default_rng(900 + seed)
+    snap = _random_snapshot(rng, n, dmax)
+    if seed == 6:
+        snap.planes[0][7, 1] = 40_000  # Used beyond int16: that plane alone stays int32
+    batch = _random_pods(rng, 60, dmax)
+    want = oracle.score_packed(snap, batch)
+    arrs = v.capi.narrow_planes(snap)
+    widths = [a.dtype.itemsize for a in arrs]
+    assert min(widths) == 1 and (seed != 6 or widths[0] == 4)
+    with v.Context(max_nodes=n, max_devices=dmax, max_pods=batch.n_pods, max_reqs=batch.n_reqs,
+                   max_picks=int(batch.nums.sum())) as ctx:
+        ctx.upload_narrow(snap)  # pageable numpy arrays
+        planes, ndev = ctx.download_snapshot()
+        assert np.array_equal(planes, snap.planes) and np.array_equal(ndev, snap.ndev)
+        assert_same(ctx.score(batch), want, "narrow, pageable")
+        pinned = [torch.from_numpy(a.reshape(-1).copy()).pin_memory() for a in arrs]
+        for asynchronous in (False, True):
+            ctx.upload(v.Snapshot(np.zeros_like(snap.planes), np.zeros_like(snap.ndev), snap.type_names))  # wipe
+            ctx.upload_narrow_ptrs(n, dmax, [t.data_ptr() for t in pinned[:8]], pinned[8].data_ptr(), widths,
+                                   asynchronous=asynchronous)
+            planes, ndev = ctx.download_snapshot()
+            assert np.array_equal(planes, snap.planes) and np.array_equal(ndev, snap.ndev), asynchronous
+            assert_same(ctx.score(batch), want, f"narrow, pinned, async={asynchronous}")
+
+
+def test_narrow_upload_errors(built):
+    """a width other than 1, 2, 4 is VGS_EINVAL; a value out of range in a narrow plane is reported like in an int32 one
+    (queued upload: by the next call that needs the snapshot)"""
+    snap, batch = v.workload.make_config("cfg3", 200, 8)
+    arrs = v.capi.narrow_planes(snap)
+    widths = [a.dtype.itemsize for a in arrs]
+    with v.Context(max_nodes=200, max_devices=snap.dmax, max_pods=8) as ctx:
+        with pytest.raises(v.VgsError) as e:
+            ctx.upload_narrow_ptrs(200, snap.dmax, [a.ctypes.data for a in arrs[:8]], arrs[8].ctypes.data, [3] + widths[1:])
+        assert e.value.code == v.capi.VGS_EINVAL
+        bad = [a.copy() for a in arrs]
+        bad[8][5] = snap.dmax + 1  # len(node.Devices) beyond dmax
+        ctx.set_type_flags([v.capi.host_type_flags(t) for t in snap.type_names])
+        ctx.type_names = snap.type_names
+        ctx.upload_narrow_ptrs(200, snap.dmax, [a.ctypes.data for a in bad[:8]], bad[8].ctypes.data, widths, asynchronous=True)
+        with pytest.raises(v.VgsError):
+            ctx.score(batch)
+        ctx.upload_narrow(snap)
+        assert_same(ctx.score(batch), oracle.score_packed(snap, batch), "after the bad upload")
+
+
 def test_contexts_give_their_memory_back(built):
     """vgs_destroy releases everything a context took -- the planes, the arena, the verify matrices, the drain's score
     matrices (allocated at the first chunked drain): the device's free memory after 12 contexts that scored, drained
