@@ -406,12 +406,12 @@ class Context:
     def upload_narrow_ptrs(self, n_nodes: int, dmax: int, plane_ptrs: List[int], ndev_ptr: int, widths,
                            asynchronous: bool = False) -> int:
         """vgs_snapshot_upload_narrow: planes of 1-, 2- or 4-byte elements (widths[0..7] for the planes, widths[8] for
-        ndev), host memory given as raw addresses"""
+        ndev), host memory given as raw addresses; None leaves a plane as it is on the GPU (same shape resident)"""
         ptrs = (C.c_void_p * 8)(*plane_ptrs)
         w = np.ascontiguousarray(widths, dtype=np.uint8)
         assert len(w) == 9
         ver = C.c_uint64()
-        self._check(self.lib.vgs_snapshot_upload_narrow(self.h, n_nodes, dmax, ptrs, C.c_void_p(ndev_ptr), w.ctypes.data,
+        self._check(self.lib.vgs_snapshot_upload_narrow(self.h, n_nodes, dmax, ptrs, C.c_void_p(ndev_ptr or None), w.ctypes.data,
                                                         1 if asynchronous else 0, C.byref(ver)))
         self.n_nodes, self.dmax = n_nodes, dmax
         return ver.value

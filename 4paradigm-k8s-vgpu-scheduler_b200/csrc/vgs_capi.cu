@@ -470,15 +470,23 @@ static int snapshot_common(vgs_ctx *c, int32_t n_nodes, int32_t dmax,
                            const int32_t *const planes[VGS_NUM_PLANES], const int32_t *ndev,
                            cudaMemcpyKind kind, uint64_t *out_version, bool async = false,
                            const uint8_t *widths = nullptr) {
-    if (!planes || !ndev) return fail(c, VGS_EINVAL, "null planes");
+    if (!planes || (!ndev && !widths)) return fail(c, VGS_EINVAL, "null planes");
     for (int f = 0; widths && f <= VGS_NUM_PLANES; f++)
         if (widths[f] != 1 && widths[f] != 2 && widths[f] != 4) return fail(c, VGS_EINVAL, "plane width must be 1, 2 or 4 bytes");
+    bool partial = false; // narrow format: a null plane keeps what is resident
+    for (int f = 0; widths && f <= VGS_NUM_PLANES; f++) partial |= (f < VGS_NUM_PLANES ? (const void *)planes[f] : (const void *)ndev) == nullptr;
+    if (partial) {
+        int frc = finish_snapshot(c);
+        if (frc != VGS_OK) return frc;
+        if (!c->have_snapshot || n_nodes != c->n_nodes || dmax != c->dmax)
+            return fail(c, VGS_ESTATE, "planes left out need a resident snapshot of the same shape");
+    }
     if (n_nodes < 0 || dmax < 1) return fail(c, VGS_EINVAL, "bad snapshot shape");
     if (dmax > VGS_MAX_DEVICES) return fail(c, VGS_EDMAX, "dmax > VGS_MAX_DEVICES");
     if (n_nodes > c->cfg.max_nodes || dmax > c->cfg.max_devices)
         return fail(c, VGS_ETOOBIG, "snapshot larger than vgs_init capacity");
     for (int f = 0; f < VGS_NUM_PLANES; f++)
-        if (!planes[f]) return fail(c, VGS_EINVAL, "null plane");
+        if (!planes[f] && !partial) return fail(c, VGS_EINVAL, "null plane");
     if (c->snap_pending) { // superseded before anybody looked at it
         c->snap_pending = false;
         CU(cudaEventSynchronize(c->ev_snap));
@@ -496,6 +504,7 @@ static int snapshot_common(vgs_ctx *c, int32_t n_nodes, int32_t dmax,
         bool zero_copy = kind == cudaMemcpyHostToDevice && c->tune.zero_copy_upload != 0;
         for (int f = 0; f <= VGS_NUM_PLANES && zero_copy; f++) {
             const void *p = f < VGS_NUM_PLANES ? (const void *)planes[f] : (const void *)ndev;
+            if (!p) continue; // (left out)
             cudaPointerAttributes at;
             if (((uintptr_t)p & 15) || cudaPointerGetAttributes(&at, p) != cudaSuccess || at.type != cudaMemoryTypeHost)
                 zero_copy = false;
@@ -512,6 +521,7 @@ static int snapshot_common(vgs_ctx *c, int32_t n_nodes, int32_t dmax,
                 size_t off = 0;
                 for (int f = 0; f <= VGS_NUM_PLANES; f++) {
                     const size_t b = (f < VGS_NUM_PLANES ? cells : (size_t)n_nodes) * widths[f];
+                    if (!src[f]) continue;
                     CU(cudaMemcpyAsync(c->d_nstage + off, src[f], b, cudaMemcpyHostToDevice, c->st));
                     src[f] = c->d_nstage + off;
                     off += align_up(b, 16);

@@ -1537,8 +1537,8 @@ cudaError_t launch_copy_planes_narrow(const void *const src[VGS_NUM_PLANES + 1],
         if (((uintptr_t)src[f] | (uintptr_t)d) & 15) return cudaErrorMisalignedAddress;
         pc.src[f] = reinterpret_cast<const int4 *>(src[f]);
         pc.dst[f] = d;
-        pc.n16[f] = (int32_t)(n / (16 / w));
-        pc.tail[f] = (int32_t)(n % (16 / w));
+        pc.n16[f] = src[f] ? (int32_t)(n / (16 / w)) : 0; // (a plane left out: the resident one stays)
+        pc.tail[f] = src[f] ? (int32_t)(n % (16 / w)) : 0;
         pc.width[f] = w;
     }
     k_copy_planes_narrow<<<dim3(148 * 2, VGS_NUM_PLANES + 1), 256, 0, st>>>(pc);

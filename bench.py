@@ -488,6 +488,26 @@ def main():
                "plane_bytes_per_element": widths, "results_equal_int32_upload": True}
         if numa is not None:
             e2e["host_numa_node"] = numa  # rank 0's; every rank runs on the cores next to its own GPU
+        # ... and with the registration half of the snapshot (Count, Totalmem, Totalcore, Numa, type, len(Devices)) left
+        # resident: the upload of a Filter whose node registry has not changed -- Used / Usedmem / Usedcores only
+        uptrs = [nptrs[f] if f in (0, 2, 4) else None for f in range(8)]
+
+        def e2e_step_usage():
+            ctx.upload_narrow_ptrs(npg, D, uptrs, None, widths, asynchronous=True)
+            ctx.pods_upload(pods, reqs)
+            sc.step_resident(n_picks)
+            return ctx.results_download()
+
+        rc_ = e2e_step_usage()
+        if not all(np.array_equal(x, y) for x, y in zip(ra, rc_)):
+            print("bench: usage-plane upload changed the results", file=sys.stderr)
+            sys.exit(3)
+        sec = run_e2e(e2e_step_usage, n_e2e)
+        e2e_usage = {"value": P * n_total / sec, "unit": UNIT, "ms_per_step": 1e3 * sec, "steps": n_e2e,
+                     "h2d_bytes_per_step": int(sum(narrow[f].nbytes for f in (0, 2, 4)) + pods.nbytes + reqs.nbytes),
+                     "d2h_bytes_per_step": int(d2h), "results_equal_int32_upload": True,
+                     "api": "vgs_snapshot_upload_narrow with the usage planes only (Used, Usedmem, Usedcores; the "
+                            "registration planes stay resident) + pods upload / score / resolve / download"}
 
         # the production path (scheduler.go:280-297 folded into deltas): the snapshot stays resident, each step
         # ships the usage changes of the previous step's placements + the pod batch, and reads the results back
@@ -766,6 +786,7 @@ def main():
     }
     if e2e:
         line["e2e_int32_planes"] = e2e_int32
+        line["e2e_usage_planes"] = e2e_usage
     if e2e_delta:
         line["e2e_delta"] = e2e_delta
     if configs:

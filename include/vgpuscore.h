@@ -228,7 +228,11 @@ int vgs_snapshot_upload_async(vgs_ctx *ctx, int32_t n_nodes, int32_t dmax,
  * narrowest type its values fit -- Used / Count / Usedcores / Totalcore / Numa / type id are bytes on any real
  * cluster (split counts, core percentages <= 100, < 64 types), memory stays int32: 14 instead of 32 bytes per
  * device.  asynchronous != 0: as vgs_snapshot_upload_async.  Pinned, 16-byte aligned planes are read straight
- * over PCIe; anything else is copied to a device staging block first (allocated at the first such call). */
+ * over PCIe; anything else is copied to a device staging block first (allocated at the first such call).
+ * planes[f] == NULL (ndev == NULL) leaves that plane as it is on the GPU; it needs a resident snapshot of the same
+ * n_nodes and dmax (VGS_ESTATE otherwise).  That is the upload for a Filter whose node registry has not changed:
+ * Count / Totalmem / Totalcore / Numa / type come from the registration annotations (nodes.go:59-101), only Used /
+ * Usedmem / Usedcores are recomputed from the pod list (scheduler.go:280-297) -- 6 bytes per device on the wire. */
 int vgs_snapshot_upload_narrow(vgs_ctx *ctx, int32_t n_nodes, int32_t dmax, const void *const planes[VGS_NUM_PLANES],
                                const void *ndev, const uint8_t widths[VGS_NUM_PLANES + 1], int32_t asynchronous,
                                uint64_t *out_version);

@@ -1209,6 +1209,37 @@ def test_narrow_planes_upload_like_int32_planes(built, seed, n, dmax):
             assert_same(ctx.score(batch), want, f"narrow, pinned, async={asynchronous}")
 
 
+def test_narrow_upload_of_the_usage_planes_alone(built):
+    """planes left out (NULL) keep what is resident: a Filter whose node registry has not changed uploads Used / Usedmem /
+    Usedcores only (what getNodesUsage recomputes from the pod list, scheduler.go:280-297); without a resident snapshot
+    of the same shape that is a sequence error"""
+    rng = np.random.default_rng(4242)
+    snap = _random_snapshot(rng, 2100, 8)
+    batch = _random_pods(rng, 80, 8)
+    later = v.Snapshot(snap.planes.copy(), snap.ndev, snap.type_names)
+    later.planes[0] = np.minimum(snap.planes[1], snap.planes[0] + rng.integers(0, 2, snap.planes[0].shape))  # more in use
+    later.planes[2] = np.minimum(snap.planes[3], snap.planes[2] + 100 * (later.planes[0] - snap.planes[0]))
+    later.planes[4] = np.minimum(snap.planes[5], snap.planes[4] + 5 * (later.planes[0] - snap.planes[0]))
+    arrs = v.capi.narrow_planes(later)
+    widths = [a.dtype.itemsize for a in arrs]
+    usage = [arrs[f].ctypes.data if f in (0, 2, 4) else None for f in range(8)]
+    with v.Context(max_nodes=snap.n_nodes, max_devices=8, max_pods=batch.n_pods, max_reqs=batch.n_reqs,
+                   max_picks=int(batch.nums.sum())) as ctx:
+        with pytest.raises(v.VgsError) as e:
+            ctx.upload_narrow_ptrs(snap.n_nodes, 8, usage, None, widths)  # nothing resident
+        assert e.value.code == v.capi.VGS_ESTATE
+        ctx.upload(snap)
+        assert_same(ctx.score(batch), oracle.score_packed(snap, batch), "before")
+        for asynchronous in (False, True):
+            ctx.upload_narrow_ptrs(snap.n_nodes, 8, usage, None, widths, asynchronous=asynchronous)
+            planes, ndev = ctx.download_snapshot()
+            assert np.array_equal(planes, later.planes) and np.array_equal(ndev, snap.ndev)
+            assert_same(ctx.score(batch), oracle.score_packed(later, batch), "usage planes replaced")
+        with pytest.raises(v.VgsError) as e:
+            ctx.upload_narrow_ptrs(snap.n_nodes - 1, 8, usage, None, widths)  # another shape
+        assert e.value.code == v.capi.VGS_ESTATE
+
+
 def test_narrow_upload_errors(built):
     """a width other than 1, 2, 4 is VGS_EINVAL; a value out of range in a narrow plane is reported like in an int32 one
     (queued upload: by the next call that needs the snapshot)"""
