@@ -171,3 +171,23 @@ def test_header_is_plain_c99_and_links(built, tmp_path):
                            str(src), "-o", str(exe), "-L", libdir, "-lvgpuscore", f"-Wl,-rpath,{libdir}"])
     out = subprocess.check_output([str(exe)]).decode().split()
     assert int(out[0]) >= 1 and out[1:] == ["32", "16"]
+
+
+def test_narrow_planes_pick_the_narrowest_type():
+    """the packer side of vgs_snapshot_upload_narrow: every plane in the narrowest of int8 / int16 / int32 that holds
+    its values, values unchanged (the GPU sign-extends them back to the int32 planes)"""
+    planes = np.zeros((8, 5, 4), np.int32)
+    planes[0, 1, 2], planes[0, 0, 0] = 127, -128          # int8 to the edge
+    planes[1, 1, 1] = 128                                  # one past: int16
+    planes[2, 0, 3] = -32769                               # one past int16: int32
+    planes[3] = 183359                                     # memory in MB
+    planes[4, 2, 2] = 32767
+    planes[5, 4, 3] = -129
+    ndev = np.array([0, 4, 2, 4, 1], np.int32)
+    arrs = v.capi.narrow_planes(v.Snapshot(planes, ndev, ["NVIDIA-A100"]))
+    assert [a.dtype.itemsize for a in arrs] == [1, 2, 4, 4, 2, 2, 1, 1, 1]
+    for f in range(8):
+        assert np.array_equal(arrs[f].astype(np.int32), planes[f]) and arrs[f].flags["C_CONTIGUOUS"]
+    assert np.array_equal(arrs[8].astype(np.int32), ndev)
+    empty = v.capi.narrow_planes(v.Snapshot(np.zeros((8, 0, 4), np.int32), np.zeros(0, np.int32), ["x"]))
+    assert [a.dtype.itemsize for a in empty] == [1] * 9
