@@ -33,7 +33,7 @@ EXPORTS = (
     "vgs_results_download", "vgs_sync", "vgs_keys_device", "vgs_keys_merge", "vgs_results_device",
     "vgs_verify_download", "vgs_last_timing", "vgs_host_typemask", "vgs_host_numa_bind",
     "vgs_host_encode_pod_devices", "vgs_host_decode_node_devices", "vgs_score_batch_noalloc",
-    "vgs_tuning_defaults", "vgs_last_plan", "vgs_snapshot_upload_narrow",
+    "vgs_tuning_defaults", "vgs_last_plan", "vgs_snapshot_upload_narrow", "vgs_host_to_upper",
     "vgs_group_init", "vgs_group_destroy", "vgs_group_last_error", "vgs_group_snapshot_upload",
     "vgs_group_snapshot_type_flags", "vgs_group_snapshot_delta", "vgs_group_score_batch", "vgs_group_last_timing",
 )
@@ -129,6 +129,8 @@ def load_library() -> C.CDLL:
     lib.vgs_host_typemask_mlu.argtypes = [i32, C.c_char_p, C.c_char_p, C.POINTER(C.c_char_p), i32,
                                           C.POINTER(C.c_uint32)]
     lib.vgs_host_typemask_mlu.restype = C.c_uint64
+    lib.vgs_host_to_upper.argtypes = [C.c_char_p, C.c_char_p, i32]
+    lib.vgs_host_to_upper.restype = i32
     lib.vgs_host_type_flags.argtypes = [C.c_char_p]
     lib.vgs_host_type_flags.restype = C.c_uint32
     lib.vgs_snapshot_delta.argtypes = [vp, i32, vp]
@@ -192,6 +194,15 @@ def host_typemask_mlu(memreq: int, annos: Dict[str, str], type_names: List[str])
     m = lib.vgs_host_typemask_mlu(int(memreq), _b(annos.get(ANNO_MLU_USE)), _b(annos.get(ANNO_MLU_NOUSE)), arr,
                                   len(type_names), C.byref(fl))
     return int(m), int(fl.value)
+
+
+def host_to_upper(s: bytes) -> bytes:
+    """vgs_host_to_upper: Go 1.19 strings.ToUpper of a byte string (any bytes, NUL-free)"""
+    lib = load_library()
+    n = lib.vgs_host_to_upper(s, None, 0)
+    buf = C.create_string_buffer(n + 1)
+    lib.vgs_host_to_upper(s, buf, n + 1)
+    return buf.raw[:n]
 
 
 def host_type_flags(type_name: str) -> int:

@@ -7,7 +7,7 @@
 //
 // Mirrors: pkg/scheduler/score.go:71-84 (checkType), pkg/device/nvidia/device.go:62-94
 // (checkGPUtype), :96-105 (assertNuma), :107-112 (CheckType), pkg/util/util.go:110-126
-// (EncodeContainerDevices / EncodePodDevices).
+// (EncodeContainerDevices / EncodePodDevices); strings.ToUpper / strings.Map / unicode.ToUpper of Go 1.19.
 #include <algorithm>
 #include <cstdint>
 #include <string>
@@ -17,12 +17,94 @@
 
 namespace {
 
-// Go strings.ToUpper on ASCII; bytes >= 0x80 pass through unchanged (Go maps them by
-// Unicode case tables; device model strings are ASCII).
+// ---- Go 1.19 strings.ToUpper ---------------------------------------------------------------------------------
+// ASCII strings are folded byte by byte; anything else goes rune by rune through unicode.ToUpper = the SIMPLE
+// uppercase mapping of Unicode 13.0.0 (one rune to one rune: U+00DF stays, U+0131 and U+017F become ASCII I and S).
+// strings.Map decodes like a range loop, so every byte that is not part of a valid encoding becomes U+FFFD in the
+// result.  The table is generated (tools/make_upper_table.py).
+struct UpperRun {
+    uint32_t lo, hi;
+    int32_t stride, delta;
+};
+const UpperRun kUpperRuns[] = {
+#include "vgs_upper_table.inc"
+};
+constexpr uint32_t kRuneError = 0xFFFD;
+
+uint32_t rune_upper(uint32_t r) {
+    if (r < 0x80) return (r >= 'a' && r <= 'z') ? r - 32 : r;
+    const UpperRun *b = kUpperRuns, *e = kUpperRuns + sizeof kUpperRuns / sizeof kUpperRuns[0];
+    const UpperRun *it = std::upper_bound(b, e, r, [](uint32_t x, const UpperRun &u) { return x < u.lo; });
+    if (it == b) return r;
+    --it; // the last run that starts at or below r
+    if (r <= it->hi && (r - it->lo) % (uint32_t)it->stride == 0) return (uint32_t)((int32_t)r + it->delta);
+    return r;
+}
+
+// utf8.DecodeRuneInString: (rune, width); (U+FFFD, 1) for a byte that does not start a valid encoding (overlong forms,
+// surrogates, values above U+10FFFF and truncated sequences included)
+uint32_t decode_rune(const std::string &s, size_t i, size_t *width) {
+    const size_t n = s.size() - i;
+    auto at = [&](size_t k) { return (uint32_t)(unsigned char)s[i + k]; };
+    auto cont = [&](size_t k, uint32_t lo, uint32_t hi) { return k < n && at(k) >= lo && at(k) <= hi; };
+    const uint32_t b0 = at(0);
+    *width = 1;
+    if (b0 < 0x80) return b0;
+    if (b0 >= 0xC2 && b0 <= 0xDF) {
+        if (!cont(1, 0x80, 0xBF)) return kRuneError;
+        *width = 2;
+        return ((b0 & 0x1F) << 6) | (at(1) & 0x3F);
+    }
+    if (b0 >= 0xE0 && b0 <= 0xEF) {
+        const uint32_t lo = b0 == 0xE0 ? 0xA0 : 0x80, hi = b0 == 0xED ? 0x9F : 0xBF;
+        if (!cont(1, lo, hi) || !cont(2, 0x80, 0xBF)) return kRuneError;
+        *width = 3;
+        return ((b0 & 0x0F) << 12) | ((at(1) & 0x3F) << 6) | (at(2) & 0x3F);
+    }
+    if (b0 >= 0xF0 && b0 <= 0xF4) {
+        const uint32_t lo = b0 == 0xF0 ? 0x90 : 0x80, hi = b0 == 0xF4 ? 0x8F : 0xBF;
+        if (!cont(1, lo, hi) || !cont(2, 0x80, 0xBF) || !cont(3, 0x80, 0xBF)) return kRuneError;
+        *width = 4;
+        return ((b0 & 0x07) << 18) | ((at(1) & 0x3F) << 12) | ((at(2) & 0x3F) << 6) | (at(3) & 0x3F);
+    }
+    return kRuneError;
+}
+
+void append_rune(std::string &out, uint32_t r) {
+    if (r < 0x80) {
+        out.push_back((char)r);
+    } else if (r < 0x800) {
+        out.push_back((char)(0xC0 | (r >> 6)));
+        out.push_back((char)(0x80 | (r & 0x3F)));
+    } else if (r < 0x10000) {
+        out.push_back((char)(0xE0 | (r >> 12)));
+        out.push_back((char)(0x80 | ((r >> 6) & 0x3F)));
+        out.push_back((char)(0x80 | (r & 0x3F)));
+    } else {
+        out.push_back((char)(0xF0 | (r >> 18)));
+        out.push_back((char)(0x80 | ((r >> 12) & 0x3F)));
+        out.push_back((char)(0x80 | ((r >> 6) & 0x3F)));
+        out.push_back((char)(0x80 | (r & 0x3F)));
+    }
+}
+
 std::string upper(const std::string &s) {
-    std::string r(s);
-    for (char &ch : r)
-        if (ch >= 'a' && ch <= 'z') ch = (char)(ch - 'a' + 'A');
+    bool ascii = true;
+    for (char ch : s) ascii = ascii && (unsigned char)ch < 0x80;
+    std::string r;
+    if (ascii) {
+        r = s;
+        for (char &ch : r)
+            if (ch >= 'a' && ch <= 'z') ch = (char)(ch - 'a' + 'A');
+        return r;
+    }
+    r.reserve(s.size() + 4);
+    for (size_t i = 0; i < s.size();) {
+        size_t w;
+        const uint32_t c = decode_rune(s, i, &w);
+        append_rune(r, rune_upper(c));
+        i += w;
+    }
     return r;
 }
 
@@ -103,6 +185,17 @@ int32_t parse_int32_go(const std::string &t) {
 } // namespace
 
 extern "C" {
+
+int32_t vgs_host_to_upper(const char *s, char *out, int32_t cap) {
+    if (!s) return -1;
+    const std::string u = upper(std::string(s));
+    if (out && cap > 0) {
+        const size_t n = std::min(u.size(), (size_t)cap - 1);
+        std::copy(u.begin(), u.begin() + n, out);
+        out[n] = 0;
+    }
+    return (int32_t)u.size();
+}
 
 uint64_t vgs_host_typemask(const char *req_type, const char *use_gputype, const char *nouse_gputype,
                            const char *const *types, int32_t n_types) {

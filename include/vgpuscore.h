@@ -426,6 +426,11 @@ int vgs_last_plan(vgs_ctx *ctx, vgs_plan *out);
  * pass hygon.com/use-dcutype / nouse-dcutype).  Other request types: mask 0. */
 uint64_t vgs_host_typemask(const char *req_type, const char *use_gputype,
                            const char *nouse_gputype, const char *const *types, int32_t n_types);
+/* strings.ToUpper as Go 1.19 computes it (what checkGPUtype / checkDCUtype / checkMLUtype fold both sides of their
+ * substring test with, nvidia/device.go:66-86): ASCII byte by byte, anything else rune by rune through the simple
+ * uppercase mapping of Unicode 13.0.0, bytes outside a valid UTF-8 encoding replaced by U+FFFD.  Writes at most
+ * cap - 1 bytes + NUL into out (out may be NULL); returns the length of the whole result, -1 for a NULL string. */
+int32_t vgs_host_to_upper(const char *s, char *out, int32_t cap);
 /* the Cambricon vendor (cambricon/device.go:60-104; req_type "MLU", pass
  * cambricon.com/use-mlutype / nouse-mlutype): bit t = the card contains "MLU", survives
  * checkMLUtype, and is not ruled out by ":94-96 Memreq != 0 on a card that is not a 370".

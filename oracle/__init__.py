@@ -3,4 +3,4 @@
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
 legs may import this package.  PARITY UNPINNED (see oracle/score_ref.h).
 """
-from .ref import build, score_faithful, score_packed, typemask  # noqa: F401
+from .ref import build, score_faithful, score_packed, to_upper, typemask  # noqa: F401

@@ -52,7 +52,7 @@ class _PodsPacked(C.Structure):
 
 def build(force: bool = False) -> str:
     """compile the C restatement (building the checker is not using it)"""
-    src = [os.path.join(_HERE, f) for f in ("score_ref.c", "score_ref.h")]
+    src = [os.path.join(_HERE, f) for f in ("score_ref.c", "score_ref.h", "upper_table.inc")]
     if force or not os.path.exists(_SO) or any(os.path.getmtime(s) > os.path.getmtime(_SO) for s in src):
         subprocess.check_call(["make", "-C", _HERE, "-s"])
     return _SO
@@ -95,6 +95,17 @@ def _annos_struct(an):
     return _Annos(_b(an.get(ANNO_USE)), _b(an.get(ANNO_NOUSE)), _b(an.get(ANNO_NUMA)),
                   _b(an.get("hygon.com/use-dcutype")), _b(an.get("hygon.com/nouse-dcutype")),
                   _b(an.get("cambricon.com/use-mlutype")), _b(an.get("cambricon.com/nouse-mlutype")))
+
+
+def to_upper(s: bytes) -> bytes:
+    """strings.ToUpper as the restatement computes it (any NUL-free bytes)"""
+    lib = _load()
+    lib.ref_strings_to_upper.argtypes = [C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t]
+    lib.ref_strings_to_upper.restype = C.c_size_t
+    n = lib.ref_strings_to_upper(s, len(s), None, 0)
+    buf = C.create_string_buffer(n + 1)
+    lib.ref_strings_to_upper(s, len(s), buf, n + 1)
+    return buf.raw[:n]
 
 
 def typemask(annos: dict, req_type: str, type_names, memreq: int = 0) -> tuple:

@@ -18,6 +18,7 @@
 #ifndef VGPU_ORACLE_SCORE_REF_H
 #define VGPU_ORACLE_SCORE_REF_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -93,6 +94,8 @@ typedef struct {
 
 /* ---- string policy (pkg/device/nvidia/device.go:62-112, score.go:71-84) -- */
 int ref_strings_contains(const char *s, const char *sub);
+/* strings.ToUpper (Go 1.19, Unicode 13.0.0) of s[0..n) into out (cap bytes, NUL-terminated); returns the whole length */
+size_t ref_strings_to_upper(const char *s, size_t n, char *out, size_t cap);
 int ref_parse_bool(const char *s, int *ok);
 int ref_checkGPUtype(const ref_Annos *annos, const char *cardtype);
 int ref_assertNuma(const ref_Annos *annos);
