@@ -144,3 +144,20 @@ def test_type_policy_folds_like_go(built):
     for tok in ("ж", "Ж", "mlu370-ж"):
         an = {v.capi.ANNO_MLU_USE: tok}
         assert v.capi.host_typemask_mlu(0, an, mlu)[0] == oracle.typemask(an, "MLU", mlu)[0] == (0b11 if len(tok) <= 2 else 0b01), tok
+
+
+def test_committed_tables_are_what_the_generator_writes(tmp_path):
+    """csrc/vgs_upper_table.inc and oracle/upper_table.inc are generated files: byte for byte what
+    tools/make_upper_table.py writes from this interpreter's Unicode data, and equal to each other"""
+    import importlib.util
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("make_upper_table", os.path.join(root, "tools", "make_upper_table.py"))
+    gen = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(gen)
+    pairs = gen.table()
+    out = tmp_path / "t.inc"
+    gen.emit(str(out), gen.runs(pairs), len(pairs))
+    want = out.read_bytes()
+    for rel in ("4paradigm-k8s-vgpu-scheduler_b200/csrc/vgs_upper_table.inc", "oracle/upper_table.inc"):
+        assert open(os.path.join(root, rel), "rb").read() == want, rel
